@@ -1,0 +1,162 @@
+/* ivfhnsw_b200.h -- C ABI of the B200-native IVF-HNSW search + indexing path.
+ *
+ * This is the drop-in boundary.  The reference has no FFI
+ * layer: its boundary is the C++ API of ivfhnsw::IndexIVF_HNSW /
+ * IndexIVF_HNSW_Grouping.  The C++ shims in include/ivf-hnsw/ forward every hot
+ * method to one entry point below; the reference method each one replaces is
+ * cited next to it (paths relative to the reference root).
+ *
+ * Conventions: every function returns 0 on success and a negative value on
+ * failure (message via ivfhnsw_b200_last_error); nothing throws.  Pointers are
+ * HOST pointers unless the parameter name ends in _dev.  The library needs an
+ * sm_100a device: there is NO CPU fallback -- without a usable GPU every
+ * compute call fails with IVFHNSW_B200_ENODEV.
+ *
+ * Result layout of the search calls: distances/labels are sorted ascending by
+ * (distance, scan order); unfilled slots hold FLT_MAX / -1 exactly like
+ * faiss::maxheap_heapify (faiss/Heap.h:224-233).  The C++ shim re-orders them
+ * into the reference's max-heap layout.
+ */
+#ifndef IVFHNSW_B200_H
+#define IVFHNSW_B200_H
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+typedef struct ivfhnsw_b200 ivfhnsw_b200_t;
+
+#define IVFHNSW_B200_OK 0
+#define IVFHNSW_B200_EINVAL (-1)  /* bad argument / unsupported shape           */
+#define IVFHNSW_B200_ECUDA (-2)   /* a CUDA call or kernel failed               */
+#define IVFHNSW_B200_ENODEV (-3)  /* no usable sm_100 device                    */
+#define IVFHNSW_B200_ESTATE (-4)  /* call order violated (e.g. search w/o lists)*/
+
+/* ABI version of this header; ivfhnsw_b200_abi_version() must return it. */
+#define IVFHNSW_B200_ABI 1
+int ivfhnsw_b200_abi_version(void);
+
+/* -- lifetime ---------------------------------------------------------------
+ * IndexIVF_HNSW::IndexIVF_HNSW (IndexIVF_HNSW.cpp:8-24) and
+ * IndexIVF_HNSW_Grouping::IndexIVF_HNSW_Grouping (IndexIVF_HNSW_Grouping.cpp:29-41).
+ * nsubc == 0 selects IVFADC, nsubc > 0 Grouping (nsubc <= 256).
+ * code_size (= PQ M) must be 8, 16, 32 or 64 and divide d; nbits must be 8. */
+int ivfhnsw_b200_create(ivfhnsw_b200_t **out, size_t d, size_t nc, size_t code_size, size_t nbits,
+                        size_t nsubc, int device);
+void ivfhnsw_b200_destroy(ivfhnsw_b200_t *h);
+const char *ivfhnsw_b200_last_error(const ivfhnsw_b200_t *h);
+
+/* -- sharding: this handle owns the inverted lists of
+ * centroids [c_begin, c_end) only; all metadata stays replicated.  Lists
+ * outside the range still count for the max_codes rule but are not scanned.
+ * Default is [0, nc).  Must be called before lists are loaded/added. */
+int ivfhnsw_b200_set_shard(ivfhnsw_b200_t *h, size_t c_begin, size_t c_end);
+
+/* -- model state ------------------------------------------------------------*/
+/* centroid table = hnswlib::HierarchicalNSW::getDataByInternalId (hnswlib/hnswalg.h:76-78),
+ * filled by IndexIVF_HNSW::build_quantizer (IndexIVF_HNSW.cpp:40-65); nc x d row-major */
+int ivfhnsw_b200_set_centroids(ivfhnsw_b200_t *h, const float *centroids);
+/* faiss::ProductQuantizer::centroids of index->pq, layout [M][256][dsub] (faiss/ProductQuantizer.h) */
+int ivfhnsw_b200_set_pq(ivfhnsw_b200_t *h, const float *pq_centroids);
+/* index->norm_pq centroids: 256 floats (IndexIVF_HNSW.cpp:14) */
+int ivfhnsw_b200_set_norm_pq(ivfhnsw_b200_t *h, const float *norm_centroids);
+/* index->opq_matrix->A, d x d row-major [d_out][d_in] (faiss/VectorTransform.h:84-85); NULL clears */
+int ivfhnsw_b200_set_opq(ivfhnsw_b200_t *h, const float *A);
+/* public members nprobe, max_codes, do_opq, do_pruning (IndexIVF_HNSW.h:58-62, IndexIVF_HNSW_Grouping.h:18) */
+int ivfhnsw_b200_set_params(ivfhnsw_b200_t *h, size_t nprobe, size_t max_codes, int do_opq, int do_pruning);
+
+/* IndexIVF_HNSW::compute_centroid_norms (IndexIVF_HNSW.cpp:781-787) */
+int ivfhnsw_b200_compute_centroid_norms(ivfhnsw_b200_t *h);
+int ivfhnsw_b200_get_centroid_norms(ivfhnsw_b200_t *h, float *out /* nc */);
+int ivfhnsw_b200_set_centroid_norms(ivfhnsw_b200_t *h, const float *in /* nc, e.g. from read() */);
+/* IndexIVF_HNSW::rotate_quantizer (IndexIVF_HNSW.cpp:789-800): centroids <- centroids * A^T on the device */
+int ivfhnsw_b200_rotate_quantizer(ivfhnsw_b200_t *h);
+int ivfhnsw_b200_get_centroids(ivfhnsw_b200_t *h, float *out /* nc*d */);
+
+/* -- indexing ---------------------------------------------------------------*/
+/* IndexIVF_HNSW::assign (IndexIVF_HNSW.cpp:68-72): exact nearest centroid (k must be 1) */
+int ivfhnsw_b200_assign(ivfhnsw_b200_t *h, size_t n, const float *x, uint32_t *labels, size_t k);
+/* same, base vectors given as bytes (what readXvecFvec<uint8_t> expands, utils.h:112-127) */
+int ivfhnsw_b200_assign_u8(ivfhnsw_b200_t *h, size_t n, const uint8_t *x, uint32_t *labels);
+/* IndexIVF_HNSW::add_batch (IndexIVF_HNSW.cpp:75-138); precomputed_idx may be NULL (assign first) */
+int ivfhnsw_b200_add_batch(ivfhnsw_b200_t *h, size_t n, const float *x, const uint32_t *xids,
+                           const uint32_t *precomputed_idx);
+/* IndexIVF_HNSW_Grouping::add_group (IndexIVF_HNSW_Grouping.cpp:43-157); thread-safe per distinct group:
+ * vectors are staged and encoded at finalize() */
+int ivfhnsw_b200_add_group(ivfhnsw_b200_t *h, size_t group_idx, size_t group_size, const float *x,
+                           const uint32_t *ids);
+/* device-resident bulk variant used by the ingest path: x_dev [n][d] f32, ids_dev [n], group_dev [n]
+ * (any order; the per-group order of appearance is kept) */
+int ivfhnsw_b200_add_points_dev(ivfhnsw_b200_t *h, size_t n, const float *x_dev, const uint32_t *ids_dev,
+                                const uint32_t *idx_dev);
+/* flush point: builds the device CSR lists (stable by list [, sub-group]) from everything added so far.
+ * For Grouping also computes nn_centroid_idxs / alphas / sub-groups (add_group body) and
+ * compute_inter_centroid_dists (IndexIVF_HNSW_Grouping.cpp:620-631). */
+int ivfhnsw_b200_finalize(ivfhnsw_b200_t *h);
+
+/* -- list import / export: the per-list vectors of read()/write()
+ * (IndexIVF_HNSW.cpp:637-663,758-779; IndexIVF_HNSW_Grouping.cpp:397-483), flattened as CSR.
+ * list_off[nc+1]; ids[N]; codes[N*code_size]; norm_codes[N];
+ * Grouping only (else NULL): nn_idx[nc*nsubc], sub_sizes[nc*nsubc], alphas[nc], icd[nc*nsubc]. */
+int ivfhnsw_b200_load_lists(ivfhnsw_b200_t *h, const int64_t *list_off, const uint32_t *ids,
+                            const uint8_t *codes, const uint8_t *norm_codes, const uint32_t *nn_idx,
+                            const uint32_t *sub_sizes, const float *alphas, const float *icd);
+int ivfhnsw_b200_ntotal(ivfhnsw_b200_t *h, size_t *ntotal);
+int ivfhnsw_b200_export_lists(ivfhnsw_b200_t *h, int64_t *list_off, uint32_t *ids, uint8_t *codes,
+                              uint8_t *norm_codes, uint32_t *nn_idx, uint32_t *sub_sizes, float *alphas,
+                              float *icd);
+
+/* -- search -----------------------------------------------------------------*/
+/* coarse stage alone = quantizer->searchKnn(query, nprobe) unloaded nearest-first
+ * (IndexIVF_HNSW.cpp:248-259), but EXACT.  x are raw queries (OPQ applied inside when do_opq). */
+int ivfhnsw_b200_coarse(ivfhnsw_b200_t *h, size_t nq, const float *x, size_t nprobe, float *dists,
+                        uint32_t *idxs);
+/* IndexIVF_HNSW::search / IndexIVF_HNSW_Grouping::search (IndexIVF_HNSW.cpp:234-296,
+ * IndexIVF_HNSW_Grouping.cpp:188-363) for nq queries at once */
+int ivfhnsw_b200_search(ivfhnsw_b200_t *h, size_t nq, size_t k, const float *x, float *distances,
+                        int64_t *labels);
+/* IndexIVF_HNSW::search2 (IndexIVF_HNSW.cpp:453-492): coarse candidates supplied by the caller
+ * ([nq][nprobe], nearest first).  Also accepted for Grouping handles (parity seam). */
+int ivfhnsw_b200_search_given_coarse(ivfhnsw_b200_t *h, size_t nq, size_t k, const float *x,
+                                     const float *coarse_dists, const uint32_t *coarse_idxs,
+                                     float *distances, int64_t *labels);
+/* device-resident variants (inputs/outputs already in HBM, asynchronous on the handle's stream
+ * until ivfhnsw_b200_sync) -- what bench.py times for the "value" figure */
+int ivfhnsw_b200_search_dev(ivfhnsw_b200_t *h, size_t nq, size_t k, const float *x_dev, float *distances_dev,
+                            int64_t *labels_dev);
+int ivfhnsw_b200_search_given_coarse_dev(ivfhnsw_b200_t *h, size_t nq, size_t k, const float *x_dev,
+                                         const float *coarse_dists_dev, const uint32_t *coarse_idxs_dev,
+                                         float *distances_dev, int64_t *labels_dev);
+int ivfhnsw_b200_coarse_dev(ivfhnsw_b200_t *h, size_t nq, const float *x_dev, size_t nprobe,
+                            float *dists_dev, uint32_t *idxs_dev);
+int ivfhnsw_b200_sync(ivfhnsw_b200_t *h);
+
+/* -- introspection for tests, bench and profiles ----------------------------*/
+typedef struct ivfhnsw_b200_stats {
+    uint64_t kernel_launches;   /* kernels of this library launched since create/reset          */
+    uint64_t scanned_codes;     /* codes whose ADC distance was required by the reference rule  */
+    uint64_t walked_codes;      /* codes actually streamed by the scan kernel (>= scanned)      */
+    uint64_t queries;           /* queries searched                                             */
+    double scan_ms;             /* CUDA-event time spent in the ADC scan kernel                 */
+    double coarse_ms;           /* ... in the coarse GEMM + select kernels                      */
+    double prep_ms;             /* ... in work-list / sub-centroid kernels                      */
+    uint64_t scan_launches;     /* number of scan-kernel launches included in scan_ms           */
+    uint64_t coarse_flops;      /* 2*nc*d per query/vector pushed through the coarse GEMM       */
+} ivfhnsw_b200_stats_t;
+/* timing != 0 brackets each stage with CUDA events on the handle's stream (adds a sync per call) */
+int ivfhnsw_b200_set_timing(ivfhnsw_b200_t *h, int timing);
+int ivfhnsw_b200_get_stats(ivfhnsw_b200_t *h, ivfhnsw_b200_stats_t *out);
+int ivfhnsw_b200_reset_stats(ivfhnsw_b200_t *h);
+/* Grouping debug outputs of the last search call's first min(nq, cap) queries: pruning threshold per
+ * query (IndexIVF_HNSW_Grouping.cpp:261) and codes scanned per query */
+int ivfhnsw_b200_last_thresholds(ivfhnsw_b200_t *h, size_t cap, float *thresholds, uint32_t *scanned);
+/* tuning knobs: "coarse_slack", "coarse_impl" (0 = SIMT fp32, 1 = tcgen05 bf16), "scan_split" (0 = auto) */
+int ivfhnsw_b200_set_option(ivfhnsw_b200_t *h, const char *name, long value);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* IVFHNSW_B200_H */

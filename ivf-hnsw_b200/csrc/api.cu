@@ -1,0 +1,1091 @@
+// C ABI of libivfhnsw_b200.so (declared in include/ivfhnsw_b200.h): handle state, host-side
+// orchestration of the kernels in scan.cu / coarse.cu / build.cu / dense.cu.  No CPU fallback:
+// every compute entry point needs a CUDA device and fails loudly otherwise.
+#include <cuda_runtime.h>
+#include <cub/cub.cuh>
+
+#include <algorithm>
+#include <cstdarg>
+#include <cstdio>
+#include <cstring>
+#include <mutex>
+#include <string>
+#include <vector>
+
+#include "../../include/ivfhnsw_b200.h"
+#include "common.cuh"
+#include "kernels.h"
+
+namespace ivfb200 {
+cudaError_t launch_group_points(cudaStream_t st, uint64_t *launches, int mode, int nc, int d, int nsubc,
+                                const float *x, const uint32_t *order, const uint32_t *grp_off,
+                                const float *centroids, const uint32_t *nn_idx, const float *icd,
+                                const float *alphas, float *num, float *den, uint8_t *sub);
+cudaError_t launch_slot_scan(cudaStream_t st, uint64_t *launches, int nc, uint32_t align, const uint32_t *size,
+                             uint32_t *slot, uint32_t *raw_off, uint32_t *total_slots);
+cudaError_t launch_scatter_lists2(cudaStream_t st, uint64_t *launches, size_t n, int M, int key_div,
+                                  const uint32_t *order, const uint32_t *sorted_key, const uint32_t *raw_off,
+                                  const uint32_t *list_slot, const uint32_t *ids, const uint8_t *codes,
+                                  const uint8_t *norm_codes, uint8_t *out_codes, uint8_t *out_norm, uint8_t *out_sub,
+                                  uint32_t *out_ids);
+cudaError_t launch_gather_lists(cudaStream_t st, uint64_t *launches, int nc, int M, const uint32_t *list_size,
+                                const uint32_t *list_slot, const uint32_t *raw_off, const uint8_t *codes,
+                                const uint8_t *norm_codes, const uint32_t *ids, uint8_t *out_codes, uint8_t *out_norm,
+                                uint32_t *out_ids);
+cudaError_t launch_f32_to_bf16(cudaStream_t st, uint64_t *launches, size_t n, const float *x, void *out);
+}  // namespace ivfb200
+
+using namespace ivfb200;
+
+namespace {
+
+struct DevBuf {
+    void *p = nullptr;
+    size_t cap = 0;
+    cudaError_t ensure(size_t bytes)
+    {
+        if (bytes <= cap) return cudaSuccess;
+        if (p) cudaFree(p);
+        p = nullptr;
+        cap = 0;
+        cudaError_t e = cudaMalloc(&p, bytes);
+        if (e == cudaSuccess) cap = bytes;
+        return e;
+    }
+    // keep the first `keep` bytes
+    cudaError_t grow(size_t bytes, size_t keep, cudaStream_t st)
+    {
+        if (bytes <= cap) return cudaSuccess;
+        size_t ncap = std::max(bytes, cap + cap / 2);
+        void *np = nullptr;
+        cudaError_t e = cudaMalloc(&np, ncap);
+        if (e != cudaSuccess) return e;
+        if (p && keep) {
+            e = cudaMemcpyAsync(np, p, keep, cudaMemcpyDeviceToDevice, st);
+            if (e != cudaSuccess) return e;
+            e = cudaStreamSynchronize(st);
+            if (e != cudaSuccess) return e;
+        }
+        if (p) cudaFree(p);
+        p = np;
+        cap = ncap;
+        return cudaSuccess;
+    }
+    void release()
+    {
+        if (p) cudaFree(p);
+        p = nullptr;
+        cap = 0;
+    }
+    template <typename T> T *as() const { return reinterpret_cast<T *>(p); }
+};
+
+__global__ void iota_kernel(size_t n, uint32_t *out)
+{
+    for (size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (size_t)gridDim.x * blockDim.x)
+        out[i] = (uint32_t)i;
+}
+__global__ void make_key_kernel(size_t n, const uint32_t *list, const uint8_t *sub, uint32_t mul, uint32_t *key)
+{
+    for (size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (size_t)gridDim.x * blockDim.x)
+        key[i] = list[i] * mul + (sub ? (uint32_t)sub[i] : 0u);
+}
+__global__ void key_to_list_kernel(size_t n, const uint32_t *key, uint32_t div, uint32_t *list)
+{
+    for (size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (size_t)gridDim.x * blockDim.x)
+        list[i] = key[i] / div;
+}
+// expand CSR offsets into one list id (and sub-group id) per record
+__global__ void csr_to_keys_kernel(int nc, int nsubc, const int64_t *list_off, const uint32_t *sub_sizes,
+                                   uint32_t *list, uint8_t *sub)
+{
+    const int c = blockIdx.x;
+    const int64_t beg = list_off[c], end = list_off[c + 1];
+    for (int64_t j = beg + threadIdx.x; j < end; j += blockDim.x) list[j] = (uint32_t)c;
+    if (sub && threadIdx.x == 0) {
+        int64_t pos = beg;
+        for (int s = 0; s < nsubc; s++) {
+            const uint32_t n = sub_sizes[(size_t)c * nsubc + s];
+            for (uint32_t j = 0; j < n && pos < end; j++) sub[pos++] = (uint8_t)s;
+        }
+    }
+}
+__global__ void reduce_u32_kernel(int n, const uint32_t *a, const uint32_t *b, unsigned long long *out)
+{
+    unsigned long long sa = 0, sb = 0;
+    for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x) { sa += a[i]; sb += b[i]; }
+    for (int off = 16; off > 0; off >>= 1) {
+        sa += __shfl_xor_sync(0xffffffffu, sa, off);
+        sb += __shfl_xor_sync(0xffffffffu, sb, off);
+    }
+    if ((threadIdx.x & 31) == 0) { atomicAdd(&out[0], sa); atomicAdd(&out[1], sb); }
+}
+
+unsigned grid_for(size_t n, int per = 256, unsigned cap = 148 * 16)
+{
+    size_t b = (n + per - 1) / per;
+    if (b < 1) b = 1;
+    return (unsigned)std::min<size_t>(b, cap);
+}
+
+}  // namespace
+
+struct ivfhnsw_b200 {
+    int device = 0;
+    size_t d = 0, nc = 0, M = 0, nsubc = 0;
+    size_t nprobe = 1, max_codes = 1000000000;
+    bool do_opq = false, do_pruning = false;
+    uint32_t c_begin = 0, c_end = 0;
+    cudaStream_t stream = nullptr;
+    cudaEvent_t ev[4] = {nullptr, nullptr, nullptr, nullptr};
+    std::string err;
+    std::mutex mu;
+
+    // model
+    DevBuf centroids, centroid_norms, cnorm_gemm, cent_bf16, pqc, norm_table, opqA;
+    bool have_centroids = false, have_pq = false, have_norm = false, have_opq = false, have_cnorms = false;
+    bool gemm_norms_valid = false, bf16_valid = false;
+    // lists (device CSR in slot space)
+    DevBuf list_size, list_slot, raw_off, codes, norm_codes, sub_ids, ids;
+    DevBuf nn_idx, sub_sizes, alphas, icd;
+    bool have_lists = false, have_group_meta = false;
+    size_t ntotal = 0, nslots = 0;
+    // staging (records not yet in the CSR)
+    DevBuf st_list, st_ids, st_codes, st_norm, st_sub, st_x;
+    size_t st_n = 0;          // encoded records staged (IVFADC) or points staged (Grouping)
+    bool st_dirty = false;
+    // workspace
+    DevBuf w_x, w_xrot, w_cd, w_ci, w_seg, w_sub_base, w_qsd, w_part, w_coarse, w_xbf16, w_out_d, w_out_l;
+    DevBuf w_a, w_b, w_c, w_d2, w_e, w_f, w_cub, w_small;
+    DevBuf counters;  // [0] scanned, [1] walked
+    // options / stats
+    long coarse_slack = 8, coarse_impl = 0, scan_split = 0, query_batch = 0, debug = 0;
+    bool timing = false;
+    ivfhnsw_b200_stats_t stats{};
+    std::vector<float> last_thr;
+    std::vector<uint32_t> last_scanned;
+
+    int fail(int code, const char *fmt, ...)
+    {
+        char buf[512];
+        va_list ap;
+        va_start(ap, fmt);
+        vsnprintf(buf, sizeof buf, fmt, ap);
+        va_end(ap);
+        err = buf;
+        return code;
+    }
+};
+
+#define CU(call)                                                                                         \
+    do {                                                                                                 \
+        cudaError_t e__ = (call);                                                                        \
+        if (e__ != cudaSuccess)                                                                          \
+            return h->fail(IVFHNSW_B200_ECUDA, "%s:%d %s -> %s", __FILE__, __LINE__, #call, cudaGetErrorString(e__)); \
+    } while (0)
+
+#define LAUNCHES (&h->stats.kernel_launches)
+
+static int bind(ivfhnsw_b200_t *h)
+{
+    CU(cudaSetDevice(h->device));
+    return 0;
+}
+
+extern "C" {
+
+int ivfhnsw_b200_abi_version(void) { return IVFHNSW_B200_ABI; }
+
+int ivfhnsw_b200_create(ivfhnsw_b200_t **out, size_t d, size_t nc, size_t code_size, size_t nbits, size_t nsubc,
+                        int device)
+{
+    if (!out) return IVFHNSW_B200_EINVAL;
+    *out = nullptr;
+    ivfhnsw_b200_t *h = new ivfhnsw_b200();
+    *out = h;  // returned even on failure so that last_error() is readable; caller destroys it
+    h->device = device;
+    h->d = d; h->nc = nc; h->M = code_size; h->nsubc = nsubc;
+    h->c_begin = 0; h->c_end = (uint32_t)nc;
+    if (nbits != 8) return h->fail(IVFHNSW_B200_EINVAL, "nbits_per_idx must be 8 (got %zu)", nbits);
+    if (!(code_size == 8 || code_size == 16 || code_size == 32 || code_size == 64))
+        return h->fail(IVFHNSW_B200_EINVAL, "bytes_per_code must be 8, 16, 32 or 64 (got %zu)", code_size);
+    if (d == 0 || d % code_size != 0 || d % 4 != 0)
+        return h->fail(IVFHNSW_B200_EINVAL, "dim %zu must be a multiple of 4 and of bytes_per_code %zu", d, code_size);
+    if (nc == 0 || nc >= (1ull << 31)) return h->fail(IVFHNSW_B200_EINVAL, "bad ncentroids %zu", nc);
+    if (nsubc > 256) return h->fail(IVFHNSW_B200_EINVAL, "nsubcentroids %zu > 256 unsupported", nsubc);
+    int ndev = 0;
+    cudaError_t e = cudaGetDeviceCount(&ndev);
+    if (e != cudaSuccess || ndev == 0 || device < 0 || device >= ndev)
+        return h->fail(IVFHNSW_B200_ENODEV, "no usable CUDA device %d (%s); this library has no CPU fallback", device,
+                       e == cudaSuccess ? "device index out of range" : cudaGetErrorString(e));
+    cudaDeviceProp prop;
+    CU(cudaGetDeviceProperties(&prop, device));
+    if (prop.major != 10)
+        return h->fail(IVFHNSW_B200_ENODEV, "device %d is sm_%d%d; kernels are built for sm_100a only", device, prop.major,
+                       prop.minor);
+    CU(cudaSetDevice(device));
+    CU(cudaStreamCreateWithFlags(&h->stream, cudaStreamNonBlocking));
+    for (int i = 0; i < 4; i++) CU(cudaEventCreate(&h->ev[i]));
+    CU(h->counters.ensure(64));
+    CU(cudaMemsetAsync(h->counters.p, 0, 64, h->stream));
+    CU(h->centroid_norms.ensure(nc * 4));
+    CU(cudaMemsetAsync(h->centroid_norms.p, 0, nc * 4, h->stream));
+    if (nsubc) {
+        CU(h->alphas.ensure(nc * 4));
+        CU(cudaMemsetAsync(h->alphas.p, 0, nc * 4, h->stream));
+    }
+    CU(cudaStreamSynchronize(h->stream));
+    return 0;
+}
+
+void ivfhnsw_b200_destroy(ivfhnsw_b200_t *h)
+{
+    if (!h) return;
+    if (h->stream) {
+        cudaSetDevice(h->device);
+        cudaStreamSynchronize(h->stream);
+    }
+    DevBuf *bufs[] = {&h->centroids, &h->centroid_norms, &h->cnorm_gemm, &h->cent_bf16, &h->pqc, &h->norm_table,
+                      &h->opqA, &h->list_size, &h->list_slot, &h->raw_off, &h->codes, &h->norm_codes, &h->sub_ids,
+                      &h->ids, &h->nn_idx, &h->sub_sizes, &h->alphas, &h->icd, &h->st_list, &h->st_ids, &h->st_codes,
+                      &h->st_norm, &h->st_sub, &h->st_x, &h->w_x, &h->w_xrot, &h->w_cd, &h->w_ci, &h->w_seg,
+                      &h->w_sub_base, &h->w_qsd, &h->w_part, &h->w_coarse, &h->w_xbf16, &h->w_out_d, &h->w_out_l,
+                      &h->w_a, &h->w_b, &h->w_c, &h->w_d2, &h->w_e, &h->w_f, &h->w_cub, &h->w_small, &h->counters};
+    for (DevBuf *b : bufs) b->release();
+    for (int i = 0; i < 4; i++)
+        if (h->ev[i]) cudaEventDestroy(h->ev[i]);
+    if (h->stream) cudaStreamDestroy(h->stream);
+    delete h;
+}
+
+const char *ivfhnsw_b200_last_error(const ivfhnsw_b200_t *h) { return h ? h->err.c_str() : "null handle"; }
+
+int ivfhnsw_b200_set_shard(ivfhnsw_b200_t *h, size_t c_begin, size_t c_end)
+{
+    if (c_begin > c_end || c_end > h->nc) return h->fail(IVFHNSW_B200_EINVAL, "bad shard range");
+    h->c_begin = (uint32_t)c_begin;
+    h->c_end = (uint32_t)c_end;
+    return 0;
+}
+
+static int upload(ivfhnsw_b200_t *h, DevBuf &b, const void *src, size_t bytes)
+{
+    CU(b.ensure(bytes));
+    CU(cudaMemcpyAsync(b.p, src, bytes, cudaMemcpyHostToDevice, h->stream));
+    CU(cudaStreamSynchronize(h->stream));
+    return 0;
+}
+
+int ivfhnsw_b200_set_centroids(ivfhnsw_b200_t *h, const float *c)
+{
+    if (bind(h)) return IVFHNSW_B200_ECUDA;
+    if (int r = upload(h, h->centroids, c, h->nc * h->d * 4)) return r;
+    h->have_centroids = true;
+    h->gemm_norms_valid = false;
+    h->bf16_valid = false;
+    return 0;
+}
+int ivfhnsw_b200_set_pq(ivfhnsw_b200_t *h, const float *p)
+{
+    if (bind(h)) return IVFHNSW_B200_ECUDA;
+    if (int r = upload(h, h->pqc, p, h->d * 256 * 4)) return r;
+    h->have_pq = true;
+    return 0;
+}
+int ivfhnsw_b200_set_norm_pq(ivfhnsw_b200_t *h, const float *t)
+{
+    if (bind(h)) return IVFHNSW_B200_ECUDA;
+    if (int r = upload(h, h->norm_table, t, 256 * 4)) return r;
+    h->have_norm = true;
+    return 0;
+}
+int ivfhnsw_b200_set_opq(ivfhnsw_b200_t *h, const float *A)
+{
+    if (!A) { h->have_opq = false; return 0; }
+    if (bind(h)) return IVFHNSW_B200_ECUDA;
+    if (int r = upload(h, h->opqA, A, h->d * h->d * 4)) return r;
+    h->have_opq = true;
+    return 0;
+}
+int ivfhnsw_b200_set_params(ivfhnsw_b200_t *h, size_t nprobe, size_t max_codes, int do_opq, int do_pruning)
+{
+    if (nprobe == 0 || nprobe > h->nc) return h->fail(IVFHNSW_B200_EINVAL, "nprobe %zu out of range (nc = %zu)", nprobe, h->nc);
+    if (nprobe > 2048) return h->fail(IVFHNSW_B200_EINVAL, "nprobe %zu > 2048 unsupported", nprobe);
+    h->nprobe = nprobe;
+    h->max_codes = max_codes;
+    h->do_opq = do_opq != 0;
+    h->do_pruning = do_pruning != 0;
+    return 0;
+}
+int ivfhnsw_b200_set_option(ivfhnsw_b200_t *h, const char *name, long v)
+{
+    if (!strcmp(name, "coarse_slack")) h->coarse_slack = v;
+    else if (!strcmp(name, "coarse_impl")) h->coarse_impl = v;
+    else if (!strcmp(name, "scan_split")) h->scan_split = v;
+    else if (!strcmp(name, "query_batch")) h->query_batch = v;
+    else if (!strcmp(name, "debug")) h->debug = v;
+    else return h->fail(IVFHNSW_B200_EINVAL, "unknown option %s", name);
+    return 0;
+}
+int ivfhnsw_b200_set_timing(ivfhnsw_b200_t *h, int t) { h->timing = t != 0; return 0; }
+int ivfhnsw_b200_sync(ivfhnsw_b200_t *h)
+{
+    if (bind(h)) return IVFHNSW_B200_ECUDA;
+    CU(cudaStreamSynchronize(h->stream));
+    return 0;
+}
+
+int ivfhnsw_b200_compute_centroid_norms(ivfhnsw_b200_t *h)
+{
+    if (bind(h)) return IVFHNSW_B200_ECUDA;
+    if (!h->have_centroids) return h->fail(IVFHNSW_B200_ESTATE, "centroids not set");
+    CU(launch_row_norms(h->stream, LAUNCHES, h->nc, (int)h->d, h->centroids.as<float>(), h->centroid_norms.as<float>()));
+    CU(cudaStreamSynchronize(h->stream));
+    h->have_cnorms = true;
+    return 0;
+}
+int ivfhnsw_b200_get_centroid_norms(ivfhnsw_b200_t *h, float *out)
+{
+    if (bind(h)) return IVFHNSW_B200_ECUDA;
+    CU(cudaMemcpyAsync(out, h->centroid_norms.p, h->nc * 4, cudaMemcpyDeviceToHost, h->stream));
+    CU(cudaStreamSynchronize(h->stream));
+    return 0;
+}
+int ivfhnsw_b200_set_centroid_norms(ivfhnsw_b200_t *h, const float *in)
+{
+    if (bind(h)) return IVFHNSW_B200_ECUDA;
+    if (int r = upload(h, h->centroid_norms, in, h->nc * 4)) return r;
+    h->have_cnorms = true;
+    return 0;
+}
+int ivfhnsw_b200_get_centroids(ivfhnsw_b200_t *h, float *out)
+{
+    if (bind(h)) return IVFHNSW_B200_ECUDA;
+    if (!h->have_centroids) return h->fail(IVFHNSW_B200_ESTATE, "centroids not set");
+    CU(cudaMemcpyAsync(out, h->centroids.p, h->nc * h->d * 4, cudaMemcpyDeviceToHost, h->stream));
+    CU(cudaStreamSynchronize(h->stream));
+    return 0;
+}
+int ivfhnsw_b200_rotate_quantizer(ivfhnsw_b200_t *h)
+{
+    if (bind(h)) return IVFHNSW_B200_ECUDA;
+    if (!h->have_opq) return h->fail(IVFHNSW_B200_ESTATE, "OPQ encoding is turned off (no matrix set)");
+    if (!h->have_centroids) return h->fail(IVFHNSW_B200_ESTATE, "centroids not set");
+    CU(h->w_a.ensure(h->nc * h->d * 4));
+    CU(launch_rotate(h->stream, LAUNCHES, h->nc, (int)h->d, h->opqA.as<float>(), false, h->centroids.as<float>(),
+                     h->w_a.as<float>()));
+    CU(cudaMemcpyAsync(h->centroids.p, h->w_a.p, h->nc * h->d * 4, cudaMemcpyDeviceToDevice, h->stream));
+    CU(cudaStreamSynchronize(h->stream));
+    h->gemm_norms_valid = false;
+    h->bf16_valid = false;
+    return 0;
+}
+
+// ------------------------------------------------------------------------------------ coarse helpers
+static int ensure_gemm_side(ivfhnsw_b200_t *h)
+{
+    if (!h->gemm_norms_valid) {
+        // ||c||^2 over ALL dims for the GEMM ranking value (the exact re-rank uses fstdistfunc numerics)
+        CU(h->cnorm_gemm.ensure(h->nc * 4));
+        CU(launch_row_norms(h->stream, LAUNCHES, h->nc, (int)h->d, h->centroids.as<float>(), h->cnorm_gemm.as<float>()));
+        h->gemm_norms_valid = true;
+    }
+    if (h->coarse_impl == 1 && !h->bf16_valid) {
+        CU(h->cent_bf16.ensure(h->nc * h->d * 2));
+        CU(launch_f32_to_bf16(h->stream, LAUNCHES, h->nc * h->d, h->centroids.as<float>(), h->cent_bf16.p));
+        h->bf16_valid = true;
+    }
+    return 0;
+}
+
+// exact nprobe nearest centroids for nq device-resident (already rotated) queries
+static int coarse_dev(ivfhnsw_b200_t *h, size_t nq, const float *xq, size_t nprobe, int exclude_self, float *out_d,
+                      uint32_t *out_i)
+{
+    if (!h->have_centroids) return h->fail(IVFHNSW_B200_ESTATE, "centroids not set (build_quantizer)");
+    if (int r = ensure_gemm_side(h)) return r;
+    const int slack = (int)h->coarse_slack;
+    int cand_cap = 0;
+    const size_t per_q = coarse_work_bytes(1, (int)h->nc, (int)nprobe + slack, &cand_cap);
+    size_t qb = std::min<size_t>(nq, std::max<size_t>(128, ((size_t)3 << 29) / per_q));
+    CU(h->w_coarse.ensure(qb * per_q + 256));
+    if (h->coarse_impl == 1) CU(h->w_xbf16.ensure(qb * h->d * 2 + 256));
+    const size_t ngroups = (h->nc + COARSE_GROUP - 1) / COARSE_GROUP;
+    for (size_t q0 = 0; q0 < nq; q0 += qb) {
+        const size_t nb = std::min(qb, nq - q0);
+        CoarseWork W;
+        W.grp_val = h->w_coarse.as<float>();
+        W.grp_idx = reinterpret_cast<uint32_t *>(W.grp_val + qb * ngroups * COARSE_T);
+        W.err = reinterpret_cast<uint32_t *>(h->counters.as<unsigned long long>() + 4);
+        W.cand = nullptr; W.cand_d = nullptr;
+        W.cand_cap = cand_cap;
+        // exclude_self needs global row ids: only used with q0 == 0-based centroid batches
+        const float *cents = h->centroids.as<float>();
+        CU(launch_coarse(h->stream, LAUNCHES, (int)h->coarse_impl, (int)nb, (int)h->nc, (int)h->d, (int)nprobe, slack,
+                         xq + q0 * h->d, cents, h->cnorm_gemm.as<float>(), h->cent_bf16.p, h->w_xbf16.p, W,
+                         exclude_self ? (int)q0 : -1, out_d + q0 * nprobe, out_i + q0 * nprobe));
+    }
+    h->stats.coarse_flops += (uint64_t)2 * h->nc * h->d * nq;
+    return 0;
+}
+
+int ivfhnsw_b200_coarse_dev(ivfhnsw_b200_t *h, size_t nq, const float *x_dev, size_t nprobe, float *dists_dev,
+                            uint32_t *idxs_dev)
+{
+    if (bind(h)) return IVFHNSW_B200_ECUDA;
+    if (nprobe == 0 || nprobe > h->nc) return h->fail(IVFHNSW_B200_EINVAL, "nprobe out of range");
+    const float *xq = x_dev;
+    if (h->do_opq) {
+        if (!h->have_opq) return h->fail(IVFHNSW_B200_ESTATE, "do_opq set but no OPQ matrix");
+        CU(h->w_xrot.ensure(nq * h->d * 4));
+        CU(launch_rotate(h->stream, LAUNCHES, nq, (int)h->d, h->opqA.as<float>(), false, x_dev, h->w_xrot.as<float>()));
+        xq = h->w_xrot.as<float>();
+    }
+    return coarse_dev(h, nq, xq, nprobe, 0, dists_dev, idxs_dev);
+}
+
+int ivfhnsw_b200_coarse(ivfhnsw_b200_t *h, size_t nq, const float *x, size_t nprobe, float *dists, uint32_t *idxs)
+{
+    if (bind(h)) return IVFHNSW_B200_ECUDA;
+    if (nq == 0) return 0;
+    CU(h->w_x.ensure(nq * h->d * 4));
+    CU(h->w_cd.ensure(nq * nprobe * 4));
+    CU(h->w_ci.ensure(nq * nprobe * 4));
+    CU(cudaMemcpyAsync(h->w_x.p, x, nq * h->d * 4, cudaMemcpyHostToDevice, h->stream));
+    if (int r = ivfhnsw_b200_coarse_dev(h, nq, h->w_x.as<float>(), nprobe, h->w_cd.as<float>(), h->w_ci.as<uint32_t>()))
+        return r;
+    CU(cudaMemcpyAsync(dists, h->w_cd.p, nq * nprobe * 4, cudaMemcpyDeviceToHost, h->stream));
+    CU(cudaMemcpyAsync(idxs, h->w_ci.p, nq * nprobe * 4, cudaMemcpyDeviceToHost, h->stream));
+    CU(cudaStreamSynchronize(h->stream));
+    return 0;
+}
+
+// assign for device-resident vectors (k = 1): labels_dev[n]
+static int assign_dev(ivfhnsw_b200_t *h, size_t n, const float *x_dev, uint32_t *labels_dev)
+{
+    CU(h->w_cd.ensure(n * 4));
+    return coarse_dev(h, n, x_dev, 1, 0, h->w_cd.as<float>(), labels_dev);
+}
+
+int ivfhnsw_b200_assign(ivfhnsw_b200_t *h, size_t n, const float *x, uint32_t *labels, size_t k)
+{
+    if (bind(h)) return IVFHNSW_B200_ECUDA;
+    if (k != 1) return h->fail(IVFHNSW_B200_EINVAL, "assign: only k = 1 is supported (every caller of the reference uses 1)");
+    const size_t chunk = 1 << 18;
+    CU(h->w_x.ensure(std::min(n, chunk) * h->d * 4));
+    CU(h->w_ci.ensure(std::max<size_t>(std::min(n, chunk) * 4, h->w_ci.cap)));
+    for (size_t i0 = 0; i0 < n; i0 += chunk) {
+        const size_t nb = std::min(chunk, n - i0);
+        CU(cudaMemcpyAsync(h->w_x.p, x + i0 * h->d, nb * h->d * 4, cudaMemcpyHostToDevice, h->stream));
+        if (int r = assign_dev(h, nb, h->w_x.as<float>(), h->w_ci.as<uint32_t>())) return r;
+        CU(cudaMemcpyAsync(labels + i0, h->w_ci.p, nb * 4, cudaMemcpyDeviceToHost, h->stream));
+        CU(cudaStreamSynchronize(h->stream));
+    }
+    return 0;
+}
+
+int ivfhnsw_b200_assign_u8(ivfhnsw_b200_t *h, size_t n, const uint8_t *x, uint32_t *labels)
+{
+    if (bind(h)) return IVFHNSW_B200_ECUDA;
+    const size_t chunk = 1 << 18;
+    CU(h->w_x.ensure(std::min(n, chunk) * h->d * 4));
+    CU(h->w_b.ensure(std::min(n, chunk) * h->d));
+    CU(h->w_ci.ensure(std::max<size_t>(std::min(n, chunk) * 4, h->w_ci.cap)));
+    for (size_t i0 = 0; i0 < n; i0 += chunk) {
+        const size_t nb = std::min(chunk, n - i0);
+        CU(cudaMemcpyAsync(h->w_b.p, x + i0 * h->d, nb * h->d, cudaMemcpyHostToDevice, h->stream));
+        CU(launch_u8_to_f32(h->stream, LAUNCHES, nb * h->d, h->w_b.as<uint8_t>(), h->w_x.as<float>()));
+        if (int r = assign_dev(h, nb, h->w_x.as<float>(), h->w_ci.as<uint32_t>())) return r;
+        CU(cudaMemcpyAsync(labels + i0, h->w_ci.p, nb * 4, cudaMemcpyDeviceToHost, h->stream));
+        CU(cudaStreamSynchronize(h->stream));
+    }
+    return 0;
+}
+
+// ------------------------------------------------------------------------------------ encoding
+// codes / norm codes for n device vectors against base rows given by (idx[, sub]); chunked scratch
+static int encode_dev(ivfhnsw_b200_t *h, size_t n, const float *x_dev, const uint32_t *idx_dev, const uint8_t *sub_dev,
+                      uint8_t *codes_dev, uint8_t *norm_dev)
+{
+    if (!h->have_pq || !h->have_norm) return h->fail(IVFHNSW_B200_ESTATE, "PQ codebooks not set (train_pq / read)");
+    if (h->do_opq && !h->have_opq) return h->fail(IVFHNSW_B200_ESTATE, "do_opq set but no OPQ matrix");
+    const int d = (int)h->d, M = (int)h->M, nsubc = (int)h->nsubc;
+    const size_t chunk = std::min<size_t>(n, 1 << 19);
+    CU(h->w_a.ensure(chunk * d * 4));
+    CU(h->w_c.ensure(chunk * d * 4));
+    const float *cen = h->centroids.as<float>();
+    const uint32_t *nn = sub_dev ? h->nn_idx.as<uint32_t>() : nullptr;
+    const float *al = sub_dev ? h->alphas.as<float>() : nullptr;
+    for (size_t i0 = 0; i0 < n; i0 += chunk) {
+        const size_t nb = std::min(chunk, n - i0);
+        float *R = h->w_a.as<float>(), *D = h->w_c.as<float>();
+        const uint8_t *sb = sub_dev ? sub_dev + i0 : nullptr;
+        // residuals (IndexIVF_HNSW.cpp:85-94)
+        CU(launch_residual(h->stream, LAUNCHES, nb, d, x_dev + i0 * d, idx_dev + i0, sb, cen, nn, al, nsubc, -1.f,
+                           nullptr, R));
+        if (h->do_opq) {
+            CU(launch_rotate(h->stream, LAUNCHES, nb, d, h->opqA.as<float>(), false, R, D));
+            std::swap(R, D);
+        }
+        // encode / decode (:96-109)
+        CU(launch_pq_encode(h->stream, LAUNCHES, nb, d, M, h->pqc.as<float>(), R, codes_dev + i0 * M));
+        CU(launch_pq_decode(h->stream, LAUNCHES, nb, d, M, h->pqc.as<float>(), codes_dev + i0 * M, D));
+        if (h->do_opq) {
+            CU(launch_rotate(h->stream, LAUNCHES, nb, d, h->opqA.as<float>(), true, D, R));
+            std::swap(R, D);
+        }
+        // reconstruct, norm, norm code (:111-121)
+        CU(launch_residual(h->stream, LAUNCHES, nb, d, nullptr, idx_dev + i0, sb, cen, nn, al, nsubc, 1.f, D, R));
+        CU(launch_norm_encode(h->stream, LAUNCHES, nb, d, R, h->norm_table.as<float>(), norm_dev + i0, nullptr));
+    }
+    return 0;
+}
+
+static int stage_reserve(ivfhnsw_b200_t *h, size_t extra, bool points)
+{
+    const size_t n = h->st_n + extra;
+    CU(h->st_list.grow(n * 4, h->st_n * 4, h->stream));
+    CU(h->st_ids.grow(n * 4, h->st_n * 4, h->stream));
+    if (points) {
+        CU(h->st_x.grow(n * h->d * 4, h->st_n * h->d * 4, h->stream));
+    } else {
+        CU(h->st_codes.grow(n * h->M, h->st_n * h->M, h->stream));
+        CU(h->st_norm.grow(n, h->st_n, h->stream));
+        if (h->nsubc) CU(h->st_sub.grow(n, h->st_n, h->stream));
+    }
+    return 0;
+}
+
+static int unstage_existing_lists(ivfhnsw_b200_t *h);
+
+int ivfhnsw_b200_add_batch(ivfhnsw_b200_t *h, size_t n, const float *x, const uint32_t *xids, const uint32_t *idx)
+{
+    std::lock_guard<std::mutex> lk(h->mu);
+    if (bind(h)) return IVFHNSW_B200_ECUDA;
+    if (h->nsubc) return h->fail(IVFHNSW_B200_EINVAL, "add_batch on a Grouping index: use add_group");
+    if (!h->have_centroids) return h->fail(IVFHNSW_B200_ESTATE, "centroids not set");
+    if (n == 0) return 0;
+    if (h->have_lists && !h->st_dirty) { if (int r = unstage_existing_lists(h)) return r; }
+    if (int r = stage_reserve(h, n, false)) return r;
+    const size_t chunk = 1 << 18;
+    CU(h->w_x.ensure(std::min(n, chunk) * h->d * 4));
+    for (size_t i0 = 0; i0 < n; i0 += chunk) {
+        const size_t nb = std::min(chunk, n - i0);
+        uint32_t *dl = h->st_list.as<uint32_t>() + h->st_n;
+        CU(cudaMemcpyAsync(h->w_x.p, x + i0 * h->d, nb * h->d * 4, cudaMemcpyHostToDevice, h->stream));
+        CU(cudaMemcpyAsync(h->st_ids.as<uint32_t>() + h->st_n, xids + i0, nb * 4, cudaMemcpyHostToDevice, h->stream));
+        if (idx) CU(cudaMemcpyAsync(dl, idx + i0, nb * 4, cudaMemcpyHostToDevice, h->stream));
+        else if (int r = assign_dev(h, nb, h->w_x.as<float>(), dl)) return r;
+        if (int r = encode_dev(h, nb, h->w_x.as<float>(), dl, nullptr, h->st_codes.as<uint8_t>() + h->st_n * h->M,
+                               h->st_norm.as<uint8_t>() + h->st_n))
+            return r;
+        CU(cudaStreamSynchronize(h->stream));
+        h->st_n += nb;
+    }
+    h->st_dirty = true;
+    return 0;
+}
+
+int ivfhnsw_b200_add_points_dev(ivfhnsw_b200_t *h, size_t n, const float *x_dev, const uint32_t *ids_dev,
+                                const uint32_t *idx_dev)
+{
+    std::lock_guard<std::mutex> lk(h->mu);
+    if (bind(h)) return IVFHNSW_B200_ECUDA;
+    if (n == 0) return 0;
+    if (h->have_lists && !h->st_dirty) {
+        if (h->nsubc) return h->fail(IVFHNSW_B200_ESTATE, "Grouping index already finalized: incremental add unsupported");
+        if (int r = unstage_existing_lists(h)) return r;
+    }
+    const bool points = h->nsubc != 0;
+    if (int r = stage_reserve(h, n, points)) return r;
+    uint32_t *dl = h->st_list.as<uint32_t>() + h->st_n;
+    if (idx_dev) CU(cudaMemcpyAsync(dl, idx_dev, n * 4, cudaMemcpyDeviceToDevice, h->stream));
+    else if (int r = assign_dev(h, n, x_dev, dl)) return r;
+    CU(cudaMemcpyAsync(h->st_ids.as<uint32_t>() + h->st_n, ids_dev, n * 4, cudaMemcpyDeviceToDevice, h->stream));
+    if (points) {
+        CU(cudaMemcpyAsync(h->st_x.as<float>() + h->st_n * h->d, x_dev, n * h->d * 4, cudaMemcpyDeviceToDevice, h->stream));
+    } else {
+        if (int r = encode_dev(h, n, x_dev, dl, nullptr, h->st_codes.as<uint8_t>() + h->st_n * h->M,
+                               h->st_norm.as<uint8_t>() + h->st_n))
+            return r;
+    }
+    CU(cudaStreamSynchronize(h->stream));
+    h->st_n += n;
+    h->st_dirty = true;
+    return 0;
+}
+
+int ivfhnsw_b200_add_group(ivfhnsw_b200_t *h, size_t g, size_t n, const float *x, const uint32_t *ids)
+{
+    std::lock_guard<std::mutex> lk(h->mu);  // called concurrently from an OpenMP loop in the reference's tests
+    if (bind(h)) return IVFHNSW_B200_ECUDA;
+    if (!h->nsubc) return h->fail(IVFHNSW_B200_EINVAL, "add_group on an IVFADC index");
+    if (g >= h->nc) return h->fail(IVFHNSW_B200_EINVAL, "group index out of range");
+    if (h->have_lists && !h->st_dirty)
+        return h->fail(IVFHNSW_B200_ESTATE, "Grouping index already finalized: incremental add_group unsupported");
+    h->st_dirty = true;  // even empty groups mark the index as "being built" (nn lists are computed at finalize)
+    if (n == 0) return 0;
+    if (int r = stage_reserve(h, n, true)) return r;
+    std::vector<uint32_t> gl(n, (uint32_t)g);
+    CU(cudaMemcpyAsync(h->st_list.as<uint32_t>() + h->st_n, gl.data(), n * 4, cudaMemcpyHostToDevice, h->stream));
+    CU(cudaMemcpyAsync(h->st_ids.as<uint32_t>() + h->st_n, ids, n * 4, cudaMemcpyHostToDevice, h->stream));
+    CU(cudaMemcpyAsync(h->st_x.as<float>() + h->st_n * h->d, x, n * h->d * 4, cudaMemcpyHostToDevice, h->stream));
+    CU(cudaStreamSynchronize(h->stream));
+    h->st_n += n;
+    return 0;
+}
+
+// ------------------------------------------------------------------------------------ CSR build
+// staged records (st_list[, st_sub], st_ids, st_codes, st_norm) -> slot-space lists
+static int build_csr(ivfhnsw_b200_t *h)
+{
+    const size_t n = h->st_n;
+    const int nc = (int)h->nc, M = (int)h->M, nsubc = (int)h->nsubc;
+    const uint32_t key_div = nsubc ? (uint32_t)nsubc : 1u;
+    if ((uint64_t)nc * key_div >= (1ull << 32)) return h->fail(IVFHNSW_B200_EINVAL, "nc * nsubc overflows 32 bits");
+    cudaStream_t st = h->stream;
+    CU(h->list_size.ensure((size_t)nc * 4));
+    CU(h->list_slot.ensure((size_t)nc * 4));
+    CU(h->raw_off.ensure((size_t)(nc + 1) * 4));
+    CU(cudaMemsetAsync(h->list_size.p, 0, (size_t)nc * 4, st));
+    if (nsubc) {
+        CU(h->sub_sizes.ensure((size_t)nc * nsubc * 4));
+        CU(cudaMemsetAsync(h->sub_sizes.p, 0, (size_t)nc * nsubc * 4, st));
+    }
+    uint32_t *keys_in = nullptr, *keys_out = nullptr, *ord_in = nullptr, *ord_out = nullptr;
+    if (n) {
+        CU(h->w_d2.ensure(n * 16));
+        keys_in = h->w_d2.as<uint32_t>(); keys_out = keys_in + n; ord_in = keys_out + n; ord_out = ord_in + n;
+        make_key_kernel<<<grid_for(n), 256, 0, st>>>(n, h->st_list.as<uint32_t>(), nsubc ? h->st_sub.as<uint8_t>() : nullptr,
+                                                     key_div, keys_in);
+        iota_kernel<<<grid_for(n), 256, 0, st>>>(n, ord_in);
+        h->stats.kernel_launches += 2;
+        size_t tmp = 0;
+        int bits = 1;
+        while (((uint64_t)nc * key_div) >> bits) bits++;
+        CU(cub::DeviceRadixSort::SortPairs(nullptr, tmp, keys_in, keys_out, ord_in, ord_out, (int)n, 0, bits, st));
+        CU(h->w_cub.ensure(tmp + 16));
+        CU(cub::DeviceRadixSort::SortPairs(h->w_cub.p, tmp, keys_in, keys_out, ord_in, ord_out, (int)n, 0, bits, st));
+        h->stats.kernel_launches += 4;
+        CU(launch_hist(st, LAUNCHES, n, h->st_list.as<uint32_t>(), h->list_size.as<uint32_t>()));
+        if (nsubc) CU(launch_hist(st, LAUNCHES, n, keys_in, h->sub_sizes.as<uint32_t>()));
+    }
+    const uint32_t align = M <= 16 ? 16u : 32u;
+    CU(h->w_small.ensure(64));
+    CU(launch_slot_scan(st, LAUNCHES, nc, align, h->list_size.as<uint32_t>(), h->list_slot.as<uint32_t>(),
+                        h->raw_off.as<uint32_t>(), h->w_small.as<uint32_t>()));
+    uint32_t tot[2] = {0, 0};
+    CU(cudaMemcpyAsync(tot, h->w_small.p, 8, cudaMemcpyDeviceToHost, st));
+    CU(cudaStreamSynchronize(st));
+    const uint64_t total_slots = ((uint64_t)tot[1] << 32) | tot[0];
+    if (total_slots + 64 >= (1ull << 32)) return h->fail(IVFHNSW_B200_EINVAL, "index too large for 32-bit slot ids");
+    const size_t nslots = (size_t)total_slots + 64;
+    CU(h->codes.ensure(nslots * M));
+    CU(h->norm_codes.ensure(nslots));
+    CU(h->ids.ensure(nslots * 4));
+    CU(cudaMemsetAsync(h->codes.p, 0, nslots * M, st));
+    CU(cudaMemsetAsync(h->norm_codes.p, 0, nslots, st));
+    CU(cudaMemsetAsync(h->ids.p, 0, nslots * 4, st));
+    if (nsubc) {
+        CU(h->sub_ids.ensure(nslots));
+        CU(cudaMemsetAsync(h->sub_ids.p, 0, nslots, st));
+    }
+    if (n)
+        CU(launch_scatter_lists2(st, LAUNCHES, n, M, (int)key_div, ord_out, keys_out, h->raw_off.as<uint32_t>(),
+                                 h->list_slot.as<uint32_t>(), h->st_ids.as<uint32_t>(), h->st_codes.as<uint8_t>(),
+                                 h->st_norm.as<uint8_t>(), h->codes.as<uint8_t>(), h->norm_codes.as<uint8_t>(),
+                                 nsubc ? h->sub_ids.as<uint8_t>() : nullptr, h->ids.as<uint32_t>()));
+    CU(cudaStreamSynchronize(st));
+    h->nslots = nslots;
+    h->ntotal = n;
+    h->have_lists = true;
+    return 0;
+}
+
+// pull the current CSR back into the staging arrays so that more records can be appended
+static int unstage_existing_lists(ivfhnsw_b200_t *h)
+{
+    const size_t n = h->ntotal;
+    h->st_n = 0;
+    if (n == 0) return 0;
+    if (int r = stage_reserve(h, n, false)) return r;
+    CU(launch_gather_lists(h->stream, LAUNCHES, (int)h->nc, (int)h->M, h->list_size.as<uint32_t>(),
+                           h->list_slot.as<uint32_t>(), h->raw_off.as<uint32_t>(), h->codes.as<uint8_t>(),
+                           h->norm_codes.as<uint8_t>(), h->ids.as<uint32_t>(), h->st_codes.as<uint8_t>(),
+                           h->st_norm.as<uint8_t>(), h->st_ids.as<uint32_t>()));
+    // list id per record from raw offsets
+    CU(h->w_e.ensure((h->nc + 1) * 8));
+    std::vector<uint32_t> ro(h->nc + 1);
+    CU(cudaMemcpyAsync(ro.data(), h->raw_off.p, (h->nc + 1) * 4, cudaMemcpyDeviceToHost, h->stream));
+    CU(cudaStreamSynchronize(h->stream));
+    std::vector<int64_t> off(h->nc + 1);
+    for (size_t i = 0; i <= h->nc; i++) off[i] = ro[i];
+    CU(cudaMemcpyAsync(h->w_e.p, off.data(), (h->nc + 1) * 8, cudaMemcpyHostToDevice, h->stream));
+    csr_to_keys_kernel<<<(unsigned)h->nc, 128, 0, h->stream>>>((int)h->nc, 0, h->w_e.as<int64_t>(), nullptr,
+                                                              h->st_list.as<uint32_t>(), nullptr);
+    ++h->stats.kernel_launches;
+    CU(cudaStreamSynchronize(h->stream));
+    h->st_n = n;
+    return 0;
+}
+
+// Grouping: nn lists, alphas, sub-group ids and codes for the staged points, then the CSR
+static int finalize_grouping(ivfhnsw_b200_t *h)
+{
+    const int nc = (int)h->nc, d = (int)h->d, nsubc = (int)h->nsubc;
+    const size_t n = h->st_n;
+    cudaStream_t st = h->stream;
+    if ((size_t)nsubc + 1 > h->nc) return h->fail(IVFHNSW_B200_EINVAL, "nsubc + 1 > nc");
+    // K-G3: nsubc nearest other centroids of every centroid (IndexIVF_HNSW_Grouping.cpp:47-63), exact
+    CU(h->nn_idx.ensure((size_t)nc * nsubc * 4));
+    CU(h->icd.ensure((size_t)nc * nsubc * 4));
+    if (int r = coarse_dev(h, nc, h->centroids.as<float>(), nsubc, 1, h->icd.as<float>(), h->nn_idx.as<uint32_t>()))
+        return r;
+    h->have_group_meta = true;
+    CU(cudaMemsetAsync(h->alphas.p, 0, (size_t)nc * 4, st));
+    if (n) {
+        // sort points by group (stable) -> order, grp_off
+        CU(h->w_d2.ensure(n * 16));
+        uint32_t *keys_out = h->w_d2.as<uint32_t>(), *ord_in = keys_out + n, *ord_out = ord_in + n;
+        iota_kernel<<<grid_for(n), 256, 0, st>>>(n, ord_in);
+        ++h->stats.kernel_launches;
+        size_t tmp = 0;
+        int bits = 1;
+        while (((uint64_t)nc) >> bits) bits++;
+        CU(cub::DeviceRadixSort::SortPairs(nullptr, tmp, h->st_list.as<uint32_t>(), keys_out, ord_in, ord_out, (int)n, 0,
+                                           bits, st));
+        CU(h->w_cub.ensure(tmp + 16));
+        CU(cub::DeviceRadixSort::SortPairs(h->w_cub.p, tmp, h->st_list.as<uint32_t>(), keys_out, ord_in, ord_out, (int)n,
+                                           0, bits, st));
+        h->stats.kernel_launches += 4;
+        CU(h->w_e.ensure((size_t)(nc + 1) * 12 + 64));
+        uint32_t *gsize = h->w_e.as<uint32_t>(), *gslot = gsize + nc, *goff = gslot + nc;
+        CU(cudaMemsetAsync(gsize, 0, (size_t)nc * 4, st));
+        CU(launch_hist(st, LAUNCHES, n, h->st_list.as<uint32_t>(), gsize));
+        CU(h->w_small.ensure(64));
+        CU(launch_slot_scan(st, LAUNCHES, nc, 1, gsize, gslot, goff, h->w_small.as<uint32_t>()));
+        // compute_alpha (:691-728) then sub-centroid assignment (:673-689)
+        CU(h->w_f.ensure(n * 8));
+        float *num = h->w_f.as<float>(), *den = num + n;
+        CU(launch_group_points(st, LAUNCHES, 0, nc, d, nsubc, h->st_x.as<float>(), ord_out, goff, h->centroids.as<float>(),
+                               h->nn_idx.as<uint32_t>(), h->icd.as<float>(), nullptr, num, den, nullptr));
+        CU(launch_alpha_reduce(st, LAUNCHES, nc, goff, num, den, h->alphas.as<float>()));
+        CU(h->st_sub.ensure(n));
+        CU(launch_group_points(st, LAUNCHES, 1, nc, d, nsubc, h->st_x.as<float>(), ord_out, goff, h->centroids.as<float>(),
+                               h->nn_idx.as<uint32_t>(), h->icd.as<float>(), h->alphas.as<float>(), nullptr, nullptr,
+                               h->st_sub.as<uint8_t>()));
+        CU(h->st_codes.ensure(n * h->M));
+        CU(h->st_norm.ensure(n));
+        if (int r = encode_dev(h, n, h->st_x.as<float>(), h->st_list.as<uint32_t>(), h->st_sub.as<uint8_t>(),
+                               h->st_codes.as<uint8_t>(), h->st_norm.as<uint8_t>()))
+            return r;
+    }
+    if (int r = build_csr(h)) return r;
+    h->st_x.release();  // raw vectors are not needed any more
+    return 0;
+}
+
+int ivfhnsw_b200_finalize(ivfhnsw_b200_t *h)
+{
+    std::lock_guard<std::mutex> lk(h->mu);
+    if (bind(h)) return IVFHNSW_B200_ECUDA;
+    if (h->have_lists && !h->st_dirty) return 0;
+    if (!h->have_centroids) return h->fail(IVFHNSW_B200_ESTATE, "centroids not set");
+    int r = h->nsubc ? finalize_grouping(h) : build_csr(h);
+    if (r) return r;
+    h->st_dirty = false;
+    return 0;
+}
+
+int ivfhnsw_b200_load_lists(ivfhnsw_b200_t *h, const int64_t *list_off, const uint32_t *ids, const uint8_t *codes,
+                            const uint8_t *norm_codes, const uint32_t *nn_idx, const uint32_t *sub_sizes,
+                            const float *alphas, const float *icd)
+{
+    std::lock_guard<std::mutex> lk(h->mu);
+    if (bind(h)) return IVFHNSW_B200_ECUDA;
+    const size_t nc = h->nc, nsubc = h->nsubc, M = h->M;
+    if (list_off[0] != 0) return h->fail(IVFHNSW_B200_EINVAL, "list_off[0] must be 0");
+    const size_t n = (size_t)list_off[nc];
+    if (nsubc && (!nn_idx || !sub_sizes || !alphas || !icd))
+        return h->fail(IVFHNSW_B200_EINVAL, "Grouping index needs nn_idx, sub_sizes, alphas, icd");
+    h->st_n = 0;
+    if (int r = stage_reserve(h, std::max<size_t>(n, 1), false)) return r;
+    cudaStream_t st = h->stream;
+    CU(h->w_e.ensure((nc + 1) * 8));
+    CU(cudaMemcpyAsync(h->w_e.p, list_off, (nc + 1) * 8, cudaMemcpyHostToDevice, st));
+    if (n) {
+        CU(cudaMemcpyAsync(h->st_ids.p, ids, n * 4, cudaMemcpyHostToDevice, st));
+        CU(cudaMemcpyAsync(h->st_codes.p, codes, n * M, cudaMemcpyHostToDevice, st));
+        CU(cudaMemcpyAsync(h->st_norm.p, norm_codes, n, cudaMemcpyHostToDevice, st));
+    }
+    if (nsubc) {
+        CU(h->nn_idx.ensure(nc * nsubc * 4));
+        CU(h->icd.ensure(nc * nsubc * 4));
+        CU(h->w_f.ensure(nc * nsubc * 4));
+        CU(cudaMemcpyAsync(h->nn_idx.p, nn_idx, nc * nsubc * 4, cudaMemcpyHostToDevice, st));
+        CU(cudaMemcpyAsync(h->icd.p, icd, nc * nsubc * 4, cudaMemcpyHostToDevice, st));
+        CU(cudaMemcpyAsync(h->alphas.p, alphas, nc * 4, cudaMemcpyHostToDevice, st));
+        CU(cudaMemcpyAsync(h->w_f.p, sub_sizes, nc * nsubc * 4, cudaMemcpyHostToDevice, st));
+        h->have_group_meta = true;
+    }
+    csr_to_keys_kernel<<<(unsigned)nc, 128, 0, st>>>((int)nc, (int)nsubc, h->w_e.as<int64_t>(),
+                                                    nsubc ? h->w_f.as<uint32_t>() : nullptr, h->st_list.as<uint32_t>(),
+                                                    nsubc ? h->st_sub.as<uint8_t>() : nullptr);
+    ++h->stats.kernel_launches;
+    CU(cudaStreamSynchronize(st));
+    h->st_n = n;
+    if (int r = build_csr(h)) return r;
+    h->st_dirty = false;
+    return 0;
+}
+
+int ivfhnsw_b200_ntotal(ivfhnsw_b200_t *h, size_t *ntotal)
+{
+    *ntotal = h->st_dirty ? h->st_n : h->ntotal;
+    return 0;
+}
+
+int ivfhnsw_b200_export_lists(ivfhnsw_b200_t *h, int64_t *list_off, uint32_t *ids, uint8_t *codes, uint8_t *norm_codes,
+                              uint32_t *nn_idx, uint32_t *sub_sizes, float *alphas, float *icd)
+{
+    if (int r = ivfhnsw_b200_finalize(h)) return r;
+    std::lock_guard<std::mutex> lk(h->mu);
+    if (bind(h)) return IVFHNSW_B200_ECUDA;
+    if (!h->have_lists) return h->fail(IVFHNSW_B200_ESTATE, "no lists");
+    const size_t nc = h->nc, n = h->ntotal, M = h->M, nsubc = h->nsubc;
+    cudaStream_t st = h->stream;
+    std::vector<uint32_t> ro(nc + 1);
+    CU(cudaMemcpyAsync(ro.data(), h->raw_off.p, (nc + 1) * 4, cudaMemcpyDeviceToHost, st));
+    CU(cudaStreamSynchronize(st));
+    for (size_t i = 0; i <= nc; i++) list_off[i] = ro[i];
+    if (n) {
+        CU(h->w_a.ensure(n * M));
+        CU(h->w_b.ensure(n));
+        CU(h->w_c.ensure(n * 4));
+        CU(launch_gather_lists(st, LAUNCHES, (int)nc, (int)M, h->list_size.as<uint32_t>(), h->list_slot.as<uint32_t>(),
+                               h->raw_off.as<uint32_t>(), h->codes.as<uint8_t>(), h->norm_codes.as<uint8_t>(),
+                               h->ids.as<uint32_t>(), h->w_a.as<uint8_t>(), h->w_b.as<uint8_t>(), h->w_c.as<uint32_t>()));
+        CU(cudaMemcpyAsync(codes, h->w_a.p, n * M, cudaMemcpyDeviceToHost, st));
+        CU(cudaMemcpyAsync(norm_codes, h->w_b.p, n, cudaMemcpyDeviceToHost, st));
+        CU(cudaMemcpyAsync(ids, h->w_c.p, n * 4, cudaMemcpyDeviceToHost, st));
+    }
+    if (nsubc) {
+        if (nn_idx) CU(cudaMemcpyAsync(nn_idx, h->nn_idx.p, nc * nsubc * 4, cudaMemcpyDeviceToHost, st));
+        if (sub_sizes) CU(cudaMemcpyAsync(sub_sizes, h->sub_sizes.p, nc * nsubc * 4, cudaMemcpyDeviceToHost, st));
+        if (alphas) CU(cudaMemcpyAsync(alphas, h->alphas.p, nc * 4, cudaMemcpyDeviceToHost, st));
+        if (icd) CU(cudaMemcpyAsync(icd, h->icd.p, nc * nsubc * 4, cudaMemcpyDeviceToHost, st));
+    }
+    CU(cudaStreamSynchronize(st));
+    return 0;
+}
+
+// ------------------------------------------------------------------------------------ search
+static size_t align256(size_t x) { return (x + 255) & ~(size_t)255; }
+
+static int search_core(ivfhnsw_b200_t *h, size_t nq, size_t k, const float *x_dev, const float *cd_dev,
+                       const uint32_t *ci_dev, float *out_d, int64_t *out_l)
+{
+    if (!h->have_lists || h->st_dirty) return h->fail(IVFHNSW_B200_ESTATE, "lists not built: call finalize()/read() first");
+    if (!h->have_pq || !h->have_norm) return h->fail(IVFHNSW_B200_ESTATE, "PQ codebooks not set");
+    if (!h->have_centroids) return h->fail(IVFHNSW_B200_ESTATE, "centroids not set");
+    if (h->do_opq && !h->have_opq) return h->fail(IVFHNSW_B200_ESTATE, "do_opq set but no OPQ matrix");
+    if (k == 0 || k > 2048) return h->fail(IVFHNSW_B200_EINVAL, "k %zu out of range [1, 2048]", k);
+    if (nq == 0) return 0;
+    const int d = (int)h->d, M = (int)h->M, nprobe = (int)h->nprobe, nsubc = (int)h->nsubc;
+    const bool grouping = nsubc > 0;
+    cudaStream_t st = h->stream;
+    const size_t smem = scan_smem_bytes(M, nprobe, (int)k, nsubc);
+    if (smem > 227 * 1024) return h->fail(IVFHNSW_B200_EINVAL, "nprobe/k too large for the scan kernel (%zu B smem)", smem);
+
+    // per-query workspace and batch size
+    const size_t seg_q = align256((size_t)(5 * nprobe + 1) * 4 + 16);
+    const size_t sub_q = grouping ? (size_t)nprobe * nsubc * 4 : 0;
+    size_t qb = h->query_batch > 0 ? (size_t)h->query_batch : 16384;
+    const size_t per_q = seg_q + 2 * sub_q + 32 * k * 12 + (size_t)d * 4 + (size_t)nprobe * 8;
+    qb = std::min(qb, std::max<size_t>(64, ((size_t)1 << 31) / per_q));
+    qb = std::min(qb, nq);
+    int nsplit = (int)h->scan_split;
+    if (nsplit <= 0) {
+        const size_t target = 148 * 6;
+        nsplit = (int)std::min<size_t>(32, (target + std::min(qb, nq) - 1) / std::min(qb, nq));
+    }
+    nsplit = std::max(1, std::min(nsplit, 32));
+
+    CU(h->w_seg.ensure(qb * ((size_t)(5 * nprobe + 1) * 4) + qb * 12 + 1024));
+    if (grouping) {
+        CU(h->w_sub_base.ensure(qb * sub_q + 256));
+        CU(h->w_qsd.ensure(qb * sub_q + 256));
+    }
+    if (nsplit > 1) CU(h->w_part.ensure(qb * nsplit * k * 12 + 256));
+    if (!cd_dev) {
+        CU(h->w_cd.ensure(qb * nprobe * 4));
+        CU(h->w_ci.ensure(qb * nprobe * 4));
+    }
+    if (h->do_opq) CU(h->w_xrot.ensure(qb * d * 4));
+
+    DeviceLists L;
+    L.list_size = h->list_size.as<uint32_t>(); L.list_slot = h->list_slot.as<uint32_t>();
+    L.codes = h->codes.as<uint8_t>(); L.norm_codes = h->norm_codes.as<uint8_t>();
+    L.sub_ids = grouping ? h->sub_ids.as<uint8_t>() : nullptr; L.ids = h->ids.as<uint32_t>();
+    L.nn_idx = h->nn_idx.as<uint32_t>(); L.sub_sizes = h->sub_sizes.as<uint32_t>();
+    L.alphas = h->alphas.as<float>(); L.icd = h->icd.as<float>();
+    L.centroid_norms = h->centroid_norms.as<float>(); L.centroids = h->centroids.as<float>();
+
+    SegTables T;
+    {
+        uint8_t *p = h->w_seg.as<uint8_t>();
+        T.slot = reinterpret_cast<uint32_t *>(p); p += qb * nprobe * 4;
+        T.n = reinterpret_cast<uint32_t *>(p); p += qb * nprobe * 4;
+        T.base = reinterpret_cast<float *>(p); p += qb * nprobe * 4;
+        T.seq = reinterpret_cast<uint32_t *>(p); p += qb * nprobe * 4;
+        T.piece_off = reinterpret_cast<uint32_t *>(p); p += qb * (nprobe + 1) * 4;
+        T.threshold = reinterpret_cast<float *>(p); p += qb * 4;
+        T.nscanned = reinterpret_cast<uint32_t *>(p); p += qb * 4;
+        T.nwalked = reinterpret_cast<uint32_t *>(p); p += qb * 4;
+        T.sub_base = grouping ? h->w_sub_base.as<float>() : nullptr;
+        T.qsd = grouping ? h->w_qsd.as<float>() : nullptr;
+    }
+    h->last_thr.clear();
+    h->last_scanned.clear();
+
+    for (size_t q0 = 0; q0 < nq; q0 += qb) {
+        const int nb = (int)std::min(qb, nq - q0);
+        const float *xq = x_dev + q0 * d;
+        if (h->timing) CU(cudaEventRecord(h->ev[0], st));
+        if (h->do_opq) {   // IndexIVF_HNSW.cpp:240
+            CU(launch_rotate(st, LAUNCHES, nb, d, h->opqA.as<float>(), false, xq, h->w_xrot.as<float>()));
+            xq = h->w_xrot.as<float>();
+        }
+        const float *cd;
+        const uint32_t *ci;
+        if (cd_dev) { cd = cd_dev + q0 * nprobe; ci = ci_dev + q0 * nprobe; }
+        else {
+            if (int r = coarse_dev(h, nb, xq, nprobe, 0, h->w_cd.as<float>(), h->w_ci.as<uint32_t>())) return r;
+            cd = h->w_cd.as<float>(); ci = h->w_ci.as<uint32_t>();
+        }
+        if (h->timing) CU(cudaEventRecord(h->ev[1], st));
+        if (grouping)
+            CU(launch_prep_grouping(st, LAUNCHES, nb, d, nprobe, nsubc, h->max_codes, h->do_pruning, xq, cd, ci, L,
+                                    h->c_begin, h->c_end, T));
+        else
+            CU(launch_prep_adc(st, LAUNCHES, nb, nprobe, h->max_codes, cd, ci, L, h->c_begin, h->c_end, T));
+        reduce_u32_kernel<<<grid_for(nb, 256, 64), 256, 0, st>>>(nb, T.nscanned, T.nwalked,
+                                                                h->counters.as<unsigned long long>());
+        ++h->stats.kernel_launches;
+        if (h->timing) CU(cudaEventRecord(h->ev[2], st));
+        float *pd = nullptr;
+        uint32_t *ps = nullptr, *pl = nullptr;
+        if (nsplit > 1) {
+            pd = h->w_part.as<float>();
+            ps = reinterpret_cast<uint32_t *>(pd + (size_t)qb * nsplit * k);
+            pl = ps + (size_t)qb * nsplit * k;
+        }
+        CU(launch_scan(st, LAUNCHES, M, grouping, nb, d, nprobe, nsubc, (int)k, nsplit, xq, h->pqc.as<float>(),
+                       h->norm_table.as<float>(), L, T, pd, ps, pl, out_d + q0 * k, out_l + q0 * k));
+        if (h->timing) CU(cudaEventRecord(h->ev[3], st));
+        if (nsplit > 1)
+            CU(launch_merge(st, LAUNCHES, nb, (int)k, nsplit, pd, ps, pl, L.ids, out_d + q0 * k, out_l + q0 * k));
+        if (h->timing) {
+            CU(cudaStreamSynchronize(st));
+            float ms = 0;
+            CU(cudaEventElapsedTime(&ms, h->ev[0], h->ev[1])); h->stats.coarse_ms += ms;
+            CU(cudaEventElapsedTime(&ms, h->ev[1], h->ev[2])); h->stats.prep_ms += ms;
+            CU(cudaEventElapsedTime(&ms, h->ev[2], h->ev[3])); h->stats.scan_ms += ms;
+            h->stats.scan_launches += 1;
+        }
+        if (q0 == 0 && h->debug) {   // keep debug outputs of the first batch (copied lazily by last_thresholds)
+            h->last_thr.resize(nb);
+            h->last_scanned.resize(nb);
+            CU(cudaMemcpyAsync(h->last_thr.data(), T.threshold, (size_t)nb * 4, cudaMemcpyDeviceToHost, st));
+            CU(cudaMemcpyAsync(h->last_scanned.data(), T.nscanned, (size_t)nb * 4, cudaMemcpyDeviceToHost, st));
+            if (nq > qb) CU(cudaStreamSynchronize(st));  // T is reused by the next batch
+        }
+    }
+    h->stats.queries += nq;
+    return 0;
+}
+
+int ivfhnsw_b200_search_given_coarse_dev(ivfhnsw_b200_t *h, size_t nq, size_t k, const float *x_dev,
+                                         const float *cd_dev, const uint32_t *ci_dev, float *dd, int64_t *ld)
+{
+    if (bind(h)) return IVFHNSW_B200_ECUDA;
+    return search_core(h, nq, k, x_dev, cd_dev, ci_dev, dd, ld);
+}
+int ivfhnsw_b200_search_dev(ivfhnsw_b200_t *h, size_t nq, size_t k, const float *x_dev, float *dd, int64_t *ld)
+{
+    if (bind(h)) return IVFHNSW_B200_ECUDA;
+    return search_core(h, nq, k, x_dev, nullptr, nullptr, dd, ld);
+}
+
+static int search_host(ivfhnsw_b200_t *h, size_t nq, size_t k, const float *x, const float *cd, const uint32_t *ci,
+                       float *distances, int64_t *labels)
+{
+    if (bind(h)) return IVFHNSW_B200_ECUDA;
+    if (nq == 0) return 0;
+    cudaStream_t st = h->stream;
+    const size_t np = h->nprobe;
+    CU(h->w_x.ensure(nq * h->d * 4));
+    CU(h->w_out_d.ensure(nq * k * 4));
+    CU(h->w_out_l.ensure(nq * k * 8));
+    CU(cudaMemcpyAsync(h->w_x.p, x, nq * h->d * 4, cudaMemcpyHostToDevice, st));
+    const float *cdd = nullptr;
+    const uint32_t *cid = nullptr;
+    if (cd) {
+        CU(h->w_e.ensure(nq * np * 4));
+        CU(h->w_f.ensure(nq * np * 4));
+        CU(cudaMemcpyAsync(h->w_e.p, cd, nq * np * 4, cudaMemcpyHostToDevice, st));
+        CU(cudaMemcpyAsync(h->w_f.p, ci, nq * np * 4, cudaMemcpyHostToDevice, st));
+        cdd = h->w_e.as<float>();
+        cid = h->w_f.as<uint32_t>();
+    }
+    if (int r = search_core(h, nq, k, h->w_x.as<float>(), cdd, cid, h->w_out_d.as<float>(), h->w_out_l.as<int64_t>()))
+        return r;
+    CU(cudaMemcpyAsync(distances, h->w_out_d.p, nq * k * 4, cudaMemcpyDeviceToHost, st));
+    CU(cudaMemcpyAsync(labels, h->w_out_l.p, nq * k * 8, cudaMemcpyDeviceToHost, st));
+    CU(cudaStreamSynchronize(st));
+    return 0;
+}
+
+int ivfhnsw_b200_search(ivfhnsw_b200_t *h, size_t nq, size_t k, const float *x, float *distances, int64_t *labels)
+{
+    return search_host(h, nq, k, x, nullptr, nullptr, distances, labels);
+}
+int ivfhnsw_b200_search_given_coarse(ivfhnsw_b200_t *h, size_t nq, size_t k, const float *x, const float *cd,
+                                     const uint32_t *ci, float *distances, int64_t *labels)
+{
+    if (!cd || !ci) return h->fail(IVFHNSW_B200_EINVAL, "coarse candidates missing");
+    return search_host(h, nq, k, x, cd, ci, distances, labels);
+}
+
+int ivfhnsw_b200_get_stats(ivfhnsw_b200_t *h, ivfhnsw_b200_stats_t *out)
+{
+    if (bind(h)) return IVFHNSW_B200_ECUDA;
+    unsigned long long c[8] = {0};
+    CU(cudaStreamSynchronize(h->stream));
+    CU(cudaMemcpy(c, h->counters.p, 64, cudaMemcpyDeviceToHost));
+    h->stats.scanned_codes = c[0];
+    h->stats.walked_codes = c[1];
+    *out = h->stats;
+    if (c[4] & 0xffffffffull)
+        return h->fail(IVFHNSW_B200_ECUDA, "coarse select overflow flags 0x%llx (raise coarse_slack)", c[4] & 0xffffffffull);
+    return 0;
+}
+int ivfhnsw_b200_reset_stats(ivfhnsw_b200_t *h)
+{
+    if (bind(h)) return IVFHNSW_B200_ECUDA;
+    CU(cudaStreamSynchronize(h->stream));
+    CU(cudaMemset(h->counters.p, 0, 64));
+    h->stats = ivfhnsw_b200_stats_t{};
+    return 0;
+}
+int ivfhnsw_b200_last_thresholds(ivfhnsw_b200_t *h, size_t cap, float *thresholds, uint32_t *scanned)
+{
+    if (bind(h)) return IVFHNSW_B200_ECUDA;
+    CU(cudaStreamSynchronize(h->stream));
+    const size_t n = std::min(cap, h->last_thr.size());
+    if (thresholds) memcpy(thresholds, h->last_thr.data(), n * 4);
+    if (scanned) memcpy(scanned, h->last_scanned.data(), n * 4);
+    return (int)n;
+}
+
+}  // extern "C"

@@ -1,0 +1,295 @@
+// Coarse stage (K-A1 / K-A2 / K-G3): exact nearest centroids as a GEMM with a fused
+// "best COARSE_T of every group of COARSE_GROUP centroids" epilogue, followed by a per-query
+// select + verify + exact fp32 re-rank.
+//
+// Replaces hnswlib::HierarchicalNSW::searchKnn as used by
+//   IndexIVF_HNSW::assign                (IndexIVF_HNSW.cpp:68-72)     nprobe = 1
+//   IndexIVF_HNSW::search                (IndexIVF_HNSW.cpp:248-259)   nprobe nearest, ascending
+//   IndexIVF_HNSW_Grouping::add_group    (IndexIVF_HNSW_Grouping.cpp:47-63) nsubc nearest other centroids
+// with an EXACT search.  Output distances use the reference's fstdistfunc numerics
+// (hnswlib/hnswalg.cpp:326-356: floor(d/16)*16 dims, 8 partial sums).
+//
+// Exactness argument: the GEMM keeps, per (query, group), the COARSE_T smallest approximate
+// distances.  Let tau be the K'-th smallest kept value (K' = nprobe + slack).  Any element a group
+// did NOT keep is >= that group's COARSE_T-th kept value; so if that value is > tau the group hides
+// nothing that could be among the K' best.  Groups that fail the test are expanded in full.
+// The K' (+ expansions) candidates are then re-ranked with exact fp32 distances.
+#include "common.cuh"
+#include "kernels.h"
+
+namespace ivfb200 {
+
+// ---------------------------------------------------------------------------------------------
+// impl 0: fp32 SIMT tile GEMM, 128 queries x 128 centroids per CTA, 8x8 micro-tiles.
+// value(q, c) = ||c||^2 - 2 <q, c>   (||q||^2 is constant per query and irrelevant for ranking)
+// ---------------------------------------------------------------------------------------------
+#define CG_BM 128
+#define CG_BN COARSE_GROUP
+#define CG_BK 8
+
+__global__ void __launch_bounds__(256) coarse_gemm_simt_kernel(int nq, int nc, int d, const float *__restrict__ Q,
+                                                               const float *__restrict__ Cn,
+                                                               const float *__restrict__ cnorm, int self_off,
+                                                               float *__restrict__ grp_val,
+                                                               uint32_t *__restrict__ grp_idx)
+{
+    extern __shared__ __align__(16) float sm[];
+    float *As = sm;                      // [CG_BK][CG_BM]
+    float *Bs = As + CG_BK * CG_BM;      // [CG_BK][CG_BN]
+    float *D = Bs + CG_BK * CG_BN;       // [CG_BM][CG_BN + 1]
+    const int tid = threadIdx.x, tx = tid & 15, ty = tid >> 4;
+    const int g = blockIdx.x, ngroups = gridDim.x;
+    const int q0 = blockIdx.y * CG_BM, c0 = g * CG_BN;
+    float acc[8][8];
+#pragma unroll
+    for (int i = 0; i < 8; i++)
+#pragma unroll
+        for (int j = 0; j < 8; j++) acc[i][j] = 0.f;
+
+    const int lrow = tid >> 1, lk = (tid & 1) * 4;
+    for (int k0 = 0; k0 < d; k0 += CG_BK) {
+        float4 av = make_float4(0, 0, 0, 0), bv = make_float4(0, 0, 0, 0);
+        if (q0 + lrow < nq && k0 + lk < d) av = *reinterpret_cast<const float4 *>(Q + (size_t)(q0 + lrow) * d + k0 + lk);
+        if (c0 + lrow < nc && k0 + lk < d) bv = *reinterpret_cast<const float4 *>(Cn + (size_t)(c0 + lrow) * d + k0 + lk);
+        As[(lk + 0) * CG_BM + lrow] = av.x; As[(lk + 1) * CG_BM + lrow] = av.y;
+        As[(lk + 2) * CG_BM + lrow] = av.z; As[(lk + 3) * CG_BM + lrow] = av.w;
+        Bs[(lk + 0) * CG_BN + lrow] = bv.x; Bs[(lk + 1) * CG_BN + lrow] = bv.y;
+        Bs[(lk + 2) * CG_BN + lrow] = bv.z; Bs[(lk + 3) * CG_BN + lrow] = bv.w;
+        __syncthreads();
+#pragma unroll
+        for (int kk = 0; kk < CG_BK; kk++) {
+            float a[8], b[8];
+            const float4 a0 = *reinterpret_cast<const float4 *>(As + kk * CG_BM + ty * 8);
+            const float4 a1 = *reinterpret_cast<const float4 *>(As + kk * CG_BM + ty * 8 + 4);
+            const float4 b0 = *reinterpret_cast<const float4 *>(Bs + kk * CG_BN + tx * 8);
+            const float4 b1 = *reinterpret_cast<const float4 *>(Bs + kk * CG_BN + tx * 8 + 4);
+            a[0] = a0.x; a[1] = a0.y; a[2] = a0.z; a[3] = a0.w; a[4] = a1.x; a[5] = a1.y; a[6] = a1.z; a[7] = a1.w;
+            b[0] = b0.x; b[1] = b0.y; b[2] = b0.z; b[3] = b0.w; b[4] = b1.x; b[5] = b1.y; b[6] = b1.z; b[7] = b1.w;
+#pragma unroll
+            for (int i = 0; i < 8; i++)
+#pragma unroll
+                for (int j = 0; j < 8; j++) acc[i][j] = fmaf(a[i], b[j], acc[i][j]);
+        }
+        __syncthreads();
+    }
+#pragma unroll
+    for (int j = 0; j < 8; j++) {
+        const int c = c0 + tx * 8 + j;
+        const float cn = c < nc ? cnorm[c] : 0.f;
+#pragma unroll
+        for (int i = 0; i < 8; i++) {
+            const int q = q0 + ty * 8 + i;
+            float v = cn - 2.f * acc[i][j];
+            if (c >= nc || (self_off >= 0 && c == q + self_off)) v = __int_as_float(0x7f800000);
+            D[(ty * 8 + i) * (CG_BN + 1) + tx * 8 + j] = v;
+        }
+    }
+    __syncthreads();
+    if (tid < CG_BM && q0 + tid < nq) {
+        float v[COARSE_T];
+        uint32_t ix[COARSE_T];
+#pragma unroll
+        for (int t = 0; t < COARSE_T; t++) { v[t] = __int_as_float(0x7f800000); ix[t] = 0xffffffffu; }
+        const float *row = D + tid * (CG_BN + 1);
+        for (int j = 0; j < CG_BN; j++) {
+            float x = row[j];
+            if (x < v[COARSE_T - 1]) {
+                uint32_t xi = (uint32_t)(c0 + j);
+#pragma unroll
+                for (int t = 0; t < COARSE_T; t++) {
+                    if (x < v[t]) {
+                        const float tv = v[t]; const uint32_t ti = ix[t];
+                        v[t] = x; ix[t] = xi; x = tv; xi = ti;
+                    }
+                }
+            }
+        }
+        const size_t o = ((size_t)(q0 + tid) * ngroups + g) * COARSE_T;
+#pragma unroll
+        for (int t = 0; t < COARSE_T; t++) { grp_val[o + t] = v[t]; grp_idx[o + t] = ix[t]; }
+    }
+}
+
+// ---------------------------------------------------------------------------------------------
+// select + verify + exact re-rank.  One CTA per query.
+// ---------------------------------------------------------------------------------------------
+static __device__ __forceinline__ uint32_t fkey(float f)
+{
+    const uint32_t b = __float_as_uint(f);
+    return (b & 0x80000000u) ? ~b : (b | 0x80000000u);
+}
+
+#define SEL_MAX_FLAGGED 32
+
+__global__ void __launch_bounds__(256) coarse_select_kernel(int nc, int d, int ngroups, int nprobe, int kprime,
+                                                            int cand_cap, const float *__restrict__ Q,
+                                                            const float *__restrict__ Cn,
+                                                            const float *__restrict__ grp_val,
+                                                            const uint32_t *__restrict__ grp_idx,
+                                                            int self_off, uint32_t *__restrict__ err,
+                                                            float *__restrict__ out_d, uint32_t *__restrict__ out_i)
+{
+    extern __shared__ __align__(16) uint8_t smraw[];
+    float *sq = reinterpret_cast<float *>(smraw);                 // [d]
+    uint32_t *cand = reinterpret_cast<uint32_t *>(sq + d);        // [cand_cap]
+    float *cand_d = reinterpret_cast<float *>(cand + cand_cap);   // [cand_cap]
+    __shared__ uint32_t hist[256];
+    __shared__ uint32_t s_prefix, s_remaining, s_ncand, s_nflag, s_less;
+    __shared__ uint32_t s_flag[SEL_MAX_FLAGGED];
+    const int q = blockIdx.x, tid = threadIdx.x;
+    const int n = ngroups * COARSE_T;
+    const float *gv = grp_val + (size_t)q * n;
+    const uint32_t *gi = grp_idx + (size_t)q * n;
+    for (int i = tid; i < d; i += 256) sq[i] = Q[(size_t)q * d + i];
+    if (tid == 0) { s_prefix = 0; s_remaining = (uint32_t)kprime; s_ncand = 0; s_nflag = 0; s_less = 0; }
+    __syncthreads();
+
+    // ---- radix select: key of the kprime-th smallest kept value
+    for (int pass = 0; pass < 4; pass++) {
+        const int shift = 24 - 8 * pass;
+        hist[tid] = 0;
+        __syncthreads();
+        const uint32_t prefix = s_prefix;
+        const uint32_t pmask = pass == 0 ? 0u : (0xffffffffu << (shift + 8));
+        for (int i = tid; i < n; i += 256) {
+            const uint32_t kx = fkey(gv[i]);
+            if ((kx & pmask) == prefix) atomicAdd(&hist[(kx >> shift) & 255u], 1u);
+        }
+        __syncthreads();
+        if (tid == 0) {
+            uint32_t rem = s_remaining, cum = 0;
+            int b = 0;
+            for (; b < 256; b++) {
+                if (cum + hist[b] >= rem) break;
+                cum += hist[b];
+            }
+            if (b == 256) b = 255;  // kprime > n cannot happen (host clamps)
+            s_prefix = prefix | ((uint32_t)b << shift);
+            s_remaining = rem - cum;
+            s_less += cum;
+        }
+        __syncthreads();
+    }
+    const uint32_t tau = s_prefix;       // key of the kprime-th smallest
+    // ---- verify groups: a group whose COARSE_T-th kept value is <= tau may hide candidates
+    for (int g = tid; g < ngroups; g += 256) {
+        if (fkey(gv[g * COARSE_T + COARSE_T - 1]) <= tau && gi[g * COARSE_T + COARSE_T - 1] != 0xffffffffu) {
+            const uint32_t f = atomicAdd(&s_nflag, 1u);
+            if (f < SEL_MAX_FLAGGED) s_flag[f] = (uint32_t)g;
+        }
+    }
+    __syncthreads();
+    uint32_t nflag = s_nflag;
+    if (nflag > SEL_MAX_FLAGGED) {
+        if (tid == 0) atomicOr(err, 1u);
+        nflag = SEL_MAX_FLAGGED;
+    }
+    // ---- collect: kept entries with key <= tau outside flagged groups, then flagged groups in full
+    for (int i = tid; i < n; i += 256) {
+        const uint32_t kx = fkey(gv[i]);
+        const uint32_t id = gi[i];
+        if (kx <= tau && id != 0xffffffffu) {
+            const uint32_t g = (uint32_t)(i / COARSE_T);
+            bool flagged = false;
+            for (uint32_t f = 0; f < nflag; f++) flagged |= (s_flag[f] == g);
+            if (!flagged) {
+                const uint32_t p = atomicAdd(&s_ncand, 1u);
+                if (p < (uint32_t)cand_cap) cand[p] = id;
+            }
+        }
+    }
+    __syncthreads();
+    for (uint32_t f = 0; f < nflag; f++) {
+        const uint32_t g = s_flag[f];
+        for (int j = tid; j < COARSE_GROUP; j += 256) {
+            const uint32_t id = g * COARSE_GROUP + j;
+            if (id < (uint32_t)nc && !(self_off >= 0 && id == (uint32_t)(q + self_off))) {
+                const uint32_t p = atomicAdd(&s_ncand, 1u);
+                if (p < (uint32_t)cand_cap) cand[p] = id;
+            }
+        }
+    }
+    __syncthreads();
+    uint32_t ncand = s_ncand;
+    if (ncand > (uint32_t)cand_cap) {   // ties at tau can exceed the slack: flag, keep what fits
+        if (tid == 0) atomicOr(err, 2u);
+        ncand = cand_cap;
+    }
+    // ---- exact distances, reference numerics (8 lanes per candidate)
+    const int lane = tid & 31, warp = tid >> 5, oct = lane >> 3, sub = lane & 7;
+    for (uint32_t e0 = warp * 4; e0 < ncand; e0 += 32) {
+        const uint32_t e = e0 + oct;
+        const uint32_t id = e < ncand ? cand[e] : 0u;
+        const float dist = l2sqr16_octet(sq, Cn + (size_t)id * d, d, sub);
+        if (e < ncand && sub == 0) cand_d[e] = dist;
+    }
+    __syncthreads();
+    // ---- rank by (dist, idx) ascending == unload order of priority_queue<pair<float, idx_t>>
+    for (uint32_t e = tid; e < ncand; e += 256) {
+        const float ed = cand_d[e];
+        const uint32_t ei = cand[e];
+        uint32_t rank = 0;
+        for (uint32_t o = 0; o < ncand; o++) rank += key_less(cand_d[o], cand[o], ed, ei) ? 1u : 0u;
+        if (rank < (uint32_t)nprobe) {
+            out_d[(size_t)q * nprobe + rank] = ed;
+            out_i[(size_t)q * nprobe + rank] = ei;
+        }
+    }
+    if (ncand < (uint32_t)nprobe) {
+        if (tid == 0) atomicOr(err, 4u);
+        for (uint32_t r = ncand + tid; r < (uint32_t)nprobe; r += 256) {
+            out_d[(size_t)q * nprobe + r] = FLT_MAX;
+            out_i[(size_t)q * nprobe + r] = 0;
+        }
+    }
+}
+
+size_t coarse_work_bytes(int nq, int nc, int kprime, int *cand_cap)
+{
+    const size_t ngroups = (nc + COARSE_GROUP - 1) / COARSE_GROUP;
+    *cand_cap = kprime + 64 + COARSE_GROUP * SEL_MAX_FLAGGED;
+    return (size_t)nq * ngroups * COARSE_T * 8 + 256;
+}
+
+cudaError_t launch_coarse_tc(cudaStream_t st, uint64_t *launches, int nq, int nc, int d, const float *queries,
+                             const void *cent_bf16, void *xq_bf16, const float *cnorm_gemm, int self_off,
+                             float *grp_val, uint32_t *grp_idx);  // coarse_tc.cu
+
+cudaError_t launch_coarse(cudaStream_t st, uint64_t *launches, int impl, int nq, int nc, int d, int nprobe,
+                          int slack, const float *queries, const float *centroids, const float *cnorm_gemm,
+                          const void *cent_bf16, void *xq_bf16, const CoarseWork &W, int self_off,
+                          float *out_d, uint32_t *out_i)
+{
+    if (nq == 0) return cudaSuccess;
+    const int ngroups = (nc + COARSE_GROUP - 1) / COARSE_GROUP;
+    cudaError_t e;
+    if (impl == 1) {
+        e = launch_coarse_tc(st, launches, nq, nc, d, queries, cent_bf16, xq_bf16, cnorm_gemm, self_off,
+                             W.grp_val, W.grp_idx);
+        if (e != cudaSuccess) return e;
+    } else {
+        const size_t sm = (size_t)(CG_BK * CG_BM + CG_BK * CG_BN + CG_BM * (CG_BN + 1)) * sizeof(float);
+        e = cudaFuncSetAttribute(coarse_gemm_simt_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sm);
+        if (e != cudaSuccess) return e;
+        dim3 grid(ngroups, (nq + CG_BM - 1) / CG_BM);
+        coarse_gemm_simt_kernel<<<grid, 256, sm, st>>>(nq, nc, d, queries, centroids, cnorm_gemm, self_off,
+                                                      W.grp_val, W.grp_idx);
+        ++*launches;
+        e = cudaGetLastError();
+        if (e != cudaSuccess) return e;
+    }
+    int avail = nc - (self_off >= 0 ? 1 : 0);
+    int kprime = nprobe + slack;
+    if (kprime > avail) kprime = avail;
+    if (kprime > ngroups * COARSE_T) kprime = ngroups * COARSE_T;
+    if (kprime < 1) kprime = 1;
+    const size_t sm2 = (size_t)d * 4 + (size_t)W.cand_cap * 8;
+    e = cudaFuncSetAttribute(coarse_select_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sm2);
+    if (e != cudaSuccess) return e;
+    coarse_select_kernel<<<nq, 256, sm2, st>>>(nc, d, ngroups, nprobe, kprime, W.cand_cap, queries, centroids,
+                                               W.grp_val, W.grp_idx, self_off, W.err, out_d, out_i);
+    ++*launches;
+    return cudaGetLastError();
+}
+
+}  // namespace ivfb200

@@ -1,0 +1,78 @@
+// Shared device/host helpers for the ivfhnsw_b200 kernels (sm_100a only).
+#pragma once
+#include <cuda_runtime.h>
+#include <cstdint>
+#include <cstdio>
+#include <cfloat>
+
+#define IVF_FULL_MASK 0xffffffffu
+#define IVF_INVALID_SLOT 0xffffffffu
+
+// ADC scan geometry
+#define SCAN_THREADS 256
+#define SCAN_WARPS 8
+#define SCAN_CHUNK 32                      // codes per warp step (one per lane)
+#define SCAN_PIECE_CHUNKS 4                // chunks a warp keeps in flight
+#define SCAN_PIECE (SCAN_CHUNK * SCAN_PIECE_CHUNKS)
+#define SCAN_WCAP 64                       // per-warp candidate buffer entries
+
+// coarse stage geometry: centroids are processed in groups of COARSE_GROUP, the
+// GEMM epilogue keeps the COARSE_T best of each group per query
+#define COARSE_GROUP 128
+#define COARSE_T 4
+
+static __device__ __forceinline__ uint32_t lane_id() { return threadIdx.x & 31; }
+
+static __device__ __forceinline__ uint32_t prmt(uint32_t a, uint32_t b, uint32_t sel)
+{
+    uint32_t d;
+    asm("prmt.b32 %0, %1, %2, %3;" : "=r"(d) : "r"(a), "r"(b), "r"(sel));
+    return d;
+}
+
+// streaming 128-bit / 64-bit loads that do not pollute L1
+static __device__ __forceinline__ uint4 ldg_stream_128(const void *p)
+{
+    uint4 r;
+    asm volatile("ld.global.nc.L1::no_allocate.v4.u32 {%0,%1,%2,%3}, [%4];"
+                 : "=r"(r.x), "=r"(r.y), "=r"(r.z), "=r"(r.w) : "l"(p));
+    return r;
+}
+static __device__ __forceinline__ uint2 ldg_stream_64(const void *p)
+{
+    uint2 r;
+    asm volatile("ld.global.nc.L1::no_allocate.v2.u32 {%0,%1}, [%2];" : "=r"(r.x), "=r"(r.y) : "l"(p));
+    return r;
+}
+static __device__ __forceinline__ uint32_t ldg_stream_u8(const uint8_t *p)
+{
+    uint32_t r;
+    asm volatile("ld.global.nc.L1::no_allocate.u8 %0, [%1];" : "=r"(r) : "l"(p));
+    return r;
+}
+
+// (distance, sequence) lexicographic "a before b"
+static __device__ __forceinline__ bool key_less(float da, uint32_t sa, float db, uint32_t sb)
+{
+    return da < db || (da == db && sa < sb);
+}
+
+// ivfhnsw::fvec_L2sqr (reference utils.cpp:22-51) lane structure: 8 partial sums over
+// floor(d/16)*16 dims, partials added left to right.  Executed by 8 consecutive lanes
+// (sub = lane & 7); every lane of the octet returns the result.
+static __device__ __forceinline__ float l2sqr16_octet(const float *__restrict__ x, const float *__restrict__ y,
+                                                      int d, int sub)
+{
+    const int n = (d >> 4) << 4;
+    float acc = 0.f;
+    for (int i = sub; i < n; i += 8) {
+        const float df = x[i] - y[i];
+        acc = fmaf(df, df, acc);
+    }
+    const uint32_t lane = lane_id();
+    const int base = lane & ~7;
+    float r = __shfl_sync(IVF_FULL_MASK, acc, base);
+#pragma unroll
+    for (int l = 1; l < 8; l++) r += __shfl_sync(IVF_FULL_MASK, acc, base + l);
+    return r;
+}

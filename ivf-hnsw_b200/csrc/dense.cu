@@ -1,0 +1,90 @@
+// Small dense helpers: OPQ rotation (K-R1), row norms (K-N), u8 -> f32 expansion.
+#include "common.cuh"
+#include "kernels.h"
+
+namespace ivfb200 {
+
+// LinearTransform::apply_noalloc / transform_transpose (faiss/VectorTransform.cpp:106-158) for a
+// d x d matrix without bias.  8 rows per CTA staged in shared memory; thread o owns output column o.
+template <bool TRANSPOSE>
+__global__ void __launch_bounds__(128) rotate_kernel(size_t n, int d, const float *__restrict__ A,
+                                                     const float *__restrict__ x, float *__restrict__ out)
+{
+    extern __shared__ float sx[];  // [8][d]
+    const size_t row0 = (size_t)blockIdx.x * 8;
+    const int rows = (int)((n - row0) < 8 ? (n - row0) : 8);
+    for (int i = threadIdx.x; i < rows * d; i += blockDim.x) sx[i] = x[row0 * d + i];
+    __syncthreads();
+    for (int o = threadIdx.x; o < d; o += blockDim.x) {
+        float acc[8];
+#pragma unroll
+        for (int r = 0; r < 8; r++) acc[r] = 0.f;
+        for (int j = 0; j < d; j++) {
+            const float a = TRANSPOSE ? __ldg(A + (size_t)j * d + o) : __ldg(A + (size_t)o * d + j);
+#pragma unroll
+            for (int r = 0; r < 8; r++) acc[r] = fmaf(a, sx[r * d + j], acc[r]);
+        }
+        for (int r = 0; r < rows; r++) out[(row0 + r) * d + o] = acc[r];
+    }
+}
+
+cudaError_t launch_rotate(cudaStream_t st, uint64_t *launches, size_t n, int d, const float *A, bool transpose,
+                          const float *x, float *out)
+{
+    if (n == 0) return cudaSuccess;
+    const unsigned grid = (unsigned)((n + 7) / 8);
+    const size_t sm = (size_t)8 * d * sizeof(float);
+    if (transpose) rotate_kernel<true><<<grid, 128, sm, st>>>(n, d, A, x, out);
+    else rotate_kernel<false><<<grid, 128, sm, st>>>(n, d, A, x, out);
+    ++*launches;
+    return cudaGetLastError();
+}
+
+// faiss::fvec_norm_L2sqr (faiss/utils.cpp:632-650): 4 partial sums, (s0+s1)+(s2+s3).
+// Four consecutive lanes per row.
+__global__ void row_norms_kernel(size_t n, int d, const float *__restrict__ x, float *__restrict__ out)
+{
+    const size_t t = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+    const size_t row = t >> 2;
+    const int sub = (int)(t & 3);
+    float acc = 0.f;
+    if (row < n) {
+        const float *r = x + row * d;
+        for (int i = sub; i < d; i += 4) acc = fmaf(r[i], r[i], acc);
+    }
+    const int lane = threadIdx.x & 31, b = lane & ~3;
+    const float s0 = __shfl_sync(IVF_FULL_MASK, acc, b), s1 = __shfl_sync(IVF_FULL_MASK, acc, b + 1);
+    const float s2 = __shfl_sync(IVF_FULL_MASK, acc, b + 2), s3 = __shfl_sync(IVF_FULL_MASK, acc, b + 3);
+    if (row < n && sub == 0) out[row] = (s0 + s1) + (s2 + s3);
+}
+
+cudaError_t launch_row_norms(cudaStream_t st, uint64_t *launches, size_t n, int d, const float *x, float *out)
+{
+    if (n == 0) return cudaSuccess;
+    const size_t threads = n * 4;
+    row_norms_kernel<<<(unsigned)((threads + 255) / 256), 256, 0, st>>>(n, d, x, out);
+    ++*launches;
+    return cudaGetLastError();
+}
+
+__global__ void u8_to_f32_kernel(size_t n4, const uchar4 *__restrict__ x, float4 *__restrict__ out)
+{
+    for (size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < n4; i += (size_t)gridDim.x * blockDim.x) {
+        const uchar4 v = x[i];
+        out[i] = make_float4((float)v.x, (float)v.y, (float)v.z, (float)v.w);
+    }
+}
+
+cudaError_t launch_u8_to_f32(cudaStream_t st, uint64_t *launches, size_t n, const uint8_t *x, float *out)
+{
+    if (n == 0) return cudaSuccess;
+    const size_t n4 = n / 4;  // callers pass n = rows * d with d % 4 == 0
+    size_t blocks = (n4 + 255) / 256;
+    if (blocks > 148 * 16) blocks = 148 * 16;
+    u8_to_f32_kernel<<<(unsigned)blocks, 256, 0, st>>>(n4, reinterpret_cast<const uchar4 *>(x),
+                                                     reinterpret_cast<float4 *>(out));
+    ++*launches;
+    return cudaGetLastError();
+}
+
+}  // namespace ivfb200

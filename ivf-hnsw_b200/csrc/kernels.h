@@ -1,0 +1,106 @@
+// Host-callable launchers of the ivfhnsw_b200 kernels.  Every launcher enqueues on
+// `st`, returns the cudaError of the launch and bumps *launches by the kernels it issued.
+#pragma once
+#include <cuda_runtime.h>
+#include <cstddef>
+#include <cstdint>
+
+namespace ivfb200 {
+
+// ----------------------------------------------------------------------------- index (device CSR)
+struct DeviceLists {
+    // slot space: list c occupies slots [list_slot[c], list_slot[c] + list_size[c]); list starts are
+    // aligned to `align` slots (16 for M <= 16, 32 otherwise) and the arrays end with 32 pad slots.
+    const uint32_t *list_size;   // [nc]
+    const uint32_t *list_slot;   // [nc]
+    const uint8_t *codes;        // [nslots][M], byte-permuted per slot (see scan.cu)
+    const uint8_t *norm_codes;   // [nslots]
+    const uint8_t *sub_ids;      // [nslots] sub-group of each code (Grouping) or nullptr
+    const uint32_t *ids;         // [nslots]
+    // grouping metadata (nullptr for IVFADC)
+    const uint32_t *nn_idx;      // [nc][nsubc]
+    const uint32_t *sub_sizes;   // [nc][nsubc]
+    const float *alphas;         // [nc]
+    const float *icd;            // [nc][nsubc]
+    const float *centroid_norms; // [nc]
+    const float *centroids;      // [nc][d]  (search-time table, i.e. rotated when OPQ)
+};
+
+// per-query segment tables produced by the prep kernels, consumed by the scan kernel
+struct SegTables {
+    uint32_t *slot;       // [nq][nprobe]   first slot of the probed list
+    uint32_t *n;          // [nq][nprobe]   codes to walk (0 = skipped / empty / after cut-off / not owned)
+    float *base;          // [nq][nprobe]   term1 (IVFADC) -- Grouping uses sub_base instead
+    uint32_t *seq;        // [nq][nprobe]   scan-order number of the list's first code
+    uint32_t *piece_off;  // [nq][nprobe+1] exclusive prefix of ceil(n / SCAN_PIECE)
+    float *sub_base;      // [nq][nprobe][nsubc] term1+term2 per sub-group, +inf = pruned/empty (Grouping)
+    float *qsd;           // [nq][nprobe][nsubc] scratch: d(q, n_s), then query_subcentroid_dists
+    float *threshold;     // [nq]
+    uint32_t *nscanned;   // [nq] codes the reference rule scans
+    uint32_t *nwalked;    // [nq] codes the scan kernel streams
+};
+
+cudaError_t launch_prep_adc(cudaStream_t st, uint64_t *launches, int nq, int nprobe, uint64_t max_codes,
+                            const float *coarse_d, const uint32_t *coarse_i, const DeviceLists &L,
+                            uint32_t c_begin, uint32_t c_end, const SegTables &T);
+
+cudaError_t launch_prep_grouping(cudaStream_t st, uint64_t *launches, int nq, int d, int nprobe, int nsubc,
+                                 uint64_t max_codes, bool do_pruning, const float *queries,
+                                 const float *coarse_d, const uint32_t *coarse_i, const DeviceLists &L,
+                                 uint32_t c_begin, uint32_t c_end, const SegTables &T);
+
+size_t scan_smem_bytes(int M, int nprobe, int k, int nsubc);
+// partial outputs [nq][nsplit][k]; when nsplit == 1 the kernel writes the final (distances, labels) directly
+cudaError_t launch_scan(cudaStream_t st, uint64_t *launches, int M, bool grouping, int nq, int d, int nprobe,
+                        int nsubc, int k, int nsplit, const float *queries, const float *pqc,
+                        const float *norm_table, const DeviceLists &L, const SegTables &T, float *part_d,
+                        uint32_t *part_seq, uint32_t *part_slot, float *out_d, int64_t *out_labels);
+cudaError_t launch_merge(cudaStream_t st, uint64_t *launches, int nq, int k, int nsplit, const float *part_d,
+                         const uint32_t *part_seq, const uint32_t *part_slot, const uint32_t *ids,
+                         float *out_d, int64_t *out_labels);
+
+// ----------------------------------------------------------------------------- small dense helpers
+// out[n][d] = x[n][d] * A^T (transpose == false: y = A x per row, LinearTransform::apply_noalloc)
+//           = x[n][d] * A   (transpose == true : transform_transpose)
+cudaError_t launch_rotate(cudaStream_t st, uint64_t *launches, size_t n, int d, const float *A, bool transpose,
+                          const float *x, float *out);
+cudaError_t launch_row_norms(cudaStream_t st, uint64_t *launches, size_t n, int d, const float *x, float *out);
+cudaError_t launch_u8_to_f32(cudaStream_t st, uint64_t *launches, size_t n, const uint8_t *x, float *out);
+
+// ----------------------------------------------------------------------------- coarse stage
+struct CoarseWork {
+    float *grp_val;     // [nq][ngroups][COARSE_T]
+    uint32_t *grp_idx;  // [nq][ngroups][COARSE_T]
+    uint32_t *cand;     // [nq][cand_cap] candidate centroid ids
+    float *cand_d;      // [nq][cand_cap]
+    uint32_t *err;      // [1] sticky overflow flag
+    int cand_cap;
+};
+size_t coarse_work_bytes(int nq, int nc, int kprime, int *cand_cap);
+// exact top-`nprobe` (ascending (dist, idx), fstdistfunc numerics) of every query among `nc` centroids.
+// impl 0: fp32 SIMT tile GEMM; impl 1: tcgen05 bf16 GEMM (needs cent_bf16 / xq_bf16 scratch).
+cudaError_t launch_coarse(cudaStream_t st, uint64_t *launches, int impl, int nq, int nc, int d, int nprobe,
+                          int slack, const float *queries, const float *centroids, const float *cnorm_gemm,
+                          const void *cent_bf16, void *xq_bf16, const CoarseWork &W, int self_off /* -1 = none */,
+                          float *out_d, uint32_t *out_i);
+
+// ----------------------------------------------------------------------------- indexing
+// residual rows: out[i] = x[i] - base_row(i); base_row = centroid[idx[i]] or, for Grouping,
+// centroid[g] + alpha[g] * (centroid[nn_idx[g][sub[i]]] - centroid[g])
+cudaError_t launch_residual(cudaStream_t st, uint64_t *launches, size_t n, int d, const float *x,
+                            const uint32_t *idx, const uint8_t *sub, const float *centroids, const uint32_t *nn_idx,
+                            const float *alphas, int nsubc, float sign, const float *addend, float *out);
+cudaError_t launch_pq_encode(cudaStream_t st, uint64_t *launches, size_t n, int d, int M, const float *pqc,
+                             const float *residuals, uint8_t *codes);
+cudaError_t launch_pq_decode(cudaStream_t st, uint64_t *launches, size_t n, int d, int M, const float *pqc,
+                             const uint8_t *codes, float *out);
+cudaError_t launch_norm_encode(cudaStream_t st, uint64_t *launches, size_t n, int d, const float *recon,
+                               const float *norm_table, uint8_t *norm_codes, float *norms_out);
+// icd[c][s] = L2sqr16(centroid[nn_idx[c][s]], centroid[c])
+cudaError_t launch_gather_dists(cudaStream_t st, uint64_t *launches, int nrow, int per_row, int d,
+                                const float *rows_x, const uint32_t *idx, const float *table, float *out);
+cudaError_t launch_alpha_reduce(cudaStream_t st, uint64_t *launches, int nc, const uint32_t *grp_off,
+                                const float *num, const float *den, float *alphas);
+cudaError_t launch_hist(cudaStream_t st, uint64_t *launches, size_t n, const uint32_t *key, uint32_t *hist);
+
+}  // namespace ivfb200

@@ -1,0 +1,798 @@
+// ADC inverted-list scan for sm_100a: work-list construction (K-P / K-G1), the scan
+// itself with the per-query lookup table held in shared memory (K-L1 + K-S1/K-S2) and
+// the partial top-k merge (K-M1).
+//
+// Replaces, for a whole batch of queries at once, the body of
+//   IndexIVF_HNSW::search            IndexIVF_HNSW.cpp:262-293   (and search2, :453-492)
+//   IndexIVF_HNSW_Grouping::search   IndexIVF_HNSW_Grouping.cpp:222-353
+//
+// Data layout (what makes the table gathers bank-conflict free):
+//   * device codes are stored per slot with their bytes XOR-permuted by the lane that will
+//     read them: stored[t] = code[t ^ (slot & (min(M,32)-1))].  A warp reads 32 consecutive
+//     slots, one per lane, with one 128-bit load each (M = 16).
+//   * the per-query table lives in shared memory as 256 rows of 64 words (256 B).  Row j holds,
+//     for every sub-quantizer m, the value -2<q_m, c_{m,j}> at word R*m + copy (R = 32/M copies)
+//     and in words 32..63 the decoded norm norm_table[j] replicated 32 times.
+//     At step t lane l needs sub-quantizer m = t ^ (l % M), which it finds at word
+//     R*m + l/M: for a fixed t these 32 words are distinct banks whatever the code bytes are,
+//     and the norm lookup (word 32 + l) is conflict free as well.
+//   * a lookup address is built with ONE prmt: byte1 = code byte, byte0 = per-lane word offset.
+//
+// A CTA (8 warps) owns one (query, split); warps pull 128-code pieces of the query's segment
+// list from a shared counter, keep their candidates in a private buffer and merge them into the
+// CTA's top-k under a lock only when the buffer fills (rare once the threshold has dropped).
+#include "common.cuh"
+#include "kernels.h"
+
+namespace ivfb200 {
+
+// =============================================================================================
+// K-P: IVFADC work list.  One warp per query.  Reproduces the sequential max_codes rule of
+// IndexIVF_HNSW.cpp:267-293: lists are taken in rank order, empty lists are skipped, and the loop
+// stops AFTER the list that makes ncode >= max_codes  <=>  list i is scanned iff the sizes of the
+// lists before it sum to < max_codes.
+// =============================================================================================
+__global__ void prep_adc_kernel(int nq, int nprobe, uint64_t max_codes, const float *__restrict__ coarse_d,
+                                const uint32_t *__restrict__ coarse_i, DeviceLists L, uint32_t c_begin,
+                                uint32_t c_end, SegTables T)
+{
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const int q = blockIdx.x * (blockDim.x >> 5) + warp;
+    if (q >= nq) return;
+    uint64_t run = 0;
+    uint32_t run_pieces = 0, scanned = 0, walked = 0;
+    for (int base = 0; base < nprobe; base += 32) {
+        const int i = base + lane;
+        uint32_t c = 0, sz = 0;
+        float cd = 0.f;
+        if (i < nprobe) {
+            c = coarse_i[(size_t)q * nprobe + i];
+            cd = coarse_d[(size_t)q * nprobe + i];
+            sz = L.list_size[c];
+        }
+        uint64_t incl = sz;
+#pragma unroll
+        for (int off = 1; off < 32; off <<= 1) {
+            const uint64_t t = __shfl_up_sync(IVF_FULL_MASK, incl, off);
+            if (lane >= off) incl += t;
+        }
+        const uint64_t excl = run + incl - sz;
+        const bool active = (i < nprobe) && sz > 0 && excl < max_codes;
+        const bool owned = c >= c_begin && c < c_end;
+        const uint32_t n = (active && owned) ? sz : 0u;
+        const uint32_t pieces = (n + SCAN_PIECE - 1) / SCAN_PIECE;
+        uint32_t incl_p = pieces;
+#pragma unroll
+        for (int off = 1; off < 32; off <<= 1) {
+            const uint32_t t = __shfl_up_sync(IVF_FULL_MASK, incl_p, off);
+            if (lane >= off) incl_p += t;
+        }
+        if (i < nprobe) {
+            const size_t o = (size_t)q * nprobe + i;
+            T.slot[o] = L.list_slot[c];
+            T.n[o] = n;
+            T.base[o] = cd - L.centroid_norms[c];
+            T.seq[o] = (uint32_t)excl;
+            T.piece_off[(size_t)q * (nprobe + 1) + i] = run_pieces + incl_p - pieces;
+        }
+        run += __shfl_sync(IVF_FULL_MASK, incl, 31);
+        run_pieces += __shfl_sync(IVF_FULL_MASK, incl_p, 31);
+        uint32_t s = n;
+#pragma unroll
+        for (int off = 16; off > 0; off >>= 1) s += __shfl_xor_sync(IVF_FULL_MASK, s, off);
+        scanned += s;
+        walked += s;
+    }
+    if (lane == 0) {
+        T.piece_off[(size_t)q * (nprobe + 1) + nprobe] = run_pieces;
+        T.nscanned[q] = scanned;
+        T.nwalked[q] = walked;
+        T.threshold[q] = 0.f;
+    }
+}
+
+cudaError_t launch_prep_adc(cudaStream_t st, uint64_t *launches, int nq, int nprobe, uint64_t max_codes,
+                            const float *coarse_d, const uint32_t *coarse_i, const DeviceLists &L,
+                            uint32_t c_begin, uint32_t c_end, const SegTables &T)
+{
+    if (nq == 0) return cudaSuccess;
+    const int wpb = 4;
+    prep_adc_kernel<<<(nq + wpb - 1) / wpb, wpb * 32, 0, st>>>(nq, nprobe, max_codes, coarse_d, coarse_i, L,
+                                                              c_begin, c_end, T);
+    ++*launches;
+    return cudaGetLastError();
+}
+
+// =============================================================================================
+// K-G1a: distances from each query to the neighbour centroids n_s of every probed list
+// (the lazily memoised ivfhnsw::fvec_L2sqr calls of IndexIVF_HNSW_Grouping.cpp:246-250,312-316).
+// One CTA per query.  The memo semantics are kept: if n_s is itself one of the probed centroids
+// its distance is the coarse one (query_centroid_dists[n] was set at :207-220) unless that value
+// is < EPS, in which case the reference recomputes it.
+// Output: T.qsd[q][i][s] = d(q, n_s)   (0 where the list or the sub-group is empty)
+// =============================================================================================
+__global__ void __launch_bounds__(256) group_dqn_kernel(int d, int nprobe, int nsubc, int ht_size,
+                                                        const float *__restrict__ queries,
+                                                        const float *__restrict__ coarse_d,
+                                                        const uint32_t *__restrict__ coarse_i, DeviceLists L,
+                                                        SegTables T)
+{
+    extern __shared__ __align__(16) uint8_t sm[];
+    float *sq = reinterpret_cast<float *>(sm);                         // [d]
+    uint32_t *hk = reinterpret_cast<uint32_t *>(sq + d);               // [ht_size] keys
+    float *hv = reinterpret_cast<float *>(hk + ht_size);               // [ht_size] values
+    const int q = blockIdx.x, tid = threadIdx.x;
+    for (int i = tid; i < d; i += blockDim.x) sq[i] = queries[(size_t)q * d + i];
+    for (int i = tid; i < ht_size; i += blockDim.x) hk[i] = 0xffffffffu;
+    __syncthreads();
+    const uint32_t hmask = ht_size - 1;
+    for (int i = tid; i < nprobe; i += blockDim.x) {
+        const uint32_t c = coarse_i[(size_t)q * nprobe + i];
+        uint32_t p = (c * 2654435761u) & hmask;
+        while (true) {
+            const uint32_t prev = atomicCAS(&hk[p], 0xffffffffu, c);
+            if (prev == 0xffffffffu || prev == c) { hv[p] = coarse_d[(size_t)q * nprobe + i]; break; }
+            p = (p + 1) & hmask;
+        }
+    }
+    __syncthreads();
+    const int lane = tid & 31, warp = tid >> 5, oct = lane >> 3, sub = lane & 7;
+    const int npairs = nprobe * nsubc;
+    for (int e0 = warp * 4; e0 < npairs; e0 += (blockDim.x >> 5) * 4) {
+        const int e = e0 + oct;
+        bool need = false;
+        uint32_t n = 0;
+        float memo = 0.f;
+        bool have_memo = false;
+        if (e < npairs) {
+            const int i = e / nsubc, s = e - i * nsubc;
+            const uint32_t c = coarse_i[(size_t)q * nprobe + i];
+            if (L.list_size[c] != 0 && L.sub_sizes[(size_t)c * nsubc + s] != 0) {
+                need = true;
+                n = L.nn_idx[(size_t)c * nsubc + s];
+                uint32_t p = (n * 2654435761u) & hmask;
+                while (true) {
+                    const uint32_t kx = hk[p];
+                    if (kx == 0xffffffffu) break;
+                    if (kx == n) { memo = hv[p]; have_memo = memo >= 0.00001f; break; }
+                    p = (p + 1) & hmask;
+                }
+            }
+        }
+        const float dist = l2sqr16_octet(sq, L.centroids + (size_t)n * d, d, sub);
+        if (e < npairs && sub == 0)
+            T.qsd[(size_t)q * npairs + e] = need ? (have_memo ? memo : dist) : 0.f;
+    }
+}
+
+// =============================================================================================
+// K-G1b: pruning threshold, kept sub-groups, max_codes rule and segment tables for Grouping.
+// One warp (one block) per query.  Follows IndexIVF_HNSW_Grouping.cpp:222-262 and :283-353
+// including SURVEY.md 8(a) Q1: qsd rows exist only for non-empty lists, rows beyond the
+// 2*max_codes horizon stay 0, empty sub-groups are never looked at, and the threshold is the
+// SEQUENTIAL fp32 sum in (probe, sub-group) order divided by the count.
+// In : T.qsd[q][i][s] = d(q, n_s).   Out: T.sub_base[q][i][s] = term1 + term2 or +inf.
+// =============================================================================================
+__global__ void __launch_bounds__(32) prep_grouping_kernel(int nprobe, int nsubc, uint64_t max_codes,
+                                                           int do_pruning, const float *__restrict__ coarse_d,
+                                                           const uint32_t *__restrict__ coarse_i, DeviceLists L,
+                                                           uint32_t c_begin, uint32_t c_end, SegTables T)
+{
+    extern __shared__ __align__(16) uint8_t sm[];
+    uint32_t *s_c = reinterpret_cast<uint32_t *>(sm);     // [nprobe] centroid id
+    uint32_t *s_sz = s_c + nprobe;                        // [nprobe] list size
+    uint32_t *s_kept = s_sz + nprobe;                     // [nprobe] kept codes
+    uint8_t *s_inh = reinterpret_cast<uint8_t *>(s_kept + nprobe);  // [nprobe] inside pass-1 horizon
+    const int q = blockIdx.x, lane = threadIdx.x;
+    const size_t qo = (size_t)q * nprobe;
+    const int npairs = nprobe * nsubc;
+    float *qsd = T.qsd + (size_t)q * npairs;      // d(q, n_s)
+    float *sb = T.sub_base + (size_t)q * npairs;  // scratch for qsd values, then final bases
+
+    // ---- pass-1 horizon (:229-259): list i is visited iff non-empty and sum of earlier sizes < 2*max_codes
+    uint64_t run = 0;
+    for (int base = 0; base < nprobe; base += 32) {
+        const int i = base + lane;
+        uint32_t c = 0, sz = 0;
+        if (i < nprobe) { c = coarse_i[qo + i]; sz = L.list_size[c]; }
+        uint64_t incl = sz;
+#pragma unroll
+        for (int off = 1; off < 32; off <<= 1) {
+            const uint64_t t = __shfl_up_sync(IVF_FULL_MASK, incl, off);
+            if (lane >= off) incl += t;
+        }
+        const uint64_t excl = run + incl - sz;
+        if (i < nprobe) {
+            s_c[i] = c;
+            s_sz[i] = sz;
+            s_inh[i] = (sz > 0 && excl < 2 * max_codes) ? 1 : 0;
+        }
+        run += __shfl_sync(IVF_FULL_MASK, incl, 31);
+    }
+    __syncwarp();
+
+    // ---- qsd values (:251-252), NaN marks "does not contribute"
+    uint32_t count = 0;
+    if (do_pruning) {
+        for (int e = lane; e < npairs; e += 32) {
+            const int i = e / nsubc, s = e - i * nsubc;
+            const uint32_t c = s_c[i];
+            float v = __int_as_float(0x7fc00000);
+            if (s_inh[i] && L.sub_sizes[(size_t)c * nsubc + s] != 0) {
+                const float alpha = L.alphas[c];
+                const float oma = __fsub_rn(1.f, alpha);
+                const float term1 = __fmul_rn(oma, coarse_d[qo + i]);
+                const float inner = __fsub_rn(__fmul_rn(oma, L.icd[(size_t)c * nsubc + s]), qsd[e]);
+                v = __fsub_rn(term1, __fmul_rn(alpha, inner));
+                count++;
+            }
+            sb[e] = v;
+        }
+#pragma unroll
+        for (int off = 16; off > 0; off >>= 1) count += __shfl_xor_sync(IVF_FULL_MASK, count, off);
+    }
+    __syncwarp();
+    float threshold = 0.f;
+    if (do_pruning) {
+        // sequential sum in reference order: coalesced loads, then every lane replays the 32 values
+        // in order through shuffles (all lanes hold the same accumulator)
+        float acc = 0.f;
+        for (int e0 = 0; e0 < npairs; e0 += 32) {
+            const float mine = (e0 + lane < npairs) ? sb[e0 + lane] : __int_as_float(0x7fc00000);
+#pragma unroll
+            for (int j = 0; j < 32; j++) {
+                const float v = __shfl_sync(IVF_FULL_MASK, mine, j);
+                if (v == v) acc = __fadd_rn(acc, v);
+            }
+        }
+        threshold = acc / (float)count;  // count == 0 -> NaN like the reference's 0/0
+    }
+    __syncwarp();
+
+    // ---- pass 2 bookkeeping (:283-353): kept sub-groups and their bases
+    for (int i = 0; i < nprobe; i++) {
+        const uint32_t c = s_c[i];
+        uint32_t kept = 0;
+        if (s_sz[i] != 0) {
+            const float alpha = L.alphas[c];
+            const float oma = __fsub_rn(1.f, alpha);
+            const float term1 = __fmul_rn(oma, __fsub_rn(coarse_d[qo + i], L.centroid_norms[c]));
+            for (int s = lane; s < nsubc; s += 32) {
+                const int e = i * nsubc + s;
+                const uint32_t ss = L.sub_sizes[(size_t)c * nsubc + s];
+                float out = __int_as_float(0x7f800000);
+                if (ss != 0) {
+                    bool keep = true;
+                    if (do_pruning) {
+                        const float qv = s_inh[i] ? sb[e] : 0.f;  // rows past the horizon stay 0 (:228)
+                        keep = qv < threshold;
+                    }
+                    if (keep) {
+                        const uint32_t n = L.nn_idx[(size_t)c * nsubc + s];
+                        const float term2 = __fmul_rn(alpha, __fsub_rn(qsd[e], L.centroid_norms[n]));
+                        out = __fadd_rn(term1, term2);
+                        kept += ss;
+                    }
+                }
+                sb[e] = out;
+            }
+        }
+#pragma unroll
+        for (int off = 16; off > 0; off >>= 1) kept += __shfl_xor_sync(IVF_FULL_MASK, kept, off);
+        if (lane == 0) s_kept[i] = kept;
+    }
+    __syncwarp();
+
+    // ---- max_codes rule on the KEPT codes (:337,349) and segment tables
+    uint64_t run_k = 0, run_w = 0;
+    uint32_t run_pieces = 0, scanned = 0, walked = 0;
+    for (int base = 0; base < nprobe; base += 32) {
+        const int i = base + lane;
+        uint32_t c = 0, sz = 0, kp = 0;
+        if (i < nprobe) { c = s_c[i]; sz = s_sz[i]; kp = s_kept[i]; }
+        uint64_t incl_k = kp;
+#pragma unroll
+        for (int off = 1; off < 32; off <<= 1) {
+            const uint64_t t = __shfl_up_sync(IVF_FULL_MASK, incl_k, off);
+            if (lane >= off) incl_k += t;
+        }
+        const uint64_t excl_k = run_k + incl_k - kp;
+        const bool active = (i < nprobe) && sz > 0 && excl_k < max_codes;
+        const bool owned = c >= c_begin && c < c_end;
+        const uint32_t wsz = active ? sz : 0u;  // walk order numbering is global (all shards)
+        uint64_t incl_w = wsz;
+#pragma unroll
+        for (int off = 1; off < 32; off <<= 1) {
+            const uint64_t t = __shfl_up_sync(IVF_FULL_MASK, incl_w, off);
+            if (lane >= off) incl_w += t;
+        }
+        const uint32_t n = (active && owned && kp > 0) ? sz : 0u;
+        const uint32_t pieces = (n + SCAN_PIECE - 1) / SCAN_PIECE;
+        uint32_t incl_p = pieces;
+#pragma unroll
+        for (int off = 1; off < 32; off <<= 1) {
+            const uint32_t t = __shfl_up_sync(IVF_FULL_MASK, incl_p, off);
+            if (lane >= off) incl_p += t;
+        }
+        if (i < nprobe) {
+            T.slot[qo + i] = L.list_slot[c];
+            T.n[qo + i] = n;
+            T.base[qo + i] = 0.f;
+            T.seq[qo + i] = (uint32_t)(run_w + incl_w - wsz);
+            T.piece_off[(size_t)q * (nprobe + 1) + i] = run_pieces + incl_p - pieces;
+        }
+        run_k += __shfl_sync(IVF_FULL_MASK, incl_k, 31);
+        run_w += __shfl_sync(IVF_FULL_MASK, incl_w, 31);
+        run_pieces += __shfl_sync(IVF_FULL_MASK, incl_p, 31);
+        uint32_t a = (active && owned) ? kp : 0u, b = n;
+#pragma unroll
+        for (int off = 16; off > 0; off >>= 1) {
+            a += __shfl_xor_sync(IVF_FULL_MASK, a, off);
+            b += __shfl_xor_sync(IVF_FULL_MASK, b, off);
+        }
+        scanned += a;
+        walked += b;
+    }
+    if (lane == 0) {
+        T.piece_off[(size_t)q * (nprobe + 1) + nprobe] = run_pieces;
+        T.nscanned[q] = scanned;
+        T.nwalked[q] = walked;
+        T.threshold[q] = threshold;
+    }
+}
+
+cudaError_t launch_prep_grouping(cudaStream_t st, uint64_t *launches, int nq, int d, int nprobe, int nsubc,
+                                 uint64_t max_codes, bool do_pruning, const float *queries,
+                                 const float *coarse_d, const uint32_t *coarse_i, const DeviceLists &L,
+                                 uint32_t c_begin, uint32_t c_end, const SegTables &T)
+{
+    if (nq == 0) return cudaSuccess;
+    int ht = 64;
+    while (ht < 4 * nprobe) ht <<= 1;
+    const size_t sm1 = (size_t)d * 4 + (size_t)ht * 8;
+    cudaError_t e = cudaFuncSetAttribute(group_dqn_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sm1);
+    if (e != cudaSuccess) return e;
+    group_dqn_kernel<<<nq, 256, sm1, st>>>(d, nprobe, nsubc, ht, queries, coarse_d, coarse_i, L, T);
+    ++*launches;
+    e = cudaGetLastError();
+    if (e != cudaSuccess) return e;
+    const size_t sm2 = (size_t)nprobe * 13 + 16;
+    prep_grouping_kernel<<<nq, 32, sm2, st>>>(nprobe, nsubc, max_codes, do_pruning ? 1 : 0, coarse_d, coarse_i, L,
+                                              c_begin, c_end, T);
+    ++*launches;
+    return cudaGetLastError();
+}
+
+// =============================================================================================
+// K-L1 + K-S1/K-S2: the scan
+// =============================================================================================
+struct ScanArgs {
+    int d, nprobe, nsubc, k, nsplit;
+    const float *queries;     // [nq][d] (already OPQ-rotated)
+    const float *pqc;         // [M][256][dsub]
+    const float *norm_table;  // [256]
+    DeviceLists L;
+    SegTables T;
+    float *part_d;            // [nq][nsplit][k]
+    uint32_t *part_seq;
+    uint32_t *part_slot;
+    float *out_d;             // [nq][k]   (nsplit == 1)
+    int64_t *out_labels;
+};
+
+template <int M> struct ScanCfg {
+    static constexpr int ML = M < 32 ? M : 32;      // sub-quantizers resolved by the lane XOR
+    static constexpr int R = 32 / ML;               // table copies per sub-quantizer
+    static constexpr int NW = M / 4;                // 32-bit words per code
+    static constexpr int NO = ML / 4;               // packed per-lane offset registers
+    static constexpr int LUT_BYTES = 65536 + (M == 64 ? 32768 : 0);
+};
+
+static __host__ __device__ inline size_t scan_small_smem(int nprobe, int k, int nsubc)
+{
+    size_t b = 0;
+    b += (size_t)(5 * nprobe + 1) * 4;          // segment tables
+    b += (size_t)k * 12;                        // top-k
+    b += (size_t)SCAN_WARPS * SCAN_WCAP * 12;   // warp candidate buffers
+    b += (size_t)SCAN_WARPS * nsubc * 4;        // warp sub-group bases
+    b += 64;                                    // control words
+    return (b + 15) & ~(size_t)15;
+}
+
+size_t scan_smem_bytes(int M, int nprobe, int k, int nsubc)
+{
+    return (size_t)(M == 64 ? 98304 : 65536) + scan_small_smem(nprobe, k, nsubc);
+}
+
+// control words
+struct ScanCtl {
+    int piece_ctr;
+    int lock;
+    int worst_pos;
+    uint32_t worst_seq;
+    float worst_d;   // == the insertion threshold
+    int pad[3];
+};
+
+// Merge one warp's candidate buffer into the CTA top-k.  Warp-collective.
+static __device__ __forceinline__ void flush_candidates(volatile ScanCtl *ctl, float *topk_d, uint32_t *topk_seq,
+                                                        uint32_t *topk_slot, int k, const float *wd,
+                                                        const uint32_t *wseq, const uint32_t *wslot, int count,
+                                                        int lane)
+{
+    if (count == 0) return;
+    __syncwarp();
+    if (lane == 0) {
+        while (atomicCAS((int *)&ctl->lock, 0, 1) != 0) { }
+        __threadfence_block();
+    }
+    __syncwarp();
+    for (int c = 0; c < count; c++) {
+        const float cd = wd[c];
+        const uint32_t cs = wseq[c];
+        const float w_d = ctl->worst_d;
+        const uint32_t w_s = ctl->worst_seq;
+        if (key_less(cd, cs, w_d, w_s)) {
+            const int wp = ctl->worst_pos;
+            if (lane == 0) {
+                topk_d[wp] = cd;
+                topk_seq[wp] = cs;
+                topk_slot[wp] = wslot[c];
+            }
+            __syncwarp();
+            // new worst = lexicographic max over the k entries
+            float bd = -FLT_MAX;
+            uint32_t bs = 0;
+            int bp = -1;
+            for (int e = lane; e < k; e += 32) {
+                const float ed = topk_d[e];
+                const uint32_t es = topk_seq[e];
+                if (bp < 0 || key_less(bd, bs, ed, es)) { bd = ed; bs = es; bp = e; }
+            }
+#pragma unroll
+            for (int off = 16; off > 0; off >>= 1) {
+                const float od = __shfl_xor_sync(IVF_FULL_MASK, bd, off);
+                const uint32_t os = __shfl_xor_sync(IVF_FULL_MASK, bs, off);
+                const int op = __shfl_xor_sync(IVF_FULL_MASK, bp, off);
+                if (op >= 0 && (bp < 0 || key_less(bd, bs, od, os))) { bd = od; bs = os; bp = op; }
+            }
+            if (lane == 0) {
+                ctl->worst_pos = bp;
+                ctl->worst_seq = bs;
+                ctl->worst_d = bd;
+            }
+            __syncwarp();
+        }
+    }
+    __syncwarp();
+    if (lane == 0) {
+        __threadfence_block();
+        atomicExch((int *)&ctl->lock, 0);
+    }
+}
+
+template <int M, bool GROUPING>
+__global__ void __launch_bounds__(SCAN_THREADS) scan_kernel(ScanArgs a)
+{
+    using C = ScanCfg<M>;
+    extern __shared__ __align__(1024) uint8_t smem[];
+    uint8_t *lut = smem;  // [256][64] floats (+ [256][32] norm replicas for M == 64)
+    uint8_t *p = smem + C::LUT_BYTES;
+    uint32_t *s_slot = reinterpret_cast<uint32_t *>(p); p += a.nprobe * 4;
+    uint32_t *s_n = reinterpret_cast<uint32_t *>(p); p += a.nprobe * 4;
+    float *s_base = reinterpret_cast<float *>(p); p += a.nprobe * 4;
+    uint32_t *s_seq = reinterpret_cast<uint32_t *>(p); p += a.nprobe * 4;
+    uint32_t *s_poff = reinterpret_cast<uint32_t *>(p); p += (a.nprobe + 1) * 4;
+    float *topk_d = reinterpret_cast<float *>(p); p += a.k * 4;
+    uint32_t *topk_seq = reinterpret_cast<uint32_t *>(p); p += a.k * 4;
+    uint32_t *topk_slot = reinterpret_cast<uint32_t *>(p); p += a.k * 4;
+    float *wbuf_d = reinterpret_cast<float *>(p); p += SCAN_WARPS * SCAN_WCAP * 4;
+    uint32_t *wbuf_seq = reinterpret_cast<uint32_t *>(p); p += SCAN_WARPS * SCAN_WCAP * 4;
+    uint32_t *wbuf_slot = reinterpret_cast<uint32_t *>(p); p += SCAN_WARPS * SCAN_WCAP * 4;
+    float *wsub_all = reinterpret_cast<float *>(p); p += SCAN_WARPS * a.nsubc * 4;
+    p = reinterpret_cast<uint8_t *>((reinterpret_cast<uintptr_t>(p) + 15) & ~(uintptr_t)15);
+    volatile ScanCtl *ctl = reinterpret_cast<volatile ScanCtl *>(p);
+
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    const int q = blockIdx.x / a.nsplit, split = blockIdx.x - q * a.nsplit;
+    const int nprobe = a.nprobe, k = a.k;
+    const int dsub = a.d / M;
+
+    // ---- stage the query's segment tables and initialise the top-k
+    {
+        const size_t o = (size_t)q * nprobe;
+        for (int i = tid; i < nprobe; i += SCAN_THREADS) {
+            s_slot[i] = a.T.slot[o + i];
+            s_n[i] = a.T.n[o + i];
+            s_base[i] = a.T.base[o + i];
+            s_seq[i] = a.T.seq[o + i];
+        }
+        for (int i = tid; i <= nprobe; i += SCAN_THREADS) s_poff[i] = a.T.piece_off[(size_t)q * (nprobe + 1) + i];
+        for (int e = tid; e < k; e += SCAN_THREADS) {
+            topk_d[e] = FLT_MAX;
+            topk_seq[e] = 0xffffffffu - (uint32_t)e;
+            topk_slot[e] = IVF_INVALID_SLOT;
+        }
+        if (tid == 0) {
+            ctl->piece_ctr = 0;
+            ctl->lock = 0;
+            ctl->worst_pos = 0;
+            ctl->worst_seq = 0xffffffffu;
+            ctl->worst_d = FLT_MAX;
+        }
+    }
+    __syncthreads();
+    const int npieces = (int)s_poff[nprobe];
+    const bool has_work = split < npieces;   // CTA-uniform
+
+    // ---- K-L1: per-query table straight into shared memory
+    // (ProductQuantizer::compute_inner_prod_table, faiss/ProductQuantizer.cpp:424-436, scaled by -2 so
+    //  that the scan adds instead of computing 2*pq_L2sqr, IndexIVF_HNSW.cpp:283; x2 is exact in fp32)
+    if (has_work) {
+        const float *qv = a.queries + (size_t)q * a.d;
+        float *lutf = reinterpret_cast<float *>(lut);
+        constexpr int NPASS = (M == 64) ? 2 : 1;
+#pragma unroll
+        for (int pass = 0; pass < NPASS; pass++) {
+            const int m = (M == 64) ? (lane + 32 * pass) : (lane / C::R);
+            const float *qs = qv + m * dsub;
+            const float *cb = a.pqc + (size_t)m * 256 * dsub;
+            if ((dsub & 3) == 0 && dsub <= 16) {
+                float4 qr[4];
+#pragma unroll
+                for (int t = 0; t < 4; t++)
+                    qr[t] = (t * 4 < dsub) ? *reinterpret_cast<const float4 *>(qs + t * 4) : make_float4(0, 0, 0, 0);
+#pragma unroll 4
+                for (int jj = 0; jj < 32; jj++) {
+                    const int j = warp * 32 + jj;
+                    const float4 *c4 = reinterpret_cast<const float4 *>(cb + (size_t)j * dsub);
+                    float s = 0.f;
+#pragma unroll
+                    for (int t = 0; t < 4; t++)
+                        if (t * 4 < dsub) {
+                            const float4 v = __ldg(c4 + t);
+                            s = fmaf(qr[t].x, v.x, s);
+                            s = fmaf(qr[t].y, v.y, s);
+                            s = fmaf(qr[t].z, v.z, s);
+                            s = fmaf(qr[t].w, v.w, s);
+                        }
+                    lutf[j * 64 + lane + 32 * pass] = -2.f * s;
+                }
+            } else {
+#pragma unroll 2
+                for (int jj = 0; jj < 32; jj++) {
+                    const int j = warp * 32 + jj;
+                    const float *c = cb + (size_t)j * dsub;
+                    float s = 0.f;
+                    for (int t = 0; t < dsub; t++) s = fmaf(qs[t], __ldg(c + t), s);
+                    lutf[j * 64 + lane + 32 * pass] = -2.f * s;
+                }
+            }
+        }
+        // decoded norms (norm_pq->decode, IndexIVF_HNSW.cpp:280): one replica per bank
+        for (int jj = 0; jj < 32; jj++) {
+            const int j = warp * 32 + jj;
+            const float v = __ldg(a.norm_table + j);
+            if (M == 64) lutf[16384 + j * 32 + lane] = v;
+            else lutf[j * 64 + 32 + lane] = v;
+        }
+    }
+    __syncthreads();
+
+    // ---- per-lane word offsets: step t reads word R*((t%ML) ^ (lane%ML)) + lane/ML
+    uint32_t O[C::NO];
+#pragma unroll
+    for (int w = 0; w < C::NO; w++) {
+        uint32_t v = 0;
+#pragma unroll
+        for (int b = 0; b < 4; b++) {
+            const int t = w * 4 + b;
+            const uint32_t word = C::R * ((t ^ lane) & (C::ML - 1)) + lane / C::ML;
+            v |= (word * 4u) << (8 * b);
+        }
+        O[w] = v;
+    }
+    const uint32_t Onorm = 128u + 4u * lane;  // M < 64: byte0 = offset of word 32 + lane, bytes 1..3 = 0
+
+    float *wd = wbuf_d + warp * SCAN_WCAP;
+    uint32_t *wseq = wbuf_seq + warp * SCAN_WCAP;
+    uint32_t *wslot = wbuf_slot + warp * SCAN_WCAP;
+    float *wsub = wsub_all + warp * a.nsubc;
+    int wcount = 0;
+
+    // ---- K-S: pull pieces
+    while (has_work) {
+        int pc = 0;
+        if (lane == 0) pc = atomicAdd((int *)&ctl->piece_ctr, 1);
+        pc = __shfl_sync(IVF_FULL_MASK, pc, 0);
+        const int piece = pc * a.nsplit + split;
+        if (piece >= npieces) break;
+        int seg = 0;
+        for (int b = 0; b < nprobe; b += 32) {
+            const int i = b + lane;
+            const bool le = (i < nprobe) && ((int)s_poff[i] <= piece);
+            seg += __popc(__ballot_sync(IVF_FULL_MASK, le));
+        }
+        seg -= 1;
+        const int pk = piece - (int)s_poff[seg];
+        const int rem = (int)s_n[seg] - pk * SCAN_PIECE;   // > 0
+        const uint32_t slot0 = s_slot[seg] + (uint32_t)pk * SCAN_PIECE;
+        const uint32_t seq0 = s_seq[seg] + (uint32_t)pk * SCAN_PIECE;
+        float base = s_base[seg];
+        if (GROUPING) {
+            __syncwarp();
+            const float *sbg = a.T.sub_base + ((size_t)q * nprobe + seg) * a.nsubc;
+            for (int s = lane; s < a.nsubc; s += 32) wsub[s] = sbg[s];
+            __syncwarp();
+        }
+
+        // issue every load of the piece before the first use
+        uint32_t cw[SCAN_PIECE_CHUNKS][C::NW];
+        uint32_t nm[SCAN_PIECE_CHUNKS], sid[SCAN_PIECE_CHUNKS];
+#pragma unroll
+        for (int c = 0; c < SCAN_PIECE_CHUNKS; c++) {
+            if (c * SCAN_CHUNK < rem) {
+                const uint32_t slot = slot0 + c * SCAN_CHUNK + lane;
+                const uint8_t *cp = a.L.codes + (size_t)slot * M;
+                if (M == 8) {
+                    const uint2 v = ldg_stream_64(cp);
+                    cw[c][0] = v.x; cw[c][1] = v.y;
+                } else {
+#pragma unroll
+                    for (int w4 = 0; w4 < C::NW / 4; w4++) {
+                        const uint4 v = ldg_stream_128(cp + w4 * 16);
+                        cw[c][w4 * 4 + 0] = v.x; cw[c][w4 * 4 + 1] = v.y;
+                        cw[c][w4 * 4 + 2] = v.z; cw[c][w4 * 4 + 3] = v.w;
+                    }
+                }
+                nm[c] = ldg_stream_u8(a.L.norm_codes + slot);
+                sid[c] = GROUPING ? ldg_stream_u8(a.L.sub_ids + slot) : 0u;
+            }
+        }
+#pragma unroll
+        for (int c = 0; c < SCAN_PIECE_CHUNKS; c++) {
+            if (c * SCAN_CHUNK < rem) {   // warp-uniform
+                float acc0 = GROUPING ? wsub[sid[c]] : base;
+                float acc1;
+                if (M == 64) acc1 = *reinterpret_cast<const float *>(lut + 65536 + nm[c] * 128u + 4u * lane);
+                else acc1 = *reinterpret_cast<const float *>(lut + prmt(nm[c], Onorm, 0x5504u));
+#pragma unroll
+                for (int t = 0; t < M; t++) {
+                    const int b = t & 3;
+                    const uint32_t sel = 0xCC00u | (uint32_t)(b << 4) | (uint32_t)(4 + b);
+                    const uint32_t addr = prmt(cw[c][t >> 2], O[(t & (C::ML - 1)) >> 2], sel);
+                    const float v = *reinterpret_cast<const float *>(lut + (t >= 32 ? 128 : 0) + addr);
+                    if (t & 1) acc1 += v; else acc0 += v;
+                }
+                const float dist = acc0 + acc1;
+                const bool valid = (c * SCAN_CHUNK + lane) < rem;
+                const float thr = ctl->worst_d;
+                bool pass = valid && dist <= thr;
+                uint32_t bal = __ballot_sync(IVF_FULL_MASK, pass);
+                if (bal) {
+                    int n = __popc(bal);
+                    if (wcount + n > SCAN_WCAP) {
+                        flush_candidates(ctl, topk_d, topk_seq, topk_slot, k, wd, wseq, wslot, wcount, lane);
+                        wcount = 0;
+                        pass = valid && dist <= ctl->worst_d;
+                        bal = __ballot_sync(IVF_FULL_MASK, pass);
+                        n = __popc(bal);
+                    }
+                    if (pass) {
+                        const int pos = wcount + __popc(bal & ((1u << lane) - 1u));
+                        wd[pos] = dist;
+                        wseq[pos] = seq0 + c * SCAN_CHUNK + lane;
+                        wslot[pos] = slot0 + c * SCAN_CHUNK + lane;
+                    }
+                    wcount += n;
+                }
+            }
+        }
+    }
+    flush_candidates(ctl, topk_d, topk_seq, topk_slot, k, wd, wseq, wslot, wcount, lane);
+    __syncthreads();
+
+    // ---- rank-sort the k survivors by (distance, scan order) and write them out
+    for (int e = tid; e < k; e += SCAN_THREADS) {
+        const float ed = topk_d[e];
+        const uint32_t es = topk_seq[e];
+        int rank = 0;
+        for (int o = 0; o < k; o++) rank += key_less(topk_d[o], topk_seq[o], ed, es) ? 1 : 0;
+        const uint32_t slot = topk_slot[e];
+        if (a.nsplit == 1) {
+            a.out_d[(size_t)q * k + rank] = ed;
+            a.out_labels[(size_t)q * k + rank] = slot == IVF_INVALID_SLOT ? (int64_t)-1 : (int64_t)a.L.ids[slot];
+        } else {
+            const size_t o = ((size_t)q * a.nsplit + split) * k + rank;
+            a.part_d[o] = ed;
+            a.part_seq[o] = es;
+            a.part_slot[o] = slot;
+        }
+    }
+}
+
+template <int M, bool G>
+static cudaError_t launch_scan_t(cudaStream_t st, int nq, const ScanArgs &a)
+{
+    const size_t smem = scan_smem_bytes(M, a.nprobe, a.k, a.nsubc);
+    cudaError_t e = cudaFuncSetAttribute(scan_kernel<M, G>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+    if (e != cudaSuccess) return e;
+    scan_kernel<M, G><<<(unsigned)((size_t)nq * a.nsplit), SCAN_THREADS, smem, st>>>(a);
+    return cudaGetLastError();
+}
+
+cudaError_t launch_scan(cudaStream_t st, uint64_t *launches, int M, bool grouping, int nq, int d, int nprobe,
+                        int nsubc, int k, int nsplit, const float *queries, const float *pqc,
+                        const float *norm_table, const DeviceLists &L, const SegTables &T, float *part_d,
+                        uint32_t *part_seq, uint32_t *part_slot, float *out_d, int64_t *out_labels)
+{
+    if (nq == 0) return cudaSuccess;
+    ScanArgs a;
+    a.d = d; a.nprobe = nprobe; a.nsubc = grouping ? nsubc : 0; a.k = k; a.nsplit = nsplit;
+    a.queries = queries; a.pqc = pqc; a.norm_table = norm_table; a.L = L; a.T = T;
+    a.part_d = part_d; a.part_seq = part_seq; a.part_slot = part_slot; a.out_d = out_d; a.out_labels = out_labels;
+    ++*launches;
+#define IVF_SCAN_CASE(MM)                                                              \
+    case MM: return grouping ? launch_scan_t<MM, true>(st, nq, a) : launch_scan_t<MM, false>(st, nq, a);
+    switch (M) {
+        IVF_SCAN_CASE(8)
+        IVF_SCAN_CASE(16)
+        IVF_SCAN_CASE(32)
+        IVF_SCAN_CASE(64)
+    }
+#undef IVF_SCAN_CASE
+    --*launches;
+    return cudaErrorInvalidValue;
+}
+
+// =============================================================================================
+// K-M1: merge the nsplit sorted partial top-k lists of each query (keys are unique per query)
+// =============================================================================================
+__global__ void __launch_bounds__(256) merge_kernel(int k, int nsplit, const float *__restrict__ part_d,
+                                                    const uint32_t *__restrict__ part_seq,
+                                                    const uint32_t *__restrict__ part_slot,
+                                                    const uint32_t *__restrict__ ids, float *out_d,
+                                                    int64_t *out_labels)
+{
+    const int q = blockIdx.x;
+    const size_t base = (size_t)q * nsplit * k;
+    const int n = nsplit * k;
+    for (int e = threadIdx.x; e < n; e += blockDim.x) {
+        const float ed = part_d[base + e];
+        const uint32_t es = part_seq[base + e];
+        const int mine = e / k;
+        int rank = e - mine * k;  // elements before it in its own (sorted) list
+        for (int s = 0; s < nsplit && rank < k; s++) {
+            if (s == mine) continue;
+            const float *ld = part_d + base + (size_t)s * k;
+            const uint32_t *ls = part_seq + base + (size_t)s * k;
+            int lo = 0, hi = k;  // count of elements of list s that come before (ed, es)
+            while (lo < hi) {
+                const int mid = (lo + hi) >> 1;
+                // empty entries of different lists share keys (FLT_MAX, 0xffffffff - e): break ties by list
+                const float md = ld[mid];
+                const uint32_t ms = ls[mid];
+                const bool before = key_less(md, ms, ed, es) || (md == ed && ms == es && s < mine);
+                if (before) lo = mid + 1; else hi = mid;
+            }
+            rank += lo;
+        }
+        if (rank < k) {
+            const uint32_t slot = part_slot[base + e];
+            out_d[(size_t)q * k + rank] = ed;
+            out_labels[(size_t)q * k + rank] = slot == IVF_INVALID_SLOT ? (int64_t)-1 : (int64_t)ids[slot];
+        }
+    }
+}
+
+cudaError_t launch_merge(cudaStream_t st, uint64_t *launches, int nq, int k, int nsplit, const float *part_d,
+                         const uint32_t *part_seq, const uint32_t *part_slot, const uint32_t *ids,
+                         float *out_d, int64_t *out_labels)
+{
+    if (nq == 0) return cudaSuccess;
+    merge_kernel<<<nq, 256, 0, st>>>(k, nsplit, part_d, part_seq, part_slot, ids, out_d, out_labels);
+    ++*launches;
+    return cudaGetLastError();
+}
+
+}  // namespace ivfb200

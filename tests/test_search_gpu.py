@@ -1,0 +1,138 @@
+"""GPU parity tests: the CUDA path (through the C ABI) against the golden fixtures of the compiled
+reference and against the plain-C port, on the reference's own candidate lists (search2 seam)."""
+import numpy as np
+import pytest
+
+from conftest import golden_names, load_golden, load_pkg, dist_close, labels_match_up_to_ties
+
+pytestmark = pytest.mark.gpu
+
+
+def make_index(pkg, ix, search_time=True):
+    cls = pkg.IndexIVF_HNSW_Grouping if ix["nsubc"] else pkg.IndexIVF_HNSW
+    args = (ix["d"], ix["nc"], ix["M"], 8) + ((ix["nsubc"],) if ix["nsubc"] else ())
+    idx = cls(*args)
+    idx.build_quantizer(centroids=ix["centroids"] if search_time else ix["centroids_build"])
+    idx.set_pq(ix["pqc"], ix["norm_table"], ix["opq"])
+    idx.do_opq = ix["opq"] is not None
+    return idx
+
+
+@pytest.mark.parametrize("name", golden_names())
+def test_search_given_reference_candidates(name):
+    """Identical coarse candidate lists in -> labels identical up to equal-distance ties, distances
+    within 1e-4 relative (BASELINE.json north_star)."""
+    pkg = load_pkg()
+    g, ix, runs = load_golden(name)
+    k, nprobe = int(g["k"]), int(g["nprobe"])
+    scale = float(ix["centroid_norms"].max())
+    idx = make_index(pkg, ix)
+    idx.load_index_dict(ix)
+    idx.nprobe = nprobe
+    for tag, mc, pr in runs:
+        idx.max_codes, idx.do_pruning = mc, pr
+        D, L = idx.search2(k, g["Q"], g["cd_" + tag], g["ci_" + tag])
+        Dr, Lr = g["D_" + tag], g["L_" + tag]
+        o = np.argsort(Dr, axis=1, kind="stable")
+        Drs, Lrs = np.take_along_axis(Dr, o, 1), np.take_along_axis(Lr, o, 1)
+        assert dist_close(D, Drs, scale), (name, tag, np.abs(D - Drs).max())
+        assert labels_match_up_to_ties(D, L, Drs, Lrs, scale) == 0, (name, tag)
+        exact = np.mean([set(a) == set(b) for a, b in zip(L.tolist(), Lr.tolist())])
+        assert exact >= 0.95, (name, tag, exact)
+    idx.close()
+
+
+@pytest.mark.parametrize("name", golden_names())
+@pytest.mark.parametrize("split", [1, 3])
+def test_search_splits_and_port(port, name, split):
+    """Same answers whatever the split factor (partial top-k + merge), checked against the port;
+    Grouping additionally checks the pruning threshold and the number of scanned codes."""
+    pkg = load_pkg()
+    g, ix, runs = load_golden(name)
+    k, nprobe = int(g["k"]), int(g["nprobe"])
+    scale = float(ix["centroid_norms"].max())
+    idx = make_index(pkg, ix)
+    idx.load_index_dict(ix)
+    idx.nprobe = nprobe
+    idx.set_option("scan_split", split)
+    idx.set_option("debug", 1)
+    for tag, mc, pr in runs:
+        idx.max_codes, idx.do_pruning = mc, pr
+        D, L = idx.search2(k, g["Q"], g["cd_" + tag], g["ci_" + tag])
+        Dp, Lp, thr, scanned, ncode = port.search(ix, g["Q"], g["cd_" + tag], g["ci_" + tag], k, nprobe, mc, pr,
+                                                  debug=True)
+        o = np.argsort(Dp, axis=1, kind="stable")
+        Dps, Lps = np.take_along_axis(Dp, o, 1), np.take_along_axis(Lp, o, 1)
+        assert dist_close(D, Dps, scale), (name, tag)
+        assert labels_match_up_to_ties(D, L, Dps, Lps, scale) == 0, (name, tag)
+        gthr, gsc = idx.last_thresholds(D.shape[0])
+        assert np.array_equal(gsc.astype(np.uint64), ncode), (name, tag)
+        if ix["nsubc"] and pr:
+            assert np.allclose(gthr, thr, rtol=1e-5), (name, tag)
+    idx.close()
+
+
+@pytest.mark.parametrize("name", golden_names())
+def test_coarse_exact_matches_port(port, name):
+    """K-A2: exact nprobe nearest centroids, ascending (dist, idx), fstdistfunc numerics."""
+    pkg = load_pkg()
+    g, ix, runs = load_golden(name)
+    nprobe = int(g["nprobe"])
+    idx = make_index(pkg, ix)
+    cd, ci = idx.coarse(g["Q"], nprobe)
+    Q = g["Q"] if ix["opq"] is None else port.opq_apply(ix["opq"], g["Q"])
+    pd, pi = port.coarse(Q, ix["centroids"], nprobe)
+    assert np.allclose(cd, pd, rtol=1e-5, atol=1e-4)
+    agree = np.mean(ci == pi)
+    assert agree >= 0.999, agree       # only fp-tie swaps may differ
+    assert np.all(np.diff(cd, axis=1) >= 0)
+    idx.close()
+
+
+@pytest.mark.parametrize("name", golden_names())
+def test_full_search_recall_not_below_reference(port, name):
+    """Full GPU path (exact coarse + scan): every returned distance is a true ADC distance of the
+    port on the GPU's own candidates, and 1-recall@k vs the reference's answers is >= what the
+    reference's HNSW coarse stage achieved against the exhaustive-probe answer."""
+    pkg = load_pkg()
+    g, ix, runs = load_golden(name)
+    k, nprobe = int(g["k"]), int(g["nprobe"])
+    scale = float(ix["centroid_norms"].max())
+    idx = make_index(pkg, ix)
+    idx.load_index_dict(ix)
+    idx.nprobe = nprobe
+    tag, mc, pr = runs[0]
+    idx.max_codes, idx.do_pruning = mc, pr
+    D, L = idx.search(k, g["Q"])
+    cd, ci = idx.coarse(g["Q"], nprobe)
+    Dp, Lp = port.search(ix, g["Q"], cd, ci, k, nprobe, mc, pr)
+    o = np.argsort(Dp, axis=1, kind="stable")
+    Dps, Lps = np.take_along_axis(Dp, o, 1), np.take_along_axis(Lp, o, 1)
+    assert dist_close(D, Dps, scale)
+    assert labels_match_up_to_ties(D, L, Dps, Lps, scale) == 0
+    # best distance found by the exact coarse stage is never worse than the HNSW one
+    Dr = np.sort(g["D_" + tag], axis=1)
+    assert np.mean(D[:, 0] <= Dr[:, 0] * (1 + 1e-4) + 1e-3 * scale * 1e-2) >= 0.99
+    idx.close()
+
+
+def test_empty_and_ragged_inputs(port):
+    """Edge cases: nq = 0, k larger than the number of scanned codes (-1 / FLT_MAX padding like
+    faiss::maxheap_heapify), empty probed lists, nprobe = 1."""
+    pkg = load_pkg()
+    g, ix, runs = load_golden("adc_d32")
+    idx = make_index(pkg, ix)
+    idx.load_index_dict(ix)
+    idx.nprobe, idx.max_codes = 1, 10 ** 9
+    D, L = idx.search(10, np.zeros((0, ix["d"]), np.float32))
+    assert D.shape == (0, 10)
+    k = 400   # more than one list holds
+    cd, ci = g["cd_mc0_pr0"][:, :1].copy(), g["ci_mc0_pr0"][:, :1].copy()
+    D, L = idx.search2(k, g["Q"], cd, ci)
+    Dp, Lp = port.search(ix, g["Q"], cd, ci, k, 1, 10 ** 9)
+    sizes = np.diff(ix["list_off"])[ci[:, 0]]
+    for i in range(D.shape[0]):
+        n = int(min(sizes[i], k))
+        assert np.all(L[i, n:] == -1) and np.all(D[i, n:] > 1e38)
+        assert set(L[i, :n].tolist()) == set(Lp[i][Lp[i] >= 0].tolist())
+    idx.close()
