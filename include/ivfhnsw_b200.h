@@ -76,6 +76,15 @@ int ivfhnsw_b200_set_centroid_norms(ivfhnsw_b200_t *h, const float *in /* nc, e.
 int ivfhnsw_b200_rotate_quantizer(ivfhnsw_b200_t *h);
 int ivfhnsw_b200_get_centroids(ivfhnsw_b200_t *h, float *out /* nc*d */);
 
+/* -- training ---------------------------------------------------------------*/
+/* IndexIVF_HNSW::train_pq / IndexIVF_HNSW_Grouping::train_pq (IndexIVF_HNSW.cpp:536-593,
+ * IndexIVF_HNSW_Grouping.cpp:486-618): assign, residuals (to the sub-centroid for Grouping), OPQ rotation
+ * when do_opq (OPQMatrix::train, faiss/VectorTransform.cpp:587-744), M x 256-way k-means
+ * (faiss/Clustering.cpp:67-230, 25 iterations), then the 1-D norm codebook.  n x d host vectors. */
+int ivfhnsw_b200_train_pq(ivfhnsw_b200_t *h, size_t n, const float *x);
+/* host copies of the model for index->pq->centroids / norm_pq->centroids / opq_matrix->A (any may be NULL) */
+int ivfhnsw_b200_get_pq(ivfhnsw_b200_t *h, float *pq_centroids, float *norm_centroids, float *opq_A);
+
 /* -- indexing ---------------------------------------------------------------*/
 /* IndexIVF_HNSW::assign (IndexIVF_HNSW.cpp:68-72): exact nearest centroid (k must be 1) */
 int ivfhnsw_b200_assign(ivfhnsw_b200_t *h, size_t n, const float *x, uint32_t *labels, size_t k);

@@ -73,6 +73,8 @@ def lib():
         "ivfhnsw_b200_set_centroid_norms": ([H, vp], C.c_int),
         "ivfhnsw_b200_rotate_quantizer": ([H], C.c_int),
         "ivfhnsw_b200_get_centroids": ([H, vp], C.c_int),
+        "ivfhnsw_b200_train_pq": ([H, sz, vp], C.c_int),
+        "ivfhnsw_b200_get_pq": ([H, vp, vp, vp], C.c_int),
         "ivfhnsw_b200_assign": ([H, sz, vp, vp, sz], C.c_int),
         "ivfhnsw_b200_assign_u8": ([H, sz, vp, vp], C.c_int),
         "ivfhnsw_b200_add_batch": ([H, sz, vp, vp, vp], C.c_int),
@@ -238,6 +240,19 @@ class IndexIVF_HNSW:
         self.opq_matrix = None if opq_matrix is None else _np(opq_matrix, np.float32)
         self._ck(self._L.ivfhnsw_b200_set_opq(self._h, None if self.opq_matrix is None else
                                               self.opq_matrix.ctypes.data))
+
+    def train_pq(self, x):
+        """IndexIVF_HNSW::train_pq / IndexIVF_HNSW_Grouping::train_pq on the GPU; afterwards
+        pq_centroids / norm_centroids / opq_matrix hold the trained model like index->pq etc."""
+        self._push_params()
+        x = _np(x, np.float32).reshape(-1, self.d)
+        self._ck(self._L.ivfhnsw_b200_train_pq(self._h, x.shape[0], x.ctypes.data))
+        self.pq_centroids = np.zeros(self.d * 256, np.float32)
+        self.norm_centroids = np.zeros(256, np.float32)
+        A = np.zeros((self.d, self.d), np.float32) if self.do_opq else None
+        self._ck(self._L.ivfhnsw_b200_get_pq(self._h, self.pq_centroids.ctypes.data, self.norm_centroids.ctypes.data,
+                                             None if A is None else A.ctypes.data))
+        self.opq_matrix = A
 
     def compute_centroid_norms(self):
         self._ck(self._L.ivfhnsw_b200_finalize(self._h))  # flush point, SURVEY.md 8(b)

@@ -12,9 +12,8 @@
 #include <string>
 #include <vector>
 
-#include "../../include/ivfhnsw_b200.h"
 #include "common.cuh"
-#include "kernels.h"
+#include "handle.h"
 
 namespace ivfb200 {
 cudaError_t launch_group_points(cudaStream_t st, uint64_t *launches, int mode, int nc, int d, int nsubc,
@@ -38,47 +37,6 @@ cudaError_t launch_f32_to_bf16(cudaStream_t st, uint64_t *launches, size_t n, co
 using namespace ivfb200;
 
 namespace {
-
-struct DevBuf {
-    void *p = nullptr;
-    size_t cap = 0;
-    cudaError_t ensure(size_t bytes)
-    {
-        if (bytes <= cap) return cudaSuccess;
-        if (p) cudaFree(p);
-        p = nullptr;
-        cap = 0;
-        cudaError_t e = cudaMalloc(&p, bytes);
-        if (e == cudaSuccess) cap = bytes;
-        return e;
-    }
-    // keep the first `keep` bytes
-    cudaError_t grow(size_t bytes, size_t keep, cudaStream_t st)
-    {
-        if (bytes <= cap) return cudaSuccess;
-        size_t ncap = std::max(bytes, cap + cap / 2);
-        void *np = nullptr;
-        cudaError_t e = cudaMalloc(&np, ncap);
-        if (e != cudaSuccess) return e;
-        if (p && keep) {
-            e = cudaMemcpyAsync(np, p, keep, cudaMemcpyDeviceToDevice, st);
-            if (e != cudaSuccess) return e;
-            e = cudaStreamSynchronize(st);
-            if (e != cudaSuccess) return e;
-        }
-        if (p) cudaFree(p);
-        p = np;
-        cap = ncap;
-        return cudaSuccess;
-    }
-    void release()
-    {
-        if (p) cudaFree(p);
-        p = nullptr;
-        cap = 0;
-    }
-    template <typename T> T *as() const { return reinterpret_cast<T *>(p); }
-};
 
 __global__ void iota_kernel(size_t n, uint32_t *out)
 {
@@ -129,62 +87,6 @@ unsigned grid_for(size_t n, int per = 256, unsigned cap = 148 * 16)
 }
 
 }  // namespace
-
-struct ivfhnsw_b200 {
-    int device = 0;
-    size_t d = 0, nc = 0, M = 0, nsubc = 0;
-    size_t nprobe = 1, max_codes = 1000000000;
-    bool do_opq = false, do_pruning = false;
-    uint32_t c_begin = 0, c_end = 0;
-    cudaStream_t stream = nullptr;
-    cudaEvent_t ev[4] = {nullptr, nullptr, nullptr, nullptr};
-    std::string err;
-    std::mutex mu;
-
-    // model
-    DevBuf centroids, centroid_norms, cnorm_gemm, cent_bf16, pqc, norm_table, opqA;
-    bool have_centroids = false, have_pq = false, have_norm = false, have_opq = false, have_cnorms = false;
-    bool gemm_norms_valid = false, bf16_valid = false;
-    // lists (device CSR in slot space)
-    DevBuf list_size, list_slot, raw_off, codes, norm_codes, sub_ids, ids;
-    DevBuf nn_idx, sub_sizes, alphas, icd;
-    bool have_lists = false, have_group_meta = false;
-    size_t ntotal = 0, nslots = 0;
-    // staging (records not yet in the CSR)
-    DevBuf st_list, st_ids, st_codes, st_norm, st_sub, st_x;
-    size_t st_n = 0;          // encoded records staged (IVFADC) or points staged (Grouping)
-    bool st_dirty = false;
-    // workspace
-    DevBuf w_x, w_xrot, w_cd, w_ci, w_seg, w_sub_base, w_qsd, w_part, w_coarse, w_xbf16, w_out_d, w_out_l;
-    DevBuf w_a, w_b, w_c, w_d2, w_e, w_f, w_cub, w_small;
-    DevBuf counters;  // [0] scanned, [1] walked
-    // options / stats
-    long coarse_slack = 8, coarse_impl = 0, scan_split = 0, query_batch = 0, debug = 0;
-    bool timing = false;
-    ivfhnsw_b200_stats_t stats{};
-    std::vector<float> last_thr;
-    std::vector<uint32_t> last_scanned;
-
-    int fail(int code, const char *fmt, ...)
-    {
-        char buf[512];
-        va_list ap;
-        va_start(ap, fmt);
-        vsnprintf(buf, sizeof buf, fmt, ap);
-        va_end(ap);
-        err = buf;
-        return code;
-    }
-};
-
-#define CU(call)                                                                                         \
-    do {                                                                                                 \
-        cudaError_t e__ = (call);                                                                        \
-        if (e__ != cudaSuccess)                                                                          \
-            return h->fail(IVFHNSW_B200_ECUDA, "%s:%d %s -> %s", __FILE__, __LINE__, #call, cudaGetErrorString(e__)); \
-    } while (0)
-
-#define LAUNCHES (&h->stats.kernel_launches)
 
 static int bind(ivfhnsw_b200_t *h)
 {
@@ -283,6 +185,7 @@ int ivfhnsw_b200_set_centroids(ivfhnsw_b200_t *h, const float *c)
     h->have_centroids = true;
     h->gemm_norms_valid = false;
     h->bf16_valid = false;
+    if (!h->have_lists) h->have_group_meta = false;
     return 0;
 }
 int ivfhnsw_b200_set_pq(ivfhnsw_b200_t *h, const float *p)
@@ -399,8 +302,8 @@ static int ensure_gemm_side(ivfhnsw_b200_t *h)
 }
 
 // exact nprobe nearest centroids for nq device-resident (already rotated) queries
-static int coarse_dev(ivfhnsw_b200_t *h, size_t nq, const float *xq, size_t nprobe, int exclude_self, float *out_d,
-                      uint32_t *out_i)
+int ivfb200_coarse_dev(ivfhnsw_b200_t *h, size_t nq, const float *xq, size_t nprobe, int exclude_self, float *out_d,
+                        uint32_t *out_i)
 {
     if (!h->have_centroids) return h->fail(IVFHNSW_B200_ESTATE, "centroids not set (build_quantizer)");
     if (int r = ensure_gemm_side(h)) return r;
@@ -441,7 +344,7 @@ int ivfhnsw_b200_coarse_dev(ivfhnsw_b200_t *h, size_t nq, const float *x_dev, si
         CU(launch_rotate(h->stream, LAUNCHES, nq, (int)h->d, h->opqA.as<float>(), false, x_dev, h->w_xrot.as<float>()));
         xq = h->w_xrot.as<float>();
     }
-    return coarse_dev(h, nq, xq, nprobe, 0, dists_dev, idxs_dev);
+    return ivfb200_coarse_dev(h, nq, xq, nprobe, 0, dists_dev, idxs_dev);
 }
 
 int ivfhnsw_b200_coarse(ivfhnsw_b200_t *h, size_t nq, const float *x, size_t nprobe, float *dists, uint32_t *idxs)
@@ -461,10 +364,10 @@ int ivfhnsw_b200_coarse(ivfhnsw_b200_t *h, size_t nq, const float *x, size_t npr
 }
 
 // assign for device-resident vectors (k = 1): labels_dev[n]
-static int assign_dev(ivfhnsw_b200_t *h, size_t n, const float *x_dev, uint32_t *labels_dev)
+int ivfb200_assign_dev(ivfhnsw_b200_t *h, size_t n, const float *x_dev, uint32_t *labels_dev)
 {
     CU(h->w_cd.ensure(n * 4));
-    return coarse_dev(h, n, x_dev, 1, 0, h->w_cd.as<float>(), labels_dev);
+    return ivfb200_coarse_dev(h, n, x_dev, 1, 0, h->w_cd.as<float>(), labels_dev);
 }
 
 int ivfhnsw_b200_assign(ivfhnsw_b200_t *h, size_t n, const float *x, uint32_t *labels, size_t k)
@@ -477,7 +380,7 @@ int ivfhnsw_b200_assign(ivfhnsw_b200_t *h, size_t n, const float *x, uint32_t *l
     for (size_t i0 = 0; i0 < n; i0 += chunk) {
         const size_t nb = std::min(chunk, n - i0);
         CU(cudaMemcpyAsync(h->w_x.p, x + i0 * h->d, nb * h->d * 4, cudaMemcpyHostToDevice, h->stream));
-        if (int r = assign_dev(h, nb, h->w_x.as<float>(), h->w_ci.as<uint32_t>())) return r;
+        if (int r = ivfb200_assign_dev(h, nb, h->w_x.as<float>(), h->w_ci.as<uint32_t>())) return r;
         CU(cudaMemcpyAsync(labels + i0, h->w_ci.p, nb * 4, cudaMemcpyDeviceToHost, h->stream));
         CU(cudaStreamSynchronize(h->stream));
     }
@@ -495,7 +398,7 @@ int ivfhnsw_b200_assign_u8(ivfhnsw_b200_t *h, size_t n, const uint8_t *x, uint32
         const size_t nb = std::min(chunk, n - i0);
         CU(cudaMemcpyAsync(h->w_b.p, x + i0 * h->d, nb * h->d, cudaMemcpyHostToDevice, h->stream));
         CU(launch_u8_to_f32(h->stream, LAUNCHES, nb * h->d, h->w_b.as<uint8_t>(), h->w_x.as<float>()));
-        if (int r = assign_dev(h, nb, h->w_x.as<float>(), h->w_ci.as<uint32_t>())) return r;
+        if (int r = ivfb200_assign_dev(h, nb, h->w_x.as<float>(), h->w_ci.as<uint32_t>())) return r;
         CU(cudaMemcpyAsync(labels + i0, h->w_ci.p, nb * 4, cudaMemcpyDeviceToHost, h->stream));
         CU(cudaStreamSynchronize(h->stream));
     }
@@ -504,10 +407,14 @@ int ivfhnsw_b200_assign_u8(ivfhnsw_b200_t *h, size_t n, const uint8_t *x, uint32
 
 // ------------------------------------------------------------------------------------ encoding
 // codes / norm codes for n device vectors against base rows given by (idx[, sub]); chunked scratch
-static int encode_dev(ivfhnsw_b200_t *h, size_t n, const float *x_dev, const uint32_t *idx_dev, const uint8_t *sub_dev,
-                      uint8_t *codes_dev, uint8_t *norm_dev)
+int ivfb200_encode_dev(ivfhnsw_b200_t *h, size_t n, const float *x_dev, const uint32_t *idx_dev,
+                        const uint8_t *sub_dev, const float *alphas_dev, uint8_t *codes_dev, uint8_t *norm_dev,
+                        float *norms_out, float *residual_out)
 {
-    if (!h->have_pq || !h->have_norm) return h->fail(IVFHNSW_B200_ESTATE, "PQ codebooks not set (train_pq / read)");
+    // residual_out != nullptr: only the (rotated) residuals are produced (training); otherwise codes + norm codes
+    // (norm_dev may be nullptr when only norms_out is wanted)
+    if (!residual_out && (!h->have_pq || (norm_dev && !h->have_norm)))
+        return h->fail(IVFHNSW_B200_ESTATE, "PQ codebooks not set (train_pq / read)");
     if (h->do_opq && !h->have_opq) return h->fail(IVFHNSW_B200_ESTATE, "do_opq set but no OPQ matrix");
     const int d = (int)h->d, M = (int)h->M, nsubc = (int)h->nsubc;
     const size_t chunk = std::min<size_t>(n, 1 << 19);
@@ -515,7 +422,7 @@ static int encode_dev(ivfhnsw_b200_t *h, size_t n, const float *x_dev, const uin
     CU(h->w_c.ensure(chunk * d * 4));
     const float *cen = h->centroids.as<float>();
     const uint32_t *nn = sub_dev ? h->nn_idx.as<uint32_t>() : nullptr;
-    const float *al = sub_dev ? h->alphas.as<float>() : nullptr;
+    const float *al = sub_dev ? alphas_dev : nullptr;
     for (size_t i0 = 0; i0 < n; i0 += chunk) {
         const size_t nb = std::min(chunk, n - i0);
         float *R = h->w_a.as<float>(), *D = h->w_c.as<float>();
@@ -527,6 +434,10 @@ static int encode_dev(ivfhnsw_b200_t *h, size_t n, const float *x_dev, const uin
             CU(launch_rotate(h->stream, LAUNCHES, nb, d, h->opqA.as<float>(), false, R, D));
             std::swap(R, D);
         }
+        if (residual_out) {
+            CU(cudaMemcpyAsync(residual_out + i0 * d, R, nb * d * 4, cudaMemcpyDeviceToDevice, h->stream));
+            continue;
+        }
         // encode / decode (:96-109)
         CU(launch_pq_encode(h->stream, LAUNCHES, nb, d, M, h->pqc.as<float>(), R, codes_dev + i0 * M));
         CU(launch_pq_decode(h->stream, LAUNCHES, nb, d, M, h->pqc.as<float>(), codes_dev + i0 * M, D));
@@ -536,7 +447,8 @@ static int encode_dev(ivfhnsw_b200_t *h, size_t n, const float *x_dev, const uin
         }
         // reconstruct, norm, norm code (:111-121)
         CU(launch_residual(h->stream, LAUNCHES, nb, d, nullptr, idx_dev + i0, sb, cen, nn, al, nsubc, 1.f, D, R));
-        CU(launch_norm_encode(h->stream, LAUNCHES, nb, d, R, h->norm_table.as<float>(), norm_dev + i0, nullptr));
+        CU(launch_norm_encode(h->stream, LAUNCHES, nb, d, R, h->norm_table.as<float>(), norm_dev ? norm_dev + i0 : nullptr,
+                              norms_out ? norms_out + i0 : nullptr));
     }
     return 0;
 }
@@ -575,9 +487,9 @@ int ivfhnsw_b200_add_batch(ivfhnsw_b200_t *h, size_t n, const float *x, const ui
         CU(cudaMemcpyAsync(h->w_x.p, x + i0 * h->d, nb * h->d * 4, cudaMemcpyHostToDevice, h->stream));
         CU(cudaMemcpyAsync(h->st_ids.as<uint32_t>() + h->st_n, xids + i0, nb * 4, cudaMemcpyHostToDevice, h->stream));
         if (idx) CU(cudaMemcpyAsync(dl, idx + i0, nb * 4, cudaMemcpyHostToDevice, h->stream));
-        else if (int r = assign_dev(h, nb, h->w_x.as<float>(), dl)) return r;
-        if (int r = encode_dev(h, nb, h->w_x.as<float>(), dl, nullptr, h->st_codes.as<uint8_t>() + h->st_n * h->M,
-                               h->st_norm.as<uint8_t>() + h->st_n))
+        else if (int r = ivfb200_assign_dev(h, nb, h->w_x.as<float>(), dl)) return r;
+        if (int r = ivfb200_encode_dev(h, nb, h->w_x.as<float>(), dl, nullptr, nullptr, h->st_codes.as<uint8_t>() + h->st_n * h->M,
+                               h->st_norm.as<uint8_t>() + h->st_n, nullptr, nullptr))
             return r;
         CU(cudaStreamSynchronize(h->stream));
         h->st_n += nb;
@@ -600,13 +512,13 @@ int ivfhnsw_b200_add_points_dev(ivfhnsw_b200_t *h, size_t n, const float *x_dev,
     if (int r = stage_reserve(h, n, points)) return r;
     uint32_t *dl = h->st_list.as<uint32_t>() + h->st_n;
     if (idx_dev) CU(cudaMemcpyAsync(dl, idx_dev, n * 4, cudaMemcpyDeviceToDevice, h->stream));
-    else if (int r = assign_dev(h, n, x_dev, dl)) return r;
+    else if (int r = ivfb200_assign_dev(h, n, x_dev, dl)) return r;
     CU(cudaMemcpyAsync(h->st_ids.as<uint32_t>() + h->st_n, ids_dev, n * 4, cudaMemcpyDeviceToDevice, h->stream));
     if (points) {
         CU(cudaMemcpyAsync(h->st_x.as<float>() + h->st_n * h->d, x_dev, n * h->d * 4, cudaMemcpyDeviceToDevice, h->stream));
     } else {
-        if (int r = encode_dev(h, n, x_dev, dl, nullptr, h->st_codes.as<uint8_t>() + h->st_n * h->M,
-                               h->st_norm.as<uint8_t>() + h->st_n))
+        if (int r = ivfb200_encode_dev(h, n, x_dev, dl, nullptr, nullptr, h->st_codes.as<uint8_t>() + h->st_n * h->M,
+                               h->st_norm.as<uint8_t>() + h->st_n, nullptr, nullptr))
             return r;
     }
     CU(cudaStreamSynchronize(h->stream));
@@ -729,55 +641,72 @@ static int unstage_existing_lists(ivfhnsw_b200_t *h)
     return 0;
 }
 
+// K-G3: nsubc nearest other centroids of every centroid (IndexIVF_HNSW_Grouping.cpp:47-63), exact, and the
+// distances to them (== compute_inter_centroid_dists, :620-631).  Cached until the centroids change.
+int ivfb200_ensure_group_meta(ivfhnsw_b200_t *h)
+{
+    if (h->have_group_meta) return 0;
+    const int nc = (int)h->nc, nsubc = (int)h->nsubc;
+    if ((size_t)nsubc + 1 > h->nc) return h->fail(IVFHNSW_B200_EINVAL, "nsubc + 1 > nc");
+    CU(h->nn_idx.ensure((size_t)nc * nsubc * 4));
+    CU(h->icd.ensure((size_t)nc * nsubc * 4));
+    if (int r = ivfb200_coarse_dev(h, nc, h->centroids.as<float>(), nsubc, 1, h->icd.as<float>(), h->nn_idx.as<uint32_t>()))
+        return r;
+    h->have_group_meta = true;
+    return 0;
+}
+
+// compute_alpha (:691-728) and compute_subcentroid_idxs (:673-689) for n device points
+int ivfb200_group_stage(ivfhnsw_b200_t *h, size_t n, const float *x_dev, const uint32_t *list_dev, float *alphas_out,
+                         uint8_t *sub_out)
+{
+    const int nc = (int)h->nc, d = (int)h->d, nsubc = (int)h->nsubc;
+    cudaStream_t st = h->stream;
+    if (int r = ivfb200_ensure_group_meta(h)) return r;
+    CU(cudaMemsetAsync(alphas_out, 0, (size_t)nc * 4, st));
+    if (n == 0) return 0;
+    // sort points by group (stable) -> order, grp_off
+    CU(h->w_d2.ensure(n * 16));
+    uint32_t *keys_out = h->w_d2.as<uint32_t>(), *ord_in = keys_out + n, *ord_out = ord_in + n;
+    iota_kernel<<<grid_for(n), 256, 0, st>>>(n, ord_in);
+    ++h->stats.kernel_launches;
+    size_t tmp = 0;
+    int bits = 1;
+    while (((uint64_t)nc) >> bits) bits++;
+    CU(cub::DeviceRadixSort::SortPairs(nullptr, tmp, list_dev, keys_out, ord_in, ord_out, (int)n, 0, bits, st));
+    CU(h->w_cub.ensure(tmp + 16));
+    CU(cub::DeviceRadixSort::SortPairs(h->w_cub.p, tmp, list_dev, keys_out, ord_in, ord_out, (int)n, 0, bits, st));
+    h->stats.kernel_launches += 4;
+    CU(h->w_e.ensure((size_t)(nc + 1) * 12 + 64));
+    uint32_t *gsize = h->w_e.as<uint32_t>(), *gslot = gsize + nc, *goff = gslot + nc;
+    CU(cudaMemsetAsync(gsize, 0, (size_t)nc * 4, st));
+    CU(launch_hist(st, LAUNCHES, n, list_dev, gsize));
+    CU(h->w_small.ensure(64));
+    CU(launch_slot_scan(st, LAUNCHES, nc, 1, gsize, gslot, goff, h->w_small.as<uint32_t>()));
+    CU(h->w_f.ensure(n * 8));
+    float *num = h->w_f.as<float>(), *den = num + n;
+    CU(launch_group_points(st, LAUNCHES, 0, nc, d, nsubc, x_dev, ord_out, goff, h->centroids.as<float>(),
+                           h->nn_idx.as<uint32_t>(), h->icd.as<float>(), nullptr, num, den, nullptr));
+    CU(launch_alpha_reduce(st, LAUNCHES, nc, goff, num, den, alphas_out));
+    CU(launch_group_points(st, LAUNCHES, 1, nc, d, nsubc, x_dev, ord_out, goff, h->centroids.as<float>(),
+                           h->nn_idx.as<uint32_t>(), h->icd.as<float>(), alphas_out, nullptr, nullptr, sub_out));
+    return 0;
+}
+
 // Grouping: nn lists, alphas, sub-group ids and codes for the staged points, then the CSR
 static int finalize_grouping(ivfhnsw_b200_t *h)
 {
-    const int nc = (int)h->nc, d = (int)h->d, nsubc = (int)h->nsubc;
     const size_t n = h->st_n;
-    cudaStream_t st = h->stream;
-    if ((size_t)nsubc + 1 > h->nc) return h->fail(IVFHNSW_B200_EINVAL, "nsubc + 1 > nc");
-    // K-G3: nsubc nearest other centroids of every centroid (IndexIVF_HNSW_Grouping.cpp:47-63), exact
-    CU(h->nn_idx.ensure((size_t)nc * nsubc * 4));
-    CU(h->icd.ensure((size_t)nc * nsubc * 4));
-    if (int r = coarse_dev(h, nc, h->centroids.as<float>(), nsubc, 1, h->icd.as<float>(), h->nn_idx.as<uint32_t>()))
+    CU(h->st_sub.ensure(std::max<size_t>(n, 1)));
+    if (int r = ivfb200_group_stage(h, n, h->st_x.as<float>(), h->st_list.as<uint32_t>(), h->alphas.as<float>(),
+                            h->st_sub.as<uint8_t>()))
         return r;
-    h->have_group_meta = true;
-    CU(cudaMemsetAsync(h->alphas.p, 0, (size_t)nc * 4, st));
     if (n) {
-        // sort points by group (stable) -> order, grp_off
-        CU(h->w_d2.ensure(n * 16));
-        uint32_t *keys_out = h->w_d2.as<uint32_t>(), *ord_in = keys_out + n, *ord_out = ord_in + n;
-        iota_kernel<<<grid_for(n), 256, 0, st>>>(n, ord_in);
-        ++h->stats.kernel_launches;
-        size_t tmp = 0;
-        int bits = 1;
-        while (((uint64_t)nc) >> bits) bits++;
-        CU(cub::DeviceRadixSort::SortPairs(nullptr, tmp, h->st_list.as<uint32_t>(), keys_out, ord_in, ord_out, (int)n, 0,
-                                           bits, st));
-        CU(h->w_cub.ensure(tmp + 16));
-        CU(cub::DeviceRadixSort::SortPairs(h->w_cub.p, tmp, h->st_list.as<uint32_t>(), keys_out, ord_in, ord_out, (int)n,
-                                           0, bits, st));
-        h->stats.kernel_launches += 4;
-        CU(h->w_e.ensure((size_t)(nc + 1) * 12 + 64));
-        uint32_t *gsize = h->w_e.as<uint32_t>(), *gslot = gsize + nc, *goff = gslot + nc;
-        CU(cudaMemsetAsync(gsize, 0, (size_t)nc * 4, st));
-        CU(launch_hist(st, LAUNCHES, n, h->st_list.as<uint32_t>(), gsize));
-        CU(h->w_small.ensure(64));
-        CU(launch_slot_scan(st, LAUNCHES, nc, 1, gsize, gslot, goff, h->w_small.as<uint32_t>()));
-        // compute_alpha (:691-728) then sub-centroid assignment (:673-689)
-        CU(h->w_f.ensure(n * 8));
-        float *num = h->w_f.as<float>(), *den = num + n;
-        CU(launch_group_points(st, LAUNCHES, 0, nc, d, nsubc, h->st_x.as<float>(), ord_out, goff, h->centroids.as<float>(),
-                               h->nn_idx.as<uint32_t>(), h->icd.as<float>(), nullptr, num, den, nullptr));
-        CU(launch_alpha_reduce(st, LAUNCHES, nc, goff, num, den, h->alphas.as<float>()));
-        CU(h->st_sub.ensure(n));
-        CU(launch_group_points(st, LAUNCHES, 1, nc, d, nsubc, h->st_x.as<float>(), ord_out, goff, h->centroids.as<float>(),
-                               h->nn_idx.as<uint32_t>(), h->icd.as<float>(), h->alphas.as<float>(), nullptr, nullptr,
-                               h->st_sub.as<uint8_t>()));
         CU(h->st_codes.ensure(n * h->M));
         CU(h->st_norm.ensure(n));
-        if (int r = encode_dev(h, n, h->st_x.as<float>(), h->st_list.as<uint32_t>(), h->st_sub.as<uint8_t>(),
-                               h->st_codes.as<uint8_t>(), h->st_norm.as<uint8_t>()))
+        if (int r = ivfb200_encode_dev(h, n, h->st_x.as<float>(), h->st_list.as<uint32_t>(), h->st_sub.as<uint8_t>(),
+                               h->alphas.as<float>(), h->st_codes.as<uint8_t>(), h->st_norm.as<uint8_t>(), nullptr,
+                               nullptr))
             return r;
     }
     if (int r = build_csr(h)) return r;
@@ -960,7 +889,7 @@ static int search_core(ivfhnsw_b200_t *h, size_t nq, size_t k, const float *x_de
         const uint32_t *ci;
         if (cd_dev) { cd = cd_dev + q0 * nprobe; ci = ci_dev + q0 * nprobe; }
         else {
-            if (int r = coarse_dev(h, nb, xq, nprobe, 0, h->w_cd.as<float>(), h->w_ci.as<uint32_t>())) return r;
+            if (int r = ivfb200_coarse_dev(h, nb, xq, nprobe, 0, h->w_cd.as<float>(), h->w_ci.as<uint32_t>())) return r;
             cd = h->w_cd.as<float>(); ci = h->w_ci.as<uint32_t>();
         }
         if (h->timing) CU(cudaEventRecord(h->ev[1], st));

@@ -182,7 +182,7 @@ __global__ void __launch_bounds__(256) norm_encode_kernel(size_t n, int d, const
                                                           uint8_t *__restrict__ norm_codes, float *__restrict__ norms_out)
 {
     __shared__ float st_[256];
-    st_[threadIdx.x] = norm_table[threadIdx.x];
+    st_[threadIdx.x] = norm_table ? norm_table[threadIdx.x] : 0.f;
     __syncthreads();
     const int lane = threadIdx.x & 31, sub = lane & 3, b = lane & ~3;
     const size_t nthreads = (size_t)gridDim.x * blockDim.x;
@@ -211,7 +211,7 @@ __global__ void __launch_bounds__(256) norm_encode_kernel(size_t n, int d, const
             if (ob < best || (ob == best && oi < bi)) { best = ob; bi = oi; }
         }
         if (row < n && sub == 0) {
-            norm_codes[row] = (uint8_t)bi;
+            if (norm_codes) norm_codes[row] = (uint8_t)bi;
             if (norms_out) norms_out[row] = nr;
         }
     }
@@ -244,16 +244,16 @@ static __device__ __forceinline__ float faiss_inner_product_dev(const float *x, 
     int i = 0;
     for (; i + 8 <= d; i += 8)
 #pragma unroll
-        for (int l = 0; l < 8; l++) l8[l] = fmaf(x[(i + l) * ystride1], y[i + l], l8[l]);
+        for (int l = 0; l < 8; l++) l8[l] = __fadd_rn(l8[l], __fmul_rn(x[(i + l) * ystride1], y[i + l]));
     float l4[4];
 #pragma unroll
     for (int l = 0; l < 4; l++) l4[l] = l8[l + 4] + l8[l];
     if (d - i >= 4) {
 #pragma unroll
-        for (int l = 0; l < 4; l++) l4[l] = fmaf(x[(i + l) * ystride1], y[i + l], l4[l]);
+        for (int l = 0; l < 4; l++) l4[l] = __fadd_rn(l4[l], __fmul_rn(x[(i + l) * ystride1], y[i + l]));
         i += 4;
     }
-    for (int l = 0; i + l < d; l++) l4[l] = fmaf(x[(i + l) * ystride1], y[i + l], l4[l]);
+    for (int l = 0; i + l < d; l++) l4[l] = __fadd_rn(l4[l], __fmul_rn(x[(i + l) * ystride1], y[i + l]));
     return (l4[0] + l4[1]) + (l4[2] + l4[3]);
 }
 
@@ -317,7 +317,7 @@ __global__ void __launch_bounds__(256) group_points_kernel(int d, int nsubc, con
                     for (int l = 0; l < 8; l++) {
                         const float sc = __fadd_rn(cen[i + l], __fmul_rn(a, row[i + l]));
                         const float df = pt[i + l] - sc;
-                        l8[l] = fmaf(df, df, l8[l]);
+                        l8[l] = __fadd_rn(l8[l], __fmul_rn(df, df));
                     }
                 float dist = l8[0];
 #pragma unroll
@@ -334,7 +334,7 @@ __global__ void __launch_bounds__(256) group_points_kernel(int d, int nsubc, con
 #pragma unroll
                     for (int l = 0; l < 8; l++) {
                         const float df = row[i + l] - pt[i + l];
-                        l8[l] = fmaf(df, df, l8[l]);
+                        l8[l] = __fadd_rn(l8[l], __fmul_rn(df, df));
                     }
                 float dist = l8[0];
 #pragma unroll

@@ -67,7 +67,7 @@ static __device__ __forceinline__ float l2sqr16_octet(const float *__restrict__ 
     float acc = 0.f;
     for (int i = sub; i < n; i += 8) {
         const float df = x[i] - y[i];
-        acc = fmaf(df, df, acc);
+        acc = __fadd_rn(acc, __fmul_rn(df, df));   // unfused, like the pinned C restatement
     }
     const uint32_t lane = lane_id();
     const int base = lane & ~7;
