@@ -141,7 +141,20 @@ int ivfhnsw_b200_search_given_coarse_dev(ivfhnsw_b200_t *h, size_t nq, size_t k,
                                          float *distances_dev, int64_t *labels_dev);
 int ivfhnsw_b200_coarse_dev(ivfhnsw_b200_t *h, size_t nq, const float *x_dev, size_t nprobe,
                             float *dists_dev, uint32_t *idxs_dev);
+/* sharded search: this handle scans only the lists it owns (set_shard) and returns its
+ * sorted partial top-k together with the global scan-order key of every hit; coarse candidates NULL =
+ * computed here over the (replicated) centroid table, identical on every rank */
+int ivfhnsw_b200_search_partial_dev(ivfhnsw_b200_t *h, size_t nq, size_t k, const float *x_dev,
+                                    const float *coarse_dists_dev, const uint32_t *coarse_idxs_dev,
+                                    float *part_d_dev, uint32_t *part_seq_dev, int64_t *part_labels_dev);
+/* merge the partial results of nparts shards laid out [part][nq][k] (the output of an NCCL all-gather)
+ * into the final top-k by (distance, scan order) -- the same order a single GPU produces */
+int ivfhnsw_b200_merge_partials_dev(ivfhnsw_b200_t *h, size_t nq, size_t k, size_t nparts,
+                                    const float *part_d_dev, const uint32_t *part_seq_dev,
+                                    const int64_t *part_labels_dev, float *distances_dev, int64_t *labels_dev);
 int ivfhnsw_b200_sync(ivfhnsw_b200_t *h);
+/* run on a caller-owned CUDA stream (cudaStream_t, e.g. torch's current stream); NULL = back to a private one */
+int ivfhnsw_b200_set_stream(ivfhnsw_b200_t *h, void *stream);
 
 /* -- introspection for tests, bench and profiles ----------------------------*/
 typedef struct ivfhnsw_b200_stats {

@@ -90,7 +90,10 @@ def lib():
         "ivfhnsw_b200_search_dev": ([H, sz, sz, vp, vp, vp], C.c_int),
         "ivfhnsw_b200_search_given_coarse_dev": ([H, sz, sz, vp, vp, vp, vp, vp], C.c_int),
         "ivfhnsw_b200_coarse_dev": ([H, sz, vp, sz, vp, vp], C.c_int),
+        "ivfhnsw_b200_search_partial_dev": ([H, sz, sz, vp, vp, vp, vp, vp, vp], C.c_int),
+        "ivfhnsw_b200_merge_partials_dev": ([H, sz, sz, sz, vp, vp, vp, vp, vp], C.c_int),
         "ivfhnsw_b200_sync": ([H], C.c_int),
+        "ivfhnsw_b200_set_stream": ([H, vp], C.c_int),
         "ivfhnsw_b200_set_timing": ([H, C.c_int], C.c_int),
         "ivfhnsw_b200_get_stats": ([H, C.POINTER(Stats)], C.c_int),
         "ivfhnsw_b200_reset_stats": ([H], C.c_int),
@@ -473,6 +476,21 @@ class IndexIVF_HNSW:
         """The C-ABI call with caller-owned HOST buffers (numpy or pinned torch): H2D + search + D2H."""
         self._push_params()
         self._ck(self._L.ivfhnsw_b200_search(self._h, x_host.shape[0], k, _ptr(x_host), _ptr(D_host), _ptr(L_host)))
+
+    def search_partial_dev(self, k, x_dev, part_d, part_seq, part_labels, coarse=None):
+        """This shard's sorted partial top-k (dist, scan-order key, label) for all queries."""
+        self._push_params()
+        cd, ci = (None, None) if coarse is None else coarse
+        self._ck(self._L.ivfhnsw_b200_search_partial_dev(self._h, x_dev.shape[0], k, _ptr(x_dev), _ptr(cd), _ptr(ci),
+                                                         _ptr(part_d), _ptr(part_seq), _ptr(part_labels)))
+
+    def merge_partials_dev(self, k, nq, nparts, part_d, part_seq, part_labels, D_dev, L_dev):
+        self._ck(self._L.ivfhnsw_b200_merge_partials_dev(self._h, nq, k, nparts, _ptr(part_d), _ptr(part_seq),
+                                                         _ptr(part_labels), _ptr(D_dev), _ptr(L_dev)))
+
+    def set_stream(self, cuda_stream_ptr):
+        """Run on a caller-owned stream, e.g. torch.cuda.current_stream().cuda_stream (0/None = private)."""
+        self._ck(self._L.ivfhnsw_b200_set_stream(self._h, cuda_stream_ptr or None))
 
     def sync(self):
         self._ck(self._L.ivfhnsw_b200_sync(self._h))

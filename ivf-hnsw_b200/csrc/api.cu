@@ -156,7 +156,7 @@ void ivfhnsw_b200_destroy(ivfhnsw_b200_t *h)
     for (DevBuf *b : bufs) b->release();
     for (int i = 0; i < 4; i++)
         if (h->ev[i]) cudaEventDestroy(h->ev[i]);
-    if (h->stream) cudaStreamDestroy(h->stream);
+    if (h->stream && h->own_stream) cudaStreamDestroy(h->stream);
     delete h;
 }
 
@@ -231,6 +231,20 @@ int ivfhnsw_b200_set_option(ivfhnsw_b200_t *h, const char *name, long v)
     return 0;
 }
 int ivfhnsw_b200_set_timing(ivfhnsw_b200_t *h, int t) { h->timing = t != 0; return 0; }
+int ivfhnsw_b200_set_stream(ivfhnsw_b200_t *h, void *stream)
+{
+    if (bind(h)) return IVFHNSW_B200_ECUDA;
+    CU(cudaStreamSynchronize(h->stream));
+    if (h->own_stream && h->stream) CU(cudaStreamDestroy(h->stream));
+    if (stream) {
+        h->stream = reinterpret_cast<cudaStream_t>(stream);
+        h->own_stream = false;
+    } else {
+        CU(cudaStreamCreateWithFlags(&h->stream, cudaStreamNonBlocking));
+        h->own_stream = true;
+    }
+    return 0;
+}
 int ivfhnsw_b200_sync(ivfhnsw_b200_t *h)
 {
     if (bind(h)) return IVFHNSW_B200_ECUDA;
@@ -812,7 +826,7 @@ int ivfhnsw_b200_export_lists(ivfhnsw_b200_t *h, int64_t *list_off, uint32_t *id
 static size_t align256(size_t x) { return (x + 255) & ~(size_t)255; }
 
 static int search_core(ivfhnsw_b200_t *h, size_t nq, size_t k, const float *x_dev, const float *cd_dev,
-                       const uint32_t *ci_dev, float *out_d, int64_t *out_l)
+                       const uint32_t *ci_dev, float *out_d, int64_t *out_l, uint32_t *out_seq = nullptr)
 {
     if (!h->have_lists || h->st_dirty) return h->fail(IVFHNSW_B200_ESTATE, "lists not built: call finalize()/read() first");
     if (!h->have_pq || !h->have_norm) return h->fail(IVFHNSW_B200_ESTATE, "PQ codebooks not set");
@@ -910,10 +924,12 @@ static int search_core(ivfhnsw_b200_t *h, size_t nq, size_t k, const float *x_de
             pl = ps + (size_t)qb * nsplit * k;
         }
         CU(launch_scan(st, LAUNCHES, M, grouping, nb, d, nprobe, nsubc, (int)k, nsplit, xq, h->pqc.as<float>(),
-                       h->norm_table.as<float>(), L, T, pd, ps, pl, out_d + q0 * k, out_l + q0 * k));
+                       h->norm_table.as<float>(), L, T, pd, ps, pl, out_d + q0 * k, out_l + q0 * k,
+                       out_seq ? out_seq + q0 * k : nullptr));
         if (h->timing) CU(cudaEventRecord(h->ev[3], st));
         if (nsplit > 1)
-            CU(launch_merge(st, LAUNCHES, nb, (int)k, nsplit, pd, ps, pl, L.ids, out_d + q0 * k, out_l + q0 * k));
+            CU(launch_merge(st, LAUNCHES, nb, (int)k, nsplit, pd, ps, pl, L.ids, out_d + q0 * k, out_l + q0 * k,
+                            out_seq ? out_seq + q0 * k : nullptr));
         if (h->timing) {
             CU(cudaStreamSynchronize(st));
             float ms = 0;
@@ -944,6 +960,23 @@ int ivfhnsw_b200_search_dev(ivfhnsw_b200_t *h, size_t nq, size_t k, const float 
 {
     if (bind(h)) return IVFHNSW_B200_ECUDA;
     return search_core(h, nq, k, x_dev, nullptr, nullptr, dd, ld);
+}
+
+int ivfhnsw_b200_search_partial_dev(ivfhnsw_b200_t *h, size_t nq, size_t k, const float *x_dev, const float *cd_dev,
+                                    const uint32_t *ci_dev, float *part_d, uint32_t *part_seq, int64_t *part_labels)
+{
+    if (bind(h)) return IVFHNSW_B200_ECUDA;
+    return search_core(h, nq, k, x_dev, cd_dev, ci_dev, part_d, part_labels, part_seq);
+}
+int ivfhnsw_b200_merge_partials_dev(ivfhnsw_b200_t *h, size_t nq, size_t k, size_t nparts, const float *part_d,
+                                    const uint32_t *part_seq, const int64_t *part_labels, float *out_d,
+                                    int64_t *out_labels)
+{
+    if (bind(h)) return IVFHNSW_B200_ECUDA;
+    if (nparts == 0 || nparts > 64) return h->fail(IVFHNSW_B200_EINVAL, "nparts out of range");
+    CU(launch_merge_shards(h->stream, LAUNCHES, (int)nq, (int)k, (int)nparts, part_d, part_seq, part_labels, out_d,
+                           out_labels));
+    return 0;
 }
 
 static int search_host(ivfhnsw_b200_t *h, size_t nq, size_t k, const float *x, const float *cd, const uint32_t *ci,

@@ -54,10 +54,15 @@ size_t scan_smem_bytes(int M, int nprobe, int k, int nsubc);
 cudaError_t launch_scan(cudaStream_t st, uint64_t *launches, int M, bool grouping, int nq, int d, int nprobe,
                         int nsubc, int k, int nsplit, const float *queries, const float *pqc,
                         const float *norm_table, const DeviceLists &L, const SegTables &T, float *part_d,
-                        uint32_t *part_seq, uint32_t *part_slot, float *out_d, int64_t *out_labels);
+                        uint32_t *part_seq, uint32_t *part_slot, float *out_d, int64_t *out_labels,
+                        uint32_t *out_seq /* optional */);
 cudaError_t launch_merge(cudaStream_t st, uint64_t *launches, int nq, int k, int nsplit, const float *part_d,
                          const uint32_t *part_seq, const uint32_t *part_slot, const uint32_t *ids,
-                         float *out_d, int64_t *out_labels);
+                         float *out_d, int64_t *out_labels, uint32_t *out_seq /* optional */);
+// merge of nparts shard results laid out [part][nq][k] (what an all-gather produces)
+cudaError_t launch_merge_shards(cudaStream_t st, uint64_t *launches, int nq, int k, int nparts, const float *part_d,
+                                const uint32_t *part_seq, const int64_t *part_labels, float *out_d,
+                                int64_t *out_labels);
 
 // ----------------------------------------------------------------------------- small dense helpers
 // out[n][d] = x[n][d] * A^T (transpose == false: y = A x per row, LinearTransform::apply_noalloc)

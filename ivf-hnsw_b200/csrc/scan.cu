@@ -106,8 +106,11 @@ cudaError_t launch_prep_adc(cudaStream_t st, uint64_t *launches, int nq, int npr
 // =============================================================================================
 // K-G1a: distances from each query to the neighbour centroids n_s of every probed list
 // (the lazily memoised ivfhnsw::fvec_L2sqr calls of IndexIVF_HNSW_Grouping.cpp:246-250,312-316).
-// One CTA per query.  The memo semantics are kept: if n_s is itself one of the probed centroids
-// its distance is the coarse one (query_centroid_dists[n] was set at :207-220) unless that value
+// One CTA per query.  Like the reference's nc-sized memo (query_centroid_dists, :57) every distinct
+// centroid is evaluated ONCE per query: the neighbour ids of all probed lists are de-duplicated in a
+// shared-memory hash table (the 64-NN lists of the probed centroids overlap heavily), which cuts the
+// gathered centroid rows -- the dominant traffic of this stage -- several-fold.  Memo semantics kept:
+// a neighbour that is itself a probed centroid reuses the coarse distance (:207-220) unless that value
 // is < EPS, in which case the reference recomputes it.
 // Output: T.qsd[q][i][s] = d(q, n_s)   (0 where the list or the sub-group is empty)
 // =============================================================================================
@@ -120,48 +123,70 @@ __global__ void __launch_bounds__(256) group_dqn_kernel(int d, int nprobe, int n
     extern __shared__ __align__(16) uint8_t sm[];
     float *sq = reinterpret_cast<float *>(sm);                         // [d]
     uint32_t *hk = reinterpret_cast<uint32_t *>(sq + d);               // [ht_size] keys
-    float *hv = reinterpret_cast<float *>(hk + ht_size);               // [ht_size] values
+    float *hv = reinterpret_cast<float *>(hk + ht_size);               // [ht_size] values (NaN = to compute)
+    uint16_t *work = reinterpret_cast<uint16_t *>(hv + ht_size);       // [ht_size] slots to compute
+    __shared__ int s_nwork;
     const int q = blockIdx.x, tid = threadIdx.x;
+    const float qnan = __int_as_float(0x7fc00000);
     for (int i = tid; i < d; i += blockDim.x) sq[i] = queries[(size_t)q * d + i];
     for (int i = tid; i < ht_size; i += blockDim.x) hk[i] = 0xffffffffu;
+    if (tid == 0) s_nwork = 0;
     __syncthreads();
     const uint32_t hmask = ht_size - 1;
+    // memo of the coarse stage
     for (int i = tid; i < nprobe; i += blockDim.x) {
         const uint32_t c = coarse_i[(size_t)q * nprobe + i];
+        const float v = coarse_d[(size_t)q * nprobe + i];
         uint32_t p = (c * 2654435761u) & hmask;
         while (true) {
             const uint32_t prev = atomicCAS(&hk[p], 0xffffffffu, c);
-            if (prev == 0xffffffffu || prev == c) { hv[p] = coarse_d[(size_t)q * nprobe + i]; break; }
+            if (prev == 0xffffffffu || prev == c) { hv[p] = v >= 0.00001f ? v : qnan; break; }
             p = (p + 1) & hmask;
         }
     }
     __syncthreads();
-    const int lane = tid & 31, warp = tid >> 5, oct = lane >> 3, sub = lane & 7;
     const int npairs = nprobe * nsubc;
-    for (int e0 = warp * 4; e0 < npairs; e0 += (blockDim.x >> 5) * 4) {
-        const int e = e0 + oct;
-        bool need = false;
-        uint32_t n = 0;
-        float memo = 0.f;
-        bool have_memo = false;
-        if (e < npairs) {
-            const int i = e / nsubc, s = e - i * nsubc;
-            const uint32_t c = coarse_i[(size_t)q * nprobe + i];
-            if (L.list_size[c] != 0 && L.sub_sizes[(size_t)c * nsubc + s] != 0) {
-                need = true;
-                n = L.nn_idx[(size_t)c * nsubc + s];
-                uint32_t p = (n * 2654435761u) & hmask;
-                while (true) {
-                    const uint32_t kx = hk[p];
-                    if (kx == 0xffffffffu) break;
-                    if (kx == n) { memo = hv[p]; have_memo = memo >= 0.00001f; break; }
-                    p = (p + 1) & hmask;
-                }
-            }
+    // insert every needed neighbour id once
+    for (int e = tid; e < npairs; e += blockDim.x) {
+        const int i = e / nsubc, s = e - i * nsubc;
+        const uint32_t c = coarse_i[(size_t)q * nprobe + i];
+        if (L.list_size[c] == 0 || L.sub_sizes[(size_t)c * nsubc + s] == 0) continue;
+        const uint32_t n = L.nn_idx[(size_t)c * nsubc + s];
+        uint32_t p = (n * 2654435761u) & hmask;
+        while (true) {
+            const uint32_t prev = atomicCAS(&hk[p], 0xffffffffu, n);
+            if (prev == 0xffffffffu) { hv[p] = qnan; break; }
+            if (prev == n) break;
+            p = (p + 1) & hmask;
         }
+    }
+    __syncthreads();
+    for (int p = tid; p < ht_size; p += blockDim.x) {
+        const float v = hv[p];
+        if (hk[p] != 0xffffffffu && v != v) work[atomicAdd(&s_nwork, 1)] = (uint16_t)p;
+    }
+    __syncthreads();
+    const int nwork = s_nwork;
+    const int lane = tid & 31, warp = tid >> 5, oct = lane >> 3, sub = lane & 7;
+    for (int w0 = warp * 4; w0 < nwork; w0 += (blockDim.x >> 5) * 4) {
+        const int w = w0 + oct;
+        const int p = w < nwork ? work[w] : 0;
+        const uint32_t n = w < nwork ? hk[p] : 0u;
         const float dist = l2sqr16_octet(sq, L.centroids + (size_t)n * d, d, sub);
-        if (e < npairs && sub == 0)
-            T.qsd[(size_t)q * npairs + e] = need ? (have_memo ? memo : dist) : 0.f;
+        if (w < nwork && sub == 0) hv[p] = dist;
+    }
+    __syncthreads();
+    for (int e = tid; e < npairs; e += blockDim.x) {
+        const int i = e / nsubc, s = e - i * nsubc;
+        const uint32_t c = coarse_i[(size_t)q * nprobe + i];
+        float out = 0.f;
+        if (L.list_size[c] != 0 && L.sub_sizes[(size_t)c * nsubc + s] != 0) {
+            const uint32_t n = L.nn_idx[(size_t)c * nsubc + s];
+            uint32_t p = (n * 2654435761u) & hmask;
+            while (hk[p] != n) p = (p + 1) & hmask;
+            out = hv[p];
+        }
+        T.qsd[(size_t)q * npairs + e] = out;
     }
 }
 
@@ -348,8 +373,9 @@ cudaError_t launch_prep_grouping(cudaStream_t st, uint64_t *launches, int nq, in
 {
     if (nq == 0) return cudaSuccess;
     int ht = 64;
-    while (ht < 4 * nprobe) ht <<= 1;
-    const size_t sm1 = (size_t)d * 4 + (size_t)ht * 8;
+    while (ht < nprobe * nsubc + nprobe + 1) ht <<= 1;   // can never fill up
+    if (ht > 65536) return cudaErrorInvalidValue;       // uint16 work list
+    const size_t sm1 = (size_t)d * 4 + (size_t)ht * 10;
     cudaError_t e = cudaFuncSetAttribute(group_dqn_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sm1);
     if (e != cudaSuccess) return e;
     group_dqn_kernel<<<nq, 256, sm1, st>>>(d, nprobe, nsubc, ht, queries, coarse_d, coarse_i, L, T);
@@ -378,6 +404,7 @@ struct ScanArgs {
     uint32_t *part_slot;
     float *out_d;             // [nq][k]   (nsplit == 1)
     int64_t *out_labels;
+    uint32_t *out_seq;        // [nq][k] scan-order keys of the results (optional, sharded search)
 };
 
 template <int M> struct ScanCfg {
@@ -414,7 +441,16 @@ struct ScanCtl {
     int pad[3];
 };
 
-// Merge one warp's candidate buffer into the CTA top-k.  Warp-collective.
+static __device__ __forceinline__ uint32_t fkey_u32(float f)
+{
+    const uint32_t b = __float_as_uint(f);
+    return (b & 0x80000000u) ? ~b : (b | 0x80000000u);   // order-preserving float -> uint
+}
+
+// Merge one warp's candidate buffer (<= SCAN_WCAP = 64 entries) into the CTA top-k.  Warp-collective.
+// Candidates are pre-filtered lane-parallel against the current worst entry (two per lane); only the
+// survivors are inserted one by one under the CTA lock, and the survivor mask is re-evaluated after
+// every insertion because the worst entry only improves.
 static __device__ __forceinline__ void flush_candidates(volatile ScanCtl *ctl, float *topk_d, uint32_t *topk_seq,
                                                         uint32_t *topk_slot, int k, const float *wd,
                                                         const uint32_t *wseq, const uint32_t *wslot, int count,
@@ -422,53 +458,62 @@ static __device__ __forceinline__ void flush_candidates(volatile ScanCtl *ctl, f
 {
     if (count == 0) return;
     __syncwarp();
+    const bool h0 = lane < count, h1 = lane + 32 < count;
+    const float d0 = h0 ? wd[lane] : FLT_MAX, d1 = h1 ? wd[lane + 32] : FLT_MAX;
+    const uint32_t s0 = h0 ? wseq[lane] : 0xffffffffu, s1 = h1 ? wseq[lane + 32] : 0xffffffffu;
+    float w_d = ctl->worst_d;          // unlocked read: stale values are only larger
+    uint32_t w_s = ctl->worst_seq;
+    bool a0 = h0 && key_less(d0, s0, w_d, w_s), a1 = h1 && key_less(d1, s1, w_d, w_s);
+    if (!__any_sync(IVF_FULL_MASK, a0 || a1)) return;
     if (lane == 0) {
         while (atomicCAS((int *)&ctl->lock, 0, 1) != 0) { }
         __threadfence_block();
     }
     __syncwarp();
-    for (int c = 0; c < count; c++) {
-        const float cd = wd[c];
-        const uint32_t cs = wseq[c];
-        const float w_d = ctl->worst_d;
-        const uint32_t w_s = ctl->worst_seq;
-        if (key_less(cd, cs, w_d, w_s)) {
-            const int wp = ctl->worst_pos;
-            if (lane == 0) {
-                topk_d[wp] = cd;
-                topk_seq[wp] = cs;
-                topk_slot[wp] = wslot[c];
-            }
-            __syncwarp();
-            // new worst = lexicographic max over the k entries
-            float bd = -FLT_MAX;
-            uint32_t bs = 0;
-            int bp = -1;
-            for (int e = lane; e < k; e += 32) {
-                const float ed = topk_d[e];
-                const uint32_t es = topk_seq[e];
-                if (bp < 0 || key_less(bd, bs, ed, es)) { bd = ed; bs = es; bp = e; }
-            }
-#pragma unroll
-            for (int off = 16; off > 0; off >>= 1) {
-                const float od = __shfl_xor_sync(IVF_FULL_MASK, bd, off);
-                const uint32_t os = __shfl_xor_sync(IVF_FULL_MASK, bs, off);
-                const int op = __shfl_xor_sync(IVF_FULL_MASK, bp, off);
-                if (op >= 0 && (bp < 0 || key_less(bd, bs, od, os))) { bd = od; bs = os; bp = op; }
-            }
-            if (lane == 0) {
-                ctl->worst_pos = bp;
-                ctl->worst_seq = bs;
-                ctl->worst_d = bd;
-            }
-            __syncwarp();
+    w_d = ctl->worst_d;
+    w_s = ctl->worst_seq;
+    int wp = ctl->worst_pos;
+    while (true) {
+        a0 = a0 && key_less(d0, s0, w_d, w_s);
+        a1 = a1 && key_less(d1, s1, w_d, w_s);
+        const uint32_t b0 = __ballot_sync(IVF_FULL_MASK, a0), b1 = __ballot_sync(IVF_FULL_MASK, a1);
+        if (!(b0 | b1)) break;
+        const int src = b0 ? (__ffs(b0) - 1) : (__ffs(b1) - 1);
+        const float cd = __shfl_sync(IVF_FULL_MASK, b0 ? d0 : d1, src);
+        const uint32_t cs = __shfl_sync(IVF_FULL_MASK, b0 ? s0 : s1, src);
+        if (lane == src) { if (b0) a0 = false; else a1 = false; }
+        if (lane == 0) {
+            topk_d[wp] = cd;
+            topk_seq[wp] = cs;
+            topk_slot[wp] = wslot[b0 ? src : src + 32];
         }
+        __syncwarp();
+        // new worst = lexicographic max of (dist, seq) over the k entries
+        uint32_t bk = 0, bs = 0;
+        float bd = 0.f;
+        int bp = -1;
+        for (int e = lane; e < k; e += 32) {
+            const float ed = topk_d[e];
+            const uint32_t ek = fkey_u32(ed), es = topk_seq[e];
+            if (bp < 0 || ek > bk || (ek == bk && es > bs)) { bk = ek; bs = es; bd = ed; bp = e; }
+        }
+        const uint32_t mk = __reduce_max_sync(IVF_FULL_MASK, bp >= 0 ? bk : 0u);
+        bool is = bp >= 0 && bk == mk;
+        const uint32_t ms = __reduce_max_sync(IVF_FULL_MASK, is ? bs : 0u);
+        is = is && bs == ms;
+        const int win = __ffs(__ballot_sync(IVF_FULL_MASK, is)) - 1;
+        wp = __shfl_sync(IVF_FULL_MASK, bp, win);
+        w_d = __shfl_sync(IVF_FULL_MASK, bd, win);
+        w_s = ms;
     }
-    __syncwarp();
     if (lane == 0) {
+        ctl->worst_pos = wp;
+        ctl->worst_seq = w_s;
+        ctl->worst_d = w_d;
         __threadfence_block();
         atomicExch((int *)&ctl->lock, 0);
     }
+    __syncwarp();
 }
 
 template <int M, bool GROUPING>
@@ -702,6 +747,7 @@ __global__ void __launch_bounds__(SCAN_THREADS) scan_kernel(ScanArgs a)
         if (a.nsplit == 1) {
             a.out_d[(size_t)q * k + rank] = ed;
             a.out_labels[(size_t)q * k + rank] = slot == IVF_INVALID_SLOT ? (int64_t)-1 : (int64_t)a.L.ids[slot];
+            if (a.out_seq) a.out_seq[(size_t)q * k + rank] = es;
         } else {
             const size_t o = ((size_t)q * a.nsplit + split) * k + rank;
             a.part_d[o] = ed;
@@ -724,10 +770,12 @@ static cudaError_t launch_scan_t(cudaStream_t st, int nq, const ScanArgs &a)
 cudaError_t launch_scan(cudaStream_t st, uint64_t *launches, int M, bool grouping, int nq, int d, int nprobe,
                         int nsubc, int k, int nsplit, const float *queries, const float *pqc,
                         const float *norm_table, const DeviceLists &L, const SegTables &T, float *part_d,
-                        uint32_t *part_seq, uint32_t *part_slot, float *out_d, int64_t *out_labels)
+                        uint32_t *part_seq, uint32_t *part_slot, float *out_d, int64_t *out_labels,
+                        uint32_t *out_seq)
 {
     if (nq == 0) return cudaSuccess;
     ScanArgs a;
+    a.out_seq = out_seq;
     a.d = d; a.nprobe = nprobe; a.nsubc = grouping ? nsubc : 0; a.k = k; a.nsplit = nsplit;
     a.queries = queries; a.pqc = pqc; a.norm_table = norm_table; a.L = L; a.T = T;
     a.part_d = part_d; a.part_seq = part_seq; a.part_slot = part_slot; a.out_d = out_d; a.out_labels = out_labels;
@@ -746,26 +794,32 @@ cudaError_t launch_scan(cudaStream_t st, uint64_t *launches, int M, bool groupin
 }
 
 // =============================================================================================
-// K-M1: merge the nsplit sorted partial top-k lists of each query (keys are unique per query)
+// K-M1: merge the sorted partial top-k lists of each query (keys (dist, seq) are unique per query).
+// List s of query q starts at q * q_stride + s * p_stride.  LABELS_IN = false: payload is a slot that
+// is translated through ids[] (splits of one GPU); true: payload already is the int64 label (shards
+// gathered from several GPUs).
 // =============================================================================================
-__global__ void __launch_bounds__(256) merge_kernel(int k, int nsplit, const float *__restrict__ part_d,
+template <bool LABELS_IN>
+__global__ void __launch_bounds__(256) merge_kernel(int k, int nparts, size_t q_stride, size_t p_stride,
+                                                    const float *__restrict__ part_d,
                                                     const uint32_t *__restrict__ part_seq,
-                                                    const uint32_t *__restrict__ part_slot,
+                                                    const void *__restrict__ part_payload,
                                                     const uint32_t *__restrict__ ids, float *out_d,
-                                                    int64_t *out_labels)
+                                                    int64_t *out_labels, uint32_t *out_seq)
 {
     const int q = blockIdx.x;
-    const size_t base = (size_t)q * nsplit * k;
-    const int n = nsplit * k;
+    const size_t base = (size_t)q * q_stride;
+    const int n = nparts * k;
     for (int e = threadIdx.x; e < n; e += blockDim.x) {
-        const float ed = part_d[base + e];
-        const uint32_t es = part_seq[base + e];
-        const int mine = e / k;
-        int rank = e - mine * k;  // elements before it in its own (sorted) list
-        for (int s = 0; s < nsplit && rank < k; s++) {
+        const int mine = e / k, pos = e - mine * k;
+        const size_t me = base + (size_t)mine * p_stride + pos;
+        const float ed = part_d[me];
+        const uint32_t es = part_seq[me];
+        int rank = pos;  // elements before it in its own (sorted) list
+        for (int s = 0; s < nparts && rank < k; s++) {
             if (s == mine) continue;
-            const float *ld = part_d + base + (size_t)s * k;
-            const uint32_t *ls = part_seq + base + (size_t)s * k;
+            const float *ld = part_d + base + (size_t)s * p_stride;
+            const uint32_t *ls = part_seq + base + (size_t)s * p_stride;
             int lo = 0, hi = k;  // count of elements of list s that come before (ed, es)
             while (lo < hi) {
                 const int mid = (lo + hi) >> 1;
@@ -778,19 +832,37 @@ __global__ void __launch_bounds__(256) merge_kernel(int k, int nsplit, const flo
             rank += lo;
         }
         if (rank < k) {
-            const uint32_t slot = part_slot[base + e];
+            int64_t lab;
+            if (LABELS_IN) lab = reinterpret_cast<const int64_t *>(part_payload)[me];
+            else {
+                const uint32_t slot = reinterpret_cast<const uint32_t *>(part_payload)[me];
+                lab = slot == IVF_INVALID_SLOT ? (int64_t)-1 : (int64_t)ids[slot];
+            }
             out_d[(size_t)q * k + rank] = ed;
-            out_labels[(size_t)q * k + rank] = slot == IVF_INVALID_SLOT ? (int64_t)-1 : (int64_t)ids[slot];
+            out_labels[(size_t)q * k + rank] = lab;
+            if (out_seq) out_seq[(size_t)q * k + rank] = es;
         }
     }
 }
 
 cudaError_t launch_merge(cudaStream_t st, uint64_t *launches, int nq, int k, int nsplit, const float *part_d,
                          const uint32_t *part_seq, const uint32_t *part_slot, const uint32_t *ids,
-                         float *out_d, int64_t *out_labels)
+                         float *out_d, int64_t *out_labels, uint32_t *out_seq)
 {
     if (nq == 0) return cudaSuccess;
-    merge_kernel<<<nq, 256, 0, st>>>(k, nsplit, part_d, part_seq, part_slot, ids, out_d, out_labels);
+    merge_kernel<false><<<nq, 256, 0, st>>>(k, nsplit, (size_t)nsplit * k, (size_t)k, part_d, part_seq, part_slot, ids,
+                                            out_d, out_labels, out_seq);
+    ++*launches;
+    return cudaGetLastError();
+}
+
+cudaError_t launch_merge_shards(cudaStream_t st, uint64_t *launches, int nq, int k, int nparts, const float *part_d,
+                                const uint32_t *part_seq, const int64_t *part_labels, float *out_d,
+                                int64_t *out_labels)
+{
+    if (nq == 0) return cudaSuccess;
+    merge_kernel<true><<<nq, 256, 0, st>>>(k, nparts, (size_t)k, (size_t)nq * k, part_d, part_seq, part_labels, nullptr,
+                                           out_d, out_labels, nullptr);
     ++*launches;
     return cudaGetLastError();
 }
