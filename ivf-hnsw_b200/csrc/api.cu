@@ -31,7 +31,6 @@ cudaError_t launch_gather_lists(cudaStream_t st, uint64_t *launches, int nc, int
                                 const uint32_t *list_slot, const uint32_t *raw_off, const uint8_t *codes,
                                 const uint8_t *norm_codes, const uint32_t *ids, uint8_t *out_codes, uint8_t *out_norm,
                                 uint32_t *out_ids);
-cudaError_t launch_f32_to_bf16(cudaStream_t st, uint64_t *launches, size_t n, const float *x, void *out);
 }  // namespace ivfb200
 
 using namespace ivfb200;
@@ -147,11 +146,11 @@ void ivfhnsw_b200_destroy(ivfhnsw_b200_t *h)
         cudaSetDevice(h->device);
         cudaStreamSynchronize(h->stream);
     }
-    DevBuf *bufs[] = {&h->centroids, &h->centroid_norms, &h->cnorm_gemm, &h->cent_bf16, &h->pqc, &h->norm_table,
+    DevBuf *bufs[] = {&h->centroids, &h->centroid_norms, &h->cnorm_gemm, &h->cent_f16, &h->pqc, &h->norm_table,
                       &h->opqA, &h->list_size, &h->list_slot, &h->raw_off, &h->codes, &h->norm_codes, &h->sub_ids,
                       &h->ids, &h->nn_idx, &h->sub_sizes, &h->alphas, &h->icd, &h->st_list, &h->st_ids, &h->st_codes,
                       &h->st_norm, &h->st_sub, &h->st_x, &h->w_x, &h->w_xrot, &h->w_cd, &h->w_ci, &h->w_seg,
-                      &h->w_sub_base, &h->w_qsd, &h->w_part, &h->w_coarse, &h->w_xbf16, &h->w_out_d, &h->w_out_l,
+                      &h->w_sub_base, &h->w_qsd, &h->w_part, &h->w_coarse, &h->w_xf16, &h->w_out_d, &h->w_out_l,
                       &h->w_a, &h->w_b, &h->w_c, &h->w_d2, &h->w_e, &h->w_f, &h->w_cub, &h->w_small, &h->counters};
     for (DevBuf *b : bufs) b->release();
     for (int i = 0; i < 4; i++)
@@ -184,7 +183,7 @@ int ivfhnsw_b200_set_centroids(ivfhnsw_b200_t *h, const float *c)
     if (int r = upload(h, h->centroids, c, h->nc * h->d * 4)) return r;
     h->have_centroids = true;
     h->gemm_norms_valid = false;
-    h->bf16_valid = false;
+    h->f16_valid = false;
     if (!h->have_lists) h->have_group_meta = false;
     return 0;
 }
@@ -294,23 +293,42 @@ int ivfhnsw_b200_rotate_quantizer(ivfhnsw_b200_t *h)
     CU(cudaMemcpyAsync(h->centroids.p, h->w_a.p, h->nc * h->d * 4, cudaMemcpyDeviceToDevice, h->stream));
     CU(cudaStreamSynchronize(h->stream));
     h->gemm_norms_valid = false;
-    h->bf16_valid = false;
+    h->f16_valid = false;
     return 0;
 }
 
 // ------------------------------------------------------------------------------------ coarse helpers
+static bool use_tc(const ivfhnsw_b200_t *h) { return h->coarse_impl == 1 && coarse_tc_supported((int)h->d); }
+
+// carve the fp16 operand buffers: centroids [hi | lo | max bits], queries [hi | lo | fac]
+static TcSide tc_side(ivfhnsw_b200_t *h, size_t qb)
+{
+    TcSide S;
+    S.dp = (int)((h->d + 7) / 8 * 8);
+    S.chi = h->cent_f16.as<__half>();
+    S.clo = S.chi ? S.chi + h->nc * S.dp : nullptr;
+    S.cmax = S.chi ? reinterpret_cast<uint32_t *>(S.clo + h->nc * S.dp) : nullptr;
+    S.qhi = h->w_xf16.as<__half>();
+    S.qlo = S.qhi ? S.qhi + qb * S.dp : nullptr;
+    S.qfac = S.qhi ? reinterpret_cast<float *>(S.qlo + qb * S.dp) : nullptr;
+    return S;
+}
+
 static int ensure_gemm_side(ivfhnsw_b200_t *h)
 {
     if (!h->gemm_norms_valid) {
-        // ||c||^2 over ALL dims for the GEMM ranking value (the exact re-rank uses fstdistfunc numerics)
+        // ||c||^2 over the dims fstdistfunc uses, for the GEMM ranking value
         CU(h->cnorm_gemm.ensure(h->nc * 4));
-        CU(launch_row_norms(h->stream, LAUNCHES, h->nc, (int)h->d, h->centroids.as<float>(), h->cnorm_gemm.as<float>()));
+        CU(launch_row_norms(h->stream, LAUNCHES, h->nc, (int)h->d, h->centroids.as<float>(), h->cnorm_gemm.as<float>(),
+                            coarse_dims((int)h->d)));
         h->gemm_norms_valid = true;
     }
-    if (h->coarse_impl == 1 && !h->bf16_valid) {
-        CU(h->cent_bf16.ensure(h->nc * h->d * 2));
-        CU(launch_f32_to_bf16(h->stream, LAUNCHES, h->nc * h->d, h->centroids.as<float>(), h->cent_bf16.p));
-        h->bf16_valid = true;
+    if (use_tc(h) && !h->f16_valid) {
+        TcSide S = tc_side(h, 0);
+        CU(h->cent_f16.ensure(h->nc * S.dp * 4 + 64));
+        S = tc_side(h, 0);
+        CU(launch_tc_prepare_centroids(h->stream, LAUNCHES, h->nc, (int)h->d, h->centroids.as<float>(), S));
+        h->f16_valid = true;
     }
     return 0;
 }
@@ -326,7 +344,9 @@ int ivfb200_coarse_dev(ivfhnsw_b200_t *h, size_t nq, const float *xq, size_t npr
     const size_t per_q = coarse_work_bytes(1, (int)h->nc, (int)nprobe + slack, &cand_cap);
     size_t qb = std::min<size_t>(nq, std::max<size_t>(128, ((size_t)3 << 29) / per_q));
     CU(h->w_coarse.ensure(qb * per_q + 256));
-    if (h->coarse_impl == 1) CU(h->w_xbf16.ensure(qb * h->d * 2 + 256));
+    const int impl = use_tc(h) ? 1 : 0;
+    if (impl) CU(h->w_xf16.ensure(qb * ((h->d + 7) / 8 * 8) * 4 + qb * 4 + 256));
+    const TcSide S = tc_side(h, qb);
     const size_t ngroups = (h->nc + COARSE_GROUP - 1) / COARSE_GROUP;
     for (size_t q0 = 0; q0 < nq; q0 += qb) {
         const size_t nb = std::min(qb, nq - q0);
@@ -338,8 +358,8 @@ int ivfb200_coarse_dev(ivfhnsw_b200_t *h, size_t nq, const float *xq, size_t npr
         W.cand_cap = cand_cap;
         // exclude_self needs global row ids: only used with q0 == 0-based centroid batches
         const float *cents = h->centroids.as<float>();
-        CU(launch_coarse(h->stream, LAUNCHES, (int)h->coarse_impl, (int)nb, (int)h->nc, (int)h->d, (int)nprobe, slack,
-                         xq + q0 * h->d, cents, h->cnorm_gemm.as<float>(), h->cent_bf16.p, h->w_xbf16.p, W,
+        CU(launch_coarse(h->stream, LAUNCHES, impl, (int)nb, (int)h->nc, (int)h->d, (int)nprobe, slack,
+                         xq + q0 * h->d, cents, h->cnorm_gemm.as<float>(), S, W,
                          exclude_self ? (int)q0 : -1, out_d + q0 * nprobe, out_i + q0 * nprobe));
     }
     h->stats.coarse_flops += (uint64_t)2 * h->nc * h->d * nq;

@@ -27,7 +27,7 @@ namespace ivfb200 {
 #define CG_BN COARSE_GROUP
 #define CG_BK 8
 
-__global__ void __launch_bounds__(256) coarse_gemm_simt_kernel(int nq, int nc, int d, const float *__restrict__ Q,
+__global__ void __launch_bounds__(256) coarse_gemm_simt_kernel(int nq, int nc, int d, int dk, const float *__restrict__ Q,
                                                                const float *__restrict__ Cn,
                                                                const float *__restrict__ cnorm, int self_off,
                                                                float *__restrict__ grp_val,
@@ -47,10 +47,10 @@ __global__ void __launch_bounds__(256) coarse_gemm_simt_kernel(int nq, int nc, i
         for (int j = 0; j < 8; j++) acc[i][j] = 0.f;
 
     const int lrow = tid >> 1, lk = (tid & 1) * 4;
-    for (int k0 = 0; k0 < d; k0 += CG_BK) {
+    for (int k0 = 0; k0 < dk; k0 += CG_BK) {
         float4 av = make_float4(0, 0, 0, 0), bv = make_float4(0, 0, 0, 0);
-        if (q0 + lrow < nq && k0 + lk < d) av = *reinterpret_cast<const float4 *>(Q + (size_t)(q0 + lrow) * d + k0 + lk);
-        if (c0 + lrow < nc && k0 + lk < d) bv = *reinterpret_cast<const float4 *>(Cn + (size_t)(c0 + lrow) * d + k0 + lk);
+        if (q0 + lrow < nq && k0 + lk < dk) av = *reinterpret_cast<const float4 *>(Q + (size_t)(q0 + lrow) * d + k0 + lk);
+        if (c0 + lrow < nc && k0 + lk < dk) bv = *reinterpret_cast<const float4 *>(Cn + (size_t)(c0 + lrow) * d + k0 + lk);
         As[(lk + 0) * CG_BM + lrow] = av.x; As[(lk + 1) * CG_BM + lrow] = av.y;
         As[(lk + 2) * CG_BM + lrow] = av.z; As[(lk + 3) * CG_BM + lrow] = av.w;
         Bs[(lk + 0) * CG_BN + lrow] = bv.x; Bs[(lk + 1) * CG_BN + lrow] = bv.y;
@@ -126,7 +126,7 @@ __global__ void __launch_bounds__(256) coarse_select_kernel(int nc, int d, int n
                                                             const float *__restrict__ Cn,
                                                             const float *__restrict__ grp_val,
                                                             const uint32_t *__restrict__ grp_idx,
-                                                            int self_off, uint32_t *__restrict__ err,
+                                                            int packed, int self_off, uint32_t *__restrict__ err,
                                                             float *__restrict__ out_d, uint32_t *__restrict__ out_i)
 {
     extern __shared__ __align__(16) uint8_t smraw[];
@@ -139,7 +139,16 @@ __global__ void __launch_bounds__(256) coarse_select_kernel(int nc, int d, int n
     const int q = blockIdx.x, tid = threadIdx.x;
     const int n = ngroups * COARSE_T;
     const float *gv = grp_val + (size_t)q * n;
-    const uint32_t *gi = grp_idx + (size_t)q * n;
+    // packed (tensor-core GEMM): the centroid is group * COARSE_GROUP + low 7 bits of the value and
+    // masked entries are >= 1e38; otherwise ids come from grp_idx and masked entries have id ~0
+    const uint32_t *gi = packed ? nullptr : grp_idx + (size_t)q * n;
+    auto entry_id = [&](int i) -> uint32_t {
+        if (!packed) return gi[i];
+        const float v = gv[i];
+        if (!(v < 1.0e38f)) return 0xffffffffu;
+        const uint32_t id = (uint32_t)(i / COARSE_T) * COARSE_GROUP + (__float_as_uint(v) & 127u);
+        return (self_off >= 0 && id == (uint32_t)(q + self_off)) ? 0xffffffffu : id;
+    };
     for (int i = tid; i < d; i += 256) sq[i] = Q[(size_t)q * d + i];
     if (tid == 0) { s_prefix = 0; s_remaining = (uint32_t)kprime; s_ncand = 0; s_nflag = 0; s_less = 0; }
     __syncthreads();
@@ -173,7 +182,8 @@ __global__ void __launch_bounds__(256) coarse_select_kernel(int nc, int d, int n
     const uint32_t tau = s_prefix;       // key of the kprime-th smallest
     // ---- verify groups: a group whose COARSE_T-th kept value is <= tau may hide candidates
     for (int g = tid; g < ngroups; g += 256) {
-        if (fkey(gv[g * COARSE_T + COARSE_T - 1]) <= tau && gi[g * COARSE_T + COARSE_T - 1] != 0xffffffffu) {
+        if (fkey(gv[g * COARSE_T + COARSE_T - 1]) <= tau && (packed ? gv[g * COARSE_T + COARSE_T - 1] < 1.0e38f
+                                                                     : gi[g * COARSE_T + COARSE_T - 1] != 0xffffffffu)) {
             const uint32_t f = atomicAdd(&s_nflag, 1u);
             if (f < SEL_MAX_FLAGGED) s_flag[f] = (uint32_t)g;
         }
@@ -187,7 +197,7 @@ __global__ void __launch_bounds__(256) coarse_select_kernel(int nc, int d, int n
     // ---- collect: kept entries with key <= tau outside flagged groups, then flagged groups in full
     for (int i = tid; i < n; i += 256) {
         const uint32_t kx = fkey(gv[i]);
-        const uint32_t id = gi[i];
+        const uint32_t id = entry_id(i);
         if (kx <= tau && id != 0xffffffffu) {
             const uint32_t g = (uint32_t)(i / COARSE_T);
             bool flagged = false;
@@ -252,34 +262,31 @@ size_t coarse_work_bytes(int nq, int nc, int kprime, int *cand_cap)
 }
 
 cudaError_t launch_coarse_tc(cudaStream_t st, uint64_t *launches, int nq, int nc, int d, const float *queries,
-                             const void *cent_bf16, void *xq_bf16, const float *cnorm_gemm, int self_off,
-                             float *grp_val, uint32_t *grp_idx);  // coarse_tc.cu
+                             const float *cnorm_gemm, const TcSide &S, float *grp_val);  // coarse_tc.cu
 
 cudaError_t launch_coarse(cudaStream_t st, uint64_t *launches, int impl, int nq, int nc, int d, int nprobe,
                           int slack, const float *queries, const float *centroids, const float *cnorm_gemm,
-                          const void *cent_bf16, void *xq_bf16, const CoarseWork &W, int self_off,
-                          float *out_d, uint32_t *out_i)
+                          const TcSide &S, const CoarseWork &W, int self_off, float *out_d, uint32_t *out_i)
 {
     if (nq == 0) return cudaSuccess;
     const int ngroups = (nc + COARSE_GROUP - 1) / COARSE_GROUP;
     cudaError_t e;
     if (impl == 1) {
-        e = launch_coarse_tc(st, launches, nq, nc, d, queries, cent_bf16, xq_bf16, cnorm_gemm, self_off,
-                             W.grp_val, W.grp_idx);
+        e = launch_coarse_tc(st, launches, nq, nc, d, queries, cnorm_gemm, S, W.grp_val);
         if (e != cudaSuccess) return e;
     } else {
         const size_t sm = (size_t)(CG_BK * CG_BM + CG_BK * CG_BN + CG_BM * (CG_BN + 1)) * sizeof(float);
         e = cudaFuncSetAttribute(coarse_gemm_simt_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sm);
         if (e != cudaSuccess) return e;
         dim3 grid(ngroups, (nq + CG_BM - 1) / CG_BM);
-        coarse_gemm_simt_kernel<<<grid, 256, sm, st>>>(nq, nc, d, queries, centroids, cnorm_gemm, self_off,
+        coarse_gemm_simt_kernel<<<grid, 256, sm, st>>>(nq, nc, d, coarse_dims(d), queries, centroids, cnorm_gemm, self_off,
                                                       W.grp_val, W.grp_idx);
         ++*launches;
         e = cudaGetLastError();
         if (e != cudaSuccess) return e;
     }
     int avail = nc - (self_off >= 0 ? 1 : 0);
-    int kprime = nprobe + slack;
+    int kprime = nprobe + slack + ((impl == 1 && self_off >= 0) ? 1 : 0);   // the packed GEMM keeps the self match
     if (kprime > avail) kprime = avail;
     if (kprime > ngroups * COARSE_T) kprime = ngroups * COARSE_T;
     if (kprime < 1) kprime = 1;
@@ -287,7 +294,7 @@ cudaError_t launch_coarse(cudaStream_t st, uint64_t *launches, int impl, int nq,
     e = cudaFuncSetAttribute(coarse_select_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sm2);
     if (e != cudaSuccess) return e;
     coarse_select_kernel<<<nq, 256, sm2, st>>>(nc, d, ngroups, nprobe, kprime, W.cand_cap, queries, centroids,
-                                               W.grp_val, W.grp_idx, self_off, W.err, out_d, out_i);
+                                               W.grp_val, W.grp_idx, impl == 1 ? 1 : 0, self_off, W.err, out_d, out_i);
     ++*launches;
     return cudaGetLastError();
 }

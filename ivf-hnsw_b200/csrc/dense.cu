@@ -42,7 +42,7 @@ cudaError_t launch_rotate(cudaStream_t st, uint64_t *launches, size_t n, int d, 
 
 // faiss::fvec_norm_L2sqr (faiss/utils.cpp:632-650): 4 partial sums, (s0+s1)+(s2+s3).
 // Four consecutive lanes per row.
-__global__ void row_norms_kernel(size_t n, int d, const float *__restrict__ x, float *__restrict__ out)
+__global__ void row_norms_kernel(size_t n, int d, int dk, const float *__restrict__ x, float *__restrict__ out)
 {
     const size_t t = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
     const size_t row = t >> 2;
@@ -50,7 +50,7 @@ __global__ void row_norms_kernel(size_t n, int d, const float *__restrict__ x, f
     float acc = 0.f;
     if (row < n) {
         const float *r = x + row * d;
-        for (int i = sub; i < d; i += 4) acc = fmaf(r[i], r[i], acc);
+        for (int i = sub; i < dk; i += 4) acc = fmaf(r[i], r[i], acc);
     }
     const int lane = threadIdx.x & 31, b = lane & ~3;
     const float s0 = __shfl_sync(IVF_FULL_MASK, acc, b), s1 = __shfl_sync(IVF_FULL_MASK, acc, b + 1);
@@ -58,11 +58,11 @@ __global__ void row_norms_kernel(size_t n, int d, const float *__restrict__ x, f
     if (row < n && sub == 0) out[row] = (s0 + s1) + (s2 + s3);
 }
 
-cudaError_t launch_row_norms(cudaStream_t st, uint64_t *launches, size_t n, int d, const float *x, float *out)
+cudaError_t launch_row_norms(cudaStream_t st, uint64_t *launches, size_t n, int d, const float *x, float *out, int dk)
 {
     if (n == 0) return cudaSuccess;
     const size_t threads = n * 4;
-    row_norms_kernel<<<(unsigned)((threads + 255) / 256), 256, 0, st>>>(n, d, x, out);
+    row_norms_kernel<<<(unsigned)((threads + 255) / 256), 256, 0, st>>>(n, d, dk < 0 ? d : dk, x, out);
     ++*launches;
     return cudaGetLastError();
 }

@@ -71,9 +71,9 @@ struct ivfhnsw_b200 {
     std::mutex mu;
 
     // model
-    DevBuf centroids, centroid_norms, cnorm_gemm, cent_bf16, pqc, norm_table, opqA;
+    DevBuf centroids, centroid_norms, cnorm_gemm, cent_f16, pqc, norm_table, opqA;
     bool have_centroids = false, have_pq = false, have_norm = false, have_opq = false, have_cnorms = false;
-    bool gemm_norms_valid = false, bf16_valid = false;
+    bool gemm_norms_valid = false, f16_valid = false;
     // lists (device CSR in slot space)
     DevBuf list_size, list_slot, raw_off, codes, norm_codes, sub_ids, ids;
     DevBuf nn_idx, sub_sizes, alphas, icd;
@@ -84,7 +84,7 @@ struct ivfhnsw_b200 {
     size_t st_n = 0;          // encoded records staged (IVFADC) or points staged (Grouping)
     bool st_dirty = false;
     // workspace
-    DevBuf w_x, w_xrot, w_cd, w_ci, w_seg, w_sub_base, w_qsd, w_part, w_coarse, w_xbf16, w_out_d, w_out_l;
+    DevBuf w_x, w_xrot, w_cd, w_ci, w_seg, w_sub_base, w_qsd, w_part, w_coarse, w_xf16, w_out_d, w_out_l;
     DevBuf w_a, w_b, w_c, w_d2, w_e, w_f, w_cub, w_small;
     DevBuf counters;  // [0] scanned, [1] walked
     // options / stats

@@ -2,6 +2,7 @@
 // `st`, returns the cudaError of the launch and bumps *launches by the kernels it issued.
 #pragma once
 #include <cuda_runtime.h>
+#include <cuda_fp16.h>
 #include <cstddef>
 #include <cstdint>
 
@@ -69,7 +70,11 @@ cudaError_t launch_merge_shards(cudaStream_t st, uint64_t *launches, int nq, int
 //           = x[n][d] * A   (transpose == true : transform_transpose)
 cudaError_t launch_rotate(cudaStream_t st, uint64_t *launches, size_t n, int d, const float *A, bool transpose,
                           const float *x, float *out);
-cudaError_t launch_row_norms(cudaStream_t st, uint64_t *launches, size_t n, int d, const float *x, float *out);
+// squared norms of the first dk (< 0: all d) components of every row
+cudaError_t launch_row_norms(cudaStream_t st, uint64_t *launches, size_t n, int d, const float *x, float *out,
+                             int dk = -1);
+// dims the coarse distance really uses: hnswlib's fstdistfunc drops the d % 16 tail (hnswalg.cpp:326-356)
+static inline int coarse_dims(int d) { return (d >> 4) ? ((d >> 4) << 4) : d; }
 cudaError_t launch_u8_to_f32(cudaStream_t st, uint64_t *launches, size_t n, const uint8_t *x, float *out);
 
 // ----------------------------------------------------------------------------- coarse stage
@@ -82,11 +87,23 @@ struct CoarseWork {
     int cand_cap;
 };
 size_t coarse_work_bytes(int nq, int nc, int kprime, int *cand_cap);
+// operands of the tensor-core GEMM (coarse_tc.cu): fp16 hi/lo splits of the centroids and of the
+// current query batch, row pitch dp halves (a multiple of 8)
+struct TcSide {
+    __half *chi, *clo;      // [nc][dp]
+    uint32_t *cmax;         // [1] bits of max |centroid component|
+    __half *qhi, *qlo;      // [batch][dp]
+    float *qfac;            // [batch] -2 / (query scale * centroid scale)
+    int dp;
+};
+bool coarse_tc_supported(int d);
+cudaError_t launch_tc_prepare_centroids(cudaStream_t st, uint64_t *launches, size_t nc, int d, const float *centroids,
+                                        const TcSide &S);
 // exact top-`nprobe` (ascending (dist, idx), fstdistfunc numerics) of every query among `nc` centroids.
-// impl 0: fp32 SIMT tile GEMM; impl 1: tcgen05 bf16 GEMM (needs cent_bf16 / xq_bf16 scratch).
+// impl 0: fp32 SIMT tile GEMM; impl 1: tcgen05 split-fp16 GEMM (needs the TcSide operands).
 cudaError_t launch_coarse(cudaStream_t st, uint64_t *launches, int impl, int nq, int nc, int d, int nprobe,
                           int slack, const float *queries, const float *centroids, const float *cnorm_gemm,
-                          const void *cent_bf16, void *xq_bf16, const CoarseWork &W, int self_off /* -1 = none */,
+                          const TcSide &S, const CoarseWork &W, int self_off /* -1 = none */,
                           float *out_d, uint32_t *out_i);
 
 // ----------------------------------------------------------------------------- indexing

@@ -73,12 +73,15 @@ def test_search_splits_and_port(port, name, split):
 
 
 @pytest.mark.parametrize("name", golden_names())
-def test_coarse_exact_matches_port(port, name):
-    """K-A2: exact nprobe nearest centroids, ascending (dist, idx), fstdistfunc numerics."""
+@pytest.mark.parametrize("impl", [0, 1])
+def test_coarse_exact_matches_port(port, name, impl):
+    """K-A2: exact nprobe nearest centroids, ascending (dist, idx), fstdistfunc numerics; impl 0 is the
+    fp32 SIMT GEMM, impl 1 the tcgen05 split-fp16 GEMM -- both feed the same exact re-rank."""
     pkg = load_pkg()
     g, ix, runs = load_golden(name)
     nprobe = int(g["nprobe"])
     idx = make_index(pkg, ix)
+    idx.set_option("coarse_impl", impl)
     cd, ci = idx.coarse(g["Q"], nprobe)
     Q = g["Q"] if ix["opq"] is None else port.opq_apply(ix["opq"], g["Q"])
     pd, pi = port.coarse(Q, ix["centroids"], nprobe)
@@ -113,6 +116,35 @@ def test_full_search_recall_not_below_reference(port, name):
     # best distance found by the exact coarse stage is never worse than the HNSW one
     Dr = np.sort(g["D_" + tag], axis=1)
     assert np.mean(D[:, 0] <= Dr[:, 0] * (1 + 1e-4) + 1e-3 * scale * 1e-2) >= 0.99
+    idx.close()
+
+
+@pytest.mark.parametrize("shape", [(96, 1000, 300, 16), (128, 4097, 513, 32), (32, 130, 7, 8), (200, 2500, 260, 20),
+                                   (104, 777, 129, 5)])
+@pytest.mark.parametrize("spread", [1.0, 300.0])
+def test_coarse_tensor_core_vs_brute_force(shape, spread):
+    """tcgen05 coarse GEMM on ragged shapes (d not a multiple of 64, nc not a multiple of 128, nq tails,
+    large dynamic range): same neighbours as a float64 brute force."""
+    pkg = load_pkg()
+    d, nc, nq, nprobe = shape
+    rng = np.random.default_rng(d * 7 + nc)
+    C = (rng.standard_normal((nc, d)) * spread).astype(np.float32)
+    Q = (C[rng.integers(0, nc, nq)] + 0.3 * spread * rng.standard_normal((nq, d))).astype(np.float32)
+    Q[0] = 0
+    idx = pkg.IndexIVF_HNSW(d, nc, 8, 8)
+    idx.build_quantizer(centroids=C)
+    res = {}
+    for impl in (0, 1):
+        idx.set_option("coarse_impl", impl)
+        res[impl] = idx.coarse(Q, nprobe)
+    dd = ((Q.astype(np.float64)[:, None, :(d // 16) * 16] - C.astype(np.float64)[None, :, :(d // 16) * 16]) ** 2).sum(-1)
+    want = np.sort(dd, axis=1)[:, :nprobe]
+    for impl in (0, 1):
+        cd, ci = res[impl]
+        assert np.allclose(cd, want, rtol=2e-5, atol=1e-5 * spread * spread), impl
+        got = np.take_along_axis(dd, ci.astype(np.int64), 1)
+        assert np.allclose(got, want, rtol=2e-5, atol=1e-5 * spread * spread), impl
+    assert np.mean(res[0][1] == res[1][1]) >= 0.999
     idx.close()
 
 
