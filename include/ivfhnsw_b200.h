@@ -153,7 +153,11 @@ int ivfhnsw_b200_merge_partials_dev(ivfhnsw_b200_t *h, size_t nq, size_t k, size
                                     const float *part_d_dev, const uint32_t *part_seq_dev,
                                     const int64_t *part_labels_dev, float *distances_dev, int64_t *labels_dev);
 int ivfhnsw_b200_sync(ivfhnsw_b200_t *h);
-/* run on a caller-owned CUDA stream (cudaStream_t, e.g. torch's current stream); NULL = back to a private one */
+/* run on a caller-owned CUDA stream (cudaStream_t, e.g. torch's current stream); NULL = back to a private one.
+ * STREAM ORDERING: every *_dev entry point only ENQUEUES work on the handle's stream.  Device buffers
+ * produced or consumed on another stream must be ordered by the caller (an event, or ivfhnsw_b200_sync()
+ * after the call and a synchronize of the producing stream before it).  The host-pointer entry points
+ * (search, assign, add_batch, ...) synchronise internally and need nothing. */
 int ivfhnsw_b200_set_stream(ivfhnsw_b200_t *h, void *stream);
 
 /* -- introspection for tests, bench and profiles ----------------------------*/

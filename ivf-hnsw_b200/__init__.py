@@ -182,6 +182,7 @@ class IndexIVF_HNSW:
         self.pq_centroids = None      # index->pq->centroids
         self.norm_centroids = None    # index->norm_pq->centroids
         self.opq_matrix = None        # index->opq_matrix->A
+        self.device, self._ext_stream = int(device), None
         self._L = lib()
         self._h = C.c_void_p()
         rc = self._L.ivfhnsw_b200_create(C.byref(self._h), self.d, self.nc, self.code_size, nbits_per_idx,
@@ -299,11 +300,37 @@ class IndexIVF_HNSW:
         self._ck(self._L.ivfhnsw_b200_add_batch(self._h, x.shape[0], x.ctypes.data, xids.ctypes.data,
                                                 None if idx is None else idx.ctypes.data))
 
+    # -- stream ordering for the device-pointer entry points.  The C ABI enqueues on the handle's stream
+    # (private unless set_stream() was called).  Tensors usually come from torch's current stream: unless
+    # that IS the handle's stream, wait for it before the call and drain the handle's stream after it,
+    # so that the *_dev methods are safe by default and fully asynchronous once the stream is shared.
+    def _ordered(self):
+        idx = self
+
+        class _Ctx:
+            def __enter__(self_c):
+                self_c.shared = False
+                try:
+                    import torch
+                    cur = torch.cuda.current_stream(idx.device).cuda_stream
+                    self_c.shared = idx._ext_stream is not None and idx._ext_stream == cur
+                    if not self_c.shared:
+                        torch.cuda.current_stream(idx.device).synchronize()
+                except ImportError:
+                    pass
+
+            def __exit__(self_c, et, ev, tb):
+                if et is None and not self_c.shared:
+                    idx.sync()
+                return False
+        return _Ctx()
+
     def add_points_dev(self, x_dev, ids_dev, idx_dev=None):
         """Bulk ingest of device-resident vectors (torch tensors); idx_dev=None assigns on the GPU."""
         self._push_params()
-        self._ck(self._L.ivfhnsw_b200_add_points_dev(self._h, x_dev.shape[0], _ptr(x_dev), _ptr(ids_dev),
-                                                     _ptr(idx_dev)))
+        with self._ordered():
+            self._ck(self._L.ivfhnsw_b200_add_points_dev(self._h, x_dev.shape[0], _ptr(x_dev), _ptr(ids_dev),
+                                                         _ptr(idx_dev)))
 
     def finalize(self):
         self._push_params()
@@ -463,14 +490,18 @@ class IndexIVF_HNSW:
         self._push_params()
         nq = x_dev.shape[0]
         if coarse is None:
-            self._ck(self._L.ivfhnsw_b200_search_dev(self._h, nq, k, _ptr(x_dev), _ptr(D_dev), _ptr(L_dev)))
+            with self._ordered():
+                self._ck(self._L.ivfhnsw_b200_search_dev(self._h, nq, k, _ptr(x_dev), _ptr(D_dev), _ptr(L_dev)))
         else:
-            self._ck(self._L.ivfhnsw_b200_search_given_coarse_dev(self._h, nq, k, _ptr(x_dev), _ptr(coarse[0]),
-                                                                  _ptr(coarse[1]), _ptr(D_dev), _ptr(L_dev)))
+            with self._ordered():
+                self._ck(self._L.ivfhnsw_b200_search_given_coarse_dev(self._h, nq, k, _ptr(x_dev), _ptr(coarse[0]),
+                                                                      _ptr(coarse[1]), _ptr(D_dev), _ptr(L_dev)))
 
     def coarse_dev(self, x_dev, nprobe, d_dev, i_dev):
         self._push_params()
-        self._ck(self._L.ivfhnsw_b200_coarse_dev(self._h, x_dev.shape[0], _ptr(x_dev), nprobe, _ptr(d_dev), _ptr(i_dev)))
+        with self._ordered():
+            self._ck(self._L.ivfhnsw_b200_coarse_dev(self._h, x_dev.shape[0], _ptr(x_dev), nprobe, _ptr(d_dev),
+                                                     _ptr(i_dev)))
 
     def search_host_buffers(self, k, x_host, D_host, L_host):
         """The C-ABI call with caller-owned HOST buffers (numpy or pinned torch): H2D + search + D2H."""
@@ -481,16 +512,20 @@ class IndexIVF_HNSW:
         """This shard's sorted partial top-k (dist, scan-order key, label) for all queries."""
         self._push_params()
         cd, ci = (None, None) if coarse is None else coarse
-        self._ck(self._L.ivfhnsw_b200_search_partial_dev(self._h, x_dev.shape[0], k, _ptr(x_dev), _ptr(cd), _ptr(ci),
-                                                         _ptr(part_d), _ptr(part_seq), _ptr(part_labels)))
+        with self._ordered():
+            self._ck(self._L.ivfhnsw_b200_search_partial_dev(self._h, x_dev.shape[0], k, _ptr(x_dev), _ptr(cd),
+                                                             _ptr(ci), _ptr(part_d), _ptr(part_seq),
+                                                             _ptr(part_labels)))
 
     def merge_partials_dev(self, k, nq, nparts, part_d, part_seq, part_labels, D_dev, L_dev):
-        self._ck(self._L.ivfhnsw_b200_merge_partials_dev(self._h, nq, k, nparts, _ptr(part_d), _ptr(part_seq),
-                                                         _ptr(part_labels), _ptr(D_dev), _ptr(L_dev)))
+        with self._ordered():
+            self._ck(self._L.ivfhnsw_b200_merge_partials_dev(self._h, nq, k, nparts, _ptr(part_d), _ptr(part_seq),
+                                                             _ptr(part_labels), _ptr(D_dev), _ptr(L_dev)))
 
     def set_stream(self, cuda_stream_ptr):
         """Run on a caller-owned stream, e.g. torch.cuda.current_stream().cuda_stream (0/None = private)."""
         self._ck(self._L.ivfhnsw_b200_set_stream(self._h, cuda_stream_ptr or None))
+        self._ext_stream = cuda_stream_ptr or None
 
     def sync(self):
         self._ck(self._L.ivfhnsw_b200_sync(self._h))

@@ -7,6 +7,7 @@
 #include <algorithm>
 #include <cstdarg>
 #include <cstdio>
+#include <cstdlib>
 #include <cstring>
 #include <mutex>
 #include <string>
@@ -105,6 +106,7 @@ int ivfhnsw_b200_create(ivfhnsw_b200_t **out, size_t d, size_t nc, size_t code_s
     ivfhnsw_b200_t *h = new ivfhnsw_b200();
     *out = h;  // returned even on failure so that last_error() is readable; caller destroys it
     h->device = device;
+    if (const char *e = getenv("IVFHNSW_B200_COARSE_IMPL")) h->coarse_impl = atol(e);   // A/B switch for profiling
     h->d = d; h->nc = nc; h->M = code_size; h->nsubc = nsubc;
     h->c_begin = 0; h->c_end = (uint32_t)nc;
     if (nbits != 8) return h->fail(IVFHNSW_B200_EINVAL, "nbits_per_idx must be 8 (got %zu)", nbits);
@@ -150,7 +152,7 @@ void ivfhnsw_b200_destroy(ivfhnsw_b200_t *h)
                       &h->opqA, &h->list_size, &h->list_slot, &h->raw_off, &h->codes, &h->norm_codes, &h->sub_ids,
                       &h->ids, &h->nn_idx, &h->sub_sizes, &h->alphas, &h->icd, &h->st_list, &h->st_ids, &h->st_codes,
                       &h->st_norm, &h->st_sub, &h->st_x, &h->w_x, &h->w_xrot, &h->w_cd, &h->w_ci, &h->w_seg,
-                      &h->w_sub_base, &h->w_qsd, &h->w_part, &h->w_coarse, &h->w_xf16, &h->w_out_d, &h->w_out_l,
+                      &h->w_sub_base, &h->w_qsd, &h->w_part, &h->w_lut, &h->w_coarse, &h->w_xf16, &h->w_out_d, &h->w_out_l,
                       &h->w_a, &h->w_b, &h->w_c, &h->w_d2, &h->w_e, &h->w_f, &h->w_cub, &h->w_small, &h->counters};
     for (DevBuf *b : bufs) b->release();
     for (int i = 0; i < 4; i++)
@@ -864,7 +866,7 @@ static int search_core(ivfhnsw_b200_t *h, size_t nq, size_t k, const float *x_de
     const size_t seg_q = align256((size_t)(5 * nprobe + 1) * 4 + 16);
     const size_t sub_q = grouping ? (size_t)nprobe * nsubc * 4 : 0;
     size_t qb = h->query_batch > 0 ? (size_t)h->query_batch : 16384;
-    const size_t per_q = seg_q + 2 * sub_q + 32 * k * 12 + (size_t)d * 4 + (size_t)nprobe * 8;
+    const size_t per_q = seg_q + 2 * sub_q + 32 * k * 12 + (size_t)d * 4 + (size_t)nprobe * 8 + (size_t)1024 * M;
     qb = std::min(qb, std::max<size_t>(64, ((size_t)1 << 31) / per_q));
     qb = std::min(qb, nq);
     int nsplit = (int)h->scan_split;
@@ -880,6 +882,7 @@ static int search_core(ivfhnsw_b200_t *h, size_t nq, size_t k, const float *x_de
         CU(h->w_qsd.ensure(qb * sub_q + 256));
     }
     if (nsplit > 1) CU(h->w_part.ensure(qb * nsplit * k * 12 + 256));
+    CU(h->w_lut.ensure(qb * 256 * M * 4 + 256));
     if (!cd_dev) {
         CU(h->w_cd.ensure(qb * nprobe * 4));
         CU(h->w_ci.ensure(qb * nprobe * 4));
@@ -943,9 +946,12 @@ static int search_core(ivfhnsw_b200_t *h, size_t nq, size_t k, const float *x_de
             ps = reinterpret_cast<uint32_t *>(pd + (size_t)qb * nsplit * k);
             pl = ps + (size_t)qb * nsplit * k;
         }
-        CU(launch_scan(st, LAUNCHES, M, grouping, nb, d, nprobe, nsubc, (int)k, nsplit, xq, h->pqc.as<float>(),
+        CU(launch_lut(st, LAUNCHES, M, nb, d, xq, h->pqc.as<float>(), h->w_lut.as<float>()));
+        if (h->debug >= 2) CU(cudaStreamSynchronize(st));   // localise asynchronous kernel faults
+        CU(launch_scan(st, LAUNCHES, M, grouping, nb, d, nprobe, nsubc, (int)k, nsplit, h->w_lut.as<float>(),
                        h->norm_table.as<float>(), L, T, pd, ps, pl, out_d + q0 * k, out_l + q0 * k,
                        out_seq ? out_seq + q0 * k : nullptr));
+        if (h->debug >= 2) CU(cudaStreamSynchronize(st));
         if (h->timing) CU(cudaEventRecord(h->ev[3], st));
         if (nsplit > 1)
             CU(launch_merge(st, LAUNCHES, nb, (int)k, nsplit, pd, ps, pl, L.ids, out_d + q0 * k, out_l + q0 * k,

@@ -52,11 +52,13 @@ cudaError_t launch_prep_grouping(cudaStream_t st, uint64_t *launches, int nq, in
 
 size_t scan_smem_bytes(int M, int nprobe, int k, int nsubc);
 // partial outputs [nq][nsplit][k]; when nsplit == 1 the kernel writes the final (distances, labels) directly
+// compact per-query tables lutc[q][j][m] = -2 <q_m, c_{m,j}> consumed by launch_scan
+cudaError_t launch_lut(cudaStream_t st, uint64_t *launches, int M, int nq, int d, const float *queries,
+                       const float *pqc, float *lutc);
 cudaError_t launch_scan(cudaStream_t st, uint64_t *launches, int M, bool grouping, int nq, int d, int nprobe,
-                        int nsubc, int k, int nsplit, const float *queries, const float *pqc,
-                        const float *norm_table, const DeviceLists &L, const SegTables &T, float *part_d,
-                        uint32_t *part_seq, uint32_t *part_slot, float *out_d, int64_t *out_labels,
-                        uint32_t *out_seq /* optional */);
+                        int nsubc, int k, int nsplit, const float *lutc, const float *norm_table,
+                        const DeviceLists &L, const SegTables &T, float *part_d, uint32_t *part_seq,
+                        uint32_t *part_slot, float *out_d, int64_t *out_labels, uint32_t *out_seq);
 cudaError_t launch_merge(cudaStream_t st, uint64_t *launches, int nq, int k, int nsplit, const float *part_d,
                          const uint32_t *part_seq, const uint32_t *part_slot, const uint32_t *ids,
                          float *out_d, int64_t *out_labels, uint32_t *out_seq /* optional */);

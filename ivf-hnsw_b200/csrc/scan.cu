@@ -390,12 +390,79 @@ cudaError_t launch_prep_grouping(cudaStream_t st, uint64_t *launches, int nq, in
 }
 
 // =============================================================================================
-// K-L1 + K-S1/K-S2: the scan
+// K-L1: per-query lookup tables, compact form lutc[q][j][m] = -2 <q_m, c_{m,j}>
+// (ProductQuantizer::compute_inner_prod_table, faiss/ProductQuantizer.cpp:424-436, scaled by -2 so
+//  that the scan adds instead of computing 2*pq_L2sqr, IndexIVF_HNSW.cpp:283; x2 is exact in fp32).
+// Thread j owns codeword row j of every sub-quantizer: its reads of the codebook are contiguous across
+// the CTA and the M values of a row leave as 128-bit stores.  The codebook (d KB) stays L1 resident
+// while a CTA works through its queries.
+// =============================================================================================
+#define LUT_QPB 8
+template <int M>
+__global__ void __launch_bounds__(256) lut_kernel(int nq, int d, const float *__restrict__ queries,
+                                                  const float *__restrict__ pqc, float *__restrict__ lutc)
+{
+    extern __shared__ __align__(16) float sq[];   // [LUT_QPB][d]
+    const int q0 = blockIdx.x * LUT_QPB, j = threadIdx.x;
+    const int nqb = min(LUT_QPB, nq - q0);
+    for (int i = threadIdx.x; i < nqb * d; i += 256) sq[i] = queries[(size_t)q0 * d + i];
+    __syncthreads();
+    const int dsub = d / M;
+    for (int qq = 0; qq < nqb; qq++) {
+        float v[M];
+#pragma unroll
+        for (int m = 0; m < M; m++) {
+            const float *c = pqc + ((size_t)m * 256 + j) * dsub;
+            const float *qs = sq + qq * d + m * dsub;
+            float s = 0.f;
+            if ((dsub & 3) == 0) {
+                for (int t = 0; t < dsub; t += 4) {
+                    const float4 cv = __ldg(reinterpret_cast<const float4 *>(c + t));
+                    s = fmaf(qs[t], cv.x, s);
+                    s = fmaf(qs[t + 1], cv.y, s);
+                    s = fmaf(qs[t + 2], cv.z, s);
+                    s = fmaf(qs[t + 3], cv.w, s);
+                }
+            } else if ((dsub & 1) == 0) {
+                for (int t = 0; t < dsub; t += 2) {
+                    const float2 cv = __ldg(reinterpret_cast<const float2 *>(c + t));
+                    s = fmaf(qs[t], cv.x, s);
+                    s = fmaf(qs[t + 1], cv.y, s);
+                }
+            } else {
+                for (int t = 0; t < dsub; t++) s = fmaf(qs[t], __ldg(c + t), s);
+            }
+            v[m] = -2.f * s;
+        }
+        float4 *o = reinterpret_cast<float4 *>(lutc + ((size_t)(q0 + qq) * 256 + j) * M);
+#pragma unroll
+        for (int m4 = 0; m4 < M / 4; m4++) o[m4] = make_float4(v[m4 * 4], v[m4 * 4 + 1], v[m4 * 4 + 2], v[m4 * 4 + 3]);
+    }
+}
+
+cudaError_t launch_lut(cudaStream_t st, uint64_t *launches, int M, int nq, int d, const float *queries,
+                       const float *pqc, float *lutc)
+{
+    if (nq == 0) return cudaSuccess;
+    const unsigned grid = (unsigned)((nq + LUT_QPB - 1) / LUT_QPB);
+    const size_t sm = (size_t)LUT_QPB * d * 4;
+    switch (M) {
+    case 8: lut_kernel<8><<<grid, 256, sm, st>>>(nq, d, queries, pqc, lutc); break;
+    case 16: lut_kernel<16><<<grid, 256, sm, st>>>(nq, d, queries, pqc, lutc); break;
+    case 32: lut_kernel<32><<<grid, 256, sm, st>>>(nq, d, queries, pqc, lutc); break;
+    case 64: lut_kernel<64><<<grid, 256, sm, st>>>(nq, d, queries, pqc, lutc); break;
+    default: return cudaErrorInvalidValue;
+    }
+    ++*launches;
+    return cudaGetLastError();
+}
+
+// =============================================================================================
+// K-S1/K-S2: the scan
 // =============================================================================================
 struct ScanArgs {
     int d, nprobe, nsubc, k, nsplit;
-    const float *queries;     // [nq][d] (already OPQ-rotated)
-    const float *pqc;         // [M][256][dsub]
+    const float *lutc;        // [nq][256][M] compact tables from K-L1
     const float *norm_table;  // [256]
     DeviceLists L;
     SegTables T;
@@ -415,12 +482,19 @@ template <int M> struct ScanCfg {
     static constexpr int LUT_BYTES = 65536 + (M == 64 ? 32768 : 0);
 };
 
+// entries per lane of the register-resident per-warp result list: k <= 32 -> 1, k <= 128 -> 4,
+// larger k -> 0 = shared-memory list under a CTA lock
+static __host__ __device__ inline int scan_kpl(int k) { return k <= 32 ? 1 : (k <= 128 ? 4 : 0); }
+
 static __host__ __device__ inline size_t scan_small_smem(int nprobe, int k, int nsubc)
 {
     size_t b = 0;
     b += (size_t)(5 * nprobe + 1) * 4;          // segment tables
-    b += (size_t)k * 12;                        // top-k
-    b += (size_t)SCAN_WARPS * SCAN_WCAP * 12;   // warp candidate buffers
+    if (scan_kpl(k)) b += (size_t)SCAN_WARPS * k * 12;     // the warps' sorted lists, for the final merge
+    else {
+        b += (size_t)k * 12;                        // top-k
+        b += (size_t)SCAN_WARPS * SCAN_WCAP * 12;   // warp candidate buffers
+    }
     b += (size_t)SCAN_WARPS * nsubc * 4;        // warp sub-group bases
     b += 64;                                    // control words
     return (b + 15) & ~(size_t)15;
@@ -437,8 +511,9 @@ struct ScanCtl {
     int lock;
     int worst_pos;
     uint32_t worst_seq;
-    float worst_d;   // == the insertion threshold
-    int pad[3];
+    float worst_d;      // == the insertion threshold (lock path)
+    uint32_t thr_key;   // min over the warps of fkey(k-th best): a bound on the CTA's final k-th best
+    int pad[2];
 };
 
 static __device__ __forceinline__ uint32_t fkey_u32(float f)
@@ -447,10 +522,62 @@ static __device__ __forceinline__ uint32_t fkey_u32(float f)
     return (b & 0x80000000u) ? ~b : (b | 0x80000000u);   // order-preserving float -> uint
 }
 
-// Merge one warp's candidate buffer (<= SCAN_WCAP = 64 entries) into the CTA top-k.  Warp-collective.
-// Candidates are pre-filtered lane-parallel against the current worst entry (two per lane); only the
-// survivors are inserted one by one under the CTA lock, and the survivor mask is re-evaluated after
-// every insertion because the worst entry only improves.
+// ---------------------------------------------------------------------------------------------
+// Per-warp result list in registers: entry e = r * 32 + lane, ascending (distance, scan order).
+// An insertion is one ballot per register row plus a shift by one lane -- no shared memory, no lock.
+// ---------------------------------------------------------------------------------------------
+template <int KPL> struct WarpList {
+    float d[KPL > 0 ? KPL : 1];
+    uint32_t s[KPL > 0 ? KPL : 1], slot[KPL > 0 ? KPL : 1];
+    float thr_d;      // key of entry k-1: a candidate must come strictly before it
+    uint32_t thr_s;
+
+    __device__ __forceinline__ void init(int lane, int k)
+    {
+#pragma unroll
+        for (int r = 0; r < KPL; r++) {
+            d[r] = FLT_MAX;
+            s[r] = 0xffffff00u + (uint32_t)(r * 32 + lane);   // empty entries: ascending keys above any scan order
+            slot[r] = IVF_INVALID_SLOT;
+        }
+        thr_d = FLT_MAX;
+        thr_s = 0xffffff00u + (uint32_t)(k - 1);
+    }
+    // warp-uniform arguments
+    __device__ __forceinline__ void insert(float xd, uint32_t xs, uint32_t xslot, int lane, int k)
+    {
+        int pos = 0;
+#pragma unroll
+        for (int r = 0; r < KPL; r++) pos += __popc(__ballot_sync(IVF_FULL_MASK, key_less(d[r], s[r], xd, xs)));
+#pragma unroll
+        for (int r = KPL - 1; r >= 0; r--) {
+            const int e = r * 32 + lane;
+            float ud = __shfl_up_sync(IVF_FULL_MASK, d[r], 1);
+            uint32_t us = __shfl_up_sync(IVF_FULL_MASK, s[r], 1);
+            uint32_t ul = __shfl_up_sync(IVF_FULL_MASK, slot[r], 1);
+            if (r > 0) {
+                const float cd = __shfl_sync(IVF_FULL_MASK, d[r - 1], 31);
+                const uint32_t cs = __shfl_sync(IVF_FULL_MASK, s[r - 1], 31);
+                const uint32_t cl = __shfl_sync(IVF_FULL_MASK, slot[r - 1], 31);
+                if (lane == 0) { ud = cd; us = cs; ul = cl; }
+            }
+            if (e == pos) { d[r] = xd; s[r] = xs; slot[r] = xslot; }
+            else if (e > pos) { d[r] = ud; s[r] = us; slot[r] = ul; }
+        }
+        const int kr = (k - 1) >> 5, kl = (k - 1) & 31;
+        float td = d[0];
+        uint32_t ts = s[0];
+#pragma unroll
+        for (int r = 1; r < KPL; r++)
+            if (kr == r) { td = d[r]; ts = s[r]; }
+        thr_d = __shfl_sync(IVF_FULL_MASK, td, kl);
+        thr_s = __shfl_sync(IVF_FULL_MASK, ts, kl);
+    }
+};
+
+// Lock path (k > 128): merge one warp's candidate buffer (<= SCAN_WCAP = 64 entries) into the CTA
+// top-k.  Warp-collective.  Candidates are pre-filtered lane-parallel against the current worst entry
+// (two per lane); only the survivors are inserted one by one under the CTA lock.
 static __device__ __forceinline__ void flush_candidates(volatile ScanCtl *ctl, float *topk_d, uint32_t *topk_seq,
                                                         uint32_t *topk_slot, int k, const float *wd,
                                                         const uint32_t *wseq, const uint32_t *wslot, int count,
@@ -466,7 +593,7 @@ static __device__ __forceinline__ void flush_candidates(volatile ScanCtl *ctl, f
     bool a0 = h0 && key_less(d0, s0, w_d, w_s), a1 = h1 && key_less(d1, s1, w_d, w_s);
     if (!__any_sync(IVF_FULL_MASK, a0 || a1)) return;
     if (lane == 0) {
-        while (atomicCAS((int *)&ctl->lock, 0, 1) != 0) { }
+        while (atomicCAS((int *)&ctl->lock, 0, 1) != 0) __nanosleep(100);
         __threadfence_block();
     }
     __syncwarp();
@@ -516,7 +643,7 @@ static __device__ __forceinline__ void flush_candidates(volatile ScanCtl *ctl, f
     __syncwarp();
 }
 
-template <int M, bool GROUPING>
+template <int M, bool GROUPING, int KPL>
 __global__ void __launch_bounds__(SCAN_THREADS) scan_kernel(ScanArgs a)
 {
     using C = ScanCfg<M>;
@@ -528,12 +655,18 @@ __global__ void __launch_bounds__(SCAN_THREADS) scan_kernel(ScanArgs a)
     float *s_base = reinterpret_cast<float *>(p); p += a.nprobe * 4;
     uint32_t *s_seq = reinterpret_cast<uint32_t *>(p); p += a.nprobe * 4;
     uint32_t *s_poff = reinterpret_cast<uint32_t *>(p); p += (a.nprobe + 1) * 4;
-    float *topk_d = reinterpret_cast<float *>(p); p += a.k * 4;
-    uint32_t *topk_seq = reinterpret_cast<uint32_t *>(p); p += a.k * 4;
-    uint32_t *topk_slot = reinterpret_cast<uint32_t *>(p); p += a.k * 4;
-    float *wbuf_d = reinterpret_cast<float *>(p); p += SCAN_WARPS * SCAN_WCAP * 4;
-    uint32_t *wbuf_seq = reinterpret_cast<uint32_t *>(p); p += SCAN_WARPS * SCAN_WCAP * 4;
-    uint32_t *wbuf_slot = reinterpret_cast<uint32_t *>(p); p += SCAN_WARPS * SCAN_WCAP * 4;
+    // KPL > 0: [SCAN_WARPS][k] sorted warp lists; KPL == 0: CTA top-k followed by the warp buffers
+    const int nres = KPL > 0 ? SCAN_WARPS * a.k : a.k;
+    float *topk_d = reinterpret_cast<float *>(p); p += nres * 4;
+    uint32_t *topk_seq = reinterpret_cast<uint32_t *>(p); p += nres * 4;
+    uint32_t *topk_slot = reinterpret_cast<uint32_t *>(p); p += nres * 4;
+    float *wbuf_d = nullptr;
+    uint32_t *wbuf_seq = nullptr, *wbuf_slot = nullptr;
+    if (KPL == 0) {
+        wbuf_d = reinterpret_cast<float *>(p); p += SCAN_WARPS * SCAN_WCAP * 4;
+        wbuf_seq = reinterpret_cast<uint32_t *>(p); p += SCAN_WARPS * SCAN_WCAP * 4;
+        wbuf_slot = reinterpret_cast<uint32_t *>(p); p += SCAN_WARPS * SCAN_WCAP * 4;
+    }
     float *wsub_all = reinterpret_cast<float *>(p); p += SCAN_WARPS * a.nsubc * 4;
     p = reinterpret_cast<uint8_t *>((reinterpret_cast<uintptr_t>(p) + 15) & ~(uintptr_t)15);
     volatile ScanCtl *ctl = reinterpret_cast<volatile ScanCtl *>(p);
@@ -541,7 +674,6 @@ __global__ void __launch_bounds__(SCAN_THREADS) scan_kernel(ScanArgs a)
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     const int q = blockIdx.x / a.nsplit, split = blockIdx.x - q * a.nsplit;
     const int nprobe = a.nprobe, k = a.k;
-    const int dsub = a.d / M;
 
     // ---- stage the query's segment tables and initialise the top-k
     {
@@ -553,10 +685,12 @@ __global__ void __launch_bounds__(SCAN_THREADS) scan_kernel(ScanArgs a)
             s_seq[i] = a.T.seq[o + i];
         }
         for (int i = tid; i <= nprobe; i += SCAN_THREADS) s_poff[i] = a.T.piece_off[(size_t)q * (nprobe + 1) + i];
-        for (int e = tid; e < k; e += SCAN_THREADS) {
-            topk_d[e] = FLT_MAX;
-            topk_seq[e] = 0xffffffffu - (uint32_t)e;
-            topk_slot[e] = IVF_INVALID_SLOT;
+        if (KPL == 0) {
+            for (int e = tid; e < k; e += SCAN_THREADS) {
+                topk_d[e] = FLT_MAX;
+                topk_seq[e] = 0xffffffffu - (uint32_t)e;
+                topk_slot[e] = IVF_INVALID_SLOT;
+            }
         }
         if (tid == 0) {
             ctl->piece_ctr = 0;
@@ -564,62 +698,44 @@ __global__ void __launch_bounds__(SCAN_THREADS) scan_kernel(ScanArgs a)
             ctl->worst_pos = 0;
             ctl->worst_seq = 0xffffffffu;
             ctl->worst_d = FLT_MAX;
+            ctl->thr_key = 0xffffffffu;
         }
     }
     __syncthreads();
     const int npieces = (int)s_poff[nprobe];
     const bool has_work = split < npieces;   // CTA-uniform
 
-    // ---- K-L1: per-query table straight into shared memory
-    // (ProductQuantizer::compute_inner_prod_table, faiss/ProductQuantizer.cpp:424-436, scaled by -2 so
-    //  that the scan adds instead of computing 2*pq_L2sqr, IndexIVF_HNSW.cpp:283; x2 is exact in fp32)
+    // ---- expand the compact table of K-L1 into the bank-conflict-free layout
     if (has_work) {
-        const float *qv = a.queries + (size_t)q * a.d;
+        const float *lg = a.lutc + (size_t)q * 256 * M;
         float *lutf = reinterpret_cast<float *>(lut);
-        constexpr int NPASS = (M == 64) ? 2 : 1;
+        if (M >= 32) {
+            // R = 1: row j keeps its M words in order (M == 32: first half of the 64-word row)
+#pragma unroll 8
+            for (int it = 0; it < M / 4; it++) {
+                const int e4 = it * 256 + tid;                 // float4 index in [256 * M / 4)
+                const float4 v = __ldg(reinterpret_cast<const float4 *>(lg) + e4);
+                const int j = (e4 * 4) / M, m = (e4 * 4) % M;
+                *reinterpret_cast<float4 *>(lutf + j * 64 + m) = v;
+            }
+        } else {
+            // 32 consecutive elements = R rows of M values; every value is stored R times side by side
 #pragma unroll
-        for (int pass = 0; pass < NPASS; pass++) {
-            const int m = (M == 64) ? (lane + 32 * pass) : (lane / C::R);
-            const float *qs = qv + m * dsub;
-            const float *cb = a.pqc + (size_t)m * 256 * dsub;
-            if ((dsub & 3) == 0 && dsub <= 16) {
-                float4 qr[4];
-#pragma unroll
-                for (int t = 0; t < 4; t++)
-                    qr[t] = (t * 4 < dsub) ? *reinterpret_cast<const float4 *>(qs + t * 4) : make_float4(0, 0, 0, 0);
-#pragma unroll 4
-                for (int jj = 0; jj < 32; jj++) {
-                    const int j = warp * 32 + jj;
-                    const float4 *c4 = reinterpret_cast<const float4 *>(cb + (size_t)j * dsub);
-                    float s = 0.f;
-#pragma unroll
-                    for (int t = 0; t < 4; t++)
-                        if (t * 4 < dsub) {
-                            const float4 v = __ldg(c4 + t);
-                            s = fmaf(qr[t].x, v.x, s);
-                            s = fmaf(qr[t].y, v.y, s);
-                            s = fmaf(qr[t].z, v.z, s);
-                            s = fmaf(qr[t].w, v.w, s);
-                        }
-                    lutf[j * 64 + lane + 32 * pass] = -2.f * s;
-                }
-            } else {
-#pragma unroll 2
-                for (int jj = 0; jj < 32; jj++) {
-                    const int j = warp * 32 + jj;
-                    const float *c = cb + (size_t)j * dsub;
-                    float s = 0.f;
-                    for (int t = 0; t < dsub; t++) s = fmaf(qs[t], __ldg(c + t), s);
-                    lutf[j * 64 + lane + 32 * pass] = -2.f * s;
-                }
+            for (int it = 0; it < M; it++) {
+                const int e = it * 256 + tid;
+                const float v = __ldg(lg + e);
+                const int j = e / M, m = e % M;
+                if (C::R == 2) *reinterpret_cast<float2 *>(lutf + j * 64 + 2 * m) = make_float2(v, v);
+                else *reinterpret_cast<float4 *>(lutf + j * 64 + 4 * m) = make_float4(v, v, v, v);
             }
         }
         // decoded norms (norm_pq->decode, IndexIVF_HNSW.cpp:280): one replica per bank
-        for (int jj = 0; jj < 32; jj++) {
-            const int j = warp * 32 + jj;
+#pragma unroll
+        for (int it = 0; it < 8; it++) {
+            const int j = warp * 32 + it * 4 + (lane >> 3);
             const float v = __ldg(a.norm_table + j);
-            if (M == 64) lutf[16384 + j * 32 + lane] = v;
-            else lutf[j * 64 + 32 + lane] = v;
+            float *dst = (M == 64) ? (lutf + 16384 + j * 32) : (lutf + j * 64 + 32);
+            *reinterpret_cast<float4 *>(dst + (lane & 7) * 4) = make_float4(v, v, v, v);
         }
     }
     __syncthreads();
@@ -639,9 +755,11 @@ __global__ void __launch_bounds__(SCAN_THREADS) scan_kernel(ScanArgs a)
     }
     const uint32_t Onorm = 128u + 4u * lane;  // M < 64: byte0 = offset of word 32 + lane, bytes 1..3 = 0
 
-    float *wd = wbuf_d + warp * SCAN_WCAP;
-    uint32_t *wseq = wbuf_seq + warp * SCAN_WCAP;
-    uint32_t *wslot = wbuf_slot + warp * SCAN_WCAP;
+    WarpList<KPL> wl;
+    if (KPL > 0) wl.init(lane, k);
+    float *wd = KPL == 0 ? wbuf_d + warp * SCAN_WCAP : nullptr;
+    uint32_t *wseq = KPL == 0 ? wbuf_seq + warp * SCAN_WCAP : nullptr;
+    uint32_t *wslot = KPL == 0 ? wbuf_slot + warp * SCAN_WCAP : nullptr;
     float *wsub = wsub_all + warp * a.nsubc;
     int wcount = 0;
 
@@ -711,29 +829,97 @@ __global__ void __launch_bounds__(SCAN_THREADS) scan_kernel(ScanArgs a)
                 }
                 const float dist = acc0 + acc1;
                 const bool valid = (c * SCAN_CHUNK + lane) < rem;
-                const float thr = ctl->worst_d;
-                bool pass = valid && dist <= thr;
-                uint32_t bal = __ballot_sync(IVF_FULL_MASK, pass);
-                if (bal) {
-                    int n = __popc(bal);
-                    if (wcount + n > SCAN_WCAP) {
-                        flush_candidates(ctl, topk_d, topk_seq, topk_slot, k, wd, wseq, wslot, wcount, lane);
-                        wcount = 0;
-                        pass = valid && dist <= ctl->worst_d;
-                        bal = __ballot_sync(IVF_FULL_MASK, pass);
-                        n = __popc(bal);
+                if (KPL > 0) {
+                    const uint32_t sh = ctl->thr_key;   // bound shared by the warps of the CTA (ties pass)
+                    const uint32_t myseq = seq0 + c * SCAN_CHUNK + lane;
+                    const bool pass = valid && fkey_u32(dist) <= sh && key_less(dist, myseq, wl.thr_d, wl.thr_s);
+                    uint32_t bal = __ballot_sync(IVF_FULL_MASK, pass);
+                    if (bal) {
+                        do {
+                            const int src = __ffs(bal) - 1;
+                            bal &= bal - 1;
+                            const float xd = __shfl_sync(IVF_FULL_MASK, dist, src);
+                            const uint32_t xs = seq0 + c * SCAN_CHUNK + src;
+                            if (key_less(xd, xs, wl.thr_d, wl.thr_s))   // warp-uniform
+                                wl.insert(xd, xs, slot0 + c * SCAN_CHUNK + src, lane, k);
+                        } while (bal);
+                        if (lane == 0 && wl.thr_d < FLT_MAX) atomicMin((uint32_t *)&ctl->thr_key, fkey_u32(wl.thr_d));
                     }
-                    if (pass) {
-                        const int pos = wcount + __popc(bal & ((1u << lane) - 1u));
-                        wd[pos] = dist;
-                        wseq[pos] = seq0 + c * SCAN_CHUNK + lane;
-                        wslot[pos] = slot0 + c * SCAN_CHUNK + lane;
+                } else {
+                    const float thr = ctl->worst_d;
+                    bool pass = valid && dist <= thr;
+                    uint32_t bal = __ballot_sync(IVF_FULL_MASK, pass);
+                    if (bal) {
+                        int n = __popc(bal);
+                        if (wcount + n > SCAN_WCAP) {
+                            flush_candidates(ctl, topk_d, topk_seq, topk_slot, k, wd, wseq, wslot, wcount, lane);
+                            wcount = 0;
+                            pass = valid && dist <= ctl->worst_d;
+                            bal = __ballot_sync(IVF_FULL_MASK, pass);
+                            n = __popc(bal);
+                        }
+                        if (pass) {
+                            const int pos = wcount + __popc(bal & ((1u << lane) - 1u));
+                            wd[pos] = dist;
+                            wseq[pos] = seq0 + c * SCAN_CHUNK + lane;
+                            wslot[pos] = slot0 + c * SCAN_CHUNK + lane;
+                        }
+                        wcount += n;
                     }
-                    wcount += n;
                 }
             }
         }
     }
+
+    if (KPL > 0) {
+        // ---- publish the warp lists, then rank every entry among the other warps' (sorted) lists
+#pragma unroll
+        for (int r = 0; r < KPL; r++) {
+            const int e = r * 32 + lane;
+            if (e < k) {
+                topk_d[warp * k + e] = wl.d[r];
+                topk_seq[warp * k + e] = wl.s[r];
+                topk_slot[warp * k + e] = wl.slot[r];
+            }
+        }
+        __syncthreads();
+        for (int e = tid; e < SCAN_WARPS * k; e += SCAN_THREADS) {
+            const int mine = e / k, pos = e - mine * k;
+            const float ed = topk_d[e];
+            const uint32_t es = topk_seq[e];
+            int rank = pos;
+            for (int s = 0; s < SCAN_WARPS && rank < k; s++) {
+                if (s == mine) continue;
+                const float *ld = topk_d + s * k;
+                const uint32_t *ls = topk_seq + s * k;
+                int lo = 0, hi = k;
+                while (lo < hi) {
+                    const int mid = (lo + hi) >> 1;
+                    const float md = ld[mid];
+                    const uint32_t ms = ls[mid];
+                    // empty entries of different warps share keys: break those ties by warp
+                    const bool before = key_less(md, ms, ed, es) || (md == ed && ms == es && s < mine);
+                    if (before) lo = mid + 1; else hi = mid;
+                }
+                rank += lo;
+            }
+            if (rank < k) {
+                const uint32_t slot = topk_slot[e];
+                if (a.nsplit == 1) {
+                    a.out_d[(size_t)q * k + rank] = ed;
+                    a.out_labels[(size_t)q * k + rank] = slot == IVF_INVALID_SLOT ? (int64_t)-1 : (int64_t)a.L.ids[slot];
+                    if (a.out_seq) a.out_seq[(size_t)q * k + rank] = es;
+                } else {
+                    const size_t o = ((size_t)q * a.nsplit + split) * k + rank;
+                    a.part_d[o] = ed;
+                    a.part_seq[o] = es;
+                    a.part_slot[o] = slot;
+                }
+            }
+        }
+        return;
+    }
+
     flush_candidates(ctl, topk_d, topk_seq, topk_slot, k, wd, wseq, wslot, wcount, lane);
     __syncthreads();
 
@@ -757,31 +943,41 @@ __global__ void __launch_bounds__(SCAN_THREADS) scan_kernel(ScanArgs a)
     }
 }
 
-template <int M, bool G>
+template <int M, bool G, int KPL>
 static cudaError_t launch_scan_t(cudaStream_t st, int nq, const ScanArgs &a)
 {
     const size_t smem = scan_smem_bytes(M, a.nprobe, a.k, a.nsubc);
-    cudaError_t e = cudaFuncSetAttribute(scan_kernel<M, G>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+    cudaError_t e =
+        cudaFuncSetAttribute(scan_kernel<M, G, KPL>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
     if (e != cudaSuccess) return e;
-    scan_kernel<M, G><<<(unsigned)((size_t)nq * a.nsplit), SCAN_THREADS, smem, st>>>(a);
+    scan_kernel<M, G, KPL><<<(unsigned)((size_t)nq * a.nsplit), SCAN_THREADS, smem, st>>>(a);
     return cudaGetLastError();
 }
 
+template <int M, bool G>
+static cudaError_t launch_scan_k(cudaStream_t st, int nq, const ScanArgs &a)
+{
+    switch (scan_kpl(a.k)) {
+    case 1: return launch_scan_t<M, G, 1>(st, nq, a);
+    case 4: return launch_scan_t<M, G, 4>(st, nq, a);
+    default: return launch_scan_t<M, G, 0>(st, nq, a);
+    }
+}
+
 cudaError_t launch_scan(cudaStream_t st, uint64_t *launches, int M, bool grouping, int nq, int d, int nprobe,
-                        int nsubc, int k, int nsplit, const float *queries, const float *pqc,
-                        const float *norm_table, const DeviceLists &L, const SegTables &T, float *part_d,
-                        uint32_t *part_seq, uint32_t *part_slot, float *out_d, int64_t *out_labels,
-                        uint32_t *out_seq)
+                        int nsubc, int k, int nsplit, const float *lutc, const float *norm_table,
+                        const DeviceLists &L, const SegTables &T, float *part_d, uint32_t *part_seq,
+                        uint32_t *part_slot, float *out_d, int64_t *out_labels, uint32_t *out_seq)
 {
     if (nq == 0) return cudaSuccess;
     ScanArgs a;
     a.out_seq = out_seq;
     a.d = d; a.nprobe = nprobe; a.nsubc = grouping ? nsubc : 0; a.k = k; a.nsplit = nsplit;
-    a.queries = queries; a.pqc = pqc; a.norm_table = norm_table; a.L = L; a.T = T;
+    a.lutc = lutc; a.norm_table = norm_table; a.L = L; a.T = T;
     a.part_d = part_d; a.part_seq = part_seq; a.part_slot = part_slot; a.out_d = out_d; a.out_labels = out_labels;
     ++*launches;
 #define IVF_SCAN_CASE(MM)                                                              \
-    case MM: return grouping ? launch_scan_t<MM, true>(st, nq, a) : launch_scan_t<MM, false>(st, nq, a);
+    case MM: return grouping ? launch_scan_k<MM, true>(st, nq, a) : launch_scan_k<MM, false>(st, nq, a);
     switch (M) {
         IVF_SCAN_CASE(8)
         IVF_SCAN_CASE(16)
