@@ -104,122 +104,46 @@ cudaError_t launch_prep_adc(cudaStream_t st, uint64_t *launches, int nq, int npr
 }
 
 // =============================================================================================
-// K-G1a: distances from each query to the neighbour centroids n_s of every probed list
-// (the lazily memoised ivfhnsw::fvec_L2sqr calls of IndexIVF_HNSW_Grouping.cpp:246-250,312-316).
-// One CTA per query.  Like the reference's nc-sized memo (query_centroid_dists, :57) every distinct
-// centroid is evaluated ONCE per query: the neighbour ids of all probed lists are de-duplicated in a
-// shared-memory hash table (the 64-NN lists of the probed centroids overlap heavily), which cuts the
-// gathered centroid rows -- the dominant traffic of this stage -- several-fold.  Memo semantics kept:
-// a neighbour that is itself a probed centroid reuses the coarse distance (:207-220) unless that value
-// is < EPS, in which case the reference recomputes it.
-// Output: T.qsd[q][i][s] = d(q, n_s)   (0 where the list or the sub-group is empty)
+// Grouping work list (IndexIVF_HNSW_Grouping.cpp:222-262 and :283-353), three kernels:
+//
+//  K-G1  one CTA per query.  Distances from the query to the neighbour centroids n_s of every probed
+//        list (the lazily memoised ivfhnsw::fvec_L2sqr calls of :246-250 and :312-316).  Like the
+//        reference's nc-sized memo (query_centroid_dists, :57) every distinct centroid is evaluated ONCE
+//        per query: the neighbour ids of all probed lists are de-duplicated in a shared-memory hash table
+//        (the 64-NN lists of the probed centroids overlap heavily).  Memo semantics kept: a neighbour that
+//        is itself a probed centroid reuses the coarse distance (:207-220) unless that value is < EPS.
+//        One THREAD per distance, 256-bit row loads, the 8 partial sums of fvec_L2sqr in registers: the
+//        gather is bound by L2 bandwidth, so what matters is the number of sectors in flight.
+//        Out: T.qsd[q][i][s]      = the pruning value query_subcentroid_dists (:251-252), NaN where it
+//                                   does not contribute to the threshold
+//             T.sub_base[q][i][s] = term1 + term2 of the sub-group (+inf for empty ones)
+//             T.nscanned[q]       = number of contributing values (scratch for K-G2)
+//  K-G2  pruning threshold = SEQUENTIAL fp32 sum of the contributing values in (probe, sub-group) order
+//        divided by their count.  The chain is inherently serial per query, so a CTA
+//        runs 32 queries side by side: tiles are transposed through shared memory and lane <-> query.
+//  K-G3  one CTA per query: applies the threshold (rows past the 2*max_codes horizon compare 0, :228),
+//        counts the kept codes per list, applies the max_codes rule on the KEPT codes (:337,349) and
+//        writes the segment tables.
 // =============================================================================================
-__global__ void __launch_bounds__(256) group_dqn_kernel(int d, int nprobe, int nsubc, int ht_size,
-                                                        const float *__restrict__ queries,
-                                                        const float *__restrict__ coarse_d,
-                                                        const uint32_t *__restrict__ coarse_i, DeviceLists L,
-                                                        SegTables T)
-{
-    extern __shared__ __align__(16) uint8_t sm[];
-    float *sq = reinterpret_cast<float *>(sm);                         // [d]
-    uint32_t *hk = reinterpret_cast<uint32_t *>(sq + d);               // [ht_size] keys
-    float *hv = reinterpret_cast<float *>(hk + ht_size);               // [ht_size] values (NaN = to compute)
-    uint16_t *work = reinterpret_cast<uint16_t *>(hv + ht_size);       // [ht_size] slots to compute
-    __shared__ int s_nwork;
-    const int q = blockIdx.x, tid = threadIdx.x;
-    const float qnan = __int_as_float(0x7fc00000);
-    for (int i = tid; i < d; i += blockDim.x) sq[i] = queries[(size_t)q * d + i];
-    for (int i = tid; i < ht_size; i += blockDim.x) hk[i] = 0xffffffffu;
-    if (tid == 0) s_nwork = 0;
-    __syncthreads();
-    const uint32_t hmask = ht_size - 1;
-    // memo of the coarse stage
-    for (int i = tid; i < nprobe; i += blockDim.x) {
-        const uint32_t c = coarse_i[(size_t)q * nprobe + i];
-        const float v = coarse_d[(size_t)q * nprobe + i];
-        uint32_t p = (c * 2654435761u) & hmask;
-        while (true) {
-            const uint32_t prev = atomicCAS(&hk[p], 0xffffffffu, c);
-            if (prev == 0xffffffffu || prev == c) { hv[p] = v >= 0.00001f ? v : qnan; break; }
-            p = (p + 1) & hmask;
-        }
-    }
-    __syncthreads();
-    const int npairs = nprobe * nsubc;
-    // insert every needed neighbour id once
-    for (int e = tid; e < npairs; e += blockDim.x) {
-        const int i = e / nsubc, s = e - i * nsubc;
-        const uint32_t c = coarse_i[(size_t)q * nprobe + i];
-        if (L.list_size[c] == 0 || L.sub_sizes[(size_t)c * nsubc + s] == 0) continue;
-        const uint32_t n = L.nn_idx[(size_t)c * nsubc + s];
-        uint32_t p = (n * 2654435761u) & hmask;
-        while (true) {
-            const uint32_t prev = atomicCAS(&hk[p], 0xffffffffu, n);
-            if (prev == 0xffffffffu) { hv[p] = qnan; break; }
-            if (prev == n) break;
-            p = (p + 1) & hmask;
-        }
-    }
-    __syncthreads();
-    for (int p = tid; p < ht_size; p += blockDim.x) {
-        const float v = hv[p];
-        if (hk[p] != 0xffffffffu && v != v) work[atomicAdd(&s_nwork, 1)] = (uint16_t)p;
-    }
-    __syncthreads();
-    const int nwork = s_nwork;
-    const int lane = tid & 31, warp = tid >> 5, oct = lane >> 3, sub = lane & 7;
-    for (int w0 = warp * 4; w0 < nwork; w0 += (blockDim.x >> 5) * 4) {
-        const int w = w0 + oct;
-        const int p = w < nwork ? work[w] : 0;
-        const uint32_t n = w < nwork ? hk[p] : 0u;
-        const float dist = l2sqr16_octet(sq, L.centroids + (size_t)n * d, d, sub);
-        if (w < nwork && sub == 0) hv[p] = dist;
-    }
-    __syncthreads();
-    for (int e = tid; e < npairs; e += blockDim.x) {
-        const int i = e / nsubc, s = e - i * nsubc;
-        const uint32_t c = coarse_i[(size_t)q * nprobe + i];
-        float out = 0.f;
-        if (L.list_size[c] != 0 && L.sub_sizes[(size_t)c * nsubc + s] != 0) {
-            const uint32_t n = L.nn_idx[(size_t)c * nsubc + s];
-            uint32_t p = (n * 2654435761u) & hmask;
-            while (hk[p] != n) p = (p + 1) & hmask;
-            out = hv[p];
-        }
-        T.qsd[(size_t)q * npairs + e] = out;
-    }
-}
+#define G1_THREADS 256
 
-// =============================================================================================
-// K-G1b: pruning threshold, kept sub-groups, max_codes rule and segment tables for Grouping.
-// One warp (one block) per query.  Follows IndexIVF_HNSW_Grouping.cpp:222-262 and :283-353
-// including SURVEY.md 8(a) Q1: qsd rows exist only for non-empty lists, rows beyond the
-// 2*max_codes horizon stay 0, empty sub-groups are never looked at, and the threshold is the
-// SEQUENTIAL fp32 sum in (probe, sub-group) order divided by the count.
-// In : T.qsd[q][i][s] = d(q, n_s).   Out: T.sub_base[q][i][s] = term1 + term2 or +inf.
-// =============================================================================================
-__global__ void __launch_bounds__(32) prep_grouping_kernel(int nprobe, int nsubc, uint64_t max_codes,
-                                                           int do_pruning, const float *__restrict__ coarse_d,
-                                                           const uint32_t *__restrict__ coarse_i, DeviceLists L,
-                                                           uint32_t c_begin, uint32_t c_end, SegTables T)
-{
-    extern __shared__ __align__(16) uint8_t sm[];
-    uint32_t *s_c = reinterpret_cast<uint32_t *>(sm);     // [nprobe] centroid id
-    uint32_t *s_sz = s_c + nprobe;                        // [nprobe] list size
-    uint32_t *s_kept = s_sz + nprobe;                     // [nprobe] kept codes
-    uint8_t *s_inh = reinterpret_cast<uint8_t *>(s_kept + nprobe);  // [nprobe] inside pass-1 horizon
-    const int q = blockIdx.x, lane = threadIdx.x;
-    const size_t qo = (size_t)q * nprobe;
-    const int npairs = nprobe * nsubc;
-    float *qsd = T.qsd + (size_t)q * npairs;      // d(q, n_s)
-    float *sb = T.sub_base + (size_t)q * npairs;  // scratch for qsd values, then final bases
+struct ProbeMeta {
+    uint32_t *c;      // centroid id
+    uint32_t *sz;     // list size
+    uint8_t *inh;     // inside the pass-1 horizon
+};
 
-    // ---- pass-1 horizon (:229-259): list i is visited iff non-empty and sum of earlier sizes < 2*max_codes
+// pass-1 horizon (:229-259): list i is visited iff non-empty and the sizes before it sum to < 2*max_codes.
+// Executed by warp 0; results in shared memory.
+static __device__ __forceinline__ void probe_meta_warp0(int nprobe, uint64_t max_codes, const uint32_t *coarse_i_q,
+                                                        const DeviceLists &L, uint32_t *s_c, uint32_t *s_sz,
+                                                        uint8_t *s_inh, int lane)
+{
     uint64_t run = 0;
     for (int base = 0; base < nprobe; base += 32) {
         const int i = base + lane;
         uint32_t c = 0, sz = 0;
-        if (i < nprobe) { c = coarse_i[qo + i]; sz = L.list_size[c]; }
+        if (i < nprobe) { c = coarse_i_q[i]; sz = L.list_size[c]; }
         uint64_t incl = sz;
 #pragma unroll
         for (int off = 1; off < 32; off <<= 1) {
@@ -234,80 +158,286 @@ __global__ void __launch_bounds__(32) prep_grouping_kernel(int nprobe, int nsubc
         }
         run += __shfl_sync(IVF_FULL_MASK, incl, 31);
     }
-    __syncwarp();
+}
 
-    // ---- qsd values (:251-252), NaN marks "does not contribute"
-    uint32_t count = 0;
-    if (do_pruning) {
-        for (int e = lane; e < npairs; e += 32) {
-            const int i = e / nsubc, s = e - i * nsubc;
-            const uint32_t c = s_c[i];
-            float v = __int_as_float(0x7fc00000);
-            if (s_inh[i] && L.sub_sizes[(size_t)c * nsubc + s] != 0) {
-                const float alpha = L.alphas[c];
-                const float oma = __fsub_rn(1.f, alpha);
-                const float term1 = __fmul_rn(oma, coarse_d[qo + i]);
-                const float inner = __fsub_rn(__fmul_rn(oma, L.icd[(size_t)c * nsubc + s]), qsd[e]);
-                v = __fsub_rn(term1, __fmul_rn(alpha, inner));
-                count++;
+static __device__ __forceinline__ void ldg_256(const float *p, float (&v)[8])
+{
+    asm volatile("ld.global.nc.v8.f32 {%0, %1, %2, %3, %4, %5, %6, %7}, [%8];"
+                 : "=f"(v[0]), "=f"(v[1]), "=f"(v[2]), "=f"(v[3]), "=f"(v[4]), "=f"(v[5]), "=f"(v[6]), "=f"(v[7])
+                 : "l"(p));
+}
+
+// ivfhnsw::fvec_L2sqr (utils.cpp:22-51) by ONE thread: 8 partial sums over floor(d/16)*16 dims, unfused
+// multiply-add like the pinned C restatement, partials added left to right.  x in shared memory.
+static __device__ __forceinline__ float l2sqr16_thread(const float *__restrict__ x, const float *__restrict__ y, int d)
+{
+    const int n = (d >> 4) << 4;
+    float acc[8];
+#pragma unroll
+    for (int j = 0; j < 8; j++) acc[j] = 0.f;
+    if ((d & 7) == 0) {
+#pragma unroll 4
+        for (int i = 0; i < n; i += 8) {
+            float yv[8];
+            ldg_256(y + i, yv);
+            const float4 x0 = *reinterpret_cast<const float4 *>(x + i), x1 = *reinterpret_cast<const float4 *>(x + i + 4);
+            const float xv[8] = {x0.x, x0.y, x0.z, x0.w, x1.x, x1.y, x1.z, x1.w};
+#pragma unroll
+            for (int j = 0; j < 8; j++) {
+                const float df = xv[j] - yv[j];
+                acc[j] = __fadd_rn(acc[j], __fmul_rn(df, df));
             }
-            sb[e] = v;
+        }
+    } else {
+        for (int i = 0; i < n; i += 8) {
+#pragma unroll
+            for (int j = 0; j < 8; j++) {
+                const float df = x[i + j] - __ldg(y + i + j);
+                acc[j] = __fadd_rn(acc[j], __fmul_rn(df, df));
+            }
+        }
+    }
+    float r = acc[0];
+#pragma unroll
+    for (int j = 1; j < 8; j++) r += acc[j];
+    return r;
+}
+
+__global__ void __launch_bounds__(G1_THREADS) group_g1_kernel(int d, int nprobe, int nsubc, int ht_size,
+                                                              uint64_t max_codes, int do_pruning,
+                                                              const float *__restrict__ queries,
+                                                              const float *__restrict__ coarse_d,
+                                                              const uint32_t *__restrict__ coarse_i, DeviceLists L,
+                                                              SegTables T)
+{
+    extern __shared__ __align__(16) uint8_t sm[];
+    float *sq = reinterpret_cast<float *>(sm);                         // [d] (d % 4 == 0)
+    uint32_t *hk = reinterpret_cast<uint32_t *>(sq + d);               // [ht_size] keys
+    float *hv = reinterpret_cast<float *>(hk + ht_size);               // [ht_size] values (NaN = to compute)
+    uint32_t *s_c = reinterpret_cast<uint32_t *>(hv + ht_size);        // [nprobe]
+    uint32_t *s_sz = s_c + nprobe;
+    float *s_alpha = reinterpret_cast<float *>(s_sz + nprobe);
+    float *s_cd = s_alpha + nprobe;
+    float *s_cn = s_cd + nprobe;
+    uint16_t *work = reinterpret_cast<uint16_t *>(s_cn + nprobe);      // [npairs + nprobe] slots to compute
+    uint8_t *s_inh = reinterpret_cast<uint8_t *>(work + (size_t)nprobe * nsubc + nprobe);
+    __shared__ int s_nwork;
+    __shared__ uint32_t s_count;
+    const int q = blockIdx.x, tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    const size_t qo = (size_t)q * nprobe;
+    const float qnan = __int_as_float(0x7fc00000);
+    for (int i = tid; i < d; i += G1_THREADS) sq[i] = queries[(size_t)q * d + i];
+    for (int i = tid; i < ht_size; i += G1_THREADS) hk[i] = 0xffffffffu;
+    if (tid == 0) { s_nwork = 0; s_count = 0; }
+    if (warp == 0) probe_meta_warp0(nprobe, max_codes, coarse_i + qo, L, s_c, s_sz, s_inh, lane);
+    __syncthreads();
+    const uint32_t hmask = ht_size - 1;
+    // per-list constants and the memo of the coarse stage
+    for (int i = tid; i < nprobe; i += G1_THREADS) {
+        const uint32_t c = s_c[i];
+        const float v = coarse_d[qo + i];
+        s_alpha[i] = L.alphas[c];
+        s_cd[i] = v;
+        s_cn[i] = L.centroid_norms[c];
+        uint32_t p = (c * 2654435761u) & hmask;
+        while (true) {
+            const uint32_t prev = atomicCAS(&hk[p], 0xffffffffu, c);
+            if (prev == 0xffffffffu || prev == c) { hv[p] = v >= 0.00001f ? v : qnan; break; }
+            p = (p + 1) & hmask;
+        }
+    }
+    __syncthreads();
+    const int npairs = nprobe * nsubc;
+    // ---- every needed neighbour id enters the table once (loads of 8 pairs in flight per thread)
+    for (int e0 = 0; e0 < npairs; e0 += G1_THREADS * 8) {
+        uint32_t nn[8];
+#pragma unroll
+        for (int u = 0; u < 8; u++) {
+            const int e = e0 + u * G1_THREADS + tid;
+            nn[u] = 0xffffffffu;
+            if (e < npairs) {
+                const int i = e / nsubc, s = e - i * nsubc;
+                if (s_sz[i] != 0) {
+                    const size_t o = (size_t)s_c[i] * nsubc + s;
+                    const uint32_t ss = __ldg(L.sub_sizes + o);
+                    const uint32_t n = __ldg(L.nn_idx + o);
+                    if (ss != 0) nn[u] = n;
+                }
+            }
         }
 #pragma unroll
-        for (int off = 16; off > 0; off >>= 1) count += __shfl_xor_sync(IVF_FULL_MASK, count, off);
+        for (int u = 0; u < 8; u++) {
+            const uint32_t n = nn[u];
+            if (n == 0xffffffffu) continue;
+            uint32_t p = (n * 2654435761u) & hmask;
+            while (true) {
+                const uint32_t prev = atomicCAS(&hk[p], 0xffffffffu, n);
+                if (prev == 0xffffffffu) { hv[p] = qnan; break; }
+                if (prev == n) break;
+                p = (p + 1) & hmask;
+            }
+        }
     }
-    __syncwarp();
-    float threshold = 0.f;
-    if (do_pruning) {
-        // sequential sum in reference order: coalesced loads, then every lane replays the 32 values
-        // in order through shuffles (all lanes hold the same accumulator)
-        float acc = 0.f;
-        for (int e0 = 0; e0 < npairs; e0 += 32) {
-            const float mine = (e0 + lane < npairs) ? sb[e0 + lane] : __int_as_float(0x7fc00000);
+    __syncthreads();
+    for (int p = tid; p < ht_size; p += G1_THREADS) {
+        const float v = hv[p];
+        if (hk[p] != 0xffffffffu && v != v) work[atomicAdd(&s_nwork, 1)] = (uint16_t)p;
+    }
+    __syncthreads();
+    const int nwork = s_nwork;
+    for (int w = tid; w < nwork; w += G1_THREADS) {
+        const int p = work[w];
+        hv[p] = l2sqr16_thread(sq, L.centroids + (size_t)hk[p] * d, d);
+    }
+    __syncthreads();
+    // ---- per sub-group: pruning value and base
+    uint32_t count = 0;
+    for (int e0 = 0; e0 < npairs; e0 += G1_THREADS * 4) {
+        uint32_t nn[4];
+        float icd[4];
 #pragma unroll
-            for (int j = 0; j < 32; j++) {
-                const float v = __shfl_sync(IVF_FULL_MASK, mine, j);
+        for (int u = 0; u < 4; u++) {
+            const int e = e0 + u * G1_THREADS + tid;
+            nn[u] = 0xffffffffu;
+            icd[u] = 0.f;
+            if (e < npairs) {
+                const int i = e / nsubc, s = e - i * nsubc;
+                if (s_sz[i] != 0) {
+                    const size_t o = (size_t)s_c[i] * nsubc + s;
+                    const uint32_t ss = __ldg(L.sub_sizes + o);
+                    const uint32_t n = __ldg(L.nn_idx + o);
+                    icd[u] = __ldg(L.icd + o);
+                    if (ss != 0) nn[u] = n;
+                }
+            }
+        }
+        float cnn[4];
+#pragma unroll
+        for (int u = 0; u < 4; u++) cnn[u] = nn[u] != 0xffffffffu ? __ldg(L.centroid_norms + nn[u]) : 0.f;
+#pragma unroll
+        for (int u = 0; u < 4; u++) {
+            const int e = e0 + u * G1_THREADS + tid;
+            if (e >= npairs) continue;
+            float r = qnan, sb = __int_as_float(0x7f800000);
+            if (nn[u] != 0xffffffffu) {
+                const int i = e / nsubc;
+                uint32_t p = (nn[u] * 2654435761u) & hmask;
+                while (hk[p] != nn[u]) p = (p + 1) & hmask;
+                const float qsd = hv[p];
+                const float alpha = s_alpha[i];
+                const float oma = __fsub_rn(1.f, alpha);
+                // :251-252  (1-a)*d(q,c) - a*((1-a)*d(c,n) - d(q,n))
+                if (do_pruning && s_inh[i]) {
+                    const float t1 = __fmul_rn(oma, s_cd[i]);
+                    const float inner = __fsub_rn(__fmul_rn(oma, icd[u]), qsd);
+                    r = __fsub_rn(t1, __fmul_rn(alpha, inner));
+                    count++;
+                }
+                // :318-322  term1 + term2
+                const float term1 = __fmul_rn(oma, __fsub_rn(s_cd[i], s_cn[i]));
+                const float term2 = __fmul_rn(alpha, __fsub_rn(qsd, cnn[u]));
+                sb = __fadd_rn(term1, term2);
+            }
+            T.qsd[(size_t)q * npairs + e] = r;
+            T.sub_base[(size_t)q * npairs + e] = sb;
+        }
+    }
+#pragma unroll
+    for (int off = 16; off > 0; off >>= 1) count += __shfl_xor_sync(IVF_FULL_MASK, count, off);
+    if (lane == 0 && count) atomicAdd(&s_count, count);
+    __syncthreads();
+    if (tid == 0) T.nscanned[q] = s_count;
+}
+
+// K-G2: lane <-> query, 32 queries per CTA, tiles of G2_TE values per query transposed through smem
+#define G2_TE 64
+__global__ void __launch_bounds__(128) group_g2_kernel(int nq, int npairs, const float *__restrict__ vals,
+                                                       const uint32_t *__restrict__ counts, float *__restrict__ thr)
+{
+    __shared__ float tile[2][32][G2_TE + 1];
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    const int q0 = blockIdx.x * 32;
+    const int ntiles = (npairs + G2_TE - 1) / G2_TE;
+    const float qnan = __int_as_float(0x7fc00000);
+    // thread t loads element (row = (t*? ) ...): 32 rows x 64 columns = 2048 values, 16 per thread,
+    // row r = idx / 64, col = idx % 64 with idx = u * 128 + tid  -> a warp reads 32 consecutive columns
+    float reg[16];
+    auto load_tile = [&](int t) {
+#pragma unroll
+        for (int u = 0; u < 16; u++) {
+            const int idx = u * 128 + tid, r = idx >> 6, c = idx & 63;
+            const int e = t * G2_TE + c, q = q0 + r;
+            reg[u] = (q < nq && e < npairs) ? __ldg(vals + (size_t)q * npairs + e) : qnan;
+        }
+    };
+    float acc = 0.f;
+    load_tile(0);
+    for (int t = 0; t < ntiles; t++) {
+        const int b = t & 1;
+#pragma unroll
+        for (int u = 0; u < 16; u++) {
+            const int idx = u * 128 + tid;
+            tile[b][idx >> 6][idx & 63] = reg[u];
+        }
+        __syncthreads();
+        if (t + 1 < ntiles) load_tile(t + 1);
+        if (warp == 0) {
+#pragma unroll 16
+            for (int c = 0; c < G2_TE; c++) {
+                const float v = tile[b][lane][c];
                 if (v == v) acc = __fadd_rn(acc, v);
             }
         }
-        threshold = acc / (float)count;  // count == 0 -> NaN like the reference's 0/0
     }
-    __syncwarp();
+    if (warp == 0 && q0 + lane < nq) thr[q0 + lane] = acc / (float)counts[q0 + lane];   // 0/0 -> NaN like the reference
+}
 
-    // ---- pass 2 bookkeeping (:283-353): kept sub-groups and their bases
-    for (int i = 0; i < nprobe; i++) {
-        const uint32_t c = s_c[i];
-        uint32_t kept = 0;
-        if (s_sz[i] != 0) {
-            const float alpha = L.alphas[c];
-            const float oma = __fsub_rn(1.f, alpha);
-            const float term1 = __fmul_rn(oma, __fsub_rn(coarse_d[qo + i], L.centroid_norms[c]));
-            for (int s = lane; s < nsubc; s += 32) {
-                const int e = i * nsubc + s;
-                const uint32_t ss = L.sub_sizes[(size_t)c * nsubc + s];
-                float out = __int_as_float(0x7f800000);
-                if (ss != 0) {
-                    bool keep = true;
-                    if (do_pruning) {
-                        const float qv = s_inh[i] ? sb[e] : 0.f;  // rows past the horizon stay 0 (:228)
-                        keep = qv < threshold;
-                    }
-                    if (keep) {
-                        const uint32_t n = L.nn_idx[(size_t)c * nsubc + s];
-                        const float term2 = __fmul_rn(alpha, __fsub_rn(qsd[e], L.centroid_norms[n]));
-                        out = __fadd_rn(term1, term2);
-                        kept += ss;
-                    }
+__global__ void __launch_bounds__(G1_THREADS) group_g3_kernel(int nprobe, int nsubc, uint64_t max_codes,
+                                                              int do_pruning,
+                                                              const uint32_t *__restrict__ coarse_i, DeviceLists L,
+                                                              uint32_t c_begin, uint32_t c_end, SegTables T)
+{
+    extern __shared__ __align__(16) uint8_t sm[];
+    uint32_t *s_c = reinterpret_cast<uint32_t *>(sm);     // [nprobe] centroid id
+    uint32_t *s_sz = s_c + nprobe;                        // [nprobe] list size
+    uint32_t *s_kept = s_sz + nprobe;                     // [nprobe] kept codes
+    uint8_t *s_inh = reinterpret_cast<uint8_t *>(s_kept + nprobe);
+    const int q = blockIdx.x, tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    const size_t qo = (size_t)q * nprobe;
+    const int npairs = nprobe * nsubc;
+    if (warp == 0) probe_meta_warp0(nprobe, max_codes, coarse_i + qo, L, s_c, s_sz, s_inh, lane);
+    for (int i = tid; i < nprobe; i += G1_THREADS) s_kept[i] = 0;
+    __syncthreads();
+    const float threshold = do_pruning ? T.threshold[q] : 0.f;
+    const float *rv = T.qsd + (size_t)q * npairs;
+    float *sb = T.sub_base + (size_t)q * npairs;
+    for (int e0 = 0; e0 < npairs; e0 += G1_THREADS * 4) {
+        uint32_t ss[4];
+        float r[4];
+#pragma unroll
+        for (int u = 0; u < 4; u++) {
+            const int e = e0 + u * G1_THREADS + tid;
+            ss[u] = 0;
+            r[u] = 0.f;
+            if (e < npairs) {
+                const int i = e / nsubc, s = e - i * nsubc;
+                if (s_sz[i] != 0) {
+                    ss[u] = __ldg(L.sub_sizes + (size_t)s_c[i] * nsubc + s);
+                    if (do_pruning && s_inh[i]) r[u] = rv[e];    // rows past the horizon stay 0 (:228)
                 }
-                sb[e] = out;
             }
         }
 #pragma unroll
-        for (int off = 16; off > 0; off >>= 1) kept += __shfl_xor_sync(IVF_FULL_MASK, kept, off);
-        if (lane == 0) s_kept[i] = kept;
+        for (int u = 0; u < 4; u++) {
+            const int e = e0 + u * G1_THREADS + tid;
+            if (e >= npairs || ss[u] == 0) continue;
+            const bool keep = !do_pruning || r[u] < threshold;
+            if (keep) atomicAdd(&s_kept[e / nsubc], ss[u]);
+            else sb[e] = __int_as_float(0x7f800000);
+        }
     }
-    __syncwarp();
-
+    __syncthreads();
+    if (warp != 0) return;
     // ---- max_codes rule on the KEPT codes (:337,349) and segment tables
     uint64_t run_k = 0, run_w = 0;
     uint32_t run_pieces = 0, scanned = 0, walked = 0;
@@ -362,7 +492,7 @@ __global__ void __launch_bounds__(32) prep_grouping_kernel(int nprobe, int nsubc
         T.piece_off[(size_t)q * (nprobe + 1) + nprobe] = run_pieces;
         T.nscanned[q] = scanned;
         T.nwalked[q] = walked;
-        T.threshold[q] = threshold;
+        if (!do_pruning) T.threshold[q] = 0.f;
     }
 }
 
@@ -372,19 +502,28 @@ cudaError_t launch_prep_grouping(cudaStream_t st, uint64_t *launches, int nq, in
                                  uint32_t c_begin, uint32_t c_end, const SegTables &T)
 {
     if (nq == 0) return cudaSuccess;
+    const int npairs = nprobe * nsubc;
     int ht = 64;
-    while (ht < nprobe * nsubc + nprobe + 1) ht <<= 1;   // can never fill up
+    while (ht < npairs + nprobe + 1) ht <<= 1;           // can never fill up
     if (ht > 65536) return cudaErrorInvalidValue;       // uint16 work list
-    const size_t sm1 = (size_t)d * 4 + (size_t)ht * 10;
-    cudaError_t e = cudaFuncSetAttribute(group_dqn_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sm1);
+    const size_t sm1 = (size_t)d * 4 + (size_t)ht * 8 + (size_t)nprobe * 20 + (size_t)(npairs + nprobe) * 2 +
+                       (size_t)nprobe + 16;
+    cudaError_t e = cudaFuncSetAttribute(group_g1_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sm1);
     if (e != cudaSuccess) return e;
-    group_dqn_kernel<<<nq, 256, sm1, st>>>(d, nprobe, nsubc, ht, queries, coarse_d, coarse_i, L, T);
+    group_g1_kernel<<<nq, G1_THREADS, sm1, st>>>(d, nprobe, nsubc, ht, max_codes, do_pruning ? 1 : 0, queries,
+                                                coarse_d, coarse_i, L, T);
     ++*launches;
     e = cudaGetLastError();
     if (e != cudaSuccess) return e;
-    const size_t sm2 = (size_t)nprobe * 13 + 16;
-    prep_grouping_kernel<<<nq, 32, sm2, st>>>(nprobe, nsubc, max_codes, do_pruning ? 1 : 0, coarse_d, coarse_i, L,
-                                              c_begin, c_end, T);
+    if (do_pruning) {
+        group_g2_kernel<<<(nq + 31) / 32, 128, 0, st>>>(nq, npairs, T.qsd, T.nscanned, T.threshold);
+        ++*launches;
+        e = cudaGetLastError();
+        if (e != cudaSuccess) return e;
+    }
+    const size_t sm3 = (size_t)nprobe * 13 + 16;
+    group_g3_kernel<<<nq, G1_THREADS, sm3, st>>>(nprobe, nsubc, max_codes, do_pruning ? 1 : 0, coarse_i, L, c_begin,
+                                                c_end, T);
     ++*launches;
     return cudaGetLastError();
 }
