@@ -125,7 +125,7 @@ cudaError_t launch_prep_adc(cudaStream_t st, uint64_t *launches, int nq, int npr
 //        counts the kept codes per list, applies the max_codes rule on the KEPT codes (:337,349) and
 //        writes the segment tables.
 // =============================================================================================
-#define G1_THREADS 256
+#define G1_THREADS 512
 
 struct ProbeMeta {
     uint32_t *c;      // centroid id
@@ -203,7 +203,13 @@ static __device__ __forceinline__ float l2sqr16_thread(const float *__restrict__
     return r;
 }
 
-__global__ void __launch_bounds__(G1_THREADS) group_g1_kernel(int d, int nprobe, int nsubc, int ht_size,
+// e -> (probe, sub-group) without an integer division when nsubc is a power of two (the usual 64)
+static __device__ __forceinline__ int pair_probe(int e, int nsubc, int sub_shift)
+{
+    return sub_shift >= 0 ? (e >> sub_shift) : (e / nsubc);
+}
+
+__global__ void __launch_bounds__(G1_THREADS) group_g1_kernel(int d, int nprobe, int nsubc, int sub_shift, int ht_size,
                                                               uint64_t max_codes, int do_pruning,
                                                               const float *__restrict__ queries,
                                                               const float *__restrict__ coarse_d,
@@ -242,7 +248,11 @@ __global__ void __launch_bounds__(G1_THREADS) group_g1_kernel(int d, int nprobe,
         uint32_t p = (c * 2654435761u) & hmask;
         while (true) {
             const uint32_t prev = atomicCAS(&hk[p], 0xffffffffu, c);
-            if (prev == 0xffffffffu || prev == c) { hv[p] = v >= 0.00001f ? v : qnan; break; }
+            if (prev == 0xffffffffu || prev == c) {
+                hv[p] = v;
+                if (!(v >= 0.00001f) && prev == 0xffffffffu) work[atomicAdd(&s_nwork, 1)] = (uint16_t)p;
+                break;
+            }
             p = (p + 1) & hmask;
         }
     }
@@ -256,7 +266,7 @@ __global__ void __launch_bounds__(G1_THREADS) group_g1_kernel(int d, int nprobe,
             const int e = e0 + u * G1_THREADS + tid;
             nn[u] = 0xffffffffu;
             if (e < npairs) {
-                const int i = e / nsubc, s = e - i * nsubc;
+                const int i = pair_probe(e, nsubc, sub_shift), s = e - i * nsubc;
                 if (s_sz[i] != 0) {
                     const size_t o = (size_t)s_c[i] * nsubc + s;
                     const uint32_t ss = __ldg(L.sub_sizes + o);
@@ -272,16 +282,11 @@ __global__ void __launch_bounds__(G1_THREADS) group_g1_kernel(int d, int nprobe,
             uint32_t p = (n * 2654435761u) & hmask;
             while (true) {
                 const uint32_t prev = atomicCAS(&hk[p], 0xffffffffu, n);
-                if (prev == 0xffffffffu) { hv[p] = qnan; break; }
+                if (prev == 0xffffffffu) { work[atomicAdd(&s_nwork, 1)] = (uint16_t)p; break; }   // first sight: to compute
                 if (prev == n) break;
                 p = (p + 1) & hmask;
             }
         }
-    }
-    __syncthreads();
-    for (int p = tid; p < ht_size; p += G1_THREADS) {
-        const float v = hv[p];
-        if (hk[p] != 0xffffffffu && v != v) work[atomicAdd(&s_nwork, 1)] = (uint16_t)p;
     }
     __syncthreads();
     const int nwork = s_nwork;
@@ -301,7 +306,7 @@ __global__ void __launch_bounds__(G1_THREADS) group_g1_kernel(int d, int nprobe,
             nn[u] = 0xffffffffu;
             icd[u] = 0.f;
             if (e < npairs) {
-                const int i = e / nsubc, s = e - i * nsubc;
+                const int i = pair_probe(e, nsubc, sub_shift), s = e - i * nsubc;
                 if (s_sz[i] != 0) {
                     const size_t o = (size_t)s_c[i] * nsubc + s;
                     const uint32_t ss = __ldg(L.sub_sizes + o);
@@ -320,7 +325,7 @@ __global__ void __launch_bounds__(G1_THREADS) group_g1_kernel(int d, int nprobe,
             if (e >= npairs) continue;
             float r = qnan, sb = __int_as_float(0x7f800000);
             if (nn[u] != 0xffffffffu) {
-                const int i = e / nsubc;
+                const int i = pair_probe(e, nsubc, sub_shift);
                 uint32_t p = (nn[u] * 2654435761u) & hmask;
                 while (hk[p] != nn[u]) p = (p + 1) & hmask;
                 const float qsd = hv[p];
@@ -392,7 +397,7 @@ __global__ void __launch_bounds__(128) group_g2_kernel(int nq, int npairs, const
     if (warp == 0 && q0 + lane < nq) thr[q0 + lane] = acc / (float)counts[q0 + lane];   // 0/0 -> NaN like the reference
 }
 
-__global__ void __launch_bounds__(G1_THREADS) group_g3_kernel(int nprobe, int nsubc, uint64_t max_codes,
+__global__ void __launch_bounds__(G1_THREADS) group_g3_kernel(int nprobe, int nsubc, int sub_shift, uint64_t max_codes,
                                                               int do_pruning,
                                                               const uint32_t *__restrict__ coarse_i, DeviceLists L,
                                                               uint32_t c_begin, uint32_t c_end, SegTables T)
@@ -420,7 +425,7 @@ __global__ void __launch_bounds__(G1_THREADS) group_g3_kernel(int nprobe, int ns
             ss[u] = 0;
             r[u] = 0.f;
             if (e < npairs) {
-                const int i = e / nsubc, s = e - i * nsubc;
+                const int i = pair_probe(e, nsubc, sub_shift), s = e - i * nsubc;
                 if (s_sz[i] != 0) {
                     ss[u] = __ldg(L.sub_sizes + (size_t)s_c[i] * nsubc + s);
                     if (do_pruning && s_inh[i]) r[u] = rv[e];    // rows past the horizon stay 0 (:228)
@@ -432,7 +437,7 @@ __global__ void __launch_bounds__(G1_THREADS) group_g3_kernel(int nprobe, int ns
             const int e = e0 + u * G1_THREADS + tid;
             if (e >= npairs || ss[u] == 0) continue;
             const bool keep = !do_pruning || r[u] < threshold;
-            if (keep) atomicAdd(&s_kept[e / nsubc], ss[u]);
+            if (keep) atomicAdd(&s_kept[pair_probe(e, nsubc, sub_shift)], ss[u]);
             else sb[e] = __int_as_float(0x7f800000);
         }
     }
@@ -510,7 +515,10 @@ cudaError_t launch_prep_grouping(cudaStream_t st, uint64_t *launches, int nq, in
                        (size_t)nprobe + 16;
     cudaError_t e = cudaFuncSetAttribute(group_g1_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sm1);
     if (e != cudaSuccess) return e;
-    group_g1_kernel<<<nq, G1_THREADS, sm1, st>>>(d, nprobe, nsubc, ht, max_codes, do_pruning ? 1 : 0, queries,
+    int sub_shift = -1;
+    for (int b = 0; b < 16; b++)
+        if ((1 << b) == nsubc) sub_shift = b;
+    group_g1_kernel<<<nq, G1_THREADS, sm1, st>>>(d, nprobe, nsubc, sub_shift, ht, max_codes, do_pruning ? 1 : 0, queries,
                                                 coarse_d, coarse_i, L, T);
     ++*launches;
     e = cudaGetLastError();
@@ -522,7 +530,7 @@ cudaError_t launch_prep_grouping(cudaStream_t st, uint64_t *launches, int nq, in
         if (e != cudaSuccess) return e;
     }
     const size_t sm3 = (size_t)nprobe * 13 + 16;
-    group_g3_kernel<<<nq, G1_THREADS, sm3, st>>>(nprobe, nsubc, max_codes, do_pruning ? 1 : 0, coarse_i, L, c_begin,
+    group_g3_kernel<<<nq, G1_THREADS, sm3, st>>>(nprobe, nsubc, sub_shift, max_codes, do_pruning ? 1 : 0, coarse_i, L, c_begin,
                                                 c_end, T);
     ++*launches;
     return cudaGetLastError();
@@ -921,11 +929,20 @@ __global__ void __launch_bounds__(SCAN_THREADS) scan_kernel(ScanArgs a)
         const uint32_t slot0 = s_slot[seg] + (uint32_t)pk * SCAN_PIECE;
         const uint32_t seq0 = s_seq[seg] + (uint32_t)pk * SCAN_PIECE;
         float base = s_base[seg];
+        // sub-group bases of this list: up to 64 sub-groups live in two registers per lane and are fetched
+        // with a shuffle (their loads overlap the code loads below); more go through shared memory
+        float sb0 = 0.f, sb1 = 0.f;
+        const bool sb_regs = a.nsubc <= 64;
         if (GROUPING) {
-            __syncwarp();
             const float *sbg = a.T.sub_base + ((size_t)q * nprobe + seg) * a.nsubc;
-            for (int s = lane; s < a.nsubc; s += 32) wsub[s] = sbg[s];
-            __syncwarp();
+            if (sb_regs) {
+                sb0 = lane < a.nsubc ? __ldg(sbg + lane) : __int_as_float(0x7f800000);
+                sb1 = lane + 32 < a.nsubc ? __ldg(sbg + lane + 32) : __int_as_float(0x7f800000);
+            } else {
+                __syncwarp();
+                for (int s = lane; s < a.nsubc; s += 32) wsub[s] = sbg[s];
+                __syncwarp();
+            }
         }
 
         // issue every load of the piece before the first use
@@ -954,7 +971,14 @@ __global__ void __launch_bounds__(SCAN_THREADS) scan_kernel(ScanArgs a)
 #pragma unroll
         for (int c = 0; c < SCAN_PIECE_CHUNKS; c++) {
             if (c * SCAN_CHUNK < rem) {   // warp-uniform
-                float acc0 = GROUPING ? wsub[sid[c]] : base;
+                float acc0 = base;
+                if (GROUPING) {
+                    if (sb_regs) {
+                        const float v0 = __shfl_sync(IVF_FULL_MASK, sb0, sid[c] & 31);
+                        const float v1 = __shfl_sync(IVF_FULL_MASK, sb1, sid[c] & 31);
+                        acc0 = (sid[c] & 32) ? v1 : v0;
+                    } else acc0 = wsub[sid[c]];
+                }
                 float acc1;
                 if (M == 64) acc1 = *reinterpret_cast<const float *>(lut + 65536 + nm[c] * 128u + 4u * lane);
                 else acc1 = *reinterpret_cast<const float *>(lut + prmt(nm[c], Onorm, 0x5504u));
