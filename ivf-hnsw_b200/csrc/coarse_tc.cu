@@ -113,19 +113,19 @@ static __device__ __forceinline__ void mbar_arrive(uint32_t bar)
 {
     asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(bar) : "memory");
 }
-// bounded wait: a protocol bug traps (-> launch error) instead of hanging the device
+// bounded wait: a protocol bug traps (-> launch error) instead of hanging the device.  try_wait suspends
+// the thread in hardware (up to the hint) instead of burning issue slots the epilogue warps need.
 static __device__ __forceinline__ void mbar_wait(uint32_t bar, uint32_t parity)
 {
     uint32_t done = 0;
-    const long long t0 = clock64();
-    while (true) {
+    for (uint32_t spins = 0;; spins++) {
         asm volatile(
-            "{\n\t.reg .pred p;\n\tmbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n\tselp.u32 %0, 1, 0, p;\n\t}"
+            "{\n\t.reg .pred p;\n\tmbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2, %3;\n\tselp.u32 %0, 1, 0, p;\n\t}"
             : "=r"(done)
-            : "r"(bar), "r"(parity)
+            : "r"(bar), "r"(parity), "r"(20000u)
             : "memory");
         if (done) break;
-        if (clock64() - t0 > 4000000000ll) __trap();
+        if (spins > (1u << 22)) __trap();
     }
 }
 static __device__ __forceinline__ void tma_load_2d(uint32_t dst, const CUtensorMap *map, int x, int y, uint32_t bar)
