@@ -1,0 +1,3 @@
+// placeholder so that sources including <faiss/utils.h> through the ivf-hnsw headers keep compiling;
+// the drop-in needs nothing from it.
+#pragma once

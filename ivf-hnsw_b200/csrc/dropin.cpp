@@ -1,0 +1,614 @@
+// Host side of the drop-in: ivfhnsw::IndexIVF_HNSW / IndexIVF_HNSW_Grouping (include/ivf-hnsw/*.h) and the
+// faiss file helpers (include/faiss/index_io.h), all forwarding to the C ABI of libivfhnsw_b200.so.
+// Compiled into libivfhnsw_dropin.so.  No arithmetic of the search / indexing path happens here.
+#include <algorithm>
+#include <cstdarg>
+#include <cstdlib>
+#include <cstring>
+#include <mutex>
+#include <stdexcept>
+#include <string>
+
+#include <ivf-hnsw/IndexIVF_HNSW.h>
+#include <ivf-hnsw/IndexIVF_HNSW_Grouping.h>
+
+#include "../../include/ivfhnsw_b200.h"
+
+// ------------------------------------------------------------------------------------------ faiss helpers
+namespace faiss {
+
+void LinearTransform::apply_noalloc(long n, const float *x, float *xt) const
+{
+    for (long i = 0; i < n; i++)
+        for (int o = 0; o < d_out; o++) {
+            float acc = have_bias ? b[o] : 0.f;
+            const float *row = A.data() + (size_t)o * d_in;
+            for (int j = 0; j < d_in; j++) acc += row[j] * x[(size_t)i * d_in + j];
+            xt[(size_t)i * d_out + o] = acc;
+        }
+}
+
+void LinearTransform::transform_transpose(long n, const float *y, float *x) const
+{
+    for (long i = 0; i < n; i++)
+        for (int j = 0; j < d_in; j++) {
+            float acc = 0.f;
+            for (int o = 0; o < d_out; o++) {
+                const float v = y[(size_t)i * d_out + o] - (have_bias ? b[o] : 0.f);
+                acc += A[(size_t)o * d_in + j] * v;
+            }
+            x[(size_t)i * d_in + j] = acc;
+        }
+}
+
+namespace {
+struct File {
+    FILE *f;
+    File(const char *name, const char *mode) : f(fopen(name, mode))
+    {
+        if (!f) throw std::runtime_error(std::string("could not open ") + name);
+    }
+    ~File() { if (f) fclose(f); }
+    void put(const void *p, size_t n) { if (fwrite(p, 1, n, f) != n) throw std::runtime_error("write error"); }
+    void get(void *p, size_t n) { if (fread(p, 1, n, f) != n) throw std::runtime_error("read error"); }
+    template <typename T> void put1(const T &v) { put(&v, sizeof(T)); }
+    template <typename T> T get1() { T v; get(&v, sizeof(T)); return v; }
+    void put_floats(const std::vector<float> &v) { put1<size_t>(v.size()); put(v.data(), v.size() * 4); }
+    void get_floats(std::vector<float> &v) { v.resize(get1<size_t>()); get(v.data(), v.size() * 4); }
+};
+}  // namespace
+
+// size_t d, M, nbits; size_t count + floats (faiss/index_io.cpp:117-124,504-513)
+void write_ProductQuantizer(const ProductQuantizer *pq, const char *fname)
+{
+    File f(fname, "wb");
+    f.put1<size_t>(pq->d);
+    f.put1<size_t>(pq->M);
+    f.put1<size_t>(pq->nbits);
+    f.put_floats(pq->centroids);
+}
+
+ProductQuantizer *read_ProductQuantizer(const char *fname)
+{
+    File f(fname, "rb");
+    const size_t d = f.get1<size_t>(), M = f.get1<size_t>(), nbits = f.get1<size_t>();
+    ProductQuantizer *pq = new ProductQuantizer(d, M, nbits);
+    f.get_floats(pq->centroids);
+    return pq;
+}
+
+// "LTra", bool have_bias, A, b, int d_in, int d_out, bool is_trained (faiss/index_io.cpp:63-105,425-470)
+void write_VectorTransform(const VectorTransform *vt, const char *fname)
+{
+    const LinearTransform *lt = dynamic_cast<const LinearTransform *>(vt);
+    if (!lt) throw std::runtime_error("only LinearTransform can be written");
+    File f(fname, "wb");
+    f.put("LTra", 4);
+    f.put1<bool>(lt->have_bias);
+    f.put_floats(lt->A);
+    f.put_floats(lt->b);
+    f.put1<int>(lt->d_in);
+    f.put1<int>(lt->d_out);
+    f.put1<bool>(lt->is_trained);
+}
+
+VectorTransform *read_VectorTransform(const char *fname)
+{
+    File f(fname, "rb");
+    char tag[4];
+    f.get(tag, 4);
+    // OPQ matrices are stored either as generic linear transforms or with their own tag plus (M, niter, ...)
+    const bool opq = !memcmp(tag, "OPQm", 4), rrot = !memcmp(tag, "rrot", 4);
+    if (memcmp(tag, "LTra", 4) && !opq && !rrot) throw std::runtime_error("unsupported VectorTransform file");
+    LinearTransform *lt = new LinearTransform();
+    lt->have_bias = f.get1<bool>();
+    f.get_floats(lt->A);
+    f.get_floats(lt->b);
+    lt->d_in = f.get1<int>();
+    lt->d_out = f.get1<int>();
+    lt->is_trained = f.get1<bool>();
+    return lt;
+}
+
+}  // namespace faiss
+
+// ------------------------------------------------------------------------------------------ utils
+namespace ivfhnsw {
+
+namespace {
+// faiss::RandomGenerator on linux + rand_perm (faiss/utils.cpp:139-159,311-321): glibc random_r, 8-byte state
+void faiss_rand_perm(std::vector<int> &perm, size_t n, long seed)
+{
+    char state[8];
+    struct random_data rd;
+    memset(&rd, 0, sizeof rd);
+    initstate_r((unsigned)seed, state, sizeof state, &rd);
+    perm.resize(n);
+    for (size_t i = 0; i < n; i++) perm[i] = (int)i;
+    for (size_t i = 0; i + 1 < n; i++) {
+        int32_t r;
+        random_r(&rd, &r);
+        std::swap(perm[i], perm[i + (size_t)(r % (int)(n - i))]);
+    }
+}
+
+uint64_t fingerprint(const float *p, size_t n)
+{
+    // pointer + size + a strided sample of the contents: cheap enough for the one-query search() path
+    uint64_t h = 1469598103934665603ull ^ (uint64_t)(uintptr_t)p;
+    h = (h ^ n) * 1099511628211ull;
+    const size_t step = n > 256 ? n / 256 : 1;
+    for (size_t i = 0; i < n; i += step) {
+        uint32_t b;
+        memcpy(&b, p + i, 4);
+        h = (h ^ b) * 1099511628211ull;
+    }
+    if (n) {
+        uint32_t b;
+        memcpy(&b, p + n - 1, 4);
+        h = (h ^ b) * 1099511628211ull;
+    }
+    return h;
+}
+
+void to_max_heap_order(size_t k, float *d, long *l)
+{
+    // ascending -> descending: a descending array is a valid faiss max-heap (root = worst), which is what
+    // reference callers that peek at distances[0] expect (faiss/Heap.h:89-143)
+    std::reverse(d, d + k);
+    std::reverse(l, l + k);
+}
+}  // namespace
+
+void random_subset(const float *x, float *x_out, size_t d, size_t nx, size_t sub_nx)
+{
+    std::vector<int> perm;
+    faiss_rand_perm(perm, nx, 1234);
+    for (size_t i = 0; i < sub_nx; i++) memcpy(x_out + i * d, x + (size_t)perm[i] * d, sizeof(float) * d);
+}
+
+float fvec_L2sqr(const float *x, const float *y, size_t d)
+{
+    float lane[8] = {0, 0, 0, 0, 0, 0, 0, 0};
+    const size_t n = (d >> 4) << 4;
+    for (size_t i = 0; i < n; i += 8)
+        for (size_t j = 0; j < 8; j++) {
+            const float df = x[i + j] - y[i + j];
+            lane[j] += df * df;
+        }
+    float r = lane[0];
+    for (int j = 1; j < 8; j++) r += lane[j];
+    return r;
+}
+
+// ------------------------------------------------------------------------------------------ IndexIVF_HNSW
+void IndexIVF_HNSW::ck(int rc, const char *what) const
+{
+    if (rc >= 0) return;
+    fprintf(stderr, "ivfhnsw_b200: %s failed: %s\n", what, h_ ? ivfhnsw_b200_last_error(h_) : "no handle");
+    exit(1);
+}
+
+void IndexIVF_HNSW::init(size_t dim, size_t ncentroids, size_t bytes_per_code, size_t nbits_per_idx, size_t nsubc)
+{
+    d = dim;
+    nc = ncentroids;
+    code_size = bytes_per_code;
+    nsubc_ = nsubc;
+    quantizer = nullptr;
+    pq = new faiss::ProductQuantizer(dim, bytes_per_code, nbits_per_idx);
+    norm_pq = new faiss::ProductQuantizer(1, 1, nbits_per_idx);
+    opq_matrix = nullptr;
+    do_opq = false;
+    nprobe = 16;
+    max_codes = 10000;
+    pruning_flag_ = false;
+    fp_pq_ = fp_norm_ = fp_opq_ = 0;
+    sent_nprobe_ = sent_max_codes_ = (size_t)-1;
+    sent_flags_ = -1;
+    h_ = nullptr;
+    const char *dev = getenv("IVFHNSW_B200_DEVICE");
+    const int rc = ivfhnsw_b200_create(&h_, dim, ncentroids, bytes_per_code, nbits_per_idx, nsubc, dev ? atoi(dev) : 0);
+    if (rc < 0) {
+        fprintf(stderr, "ivfhnsw_b200: create failed: %s\n", h_ ? ivfhnsw_b200_last_error(h_) : "no sm_100 device");
+        exit(1);
+    }
+}
+
+IndexIVF_HNSW::IndexIVF_HNSW(size_t dim, size_t ncentroids, size_t bytes_per_code, size_t nbits_per_idx, size_t)
+{
+    init(dim, ncentroids, bytes_per_code, nbits_per_idx, 0);
+}
+
+IndexIVF_HNSW::IndexIVF_HNSW(size_t dim, size_t ncentroids, size_t bytes_per_code, size_t nbits_per_idx, size_t nsubc,
+                             int)
+{
+    init(dim, ncentroids, bytes_per_code, nbits_per_idx, nsubc);
+}
+
+IndexIVF_HNSW::~IndexIVF_HNSW()
+{
+    if (quantizer) delete quantizer;
+    if (pq) delete pq;
+    if (norm_pq) delete norm_pq;
+    if (opq_matrix) delete opq_matrix;
+    if (h_) ivfhnsw_b200_destroy(h_);
+}
+
+std::vector<float> &IndexIVF_HNSW::get_centroid_norms()
+{
+    centroid_norms.resize(nc);
+    ck(ivfhnsw_b200_get_centroid_norms(h_, centroid_norms.data()), "get_centroid_norms");
+    return centroid_norms;
+}
+
+void IndexIVF_HNSW::build_quantizer(const char *path_data, const char *, const char *, size_t M, size_t efConstruction)
+{
+    // only the centroid table is needed: the coarse quantizer is the exact GEMM over it, no graph files
+    std::vector<float> cent(nc * d);
+    {
+        std::ifstream in(path_data, std::ios::binary);
+        if (!in) {
+            fprintf(stderr, "ivfhnsw_b200: cannot open centroid file %s\n", path_data);
+            exit(1);
+        }
+        readXvec<float>(in, cent.data(), d, nc);
+    }
+    ck(ivfhnsw_b200_set_centroids(h_, cent.data()), "set_centroids");
+    if (quantizer) delete quantizer;
+    quantizer = new hnswlib::HierarchicalNSW(d, nc, M, efConstruction);
+}
+
+void IndexIVF_HNSW::sync_quantizers()
+{
+    if (pq) {
+        if (pq->centroids.size() != d * 256) {
+            fprintf(stderr, "ivfhnsw_b200: residual PQ has %zu floats, expected %zu\n", pq->centroids.size(), d * 256);
+            exit(1);
+        }
+        const uint64_t fp = fingerprint(pq->centroids.data(), pq->centroids.size());
+        if (fp != fp_pq_) {
+            ck(ivfhnsw_b200_set_pq(h_, pq->centroids.data()), "set_pq");
+            fp_pq_ = fp;
+        }
+    }
+    if (norm_pq && norm_pq->centroids.size() == 256) {
+        const uint64_t fp = fingerprint(norm_pq->centroids.data(), 256);
+        if (fp != fp_norm_) {
+            ck(ivfhnsw_b200_set_norm_pq(h_, norm_pq->centroids.data()), "set_norm_pq");
+            fp_norm_ = fp;
+        }
+    }
+    if (opq_matrix && opq_matrix->A.size() == d * d) {
+        const uint64_t fp = fingerprint(opq_matrix->A.data(), d * d);
+        if (fp != fp_opq_) {
+            ck(ivfhnsw_b200_set_opq(h_, opq_matrix->A.data()), "set_opq");
+            fp_opq_ = fp;
+        }
+    }
+    const int flags = (do_opq ? 1 : 0) | (pruning_flag_ ? 2 : 0);
+    if (nprobe != sent_nprobe_ || max_codes != sent_max_codes_ || flags != sent_flags_) {
+        ck(ivfhnsw_b200_set_params(h_, nprobe, max_codes, do_opq ? 1 : 0, pruning_flag_ ? 1 : 0), "set_params");
+        sent_nprobe_ = nprobe;
+        sent_max_codes_ = max_codes;
+        sent_flags_ = flags;
+    }
+}
+
+void IndexIVF_HNSW::pull_quantizers()
+{
+    pq->centroids.resize(d * 256);
+    norm_pq->centroids.resize(256);
+    std::vector<float> A(do_opq ? d * d : 0);
+    ck(ivfhnsw_b200_get_pq(h_, pq->centroids.data(), norm_pq->centroids.data(), do_opq ? A.data() : nullptr), "get_pq");
+    fp_pq_ = fingerprint(pq->centroids.data(), pq->centroids.size());
+    fp_norm_ = fingerprint(norm_pq->centroids.data(), 256);
+    if (do_opq) {
+        if (opq_matrix) delete opq_matrix;
+        opq_matrix = new faiss::LinearTransform((int)d, (int)d, false);
+        opq_matrix->A.swap(A);
+        fp_opq_ = fingerprint(opq_matrix->A.data(), d * d);
+    }
+}
+
+void IndexIVF_HNSW::assign(size_t n, const float *x, idx_t *labels, size_t k)
+{
+    // k > 1 returns the k-th nearest like the reference (top of a k-element max-heap, IndexIVF_HNSW.cpp:71)
+    ck(ivfhnsw_b200_assign(h_, n, x, labels, k), "assign");
+}
+
+void IndexIVF_HNSW::assign_u8(size_t n, const uint8_t *x, idx_t *labels)
+{
+    ck(ivfhnsw_b200_assign_u8(h_, n, x, labels), "assign_u8");
+}
+
+void IndexIVF_HNSW::search_batch(size_t nq, size_t k, const float *x, float *distances, long *labels, bool sorted)
+{
+    static_assert(sizeof(long) == sizeof(int64_t), "labels are 64-bit");
+    sync_quantizers();
+    ck(ivfhnsw_b200_search(h_, nq, k, x, distances, reinterpret_cast<int64_t *>(labels)), "search");
+    if (!sorted)
+        for (size_t i = 0; i < nq; i++) to_max_heap_order(k, distances + i * k, labels + i * k);
+}
+
+void IndexIVF_HNSW::search(size_t k, const float *x, float *distances, long *labels)
+{
+    search_batch(1, k, x, distances, labels, false);
+}
+
+IndexIVF_HNSW::idx_t IndexIVF_HNSW::search_enn(const float *x, float *distances, long *labels)
+{
+    search_batch(1, 1, x, distances, labels, true);
+    return labels[0] < 0 ? 0 : 1;
+}
+
+void IndexIVF_HNSW::search2(size_t k, const float *x, float *distances, long *labels, float *query_centroid_dists,
+                            idx_t *centroid_idxs)
+{
+    sync_quantizers();
+    ck(ivfhnsw_b200_search_given_coarse(h_, 1, k, x, query_centroid_dists, centroid_idxs, distances,
+                                        reinterpret_cast<int64_t *>(labels)),
+       "search2");
+    to_max_heap_order(k, distances, labels);
+}
+
+void IndexIVF_HNSW::add_batch(size_t n, const float *x, const idx_t *xids, const idx_t *precomputed_idx)
+{
+    sync_quantizers();
+    ck(ivfhnsw_b200_add_batch(h_, n, x, xids, precomputed_idx), "add_batch");
+}
+
+void IndexIVF_HNSW::train_pq(size_t n, const float *x)
+{
+    // train_pq replaces all codebooks: push only the parameters (do_opq), not the stale codebooks
+    ck(ivfhnsw_b200_set_params(h_, nprobe, max_codes, do_opq ? 1 : 0, pruning_flag_ ? 1 : 0), "set_params");
+    sent_flags_ = -1;
+    ck(ivfhnsw_b200_train_pq(h_, n, x), "train_pq");
+    pull_quantizers();
+}
+
+void IndexIVF_HNSW::compute_centroid_norms()
+{
+    ck(ivfhnsw_b200_compute_centroid_norms(h_), "compute_centroid_norms");
+}
+
+void IndexIVF_HNSW::rotate_quantizer()
+{
+    if (!do_opq) {   // reference IndexIVF_HNSW.cpp:790-793
+        printf("OPQ encoding is turned off\n");
+        abort();
+    }
+    sync_quantizers();
+    ck(ivfhnsw_b200_rotate_quantizer(h_), "rotate_quantizer");
+}
+
+namespace {
+struct HostLists {
+    std::vector<int64_t> off;
+    std::vector<uint32_t> ids, nn, ss;
+    std::vector<uint8_t> codes, ncodes;
+    std::vector<float> alphas, icd;
+};
+}  // namespace
+
+void IndexIVF_HNSW::sync_host_lists()
+{
+    ck(ivfhnsw_b200_finalize(h_), "finalize");
+    size_t n = 0;
+    ck(ivfhnsw_b200_ntotal(h_, &n), "ntotal");
+    HostLists L;
+    L.off.resize(nc + 1);
+    L.ids.resize(std::max<size_t>(n, 1));
+    L.codes.resize(std::max<size_t>(n, 1) * code_size);
+    L.ncodes.resize(std::max<size_t>(n, 1));
+    if (nsubc_) { L.nn.resize(nc * nsubc_); L.ss.resize(nc * nsubc_); L.alphas.resize(nc); L.icd.resize(nc * nsubc_); }
+    ck(ivfhnsw_b200_export_lists(h_, L.off.data(), L.ids.data(), L.codes.data(), L.ncodes.data(),
+                                 nsubc_ ? L.nn.data() : nullptr, nsubc_ ? L.ss.data() : nullptr,
+                                 nsubc_ ? L.alphas.data() : nullptr, nsubc_ ? L.icd.data() : nullptr),
+       "export_lists");
+    ids.assign(nc, {});
+    codes.assign(nc, {});
+    norm_codes.assign(nc, {});
+    for (size_t c = 0; c < nc; c++) {
+        const size_t a = (size_t)L.off[c], b = (size_t)L.off[c + 1];
+        ids[c].assign(L.ids.begin() + a, L.ids.begin() + b);
+        codes[c].assign(L.codes.begin() + a * code_size, L.codes.begin() + b * code_size);
+        norm_codes[c].assign(L.ncodes.begin() + a, L.ncodes.begin() + b);
+    }
+}
+
+// File layout (reference IndexIVF_HNSW.cpp:637-663,758-779; Grouping.cpp:397-483), all vectors as
+// [uint32 count][elements]:  size_t d, nc, (nsubc); ids[nc]; codes[nc]; norm_codes[nc];
+// (nn_centroid_idxs[nc]; subgroup_sizes[nc]; alphas); centroid_norms; (inter_centroid_dists[nc])
+void IndexIVF_HNSW::write_common(std::ofstream &out, bool grouping)
+{
+    ck(ivfhnsw_b200_finalize(h_), "finalize");
+    size_t n = 0;
+    ck(ivfhnsw_b200_ntotal(h_, &n), "ntotal");
+    HostLists L;
+    L.off.resize(nc + 1);
+    L.ids.resize(std::max<size_t>(n, 1));
+    L.codes.resize(std::max<size_t>(n, 1) * code_size);
+    L.ncodes.resize(std::max<size_t>(n, 1));
+    if (grouping) { L.nn.resize(nc * nsubc_); L.ss.resize(nc * nsubc_); L.alphas.resize(nc); L.icd.resize(nc * nsubc_); }
+    ck(ivfhnsw_b200_export_lists(h_, L.off.data(), L.ids.data(), L.codes.data(), L.ncodes.data(),
+                                 grouping ? L.nn.data() : nullptr, grouping ? L.ss.data() : nullptr,
+                                 grouping ? L.alphas.data() : nullptr, grouping ? L.icd.data() : nullptr),
+       "export_lists");
+    auto put_vec = [&](const void *p, size_t count, size_t elem) {
+        const uint32_t c32 = (uint32_t)count;
+        out.write(reinterpret_cast<const char *>(&c32), 4);
+        if (count) out.write(reinterpret_cast<const char *>(p), (std::streamsize)(count * elem));
+    };
+    write_variable(out, d);
+    write_variable(out, nc);
+    if (grouping) write_variable(out, nsubc_);
+    for (size_t c = 0; c < nc; c++) put_vec(L.ids.data() + L.off[c], (size_t)(L.off[c + 1] - L.off[c]), 4);
+    for (size_t c = 0; c < nc; c++)
+        put_vec(L.codes.data() + (size_t)L.off[c] * code_size, (size_t)(L.off[c + 1] - L.off[c]) * code_size, 1);
+    for (size_t c = 0; c < nc; c++) put_vec(L.ncodes.data() + L.off[c], (size_t)(L.off[c + 1] - L.off[c]), 1);
+    if (grouping) {
+        for (size_t c = 0; c < nc; c++) put_vec(L.nn.data() + c * nsubc_, nsubc_, 4);
+        // the reference leaves subgroup_sizes empty for groups that never received points
+        for (size_t c = 0; c < nc; c++) put_vec(L.ss.data() + c * nsubc_, L.off[c + 1] > L.off[c] ? nsubc_ : 0, 4);
+        put_vec(L.alphas.data(), nc, 4);
+    }
+    std::vector<float> &cn = get_centroid_norms();
+    put_vec(cn.data(), nc, 4);
+    if (grouping)
+        for (size_t c = 0; c < nc; c++) put_vec(L.icd.data() + c * nsubc_, nsubc_, 4);
+}
+
+void IndexIVF_HNSW::read_common(std::ifstream &in, bool grouping)
+{
+    size_t fd = 0, fnc = 0, fns = 0;
+    read_variable(in, fd);
+    read_variable(in, fnc);
+    if (grouping) read_variable(in, fns);
+    if (fd != d || fnc != nc || (grouping && fns != nsubc_)) {
+        fprintf(stderr, "ivfhnsw_b200: index file is for d=%zu nc=%zu nsubc=%zu\n", fd, fnc, fns);
+        exit(1);
+    }
+    HostLists L;
+    L.off.assign(nc + 1, 0);
+    std::vector<uint32_t> v32;
+    std::vector<uint8_t> v8;
+    std::vector<float> vf;
+    for (size_t c = 0; c < nc; c++) {
+        read_vector(in, v32);
+        L.off[c + 1] = L.off[c] + (int64_t)v32.size();
+        L.ids.insert(L.ids.end(), v32.begin(), v32.end());
+    }
+    for (size_t c = 0; c < nc; c++) {
+        read_vector(in, v8);
+        L.codes.insert(L.codes.end(), v8.begin(), v8.end());
+    }
+    for (size_t c = 0; c < nc; c++) {
+        read_vector(in, v8);
+        L.ncodes.insert(L.ncodes.end(), v8.begin(), v8.end());
+    }
+    if (grouping) {
+        L.nn.assign(nc * nsubc_, 0);
+        L.ss.assign(nc * nsubc_, 0);
+        for (size_t c = 0; c < nc; c++) {
+            read_vector(in, v32);
+            std::copy(v32.begin(), v32.begin() + std::min(v32.size(), nsubc_), L.nn.begin() + c * nsubc_);
+        }
+        for (size_t c = 0; c < nc; c++) {
+            read_vector(in, v32);
+            std::copy(v32.begin(), v32.begin() + std::min(v32.size(), nsubc_), L.ss.begin() + c * nsubc_);
+        }
+        read_vector(in, L.alphas);
+    }
+    read_vector(in, vf);   // centroid norms
+    if (grouping) {
+        L.icd.assign(nc * nsubc_, 0.f);
+        std::vector<float> row;
+        for (size_t c = 0; c < nc; c++) {
+            read_vector(in, row);
+            std::copy(row.begin(), row.begin() + std::min(row.size(), nsubc_), L.icd.begin() + c * nsubc_);
+        }
+    }
+    if (L.ids.empty()) { L.ids.resize(1); L.codes.resize(code_size); L.ncodes.resize(1); }
+    sync_quantizers();
+    ck(ivfhnsw_b200_load_lists(h_, L.off.data(), L.ids.data(), L.codes.data(), L.ncodes.data(),
+                               grouping ? L.nn.data() : nullptr, grouping ? L.ss.data() : nullptr,
+                               grouping ? L.alphas.data() : nullptr, grouping ? L.icd.data() : nullptr),
+       "load_lists");
+    if (vf.size() == nc) ck(ivfhnsw_b200_set_centroid_norms(h_, vf.data()), "set_centroid_norms");
+}
+
+void IndexIVF_HNSW::write(const char *path_index)
+{
+    std::ofstream out(path_index, std::ios::binary);
+    write_common(out, false);
+}
+void IndexIVF_HNSW::write(const char *path_index, bool) { write(path_index); }
+
+void IndexIVF_HNSW::read(const char *path)
+{
+    std::ifstream in(path, std::ios::binary);
+    if (!in) {
+        fprintf(stderr, "ivfhnsw_b200: cannot open index file %s\n", path);
+        exit(1);
+    }
+    read_common(in, false);
+}
+
+// ------------------------------------------------------------------------------------------ Grouping
+IndexIVF_HNSW_Grouping::IndexIVF_HNSW_Grouping(size_t dim, size_t ncentroids, size_t bytes_per_code,
+                                               size_t nbits_per_idx, size_t nsubcentroids)
+    : IndexIVF_HNSW(dim, ncentroids, bytes_per_code, nbits_per_idx, nsubcentroids, 0), nsubc(nsubcentroids),
+      do_pruning(false)
+{
+}
+
+void IndexIVF_HNSW_Grouping::add_group(size_t group_idx, size_t group_size, const float *x, const idx_t *gids)
+{
+    // the C ABI serialises callers on the handle's mutex; quantizer sync must not race either
+    pruning_flag_ = do_pruning;
+    {
+        static std::mutex mu;   // only guards the (rare) re-upload of swapped codebooks
+        std::lock_guard<std::mutex> lk(mu);
+        sync_quantizers();
+    }
+    ck(ivfhnsw_b200_add_group(h_, group_idx, group_size, x, gids), "add_group");
+}
+
+void IndexIVF_HNSW_Grouping::search(size_t k, const float *x, float *distances, long *labels)
+{
+    pruning_flag_ = do_pruning;
+    IndexIVF_HNSW::search(k, x, distances, labels);
+}
+
+void IndexIVF_HNSW_Grouping::train_pq(size_t n, const float *x)
+{
+    pruning_flag_ = do_pruning;
+    IndexIVF_HNSW::train_pq(n, x);
+}
+
+void IndexIVF_HNSW_Grouping::compute_inter_centroid_dists()
+{
+    ck(ivfhnsw_b200_finalize(h_), "finalize");   // neighbour lists, inter-centroid distances, alphas, CSR
+}
+
+void IndexIVF_HNSW_Grouping::write(const char *path_index)
+{
+    std::ofstream out(path_index, std::ios::binary);
+    write_common(out, true);
+}
+void IndexIVF_HNSW_Grouping::write(const char *path_index, bool) { write(path_index); }
+
+void IndexIVF_HNSW_Grouping::read(const char *path_index)
+{
+    std::ifstream in(path_index, std::ios::binary);
+    if (!in) {
+        fprintf(stderr, "ivfhnsw_b200: cannot open index file %s\n", path_index);
+        exit(1);
+    }
+    pruning_flag_ = do_pruning;
+    read_common(in, true);
+}
+
+void IndexIVF_HNSW_Grouping::sync_host_lists()
+{
+    IndexIVF_HNSW::sync_host_lists();
+    std::vector<int64_t> off(nc + 1);
+    size_t n = 0;
+    ck(ivfhnsw_b200_ntotal(h_, &n), "ntotal");
+    std::vector<uint32_t> ids_(std::max<size_t>(n, 1)), nn(nc * nsubc), ss(nc * nsubc);
+    std::vector<uint8_t> cd(std::max<size_t>(n, 1) * code_size), ncd(std::max<size_t>(n, 1));
+    std::vector<float> icd(nc * nsubc);
+    alphas.resize(nc);
+    ck(ivfhnsw_b200_export_lists(h_, off.data(), ids_.data(), cd.data(), ncd.data(), nn.data(), ss.data(), alphas.data(),
+                                 icd.data()),
+       "export_lists");
+    nn_centroid_idxs.assign(nc, {});
+    subgroup_sizes.assign(nc, {});
+    for (size_t c = 0; c < nc; c++) {
+        nn_centroid_idxs[c].assign(nn.begin() + c * nsubc, nn.begin() + (c + 1) * nsubc);
+        subgroup_sizes[c].assign(ss.begin() + c * nsubc, ss.begin() + (c + 1) * nsubc);
+    }
+}
+
+}  // namespace ivfhnsw
