@@ -240,6 +240,7 @@ def main():
         dist.init_process_group("nccl", device_id=dev)
     log = (lambda m: print("[bench r%d] %s" % (rank, m), file=sys.stderr, flush=True))
     P = pkg()
+    sharding = importlib.import_module("ivf-hnsw_b200.sharding")
     idx, queries, gt0, cent_h = build_index(w, torch, dev, log)
     if args.coarse_impl >= 0:
         idx.set_option("coarse_impl", args.coarse_impl)
@@ -280,8 +281,7 @@ def main():
 
     # ------------------------------------------------------------------ our arm
     if world > 1:
-        per = (w["nc"] + world - 1) // world
-        idx.set_shard(rank * per, min(w["nc"], (rank + 1) * per))
+        idx.set_shard(*sharding.shard_range(rank, world, w["nc"]))
     stream = torch.cuda.Stream(device=dev)   # a real (non-default) stream shared by torch and the library
     torch.cuda.set_stream(stream)
     idx.set_stream(stream.cuda_stream)
@@ -300,9 +300,7 @@ def main():
             idx.search_dev(k, queries, D, L)
         else:
             idx.search_partial_dev(k, queries, pD, pS, pL)
-            dist.all_gather_into_tensor(gD, pD)
-            dist.all_gather_into_tensor(gS, pS)
-            dist.all_gather_into_tensor(gL, pL)
+            sharding.gather_partials(dist, pD, pS, pL, gD, gS, gL)
             idx.merge_partials_dev(k, nq, world, gD, gS, gL, D, L)
 
     flush = torch.empty(256 << 20, dtype=torch.uint8, device=dev)
@@ -399,9 +397,7 @@ def main():
         def e2e_step():
             qd.copy_(qh, non_blocking=True)
             idx.search_partial_dev(k, qd, pD, pS, pL)
-            dist.all_gather_into_tensor(gD, pD)
-            dist.all_gather_into_tensor(gS, pS)
-            dist.all_gather_into_tensor(gL, pL)
+            sharding.gather_partials(dist, pD, pS, pL, gD, gS, gL)
             idx.merge_partials_dev(k, nq, world, gD, gS, gL, D, L)
             Dh.copy_(D, non_blocking=True)
             Lh.copy_(L, non_blocking=True)
