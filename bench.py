@@ -294,14 +294,22 @@ def main():
         gD = torch.empty(world, nq, k, dtype=torch.float32, device=dev)
         gS = torch.empty(world, nq, k, dtype=torch.int32, device=dev)
         gL = torch.empty(world, nq, k, dtype=torch.int64, device=dev)
+        # query-parallel preparation: each rank builds the work tables of nq/world queries, records are all-gathered
+        qb0, qe0, per = sharding.query_slice(rank, world, nq)
+        tables = torch.empty(world * per, idx.tables_bytes(), dtype=torch.uint8, device=dev)
+
+    def sharded_search(q_dev):
+        idx.prepare_dev(q_dev, qb0, qe0, tables)
+        sharding.gather_tables(dist, tables, rank, per)
+        idx.scan_tables_dev(k, q_dev, tables, pD, pS, pL)
+        sharding.gather_partials(dist, pD, pS, pL, gD, gS, gL)
+        idx.merge_partials_dev(k, nq, world, gD, gS, gL, D, L)
 
     def step():
         if world == 1:
             idx.search_dev(k, queries, D, L)
         else:
-            idx.search_partial_dev(k, queries, pD, pS, pL)
-            sharding.gather_partials(dist, pD, pS, pL, gD, gS, gL)
-            idx.merge_partials_dev(k, nq, world, gD, gS, gL, D, L)
+            sharded_search(queries)
 
     flush = torch.empty(256 << 20, dtype=torch.uint8, device=dev)
     for _ in range(max(args.warmup, 3)):
@@ -343,12 +351,16 @@ def main():
         if world == 1:
             idx.search_dev(k, queries, D, L)
         else:
-            idx.search_partial_dev(k, queries, pD, pS, pL)
+            sharded_search(queries)
     torch.cuda.synchronize()
     st2 = idx.stats()
     idx.set_timing(False)
     n_t = max(1, int(st2.scan_launches))
-    scan_ms, coarse_ms, prep_ms = st2.scan_ms / n_t, st2.coarse_ms / n_t, st2.prep_ms / n_t
+    n_p = max(1, int(st2.prep_launches))
+    scan_ms, coarse_ms, prep_ms = st2.scan_ms / n_t, st2.coarse_ms / n_p, st2.prep_ms / n_p
+    gemm_ms, g1_ms, lut_ms = st2.gemm_ms / n_p, st2.g1_ms / n_p, st2.lut_ms / n_t
+    scan_kernel_ms = scan_ms - lut_ms
+    nq_prep = (qe0 - qb0) if world > 1 else nq      # queries this rank prepares per step
     code_bytes = w["M"] + 1
     peaks = {}
     try:
@@ -357,19 +369,48 @@ def main():
         pass
     hbm_peak = float(peaks.get("hbm_gbs", 6650.0))
     tf_peak = float(peaks.get("bf16_tflops_sustained", 1400.0))
-    scan_gbs = (st2.scanned_codes / 3.0) * code_bytes / (scan_ms * 1e-3) / 1e9 if scan_ms > 0 else 0.0
-    coarse_tf = 2.0 * w["nc"] * w["d"] * nq / (coarse_ms * 1e-3) / 1e12 if coarse_ms > 0 else 0.0
-    stages = {"coarse_ms": coarse_ms, "prep_ms": prep_ms, "scan_ms": scan_ms,
+    peak_src = "MEASURED_PEAKS.json" if peaks else "fallback of B200_PROFILING.md (6650 GB/s, 1400 TFLOP/s)"
+    # code_size + 1 bytes per code of the (sub-)lists the reference rule visits; this rank owns
+    # ~1/world of them.  The kernel streams whole lists (pruned sub-groups included): reported as "streamed".
+    scan_bytes = st2.scanned_codes / 3.0 / world * code_bytes
+    scan_gbs = scan_bytes / (scan_kernel_ms * 1e-3) / 1e9 if scan_kernel_ms > 0 else 0.0
+    streamed_gbs = st2.walked_codes / 3.0 / world * code_bytes / (scan_kernel_ms * 1e-3) / 1e9 if scan_kernel_ms > 0 else 0.0
+    gemm_flop = 2.0 * w["nc"] * w["d"] * nq_prep
+    coarse_tf = gemm_flop / (gemm_ms * 1e-3) / 1e12 if gemm_ms > 0 else 0.0
+    # K-G1: d*4 bytes per DISTINCT neighbour-centroid row gathered + the two [nprobe][nsubc] outputs per query
+    g1_bytes = (st2.g1_rows / 3.0) * w["d"] * 4 + nq_prep * w["nprobe"] * max(w["nsubc"], 0) * 8
+    g1_gbs = g1_bytes / (g1_ms * 1e-3) / 1e9 if g1_ms > 0 else 0.0
+    stages = {"coarse_ms": coarse_ms, "prep_ms": prep_ms, "scan_ms": scan_ms, "gemm_kernel_ms": gemm_ms,
+              "g1_kernel_ms": g1_ms, "lut_kernel_ms": lut_ms, "scan_kernel_ms": scan_kernel_ms,
               "scan_GBps_algorithmic": scan_gbs, "coarse_TFLOPs_algorithmic": coarse_tf,
+              "g1_distinct_rows_per_query": st2.g1_rows / 3.0 / max(1, nq_prep),
               "scanned_codes_per_query": st2.scanned_codes / 3.0 / nq, "walked_codes_per_query": st2.walked_codes / 3.0 / nq}
-    # roofline of the ADC scan kernel (the kernel BASELINE.json's metric names); stage shares in `stages`
-    roofline = {"kernel": "scan_kernel (K-L1+K-S2)", "bound": "hbm", "achieved": scan_gbs, "peak": hbm_peak,
-                "unit": "GB/s", "frac": scan_gbs / hbm_peak, "traffic": None,
-                "peak_source": "MEASURED_PEAKS.json hbm_gbs" if peaks else "fallback 6650 GB/s",
-                "algorithmic_bytes_per_code": code_bytes,
-                "dominant_stage": max(("coarse", coarse_ms), ("prep", prep_ms), ("scan", scan_ms), key=lambda t: t[1])[0],
-                "coarse": {"bound": "tensor", "achieved": coarse_tf, "peak": tf_peak, "unit": "TFLOP/s",
-                           "frac": coarse_tf / tf_peak}}
+    # per-launch DRAM traffic of each kernel from the committed `ncu --set full` capture (C2, one GPU)
+    traffic = {}
+    try:
+        traffic = json.load(open(os.path.join(ROOT, "profiles", "r01_ncu_traffic.json"))).get(args.workload, {})
+    except Exception:
+        pass
+    rl = {
+        "scan_kernel": {"kernel": "scan_kernel (K-S1/K-S2)", "bound": "hbm", "achieved": scan_gbs, "peak": hbm_peak,
+                        "unit": "GB/s", "frac": scan_gbs / hbm_peak, "ms": scan_kernel_ms,
+                        "algorithmic": "%d B per code of the sub-lists the reference rule scans" % code_bytes,
+                        "streamed_GBps": streamed_gbs,
+                        "traffic": traffic.get("scan_kernel") if world == 1 else None},
+        "group_g1_kernel": {"kernel": "group_g1_kernel (K-G1)", "bound": "hbm", "achieved": g1_gbs, "peak": hbm_peak,
+                            "unit": "GB/s", "frac": g1_gbs / hbm_peak, "ms": g1_ms,
+                            "algorithmic": "d*4 B per distinct neighbour row (mostly L2 hits: the centroid table is "
+                                           "25 MB) + 8 B per (probe, sub-group) written",
+                            "traffic": traffic.get("group_g1_kernel") if world == 1 else None},
+        "coarse_tc_kernel": {"kernel": "coarse_tc_kernel (K-A2 GEMM)", "bound": "tensor", "achieved": coarse_tf,
+                             "peak": tf_peak, "unit": "TFLOP/s", "frac": coarse_tf / tf_peak, "ms": gemm_ms,
+                             "algorithmic": "2*nc*d FLOP per query (the fp16 hi/lo split issues 3x that)",
+                             "traffic": traffic.get("coarse_tc_kernel") if world == 1 else None},
+    }
+    dom = max(rl.values(), key=lambda r: r["ms"])
+    roofline = dict(dom)
+    roofline["peak_source"] = peak_src
+    roofline["others"] = {kk: vv for kk, vv in rl.items() if vv is not dom}
 
     # e2e: the C-ABI call with HOST buffers (H2D of the queries + D2H of distances and labels inside)
     e2e = None
@@ -396,9 +437,7 @@ def main():
 
         def e2e_step():
             qd.copy_(qh, non_blocking=True)
-            idx.search_partial_dev(k, qd, pD, pS, pL)
-            sharding.gather_partials(dist, pD, pS, pL, gD, gS, gL)
-            idx.merge_partials_dev(k, nq, world, gD, gS, gL, D, L)
+            sharded_search(qd)
             Dh.copy_(D, non_blocking=True)
             Lh.copy_(L, non_blocking=True)
             torch.cuda.synchronize()

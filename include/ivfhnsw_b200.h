@@ -152,6 +152,16 @@ int ivfhnsw_b200_search_partial_dev(ivfhnsw_b200_t *h, size_t nq, size_t k, cons
 int ivfhnsw_b200_merge_partials_dev(ivfhnsw_b200_t *h, size_t nq, size_t k, size_t nparts,
                                     const float *part_d_dev, const uint32_t *part_seq_dev,
                                     const int64_t *part_labels_dev, float *distances_dev, int64_t *labels_dev);
+/* Two-stage form of search_partial_dev for query-parallel preparation: the work tables
+ * (coarse probes, Grouping thresholds and sub-group bases, max_codes cut) do not depend on the shard, so each
+ * rank prepares a slice [q_begin, q_end) of the nq queries into records q_begin.. of tables_dev
+ * (nq * tables_bytes, one contiguous record per query), the ranks all-gather the records, and every rank
+ * scans its own lists for all queries. */
+int ivfhnsw_b200_tables_bytes(ivfhnsw_b200_t *h, size_t *bytes_per_query);
+int ivfhnsw_b200_prepare_dev(ivfhnsw_b200_t *h, size_t nq, const float *x_dev, size_t q_begin, size_t q_end,
+                             void *tables_dev);
+int ivfhnsw_b200_scan_tables_dev(ivfhnsw_b200_t *h, size_t nq, size_t k, const float *x_dev, const void *tables_dev,
+                                 float *part_d_dev, uint32_t *part_seq_dev, int64_t *part_labels_dev);
 int ivfhnsw_b200_sync(ivfhnsw_b200_t *h);
 /* run on a caller-owned CUDA stream (cudaStream_t, e.g. torch's current stream); NULL = back to a private one.
  * STREAM ORDERING: every *_dev entry point only ENQUEUES work on the handle's stream.  Device buffers
@@ -171,6 +181,11 @@ typedef struct ivfhnsw_b200_stats {
     double prep_ms;             /* ... in work-list / sub-centroid kernels                      */
     uint64_t scan_launches;     /* number of scan-kernel launches included in scan_ms           */
     uint64_t coarse_flops;      /* 2*nc*d per query/vector pushed through the coarse GEMM       */
+    double gemm_ms;             /* ... of coarse_ms, the tensor-core GEMM kernel alone          */
+    double g1_ms;               /* ... of prep_ms, the sub-centroid distance kernel (K-G1)      */
+    double lut_ms;              /* ... of scan_ms, the lookup-table kernel (K-L1)               */
+    uint64_t g1_rows;           /* distinct neighbour-centroid rows K-G1 gathered               */
+    uint64_t prep_launches;     /* number of prep batches included in coarse_ms / prep_ms       */
 } ivfhnsw_b200_stats_t;
 /* timing != 0 brackets each stage with CUDA events on the handle's stream (adds a sync per call) */
 int ivfhnsw_b200_set_timing(ivfhnsw_b200_t *h, int timing);

@@ -41,7 +41,9 @@ def build_library(force=False):
 class Stats(C.Structure):
     _fields_ = [("kernel_launches", C.c_uint64), ("scanned_codes", C.c_uint64), ("walked_codes", C.c_uint64),
                 ("queries", C.c_uint64), ("scan_ms", C.c_double), ("coarse_ms", C.c_double),
-                ("prep_ms", C.c_double), ("scan_launches", C.c_uint64), ("coarse_flops", C.c_uint64)]
+                ("prep_ms", C.c_double), ("scan_launches", C.c_uint64), ("coarse_flops", C.c_uint64),
+                ("gemm_ms", C.c_double), ("g1_ms", C.c_double), ("lut_ms", C.c_double), ("g1_rows", C.c_uint64),
+                ("prep_launches", C.c_uint64)]
 
 
 _lib = None
@@ -92,6 +94,9 @@ def lib():
         "ivfhnsw_b200_coarse_dev": ([H, sz, vp, sz, vp, vp], C.c_int),
         "ivfhnsw_b200_search_partial_dev": ([H, sz, sz, vp, vp, vp, vp, vp, vp], C.c_int),
         "ivfhnsw_b200_merge_partials_dev": ([H, sz, sz, sz, vp, vp, vp, vp, vp], C.c_int),
+        "ivfhnsw_b200_tables_bytes": ([H, C.POINTER(C.c_size_t)], C.c_int),
+        "ivfhnsw_b200_prepare_dev": ([H, sz, vp, sz, sz, vp], C.c_int),
+        "ivfhnsw_b200_scan_tables_dev": ([H, sz, sz, vp, vp, vp, vp, vp], C.c_int),
         "ivfhnsw_b200_sync": ([H], C.c_int),
         "ivfhnsw_b200_set_stream": ([H, vp], C.c_int),
         "ivfhnsw_b200_set_timing": ([H, C.c_int], C.c_int),
@@ -516,6 +521,27 @@ class IndexIVF_HNSW:
             self._ck(self._L.ivfhnsw_b200_search_partial_dev(self._h, x_dev.shape[0], k, _ptr(x_dev), _ptr(cd),
                                                              _ptr(ci), _ptr(part_d), _ptr(part_seq),
                                                              _ptr(part_labels)))
+
+    def tables_bytes(self):
+        """Bytes of one per-query work-table record at the current nprobe (see ivfhnsw_b200_prepare_dev)."""
+        self._push_params()
+        n = C.c_size_t()
+        self._ck(self._L.ivfhnsw_b200_tables_bytes(self._h, C.byref(n)))
+        return int(n.value)
+
+    def prepare_dev(self, x_dev, q_begin, q_end, tables_dev):
+        """Coarse probes + work tables of queries [q_begin, q_end) into their records of tables_dev (uint8 [nq][bytes])."""
+        self._push_params()
+        with self._ordered():
+            self._ck(self._L.ivfhnsw_b200_prepare_dev(self._h, x_dev.shape[0], _ptr(x_dev), q_begin, q_end,
+                                                      _ptr(tables_dev)))
+
+    def scan_tables_dev(self, k, x_dev, tables_dev, part_d, part_seq, part_labels):
+        """Scan of this shard's lists for all queries, driven by (gathered) records."""
+        self._push_params()
+        with self._ordered():
+            self._ck(self._L.ivfhnsw_b200_scan_tables_dev(self._h, x_dev.shape[0], k, _ptr(x_dev), _ptr(tables_dev),
+                                                          _ptr(part_d), _ptr(part_seq), _ptr(part_labels)))
 
     def merge_partials_dev(self, k, nq, nparts, part_d, part_seq, part_labels, D_dev, L_dev):
         with self._ordered():

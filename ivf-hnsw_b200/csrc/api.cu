@@ -128,7 +128,7 @@ int ivfhnsw_b200_create(ivfhnsw_b200_t **out, size_t d, size_t nc, size_t code_s
                        prop.minor);
     CU(cudaSetDevice(device));
     CU(cudaStreamCreateWithFlags(&h->stream, cudaStreamNonBlocking));
-    for (int i = 0; i < 4; i++) CU(cudaEventCreate(&h->ev[i]));
+    for (int i = 0; i < 8; i++) CU(cudaEventCreate(&h->ev[i]));
     CU(h->counters.ensure(64));
     CU(cudaMemsetAsync(h->counters.p, 0, 64, h->stream));
     CU(h->centroid_norms.ensure(nc * 4));
@@ -155,7 +155,7 @@ void ivfhnsw_b200_destroy(ivfhnsw_b200_t *h)
                       &h->w_sub_base, &h->w_qsd, &h->w_part, &h->w_lut, &h->w_coarse, &h->w_xf16, &h->w_out_d, &h->w_out_l,
                       &h->w_a, &h->w_b, &h->w_c, &h->w_d2, &h->w_e, &h->w_f, &h->w_cub, &h->w_small, &h->counters};
     for (DevBuf *b : bufs) b->release();
-    for (int i = 0; i < 4; i++)
+    for (int i = 0; i < 8; i++)
         if (h->ev[i]) cudaEventDestroy(h->ev[i]);
     if (h->stream && h->own_stream) cudaStreamDestroy(h->stream);
     delete h;
@@ -360,9 +360,17 @@ int ivfb200_coarse_dev(ivfhnsw_b200_t *h, size_t nq, const float *xq, size_t npr
         W.cand_cap = cand_cap;
         // exclude_self needs global row ids: only used with q0 == 0-based centroid batches
         const float *cents = h->centroids.as<float>();
+        if (h->timing) CU(cudaEventRecord(h->ev[6], h->stream));
         CU(launch_coarse(h->stream, LAUNCHES, impl, (int)nb, (int)h->nc, (int)h->d, (int)nprobe, slack,
                          xq + q0 * h->d, cents, h->cnorm_gemm.as<float>(), S, W,
-                         exclude_self ? (int)q0 : -1, out_d + q0 * nprobe, out_i + q0 * nprobe));
+                         exclude_self ? (int)q0 : -1, out_d + q0 * nprobe, out_i + q0 * nprobe,
+                         h->timing ? h->ev[7] : nullptr));
+        if (h->timing) {
+            CU(cudaStreamSynchronize(h->stream));
+            float ms = 0;
+            CU(cudaEventElapsedTime(&ms, h->ev[6], h->ev[7]));
+            h->stats.gemm_ms += ms;
+        }
     }
     h->stats.coarse_flops += (uint64_t)2 * h->nc * h->d * nq;
     return 0;
@@ -847,48 +855,9 @@ int ivfhnsw_b200_export_lists(ivfhnsw_b200_t *h, int64_t *list_off, uint32_t *id
 // ------------------------------------------------------------------------------------ search
 static size_t align256(size_t x) { return (x + 255) & ~(size_t)255; }
 
-static int search_core(ivfhnsw_b200_t *h, size_t nq, size_t k, const float *x_dev, const float *cd_dev,
-                       const uint32_t *ci_dev, float *out_d, int64_t *out_l, uint32_t *out_seq = nullptr)
+static DeviceLists device_lists(ivfhnsw_b200_t *h)
 {
-    if (!h->have_lists || h->st_dirty) return h->fail(IVFHNSW_B200_ESTATE, "lists not built: call finalize()/read() first");
-    if (!h->have_pq || !h->have_norm) return h->fail(IVFHNSW_B200_ESTATE, "PQ codebooks not set");
-    if (!h->have_centroids) return h->fail(IVFHNSW_B200_ESTATE, "centroids not set");
-    if (h->do_opq && !h->have_opq) return h->fail(IVFHNSW_B200_ESTATE, "do_opq set but no OPQ matrix");
-    if (k == 0 || k > 2048) return h->fail(IVFHNSW_B200_EINVAL, "k %zu out of range [1, 2048]", k);
-    if (nq == 0) return 0;
-    const int d = (int)h->d, M = (int)h->M, nprobe = (int)h->nprobe, nsubc = (int)h->nsubc;
-    const bool grouping = nsubc > 0;
-    cudaStream_t st = h->stream;
-    const size_t smem = scan_smem_bytes(M, nprobe, (int)k, nsubc);
-    if (smem > 227 * 1024) return h->fail(IVFHNSW_B200_EINVAL, "nprobe/k too large for the scan kernel (%zu B smem)", smem);
-
-    // per-query workspace and batch size
-    const size_t seg_q = align256((size_t)(5 * nprobe + 1) * 4 + 16);
-    const size_t sub_q = grouping ? (size_t)nprobe * nsubc * 4 : 0;
-    size_t qb = h->query_batch > 0 ? (size_t)h->query_batch : 16384;
-    const size_t per_q = seg_q + 2 * sub_q + 32 * k * 12 + (size_t)d * 4 + (size_t)nprobe * 8 + (size_t)1024 * M;
-    qb = std::min(qb, std::max<size_t>(64, ((size_t)1 << 31) / per_q));
-    qb = std::min(qb, nq);
-    int nsplit = (int)h->scan_split;
-    if (nsplit <= 0) {
-        const size_t target = 148 * 6;
-        nsplit = (int)std::min<size_t>(32, (target + std::min(qb, nq) - 1) / std::min(qb, nq));
-    }
-    nsplit = std::max(1, std::min(nsplit, 32));
-
-    CU(h->w_seg.ensure(qb * ((size_t)(5 * nprobe + 1) * 4) + qb * 12 + 1024));
-    if (grouping) {
-        CU(h->w_sub_base.ensure(qb * sub_q + 256));
-        CU(h->w_qsd.ensure(qb * sub_q + 256));
-    }
-    if (nsplit > 1) CU(h->w_part.ensure(qb * nsplit * k * 12 + 256));
-    CU(h->w_lut.ensure(qb * 256 * M * 4 + 256));
-    if (!cd_dev) {
-        CU(h->w_cd.ensure(qb * nprobe * 4));
-        CU(h->w_ci.ensure(qb * nprobe * 4));
-    }
-    if (h->do_opq) CU(h->w_xrot.ensure(qb * d * 4));
-
+    const bool grouping = h->nsubc > 0;
     DeviceLists L;
     L.list_size = h->list_size.as<uint32_t>(); L.list_slot = h->list_slot.as<uint32_t>();
     L.codes = h->codes.as<uint8_t>(); L.norm_codes = h->norm_codes.as<uint8_t>();
@@ -896,26 +865,62 @@ static int search_core(ivfhnsw_b200_t *h, size_t nq, size_t k, const float *x_de
     L.nn_idx = h->nn_idx.as<uint32_t>(); L.sub_sizes = h->sub_sizes.as<uint32_t>();
     L.alphas = h->alphas.as<float>(); L.icd = h->icd.as<float>();
     L.centroid_norms = h->centroid_norms.as<float>(); L.centroids = h->centroids.as<float>();
+    return L;
+}
 
-    SegTables T;
-    {
-        uint8_t *p = h->w_seg.as<uint8_t>();
-        T.slot = reinterpret_cast<uint32_t *>(p); p += qb * nprobe * 4;
-        T.n = reinterpret_cast<uint32_t *>(p); p += qb * nprobe * 4;
-        T.base = reinterpret_cast<float *>(p); p += qb * nprobe * 4;
-        T.seq = reinterpret_cast<uint32_t *>(p); p += qb * nprobe * 4;
-        T.piece_off = reinterpret_cast<uint32_t *>(p); p += qb * (nprobe + 1) * 4;
-        T.threshold = reinterpret_cast<float *>(p); p += qb * 4;
-        T.nscanned = reinterpret_cast<uint32_t *>(p); p += qb * 4;
-        T.nwalked = reinterpret_cast<uint32_t *>(p); p += qb * 4;
-        T.sub_base = grouping ? h->w_sub_base.as<float>() : nullptr;
-        T.qsd = grouping ? h->w_qsd.as<float>() : nullptr;
+static int search_checks(ivfhnsw_b200_t *h, size_t k)
+{
+    if (!h->have_lists || h->st_dirty) return h->fail(IVFHNSW_B200_ESTATE, "lists not built: call finalize()/read() first");
+    if (!h->have_pq || !h->have_norm) return h->fail(IVFHNSW_B200_ESTATE, "PQ codebooks not set");
+    if (!h->have_centroids) return h->fail(IVFHNSW_B200_ESTATE, "centroids not set");
+    if (h->do_opq && !h->have_opq) return h->fail(IVFHNSW_B200_ESTATE, "do_opq set but no OPQ matrix");
+    if (k == 0 || k > 2048) return h->fail(IVFHNSW_B200_EINVAL, "k %zu out of range [1, 2048]", k);
+    const size_t smem = scan_smem_bytes((int)h->M, (int)h->nprobe, (int)k, (int)h->nsubc);
+    if (smem > 227 * 1024) return h->fail(IVFHNSW_B200_EINVAL, "nprobe/k too large for the scan kernel (%zu B smem)", smem);
+    return 0;
+}
+
+static size_t query_batch(const ivfhnsw_b200_t *h, size_t nq, size_t k)
+{
+    const size_t rec = seg_record_words((int)h->nprobe, (int)h->nsubc) * 4;
+    const size_t per_q = 2 * rec + 32 * k * 12 + h->d * 8 + h->nprobe * 8 + (size_t)1024 * h->M;
+    size_t qb = h->query_batch > 0 ? (size_t)h->query_batch : 16384;
+    qb = std::min(qb, std::max<size_t>(64, ((size_t)1 << 31) / per_q));
+    return std::max<size_t>(1, std::min(qb, nq));
+}
+
+// Stage 1 of a search: OPQ rotation, coarse probes (unless given) and the work tables of queries
+// [q_begin, q_end) of the batch x_dev[nq][d], written as records q_begin.. of `tables` (kernels.h SegTables).
+// The records do not depend on the shard.
+static int prepare_core(ivfhnsw_b200_t *h, size_t q_begin, size_t q_end, const float *x_dev, const float *cd_dev,
+                        const uint32_t *ci_dev, uint32_t *tables)
+{
+    const int d = (int)h->d, nprobe = (int)h->nprobe, nsubc = (int)h->nsubc;
+    const bool grouping = nsubc > 0;
+    cudaStream_t st = h->stream;
+    if (q_end <= q_begin) return 0;
+    const size_t nq = q_end - q_begin;
+    const size_t qb = query_batch(h, nq, 10);
+    const size_t stride = seg_record_words(nprobe, nsubc);
+    CU(h->w_seg.ensure(qb * 12 + 1024));
+    if (grouping) CU(h->w_qsd.ensure(qb * (size_t)nprobe * nsubc * 4 + 256));
+    if (!cd_dev) {
+        CU(h->w_cd.ensure(qb * nprobe * 4));
+        CU(h->w_ci.ensure(qb * nprobe * 4));
     }
+    if (h->do_opq) CU(h->w_xrot.ensure(qb * d * 4));
+    const DeviceLists L = device_lists(h);
     h->last_thr.clear();
     h->last_scanned.clear();
-
-    for (size_t q0 = 0; q0 < nq; q0 += qb) {
-        const int nb = (int)std::min(qb, nq - q0);
+    for (size_t q0 = q_begin; q0 < q_end; q0 += qb) {
+        const int nb = (int)std::min(qb, q_end - q0);
+        SegTables T;
+        T.rec = tables + q0 * stride;
+        T.stride = stride; T.nprobe = nprobe; T.nsubc = nsubc;
+        T.qsd = grouping ? h->w_qsd.as<float>() : nullptr;
+        T.threshold = h->w_seg.as<float>();
+        T.nscanned = reinterpret_cast<uint32_t *>(T.threshold + qb);
+        T.nwalked = T.nscanned + qb;
         const float *xq = x_dev + q0 * d;
         if (h->timing) CU(cudaEventRecord(h->ev[0], st));
         if (h->do_opq) {   // IndexIVF_HNSW.cpp:240
@@ -931,14 +936,65 @@ static int search_core(ivfhnsw_b200_t *h, size_t nq, size_t k, const float *x_de
         }
         if (h->timing) CU(cudaEventRecord(h->ev[1], st));
         if (grouping)
-            CU(launch_prep_grouping(st, LAUNCHES, nb, d, nprobe, nsubc, h->max_codes, h->do_pruning, xq, cd, ci, L,
-                                    h->c_begin, h->c_end, T));
+            CU(launch_prep_grouping(st, LAUNCHES, nb, d, nprobe, nsubc, h->max_codes, h->do_pruning, xq, cd, ci, L, T,
+                                    h->timing ? h->ev[4] : nullptr, h->counters.as<unsigned long long>() + 5));
         else
-            CU(launch_prep_adc(st, LAUNCHES, nb, nprobe, h->max_codes, cd, ci, L, h->c_begin, h->c_end, T));
+            CU(launch_prep_adc(st, LAUNCHES, nb, nprobe, h->max_codes, cd, ci, L, T));
         reduce_u32_kernel<<<grid_for(nb, 256, 64), 256, 0, st>>>(nb, T.nscanned, T.nwalked,
                                                                 h->counters.as<unsigned long long>());
         ++h->stats.kernel_launches;
+        if (h->timing) {
+            CU(cudaEventRecord(h->ev[2], st));
+            CU(cudaStreamSynchronize(st));
+            float ms = 0;
+            CU(cudaEventElapsedTime(&ms, h->ev[0], h->ev[1])); h->stats.coarse_ms += ms;
+            CU(cudaEventElapsedTime(&ms, h->ev[1], h->ev[2])); h->stats.prep_ms += ms;
+            if (grouping) { CU(cudaEventElapsedTime(&ms, h->ev[1], h->ev[4])); h->stats.g1_ms += ms; }
+            h->stats.prep_launches += 1;
+        }
+        if (q0 == q_begin && h->debug) {   // keep debug outputs of the first batch (copied lazily by last_thresholds)
+            h->last_thr.resize(nb);
+            h->last_scanned.resize(nb);
+            CU(cudaMemcpyAsync(h->last_thr.data(), T.threshold, (size_t)nb * 4, cudaMemcpyDeviceToHost, st));
+            CU(cudaMemcpyAsync(h->last_scanned.data(), T.nscanned, (size_t)nb * 4, cudaMemcpyDeviceToHost, st));
+            if (nq > qb) CU(cudaStreamSynchronize(st));  // the scratch is reused by the next batch
+        }
+    }
+    return 0;
+}
+
+// Stage 2: lookup tables + ADC scan of THIS GPU's lists for all nq queries, driven by the records.
+static int scan_core(ivfhnsw_b200_t *h, size_t nq, size_t k, const float *x_dev, const uint32_t *tables, float *out_d,
+                     int64_t *out_l, uint32_t *out_seq)
+{
+    if (nq == 0) return 0;
+    const int d = (int)h->d, M = (int)h->M, nprobe = (int)h->nprobe, nsubc = (int)h->nsubc;
+    const bool grouping = nsubc > 0;
+    cudaStream_t st = h->stream;
+    const size_t qb = query_batch(h, nq, k);
+    const size_t stride = seg_record_words(nprobe, nsubc);
+    int nsplit = (int)h->scan_split;
+    if (nsplit <= 0) {
+        const size_t target = 148 * 6;
+        nsplit = (int)std::min<size_t>(32, (target + qb - 1) / qb);
+    }
+    nsplit = std::max(1, std::min(nsplit, 32));
+    if (nsplit > 1) CU(h->w_part.ensure(qb * nsplit * k * 12 + 256));
+    CU(h->w_lut.ensure(qb * 256 * M * 4 + 256));
+    if (h->do_opq) CU(h->w_xrot.ensure(qb * d * 4));
+    const DeviceLists L = device_lists(h);
+    for (size_t q0 = 0; q0 < nq; q0 += qb) {
+        const int nb = (int)std::min(qb, nq - q0);
+        SegTables T;
+        T.rec = const_cast<uint32_t *>(tables) + q0 * stride;
+        T.stride = stride; T.nprobe = nprobe; T.nsubc = nsubc;
+        T.qsd = nullptr; T.threshold = nullptr; T.nscanned = nullptr; T.nwalked = nullptr;
+        const float *xq = x_dev + q0 * d;
         if (h->timing) CU(cudaEventRecord(h->ev[2], st));
+        if (h->do_opq) {
+            CU(launch_rotate(st, LAUNCHES, nb, d, h->opqA.as<float>(), false, xq, h->w_xrot.as<float>()));
+            xq = h->w_xrot.as<float>();
+        }
         float *pd = nullptr;
         uint32_t *ps = nullptr, *pl = nullptr;
         if (nsplit > 1) {
@@ -948,9 +1004,10 @@ static int search_core(ivfhnsw_b200_t *h, size_t nq, size_t k, const float *x_de
         }
         CU(launch_lut(st, LAUNCHES, M, nb, d, xq, h->pqc.as<float>(), h->w_lut.as<float>()));
         if (h->debug >= 2) CU(cudaStreamSynchronize(st));   // localise asynchronous kernel faults
+        if (h->timing) CU(cudaEventRecord(h->ev[5], st));
         CU(launch_scan(st, LAUNCHES, M, grouping, nb, d, nprobe, nsubc, (int)k, nsplit, h->w_lut.as<float>(),
-                       h->norm_table.as<float>(), L, T, pd, ps, pl, out_d + q0 * k, out_l + q0 * k,
-                       out_seq ? out_seq + q0 * k : nullptr));
+                       h->norm_table.as<float>(), L, T, (uint32_t)h->c_begin, (uint32_t)h->c_end, pd, ps, pl,
+                       out_d + q0 * k, out_l + q0 * k, out_seq ? out_seq + q0 * k : nullptr));
         if (h->debug >= 2) CU(cudaStreamSynchronize(st));
         if (h->timing) CU(cudaEventRecord(h->ev[3], st));
         if (nsplit > 1)
@@ -959,20 +1016,34 @@ static int search_core(ivfhnsw_b200_t *h, size_t nq, size_t k, const float *x_de
         if (h->timing) {
             CU(cudaStreamSynchronize(st));
             float ms = 0;
-            CU(cudaEventElapsedTime(&ms, h->ev[0], h->ev[1])); h->stats.coarse_ms += ms;
-            CU(cudaEventElapsedTime(&ms, h->ev[1], h->ev[2])); h->stats.prep_ms += ms;
             CU(cudaEventElapsedTime(&ms, h->ev[2], h->ev[3])); h->stats.scan_ms += ms;
+            CU(cudaEventElapsedTime(&ms, h->ev[2], h->ev[5])); h->stats.lut_ms += ms;
             h->stats.scan_launches += 1;
-        }
-        if (q0 == 0 && h->debug) {   // keep debug outputs of the first batch (copied lazily by last_thresholds)
-            h->last_thr.resize(nb);
-            h->last_scanned.resize(nb);
-            CU(cudaMemcpyAsync(h->last_thr.data(), T.threshold, (size_t)nb * 4, cudaMemcpyDeviceToHost, st));
-            CU(cudaMemcpyAsync(h->last_scanned.data(), T.nscanned, (size_t)nb * 4, cudaMemcpyDeviceToHost, st));
-            if (nq > qb) CU(cudaStreamSynchronize(st));  // T is reused by the next batch
         }
     }
     h->stats.queries += nq;
+    return 0;
+}
+
+static int search_core(ivfhnsw_b200_t *h, size_t nq, size_t k, const float *x_dev, const float *cd_dev,
+                       const uint32_t *ci_dev, float *out_d, int64_t *out_l, uint32_t *out_seq = nullptr)
+{
+    if (int r = search_checks(h, k)) return r;
+    if (nq == 0) return 0;
+    // batch-wise so that the internal record buffer stays bounded
+    const size_t qb = query_batch(h, nq, k);
+    const size_t stride = seg_record_words((int)h->nprobe, (int)h->nsubc);
+    CU(h->w_sub_base.ensure(qb * stride * 4 + 256));
+    uint32_t *tables = h->w_sub_base.as<uint32_t>();
+    for (size_t q0 = 0; q0 < nq; q0 += qb) {
+        const size_t nb = std::min(qb, nq - q0);
+        if (int r = prepare_core(h, 0, nb, x_dev + q0 * h->d, cd_dev ? cd_dev + q0 * h->nprobe : nullptr,
+                                 ci_dev ? ci_dev + q0 * h->nprobe : nullptr, tables))
+            return r;
+        if (int r = scan_core(h, nb, k, x_dev + q0 * h->d, tables, out_d + q0 * k, out_l + q0 * k,
+                              out_seq ? out_seq + q0 * k : nullptr))
+            return r;
+    }
     return 0;
 }
 
@@ -993,6 +1064,26 @@ int ivfhnsw_b200_search_partial_dev(ivfhnsw_b200_t *h, size_t nq, size_t k, cons
 {
     if (bind(h)) return IVFHNSW_B200_ECUDA;
     return search_core(h, nq, k, x_dev, cd_dev, ci_dev, part_d, part_labels, part_seq);
+}
+int ivfhnsw_b200_tables_bytes(ivfhnsw_b200_t *h, size_t *bytes_per_query)
+{
+    *bytes_per_query = seg_record_words((int)h->nprobe, (int)h->nsubc) * 4;
+    return 0;
+}
+int ivfhnsw_b200_prepare_dev(ivfhnsw_b200_t *h, size_t nq, const float *x_dev, size_t q_begin, size_t q_end,
+                             void *tables_dev)
+{
+    if (bind(h)) return IVFHNSW_B200_ECUDA;
+    if (int r = search_checks(h, 1)) return r;
+    if (q_begin > q_end || q_end > nq) return h->fail(IVFHNSW_B200_EINVAL, "query slice [%zu, %zu) outside [0, %zu)", q_begin, q_end, nq);
+    return prepare_core(h, q_begin, q_end, x_dev, nullptr, nullptr, reinterpret_cast<uint32_t *>(tables_dev));
+}
+int ivfhnsw_b200_scan_tables_dev(ivfhnsw_b200_t *h, size_t nq, size_t k, const float *x_dev, const void *tables_dev,
+                                 float *part_d, uint32_t *part_seq, int64_t *part_labels)
+{
+    if (bind(h)) return IVFHNSW_B200_ECUDA;
+    if (int r = search_checks(h, k)) return r;
+    return scan_core(h, nq, k, x_dev, reinterpret_cast<const uint32_t *>(tables_dev), part_d, part_labels, part_seq);
 }
 int ivfhnsw_b200_merge_partials_dev(ivfhnsw_b200_t *h, size_t nq, size_t k, size_t nparts, const float *part_d,
                                     const uint32_t *part_seq, const int64_t *part_labels, float *out_d,
@@ -1053,6 +1144,7 @@ int ivfhnsw_b200_get_stats(ivfhnsw_b200_t *h, ivfhnsw_b200_stats_t *out)
     CU(cudaMemcpy(c, h->counters.p, 64, cudaMemcpyDeviceToHost));
     h->stats.scanned_codes = c[0];
     h->stats.walked_codes = c[1];
+    h->stats.g1_rows = c[5];
     *out = h->stats;
     if (c[4] & 0xffffffffull)
         return h->fail(IVFHNSW_B200_ECUDA, "coarse select overflow flags 0x%llx (raise coarse_slack)", c[4] & 0xffffffffull);

@@ -266,7 +266,8 @@ cudaError_t launch_coarse_tc(cudaStream_t st, uint64_t *launches, int nq, int nc
 
 cudaError_t launch_coarse(cudaStream_t st, uint64_t *launches, int impl, int nq, int nc, int d, int nprobe,
                           int slack, const float *queries, const float *centroids, const float *cnorm_gemm,
-                          const TcSide &S, const CoarseWork &W, int self_off, float *out_d, uint32_t *out_i)
+                          const TcSide &S, const CoarseWork &W, int self_off, float *out_d, uint32_t *out_i,
+                          cudaEvent_t ev_after_gemm)
 {
     if (nq == 0) return cudaSuccess;
     const int ngroups = (nc + COARSE_GROUP - 1) / COARSE_GROUP;
@@ -283,6 +284,10 @@ cudaError_t launch_coarse(cudaStream_t st, uint64_t *launches, int impl, int nq,
                                                       W.grp_val, W.grp_idx);
         ++*launches;
         e = cudaGetLastError();
+        if (e != cudaSuccess) return e;
+    }
+    if (ev_after_gemm) {
+        e = cudaEventRecord(ev_after_gemm, st);
         if (e != cudaSuccess) return e;
     }
     int avail = nc - (self_off >= 0 ? 1 : 0);

@@ -27,28 +27,39 @@ struct DeviceLists {
     const float *centroids;      // [nc][d]  (search-time table, i.e. rotated when OPQ)
 };
 
-// per-query segment tables produced by the prep kernels, consumed by the scan kernel
+// Per-query work tables produced by the prep kernels, consumed by the scan kernel.  One contiguous RECORD
+// of `stride` 32-bit words per query so that a slice of queries is one contiguous block (multi-GPU: ranks
+// prepare disjoint query slices and all-gather the records).  Records do not depend on the shard: the scan
+// kernel keeps only the lists whose centroid id lies in its own range.
+//   [slot P][n P][base P][seq P][cid P][sub_base P*S]      P = nprobe, S = nsubc (0 for IVFADC)
 struct SegTables {
-    uint32_t *slot;       // [nq][nprobe]   first slot of the probed list
-    uint32_t *n;          // [nq][nprobe]   codes to walk (0 = skipped / empty / after cut-off / not owned)
-    float *base;          // [nq][nprobe]   term1 (IVFADC) -- Grouping uses sub_base instead
-    uint32_t *seq;        // [nq][nprobe]   scan-order number of the list's first code
-    uint32_t *piece_off;  // [nq][nprobe+1] exclusive prefix of ceil(n / SCAN_PIECE)
-    float *sub_base;      // [nq][nprobe][nsubc] term1+term2 per sub-group, +inf = pruned/empty (Grouping)
-    float *qsd;           // [nq][nprobe][nsubc] scratch: d(q, n_s), then query_subcentroid_dists
+    uint32_t *rec;        // [nq][stride]
+    size_t stride;        // words per record (multiple of 4)
+    int nprobe, nsubc;
+    float *qsd;           // [nq][nprobe][nsubc] scratch: pruning values (K-G1 -> K-G2/K-G3), not part of the record
     float *threshold;     // [nq]
-    uint32_t *nscanned;   // [nq] codes the reference rule scans
-    uint32_t *nwalked;    // [nq] codes the scan kernel streams
+    uint32_t *nscanned;   // [nq] codes the reference rule scans (all shards)
+    uint32_t *nwalked;    // [nq] codes the scan kernels stream (all shards)
+    __host__ __device__ uint32_t *slot(size_t q) const { return rec + q * stride; }                  // first slot of the list
+    __host__ __device__ uint32_t *n(size_t q) const { return rec + q * stride + nprobe; }             // codes to walk (0 = skipped)
+    __host__ __device__ float *base(size_t q) const { return reinterpret_cast<float *>(rec + q * stride + 2 * nprobe); }   // term1 (IVFADC)
+    __host__ __device__ uint32_t *seq(size_t q) const { return rec + q * stride + 3 * nprobe; }       // scan-order number of the first code
+    __host__ __device__ uint32_t *cid(size_t q) const { return rec + q * stride + 4 * nprobe; }       // centroid id (ownership test)
+    __host__ __device__ float *sub_base(size_t q) const { return reinterpret_cast<float *>(rec + q * stride + 5 * nprobe); }   // term1+term2 per sub-group, +inf = pruned/empty
 };
+static inline size_t seg_record_words(int nprobe, int nsubc)
+{
+    return ((size_t)5 * nprobe + (size_t)nprobe * nsubc + 3) & ~(size_t)3;
+}
 
 cudaError_t launch_prep_adc(cudaStream_t st, uint64_t *launches, int nq, int nprobe, uint64_t max_codes,
-                            const float *coarse_d, const uint32_t *coarse_i, const DeviceLists &L,
-                            uint32_t c_begin, uint32_t c_end, const SegTables &T);
+                            const float *coarse_d, const uint32_t *coarse_i, const DeviceLists &L, const SegTables &T);
 
 cudaError_t launch_prep_grouping(cudaStream_t st, uint64_t *launches, int nq, int d, int nprobe, int nsubc,
                                  uint64_t max_codes, bool do_pruning, const float *queries,
                                  const float *coarse_d, const uint32_t *coarse_i, const DeviceLists &L,
-                                 uint32_t c_begin, uint32_t c_end, const SegTables &T);
+                                 const SegTables &T, cudaEvent_t ev_after_g1 /* may be null */,
+                                 unsigned long long *rows_counter /* distinct neighbour rows, may be null */);
 
 size_t scan_smem_bytes(int M, int nprobe, int k, int nsubc);
 // partial outputs [nq][nsplit][k]; when nsplit == 1 the kernel writes the final (distances, labels) directly
@@ -57,8 +68,8 @@ cudaError_t launch_lut(cudaStream_t st, uint64_t *launches, int M, int nq, int d
                        const float *pqc, float *lutc);
 cudaError_t launch_scan(cudaStream_t st, uint64_t *launches, int M, bool grouping, int nq, int d, int nprobe,
                         int nsubc, int k, int nsplit, const float *lutc, const float *norm_table,
-                        const DeviceLists &L, const SegTables &T, float *part_d, uint32_t *part_seq,
-                        uint32_t *part_slot, float *out_d, int64_t *out_labels, uint32_t *out_seq);
+                        const DeviceLists &L, const SegTables &T, uint32_t c_begin, uint32_t c_end, float *part_d,
+                        uint32_t *part_seq, uint32_t *part_slot, float *out_d, int64_t *out_labels, uint32_t *out_seq);
 cudaError_t launch_merge(cudaStream_t st, uint64_t *launches, int nq, int k, int nsplit, const float *part_d,
                          const uint32_t *part_seq, const uint32_t *part_slot, const uint32_t *ids,
                          float *out_d, int64_t *out_labels, uint32_t *out_seq /* optional */);
@@ -106,7 +117,7 @@ cudaError_t launch_tc_prepare_centroids(cudaStream_t st, uint64_t *launches, siz
 cudaError_t launch_coarse(cudaStream_t st, uint64_t *launches, int impl, int nq, int nc, int d, int nprobe,
                           int slack, const float *queries, const float *centroids, const float *cnorm_gemm,
                           const TcSide &S, const CoarseWork &W, int self_off /* -1 = none */,
-                          float *out_d, uint32_t *out_i);
+                          float *out_d, uint32_t *out_i, cudaEvent_t ev_after_gemm = nullptr);
 
 // ----------------------------------------------------------------------------- indexing
 // residual rows: out[i] = x[i] - base_row(i); base_row = centroid[idx[i]] or, for Grouping,

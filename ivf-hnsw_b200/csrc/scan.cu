@@ -33,14 +33,13 @@ namespace ivfb200 {
 // lists before it sum to < max_codes.
 // =============================================================================================
 __global__ void prep_adc_kernel(int nq, int nprobe, uint64_t max_codes, const float *__restrict__ coarse_d,
-                                const uint32_t *__restrict__ coarse_i, DeviceLists L, uint32_t c_begin,
-                                uint32_t c_end, SegTables T)
+                                const uint32_t *__restrict__ coarse_i, DeviceLists L, SegTables T)
 {
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     const int q = blockIdx.x * (blockDim.x >> 5) + warp;
     if (q >= nq) return;
     uint64_t run = 0;
-    uint32_t run_pieces = 0, scanned = 0, walked = 0;
+    uint32_t scanned = 0;
     for (int base = 0; base < nprobe; base += 32) {
         const int i = base + lane;
         uint32_t c = 0, sz = 0;
@@ -58,47 +57,33 @@ __global__ void prep_adc_kernel(int nq, int nprobe, uint64_t max_codes, const fl
         }
         const uint64_t excl = run + incl - sz;
         const bool active = (i < nprobe) && sz > 0 && excl < max_codes;
-        const bool owned = c >= c_begin && c < c_end;
-        const uint32_t n = (active && owned) ? sz : 0u;
-        const uint32_t pieces = (n + SCAN_PIECE - 1) / SCAN_PIECE;
-        uint32_t incl_p = pieces;
-#pragma unroll
-        for (int off = 1; off < 32; off <<= 1) {
-            const uint32_t t = __shfl_up_sync(IVF_FULL_MASK, incl_p, off);
-            if (lane >= off) incl_p += t;
-        }
+        const uint32_t n = active ? sz : 0u;
         if (i < nprobe) {
-            const size_t o = (size_t)q * nprobe + i;
-            T.slot[o] = L.list_slot[c];
-            T.n[o] = n;
-            T.base[o] = cd - L.centroid_norms[c];
-            T.seq[o] = (uint32_t)excl;
-            T.piece_off[(size_t)q * (nprobe + 1) + i] = run_pieces + incl_p - pieces;
+            T.slot(q)[i] = L.list_slot[c];
+            T.n(q)[i] = n;
+            T.base(q)[i] = cd - L.centroid_norms[c];
+            T.seq(q)[i] = (uint32_t)excl;
+            T.cid(q)[i] = c;
         }
         run += __shfl_sync(IVF_FULL_MASK, incl, 31);
-        run_pieces += __shfl_sync(IVF_FULL_MASK, incl_p, 31);
         uint32_t s = n;
 #pragma unroll
         for (int off = 16; off > 0; off >>= 1) s += __shfl_xor_sync(IVF_FULL_MASK, s, off);
         scanned += s;
-        walked += s;
     }
     if (lane == 0) {
-        T.piece_off[(size_t)q * (nprobe + 1) + nprobe] = run_pieces;
         T.nscanned[q] = scanned;
-        T.nwalked[q] = walked;
+        T.nwalked[q] = scanned;
         T.threshold[q] = 0.f;
     }
 }
 
 cudaError_t launch_prep_adc(cudaStream_t st, uint64_t *launches, int nq, int nprobe, uint64_t max_codes,
-                            const float *coarse_d, const uint32_t *coarse_i, const DeviceLists &L,
-                            uint32_t c_begin, uint32_t c_end, const SegTables &T)
+                            const float *coarse_d, const uint32_t *coarse_i, const DeviceLists &L, const SegTables &T)
 {
     if (nq == 0) return cudaSuccess;
     const int wpb = 4;
-    prep_adc_kernel<<<(nq + wpb - 1) / wpb, wpb * 32, 0, st>>>(nq, nprobe, max_codes, coarse_d, coarse_i, L,
-                                                              c_begin, c_end, T);
+    prep_adc_kernel<<<(nq + wpb - 1) / wpb, wpb * 32, 0, st>>>(nq, nprobe, max_codes, coarse_d, coarse_i, L, T);
     ++*launches;
     return cudaGetLastError();
 }
@@ -214,7 +199,7 @@ __global__ void __launch_bounds__(G1_THREADS) group_g1_kernel(int d, int nprobe,
                                                               const float *__restrict__ queries,
                                                               const float *__restrict__ coarse_d,
                                                               const uint32_t *__restrict__ coarse_i, DeviceLists L,
-                                                              SegTables T)
+                                                              SegTables T, unsigned long long *rows_counter)
 {
     extern __shared__ __align__(16) uint8_t sm[];
     float *sq = reinterpret_cast<float *>(sm);                         // [d] (d % 4 == 0)
@@ -290,6 +275,7 @@ __global__ void __launch_bounds__(G1_THREADS) group_g1_kernel(int d, int nprobe,
     }
     __syncthreads();
     const int nwork = s_nwork;
+    if (tid == 0 && rows_counter) atomicAdd(rows_counter, (unsigned long long)nwork);
     for (int w = tid; w < nwork; w += G1_THREADS) {
         const int p = work[w];
         hv[p] = l2sqr16_thread(sq, L.centroids + (size_t)hk[p] * d, d);
@@ -344,7 +330,7 @@ __global__ void __launch_bounds__(G1_THREADS) group_g1_kernel(int d, int nprobe,
                 sb = __fadd_rn(term1, term2);
             }
             T.qsd[(size_t)q * npairs + e] = r;
-            T.sub_base[(size_t)q * npairs + e] = sb;
+            T.sub_base(q)[e] = sb;
         }
     }
 #pragma unroll
@@ -400,7 +386,7 @@ __global__ void __launch_bounds__(128) group_g2_kernel(int nq, int npairs, const
 __global__ void __launch_bounds__(G1_THREADS) group_g3_kernel(int nprobe, int nsubc, int sub_shift, uint64_t max_codes,
                                                               int do_pruning,
                                                               const uint32_t *__restrict__ coarse_i, DeviceLists L,
-                                                              uint32_t c_begin, uint32_t c_end, SegTables T)
+                                                              SegTables T)
 {
     extern __shared__ __align__(16) uint8_t sm[];
     uint32_t *s_c = reinterpret_cast<uint32_t *>(sm);     // [nprobe] centroid id
@@ -415,7 +401,7 @@ __global__ void __launch_bounds__(G1_THREADS) group_g3_kernel(int nprobe, int ns
     __syncthreads();
     const float threshold = do_pruning ? T.threshold[q] : 0.f;
     const float *rv = T.qsd + (size_t)q * npairs;
-    float *sb = T.sub_base + (size_t)q * npairs;
+    float *sb = T.sub_base(q);
     for (int e0 = 0; e0 < npairs; e0 += G1_THREADS * 4) {
         uint32_t ss[4];
         float r[4];
@@ -445,7 +431,7 @@ __global__ void __launch_bounds__(G1_THREADS) group_g3_kernel(int nprobe, int ns
     if (warp != 0) return;
     // ---- max_codes rule on the KEPT codes (:337,349) and segment tables
     uint64_t run_k = 0, run_w = 0;
-    uint32_t run_pieces = 0, scanned = 0, walked = 0;
+    uint32_t scanned = 0, walked = 0;
     for (int base = 0; base < nprobe; base += 32) {
         const int i = base + lane;
         uint32_t c = 0, sz = 0, kp = 0;
@@ -458,33 +444,24 @@ __global__ void __launch_bounds__(G1_THREADS) group_g3_kernel(int nprobe, int ns
         }
         const uint64_t excl_k = run_k + incl_k - kp;
         const bool active = (i < nprobe) && sz > 0 && excl_k < max_codes;
-        const bool owned = c >= c_begin && c < c_end;
-        const uint32_t wsz = active ? sz : 0u;  // walk order numbering is global (all shards)
+        const uint32_t wsz = active ? sz : 0u;  // walk order numbering covers every active list
         uint64_t incl_w = wsz;
 #pragma unroll
         for (int off = 1; off < 32; off <<= 1) {
             const uint64_t t = __shfl_up_sync(IVF_FULL_MASK, incl_w, off);
             if (lane >= off) incl_w += t;
         }
-        const uint32_t n = (active && owned && kp > 0) ? sz : 0u;
-        const uint32_t pieces = (n + SCAN_PIECE - 1) / SCAN_PIECE;
-        uint32_t incl_p = pieces;
-#pragma unroll
-        for (int off = 1; off < 32; off <<= 1) {
-            const uint32_t t = __shfl_up_sync(IVF_FULL_MASK, incl_p, off);
-            if (lane >= off) incl_p += t;
-        }
+        const uint32_t n = (active && kp > 0) ? sz : 0u;
         if (i < nprobe) {
-            T.slot[qo + i] = L.list_slot[c];
-            T.n[qo + i] = n;
-            T.base[qo + i] = 0.f;
-            T.seq[qo + i] = (uint32_t)(run_w + incl_w - wsz);
-            T.piece_off[(size_t)q * (nprobe + 1) + i] = run_pieces + incl_p - pieces;
+            T.slot(q)[i] = L.list_slot[c];
+            T.n(q)[i] = n;
+            T.base(q)[i] = 0.f;
+            T.seq(q)[i] = (uint32_t)(run_w + incl_w - wsz);
+            T.cid(q)[i] = c;
         }
         run_k += __shfl_sync(IVF_FULL_MASK, incl_k, 31);
         run_w += __shfl_sync(IVF_FULL_MASK, incl_w, 31);
-        run_pieces += __shfl_sync(IVF_FULL_MASK, incl_p, 31);
-        uint32_t a = (active && owned) ? kp : 0u, b = n;
+        uint32_t a = active ? kp : 0u, b = n;
 #pragma unroll
         for (int off = 16; off > 0; off >>= 1) {
             a += __shfl_xor_sync(IVF_FULL_MASK, a, off);
@@ -494,7 +471,6 @@ __global__ void __launch_bounds__(G1_THREADS) group_g3_kernel(int nprobe, int ns
         walked += b;
     }
     if (lane == 0) {
-        T.piece_off[(size_t)q * (nprobe + 1) + nprobe] = run_pieces;
         T.nscanned[q] = scanned;
         T.nwalked[q] = walked;
         if (!do_pruning) T.threshold[q] = 0.f;
@@ -504,7 +480,7 @@ __global__ void __launch_bounds__(G1_THREADS) group_g3_kernel(int nprobe, int ns
 cudaError_t launch_prep_grouping(cudaStream_t st, uint64_t *launches, int nq, int d, int nprobe, int nsubc,
                                  uint64_t max_codes, bool do_pruning, const float *queries,
                                  const float *coarse_d, const uint32_t *coarse_i, const DeviceLists &L,
-                                 uint32_t c_begin, uint32_t c_end, const SegTables &T)
+                                 const SegTables &T, cudaEvent_t ev_after_g1, unsigned long long *rows_counter)
 {
     if (nq == 0) return cudaSuccess;
     const int npairs = nprobe * nsubc;
@@ -519,10 +495,14 @@ cudaError_t launch_prep_grouping(cudaStream_t st, uint64_t *launches, int nq, in
     for (int b = 0; b < 16; b++)
         if ((1 << b) == nsubc) sub_shift = b;
     group_g1_kernel<<<nq, G1_THREADS, sm1, st>>>(d, nprobe, nsubc, sub_shift, ht, max_codes, do_pruning ? 1 : 0, queries,
-                                                coarse_d, coarse_i, L, T);
+                                                coarse_d, coarse_i, L, T, rows_counter);
     ++*launches;
     e = cudaGetLastError();
     if (e != cudaSuccess) return e;
+    if (ev_after_g1) {
+        e = cudaEventRecord(ev_after_g1, st);
+        if (e != cudaSuccess) return e;
+    }
     if (do_pruning) {
         group_g2_kernel<<<(nq + 31) / 32, 128, 0, st>>>(nq, npairs, T.qsd, T.nscanned, T.threshold);
         ++*launches;
@@ -530,8 +510,7 @@ cudaError_t launch_prep_grouping(cudaStream_t st, uint64_t *launches, int nq, in
         if (e != cudaSuccess) return e;
     }
     const size_t sm3 = (size_t)nprobe * 13 + 16;
-    group_g3_kernel<<<nq, G1_THREADS, sm3, st>>>(nprobe, nsubc, sub_shift, max_codes, do_pruning ? 1 : 0, coarse_i, L, c_begin,
-                                                c_end, T);
+    group_g3_kernel<<<nq, G1_THREADS, sm3, st>>>(nprobe, nsubc, sub_shift, max_codes, do_pruning ? 1 : 0, coarse_i, L, T);
     ++*launches;
     return cudaGetLastError();
 }
@@ -613,6 +592,7 @@ struct ScanArgs {
     const float *norm_table;  // [256]
     DeviceLists L;
     SegTables T;
+    uint32_t c_begin, c_end;  // centroid range whose lists this GPU owns
     float *part_d;            // [nq][nsplit][k]
     uint32_t *part_seq;
     uint32_t *part_slot;
@@ -822,16 +802,17 @@ __global__ void __launch_bounds__(SCAN_THREADS) scan_kernel(ScanArgs a)
     const int q = blockIdx.x / a.nsplit, split = blockIdx.x - q * a.nsplit;
     const int nprobe = a.nprobe, k = a.k;
 
-    // ---- stage the query's segment tables and initialise the top-k
+    // ---- stage the query's segment tables (keeping only the lists this GPU owns) and initialise the top-k
     {
-        const size_t o = (size_t)q * nprobe;
+        const uint32_t *r_slot = a.T.slot(q), *r_n = a.T.n(q), *r_seq = a.T.seq(q), *r_cid = a.T.cid(q);
+        const float *r_base = a.T.base(q);
         for (int i = tid; i < nprobe; i += SCAN_THREADS) {
-            s_slot[i] = a.T.slot[o + i];
-            s_n[i] = a.T.n[o + i];
-            s_base[i] = a.T.base[o + i];
-            s_seq[i] = a.T.seq[o + i];
+            const uint32_t c = r_cid[i];
+            s_slot[i] = r_slot[i];
+            s_n[i] = (c >= a.c_begin && c < a.c_end) ? r_n[i] : 0u;
+            s_base[i] = r_base[i];
+            s_seq[i] = r_seq[i];
         }
-        for (int i = tid; i <= nprobe; i += SCAN_THREADS) s_poff[i] = a.T.piece_off[(size_t)q * (nprobe + 1) + i];
         if (KPL == 0) {
             for (int e = tid; e < k; e += SCAN_THREADS) {
                 topk_d[e] = FLT_MAX;
@@ -847,6 +828,24 @@ __global__ void __launch_bounds__(SCAN_THREADS) scan_kernel(ScanArgs a)
             ctl->worst_d = FLT_MAX;
             ctl->thr_key = 0xffffffffu;
         }
+    }
+    __syncthreads();
+    // exclusive prefix of the pieces (ceil(n / SCAN_PIECE)) of the kept lists
+    if (warp == 0) {
+        uint32_t run = 0;
+        for (int b = 0; b < nprobe; b += 32) {
+            const int i = b + lane;
+            const uint32_t pieces = i < nprobe ? (s_n[i] + SCAN_PIECE - 1) / SCAN_PIECE : 0u;
+            uint32_t incl = pieces;
+#pragma unroll
+            for (int off = 1; off < 32; off <<= 1) {
+                const uint32_t t = __shfl_up_sync(IVF_FULL_MASK, incl, off);
+                if (lane >= off) incl += t;
+            }
+            if (i < nprobe) s_poff[i] = run + incl - pieces;
+            run += __shfl_sync(IVF_FULL_MASK, incl, 31);
+        }
+        if (lane == 0) s_poff[nprobe] = run;
     }
     __syncthreads();
     const int npieces = (int)s_poff[nprobe];
@@ -934,7 +933,7 @@ __global__ void __launch_bounds__(SCAN_THREADS) scan_kernel(ScanArgs a)
         float sb0 = 0.f, sb1 = 0.f;
         const bool sb_regs = a.nsubc <= 64;
         if (GROUPING) {
-            const float *sbg = a.T.sub_base + ((size_t)q * nprobe + seg) * a.nsubc;
+            const float *sbg = a.T.sub_base(q) + (size_t)seg * a.nsubc;
             if (sb_regs) {
                 sb0 = lane < a.nsubc ? __ldg(sbg + lane) : __int_as_float(0x7f800000);
                 sb1 = lane + 32 < a.nsubc ? __ldg(sbg + lane + 32) : __int_as_float(0x7f800000);
@@ -1129,14 +1128,14 @@ static cudaError_t launch_scan_k(cudaStream_t st, int nq, const ScanArgs &a)
 
 cudaError_t launch_scan(cudaStream_t st, uint64_t *launches, int M, bool grouping, int nq, int d, int nprobe,
                         int nsubc, int k, int nsplit, const float *lutc, const float *norm_table,
-                        const DeviceLists &L, const SegTables &T, float *part_d, uint32_t *part_seq,
-                        uint32_t *part_slot, float *out_d, int64_t *out_labels, uint32_t *out_seq)
+                        const DeviceLists &L, const SegTables &T, uint32_t c_begin, uint32_t c_end, float *part_d,
+                        uint32_t *part_seq, uint32_t *part_slot, float *out_d, int64_t *out_labels, uint32_t *out_seq)
 {
     if (nq == 0) return cudaSuccess;
     ScanArgs a;
     a.out_seq = out_seq;
     a.d = d; a.nprobe = nprobe; a.nsubc = grouping ? nsubc : 0; a.k = k; a.nsplit = nsplit;
-    a.lutc = lutc; a.norm_table = norm_table; a.L = L; a.T = T;
+    a.lutc = lutc; a.norm_table = norm_table; a.L = L; a.T = T; a.c_begin = c_begin; a.c_end = c_end;
     a.part_d = part_d; a.part_seq = part_seq; a.part_slot = part_slot; a.out_d = out_d; a.out_labels = out_labels;
     ++*launches;
 #define IVF_SCAN_CASE(MM)                                                              \

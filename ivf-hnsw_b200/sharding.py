@@ -17,3 +17,16 @@ def gather_partials(dist, part_d, part_seq, part_labels, out_d, out_seq, out_lab
     for out, part in ((out_d, part_d), (out_seq, part_seq), (out_labels, part_labels)):
         # concatenated along dim 0 == [world][nq][k] in memory (the flat form is what gloo accepts too)
         dist.all_gather_into_tensor(out.view(-1, *part.shape[1:]), part)
+
+
+def query_slice(rank, world, nq):
+    """Queries [begin, end) whose work tables rank `rank` prepares; `per` records per rank in the gathered buffer."""
+    per = (nq + world - 1) // world
+    begin = min(nq, rank * per)
+    return begin, min(nq, begin + per), per
+
+
+def gather_tables(dist, tables, rank, per):
+    """In-place all-gather of the per-query work-table records: `tables` is [world * per][record_bytes] and rank r
+    has filled rows [r * per, (r + 1) * per) (ivfhnsw_b200_prepare_dev); afterwards every rank holds all records."""
+    dist.all_gather_into_tensor(tables, tables[rank * per:(rank + 1) * per])
