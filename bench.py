@@ -73,7 +73,7 @@ def draw(w, torch, dev, means, n, seed):
     return x.contiguous()
 
 
-def build_index(w, torch, dev, log):
+def build_index(w, torch, dev, log, dist=None):
     """Everything on the GPU through the library's own entry points. Returns (index, queries_dev, gt0)."""
     P = pkg()
     t0 = time.time()
@@ -93,12 +93,27 @@ def build_index(w, torch, dev, log):
         sums = torch.zeros_like(cent).index_add_(0, lab.long(), learn)
         cnt = torch.zeros(w["nc"], device=dev).index_add_(0, lab.long(), torch.ones(w["nlearn"], device=dev))
         cent = torch.where(cnt[:, None] > 0, sums / cnt.clamp(min=1)[:, None], cent)
+    if dist is not None:
+        # every rank must hold the SAME index (in production they load one file): the Lloyd sums use float
+        # atomics, so take rank 0's centroids
+        dist.broadcast(cent, src=0)
     cent_h = cent.cpu().numpy()
     idx.build_quantizer(centroids=cent_h)
     log("centroids %.1fs" % (time.time() - t0))
     # train_pq on a random subset of the learn set (tests/test_ivfhnsw_sift1b.cpp:67-79)
     idx.do_opq = w["opq"]
     idx.train_pq(learn[:w["ntrain"]].cpu().numpy())
+    if dist is not None:   # same reason: the k-means accumulators are atomics
+        pqc = torch.from_numpy(np.ascontiguousarray(idx.pq_centroids, dtype=np.float32)).to(dev)
+        nrm = torch.from_numpy(np.ascontiguousarray(idx.norm_centroids, dtype=np.float32)).to(dev)
+        dist.broadcast(pqc, src=0)
+        dist.broadcast(nrm, src=0)
+        opq = None
+        if w["opq"]:
+            opq = torch.from_numpy(np.ascontiguousarray(idx.opq_matrix, dtype=np.float32)).to(dev)
+            dist.broadcast(opq, src=0)
+            opq = opq.cpu().numpy()
+        idx.set_pq(pqc.cpu().numpy(), nrm.cpu().numpy(), opq)
     log("train_pq %.1fs" % (time.time() - t0))
     del learn, lab, dist_tmp
     # base vectors: generated, assigned (K-A1) and added in 1M batches (tests/...:102,142-153)
@@ -241,7 +256,7 @@ def main():
     log = (lambda m: print("[bench r%d] %s" % (rank, m), file=sys.stderr, flush=True))
     P = pkg()
     sharding = importlib.import_module("ivf-hnsw_b200.sharding")
-    idx, queries, gt0, cent_h = build_index(w, torch, dev, log)
+    idx, queries, gt0, cent_h = build_index(w, torch, dev, log, dist)
     if args.coarse_impl >= 0:
         idx.set_option("coarse_impl", args.coarse_impl)
     nq, k, nprobe = w["nq"], w["k"], w["nprobe"]
@@ -316,6 +331,15 @@ def main():
         step()
     torch.cuda.synchronize()
     recall = float((L == gt0[:, None]).any(1).float().mean().item())
+    sharded_ok = None
+    if world > 1:
+        # the merged answer of the sharded search must be the single-GPU answer (same keys: distance, scan order)
+        Ds, Ls = D.clone(), L.clone()
+        idx.set_shard(0, w["nc"])
+        idx.search_dev(k, queries, D, L)
+        torch.cuda.synchronize()
+        sharded_ok = bool(torch.equal(Ls, L) and torch.equal(Ds, D))
+        idx.set_shard(*sharding.shard_range(rank, world, w["nc"]))
     idx.reset_stats()
     evs = [(torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)) for _ in range(args.steps)]
     if dist is not None:
@@ -472,7 +496,7 @@ def main():
         line = {"metric": "QPS at Recall@10 (k=10)", "value": value, "unit": "queries/s", "n_gpus": world,
                 "steps": args.steps, "warmup": max(args.warmup, 3), "ms_per_step": ms_per_step, "higher_is_better": True,
                 "scaling": "strong", "vs_baseline": None, "dtype": "f32", "data": "synthetic", "config": config,
-                "recall_at_10": recall, "clocks": clk.summary(), "e2e": e2e, "gpu_launches": launches,
+                "recall_at_10": recall, "sharded_equals_single_gpu": sharded_ok, "clocks": clk.summary(), "e2e": e2e, "gpu_launches": launches,
                 "roofline": roofline, "stages": stages, "cpu_baseline": cpu_baseline,
                 "scanned_codes_per_step": scanned // max(1, args.steps)}
         print(json.dumps(line), flush=True)

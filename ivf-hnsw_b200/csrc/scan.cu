@@ -566,10 +566,69 @@ __global__ void __launch_bounds__(256) lut_kernel(int nq, int d, const float *__
     }
 }
 
+// Same table, codebook rows held in REGISTERS: thread j loads c_{m,j} for every m once (d floats) and then
+// streams LUT_REG_QPB queries through them (query values broadcast from shared memory with 128-bit loads).
+// Per query and thread: d FMAs, d/4 LDS.128, M/4 STG.128 -- nothing else.  Same fmaf order as lut_kernel.
+#define LUT_REG_QPB 32
+template <int M, int DSUB>
+__global__ void __launch_bounds__(256) lut_reg_kernel(int nq, const float *__restrict__ queries,
+                                                      const float *__restrict__ pqc, float *__restrict__ lutc)
+{
+    constexpr int D = M * DSUB;
+    __shared__ __align__(16) float sq[LUT_REG_QPB * D];
+    const int q0 = blockIdx.x * LUT_REG_QPB, j = threadIdx.x;
+    const int nqb = min(LUT_REG_QPB, nq - q0);
+    for (int i = threadIdx.x; i < nqb * D; i += 256) sq[i] = queries[(size_t)q0 * D + i];
+    float c[D];
+#pragma unroll
+    for (int m = 0; m < M; m++)
+#pragma unroll
+        for (int t = 0; t < DSUB; t++) c[m * DSUB + t] = __ldg(pqc + ((size_t)m * 256 + j) * DSUB + t);
+    __syncthreads();
+    for (int qq = 0; qq < nqb; qq++) {
+        float qv[D];
+#pragma unroll
+        for (int i = 0; i < D / 4; i++) {
+            const float4 v = *reinterpret_cast<const float4 *>(sq + qq * D + i * 4);
+            qv[i * 4] = v.x; qv[i * 4 + 1] = v.y; qv[i * 4 + 2] = v.z; qv[i * 4 + 3] = v.w;
+        }
+        float4 *o = reinterpret_cast<float4 *>(lutc + ((size_t)(q0 + qq) * 256 + j) * M);
+#pragma unroll
+        for (int m4 = 0; m4 < M / 4; m4++) {
+            float r[4];
+#pragma unroll
+            for (int u = 0; u < 4; u++) {
+                const int m = m4 * 4 + u;
+                float s = 0.f;
+#pragma unroll
+                for (int t = 0; t < DSUB; t++) s = fmaf(qv[m * DSUB + t], c[m * DSUB + t], s);
+                r[u] = -2.f * s;
+            }
+            o[m4] = make_float4(r[0], r[1], r[2], r[3]);
+        }
+    }
+}
+
+template <int M, int DSUB>
+static cudaError_t launch_lut_reg(cudaStream_t st, int nq, const float *queries, const float *pqc, float *lutc)
+{
+    lut_reg_kernel<M, DSUB><<<(unsigned)((nq + LUT_REG_QPB - 1) / LUT_REG_QPB), 256, 0, st>>>(nq, queries, pqc, lutc);
+    return cudaGetLastError();
+}
+
 cudaError_t launch_lut(cudaStream_t st, uint64_t *launches, int M, int nq, int d, const float *queries,
                        const float *pqc, float *lutc)
 {
     if (nq == 0) return cudaSuccess;
+    ++*launches;
+    const int dsub = d / M;
+    // register-resident codebook for the usual shapes (d <= 128, d % 4 == 0)
+#define IVF_LUT_CASE(MM, DS) if (M == MM && dsub == DS) return launch_lut_reg<MM, DS>(st, nq, queries, pqc, lutc);
+    IVF_LUT_CASE(8, 4) IVF_LUT_CASE(8, 12) IVF_LUT_CASE(8, 16)
+    IVF_LUT_CASE(16, 2) IVF_LUT_CASE(16, 6) IVF_LUT_CASE(16, 8)
+    IVF_LUT_CASE(32, 3) IVF_LUT_CASE(32, 4)
+    IVF_LUT_CASE(64, 2)
+#undef IVF_LUT_CASE
     const unsigned grid = (unsigned)((nq + LUT_QPB - 1) / LUT_QPB);
     const size_t sm = (size_t)LUT_QPB * d * 4;
     switch (M) {
@@ -577,9 +636,8 @@ cudaError_t launch_lut(cudaStream_t st, uint64_t *launches, int M, int nq, int d
     case 16: lut_kernel<16><<<grid, 256, sm, st>>>(nq, d, queries, pqc, lutc); break;
     case 32: lut_kernel<32><<<grid, 256, sm, st>>>(nq, d, queries, pqc, lutc); break;
     case 64: lut_kernel<64><<<grid, 256, sm, st>>>(nq, d, queries, pqc, lutc); break;
-    default: return cudaErrorInvalidValue;
+    default: --*launches; return cudaErrorInvalidValue;
     }
-    ++*launches;
     return cudaGetLastError();
 }
 
