@@ -195,6 +195,7 @@ static __device__ __forceinline__ int pair_probe(int e, int nsubc, int sub_shift
 }
 
 __global__ void __launch_bounds__(G1_THREADS) group_g1_kernel(int d, int nprobe, int nsubc, int sub_shift, int ht_size,
+                                                              int mt_size,
                                                               uint64_t max_codes, int do_pruning,
                                                               const float *__restrict__ queries,
                                                               const float *__restrict__ coarse_d,
@@ -203,9 +204,11 @@ __global__ void __launch_bounds__(G1_THREADS) group_g1_kernel(int d, int nprobe,
 {
     extern __shared__ __align__(16) uint8_t sm[];
     float *sq = reinterpret_cast<float *>(sm);                         // [d] (d % 4 == 0)
-    uint32_t *hk = reinterpret_cast<uint32_t *>(sq + d);               // [ht_size] keys
-    float *hv = reinterpret_cast<float *>(hk + ht_size);               // [ht_size] values (NaN = to compute)
-    uint32_t *s_c = reinterpret_cast<uint32_t *>(hv + ht_size);        // [nprobe]
+    uint32_t *hk = reinterpret_cast<uint32_t *>(sq + d);               // [ht_size] neighbour ids to evaluate
+    float *hv = reinterpret_cast<float *>(hk + ht_size);               // [ht_size] their distances
+    uint32_t *mk = reinterpret_cast<uint32_t *>(hv + ht_size);         // [mt_size] memo of the coarse stage: probed ids
+    float *mv = reinterpret_cast<float *>(mk + mt_size);               // [mt_size] ... and their coarse distances
+    uint32_t *s_c = reinterpret_cast<uint32_t *>(mv + mt_size);        // [nprobe]
     uint32_t *s_sz = s_c + nprobe;
     float *s_alpha = reinterpret_cast<float *>(s_sz + nprobe);
     float *s_cd = s_alpha + nprobe;
@@ -219,29 +222,36 @@ __global__ void __launch_bounds__(G1_THREADS) group_g1_kernel(int d, int nprobe,
     const float qnan = __int_as_float(0x7fc00000);
     for (int i = tid; i < d; i += G1_THREADS) sq[i] = queries[(size_t)q * d + i];
     for (int i = tid; i < ht_size; i += G1_THREADS) hk[i] = 0xffffffffu;
+    for (int i = tid; i < mt_size; i += G1_THREADS) mk[i] = 0xffffffffu;
     if (tid == 0) { s_nwork = 0; s_count = 0; }
     if (warp == 0) probe_meta_warp0(nprobe, max_codes, coarse_i + qo, L, s_c, s_sz, s_inh, lane);
     __syncthreads();
-    const uint32_t hmask = ht_size - 1;
-    // per-list constants and the memo of the coarse stage
+    const uint32_t hmask = ht_size - 1, mmask = mt_size - 1;
+    // per-list constants and the memo of the coarse stage (its own small table: at most nprobe of 2*nprobe slots)
     for (int i = tid; i < nprobe; i += G1_THREADS) {
         const uint32_t c = s_c[i];
         const float v = coarse_d[qo + i];
         s_alpha[i] = L.alphas[c];
         s_cd[i] = v;
         s_cn[i] = L.centroid_norms[c];
-        uint32_t p = (c * 2654435761u) & hmask;
+        uint32_t p = (c * 2654435761u) & mmask;
         while (true) {
-            const uint32_t prev = atomicCAS(&hk[p], 0xffffffffu, c);
-            if (prev == 0xffffffffu || prev == c) {
-                hv[p] = v;
-                if (!(v >= 0.00001f) && prev == 0xffffffffu) work[atomicAdd(&s_nwork, 1)] = (uint16_t)p;
-                break;
-            }
-            p = (p + 1) & hmask;
+            const uint32_t prev = atomicCAS(&mk[p], 0xffffffffu, c);
+            if (prev == 0xffffffffu || prev == c) { mv[p] = v; break; }
+            p = (p + 1) & mmask;
         }
     }
     __syncthreads();
+    // memoised distance of centroid n, or NaN: absent, or < EPS which the reference treats as "not computed" (Q1 iv)
+    auto memo = [&](uint32_t n) -> float {
+        uint32_t p = (n * 2654435761u) & mmask;
+        while (true) {
+            const uint32_t key = mk[p];
+            if (key == n) { const float v = mv[p]; return v >= 0.00001f ? v : qnan; }
+            if (key == 0xffffffffu) return qnan;
+            p = (p + 1) & mmask;
+        }
+    };
     const int npairs = nprobe * nsubc;
     // ---- every needed neighbour id enters the table once (loads of 8 pairs in flight per thread)
     for (int e0 = 0; e0 < npairs; e0 += G1_THREADS * 8) {
@@ -264,6 +274,8 @@ __global__ void __launch_bounds__(G1_THREADS) group_g1_kernel(int d, int nprobe,
         for (int u = 0; u < 8; u++) {
             const uint32_t n = nn[u];
             if (n == 0xffffffffu) continue;
+            const float mvv = memo(n);
+            if (mvv == mvv) continue;      // the coarse stage already knows d(q, n)
             uint32_t p = (n * 2654435761u) & hmask;
             while (true) {
                 const uint32_t prev = atomicCAS(&hk[p], 0xffffffffu, n);
@@ -312,9 +324,12 @@ __global__ void __launch_bounds__(G1_THREADS) group_g1_kernel(int d, int nprobe,
             float r = qnan, sb = __int_as_float(0x7f800000);
             if (nn[u] != 0xffffffffu) {
                 const int i = pair_probe(e, nsubc, sub_shift);
-                uint32_t p = (nn[u] * 2654435761u) & hmask;
-                while (hk[p] != nn[u]) p = (p + 1) & hmask;
-                const float qsd = hv[p];
+                float qsd = memo(nn[u]);
+                if (qsd != qsd) {
+                    uint32_t p = (nn[u] * 2654435761u) & hmask;
+                    while (hk[p] != nn[u]) p = (p + 1) & hmask;
+                    qsd = hv[p];
+                }
                 const float alpha = s_alpha[i];
                 const float oma = __fsub_rn(1.f, alpha);
                 // :251-252  (1-a)*d(q,c) - a*((1-a)*d(c,n) - d(q,n))
@@ -484,17 +499,20 @@ cudaError_t launch_prep_grouping(cudaStream_t st, uint64_t *launches, int nq, in
 {
     if (nq == 0) return cudaSuccess;
     const int npairs = nprobe * nsubc;
-    int ht = 64;
-    while (ht < npairs + nprobe + 1) ht <<= 1;           // can never fill up
+    // main table: one slot per (probe, sub-group) pair at most -- it can become full but never overflow
+    // (typical load 20-30 %: the neighbour lists of the probed centroids overlap); memo table: load <= 50 %
+    int ht = 64, mt = 64;
+    while (ht < npairs) ht <<= 1;
+    while (mt < 2 * nprobe) mt <<= 1;
     if (ht > 65536) return cudaErrorInvalidValue;       // uint16 work list
-    const size_t sm1 = (size_t)d * 4 + (size_t)ht * 8 + (size_t)nprobe * 20 + (size_t)(npairs + nprobe) * 2 +
-                       (size_t)nprobe + 16;
+    const size_t sm1 = (size_t)d * 4 + (size_t)ht * 8 + (size_t)mt * 8 + (size_t)nprobe * 20 +
+                       (size_t)(npairs + nprobe) * 2 + (size_t)nprobe + 16;
     cudaError_t e = cudaFuncSetAttribute(group_g1_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sm1);
     if (e != cudaSuccess) return e;
     int sub_shift = -1;
     for (int b = 0; b < 16; b++)
         if ((1 << b) == nsubc) sub_shift = b;
-    group_g1_kernel<<<nq, G1_THREADS, sm1, st>>>(d, nprobe, nsubc, sub_shift, ht, max_codes, do_pruning ? 1 : 0, queries,
+    group_g1_kernel<<<nq, G1_THREADS, sm1, st>>>(d, nprobe, nsubc, sub_shift, ht, mt, max_codes, do_pruning ? 1 : 0, queries,
                                                 coarse_d, coarse_i, L, T, rows_counter);
     ++*launches;
     e = cudaGetLastError();

@@ -168,3 +168,43 @@ def test_empty_and_ragged_inputs(port):
         assert np.all(L[i, n:] == -1) and np.all(D[i, n:] > 1e38)
         assert set(L[i, :n].tolist()) == set(Lp[i][Lp[i] >= 0].tolist())
     idx.close()
+
+
+@pytest.mark.parametrize("name", ["adc_sift_m16", "grp_sift_m16", "grp_deep_opq"])
+@pytest.mark.parametrize("nshards", [2, 3])
+def test_sharded_search_equals_single_gpu(name, nshards):
+    """SURVEY.md 8(e) on one GPU: query-sliced preparation into shard-independent records, per-shard scans of
+    the owned centroid ranges, K-M1 merge by (distance, scan order) == the unsharded answer, bit for bit."""
+    import importlib
+    import torch
+    pkg = load_pkg()
+    sharding = importlib.import_module("ivf-hnsw_b200.sharding")
+    g, ix, runs = load_golden(name)
+    k, nprobe = int(g["k"]), int(g["nprobe"])
+    idx = make_index(pkg, ix)
+    idx.load_index_dict(ix)
+    idx.nprobe = nprobe
+    tag, mc, pr = runs[-1]
+    idx.max_codes, idx.do_pruning = mc, pr
+    dev = torch.device("cuda:0")
+    Q = torch.from_numpy(np.ascontiguousarray(g["Q"])).to(dev)
+    nq = Q.shape[0]
+    D0 = torch.empty(nq, k, device=dev); L0 = torch.empty(nq, k, dtype=torch.int64, device=dev)
+    idx.search_dev(k, Q, D0, L0)
+    # records prepared slice by slice, as the ranks would
+    per = (nq + nshards - 1) // nshards
+    tables = torch.zeros(nshards * per, idx.tables_bytes(), dtype=torch.uint8, device=dev)
+    for r in range(nshards):
+        b, e, _ = sharding.query_slice(r, nshards, nq)
+        idx.prepare_dev(Q, b, e, tables)
+    gD = torch.empty(nshards, nq, k, device=dev); gS = torch.empty(nshards, nq, k, dtype=torch.int32, device=dev)
+    gL = torch.empty(nshards, nq, k, dtype=torch.int64, device=dev)
+    for r in range(nshards):
+        idx.set_shard(*sharding.shard_range(r, nshards, ix["nc"]))
+        idx.scan_tables_dev(k, Q, tables, gD[r], gS[r], gL[r])
+    idx.set_shard(0, ix["nc"])
+    D1 = torch.empty_like(D0); L1 = torch.empty_like(L0)
+    idx.merge_partials_dev(k, nq, nshards, gD, gS, gL, D1, L1)
+    torch.cuda.synchronize()
+    assert torch.equal(L0, L1) and torch.equal(D0, D1)
+    idx.close()
