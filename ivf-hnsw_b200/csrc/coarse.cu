@@ -120,6 +120,7 @@ static __device__ __forceinline__ uint32_t fkey(float f)
 }
 
 #define SEL_MAX_FLAGGED 32
+#define SEL_CACHE 8
 
 __global__ void __launch_bounds__(256) coarse_select_kernel(int nc, int d, int ngroups, int nprobe, int kprime,
                                                             int cand_cap, const float *__restrict__ Q,
@@ -134,7 +135,7 @@ __global__ void __launch_bounds__(256) coarse_select_kernel(int nc, int d, int n
     uint32_t *cand = reinterpret_cast<uint32_t *>(sq + d);        // [cand_cap]
     float *cand_d = reinterpret_cast<float *>(cand + cand_cap);   // [cand_cap]
     __shared__ uint32_t hist[256];
-    __shared__ uint32_t s_prefix, s_remaining, s_ncand, s_nflag, s_less;
+    __shared__ uint32_t s_prefix, s_remaining, s_ncand, s_nflag, s_less, s_or, s_and;
     __shared__ uint32_t s_flag[SEL_MAX_FLAGGED];
     const int q = blockIdx.x, tid = threadIdx.x;
     const int n = ngroups * COARSE_T;
@@ -150,34 +151,89 @@ __global__ void __launch_bounds__(256) coarse_select_kernel(int nc, int d, int n
         return (self_off >= 0 && id == (uint32_t)(q + self_off)) ? 0xffffffffu : id;
     };
     for (int i = tid; i < d; i += 256) sq[i] = Q[(size_t)q * d + i];
-    if (tid == 0) { s_prefix = 0; s_remaining = (uint32_t)kprime; s_ncand = 0; s_nflag = 0; s_less = 0; }
+    if (tid == 0) { s_prefix = 0; s_remaining = (uint32_t)kprime; s_ncand = 0; s_nflag = 0; s_less = 0; s_or = 0u; s_and = 0xffffffffu; }
     __syncthreads();
 
-    // ---- radix select: key of the kprime-th smallest kept value
-    for (int pass = 0; pass < 4; pass++) {
-        const int shift = 24 - 8 * pass;
+    // ---- radix select: key of the kprime-th smallest kept value.  The keys a thread owns stay in registers
+    // across the passes when the row is short enough (nc <= 65536); warp 0 scans the histogram.
+    const bool cached = n <= 256 * SEL_CACHE;
+    uint32_t kc[SEL_CACHE];
+    if (cached) {
+#pragma unroll
+        for (int j = 0; j < SEL_CACHE; j++) {
+            const int i = tid + 256 * j;
+            kc[j] = i < n ? fkey(gv[i]) : 0xffffffffu;
+        }
+    }
+    // bits every key shares need no pass (and would put all 2048 atomics of a pass on one counter): the keys of
+    // one row usually share sign and exponent
+    {
+        uint32_t vor = 0u, vand = 0xffffffffu;
+        if (cached) {
+#pragma unroll
+            for (int j = 0; j < SEL_CACHE; j++)
+                if (tid + 256 * j < n) { vor |= kc[j]; vand &= kc[j]; }
+        } else {
+            for (int i = tid; i < n; i += 256) { const uint32_t kx = fkey(gv[i]); vor |= kx; vand &= kx; }
+        }
+        vor = __reduce_or_sync(IVF_FULL_MASK, vor);
+        vand = __reduce_and_sync(IVF_FULL_MASK, vand);
+        if ((tid & 31) == 0) { atomicOr(&s_or, vor); atomicAnd(&s_and, vand); }
+    }
+    __syncthreads();
+    const uint32_t vdiff = s_or ^ s_and;
+    int remaining_bits = vdiff ? 32 - __clz(vdiff) : 0;
+    if (tid == 0) s_prefix = remaining_bits == 32 ? 0u : (s_and & ~((1u << remaining_bits) - 1u));
+    __syncthreads();
+    while (remaining_bits > 0) {
+        const int w = remaining_bits < 8 ? remaining_bits : 8;
+        const int shift = remaining_bits - w;
+        const uint32_t dmask = (1u << w) - 1u;
         hist[tid] = 0;
         __syncthreads();
         const uint32_t prefix = s_prefix;
-        const uint32_t pmask = pass == 0 ? 0u : (0xffffffffu << (shift + 8));
-        for (int i = tid; i < n; i += 256) {
-            const uint32_t kx = fkey(gv[i]);
-            if ((kx & pmask) == prefix) atomicAdd(&hist[(kx >> shift) & 255u], 1u);
-        }
-        __syncthreads();
-        if (tid == 0) {
-            uint32_t rem = s_remaining, cum = 0;
-            int b = 0;
-            for (; b < 256; b++) {
-                if (cum + hist[b] >= rem) break;
-                cum += hist[b];
+        const uint32_t pmask = remaining_bits == 32 ? 0u : (0xffffffffu << remaining_bits);
+        if (cached) {
+#pragma unroll
+            for (int j = 0; j < SEL_CACHE; j++)
+                if ((kc[j] & pmask) == prefix && tid + 256 * j < n) atomicAdd(&hist[(kc[j] >> shift) & dmask], 1u);
+        } else {
+            for (int i = tid; i < n; i += 256) {
+                const uint32_t kx = fkey(gv[i]);
+                if ((kx & pmask) == prefix) atomicAdd(&hist[(kx >> shift) & dmask], 1u);
             }
-            if (b == 256) b = 255;  // kprime > n cannot happen (host clamps)
-            s_prefix = prefix | ((uint32_t)b << shift);
-            s_remaining = rem - cum;
-            s_less += cum;
         }
         __syncthreads();
+        if (tid < 32) {
+            // lane l owns bins 8l .. 8l+7
+            uint32_t hb[8], mine = 0;
+#pragma unroll
+            for (int b = 0; b < 8; b++) { hb[b] = hist[tid * 8 + b]; mine += hb[b]; }
+            uint32_t incl = mine;
+#pragma unroll
+            for (int o = 1; o < 32; o <<= 1) {
+                const uint32_t t = __shfl_up_sync(IVF_FULL_MASK, incl, o);
+                if (tid >= o) incl += t;
+            }
+            const uint32_t rem = s_remaining;
+            const uint32_t hit = __ballot_sync(IVF_FULL_MASK, incl >= rem);
+            const int owner = hit ? __ffs(hit) - 1 : 31;   // kprime > n cannot happen (host clamps)
+            if (tid == owner) {
+                uint32_t cum = incl - mine;
+                int b = 0;
+#pragma unroll
+                for (; b < 8; b++) {
+                    if (cum + hb[b] >= rem) break;
+                    cum += hb[b];
+                }
+                if (b == 8) b = 7;
+                s_prefix = prefix | ((uint32_t)(tid * 8 + b) << shift);
+                s_remaining = rem - cum;
+                s_less += cum;
+            }
+        }
+        __syncthreads();
+        remaining_bits = shift;
     }
     const uint32_t tau = s_prefix;       // key of the kprime-th smallest
     // ---- verify groups: a group whose COARSE_T-th kept value is <= tau may hide candidates
@@ -197,8 +253,9 @@ __global__ void __launch_bounds__(256) coarse_select_kernel(int nc, int d, int n
     // ---- collect: kept entries with key <= tau outside flagged groups, then flagged groups in full
     for (int i = tid; i < n; i += 256) {
         const uint32_t kx = fkey(gv[i]);
+        if (kx > tau) continue;
         const uint32_t id = entry_id(i);
-        if (kx <= tau && id != 0xffffffffu) {
+        if (id != 0xffffffffu) {
             const uint32_t g = (uint32_t)(i / COARSE_T);
             bool flagged = false;
             for (uint32_t f = 0; f < nflag; f++) flagged |= (s_flag[f] == g);
