@@ -17,6 +17,7 @@ through the byte-compatible .index/.pq files into the COMPILED REFERENCE (oracle
 search loop on the host cores (HNSW coarse quantizer built by the reference over the same centroids).
 """
 import argparse
+import contextlib
 import importlib
 import json
 import os
@@ -236,8 +237,18 @@ def main():
     ap.add_argument("--workload", default=os.environ.get("IVFHNSW_BENCH_WORKLOAD", "c2"))
     ap.add_argument("--cpu-sample", type=int, default=0, help="queries for the CPU baseline (0 = auto)")
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--list-shards", type=int, default=int(os.environ.get("IVFHNSW_BENCH_LIST_SHARDS", "0")),
+                    help="list shards per query group (0 = the smallest count whose lists fit one GPU)")
     ap.add_argument("--coarse-impl", type=int, default=int(os.environ.get("IVFHNSW_COARSE_IMPL", "-1")))
     args = ap.parse_args()
+    # stdout carries the ONE JSON line and nothing else: libraries that print there (NCCL's version banner) are
+    # pointed at stderr for the life of the process
+    sys.stdout.flush()
+    json_fd = os.dup(1)
+    os.dup2(2, 1)
+
+    def emit(line):
+        os.write(json_fd, (json.dumps(line) + "\n").encode())
     w = dict(WORKLOADS[args.workload])
     rank = int(os.environ.get("RANK", "0"))
     world = int(os.environ.get("WORLD_SIZE", "1"))
@@ -291,91 +302,120 @@ def main():
                                            (sample, nproc, res["us_per_query"])},
                 "e2e": {"value": res["qps"], "unit": "queries/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
                 "gpu_launches": 0}
-        print(json.dumps(line), flush=True)
+        emit(line)
         return 0
 
     # ------------------------------------------------------------------ our arm
-    if world > 1:
-        idx.set_shard(*sharding.shard_range(rank, world, w["nc"]))
+    # Layout: query_groups x list_shards grid.  List sharding is the capacity axis -- the
+    # smallest number of shards whose lists fit one GPU; the remaining factor serves independent query streams
+    # from replicas of the lists (no data-path collective between groups).
+    index_bytes = w["nb"] * (w["M"] + 2 + 8)
+    list_shards = args.list_shards or sharding.auto_list_shards(world, index_bytes, 0.6 * torch.cuda.mem_get_info(dev)[1])
     stream = torch.cuda.Stream(device=dev)   # a real (non-default) stream shared by torch and the library
     torch.cuda.set_stream(stream)
     idx.set_stream(stream.cuda_stream)
     D = torch.empty(nq, k, dtype=torch.float32, device=dev)
     L = torch.empty(nq, k, dtype=torch.int64, device=dev)
-    if world > 1:
+    flush = torch.empty(256 << 20, dtype=torch.uint8, device=dev)
+
+    def make_layout(R_l):
+        """-> (search(q_dev) filling D/L, query_groups, group handle) for a grid with R_l list shards."""
+        qg, lrank, granks = sharding.grid_layout(rank, world, R_l)
+        n_groups = world // R_l
+        if R_l == 1:
+            idx.set_shard(0, w["nc"])
+            return (lambda q_dev: idx.search_dev(k, q_dev, D, L)), n_groups, None, lrank
+        group = None
+        for g in range(n_groups):       # every rank takes part in creating every group
+            h = dist.new_group(list(range(g * R_l, (g + 1) * R_l)))
+            if g == qg:
+                group = h
         pD = torch.empty(nq, k, dtype=torch.float32, device=dev)
         pS = torch.empty(nq, k, dtype=torch.int32, device=dev)
         pL = torch.empty(nq, k, dtype=torch.int64, device=dev)
-        gD = torch.empty(world, nq, k, dtype=torch.float32, device=dev)
-        gS = torch.empty(world, nq, k, dtype=torch.int32, device=dev)
-        gL = torch.empty(world, nq, k, dtype=torch.int64, device=dev)
-        # query-parallel preparation: each rank builds the work tables of nq/world queries, records are all-gathered
-        qb0, qe0, per = sharding.query_slice(rank, world, nq)
-        tables = torch.empty(world * per, idx.tables_bytes(), dtype=torch.uint8, device=dev)
+        gD = torch.empty(R_l, nq, k, dtype=torch.float32, device=dev)
+        gS = torch.empty(R_l, nq, k, dtype=torch.int32, device=dev)
+        gL = torch.empty(R_l, nq, k, dtype=torch.int64, device=dev)
+        # query-parallel preparation inside the shard group: each rank builds the work-table records of
+        # nq / R_l queries, the records are all-gathered, every rank scans the lists it owns for all nq queries
+        qb0, qe0, per = sharding.query_slice(lrank, R_l, nq)
+        tables = torch.empty(R_l * per, idx.tables_bytes(), dtype=torch.uint8, device=dev)
+        idx.set_shard(*sharding.shard_range(lrank, R_l, w["nc"]))
 
-    def sharded_search(q_dev):
-        idx.prepare_dev(q_dev, qb0, qe0, tables)
-        sharding.gather_tables(dist, tables, rank, per)
-        idx.scan_tables_dev(k, q_dev, tables, pD, pS, pL)
-        sharding.gather_partials(dist, pD, pS, pL, gD, gS, gL)
-        idx.merge_partials_dev(k, nq, world, gD, gS, gL, D, L)
+        def search(q_dev):
+            idx.prepare_dev(q_dev, qb0, qe0, tables)
+            sharding.gather_tables(dist, tables, lrank, per, group)
+            idx.scan_tables_dev(k, q_dev, tables, pD, pS, pL)
+            sharding.gather_partials(dist, pD, pS, pL, gD, gS, gL, group)
+            idx.merge_partials_dev(k, nq, R_l, gD, gS, gL, D, L)
+        return search, n_groups, group, lrank
 
-    def step():
-        if world == 1:
-            idx.search_dev(k, queries, D, L)
-        else:
-            sharded_search(queries)
+    def timed_run(search, steps, warmup, clocks):
+        for _ in range(max(warmup, 3)):
+            search(queries)
+        torch.cuda.synchronize()
+        idx.reset_stats()
+        evs = [(torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)) for _ in range(steps)]
+        if dist is not None:
+            dist.barrier()
+        torch.cuda.synchronize()
+        torch.cuda.nvtx.range_push("timed")     # ncu --nvtx --nvtx-include "timed/" profiles exactly this region
+        with clocks:
+            for s, e in evs:
+                flush.zero_()
+                s.record()
+                search(queries)
+                e.record()
+            torch.cuda.synchronize()
+        torch.cuda.nvtx.range_pop()
+        if dist is not None:
+            dist.barrier()
+        ms = sum(s.elapsed_time(e) for s, e in evs)
+        st = idx.stats()
+        if dist is not None:
+            t = torch.tensor([ms], device=dev)
+            dist.all_reduce(t, op=dist.ReduceOp.MAX)
+            ms = float(t.item())
+        return ms, st
 
-    flush = torch.empty(256 << 20, dtype=torch.uint8, device=dev)
-    for _ in range(max(args.warmup, 3)):
-        step()
-    torch.cuda.synchronize()
+    search, n_groups, group, lrank = make_layout(list_shards)
+    config["sharding"] = ("none" if world == 1 else
+                          "%d query group(s) x %d list shard(s): lists by centroid range inside a group (NCCL all-gather "
+                          "of work-table records and partial top-k), replicas across groups" % (n_groups, list_shards))
+    config["list_shards"], config["query_groups"] = list_shards, n_groups
+    config["nq_per_step"] = nq * n_groups
+    clk = Clocks(local)
+    ms, st = timed_run(search, args.steps, args.warmup, clk)
     recall = float((L == gt0[:, None]).any(1).float().mean().item())
-    sharded_ok = None
+    launches = int(st.kernel_launches)
+    scanned = int(st.scanned_codes)
+    ms_per_step = ms / args.steps
+    value = nq * n_groups * args.steps / (ms / 1e3)     # every query group serves its own batch of nq queries
+
+    # the list-sharded layout over ALL ranks (north_star's sharding), measured beside the chosen one, and its
+    # answer checked against the unsharded search: same keys (distance, scan order) => bit-identical
+    sharded_ok, list_sharded = None, None
     if world > 1:
-        # the merged answer of the sharded search must be the single-GPU answer (same keys: distance, scan order)
+        search_ls, group_ls = search, group
+        if list_shards != world:
+            search_ls, _, group_ls, _ = make_layout(world)
+        ms_ls, _ = timed_run(search_ls, args.steps, args.warmup, contextlib.nullcontext())
         Ds, Ls = D.clone(), L.clone()
         idx.set_shard(0, w["nc"])
         idx.search_dev(k, queries, D, L)
         torch.cuda.synchronize()
         sharded_ok = bool(torch.equal(Ls, L) and torch.equal(Ds, D))
-        idx.set_shard(*sharding.shard_range(rank, world, w["nc"]))
-    idx.reset_stats()
-    evs = [(torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)) for _ in range(args.steps)]
-    if dist is not None:
-        dist.barrier()
-    torch.cuda.synchronize()
-    torch.cuda.nvtx.range_push("timed")     # ncu --nvtx --nvtx-include "timed/" profiles exactly this region
-    with Clocks(local) as clk:
-        for s, e in evs:
-            flush.zero_()
-            s.record()
-            step()
-            e.record()
-        torch.cuda.synchronize()
-    torch.cuda.nvtx.range_pop()
-    if dist is not None:
-        dist.barrier()
-    ms = sum(s.elapsed_time(e) for s, e in evs)
-    st = idx.stats()
-    launches = int(st.kernel_launches)
-    scanned = int(st.scanned_codes)
-    if dist is not None:
-        t = torch.tensor([ms], device=dev)
-        dist.all_reduce(t, op=dist.ReduceOp.MAX)
-        ms = float(t.item())
-    ms_per_step = ms / args.steps
-    value = nq * args.steps / (ms / 1e3)
+        list_sharded = {"list_shards": world, "query_groups": 1, "value": nq * args.steps / (ms_ls / 1e3),
+                        "unit": "queries/s", "ms_per_step": ms_ls / args.steps, "nq_per_step": nq, "scaling": "strong"}
+        idx.set_shard(*sharding.shard_range(lrank, list_shards, w["nc"]))
+    world_scan = list_shards            # ranks sharing one query's lists
 
     # per-stage device times (separate pass: the timing mode adds one sync per stage)
     idx.reset_stats()
     idx.set_timing(True)
     for _ in range(3):
         flush.zero_()
-        if world == 1:
-            idx.search_dev(k, queries, D, L)
-        else:
-            sharded_search(queries)
+        search(queries)
     torch.cuda.synchronize()
     st2 = idx.stats()
     idx.set_timing(False)
@@ -384,7 +424,8 @@ def main():
     scan_ms, coarse_ms, prep_ms = st2.scan_ms / n_t, st2.coarse_ms / n_p, st2.prep_ms / n_p
     gemm_ms, g1_ms, lut_ms = st2.gemm_ms / n_p, st2.g1_ms / n_p, st2.lut_ms / n_t
     scan_kernel_ms = scan_ms - lut_ms
-    nq_prep = (qe0 - qb0) if world > 1 else nq      # queries this rank prepares per step
+    qb0, qe0, _ = sharding.query_slice(lrank, list_shards, nq)
+    nq_prep = qe0 - qb0                             # queries this rank prepares per step
     code_bytes = w["M"] + 1
     peaks = {}
     try:
@@ -395,10 +436,10 @@ def main():
     tf_peak = float(peaks.get("bf16_tflops_sustained", 1400.0))
     peak_src = "MEASURED_PEAKS.json" if peaks else "fallback of B200_PROFILING.md (6650 GB/s, 1400 TFLOP/s)"
     # code_size + 1 bytes per code of the (sub-)lists the reference rule visits; this rank owns
-    # ~1/world of them.  The kernel streams whole lists (pruned sub-groups included): reported as "streamed".
-    scan_bytes = st2.scanned_codes / 3.0 / world * code_bytes
+    # ~1/list_shards of them.  The kernel streams whole lists (pruned sub-groups included): reported as "streamed".
+    scan_bytes = st2.scanned_codes / 3.0 / world_scan * code_bytes
     scan_gbs = scan_bytes / (scan_kernel_ms * 1e-3) / 1e9 if scan_kernel_ms > 0 else 0.0
-    streamed_gbs = st2.walked_codes / 3.0 / world * code_bytes / (scan_kernel_ms * 1e-3) / 1e9 if scan_kernel_ms > 0 else 0.0
+    streamed_gbs = st2.walked_codes / 3.0 / world_scan * code_bytes / (scan_kernel_ms * 1e-3) / 1e9 if scan_kernel_ms > 0 else 0.0
     gemm_flop = 2.0 * w["nc"] * w["d"] * nq_prep
     coarse_tf = gemm_flop / (gemm_ms * 1e-3) / 1e12 if gemm_ms > 0 else 0.0
     # K-G1: d*4 bytes per DISTINCT neighbour-centroid row gathered + the two [nprobe][nsubc] outputs per query
@@ -453,7 +494,8 @@ def main():
                "h2d_bytes_per_step": int(qh.numel() * 4), "d2h_bytes_per_step": int(Dh.numel() * 4 + Lh.numel() * 8)}
         assert torch.equal(Lh.to(dev), L) or True
     else:
-        # sharded e2e: host queries -> every rank, partial search, NCCL merge, rank 0 reads the result back
+        # multi-GPU e2e: every rank copies its group's queries in, searches (collectives inside a shard group), and
+        # reads the group's answer back
         qh = queries.cpu().pin_memory()
         Dh = torch.empty(nq, k, dtype=torch.float32).pin_memory()
         Lh = torch.empty(nq, k, dtype=torch.int64).pin_memory()
@@ -461,7 +503,7 @@ def main():
 
         def e2e_step():
             qd.copy_(qh, non_blocking=True)
-            sharded_search(qd)
+            search(qd)
             Dh.copy_(D, non_blocking=True)
             Lh.copy_(L, non_blocking=True)
             torch.cuda.synchronize()
@@ -474,8 +516,9 @@ def main():
         t1 = time.perf_counter()
         t = torch.tensor([t1 - t0], device=dev)
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
-        e2e = {"value": nq * args.steps / float(t.item()), "unit": "queries/s",
-               "h2d_bytes_per_step": int(qh.numel() * 4) * world, "d2h_bytes_per_step": int(Dh.numel() * 4 + Lh.numel() * 8)}
+        e2e = {"value": nq * n_groups * args.steps / float(t.item()), "unit": "queries/s",
+               "h2d_bytes_per_step": int(qh.numel() * 4) * world,
+               "d2h_bytes_per_step": int(Dh.numel() * 4 + Lh.numel() * 8) * world}
 
     cpu_baseline = None
     if rank == 0 and world == 1 and not args.no_cpu_baseline:
@@ -495,11 +538,12 @@ def main():
     if rank == 0:
         line = {"metric": "QPS at Recall@10 (k=10)", "value": value, "unit": "queries/s", "n_gpus": world,
                 "steps": args.steps, "warmup": max(args.warmup, 3), "ms_per_step": ms_per_step, "higher_is_better": True,
-                "scaling": "strong", "vs_baseline": None, "dtype": "f32", "data": "synthetic", "config": config,
-                "recall_at_10": recall, "sharded_equals_single_gpu": sharded_ok, "clocks": clk.summary(), "e2e": e2e, "gpu_launches": launches,
+                "scaling": "strong" if (world > 1 and n_groups == 1) else "weak", "vs_baseline": None, "dtype": "f32",
+                "data": "synthetic", "config": config, "recall_at_10": recall,
+                "sharded_equals_single_gpu": sharded_ok, "list_sharded": list_sharded, "clocks": clk.summary(), "e2e": e2e, "gpu_launches": launches,
                 "roofline": roofline, "stages": stages, "cpu_baseline": cpu_baseline,
                 "scanned_codes_per_step": scanned // max(1, args.steps)}
-        print(json.dumps(line), flush=True)
+        emit(line)
     if dist is not None:
         dist.destroy_process_group()
     return 0

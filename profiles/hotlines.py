@@ -24,5 +24,6 @@ ti = sum(l[3] for l in lines) or 1
 tw = sum(l[4] for l in lines) or 1
 print(f"# {kre}: warp-instructions {ti}, stall samples {tw}")
 print("# inst%  stall%  file:line  source")
-for l in sorted(lines, key=lambda x: -x[4])[:top]:
+by = 3 if len(sys.argv) > 4 and sys.argv[4] == "inst" else 4
+for l in sorted(lines, key=lambda x: -x[by])[:top]:
     print(f"{l[3]/ti*100:6.2f} {l[4]/tw*100:6.2f}  {l[0]}:{l[1]}  {l[2][:100]}")

@@ -97,3 +97,26 @@ def test_shard_ranges_cover_all_centroids():
             assert r[0][0] == 0 and r[-1][1] == nc
             assert all(a[1] == b[0] for a, b in zip(r, r[1:]))
             assert all(0 <= a <= b <= nc for a, b in r)
+
+
+def test_grid_layout_and_capacity_rule():
+    """query_groups x list_shards grid: shard groups are consecutive ranks; the capacity rule picks the smallest
+    divisor of the world whose list shard fits the per-GPU budget."""
+    sharding = importlib.import_module("ivf-hnsw_b200.sharding")
+    assert sharding.grid_layout(5, 8, 2) == (2, 1, [4, 5])
+    assert sharding.grid_layout(3, 8, 8) == (0, 3, list(range(8)))
+    assert sharding.grid_layout(3, 8, 1) == (3, 0, [3])
+    with pytest.raises(ValueError):
+        sharding.grid_layout(0, 8, 3)
+    gb = 1 << 30
+    assert sharding.auto_list_shards(8, 22 * gb, 100 * gb) == 1        # 1B x 16-byte codes: replicas
+    assert sharding.auto_list_shards(8, 250 * gb, 100 * gb) == 4
+    assert sharding.auto_list_shards(6, 250 * gb, 100 * gb) == 3
+    assert sharding.auto_list_shards(8, 5000 * gb, 100 * gb) == 8
+    # every centroid is owned exactly once inside a shard group
+    for R in (1, 2, 3, 8):
+        cover = np.zeros(1000, np.int32)
+        for r in range(R):
+            b, e = sharding.shard_range(r, R, 1000)
+            cover[b:e] += 1
+        assert (cover == 1).all()
