@@ -693,8 +693,10 @@ static __host__ __device__ inline size_t scan_small_smem(int nprobe, int k, int 
 {
     size_t b = 0;
     b += (size_t)(5 * nprobe + 1) * 4;          // segment tables
-    if (scan_kpl(k)) b += (size_t)SCAN_WARPS * k * 12;     // the warps' sorted lists, for the final merge
-    else {
+    if (scan_kpl(k)) {
+        b += (size_t)SCAN_WARPS * k * 12;     // the warps' sorted lists, for the final merge
+        if (scan_kpl(k) == 1) b += (size_t)SCAN_WARPS * 32 * 8;   // warp candidate batches (SCAN_BCAP)
+    } else {
         b += (size_t)k * 12;                        // top-k
         b += (size_t)SCAN_WARPS * SCAN_WCAP * 12;   // warp candidate buffers
     }
@@ -775,6 +777,58 @@ template <int KPL> struct WarpList {
             if (kr == r) { td = d[r]; ts = s[r]; }
         thr_d = __shfl_sync(IVF_FULL_MASK, td, kl);
         thr_s = __shfl_sync(IVF_FULL_MASK, ts, kl);
+    }
+};
+
+// k <= 32: the warp list is one entry per lane and candidates are merged a batch at a time.  Lanes append passing
+// candidates to a 32-entry per-warp buffer (one ballot per chunk, nothing serial); a full buffer is sorted by a
+// bitonic network in registers, reversed, min-ed against the list and bitonic-merged: ~200 warp instructions
+// per 32 candidates instead of ~40 per candidate.  The slot of an entry is recovered from its scan-order key
+// at the end, so the network carries (distance, scan order) only.
+#define SCAN_BCAP 32
+struct BatchList {
+    float d, thr_d;
+    uint32_t s, thr_s;
+
+    __device__ __forceinline__ void init(int lane, int k)
+    {
+        d = FLT_MAX;
+        s = 0xffffff00u + (uint32_t)lane;
+        thr_d = FLT_MAX;
+        thr_s = 0xffffff00u + (uint32_t)(k - 1);
+    }
+    // compare-exchange with lane ^ j: keep the smaller key when keep_small, else the larger
+    static __device__ __forceinline__ void cmpx(float &xd, uint32_t &xs, int j, bool keep_small)
+    {
+        const float od = __shfl_xor_sync(IVF_FULL_MASK, xd, j);
+        const uint32_t os = __shfl_xor_sync(IVF_FULL_MASK, xs, j);
+        if (key_less(od, os, xd, xs) == keep_small) { xd = od; xs = os; }
+    }
+    // cd/cs: one candidate per lane, padding = (FLT_MAX, 0xffffffff)
+    __device__ __forceinline__ void merge(float cd, uint32_t cs, int lane, int k)
+    {
+#pragma unroll
+        for (int size = 2; size <= 32; size <<= 1) {
+#pragma unroll
+            for (int j = size >> 1; j > 0; j >>= 1)
+                cmpx(cd, cs, j, ((lane & j) == 0) == ((lane & size) == 0));
+        }
+        // ascending candidates reversed against the ascending list: the lane-wise minimum is the 32 smallest of
+        // the 64 keys as a bitonic sequence
+        const float rd = __shfl_sync(IVF_FULL_MASK, cd, 31 - lane);
+        const uint32_t rs = __shfl_sync(IVF_FULL_MASK, cs, 31 - lane);
+        if (key_less(rd, rs, d, s)) { d = rd; s = rs; }
+#pragma unroll
+        for (int j = 16; j > 0; j >>= 1) cmpx(d, s, j, (lane & j) == 0);
+        thr_d = __shfl_sync(IVF_FULL_MASK, d, k - 1);
+        thr_s = __shfl_sync(IVF_FULL_MASK, s, k - 1);
+    }
+    __device__ __forceinline__ void flush(const float *bd, const uint32_t *bs, int count, int lane, int k)
+    {
+        __syncwarp();
+        const bool h = lane < count;
+        merge(h ? bd[lane] : FLT_MAX, h ? bs[lane] : 0xffffffffu, lane, k);
+        __syncwarp();
     }
 };
 
@@ -869,6 +923,9 @@ __global__ void __launch_bounds__(SCAN_THREADS) scan_kernel(ScanArgs a)
         wbuf_d = reinterpret_cast<float *>(p); p += SCAN_WARPS * SCAN_WCAP * 4;
         wbuf_seq = reinterpret_cast<uint32_t *>(p); p += SCAN_WARPS * SCAN_WCAP * 4;
         wbuf_slot = reinterpret_cast<uint32_t *>(p); p += SCAN_WARPS * SCAN_WCAP * 4;
+    } else if (KPL == 1) {
+        wbuf_d = reinterpret_cast<float *>(p); p += SCAN_WARPS * SCAN_BCAP * 4;
+        wbuf_seq = reinterpret_cast<uint32_t *>(p); p += SCAN_WARPS * SCAN_BCAP * 4;
     }
     float *wsub_all = reinterpret_cast<float *>(p); p += SCAN_WARPS * a.nsubc * 4;
     p = reinterpret_cast<uint8_t *>((reinterpret_cast<uintptr_t>(p) + 15) & ~(uintptr_t)15);
@@ -978,9 +1035,11 @@ __global__ void __launch_bounds__(SCAN_THREADS) scan_kernel(ScanArgs a)
     const uint32_t Onorm = 128u + 4u * lane;  // M < 64: byte0 = offset of word 32 + lane, bytes 1..3 = 0
 
     WarpList<KPL> wl;
-    if (KPL > 0) wl.init(lane, k);
-    float *wd = KPL == 0 ? wbuf_d + warp * SCAN_WCAP : nullptr;
-    uint32_t *wseq = KPL == 0 ? wbuf_seq + warp * SCAN_WCAP : nullptr;
+    BatchList bl;
+    if (KPL == 1) bl.init(lane, k);
+    else if (KPL > 0) wl.init(lane, k);
+    float *wd = KPL == 0 ? wbuf_d + warp * SCAN_WCAP : (KPL == 1 ? wbuf_d + warp * SCAN_BCAP : nullptr);
+    uint32_t *wseq = KPL == 0 ? wbuf_seq + warp * SCAN_WCAP : (KPL == 1 ? wbuf_seq + warp * SCAN_BCAP : nullptr);
     uint32_t *wslot = KPL == 0 ? wbuf_slot + warp * SCAN_WCAP : nullptr;
     float *wsub = wsub_all + warp * a.nsubc;
     int wcount = 0;
@@ -1067,7 +1126,29 @@ __global__ void __launch_bounds__(SCAN_THREADS) scan_kernel(ScanArgs a)
                 }
                 const float dist = acc0 + acc1;
                 const bool valid = (c * SCAN_CHUNK + lane) < rem;
-                if (KPL > 0) {
+                if (KPL == 1) {
+                    const uint32_t sh = ctl->thr_key;   // bound shared by the warps of the CTA (ties pass)
+                    const uint32_t myseq = seq0 + c * SCAN_CHUNK + lane;
+                    bool pass = valid && fkey_u32(dist) <= sh && key_less(dist, myseq, bl.thr_d, bl.thr_s);
+                    uint32_t bal = __ballot_sync(IVF_FULL_MASK, pass);
+                    if (bal) {
+                        int n = __popc(bal);
+                        if (wcount + n > SCAN_BCAP) {
+                            bl.flush(wd, wseq, wcount, lane, k);
+                            wcount = 0;
+                            if (lane == 0 && bl.thr_d < FLT_MAX) atomicMin((uint32_t *)&ctl->thr_key, fkey_u32(bl.thr_d));
+                            pass = pass && key_less(dist, myseq, bl.thr_d, bl.thr_s);
+                            bal = __ballot_sync(IVF_FULL_MASK, pass);
+                            n = __popc(bal);
+                        }
+                        if (pass) {
+                            const int pos = wcount + __popc(bal & ((1u << lane) - 1u));
+                            wd[pos] = dist;
+                            wseq[pos] = myseq;
+                        }
+                        wcount += n;
+                    }
+                } else if (KPL > 0) {
                     const uint32_t sh = ctl->thr_key;   // bound shared by the warps of the CTA (ties pass)
                     const uint32_t myseq = seq0 + c * SCAN_CHUNK + lane;
                     const bool pass = valid && fkey_u32(dist) <= sh && key_less(dist, myseq, wl.thr_d, wl.thr_s);
@@ -1111,8 +1192,17 @@ __global__ void __launch_bounds__(SCAN_THREADS) scan_kernel(ScanArgs a)
 
     if (KPL > 0) {
         // ---- publish the warp lists, then rank every entry among the other warps' (sorted) lists
+        if (KPL == 1) {
+            if (wcount) bl.flush(wd, wseq, wcount, lane, k);
+            // empty entries: one ascending key per position, above any scan order
+            const bool empty = bl.s >= 0xffffff00u;
+            if (lane < k) {
+                topk_d[warp * k + lane] = empty ? FLT_MAX : bl.d;
+                topk_seq[warp * k + lane] = empty ? 0xffffff00u + (uint32_t)lane : bl.s;
+            }
+        }
 #pragma unroll
-        for (int r = 0; r < KPL; r++) {
+        for (int r = 0; r < (KPL == 1 ? 0 : KPL); r++) {
             const int e = r * 32 + lane;
             if (e < k) {
                 topk_d[warp * k + e] = wl.d[r];
@@ -1142,7 +1232,19 @@ __global__ void __launch_bounds__(SCAN_THREADS) scan_kernel(ScanArgs a)
                 rank += lo;
             }
             if (rank < k) {
-                const uint32_t slot = topk_slot[e];
+                uint32_t slot;
+                if (KPL == 1) {
+                    // the list of scan-order key es: the last one starting at or before it
+                    slot = IVF_INVALID_SLOT;
+                    if (es < 0xffffff00u) {
+                        int lo = 0, hi = nprobe;
+                        while (lo < hi) {
+                            const int mid = (lo + hi) >> 1;
+                            if (s_seq[mid] <= es) lo = mid + 1; else hi = mid;
+                        }
+                        slot = s_slot[lo - 1] + (es - s_seq[lo - 1]);
+                    }
+                } else slot = topk_slot[e];
                 if (a.nsplit == 1) {
                     a.out_d[(size_t)q * k + rank] = ed;
                     a.out_labels[(size_t)q * k + rank] = slot == IVF_INVALID_SLOT ? (int64_t)-1 : (int64_t)a.L.ids[slot];
