@@ -195,7 +195,6 @@ static __device__ __forceinline__ int pair_probe(int e, int nsubc, int sub_shift
 }
 
 __global__ void __launch_bounds__(G1_THREADS) group_g1_kernel(int d, int nprobe, int nsubc, int sub_shift, int ht_size,
-                                                              int mt_size,
                                                               uint64_t max_codes, int do_pruning,
                                                               const float *__restrict__ queries,
                                                               const float *__restrict__ coarse_d,
@@ -204,56 +203,54 @@ __global__ void __launch_bounds__(G1_THREADS) group_g1_kernel(int d, int nprobe,
 {
     extern __shared__ __align__(16) uint8_t sm[];
     float *sq = reinterpret_cast<float *>(sm);                         // [d] (d % 4 == 0)
-    uint32_t *hk = reinterpret_cast<uint32_t *>(sq + d);               // [ht_size] neighbour ids to evaluate
-    float *hv = reinterpret_cast<float *>(hk + ht_size);               // [ht_size] their distances
-    uint32_t *mk = reinterpret_cast<uint32_t *>(hv + ht_size);         // [mt_size] memo of the coarse stage: probed ids
-    float *mv = reinterpret_cast<float *>(mk + mt_size);               // [mt_size] ... and their coarse distances
-    uint32_t *s_c = reinterpret_cast<uint32_t *>(mv + mt_size);        // [nprobe]
+    uint32_t *hk = reinterpret_cast<uint32_t *>(sq + d);               // [ht_size] centroid ids; after the distance
+                                                                       // phase: bits of their ||c||^2
+    float *hv = reinterpret_cast<float *>(hk + ht_size);               // [ht_size] d(q, centroid)
+    uint32_t *s_c = reinterpret_cast<uint32_t *>(hv + ht_size);        // [nprobe]
     uint32_t *s_sz = s_c + nprobe;
     float *s_alpha = reinterpret_cast<float *>(s_sz + nprobe);
     float *s_cd = s_alpha + nprobe;
     float *s_cn = s_cd + nprobe;
-    uint16_t *work = reinterpret_cast<uint16_t *>(s_cn + nprobe);      // [npairs + nprobe] slots to compute
-    uint8_t *s_inh = reinterpret_cast<uint8_t *>(work + (size_t)nprobe * nsubc + nprobe);
+    uint16_t *work = reinterpret_cast<uint16_t *>(s_cn + nprobe);      // [npairs] table slots to compute
+    uint16_t *ppos = work + (size_t)nprobe * nsubc;                    // [npairs] table slot of every pair
+    uint16_t *s_mpos = ppos + (size_t)nprobe * nsubc;                  // [nprobe] table slot of a memoised probe
+    uint8_t *s_inh = reinterpret_cast<uint8_t *>(s_mpos + nprobe);
     __shared__ int s_nwork;
     __shared__ uint32_t s_count;
     const int q = blockIdx.x, tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     const size_t qo = (size_t)q * nprobe;
     const float qnan = __int_as_float(0x7fc00000);
+    const uint32_t H = (uint32_t)ht_size;
     for (int i = tid; i < d; i += G1_THREADS) sq[i] = queries[(size_t)q * d + i];
     for (int i = tid; i < ht_size; i += G1_THREADS) hk[i] = 0xffffffffu;
-    for (int i = tid; i < mt_size; i += G1_THREADS) mk[i] = 0xffffffffu;
     if (tid == 0) { s_nwork = 0; s_count = 0; }
     if (warp == 0) probe_meta_warp0(nprobe, max_codes, coarse_i + qo, L, s_c, s_sz, s_inh, lane);
     __syncthreads();
-    const uint32_t hmask = ht_size - 1, mmask = mt_size - 1;
-    // per-list constants and the memo of the coarse stage (its own small table: at most nprobe of 2*nprobe slots)
+    // ---- per-list constants.  The coarse stage already knows d(q, c) of the probed centroids: they enter the
+    // table as done (the reference's query_centroid_dists memo), unless the value is < EPS, which the reference
+    // treats as "not computed" (Q1 iv).  Of a centroid listed twice the last entry counts (it overwrites).
     for (int i = tid; i < nprobe; i += G1_THREADS) {
         const uint32_t c = s_c[i];
         const float v = coarse_d[qo + i];
+        const float cn = L.centroid_norms[c];
         s_alpha[i] = L.alphas[c];
         s_cd[i] = v;
-        s_cn[i] = L.centroid_norms[c];
-        uint32_t p = (c * 2654435761u) & mmask;
-        while (true) {
-            const uint32_t prev = atomicCAS(&mk[p], 0xffffffffu, c);
-            if (prev == 0xffffffffu || prev == c) { mv[p] = v; break; }
-            p = (p + 1) & mmask;
+        s_cn[i] = cn;
+        bool last = true;
+        for (int j = i + 1; j < nprobe; j++) last = last && (s_c[j] != c);
+        uint16_t mp = 0xffffu;
+        if (last && v >= 0.00001f) {
+            uint32_t p = __umulhi(c * 2654435761u, H);
+            while (atomicCAS(&hk[p], 0xffffffffu, c) != 0xffffffffu) p = p + 1 == H ? 0u : p + 1;
+            hv[p] = v;
+            mp = (uint16_t)p;
         }
+        s_mpos[i] = mp;
     }
     __syncthreads();
-    // memoised distance of centroid n, or NaN: absent, or < EPS which the reference treats as "not computed" (Q1 iv)
-    auto memo = [&](uint32_t n) -> float {
-        uint32_t p = (n * 2654435761u) & mmask;
-        while (true) {
-            const uint32_t key = mk[p];
-            if (key == n) { const float v = mv[p]; return v >= 0.00001f ? v : qnan; }
-            if (key == 0xffffffffu) return qnan;
-            p = (p + 1) & mmask;
-        }
-    };
     const int npairs = nprobe * nsubc;
-    // ---- every needed neighbour id enters the table once (loads of 8 pairs in flight per thread)
+    // ---- every needed neighbour id enters the table once (loads of 8 pairs in flight per thread); a pair
+    // remembers its slot, first sightings go to the work list (one counter update per warp)
     for (int e0 = 0; e0 < npairs; e0 += G1_THREADS * 8) {
         uint32_t nn[8];
 #pragma unroll
@@ -272,64 +269,74 @@ __global__ void __launch_bounds__(G1_THREADS) group_g1_kernel(int d, int nprobe,
         }
 #pragma unroll
         for (int u = 0; u < 8; u++) {
+            const int e = e0 + u * G1_THREADS + tid;
             const uint32_t n = nn[u];
-            if (n == 0xffffffffu) continue;
-            const float mvv = memo(n);
-            if (mvv == mvv) continue;      // the coarse stage already knows d(q, n)
-            uint32_t p = (n * 2654435761u) & hmask;
-            while (true) {
-                const uint32_t prev = atomicCAS(&hk[p], 0xffffffffu, n);
-                if (prev == 0xffffffffu) { work[atomicAdd(&s_nwork, 1)] = (uint16_t)p; break; }   // first sight: to compute
-                if (prev == n) break;
-                p = (p + 1) & hmask;
+            uint32_t p = 0xffffu;
+            bool first = false;
+            if (n != 0xffffffffu) {
+                p = __umulhi(n * 2654435761u, H);
+                while (true) {
+                    const uint32_t prev = atomicCAS(&hk[p], 0xffffffffu, n);
+                    if (prev == 0xffffffffu) { first = true; break; }
+                    if (prev == n) break;
+                    p = p + 1 == H ? 0u : p + 1;
+                }
             }
+            const uint32_t fm = __ballot_sync(IVF_FULL_MASK, first);
+            if (fm) {
+                const int leader = __ffs(fm) - 1;
+                int base = 0;
+                if (lane == leader) base = atomicAdd(&s_nwork, __popc(fm));
+                base = __shfl_sync(IVF_FULL_MASK, base, leader);
+                if (first) work[base + __popc(fm & ((1u << lane) - 1u))] = (uint16_t)p;
+            }
+            if (e < npairs) ppos[e] = (uint16_t)p;
         }
     }
     __syncthreads();
     const int nwork = s_nwork;
     if (tid == 0 && rows_counter) atomicAdd(rows_counter, (unsigned long long)nwork);
+    // ---- one thread per distance; the slot then trades the id for the centroid's norm
+    for (int i = tid; i < nprobe; i += G1_THREADS)
+        if (s_mpos[i] != 0xffffu) hk[s_mpos[i]] = __float_as_uint(s_cn[i]);
     for (int w = tid; w < nwork; w += G1_THREADS) {
         const int p = work[w];
-        hv[p] = l2sqr16_thread(sq, L.centroids + (size_t)hk[p] * d, d);
+        const uint32_t n = hk[p];
+#ifdef G1_SKIP_DIST   /* timing experiment only: everything but the row gathers */
+        hv[p] = 1.0f + (float)p;
+#else
+        hv[p] = l2sqr16_thread(sq, L.centroids + (size_t)n * d, d);
+#endif
+        hk[p] = __float_as_uint(__ldg(L.centroid_norms + n));
     }
     __syncthreads();
     // ---- per sub-group: pruning value and base
     uint32_t count = 0;
     for (int e0 = 0; e0 < npairs; e0 += G1_THREADS * 4) {
-        uint32_t nn[4];
+        uint32_t pos[4];
         float icd[4];
 #pragma unroll
         for (int u = 0; u < 4; u++) {
             const int e = e0 + u * G1_THREADS + tid;
-            nn[u] = 0xffffffffu;
+            pos[u] = 0xffffu;
             icd[u] = 0.f;
             if (e < npairs) {
-                const int i = pair_probe(e, nsubc, sub_shift), s = e - i * nsubc;
-                if (s_sz[i] != 0) {
-                    const size_t o = (size_t)s_c[i] * nsubc + s;
-                    const uint32_t ss = __ldg(L.sub_sizes + o);
-                    const uint32_t n = __ldg(L.nn_idx + o);
-                    icd[u] = __ldg(L.icd + o);
-                    if (ss != 0) nn[u] = n;
+                pos[u] = ppos[e];
+                if (pos[u] != 0xffffu) {
+                    const int i = pair_probe(e, nsubc, sub_shift), s = e - i * nsubc;
+                    icd[u] = __ldg(L.icd + (size_t)s_c[i] * nsubc + s);
                 }
             }
         }
-        float cnn[4];
-#pragma unroll
-        for (int u = 0; u < 4; u++) cnn[u] = nn[u] != 0xffffffffu ? __ldg(L.centroid_norms + nn[u]) : 0.f;
 #pragma unroll
         for (int u = 0; u < 4; u++) {
             const int e = e0 + u * G1_THREADS + tid;
             if (e >= npairs) continue;
             float r = qnan, sb = __int_as_float(0x7f800000);
-            if (nn[u] != 0xffffffffu) {
+            if (pos[u] != 0xffffu) {
                 const int i = pair_probe(e, nsubc, sub_shift);
-                float qsd = memo(nn[u]);
-                if (qsd != qsd) {
-                    uint32_t p = (nn[u] * 2654435761u) & hmask;
-                    while (hk[p] != nn[u]) p = (p + 1) & hmask;
-                    qsd = hv[p];
-                }
+                const float qsd = hv[pos[u]];
+                const float cnn = __uint_as_float(hk[pos[u]]);
                 const float alpha = s_alpha[i];
                 const float oma = __fsub_rn(1.f, alpha);
                 // :251-252  (1-a)*d(q,c) - a*((1-a)*d(c,n) - d(q,n))
@@ -341,7 +348,7 @@ __global__ void __launch_bounds__(G1_THREADS) group_g1_kernel(int d, int nprobe,
                 }
                 // :318-322  term1 + term2
                 const float term1 = __fmul_rn(oma, __fsub_rn(s_cd[i], s_cn[i]));
-                const float term2 = __fmul_rn(alpha, __fsub_rn(qsd, cnn[u]));
+                const float term2 = __fmul_rn(alpha, __fsub_rn(qsd, cnn));
                 sb = __fadd_rn(term1, term2);
             }
             T.qsd[(size_t)q * npairs + e] = r;
@@ -499,20 +506,18 @@ cudaError_t launch_prep_grouping(cudaStream_t st, uint64_t *launches, int nq, in
 {
     if (nq == 0) return cudaSuccess;
     const int npairs = nprobe * nsubc;
-    // main table: one slot per (probe, sub-group) pair at most -- it can become full but never overflow
-    // (typical load 20-30 %: the neighbour lists of the probed centroids overlap); memo table: load <= 50 %
-    int ht = 64, mt = 64;
-    while (ht < npairs) ht <<= 1;
-    while (mt < 2 * nprobe) mt <<= 1;
-    if (ht > 65536) return cudaErrorInvalidValue;       // uint16 work list
-    const size_t sm1 = (size_t)d * 4 + (size_t)ht * 8 + (size_t)mt * 8 + (size_t)nprobe * 20 +
-                       (size_t)(npairs + nprobe) * 2 + (size_t)nprobe + 16;
+    // table: the memoised probes + one slot per (probe, sub-group) pair at most + one that stays empty
+    // (typical load 20-30 %: the neighbour lists of the probed centroids overlap)
+    const int ht = npairs + nprobe + 1;
+    if (ht > 65535) return cudaErrorInvalidValue;       // uint16 slot numbers
+    const size_t sm1 = (size_t)d * 4 + (size_t)ht * 8 + (size_t)nprobe * 20 + (size_t)npairs * 4 +
+                       (size_t)nprobe * 2 + (size_t)nprobe + 16;
     cudaError_t e = cudaFuncSetAttribute(group_g1_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sm1);
     if (e != cudaSuccess) return e;
     int sub_shift = -1;
     for (int b = 0; b < 16; b++)
         if ((1 << b) == nsubc) sub_shift = b;
-    group_g1_kernel<<<nq, G1_THREADS, sm1, st>>>(d, nprobe, nsubc, sub_shift, ht, mt, max_codes, do_pruning ? 1 : 0, queries,
+    group_g1_kernel<<<nq, G1_THREADS, sm1, st>>>(d, nprobe, nsubc, sub_shift, ht, max_codes, do_pruning ? 1 : 0, queries,
                                                 coarse_d, coarse_i, L, T, rows_counter);
     ++*launches;
     e = cudaGetLastError();
