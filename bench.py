@@ -37,6 +37,10 @@ WORKLOADS = {
                max_codes=30000, k=10, nq=10000, nlearn=2_000_000, ntrain=65536, lloyd=2, efs=100),
     "c1": dict(kind="sift", nb=1_000_000, d=128, nc=16384, M=8, nsubc=0, pruning=False, opq=False, nprobe=32,
                max_codes=1_000_000, k=10, nq=10000, nlearn=1_000_000, ntrain=65536, lloyd=2, efs=80),
+    # SIFT1B-shape (configs[3]) at 1/10 scale with the list length kept: 100M x 128 over 2^17 centroids gives the
+    # same ~760 codes per list / ~12 per sub-group as 1B over 2^20, same nprobe / max_codes operating point
+    "c4s": dict(kind="sift", nb=100_000_000, d=128, nc=131072, M=16, nsubc=64, pruning=True, opq=True, nprobe=128,
+                max_codes=100000, k=10, nq=10000, nlearn=4_000_000, ntrain=65536, lloyd=2, efs=210),
     "tiny": dict(kind="deep", nb=200_000, d=96, nc=1024, M=16, nsubc=16, pruning=True, opq=False, nprobe=16,
                  max_codes=3000, k=10, nq=1000, nlearn=100_000, ntrain=20000, lloyd=1, efs=64),
 }
@@ -276,6 +280,9 @@ def main():
                            "max_codes=30000, k=10, 10k queries/step (BASELINE configs[1])",
                      "c1": "SIFT-shape 1Mx128, 2^14 centroids, 8-byte PQ, IVFADC, nprobe=32, k=10, 10k queries/step "
                            "(BASELINE configs[0])",
+                     "c4s": "SIFT1B-shape at 1/10 scale, list length kept: 100Mx128, 2^17 centroids, 16-byte OPQ, "
+                            "Grouping(64)+Pruning, nprobe=128, max_codes=100000, k=10, 10k queries/step (BASELINE configs[3] "
+                            "scaled)",
                      "tiny": "tiny development workload"}[args.workload]
     config = {"workload": workload_name, "nb": w["nb"], "d": w["d"], "nc": w["nc"], "code_size": w["M"],
               "nsubc": w["nsubc"], "pruning": w["pruning"], "nprobe": nprobe, "max_codes": w["max_codes"], "k": k,

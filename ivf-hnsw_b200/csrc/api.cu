@@ -1005,7 +1005,7 @@ static int scan_core(ivfhnsw_b200_t *h, size_t nq, size_t k, const float *x_dev,
         CU(launch_lut(st, LAUNCHES, M, nb, d, xq, h->pqc.as<float>(), h->w_lut.as<float>()));
         if (h->debug >= 2) CU(cudaStreamSynchronize(st));   // localise asynchronous kernel faults
         if (h->timing) CU(cudaEventRecord(h->ev[5], st));
-        CU(launch_scan(st, LAUNCHES, M, grouping, nb, d, nprobe, nsubc, (int)k, nsplit, h->w_lut.as<float>(),
+        CU(launch_scan(st, LAUNCHES, M, grouping, nb, d, nprobe, nsubc, h->do_pruning, (int)k, nsplit, h->w_lut.as<float>(),
                        h->norm_table.as<float>(), L, T, (uint32_t)h->c_begin, (uint32_t)h->c_end, pd, ps, pl,
                        out_d + q0 * k, out_l + q0 * k, out_seq ? out_seq + q0 * k : nullptr));
         if (h->debug >= 2) CU(cudaStreamSynchronize(st));

@@ -12,8 +12,9 @@
 #define SCAN_THREADS 256
 #define SCAN_WARPS 8
 #define SCAN_CHUNK 32                      // codes per warp step (one per lane)
-#define SCAN_PIECE_CHUNKS 4                // chunks a warp keeps in flight
-#define SCAN_PIECE (SCAN_CHUNK * SCAN_PIECE_CHUNKS)
+#define SCAN_PF 4                          // warp steps (32 codes each) whose loads are in flight together
+#define SCAN_SEG 1024                      // list positions per work item
+#define SCAN_WBUF (SCAN_SEG / 16)          // windows of a work item (a run list is used only when shorter than that)
 #define SCAN_WCAP 64                       // per-warp candidate buffer entries
 
 // coarse stage geometry: centroids are processed in groups of COARSE_GROUP, the

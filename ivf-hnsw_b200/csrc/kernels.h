@@ -67,7 +67,7 @@ size_t scan_smem_bytes(int M, int nprobe, int k, int nsubc);
 cudaError_t launch_lut(cudaStream_t st, uint64_t *launches, int M, int nq, int d, const float *queries,
                        const float *pqc, float *lutc);
 cudaError_t launch_scan(cudaStream_t st, uint64_t *launches, int M, bool grouping, int nq, int d, int nprobe,
-                        int nsubc, int k, int nsplit, const float *lutc, const float *norm_table,
+                        int nsubc, bool pruned, int k, int nsplit, const float *lutc, const float *norm_table,
                         const DeviceLists &L, const SegTables &T, uint32_t c_begin, uint32_t c_end, float *part_d,
                         uint32_t *part_seq, uint32_t *part_slot, float *out_d, int64_t *out_labels, uint32_t *out_seq);
 cudaError_t launch_merge(cudaStream_t st, uint64_t *launches, int nq, int k, int nsplit, const float *part_d,

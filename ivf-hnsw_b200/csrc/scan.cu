@@ -669,6 +669,7 @@ cudaError_t launch_lut(cudaStream_t st, uint64_t *launches, int M, int nq, int d
 // =============================================================================================
 struct ScanArgs {
     int d, nprobe, nsubc, k, nsplit;
+    int pruned;               // Grouping: sub-groups may be pruned (sub_base = +inf) -> tile kept runs only
     const float *lutc;        // [nq][256][M] compact tables from K-L1
     const float *norm_table;  // [256]
     DeviceLists L;
@@ -697,7 +698,7 @@ static __host__ __device__ inline int scan_kpl(int k) { return k <= 32 ? 1 : (k 
 static __host__ __device__ inline size_t scan_small_smem(int nprobe, int k, int nsubc)
 {
     size_t b = 0;
-    b += (size_t)(5 * nprobe + 1) * 4;          // segment tables
+    b += (size_t)(6 * nprobe + 1) * 4;          // segment tables
     if (scan_kpl(k)) {
         b += (size_t)SCAN_WARPS * k * 12;     // the warps' sorted lists, for the final merge
         if (scan_kpl(k) == 1) b += (size_t)SCAN_WARPS * 32 * 8;   // warp candidate batches (SCAN_BCAP)
@@ -706,6 +707,7 @@ static __host__ __device__ inline size_t scan_small_smem(int nprobe, int k, int 
         b += (size_t)SCAN_WARPS * SCAN_WCAP * 12;   // warp candidate buffers
     }
     b += (size_t)SCAN_WARPS * nsubc * 4;        // warp sub-group bases
+    b += (size_t)SCAN_WARPS * SCAN_WBUF * 4;    // warp window lists
     b += 64;                                    // control words
     return (b + 15) & ~(size_t)15;
 }
@@ -917,6 +919,7 @@ __global__ void __launch_bounds__(SCAN_THREADS) scan_kernel(ScanArgs a)
     float *s_base = reinterpret_cast<float *>(p); p += a.nprobe * 4;
     uint32_t *s_seq = reinterpret_cast<uint32_t *>(p); p += a.nprobe * 4;
     uint32_t *s_poff = reinterpret_cast<uint32_t *>(p); p += (a.nprobe + 1) * 4;
+    uint32_t *s_cid = reinterpret_cast<uint32_t *>(p); p += a.nprobe * 4;
     // KPL > 0: [SCAN_WARPS][k] sorted warp lists; KPL == 0: CTA top-k followed by the warp buffers
     const int nres = KPL > 0 ? SCAN_WARPS * a.k : a.k;
     float *topk_d = reinterpret_cast<float *>(p); p += nres * 4;
@@ -933,6 +936,7 @@ __global__ void __launch_bounds__(SCAN_THREADS) scan_kernel(ScanArgs a)
         wbuf_seq = reinterpret_cast<uint32_t *>(p); p += SCAN_WARPS * SCAN_BCAP * 4;
     }
     float *wsub_all = reinterpret_cast<float *>(p); p += SCAN_WARPS * a.nsubc * 4;
+    uint32_t *wbuf_all = reinterpret_cast<uint32_t *>(p); p += SCAN_WARPS * SCAN_WBUF * 4;
     p = reinterpret_cast<uint8_t *>((reinterpret_cast<uintptr_t>(p) + 15) & ~(uintptr_t)15);
     volatile ScanCtl *ctl = reinterpret_cast<volatile ScanCtl *>(p);
 
@@ -950,6 +954,7 @@ __global__ void __launch_bounds__(SCAN_THREADS) scan_kernel(ScanArgs a)
             s_n[i] = (c >= a.c_begin && c < a.c_end) ? r_n[i] : 0u;
             s_base[i] = r_base[i];
             s_seq[i] = r_seq[i];
+            s_cid[i] = c;
         }
         if (KPL == 0) {
             for (int e = tid; e < k; e += SCAN_THREADS) {
@@ -968,12 +973,12 @@ __global__ void __launch_bounds__(SCAN_THREADS) scan_kernel(ScanArgs a)
         }
     }
     __syncthreads();
-    // exclusive prefix of the pieces (ceil(n / SCAN_PIECE)) of the kept lists
+    // exclusive prefix of the work items (ceil(n / SCAN_SEG) parts) of the kept lists
     if (warp == 0) {
         uint32_t run = 0;
         for (int b = 0; b < nprobe; b += 32) {
             const int i = b + lane;
-            const uint32_t pieces = i < nprobe ? (s_n[i] + SCAN_PIECE - 1) / SCAN_PIECE : 0u;
+            const uint32_t pieces = i < nprobe ? (s_n[i] + SCAN_SEG - 1) / SCAN_SEG : 0u;
             uint32_t incl = pieces;
 #pragma unroll
             for (int off = 1; off < 32; off <<= 1) {
@@ -1049,7 +1054,18 @@ __global__ void __launch_bounds__(SCAN_THREADS) scan_kernel(ScanArgs a)
     float *wsub = wsub_all + warp * a.nsubc;
     int wcount = 0;
 
-    // ---- K-S: pull pieces
+    // ---- K-S: pull work items = (list, SCAN_SEG-position part of it).  A part is processed as a sequence of
+    // WINDOWS of W consecutive list positions; a window may start at any position: lane l takes the position p
+    // of the window with p % W == l % W, so that (slot % ML) == (l % ML) and the table gathers stay conflict
+    // free (list starts are aligned).  M <= 16: two 16-wide windows per warp step (one per half warp);
+    // M >= 32: one 32-wide window.  Without pruning the windows tile the part; with pruning (Grouping) only
+    // the maximal runs of kept sub-groups are tiled, each from its own start, so pruned codes are neither
+    // loaded nor evaluated.
+    constexpr int W = M >= 32 ? 32 : 16;
+    constexpr int WPS = 32 / W;
+    const int half = (W == 16) ? (lane >> 4) : 0;
+    uint32_t *wbuf = wbuf_all + warp * SCAN_WBUF;
+    float thr_f = FLT_MAX;   // prefilter: min(own k-th best, bound shared by the CTA); ties pass, exact test follows
     while (has_work) {
         int pc = 0;
         if (lane == 0) pc = atomicAdd((int *)&ctl->piece_ctr, 1);
@@ -1063,132 +1079,226 @@ __global__ void __launch_bounds__(SCAN_THREADS) scan_kernel(ScanArgs a)
             seg += __popc(__ballot_sync(IVF_FULL_MASK, le));
         }
         seg -= 1;
-        const int pk = piece - (int)s_poff[seg];
-        const int rem = (int)s_n[seg] - pk * SCAN_PIECE;   // > 0
-        const uint32_t slot0 = s_slot[seg] + (uint32_t)pk * SCAN_PIECE;
-        const uint32_t seq0 = s_seq[seg] + (uint32_t)pk * SCAN_PIECE;
-        float base = s_base[seg];
+        const uint32_t lo = (uint32_t)(piece - (int)s_poff[seg]) * SCAN_SEG;
+        const uint32_t hi = min(s_n[seg], lo + SCAN_SEG);
+        const uint32_t lslot = s_slot[seg], lseq = s_seq[seg];
+        const float base = s_base[seg];
+        int nwin = (int)((hi - lo + W - 1) / W);
+        bool runs = false;
         // sub-group bases of this list: up to 64 sub-groups live in two registers per lane and are fetched
-        // with a shuffle (their loads overlap the code loads below); more go through shared memory
+        // with a shuffle; more go through shared memory
         float sb0 = 0.f, sb1 = 0.f;
         const bool sb_regs = a.nsubc <= 64;
         if (GROUPING) {
+            const float pinf = __int_as_float(0x7f800000);
             const float *sbg = a.T.sub_base(q) + (size_t)seg * a.nsubc;
             if (sb_regs) {
-                sb0 = lane < a.nsubc ? __ldg(sbg + lane) : __int_as_float(0x7f800000);
-                sb1 = lane + 32 < a.nsubc ? __ldg(sbg + lane + 32) : __int_as_float(0x7f800000);
+                sb0 = lane < a.nsubc ? __ldg(sbg + lane) : pinf;
+                sb1 = lane + 32 < a.nsubc ? __ldg(sbg + lane + 32) : pinf;
+                if (W == 16 && a.pruned && hi < (1u << 27)) {
+                    // positions of the sub-groups inside the list (lane: sub-groups lane and lane + 32)
+                    const uint32_t *szg = a.L.sub_sizes + (size_t)s_cid[seg] * a.nsubc;
+                    const uint32_t sz0 = lane < a.nsubc ? __ldg(szg + lane) : 0u;
+                    const uint32_t sz1 = lane + 32 < a.nsubc ? __ldg(szg + lane + 32) : 0u;
+                    uint32_t in0 = sz0, in1 = sz1;
+#pragma unroll
+                    for (int off = 1; off < 32; off <<= 1) {
+                        const uint32_t t0 = __shfl_up_sync(IVF_FULL_MASK, in0, off);
+                        const uint32_t t1 = __shfl_up_sync(IVF_FULL_MASK, in1, off);
+                        if (lane >= off) { in0 += t0; in1 += t1; }
+                    }
+                    in1 += __shfl_sync(IVF_FULL_MASK, in0, 31);
+                    const uint32_t o0 = max(in0 - sz0, lo), e0 = min(in0, hi);
+                    const uint32_t o1 = max(in1 - sz1, lo), e1 = min(in1, hi);
+                    const bool ne0 = o0 < e0, ne1 = o1 < e1;             // has codes inside the part
+                    const bool k0 = ne0 && sb0 < pinf, k1 = ne1 && sb1 < pinf;   // ... and is kept
+                    // run start = end of the last pruned code before the sub-group (exclusive prefix max),
+                    // run end = first pruned code after it (exclusive suffix min)
+                    uint32_t pm0 = (ne0 && !k0) ? e0 : lo, pm1 = (ne1 && !k1) ? e1 : lo;
+                    uint32_t sm0 = (ne0 && !k0) ? o0 : hi, sm1 = (ne1 && !k1) ? o1 : hi;
+#pragma unroll
+                    for (int off = 1; off < 32; off <<= 1) {
+                        const uint32_t t0 = __shfl_up_sync(IVF_FULL_MASK, pm0, off);
+                        const uint32_t t1 = __shfl_up_sync(IVF_FULL_MASK, pm1, off);
+                        const uint32_t u0 = __shfl_down_sync(IVF_FULL_MASK, sm0, off);
+                        const uint32_t u1 = __shfl_down_sync(IVF_FULL_MASK, sm1, off);
+                        if (lane >= off) { pm0 = max(pm0, t0); pm1 = max(pm1, t1); }
+                        if (lane + off < 32) { sm0 = min(sm0, u0); sm1 = min(sm1, u1); }
+                    }
+                    const uint32_t tm0 = __shfl_sync(IVF_FULL_MASK, pm0, 31);
+                    const uint32_t tn1 = __shfl_sync(IVF_FULL_MASK, sm1, 0);
+                    uint32_t rs0 = __shfl_up_sync(IVF_FULL_MASK, pm0, 1), rs1 = __shfl_up_sync(IVF_FULL_MASK, pm1, 1);
+                    uint32_t re0 = __shfl_down_sync(IVF_FULL_MASK, sm0, 1), re1 = __shfl_down_sync(IVF_FULL_MASK, sm1, 1);
+                    if (lane == 0) { rs0 = lo; rs1 = lo; }
+                    if (lane == 31) { re0 = hi; re1 = hi; }
+                    rs1 = max(rs1, tm0);
+                    re0 = min(re0, tn1);
+                    // windows of the run's 16-grid that start inside the sub-group
+                    const uint32_t f0 = rs0 + ((o0 - rs0 + 15u) & ~15u), f1 = rs1 + ((o1 - rs1 + 15u) & ~15u);
+                    const uint32_t c0 = (k0 && f0 < e0) ? ((e0 - f0 + 15u) >> 4) : 0u;
+                    const uint32_t c1 = (k1 && f1 < e1) ? ((e1 - f1 + 15u) >> 4) : 0u;
+                    uint32_t ic = c0 | (c1 << 16);       // both counts in one scan (<= SCAN_SEG / 16 + 32 each)
+#pragma unroll
+                    for (int off = 1; off < 32; off <<= 1) {
+                        const uint32_t t = __shfl_up_sync(IVF_FULL_MASK, ic, off);
+                        if (lane >= off) ic += t;
+                    }
+                    const uint32_t tot = __shfl_sync(IVF_FULL_MASK, ic, 31);
+                    const int total = (int)((tot & 0xffffu) + (tot >> 16));
+                    if (total < nwin) {      // else: walking the whole part costs no more
+                        runs = true;
+                        nwin = total;
+                        const uint32_t i0 = (ic & 0xffffu) - c0, i1 = (tot & 0xffffu) + (ic >> 16) - c1;
+                        __syncwarp();
+                        for (uint32_t t = 0; t < c0; t++) {
+                            const uint32_t p0 = f0 + 16u * t;
+                            wbuf[i0 + t] = p0 | (min(16u, re0 - p0) << 27);
+                        }
+                        for (uint32_t t = 0; t < c1; t++) {
+                            const uint32_t p1 = f1 + 16u * t;
+                            wbuf[i1 + t] = p1 | (min(16u, re1 - p1) << 27);
+                        }
+                        __syncwarp();
+                    }
+                }
             } else {
                 __syncwarp();
                 for (int s = lane; s < a.nsubc; s += 32) wsub[s] = sbg[s];
                 __syncwarp();
             }
         }
-
-        // issue every load of the piece before the first use
-        uint32_t cw[SCAN_PIECE_CHUNKS][C::NW];
-        uint32_t nm[SCAN_PIECE_CHUNKS], sid[SCAN_PIECE_CHUNKS];
-#pragma unroll
-        for (int c = 0; c < SCAN_PIECE_CHUNKS; c++) {
-            if (c * SCAN_CHUNK < rem) {
-                const uint32_t slot = slot0 + c * SCAN_CHUNK + lane;
-                const uint8_t *cp = a.L.codes + (size_t)slot * M;
-                if (M == 8) {
-                    const uint2 v = ldg_stream_64(cp);
-                    cw[c][0] = v.x; cw[c][1] = v.y;
-                } else {
-#pragma unroll
-                    for (int w4 = 0; w4 < C::NW / 4; w4++) {
-                        const uint4 v = ldg_stream_128(cp + w4 * 16);
-                        cw[c][w4 * 4 + 0] = v.x; cw[c][w4 * 4 + 1] = v.y;
-                        cw[c][w4 * 4 + 2] = v.z; cw[c][w4 * 4 + 3] = v.w;
-                    }
-                }
-                nm[c] = ldg_stream_u8(a.L.norm_codes + slot);
-                sid[c] = GROUPING ? ldg_stream_u8(a.L.sub_ids + slot) : 0u;
-            }
+        if (KPL == 1 || KPL > 0) {
+            const uint32_t sh = ctl->thr_key;
+            const uint32_t fb = (sh & 0x80000000u) ? (sh ^ 0x80000000u) : ~sh;   // inverse of fkey_u32
+            thr_f = fminf(KPL == 1 ? bl.thr_d : wl.thr_d, __uint_as_float(fb));
         }
+
+        const int nsteps = (nwin + WPS - 1) / WPS;
+        for (int j0 = 0; j0 < nsteps; j0 += SCAN_PF) {
+            // issue every load of SCAN_PF steps before the first use
+            uint32_t cw[SCAN_PF][C::NW];
+            uint32_t nm[SCAN_PF], sid[SCAN_PF], posv[SCAN_PF];
 #pragma unroll
-        for (int c = 0; c < SCAN_PIECE_CHUNKS; c++) {
-            if (c * SCAN_CHUNK < rem) {   // warp-uniform
-                float acc0 = base;
-                if (GROUPING) {
-                    if (sb_regs) {
-                        const float v0 = __shfl_sync(IVF_FULL_MASK, sb0, sid[c] & 31);
-                        const float v1 = __shfl_sync(IVF_FULL_MASK, sb1, sid[c] & 31);
-                        acc0 = (sid[c] & 32) ? v1 : v0;
-                    } else acc0 = wsub[sid[c]];
+            for (int c = 0; c < SCAN_PF; c++) {
+                const int wi = (j0 + c) * WPS + half;
+                uint32_t start = 0, len = 0;
+                if (wi < nwin) {
+                    if (runs) {
+                        const uint32_t w = wbuf[wi];
+                        start = w & 0x7ffffffu;
+                        len = w >> 27;
+                    } else {
+                        start = lo + (uint32_t)wi * W;
+                        len = min((uint32_t)W, hi - start);
+                    }
                 }
-                float acc1;
-                if (M == 64) acc1 = *reinterpret_cast<const float *>(lut + 65536 + nm[c] * 128u + 4u * lane);
-                else acc1 = *reinterpret_cast<const float *>(lut + prmt(nm[c], Onorm, 0x5504u));
+                const uint32_t rot = ((uint32_t)lane - start) & (W - 1);
+                const bool valid = rot < len;
+                posv[c] = valid ? start + rot : 0xffffffffu;
+                nm[c] = 0;
+                sid[c] = 0;
+                if (valid) {
+                    const uint32_t slot = lslot + start + rot;
+                    const uint8_t *cp = a.L.codes + (size_t)slot * M;
+                    if (M == 8) {
+                        const uint2 v = ldg_stream_64(cp);
+                        cw[c][0] = v.x; cw[c][1] = v.y;
+                    } else {
 #pragma unroll
-                for (int t = 0; t < M; t++) {
-                    const int b = t & 3;
-                    const uint32_t sel = 0xCC00u | (uint32_t)(b << 4) | (uint32_t)(4 + b);
-                    const uint32_t addr = prmt(cw[c][t >> 2], O[(t & (C::ML - 1)) >> 2], sel);
-                    const float v = *reinterpret_cast<const float *>(lut + (t >= 32 ? 128 : 0) + addr);
-                    if (t & 1) acc1 += v; else acc0 += v;
+                        for (int w4 = 0; w4 < C::NW / 4; w4++) {
+                            const uint4 v = ldg_stream_128(cp + w4 * 16);
+                            cw[c][w4 * 4 + 0] = v.x; cw[c][w4 * 4 + 1] = v.y;
+                            cw[c][w4 * 4 + 2] = v.z; cw[c][w4 * 4 + 3] = v.w;
+                        }
+                    }
+                    nm[c] = ldg_stream_u8(a.L.norm_codes + slot);
+                    if (GROUPING) sid[c] = ldg_stream_u8(a.L.sub_ids + slot);
                 }
-                const float dist = acc0 + acc1;
-                const bool valid = (c * SCAN_CHUNK + lane) < rem;
-                if (KPL == 1) {
-                    const uint32_t sh = ctl->thr_key;   // bound shared by the warps of the CTA (ties pass)
-                    const uint32_t myseq = seq0 + c * SCAN_CHUNK + lane;
-                    bool pass = valid && fkey_u32(dist) <= sh && key_less(dist, myseq, bl.thr_d, bl.thr_s);
-                    uint32_t bal = __ballot_sync(IVF_FULL_MASK, pass);
-                    if (bal) {
-                        int n = __popc(bal);
-                        if (wcount + n > SCAN_BCAP) {
-                            bl.flush(wd, wseq, wcount, lane, k);
-                            wcount = 0;
-                            if (lane == 0 && bl.thr_d < FLT_MAX) atomicMin((uint32_t *)&ctl->thr_key, fkey_u32(bl.thr_d));
-                            pass = pass && key_less(dist, myseq, bl.thr_d, bl.thr_s);
-                            bal = __ballot_sync(IVF_FULL_MASK, pass);
-                            n = __popc(bal);
-                        }
-                        if (pass) {
-                            const int pos = wcount + __popc(bal & ((1u << lane) - 1u));
-                            wd[pos] = dist;
-                            wseq[pos] = myseq;
-                        }
-                        wcount += n;
+            }
+#pragma unroll
+            for (int c = 0; c < SCAN_PF; c++) {
+                if (j0 + c < nsteps) {   // warp-uniform
+                    float acc0 = base;
+                    if (GROUPING) {
+                        if (sb_regs) {
+                            const float v0 = __shfl_sync(IVF_FULL_MASK, sb0, sid[c] & 31);
+                            const float v1 = __shfl_sync(IVF_FULL_MASK, sb1, sid[c] & 31);
+                            acc0 = (sid[c] & 32) ? v1 : v0;
+                        } else acc0 = wsub[sid[c]];
                     }
-                } else if (KPL > 0) {
-                    const uint32_t sh = ctl->thr_key;   // bound shared by the warps of the CTA (ties pass)
-                    const uint32_t myseq = seq0 + c * SCAN_CHUNK + lane;
-                    const bool pass = valid && fkey_u32(dist) <= sh && key_less(dist, myseq, wl.thr_d, wl.thr_s);
-                    uint32_t bal = __ballot_sync(IVF_FULL_MASK, pass);
-                    if (bal) {
-                        do {
-                            const int src = __ffs(bal) - 1;
-                            bal &= bal - 1;
-                            const float xd = __shfl_sync(IVF_FULL_MASK, dist, src);
-                            const uint32_t xs = seq0 + c * SCAN_CHUNK + src;
-                            if (key_less(xd, xs, wl.thr_d, wl.thr_s))   // warp-uniform
-                                wl.insert(xd, xs, slot0 + c * SCAN_CHUNK + src, lane, k);
-                        } while (bal);
-                        if (lane == 0 && wl.thr_d < FLT_MAX) atomicMin((uint32_t *)&ctl->thr_key, fkey_u32(wl.thr_d));
+                    float acc1;
+                    if (M == 64) acc1 = *reinterpret_cast<const float *>(lut + 65536 + nm[c] * 128u + 4u * lane);
+                    else acc1 = *reinterpret_cast<const float *>(lut + prmt(nm[c], Onorm, 0x5504u));
+#pragma unroll
+                    for (int t = 0; t < M; t++) {
+                        const int b = t & 3;
+                        const uint32_t sel = 0xCC00u | (uint32_t)(b << 4) | (uint32_t)(4 + b);
+                        const uint32_t addr = prmt(cw[c][t >> 2], O[(t & (C::ML - 1)) >> 2], sel);
+                        const float v = *reinterpret_cast<const float *>(lut + (t >= 32 ? 128 : 0) + addr);
+                        if (t & 1) acc1 += v; else acc0 += v;
                     }
-                } else {
-                    const float thr = ctl->worst_d;
-                    bool pass = valid && dist <= thr;
-                    uint32_t bal = __ballot_sync(IVF_FULL_MASK, pass);
-                    if (bal) {
-                        int n = __popc(bal);
-                        if (wcount + n > SCAN_WCAP) {
-                            flush_candidates(ctl, topk_d, topk_seq, topk_slot, k, wd, wseq, wslot, wcount, lane);
-                            wcount = 0;
-                            pass = valid && dist <= ctl->worst_d;
-                            bal = __ballot_sync(IVF_FULL_MASK, pass);
-                            n = __popc(bal);
+                    const float dist = acc0 + acc1;
+                    const bool valid = posv[c] != 0xffffffffu;
+                    if (KPL == 1) {
+                        if (__any_sync(IVF_FULL_MASK, valid && dist <= thr_f)) {
+                            const uint32_t myseq = lseq + posv[c];
+                            bool pass = valid && dist <= thr_f && key_less(dist, myseq, bl.thr_d, bl.thr_s);
+                            uint32_t bal = __ballot_sync(IVF_FULL_MASK, pass);
+                            if (bal) {
+                                int n = __popc(bal);
+                                if (wcount + n > SCAN_BCAP) {
+                                    bl.flush(wd, wseq, wcount, lane, k);
+                                    wcount = 0;
+                                    if (lane == 0 && bl.thr_d < FLT_MAX)
+                                        atomicMin((uint32_t *)&ctl->thr_key, fkey_u32(bl.thr_d));
+                                    thr_f = fminf(thr_f, bl.thr_d);
+                                    pass = pass && key_less(dist, myseq, bl.thr_d, bl.thr_s);
+                                    bal = __ballot_sync(IVF_FULL_MASK, pass);
+                                    n = __popc(bal);
+                                }
+                                if (pass) {
+                                    const int pos = wcount + __popc(bal & ((1u << lane) - 1u));
+                                    wd[pos] = dist;
+                                    wseq[pos] = myseq;
+                                }
+                                wcount += n;
+                            }
                         }
-                        if (pass) {
-                            const int pos = wcount + __popc(bal & ((1u << lane) - 1u));
-                            wd[pos] = dist;
-                            wseq[pos] = seq0 + c * SCAN_CHUNK + lane;
-                            wslot[pos] = slot0 + c * SCAN_CHUNK + lane;
+                    } else if (KPL > 0) {
+                        uint32_t bal = __ballot_sync(IVF_FULL_MASK, valid && dist <= thr_f);
+                        if (bal) {
+                            do {
+                                const int src = __ffs(bal) - 1;
+                                bal &= bal - 1;
+                                const float xd = __shfl_sync(IVF_FULL_MASK, dist, src);
+                                const uint32_t xp = __shfl_sync(IVF_FULL_MASK, posv[c], src);
+                                if (key_less(xd, lseq + xp, wl.thr_d, wl.thr_s))   // warp-uniform
+                                    wl.insert(xd, lseq + xp, lslot + xp, lane, k);
+                            } while (bal);
+                            if (lane == 0 && wl.thr_d < FLT_MAX) atomicMin((uint32_t *)&ctl->thr_key, fkey_u32(wl.thr_d));
+                            thr_f = fminf(thr_f, wl.thr_d);
                         }
-                        wcount += n;
+                    } else {
+                        const float thr = ctl->worst_d;
+                        bool pass = valid && dist <= thr;
+                        uint32_t bal = __ballot_sync(IVF_FULL_MASK, pass);
+                        if (bal) {
+                            int n = __popc(bal);
+                            if (wcount + n > SCAN_WCAP) {
+                                flush_candidates(ctl, topk_d, topk_seq, topk_slot, k, wd, wseq, wslot, wcount, lane);
+                                wcount = 0;
+                                pass = valid && dist <= ctl->worst_d;
+                                bal = __ballot_sync(IVF_FULL_MASK, pass);
+                                n = __popc(bal);
+                            }
+                            if (pass) {
+                                const int pos = wcount + __popc(bal & ((1u << lane) - 1u));
+                                wd[pos] = dist;
+                                wseq[pos] = lseq + posv[c];
+                                wslot[pos] = lslot + posv[c];
+                            }
+                            wcount += n;
+                        }
                     }
                 }
             }
@@ -1310,13 +1420,14 @@ static cudaError_t launch_scan_k(cudaStream_t st, int nq, const ScanArgs &a)
 }
 
 cudaError_t launch_scan(cudaStream_t st, uint64_t *launches, int M, bool grouping, int nq, int d, int nprobe,
-                        int nsubc, int k, int nsplit, const float *lutc, const float *norm_table,
+                        int nsubc, bool pruned, int k, int nsplit, const float *lutc, const float *norm_table,
                         const DeviceLists &L, const SegTables &T, uint32_t c_begin, uint32_t c_end, float *part_d,
                         uint32_t *part_seq, uint32_t *part_slot, float *out_d, int64_t *out_labels, uint32_t *out_seq)
 {
     if (nq == 0) return cudaSuccess;
     ScanArgs a;
     a.out_seq = out_seq;
+    a.pruned = (grouping && pruned) ? 1 : 0;
     a.d = d; a.nprobe = nprobe; a.nsubc = grouping ? nsubc : 0; a.k = k; a.nsplit = nsplit;
     a.lutc = lutc; a.norm_table = norm_table; a.L = L; a.T = T; a.c_begin = c_begin; a.c_end = c_end;
     a.part_d = part_d; a.part_seq = part_seq; a.part_slot = part_slot; a.out_d = out_d; a.out_labels = out_labels;
