@@ -14,6 +14,7 @@
 #define SCAN_CHUNK 32                      // codes per warp step (one per lane)
 #define SCAN_PF 4                          // warp steps (32 codes each) whose loads are in flight together
 #define SCAN_SEG 1024                      // list positions per work item
+#define SCAN_ITEMS 256                     // work items whose (list, part) is tabulated
 #define SCAN_WBUF (SCAN_SEG / 16)          // windows of a work item (a run list is used only when shorter than that)
 #define SCAN_WCAP 64                       // per-warp candidate buffer entries
 

@@ -23,6 +23,7 @@
 // CTA's top-k under a lock only when the buffer fills (rare once the threshold has dropped).
 #include "common.cuh"
 #include "kernels.h"
+#include <type_traits>
 
 namespace ivfb200 {
 
@@ -698,7 +699,7 @@ static __host__ __device__ inline int scan_kpl(int k) { return k <= 32 ? 1 : (k 
 static __host__ __device__ inline size_t scan_small_smem(int nprobe, int k, int nsubc)
 {
     size_t b = 0;
-    b += (size_t)(6 * nprobe + 1) * 4;          // segment tables
+    b += (size_t)(6 * nprobe + 1 + SCAN_ITEMS) * 4;   // segment tables, item table
     if (scan_kpl(k)) {
         b += (size_t)SCAN_WARPS * k * 12;     // the warps' sorted lists, for the final merge
         if (scan_kpl(k) == 1) b += (size_t)SCAN_WARPS * 32 * 8;   // warp candidate batches (SCAN_BCAP)
@@ -706,7 +707,7 @@ static __host__ __device__ inline size_t scan_small_smem(int nprobe, int k, int 
         b += (size_t)k * 12;                        // top-k
         b += (size_t)SCAN_WARPS * SCAN_WCAP * 12;   // warp candidate buffers
     }
-    b += (size_t)SCAN_WARPS * nsubc * 4;        // warp sub-group bases
+    if (nsubc > 64) b += (size_t)SCAN_WARPS * nsubc * 4;   // warp sub-group bases (<= 64 live in registers)
     b += (size_t)SCAN_WARPS * SCAN_WBUF * 4;    // warp window lists
     b += 64;                                    // control words
     return (b + 15) & ~(size_t)15;
@@ -920,6 +921,7 @@ __global__ void __launch_bounds__(SCAN_THREADS) scan_kernel(ScanArgs a)
     uint32_t *s_seq = reinterpret_cast<uint32_t *>(p); p += a.nprobe * 4;
     uint32_t *s_poff = reinterpret_cast<uint32_t *>(p); p += (a.nprobe + 1) * 4;
     uint32_t *s_cid = reinterpret_cast<uint32_t *>(p); p += a.nprobe * 4;
+    uint32_t *s_item = reinterpret_cast<uint32_t *>(p); p += SCAN_ITEMS * 4;
     // KPL > 0: [SCAN_WARPS][k] sorted warp lists; KPL == 0: CTA top-k followed by the warp buffers
     const int nres = KPL > 0 ? SCAN_WARPS * a.k : a.k;
     float *topk_d = reinterpret_cast<float *>(p); p += nres * 4;
@@ -935,7 +937,7 @@ __global__ void __launch_bounds__(SCAN_THREADS) scan_kernel(ScanArgs a)
         wbuf_d = reinterpret_cast<float *>(p); p += SCAN_WARPS * SCAN_BCAP * 4;
         wbuf_seq = reinterpret_cast<uint32_t *>(p); p += SCAN_WARPS * SCAN_BCAP * 4;
     }
-    float *wsub_all = reinterpret_cast<float *>(p); p += SCAN_WARPS * a.nsubc * 4;
+    float *wsub_all = reinterpret_cast<float *>(p); p += (a.nsubc > 64 ? SCAN_WARPS * a.nsubc * 4 : 0);
     uint32_t *wbuf_all = reinterpret_cast<uint32_t *>(p); p += SCAN_WARPS * SCAN_WBUF * 4;
     p = reinterpret_cast<uint8_t *>((reinterpret_cast<uintptr_t>(p) + 15) & ~(uintptr_t)15);
     volatile ScanCtl *ctl = reinterpret_cast<volatile ScanCtl *>(p);
@@ -989,6 +991,12 @@ __global__ void __launch_bounds__(SCAN_THREADS) scan_kernel(ScanArgs a)
             run += __shfl_sync(IVF_FULL_MASK, incl, 31);
         }
         if (lane == 0) s_poff[nprobe] = run;
+        __syncwarp();
+        // item -> (list, part) table for the first SCAN_ITEMS items (later ones are found by search)
+        for (int i = lane; i < nprobe; i += 32) {
+            const uint32_t p0 = s_poff[i], p1 = s_poff[i + 1];
+            for (uint32_t t = p0; t < p1 && t < SCAN_ITEMS; t++) s_item[t] = (uint32_t)i | ((t - p0) << 16);
+        }
     }
     __syncthreads();
     const int npieces = (int)s_poff[nprobe];
@@ -1073,13 +1081,20 @@ __global__ void __launch_bounds__(SCAN_THREADS) scan_kernel(ScanArgs a)
         const int piece = pc * a.nsplit + split;
         if (piece >= npieces) break;
         int seg = 0;
-        for (int b = 0; b < nprobe; b += 32) {
-            const int i = b + lane;
-            const bool le = (i < nprobe) && ((int)s_poff[i] <= piece);
-            seg += __popc(__ballot_sync(IVF_FULL_MASK, le));
+        uint32_t lo;
+        if (piece < SCAN_ITEMS) {
+            const uint32_t it = s_item[piece];
+            seg = (int)(it & 0xffffu);
+            lo = (it >> 16) * SCAN_SEG;
+        } else {
+            for (int b = 0; b < nprobe; b += 32) {
+                const int i = b + lane;
+                const bool le = (i < nprobe) && ((int)s_poff[i] <= piece);
+                seg += __popc(__ballot_sync(IVF_FULL_MASK, le));
+            }
+            seg -= 1;
+            lo = (uint32_t)(piece - (int)s_poff[seg]) * SCAN_SEG;
         }
-        seg -= 1;
-        const uint32_t lo = (uint32_t)(piece - (int)s_poff[seg]) * SCAN_SEG;
         const uint32_t hi = min(s_n[seg], lo + SCAN_SEG);
         const uint32_t lslot = s_slot[seg], lseq = s_seq[seg];
         const float base = s_base[seg];
@@ -1112,27 +1127,22 @@ __global__ void __launch_bounds__(SCAN_THREADS) scan_kernel(ScanArgs a)
                     const uint32_t o1 = max(in1 - sz1, lo), e1 = min(in1, hi);
                     const bool ne0 = o0 < e0, ne1 = o1 < e1;             // has codes inside the part
                     const bool k0 = ne0 && sb0 < pinf, k1 = ne1 && sb1 < pinf;   // ... and is kept
-                    // run start = end of the last pruned code before the sub-group (exclusive prefix max),
-                    // run end = first pruned code after it (exclusive suffix min)
-                    uint32_t pm0 = (ne0 && !k0) ? e0 : lo, pm1 = (ne1 && !k1) ? e1 : lo;
-                    uint32_t sm0 = (ne0 && !k0) ? o0 : hi, sm1 = (ne1 && !k1) ? o1 : hi;
-#pragma unroll
-                    for (int off = 1; off < 32; off <<= 1) {
-                        const uint32_t t0 = __shfl_up_sync(IVF_FULL_MASK, pm0, off);
-                        const uint32_t t1 = __shfl_up_sync(IVF_FULL_MASK, pm1, off);
-                        const uint32_t u0 = __shfl_down_sync(IVF_FULL_MASK, sm0, off);
-                        const uint32_t u1 = __shfl_down_sync(IVF_FULL_MASK, sm1, off);
-                        if (lane >= off) { pm0 = max(pm0, t0); pm1 = max(pm1, t1); }
-                        if (lane + off < 32) { sm0 = min(sm0, u0); sm1 = min(sm1, u1); }
-                    }
-                    const uint32_t tm0 = __shfl_sync(IVF_FULL_MASK, pm0, 31);
-                    const uint32_t tn1 = __shfl_sync(IVF_FULL_MASK, sm1, 0);
-                    uint32_t rs0 = __shfl_up_sync(IVF_FULL_MASK, pm0, 1), rs1 = __shfl_up_sync(IVF_FULL_MASK, pm1, 1);
-                    uint32_t re0 = __shfl_down_sync(IVF_FULL_MASK, sm0, 1), re1 = __shfl_down_sync(IVF_FULL_MASK, sm1, 1);
-                    if (lane == 0) { rs0 = lo; rs1 = lo; }
-                    if (lane == 31) { re0 = hi; re1 = hi; }
-                    rs1 = max(rs1, tm0);
-                    re0 = min(re0, tn1);
+                    // run start = end of the last pruned code before the sub-group, run end = first pruned code
+                    // after it: nearest set bits of the pruned-and-non-empty mask, bounds fetched by shuffle
+                    const uint32_t P_lo = __ballot_sync(IVF_FULL_MASK, ne0 && !k0);
+                    const uint32_t P_hi = __ballot_sync(IVF_FULL_MASK, ne1 && !k1);
+                    const uint32_t below = (1u << lane) - 1u, above = 0xfffffffeu << lane;
+                    const uint32_t bl0 = P_lo & below, bl1 = P_hi & below, ab0 = P_lo & above, ab1 = P_hi & above;
+                    const uint32_t rsa = __shfl_sync(IVF_FULL_MASK, e0, 31 - __clz(bl0 | 1u));
+                    const uint32_t rsb = __shfl_sync(IVF_FULL_MASK, e1, 31 - __clz(bl1 | 1u));
+                    const uint32_t rsc = __shfl_sync(IVF_FULL_MASK, e0, 31 - __clz(P_lo | 1u));
+                    const uint32_t rea = __shfl_sync(IVF_FULL_MASK, o0, (__ffs(ab0) - 1) & 31);
+                    const uint32_t reb = __shfl_sync(IVF_FULL_MASK, o1, (__ffs(ab1) - 1) & 31);
+                    const uint32_t rec = __shfl_sync(IVF_FULL_MASK, o1, (__ffs(P_hi) - 1) & 31);
+                    const uint32_t rs0 = bl0 ? rsa : lo;
+                    const uint32_t rs1 = bl1 ? rsb : (P_lo ? rsc : lo);
+                    const uint32_t re0 = ab0 ? rea : (P_hi ? rec : hi);
+                    const uint32_t re1 = ab1 ? reb : hi;
                     // windows of the run's 16-grid that start inside the sub-group
                     const uint32_t f0 = rs0 + ((o0 - rs0 + 15u) & ~15u), f1 = rs1 + ((o1 - rs1 + 15u) & ~15u);
                     const uint32_t c0 = (k0 && f0 < e0) ? ((e0 - f0 + 15u) >> 4) : 0u;
@@ -1173,16 +1183,16 @@ __global__ void __launch_bounds__(SCAN_THREADS) scan_kernel(ScanArgs a)
             thr_f = fminf(KPL == 1 ? bl.thr_d : wl.thr_d, __uint_as_float(fb));
         }
 
-        const int nsteps = (nwin + WPS - 1) / WPS;
-        for (int j0 = 0; j0 < nsteps; j0 += SCAN_PF) {
-            // issue every load of SCAN_PF steps before the first use
-            uint32_t cw[SCAN_PF][C::NW];
-            uint32_t nm[SCAN_PF], sid[SCAN_PF], posv[SCAN_PF];
+        // a batch of NS warp steps: every load is issued before the first use
+        auto batch = [&](auto ns_tag, const int j0, const int nlive) {
+            constexpr int NS = decltype(ns_tag)::value;
+            uint32_t cw[NS][C::NW];
+            uint32_t nm[NS], sid[NS], posv[NS];
 #pragma unroll
-            for (int c = 0; c < SCAN_PF; c++) {
+            for (int c = 0; c < NS; c++) {
                 const int wi = (j0 + c) * WPS + half;
                 uint32_t start = 0, len = 0;
-                if (wi < nwin) {
+                if (c < nlive && wi < nwin) {
                     if (runs) {
                         const uint32_t w = wbuf[wi];
                         start = w & 0x7ffffffu;
@@ -1216,8 +1226,8 @@ __global__ void __launch_bounds__(SCAN_THREADS) scan_kernel(ScanArgs a)
                 }
             }
 #pragma unroll
-            for (int c = 0; c < SCAN_PF; c++) {
-                if (j0 + c < nsteps) {   // warp-uniform
+            for (int c = 0; c < NS; c++) {
+                if (c < nlive) {   // warp-uniform
                     float acc0 = base;
                     if (GROUPING) {
                         if (sb_regs) {
@@ -1302,7 +1312,10 @@ __global__ void __launch_bounds__(SCAN_THREADS) scan_kernel(ScanArgs a)
                     }
                 }
             }
-        }
+        };
+        const int nsteps = (nwin + WPS - 1) / WPS;
+        // every batch costs a memory round trip: the tail is one batch whose steps past the end are skipped
+        for (int j0 = 0; j0 < nsteps; j0 += SCAN_PF) batch(std::integral_constant<int, SCAN_PF>(), j0, nsteps - j0);
     }
 
     if (KPL > 0) {

@@ -30,6 +30,8 @@ CASES = [
     ("grp_d32",         "sift",  32,  64,  8,  8, False, 3000, 2500, 40,  8, 10, 64),
     ("grp_deep_opq",    "deep",  96,  96, 16, 16, True,  4000, 3000, 40, 12, 10, 96),
     ("grp_sift_m16",    "sift", 128, 128, 16, 32, False, 5000, 3000, 40, 16, 10, 128),
+    # long lists and sub-groups (~750 / ~94 codes): the scan tiles runs of kept sub-groups instead of whole lists
+    ("grp_long_m16",    "sift",  64,  32, 16,  8, False, 24000, 3000, 40, 8, 10, 32),
 ]
 NSUB = 400  # base vectors kept in the fixture for indexing parity
 

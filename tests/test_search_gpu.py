@@ -170,7 +170,7 @@ def test_empty_and_ragged_inputs(port):
     idx.close()
 
 
-@pytest.mark.parametrize("name", ["adc_sift_m16", "grp_sift_m16", "grp_deep_opq"])
+@pytest.mark.parametrize("name", ["adc_sift_m16", "grp_sift_m16", "grp_deep_opq", "grp_long_m16"])
 @pytest.mark.parametrize("nshards", [2, 3])
 def test_sharded_search_equals_single_gpu(name, nshards):
     """SURVEY.md 8(e) on one GPU: query-sliced preparation into shard-independent records, per-shard scans of
