@@ -152,7 +152,7 @@ void ivfhnsw_b200_destroy(ivfhnsw_b200_t *h)
                       &h->opqA, &h->list_size, &h->list_slot, &h->raw_off, &h->codes, &h->norm_codes, &h->sub_ids,
                       &h->ids, &h->nn_idx, &h->sub_sizes, &h->alphas, &h->icd, &h->st_list, &h->st_ids, &h->st_codes,
                       &h->st_norm, &h->st_sub, &h->st_x, &h->w_x, &h->w_xrot, &h->w_cd, &h->w_ci, &h->w_seg,
-                      &h->w_sub_base, &h->w_qsd, &h->w_part, &h->w_lut, &h->w_coarse, &h->w_xf16, &h->w_out_d, &h->w_out_l,
+                      &h->w_sub_base, &h->w_qsd, &h->w_g1, &h->w_part, &h->w_lut, &h->w_coarse, &h->w_xf16, &h->w_out_d, &h->w_out_l,
                       &h->w_a, &h->w_b, &h->w_c, &h->w_d2, &h->w_e, &h->w_f, &h->w_cub, &h->w_small, &h->counters};
     for (DevBuf *b : bufs) b->release();
     for (int i = 0; i < 8; i++)
@@ -883,9 +883,10 @@ static int search_checks(ivfhnsw_b200_t *h, size_t k)
 static size_t query_batch(const ivfhnsw_b200_t *h, size_t nq, size_t k)
 {
     const size_t rec = seg_record_words((int)h->nprobe, (int)h->nsubc) * 4;
-    const size_t per_q = 2 * rec + 32 * k * 12 + h->d * 8 + h->nprobe * 8 + (size_t)1024 * h->M;
+    const size_t per_q = 2 * rec + 32 * k * 12 + h->d * 8 + h->nprobe * 8 + (size_t)1024 * h->M +
+                         (h->nsubc ? g1_work_bytes((int)h->nprobe, (int)h->nsubc) : 0);
     size_t qb = h->query_batch > 0 ? (size_t)h->query_batch : 16384;
-    qb = std::min(qb, std::max<size_t>(64, ((size_t)1 << 31) / per_q));
+    qb = std::min(qb, std::max<size_t>(64, ((size_t)3 << 30) / per_q));
     return std::max<size_t>(1, std::min(qb, nq));
 }
 
@@ -904,6 +905,7 @@ static int prepare_core(ivfhnsw_b200_t *h, size_t q_begin, size_t q_end, const f
     const size_t stride = seg_record_words(nprobe, nsubc);
     CU(h->w_seg.ensure(qb * 12 + 1024));
     if (grouping) CU(h->w_qsd.ensure(qb * (size_t)nprobe * nsubc * 4 + 256));
+    if (grouping) CU(h->w_g1.ensure(qb * g1_work_bytes(nprobe, nsubc) + 256));
     if (!cd_dev) {
         CU(h->w_cd.ensure(qb * nprobe * 4));
         CU(h->w_ci.ensure(qb * nprobe * 4));
@@ -937,6 +939,7 @@ static int prepare_core(ivfhnsw_b200_t *h, size_t q_begin, size_t q_end, const f
         if (h->timing) CU(cudaEventRecord(h->ev[1], st));
         if (grouping)
             CU(launch_prep_grouping(st, LAUNCHES, nb, d, nprobe, nsubc, h->max_codes, h->do_pruning, xq, cd, ci, L, T,
+                                    h->w_g1.p,
                                     h->timing ? h->ev[4] : nullptr, h->counters.as<unsigned long long>() + 5));
         else
             CU(launch_prep_adc(st, LAUNCHES, nb, nprobe, h->max_codes, cd, ci, L, T));

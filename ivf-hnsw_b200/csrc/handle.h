@@ -84,7 +84,7 @@ struct ivfhnsw_b200 {
     size_t st_n = 0;          // encoded records staged (IVFADC) or points staged (Grouping)
     bool st_dirty = false;
     // workspace
-    DevBuf w_x, w_xrot, w_cd, w_ci, w_seg, w_sub_base, w_qsd, w_part, w_lut, w_coarse, w_xf16, w_out_d, w_out_l;
+    DevBuf w_x, w_xrot, w_cd, w_ci, w_seg, w_sub_base, w_qsd, w_g1, w_part, w_lut, w_coarse, w_xf16, w_out_d, w_out_l;
     DevBuf w_a, w_b, w_c, w_d2, w_e, w_f, w_cub, w_small;
     DevBuf counters;  // [0] scanned, [1] walked
     // options / stats

@@ -55,10 +55,23 @@ static inline size_t seg_record_words(int nprobe, int nsubc)
 cudaError_t launch_prep_adc(cudaStream_t st, uint64_t *launches, int nq, int nprobe, uint64_t max_codes,
                             const float *coarse_d, const uint32_t *coarse_i, const DeviceLists &L, const SegTables &T);
 
+// Workspace of the Grouping preparation (K-G1a -> K-G1b -> K-G1c), per query:
+//   rows[cap]  distinct neighbour centroids: [0, nmemo) probed ones whose distance the coarse stage knows,
+//              [nmemo, nmemo + nwork) rows to evaluate;   dv[cap] = (d(q, row), ||row||^2)
+//   ppos[P*S]  dense row index of every (probe, sub-group) pair, 0xffff = none;   cnt = (nmemo, nwork)
+struct G1Work {
+    uint32_t *rows;
+    float2 *dv;
+    uint16_t *ppos;
+    uint2 *cnt;
+    int cap;          // nprobe * nsubc + nprobe
+};
+size_t g1_work_bytes(int nprobe, int nsubc);   // per query
 cudaError_t launch_prep_grouping(cudaStream_t st, uint64_t *launches, int nq, int d, int nprobe, int nsubc,
                                  uint64_t max_codes, bool do_pruning, const float *queries,
                                  const float *coarse_d, const uint32_t *coarse_i, const DeviceLists &L,
-                                 const SegTables &T, cudaEvent_t ev_after_g1 /* may be null */,
+                                 const SegTables &T, void *g1_work /* nq * g1_work_bytes() */,
+                                 cudaEvent_t ev_after_g1 /* may be null */,
                                  unsigned long long *rows_counter /* distinct neighbour rows, may be null */);
 
 size_t scan_smem_bytes(int M, int nprobe, int k, int nsubc);

@@ -195,63 +195,51 @@ static __device__ __forceinline__ int pair_probe(int e, int nsubc, int sub_shift
     return sub_shift >= 0 ? (e >> sub_shift) : (e / nsubc);
 }
 
-__global__ void __launch_bounds__(G1_THREADS) group_g1_kernel(int d, int nprobe, int nsubc, int sub_shift, int ht_size,
-                                                              uint64_t max_codes, int do_pruning,
-                                                              const float *__restrict__ queries,
-                                                              const float *__restrict__ coarse_d,
-                                                              const uint32_t *__restrict__ coarse_i, DeviceLists L,
-                                                              SegTables T, unsigned long long *rows_counter)
+// ---- K-G1a: distinct neighbour centroids of a query (hash de-duplication) -> dense row list + pair map
+__global__ void __launch_bounds__(G1_THREADS) group_g1a_kernel(int nprobe, int nsubc, int sub_shift, int ht_size,
+                                                               uint64_t max_codes,
+                                                               const float *__restrict__ coarse_d,
+                                                               const uint32_t *__restrict__ coarse_i, DeviceLists L,
+                                                               G1Work Wk, unsigned long long *rows_counter)
 {
     extern __shared__ __align__(16) uint8_t sm[];
-    float *sq = reinterpret_cast<float *>(sm);                         // [d] (d % 4 == 0)
-    uint32_t *hk = reinterpret_cast<uint32_t *>(sq + d);               // [ht_size] centroid ids; after the distance
-                                                                       // phase: bits of their ||c||^2
-    float *hv = reinterpret_cast<float *>(hk + ht_size);               // [ht_size] d(q, centroid)
-    uint32_t *s_c = reinterpret_cast<uint32_t *>(hv + ht_size);        // [nprobe]
+    uint32_t *hk = reinterpret_cast<uint32_t *>(sm);                   // [ht_size] centroid ids
+    uint32_t *s_c = hk + ht_size;                                      // [nprobe]
     uint32_t *s_sz = s_c + nprobe;
-    float *s_alpha = reinterpret_cast<float *>(s_sz + nprobe);
-    float *s_cd = s_alpha + nprobe;
-    float *s_cn = s_cd + nprobe;
-    uint16_t *work = reinterpret_cast<uint16_t *>(s_cn + nprobe);      // [npairs] table slots to compute
-    uint16_t *ppos = work + (size_t)nprobe * nsubc;                    // [npairs] table slot of every pair
-    uint16_t *s_mpos = ppos + (size_t)nprobe * nsubc;                  // [nprobe] table slot of a memoised probe
-    uint8_t *s_inh = reinterpret_cast<uint8_t *>(s_mpos + nprobe);
-    __shared__ int s_nwork;
-    __shared__ uint32_t s_count;
+    uint16_t *hidx = reinterpret_cast<uint16_t *>(s_sz + nprobe);      // [ht_size] dense row index of the slot
+    uint16_t *pslot = hidx + ht_size;                                  // [npairs] table slot of every pair
+    uint8_t *s_inh = reinterpret_cast<uint8_t *>(pslot + (size_t)nprobe * nsubc);
+    __shared__ int s_nwork, s_nmemo;
     const int q = blockIdx.x, tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     const size_t qo = (size_t)q * nprobe;
-    const float qnan = __int_as_float(0x7fc00000);
     const uint32_t H = (uint32_t)ht_size;
-    for (int i = tid; i < d; i += G1_THREADS) sq[i] = queries[(size_t)q * d + i];
+    uint32_t *rows = Wk.rows + (size_t)q * Wk.cap;
+    float2 *dv = Wk.dv + (size_t)q * Wk.cap;
     for (int i = tid; i < ht_size; i += G1_THREADS) hk[i] = 0xffffffffu;
-    if (tid == 0) { s_nwork = 0; s_count = 0; }
+    if (tid == 0) { s_nwork = 0; s_nmemo = 0; }
     if (warp == 0) probe_meta_warp0(nprobe, max_codes, coarse_i + qo, L, s_c, s_sz, s_inh, lane);
     __syncthreads();
-    // ---- per-list constants.  The coarse stage already knows d(q, c) of the probed centroids: they enter the
-    // table as done (the reference's query_centroid_dists memo), unless the value is < EPS, which the reference
-    // treats as "not computed" (Q1 iv).  Of a centroid listed twice the last entry counts (it overwrites).
+    // ---- the coarse stage already knows d(q, c) of the probed centroids: they enter the table as done (the
+    // reference's query_centroid_dists memo), unless the value is < EPS, which the reference treats as "not
+    // computed" (Q1 iv).  Of a centroid listed twice the last entry counts (it overwrites).
     for (int i = tid; i < nprobe; i += G1_THREADS) {
         const uint32_t c = s_c[i];
         const float v = coarse_d[qo + i];
-        const float cn = L.centroid_norms[c];
-        s_alpha[i] = L.alphas[c];
-        s_cd[i] = v;
-        s_cn[i] = cn;
         bool last = true;
         for (int j = i + 1; j < nprobe; j++) last = last && (s_c[j] != c);
-        uint16_t mp = 0xffffu;
         if (last && v >= 0.00001f) {
             uint32_t p = __umulhi(c * 2654435761u, H);
             while (atomicCAS(&hk[p], 0xffffffffu, c) != 0xffffffffu) p = p + 1 == H ? 0u : p + 1;
-            hv[p] = v;
-            mp = (uint16_t)p;
+            const int m = atomicAdd(&s_nmemo, 1);
+            hidx[p] = (uint16_t)m;
+            rows[m] = c;
+            dv[m] = make_float2(v, L.centroid_norms[c]);
         }
-        s_mpos[i] = mp;
     }
     __syncthreads();
-    const int npairs = nprobe * nsubc;
+    const int npairs = nprobe * nsubc, nmemo = s_nmemo;
     // ---- every needed neighbour id enters the table once (loads of 8 pairs in flight per thread); a pair
-    // remembers its slot, first sightings go to the work list (one counter update per warp)
+    // remembers its slot, first sightings get the next dense index (one counter update per warp)
     for (int e0 = 0; e0 < npairs; e0 += G1_THREADS * 8) {
         uint32_t nn[8];
 #pragma unroll
@@ -289,43 +277,166 @@ __global__ void __launch_bounds__(G1_THREADS) group_g1_kernel(int d, int nprobe,
                 int base = 0;
                 if (lane == leader) base = atomicAdd(&s_nwork, __popc(fm));
                 base = __shfl_sync(IVF_FULL_MASK, base, leader);
-                if (first) work[base + __popc(fm & ((1u << lane) - 1u))] = (uint16_t)p;
+                if (first) {
+                    const int w = nmemo + base + __popc(fm & ((1u << lane) - 1u));
+                    hidx[p] = (uint16_t)w;
+                    rows[w] = n;
+                }
             }
-            if (e < npairs) ppos[e] = (uint16_t)p;
+            if (e < npairs) pslot[e] = (uint16_t)p;
         }
     }
     __syncthreads();
-    const int nwork = s_nwork;
-    if (tid == 0 && rows_counter) atomicAdd(rows_counter, (unsigned long long)nwork);
-    // ---- one thread per distance; the slot then trades the id for the centroid's norm
-    for (int i = tid; i < nprobe; i += G1_THREADS)
-        if (s_mpos[i] != 0xffffu) hk[s_mpos[i]] = __float_as_uint(s_cn[i]);
-    for (int w = tid; w < nwork; w += G1_THREADS) {
-        const int p = work[w];
-        const uint32_t n = hk[p];
-#ifdef G1_SKIP_DIST   /* timing experiment only: everything but the row gathers */
-        hv[p] = 1.0f + (float)p;
-#else
-        hv[p] = l2sqr16_thread(sq, L.centroids + (size_t)n * d, d);
-#endif
-        hk[p] = __float_as_uint(__ldg(L.centroid_norms + n));
+    uint16_t *ppos = Wk.ppos + (size_t)q * npairs;
+    for (int e = tid; e < npairs; e += G1_THREADS) {
+        const uint16_t p = pslot[e];
+        ppos[e] = p == 0xffffu ? (uint16_t)0xffffu : hidx[p];
+    }
+    if (tid == 0) {
+        Wk.cnt[q] = make_uint2((uint32_t)nmemo, (uint32_t)s_nwork);
+        if (rows_counter) atomicAdd(rows_counter, (unsigned long long)s_nwork);
+    }
+}
+
+// ---- K-G1b: d(q, row) of the rows K-G1a listed.  The rows live in L2 (or HBM): what matters is the shape of the
+// requests.  A warp reads a row with ONE coalesced 128-bit load per lane (whole 128-byte lines, 3x the rows/s of
+// per-thread sector loads -- profiles/scratch/gather_bench2.cu), lane l forms the squared differences of its four
+// dimensions, and the 32 rows of a batch are transposed through shared memory so that lane r then owns row r and
+// adds its terms in EXACTLY the order of ivfhnsw::fvec_L2sqr (utils.cpp:22-51): 8 partial sums over
+// floor(d/16)*16 dims, unfused multiply-add like the pinned C restatement, partials added left to right.
+#define G1B_WARPS 4
+template <int NCH>   // 128-dimension chunks per row
+__global__ void __launch_bounds__(G1B_WARPS * 32, 3) group_g1b_kernel(int d, int n, const float *__restrict__ queries,
+                                                                      DeviceLists L, G1Work Wk)
+{
+    extern __shared__ __align__(16) float g1b_sm[];
+    constexpr int G = 16 / NCH;            // rows whose loads are in flight together
+    const int q = blockIdx.x, lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    const uint2 cnt = Wk.cnt[q];
+    const int nmemo = (int)cnt.x, nwork = (int)cnt.y;
+    const int stride = n + 4;              // words; (n + 4) / 4 is odd: the row-per-lane reads are conflict free
+    float *buf = g1b_sm + (size_t)warp * 32 * stride;
+    const uint32_t *rows = Wk.rows + (size_t)q * Wk.cap + nmemo;
+    float2 *dv = Wk.dv + (size_t)q * Wk.cap + nmemo;
+    float4 xq[NCH];
+#pragma unroll
+    for (int c = 0; c < NCH; c++) {
+        xq[c] = make_float4(0.f, 0.f, 0.f, 0.f);
+        if (128 * c + 4 * lane < n) xq[c] = *reinterpret_cast<const float4 *>(queries + (size_t)q * d + 128 * c + 4 * lane);
+    }
+    for (int b = warp * 32; b < nwork; b += G1B_WARPS * 32) {
+        const int nb = min(32, nwork - b);
+        const uint32_t my_row = lane < nb ? rows[b + lane] : 0u;
+        for (int g0 = 0; g0 < nb; g0 += G) {
+            float4 y[G][NCH];
+#pragma unroll
+            for (int u = 0; u < G; u++) {
+                const uint32_t row = __shfl_sync(IVF_FULL_MASK, my_row, (g0 + u) & 31);
+                const float *yr = L.centroids + (size_t)row * d;
+#pragma unroll
+                for (int c = 0; c < NCH; c++)
+                    if (g0 + u < nb && 128 * c + 4 * lane < n)
+                        y[u][c] = __ldg(reinterpret_cast<const float4 *>(yr + 128 * c + 4 * lane));
+            }
+#pragma unroll
+            for (int u = 0; u < G; u++) {
+#pragma unroll
+                for (int c = 0; c < NCH; c++)
+                    if (g0 + u < nb && 128 * c + 4 * lane < n) {
+                        const float d0 = xq[c].x - y[u][c].x, d1 = xq[c].y - y[u][c].y;
+                        const float d2 = xq[c].z - y[u][c].z, d3 = xq[c].w - y[u][c].w;
+                        *reinterpret_cast<float4 *>(buf + (size_t)(g0 + u) * stride + 128 * c + 4 * lane) =
+                            make_float4(__fmul_rn(d0, d0), __fmul_rn(d1, d1), __fmul_rn(d2, d2), __fmul_rn(d3, d3));
+                    }
+            }
+        }
+        __syncwarp();
+        if (lane < nb) {
+            const float *pr = buf + (size_t)lane * stride;
+            float acc[8];
+#pragma unroll
+            for (int j = 0; j < 8; j++) acc[j] = 0.f;
+#pragma unroll 4
+            for (int i = 0; i < n; i += 8) {
+                const float4 p0 = *reinterpret_cast<const float4 *>(pr + i), p1 = *reinterpret_cast<const float4 *>(pr + i + 4);
+                acc[0] = __fadd_rn(acc[0], p0.x); acc[1] = __fadd_rn(acc[1], p0.y);
+                acc[2] = __fadd_rn(acc[2], p0.z); acc[3] = __fadd_rn(acc[3], p0.w);
+                acc[4] = __fadd_rn(acc[4], p1.x); acc[5] = __fadd_rn(acc[5], p1.y);
+                acc[6] = __fadd_rn(acc[6], p1.z); acc[7] = __fadd_rn(acc[7], p1.w);
+            }
+            float r = acc[0];
+#pragma unroll
+            for (int j = 1; j < 8; j++) r += acc[j];
+            dv[b + lane] = make_float2(r, __ldg(L.centroid_norms + my_row));
+        }
+        __syncwarp();
+    }
+}
+
+// shapes the transposing kernel does not take (d % 4 != 0 or very long rows): one thread per row
+__global__ void __launch_bounds__(256) group_g1b_simple_kernel(int d, const float *__restrict__ queries, DeviceLists L,
+                                                               G1Work Wk)
+{
+    extern __shared__ __align__(16) float g1b_sq[];
+    const int q = blockIdx.x;
+    const uint2 cnt = Wk.cnt[q];
+    for (int i = threadIdx.x; i < d; i += blockDim.x) g1b_sq[i] = queries[(size_t)q * d + i];
+    __syncthreads();
+    const uint32_t *rows = Wk.rows + (size_t)q * Wk.cap + cnt.x;
+    float2 *dv = Wk.dv + (size_t)q * Wk.cap + cnt.x;
+    for (int w = threadIdx.x; w < (int)cnt.y; w += blockDim.x) {
+        const uint32_t n = rows[w];
+        dv[w] = make_float2(l2sqr16_thread(g1b_sq, L.centroids + (size_t)n * d, d), __ldg(L.centroid_norms + n));
+    }
+}
+
+// ---- K-G1c: per sub-group pruning value and base
+__global__ void __launch_bounds__(G1_THREADS) group_g1c_kernel(int nprobe, int nsubc, int sub_shift, uint64_t max_codes,
+                                                               int do_pruning, const float *__restrict__ coarse_d,
+                                                               const uint32_t *__restrict__ coarse_i, DeviceLists L,
+                                                               SegTables T, G1Work Wk)
+{
+    extern __shared__ __align__(16) uint8_t sm[];
+    uint32_t *s_c = reinterpret_cast<uint32_t *>(sm);      // [nprobe]
+    uint32_t *s_sz = s_c + nprobe;
+    float *s_alpha = reinterpret_cast<float *>(s_sz + nprobe);
+    float *s_cd = s_alpha + nprobe;
+    float *s_cn = s_cd + nprobe;
+    uint8_t *s_inh = reinterpret_cast<uint8_t *>(s_cn + nprobe);
+    __shared__ uint32_t s_count;
+    const int q = blockIdx.x, tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    const size_t qo = (size_t)q * nprobe;
+    const float qnan = __int_as_float(0x7fc00000);
+    if (tid == 0) s_count = 0;
+    if (warp == 0) probe_meta_warp0(nprobe, max_codes, coarse_i + qo, L, s_c, s_sz, s_inh, lane);
+    __syncthreads();
+    for (int i = tid; i < nprobe; i += G1_THREADS) {
+        const uint32_t c = s_c[i];
+        s_alpha[i] = L.alphas[c];
+        s_cd[i] = coarse_d[qo + i];
+        s_cn[i] = L.centroid_norms[c];
     }
     __syncthreads();
-    // ---- per sub-group: pruning value and base
+    const int npairs = nprobe * nsubc;
+    const uint16_t *ppos = Wk.ppos + (size_t)q * npairs;
+    const float2 *dv = Wk.dv + (size_t)q * Wk.cap;
     uint32_t count = 0;
     for (int e0 = 0; e0 < npairs; e0 += G1_THREADS * 4) {
         uint32_t pos[4];
         float icd[4];
+        float2 v[4];
 #pragma unroll
         for (int u = 0; u < 4; u++) {
             const int e = e0 + u * G1_THREADS + tid;
             pos[u] = 0xffffu;
             icd[u] = 0.f;
+            v[u] = make_float2(0.f, 0.f);
             if (e < npairs) {
                 pos[u] = ppos[e];
                 if (pos[u] != 0xffffu) {
                     const int i = pair_probe(e, nsubc, sub_shift), s = e - i * nsubc;
                     icd[u] = __ldg(L.icd + (size_t)s_c[i] * nsubc + s);
+                    v[u] = dv[pos[u]];
                 }
             }
         }
@@ -336,8 +447,8 @@ __global__ void __launch_bounds__(G1_THREADS) group_g1_kernel(int d, int nprobe,
             float r = qnan, sb = __int_as_float(0x7f800000);
             if (pos[u] != 0xffffu) {
                 const int i = pair_probe(e, nsubc, sub_shift);
-                const float qsd = hv[pos[u]];
-                const float cnn = __uint_as_float(hk[pos[u]]);
+                const float qsd = v[u].x;
+                const float cnn = v[u].y;
                 const float alpha = s_alpha[i];
                 const float oma = __fsub_rn(1.f, alpha);
                 // :251-252  (1-a)*d(q,c) - a*((1-a)*d(c,n) - d(q,n))
@@ -500,10 +611,28 @@ __global__ void __launch_bounds__(G1_THREADS) group_g3_kernel(int nprobe, int ns
     }
 }
 
+size_t g1_work_bytes(int nprobe, int nsubc)
+{
+    const size_t cap = (size_t)nprobe * nsubc + nprobe;
+    return cap * 12 + (size_t)nprobe * nsubc * 2 + 16;      // rows + (dist, norm) + pair map + counts, per query
+}
+
+template <int NCH>
+static cudaError_t launch_g1b(cudaStream_t st, int nq, int d, int n, const float *queries, const DeviceLists &L,
+                              const G1Work &Wk)
+{
+    const size_t smb = (size_t)G1B_WARPS * 32 * (n + 4) * 4;
+    cudaError_t e = cudaFuncSetAttribute(group_g1b_kernel<NCH>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smb);
+    if (e != cudaSuccess) return e;
+    group_g1b_kernel<NCH><<<nq, G1B_WARPS * 32, smb, st>>>(d, n, queries, L, Wk);
+    return cudaGetLastError();
+}
+
 cudaError_t launch_prep_grouping(cudaStream_t st, uint64_t *launches, int nq, int d, int nprobe, int nsubc,
                                  uint64_t max_codes, bool do_pruning, const float *queries,
                                  const float *coarse_d, const uint32_t *coarse_i, const DeviceLists &L,
-                                 const SegTables &T, cudaEvent_t ev_after_g1, unsigned long long *rows_counter)
+                                 const SegTables &T, void *g1_work, cudaEvent_t ev_after_g1,
+                                 unsigned long long *rows_counter)
 {
     if (nq == 0) return cudaSuccess;
     const int npairs = nprobe * nsubc;
@@ -511,15 +640,40 @@ cudaError_t launch_prep_grouping(cudaStream_t st, uint64_t *launches, int nq, in
     // (typical load 20-30 %: the neighbour lists of the probed centroids overlap)
     const int ht = npairs + nprobe + 1;
     if (ht > 65535) return cudaErrorInvalidValue;       // uint16 slot numbers
-    const size_t sm1 = (size_t)d * 4 + (size_t)ht * 8 + (size_t)nprobe * 20 + (size_t)npairs * 4 +
-                       (size_t)nprobe * 2 + (size_t)nprobe + 16;
-    cudaError_t e = cudaFuncSetAttribute(group_g1_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sm1);
-    if (e != cudaSuccess) return e;
+    G1Work Wk;
+    Wk.cap = npairs + nprobe;
+    {   // carve the per-batch workspace: [cnt][dv][rows][ppos]
+        uint8_t *p = static_cast<uint8_t *>(g1_work);
+        Wk.cnt = reinterpret_cast<uint2 *>(p); p += (size_t)nq * 8;
+        Wk.dv = reinterpret_cast<float2 *>(p); p += (size_t)nq * Wk.cap * 8;
+        Wk.rows = reinterpret_cast<uint32_t *>(p); p += (size_t)nq * Wk.cap * 4;
+        Wk.ppos = reinterpret_cast<uint16_t *>(p);
+    }
     int sub_shift = -1;
     for (int b = 0; b < 16; b++)
         if ((1 << b) == nsubc) sub_shift = b;
-    group_g1_kernel<<<nq, G1_THREADS, sm1, st>>>(d, nprobe, nsubc, sub_shift, ht, max_codes, do_pruning ? 1 : 0, queries,
-                                                coarse_d, coarse_i, L, T, rows_counter);
+    const size_t sm1 = (size_t)ht * 6 + (size_t)nprobe * 8 + (size_t)npairs * 2 + (size_t)nprobe + 16;
+    cudaError_t e = cudaFuncSetAttribute(group_g1a_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sm1);
+    if (e != cudaSuccess) return e;
+    group_g1a_kernel<<<nq, G1_THREADS, sm1, st>>>(nprobe, nsubc, sub_shift, ht, max_codes, coarse_d, coarse_i, L, Wk,
+                                                 rows_counter);
+    ++*launches;
+    e = cudaGetLastError();
+    if (e != cudaSuccess) return e;
+    const int n = (d >> 4) << 4;      // dims fvec_L2sqr uses
+    if ((d & 3) == 0 && n >= 16 && n <= 384) {
+        if (n <= 128) e = launch_g1b<1>(st, nq, d, n, queries, L, Wk);
+        else if (n <= 256) e = launch_g1b<2>(st, nq, d, n, queries, L, Wk);
+        else e = launch_g1b<3>(st, nq, d, n, queries, L, Wk);
+    } else {
+        group_g1b_simple_kernel<<<nq, 256, (size_t)d * 4, st>>>(d, queries, L, Wk);
+        e = cudaGetLastError();
+    }
+    ++*launches;
+    if (e != cudaSuccess) return e;
+    const size_t smc = (size_t)nprobe * 21 + 16;
+    group_g1c_kernel<<<nq, G1_THREADS, smc, st>>>(nprobe, nsubc, sub_shift, max_codes, do_pruning ? 1 : 0, coarse_d,
+                                                 coarse_i, L, T, Wk);
     ++*launches;
     e = cudaGetLastError();
     if (e != cudaSuccess) return e;
