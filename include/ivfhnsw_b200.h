@@ -182,7 +182,7 @@ typedef struct ivfhnsw_b200_stats {
     uint64_t scan_launches;     /* number of scan-kernel launches included in scan_ms           */
     uint64_t coarse_flops;      /* 2*nc*d per query/vector pushed through the coarse GEMM       */
     double gemm_ms;             /* ... of coarse_ms, the tensor-core GEMM kernel alone          */
-    double g1_ms;               /* ... of prep_ms, the sub-centroid distance kernel (K-G1)      */
+    double g1_ms;               /* ... of prep_ms, the sub-centroid distance kernel (K-G1b)     */
     double lut_ms;              /* ... of scan_ms, the lookup-table kernel (K-L1)               */
     uint64_t g1_rows;           /* distinct neighbour-centroid rows K-G1 gathered               */
     uint64_t prep_launches;     /* number of prep batches included in coarse_ms / prep_ms       */

@@ -128,7 +128,7 @@ int ivfhnsw_b200_create(ivfhnsw_b200_t **out, size_t d, size_t nc, size_t code_s
                        prop.minor);
     CU(cudaSetDevice(device));
     CU(cudaStreamCreateWithFlags(&h->stream, cudaStreamNonBlocking));
-    for (int i = 0; i < 8; i++) CU(cudaEventCreate(&h->ev[i]));
+    for (int i = 0; i < 10; i++) CU(cudaEventCreate(&h->ev[i]));
     CU(h->counters.ensure(64));
     CU(cudaMemsetAsync(h->counters.p, 0, 64, h->stream));
     CU(h->centroid_norms.ensure(nc * 4));
@@ -155,7 +155,7 @@ void ivfhnsw_b200_destroy(ivfhnsw_b200_t *h)
                       &h->w_sub_base, &h->w_qsd, &h->w_g1, &h->w_part, &h->w_lut, &h->w_coarse, &h->w_xf16, &h->w_out_d, &h->w_out_l,
                       &h->w_a, &h->w_b, &h->w_c, &h->w_d2, &h->w_e, &h->w_f, &h->w_cub, &h->w_small, &h->counters};
     for (DevBuf *b : bufs) b->release();
-    for (int i = 0; i < 8; i++)
+    for (int i = 0; i < 10; i++)
         if (h->ev[i]) cudaEventDestroy(h->ev[i]);
     if (h->stream && h->own_stream) cudaStreamDestroy(h->stream);
     delete h;
@@ -940,7 +940,8 @@ static int prepare_core(ivfhnsw_b200_t *h, size_t q_begin, size_t q_end, const f
         if (grouping)
             CU(launch_prep_grouping(st, LAUNCHES, nb, d, nprobe, nsubc, h->max_codes, h->do_pruning, xq, cd, ci, L, T,
                                     h->w_g1.p,
-                                    h->timing ? h->ev[4] : nullptr, h->counters.as<unsigned long long>() + 5));
+                                    h->timing ? h->ev[8] : nullptr, h->timing ? h->ev[4] : nullptr,
+                                    h->counters.as<unsigned long long>() + 5));
         else
             CU(launch_prep_adc(st, LAUNCHES, nb, nprobe, h->max_codes, cd, ci, L, T));
         reduce_u32_kernel<<<grid_for(nb, 256, 64), 256, 0, st>>>(nb, T.nscanned, T.nwalked,
@@ -952,7 +953,7 @@ static int prepare_core(ivfhnsw_b200_t *h, size_t q_begin, size_t q_end, const f
             float ms = 0;
             CU(cudaEventElapsedTime(&ms, h->ev[0], h->ev[1])); h->stats.coarse_ms += ms;
             CU(cudaEventElapsedTime(&ms, h->ev[1], h->ev[2])); h->stats.prep_ms += ms;
-            if (grouping) { CU(cudaEventElapsedTime(&ms, h->ev[1], h->ev[4])); h->stats.g1_ms += ms; }
+            if (grouping) { CU(cudaEventElapsedTime(&ms, h->ev[8], h->ev[4])); h->stats.g1_ms += ms; }
             h->stats.prep_launches += 1;
         }
         if (q0 == q_begin && h->debug) {   // keep debug outputs of the first batch (copied lazily by last_thresholds)
@@ -968,7 +969,7 @@ static int prepare_core(ivfhnsw_b200_t *h, size_t q_begin, size_t q_end, const f
 
 // Stage 2: lookup tables + ADC scan of THIS GPU's lists for all nq queries, driven by the records.
 static int scan_core(ivfhnsw_b200_t *h, size_t nq, size_t k, const float *x_dev, const uint32_t *tables, float *out_d,
-                     int64_t *out_l, uint32_t *out_seq)
+                     int64_t *out_l, uint32_t *out_seq, bool xrot_ready = false)
 {
     if (nq == 0) return 0;
     const int d = (int)h->d, M = (int)h->M, nprobe = (int)h->nprobe, nsubc = (int)h->nsubc;
@@ -995,7 +996,9 @@ static int scan_core(ivfhnsw_b200_t *h, size_t nq, size_t k, const float *x_dev,
         const float *xq = x_dev + q0 * d;
         if (h->timing) CU(cudaEventRecord(h->ev[2], st));
         if (h->do_opq) {
-            CU(launch_rotate(st, LAUNCHES, nb, d, h->opqA.as<float>(), false, xq, h->w_xrot.as<float>()));
+            // xrot_ready: prepare_core just rotated these very queries into w_xrot (one batch)
+            if (!(xrot_ready && nq <= qb))
+                CU(launch_rotate(st, LAUNCHES, nb, d, h->opqA.as<float>(), false, xq, h->w_xrot.as<float>()));
             xq = h->w_xrot.as<float>();
         }
         float *pd = nullptr;
@@ -1043,8 +1046,9 @@ static int search_core(ivfhnsw_b200_t *h, size_t nq, size_t k, const float *x_de
         if (int r = prepare_core(h, 0, nb, x_dev + q0 * h->d, cd_dev ? cd_dev + q0 * h->nprobe : nullptr,
                                  ci_dev ? ci_dev + q0 * h->nprobe : nullptr, tables))
             return r;
+        const bool xrot_ready = h->do_opq && nb <= query_batch(h, nb, 10);   // prepare_core ran ONE batch
         if (int r = scan_core(h, nb, k, x_dev + q0 * h->d, tables, out_d + q0 * k, out_l + q0 * k,
-                              out_seq ? out_seq + q0 * k : nullptr))
+                              out_seq ? out_seq + q0 * k : nullptr, xrot_ready))
             return r;
     }
     return 0;

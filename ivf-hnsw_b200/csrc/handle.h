@@ -66,7 +66,7 @@ struct ivfhnsw_b200 {
     uint32_t c_begin = 0, c_end = 0;
     cudaStream_t stream = nullptr;
     bool own_stream = true;
-    cudaEvent_t ev[8] = {nullptr, nullptr, nullptr, nullptr, nullptr, nullptr, nullptr, nullptr};
+    cudaEvent_t ev[10] = {nullptr, nullptr, nullptr, nullptr, nullptr, nullptr, nullptr, nullptr, nullptr, nullptr};
     std::string err;
     std::mutex mu;
 

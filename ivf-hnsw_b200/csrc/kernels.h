@@ -71,7 +71,7 @@ cudaError_t launch_prep_grouping(cudaStream_t st, uint64_t *launches, int nq, in
                                  uint64_t max_codes, bool do_pruning, const float *queries,
                                  const float *coarse_d, const uint32_t *coarse_i, const DeviceLists &L,
                                  const SegTables &T, void *g1_work /* nq * g1_work_bytes() */,
-                                 cudaEvent_t ev_after_g1 /* may be null */,
+                                 cudaEvent_t ev_before_g1b /* may be null */, cudaEvent_t ev_after_g1b /* may be null */,
                                  unsigned long long *rows_counter /* distinct neighbour rows, may be null */);
 
 size_t scan_smem_bytes(int M, int nprobe, int k, int nsubc);

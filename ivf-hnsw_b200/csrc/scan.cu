@@ -299,75 +299,101 @@ __global__ void __launch_bounds__(G1_THREADS) group_g1a_kernel(int nprobe, int n
 }
 
 // ---- K-G1b: d(q, row) of the rows K-G1a listed.  The rows live in L2 (or HBM): what matters is the shape of the
-// requests.  A warp reads a row with ONE coalesced 128-bit load per lane (whole 128-byte lines, 3x the rows/s of
-// per-thread sector loads -- profiles/scratch/gather_bench2.cu), lane l forms the squared differences of its four
-// dimensions, and the 32 rows of a batch are transposed through shared memory so that lane r then owns row r and
-// adds its terms in EXACTLY the order of ivfhnsw::fvec_L2sqr (utils.cpp:22-51): 8 partial sums over
-// floor(d/16)*16 dims, unfused multiply-add like the pinned C restatement, partials added left to right.
+// requests and the bytes in flight.  A warp fetches whole rows with cp.async (16 bytes per lane: full 128-byte
+// lines, 3x the rows/s of per-thread sector loads -- profiles/scratch/gather_bench2.cu) into a two-stage ring of
+// 16-row tiles in shared memory; while one tile is in flight the other is summed, TWO lanes per row: lane 2r
+// owns partial sums 0..3 of row r and lane 2r+1 partial sums 4..7, each added in EXACTLY the order of
+// ivfhnsw::fvec_L2sqr (utils.cpp:22-51) -- 8 partial sums over floor(d/16)*16 dims, unfused multiply-add like the
+// pinned C restatement -- and the partials are then added left to right.  Row pitch n + 8 words = 8 * odd:
+// the 128-bit reads of a quarter warp fall in 8 distinct bank groups.
 #define G1B_WARPS 4
-template <int NCH>   // 128-dimension chunks per row
-__global__ void __launch_bounds__(G1B_WARPS * 32, 3) group_g1b_kernel(int d, int n, const float *__restrict__ queries,
+#define G1B_TILE 16
+static __device__ __forceinline__ void cp_async16(void *smem_dst, const void *gsrc)
+{
+    asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"((uint32_t)__cvta_generic_to_shared(smem_dst)), "l"(gsrc)
+                 : "memory");
+}
+template <int N>   // dims fvec_L2sqr uses, compile time (query in registers); 0 = run time (query in shared memory)
+__global__ void __launch_bounds__(G1B_WARPS * 32, 3) group_g1b_kernel(int d, int n_rt, const float *__restrict__ queries,
                                                                       DeviceLists L, G1Work Wk)
 {
     extern __shared__ __align__(16) float g1b_sm[];
-    constexpr int G = 16 / NCH;            // rows whose loads are in flight together
+    const int n = N > 0 ? N : n_rt;
     const int q = blockIdx.x, lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
     const uint2 cnt = Wk.cnt[q];
     const int nmemo = (int)cnt.x, nwork = (int)cnt.y;
-    const int stride = n + 4;              // words; (n + 4) / 4 is odd: the row-per-lane reads are conflict free
-    float *buf = g1b_sm + (size_t)warp * 32 * stride;
+    const int pitch = n + 8;
+    float *buf = g1b_sm + (size_t)warp * 2 * G1B_TILE * pitch;
+    float *xs = g1b_sm + (size_t)G1B_WARPS * 2 * G1B_TILE * pitch;     // N == 0: the query
     const uint32_t *rows = Wk.rows + (size_t)q * Wk.cap + nmemo;
     float2 *dv = Wk.dv + (size_t)q * Wk.cap + nmemo;
-    float4 xq[NCH];
+    const int h = lane & 1, r = lane >> 1;
+    float4 xr[N > 0 ? N / 8 : 1];
+    if (N > 0) {
 #pragma unroll
-    for (int c = 0; c < NCH; c++) {
-        xq[c] = make_float4(0.f, 0.f, 0.f, 0.f);
-        if (128 * c + 4 * lane < n) xq[c] = *reinterpret_cast<const float4 *>(queries + (size_t)q * d + 128 * c + 4 * lane);
+        for (int i = 0; i < N / 8; i++) xr[i] = *reinterpret_cast<const float4 *>(queries + (size_t)q * d + 8 * i + 4 * h);
+    } else {
+        for (int i = threadIdx.x; i < n; i += G1B_WARPS * 32) xs[i] = queries[(size_t)q * d + i];
+        __syncthreads();
     }
-    for (int b = warp * 32; b < nwork; b += G1B_WARPS * 32) {
-        const int nb = min(32, nwork - b);
-        const uint32_t my_row = lane < nb ? rows[b + lane] : 0u;
-        for (int g0 = 0; g0 < nb; g0 += G) {
-            float4 y[G][NCH];
-#pragma unroll
-            for (int u = 0; u < G; u++) {
-                const uint32_t row = __shfl_sync(IVF_FULL_MASK, my_row, (g0 + u) & 31);
-                const float *yr = L.centroids + (size_t)row * d;
-#pragma unroll
-                for (int c = 0; c < NCH; c++)
-                    if (g0 + u < nb && 128 * c + 4 * lane < n)
-                        y[u][c] = __ldg(reinterpret_cast<const float4 *>(yr + 128 * c + 4 * lane));
-            }
-#pragma unroll
-            for (int u = 0; u < G; u++) {
-#pragma unroll
-                for (int c = 0; c < NCH; c++)
-                    if (g0 + u < nb && 128 * c + 4 * lane < n) {
-                        const float d0 = xq[c].x - y[u][c].x, d1 = xq[c].y - y[u][c].y;
-                        const float d2 = xq[c].z - y[u][c].z, d3 = xq[c].w - y[u][c].w;
-                        *reinterpret_cast<float4 *>(buf + (size_t)(g0 + u) * stride + 128 * c + 4 * lane) =
-                            make_float4(__fmul_rn(d0, d0), __fmul_rn(d1, d1), __fmul_rn(d2, d2), __fmul_rn(d3, d3));
-                    }
-            }
+    const int ntiles = (nwork + G1B_TILE - 1) / G1B_TILE;
+    // tile t of this warp: rows [t * TILE, ...); lane l copies bytes [16 l, 16 l + 16) (+512 per pass) of every row
+    auto issue = [&](int t, int stage) {
+        const int b = t * G1B_TILE;
+        const int nb = min(G1B_TILE, nwork - b);
+        const uint32_t my = lane < nb ? rows[b + lane] : 0u;
+        float *dst = buf + (size_t)stage * G1B_TILE * pitch;
+        for (int u = 0; u < nb; u++) {
+            const uint32_t row = __shfl_sync(IVF_FULL_MASK, my, u);
+            const float *src = L.centroids + (size_t)row * d;
+            for (int o = 4 * lane; o < n; o += 128) cp_async16(dst + (size_t)u * pitch + o, src + o);
+        }
+        asm volatile("cp.async.commit_group;" ::: "memory");
+    };
+    int t = warp;
+    if (t < ntiles) issue(t, 0);
+    for (int it = 0; t < ntiles; t += G1B_WARPS, it++) {
+        const int stage = it & 1;
+        if (t + G1B_WARPS < ntiles) {
+            issue(t + G1B_WARPS, stage ^ 1);
+            asm volatile("cp.async.wait_group 1;" ::: "memory");
+        } else {
+            asm volatile("cp.async.wait_group 0;" ::: "memory");
         }
         __syncwarp();
-        if (lane < nb) {
-            const float *pr = buf + (size_t)lane * stride;
-            float acc[8];
+        const int b = t * G1B_TILE;
+        const int nb = min(G1B_TILE, nwork - b);
+        const float *pr = buf + ((size_t)stage * G1B_TILE + r) * pitch + 4 * h;
+        float a0 = 0.f, a1 = 0.f, a2 = 0.f, a3 = 0.f;
+        if (N > 0) {
 #pragma unroll
-            for (int j = 0; j < 8; j++) acc[j] = 0.f;
+            for (int i = 0; i < N / 8; i++) {
+                const float4 y = *reinterpret_cast<const float4 *>(pr + 8 * i);
+                const float d0 = xr[i].x - y.x, d1 = xr[i].y - y.y, d2 = xr[i].z - y.z, d3 = xr[i].w - y.w;
+                a0 = __fadd_rn(a0, __fmul_rn(d0, d0));
+                a1 = __fadd_rn(a1, __fmul_rn(d1, d1));
+                a2 = __fadd_rn(a2, __fmul_rn(d2, d2));
+                a3 = __fadd_rn(a3, __fmul_rn(d3, d3));
+            }
+        } else {
 #pragma unroll 4
             for (int i = 0; i < n; i += 8) {
-                const float4 p0 = *reinterpret_cast<const float4 *>(pr + i), p1 = *reinterpret_cast<const float4 *>(pr + i + 4);
-                acc[0] = __fadd_rn(acc[0], p0.x); acc[1] = __fadd_rn(acc[1], p0.y);
-                acc[2] = __fadd_rn(acc[2], p0.z); acc[3] = __fadd_rn(acc[3], p0.w);
-                acc[4] = __fadd_rn(acc[4], p1.x); acc[5] = __fadd_rn(acc[5], p1.y);
-                acc[6] = __fadd_rn(acc[6], p1.z); acc[7] = __fadd_rn(acc[7], p1.w);
+                const float4 y = *reinterpret_cast<const float4 *>(pr + i);
+                const float4 x = *reinterpret_cast<const float4 *>(xs + i + 4 * h);
+                const float d0 = x.x - y.x, d1 = x.y - y.y, d2 = x.z - y.z, d3 = x.w - y.w;
+                a0 = __fadd_rn(a0, __fmul_rn(d0, d0));
+                a1 = __fadd_rn(a1, __fmul_rn(d1, d1));
+                a2 = __fadd_rn(a2, __fmul_rn(d2, d2));
+                a3 = __fadd_rn(a3, __fmul_rn(d3, d3));
             }
-            float r = acc[0];
-#pragma unroll
-            for (int j = 1; j < 8; j++) r += acc[j];
-            dv[b + lane] = make_float2(r, __ldg(L.centroid_norms + my_row));
+        }
+        // acc[0] + acc[1] + ... + acc[7], left to right: the even lane's four, then the odd lane's
+        const float lo4 = ((a0 + a1) + a2) + a3;
+        const float left = __shfl_sync(IVF_FULL_MASK, lo4, lane & ~1);
+        const float res = (((left + a0) + a1) + a2) + a3;
+        if (h == 1 && r < nb) {
+            const uint32_t row = rows[b + r];
+            dv[b + r] = make_float2(res, __ldg(L.centroid_norms + row));
         }
         __syncwarp();
     }
@@ -392,12 +418,14 @@ __global__ void __launch_bounds__(256) group_g1b_simple_kernel(int d, const floa
 
 // ---- K-G1c: per sub-group pruning value and base
 __global__ void __launch_bounds__(G1_THREADS) group_g1c_kernel(int nprobe, int nsubc, int sub_shift, uint64_t max_codes,
-                                                               int do_pruning, const float *__restrict__ coarse_d,
+                                                               int do_pruning, int dv_in_smem,
+                                                               const float *__restrict__ coarse_d,
                                                                const uint32_t *__restrict__ coarse_i, DeviceLists L,
                                                                SegTables T, G1Work Wk)
 {
     extern __shared__ __align__(16) uint8_t sm[];
-    uint32_t *s_c = reinterpret_cast<uint32_t *>(sm);      // [nprobe]
+    float2 *s_dv = reinterpret_cast<float2 *>(sm);         // [cap] when dv_in_smem (the pair loop gathers from it)
+    uint32_t *s_c = reinterpret_cast<uint32_t *>(sm + (dv_in_smem ? (size_t)Wk.cap * 8 : 0));      // [nprobe]
     uint32_t *s_sz = s_c + nprobe;
     float *s_alpha = reinterpret_cast<float *>(s_sz + nprobe);
     float *s_cd = s_alpha + nprobe;
@@ -420,6 +448,13 @@ __global__ void __launch_bounds__(G1_THREADS) group_g1c_kernel(int nprobe, int n
     const int npairs = nprobe * nsubc;
     const uint16_t *ppos = Wk.ppos + (size_t)q * npairs;
     const float2 *dv = Wk.dv + (size_t)q * Wk.cap;
+    if (dv_in_smem) {
+        const uint2 cnt = Wk.cnt[q];
+        const int nrows = (int)(cnt.x + cnt.y);
+        for (int i = tid; i < nrows; i += G1_THREADS) s_dv[i] = dv[i];
+        dv = s_dv;
+    }
+    __syncthreads();
     uint32_t count = 0;
     for (int e0 = 0; e0 < npairs; e0 += G1_THREADS * 4) {
         uint32_t pos[4];
@@ -617,21 +652,21 @@ size_t g1_work_bytes(int nprobe, int nsubc)
     return cap * 12 + (size_t)nprobe * nsubc * 2 + 16;      // rows + (dist, norm) + pair map + counts, per query
 }
 
-template <int NCH>
+template <int N>
 static cudaError_t launch_g1b(cudaStream_t st, int nq, int d, int n, const float *queries, const DeviceLists &L,
                               const G1Work &Wk)
 {
-    const size_t smb = (size_t)G1B_WARPS * 32 * (n + 4) * 4;
-    cudaError_t e = cudaFuncSetAttribute(group_g1b_kernel<NCH>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smb);
+    const size_t smb = (size_t)G1B_WARPS * 2 * G1B_TILE * (n + 8) * 4 + (N > 0 ? 0 : (size_t)n * 4);
+    cudaError_t e = cudaFuncSetAttribute(group_g1b_kernel<N>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smb);
     if (e != cudaSuccess) return e;
-    group_g1b_kernel<NCH><<<nq, G1B_WARPS * 32, smb, st>>>(d, n, queries, L, Wk);
+    group_g1b_kernel<N><<<nq, G1B_WARPS * 32, smb, st>>>(d, n, queries, L, Wk);
     return cudaGetLastError();
 }
 
 cudaError_t launch_prep_grouping(cudaStream_t st, uint64_t *launches, int nq, int d, int nprobe, int nsubc,
                                  uint64_t max_codes, bool do_pruning, const float *queries,
                                  const float *coarse_d, const uint32_t *coarse_i, const DeviceLists &L,
-                                 const SegTables &T, void *g1_work, cudaEvent_t ev_after_g1,
+                                 const SegTables &T, void *g1_work, cudaEvent_t ev_before_g1b, cudaEvent_t ev_after_g1,
                                  unsigned long long *rows_counter)
 {
     if (nq == 0) return cudaSuccess;
@@ -660,27 +695,34 @@ cudaError_t launch_prep_grouping(cudaStream_t st, uint64_t *launches, int nq, in
     ++*launches;
     e = cudaGetLastError();
     if (e != cudaSuccess) return e;
+    if (ev_before_g1b) {
+        e = cudaEventRecord(ev_before_g1b, st);
+        if (e != cudaSuccess) return e;
+    }
     const int n = (d >> 4) << 4;      // dims fvec_L2sqr uses
-    if ((d & 3) == 0 && n >= 16 && n <= 384) {
-        if (n <= 128) e = launch_g1b<1>(st, nq, d, n, queries, L, Wk);
-        else if (n <= 256) e = launch_g1b<2>(st, nq, d, n, queries, L, Wk);
-        else e = launch_g1b<3>(st, nq, d, n, queries, L, Wk);
+    if ((d & 3) == 0 && n >= 16 && n <= 1024) {
+        if (n == 128) e = launch_g1b<128>(st, nq, d, n, queries, L, Wk);
+        else if (n == 96) e = launch_g1b<96>(st, nq, d, n, queries, L, Wk);
+        else e = launch_g1b<0>(st, nq, d, n, queries, L, Wk);
     } else {
         group_g1b_simple_kernel<<<nq, 256, (size_t)d * 4, st>>>(d, queries, L, Wk);
         e = cudaGetLastError();
     }
     ++*launches;
     if (e != cudaSuccess) return e;
-    const size_t smc = (size_t)nprobe * 21 + 16;
-    group_g1c_kernel<<<nq, G1_THREADS, smc, st>>>(nprobe, nsubc, sub_shift, max_codes, do_pruning ? 1 : 0, coarse_d,
-                                                 coarse_i, L, T, Wk);
-    ++*launches;
-    e = cudaGetLastError();
-    if (e != cudaSuccess) return e;
     if (ev_after_g1) {
         e = cudaEventRecord(ev_after_g1, st);
         if (e != cudaSuccess) return e;
     }
+    const int dv_in_smem = 0;   // measured: staging (dist, norm) in shared memory costs occupancy and bank conflicts (C2 0.25 -> 0.39 ms)
+    const size_t smc = (size_t)nprobe * 21 + 16 + (dv_in_smem ? (size_t)Wk.cap * 8 : 0);
+    e = cudaFuncSetAttribute(group_g1c_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smc);
+    if (e != cudaSuccess) return e;
+    group_g1c_kernel<<<nq, G1_THREADS, smc, st>>>(nprobe, nsubc, sub_shift, max_codes, do_pruning ? 1 : 0, dv_in_smem,
+                                                 coarse_d, coarse_i, L, T, Wk);
+    ++*launches;
+    e = cudaGetLastError();
+    if (e != cudaSuccess) return e;
     if (do_pruning) {
         group_g2_kernel<<<(nq + 31) / 32, 128, 0, st>>>(nq, npairs, T.qsd, T.nscanned, T.threshold);
         ++*launches;
