@@ -9,6 +9,9 @@ A "step" is one pass of the hot path (coarse selection -> LUT -> Grouping/prunin
 over one batch of NQ synthetic queries.  Workload (config.workload):
   c2  DEEP-shape 10M x 96 f32, 2^16 centroids, 16-byte PQ, Grouping (nsubc 64) + Pruning, nprobe 64,
       max_codes 30000, k 10, 10k queries   (BASELINE.json configs[1]; default at every N)
+  c4s SIFT1B-shape at 1/10 scale with the list length kept: 100M x 128, 2^17 centroids, 16-byte OPQ, Grouping +
+      Pruning, nprobe 128, max_codes 100000 (configs[3] scaled: the 1B index build alone is ~17 min of GEMM)
+  c3  assign of 1M x 128 base vectors per step to 2^20 centroids, vectors/s (configs[2])
   c1  SIFT-shape 1M x 128 u8-valued, 2^14 centroids, 8-byte PQ, IVFADC, nprobe 32, k 10 (configs[0])
   tiny  smoke-sized c2 (CPU-side development only)
 The index is built ON THE GPU by the library itself (k-means centroids with K-A1, train_pq, assign,
@@ -41,6 +44,13 @@ WORKLOADS = {
     # same ~760 codes per list / ~12 per sub-group as 1B over 2^20, same nprobe / max_codes operating point
     "c4s": dict(kind="sift", nb=100_000_000, d=128, nc=131072, M=16, nsubc=64, pruning=True, opq=True, nprobe=128,
                 max_codes=100000, k=10, nq=10000, nlearn=4_000_000, ntrain=65536, lloyd=2, efs=210),
+    # configs[4] (ENN variant, run_sift1b_enn_64bits.sh: 64-BYTE codes, nprobe 1, k 1, queries = base vectors, ground
+    # truth = identity, tests/test_ivfhnsw_sift1b_enn.cpp:27-47) at 1/50 scale with the list length kept
+    "c5s": dict(kind="sift", enn=True, nb=20_000_000, d=128, nc=32768, M=64, nsubc=0, pruning=False, opq=False, nprobe=1,
+                max_codes=10 ** 9, k=1, nq=10000, nlearn=2_000_000, ntrain=65536, lloyd=2, efs=64),
+    # configs[2]: base-point assign (mkindex path), one 1M-vector batch of the 1B stream per step against 2^20
+    # centroids; ranks take different batches (data parallel over base vectors, no collective)
+    "c3": dict(kind="sift", assign=True, nb=1_000_000, d=128, nc=1 << 20, M=16, nsubc=0, nq=1_000_000),
     "tiny": dict(kind="deep", nb=200_000, d=96, nc=1024, M=16, nsubc=16, pruning=True, opq=False, nprobe=16,
                  max_codes=3000, k=10, nq=1000, nlearn=100_000, ntrain=20000, lloyd=1, efs=64),
 }
@@ -130,6 +140,9 @@ def build_index(w, torch, dev, log, dist=None):
     for b0 in range(0, w["nb"], bs):
         n = min(bs, w["nb"] - b0)
         x = draw(w, torch, dev, means, n, 99991 + b0)
+        if w.get("enn") and b0 == 0:      # ENN: the queries ARE the first base vectors, ground truth = identity
+            queries = x[:w["nq"]].clone()
+            qn = (queries * queries).sum(1)
         ids = torch.arange(b0, b0 + n, dtype=torch.int32, device=dev)
         idx.add_points_dev(x, ids, None)
         # exact ground truth (neighbour #0) for the recall figure: harness-side brute force
@@ -231,6 +244,106 @@ def run_reference_cpu(w, workdir, queries_h, gt0, nq_sample, nproc, steps=1, war
                 ms_per_step=1e3 * max(o["sec"] for o in outs))
 
 
+# --------------------------------------------------------------------------- assign workload (configs[2])
+def run_assign(args, w, torch, dev, dist, rank, world, local, log, emit):
+    """IndexIVF_HNSW::assign (IndexIVF_HNSW.cpp:68-72) of one batch of base vectors per step: K-A1 = the coarse
+    GEMM + exact re-rank with nprobe 1.  value: device-resident float batch; e2e: the C-ABI assign_u8 call with a
+    HOST uint8 batch (what mkindex streams from the .bvecs file), labels read back."""
+    P = pkg()
+    t0 = time.time()
+    means = blob_means(w, torch, dev)
+    cent = draw(w, torch, dev, means, w["nc"], 4242)          # any centroid file works for the timing
+    if dist is not None:
+        dist.broadcast(cent, src=0)
+    idx = P.IndexIVF_HNSW(w["d"], w["nc"], w["M"], 8, device=dev.index or 0)
+    idx.build_quantizer(centroids=cent.cpu().numpy())
+    n = w["nb"]
+    x = draw(w, torch, dev, means, n, 99991 + rank)
+    lab = torch.empty(n, dtype=torch.int32, device=dev)
+    dd = torch.empty(n, dtype=torch.float32, device=dev)
+    stream = torch.cuda.Stream(device=dev)
+    torch.cuda.set_stream(stream)
+    idx.set_stream(stream.cuda_stream)
+    log("quantizer ready %.1fs" % (time.time() - t0))
+    flush = torch.empty(256 << 20, dtype=torch.uint8, device=dev)
+    for _ in range(max(args.warmup, 3)):
+        idx.coarse_dev(x, 1, dd, lab)
+    torch.cuda.synchronize()
+    idx.reset_stats()
+    evs = [(torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)) for _ in range(args.steps)]
+    if dist is not None:
+        dist.barrier()
+    torch.cuda.synchronize()
+    clk = Clocks(local)
+    with clk:
+        for s_, e_ in evs:
+            flush.zero_()
+            s_.record()
+            idx.coarse_dev(x, 1, dd, lab)
+            e_.record()
+        torch.cuda.synchronize()
+    if dist is not None:
+        dist.barrier()
+    ms = sum(a.elapsed_time(b) for a, b in evs)
+    launches = int(idx.stats().kernel_launches)
+    if dist is not None:
+        t = torch.tensor([ms], device=dev)
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        ms = float(t.item())
+    # exactness spot check: the first 2048 vectors against a brute force over all centroids
+    xs = x[:2048]
+    best = torch.cat([((xs * xs).sum(1)[:, None] - 2.0 * (xs @ cent[c0:c0 + 131072].T) + (cent[c0:c0 + 131072] ** 2).sum(1)[None])
+                      for c0 in range(0, w["nc"], 131072)], 1).argmin(1)
+    agree = float((best.int() == lab[:2048]).float().mean().item())
+    idx.set_timing(True)
+    idx.reset_stats()
+    idx.coarse_dev(x, 1, dd, lab)
+    torch.cuda.synchronize()
+    st2 = idx.stats()
+    idx.set_timing(False)
+    nb_int = max(1, int(st2.prep_launches)) if st2.prep_launches else 1
+    gemm_ms = st2.gemm_ms
+    peaks = {}
+    try:
+        peaks = json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json")))
+    except Exception:
+        pass
+    tf_peak = float(peaks.get("bf16_tflops_sustained", 1400.0))
+    tf = 2.0 * w["nc"] * w["d"] * n / (gemm_ms * 1e-3) / 1e12 if gemm_ms > 0 else 0.0
+    # e2e: host uint8 batch through the C ABI (H2D + u8->f32 + assign + labels D2H)
+    idx.set_stream(0)
+    xh = x.to(torch.uint8).cpu().numpy()
+    idx.assign(xh[:10000])
+    e2e_steps = max(1, min(args.steps, 2))
+    t1 = time.perf_counter()
+    for _ in range(e2e_steps):
+        lh = idx.assign(xh)
+    t2 = time.perf_counter()
+    if rank == 0:
+        emit({"metric": "assign throughput (base vectors -> nearest of 2^20 centroids)", "value": n * world * args.steps / (ms / 1e3),
+              "unit": "vectors/s", "n_gpus": world, "steps": args.steps, "warmup": max(args.warmup, 3),
+              "ms_per_step": ms / args.steps, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
+              "dtype": "f16 split hi/lo operands, f32 accumulate, exact f32 re-rank", "data": "synthetic",
+              "config": {"workload": "assign of 1M x 128 SIFT-shape base vectors per step (per GPU) to 2^20 centroids "
+                                     "(BASELINE configs[2], one batch of the 1B stream)", "nb_per_step": n * world,
+                         "d": w["d"], "nc": w["nc"], "l2": "flushed between timed steps (256 MiB write)",
+                         "sharding": "none" if world == 1 else "data parallel over base vectors, centroids replicated"},
+              "agrees_with_brute_force": agree, "clocks": clk.summary(),
+              "e2e": {"value": n * e2e_steps / (t2 - t1), "unit": "vectors/s", "h2d_bytes_per_step": int(xh.nbytes),
+                      "d2h_bytes_per_step": int(lh.nbytes)},
+              "gpu_launches": launches,
+              "roofline": {"kernel": "coarse_tc_kernel (K-A1 GEMM)", "bound": "tensor", "achieved": tf, "peak": tf_peak,
+                           "unit": "TFLOP/s", "frac": tf / tf_peak, "ms": gemm_ms,
+                           "algorithmic": "2*nc*d FLOP per vector (the fp16 hi/lo split issues 3x that)", "traffic": None,
+                           "peak_source": "MEASURED_PEAKS.json" if peaks else "fallback"},
+              "cpu_baseline": {"value": None, "unit": "vectors/s", "cores": len(os.sched_getaffinity(0)), "kind": "reference",
+                               "sample": "not run: the reference's assign is an HNSW search whose graph over 2^20 centroids "
+                                         "takes ~5 min to build (IndexIVF_HNSW.cpp:35-39)"}})
+    if dist is not None:
+        dist.destroy_process_group()
+    return 0
+
+
 # --------------------------------------------------------------------------- main
 def main():
     ap = argparse.ArgumentParser()
@@ -271,6 +384,11 @@ def main():
     log = (lambda m: print("[bench r%d] %s" % (rank, m), file=sys.stderr, flush=True))
     P = pkg()
     sharding = importlib.import_module("ivf-hnsw_b200.sharding")
+    if w.get("assign"):
+        if args.impl == "reference":
+            emit({"impl": "reference", "unavailable": "assign over 2^20 centroids needs a ~5 min HNSW build on the CPU"})
+            return 0
+        return run_assign(args, w, torch, dev, dist, rank, world, local, log, emit)
     idx, queries, gt0, cent_h = build_index(w, torch, dev, log, dist)
     if args.coarse_impl >= 0:
         idx.set_option("coarse_impl", args.coarse_impl)
@@ -283,6 +401,8 @@ def main():
                      "c4s": "SIFT1B-shape at 1/10 scale, list length kept: 100Mx128, 2^17 centroids, 16-byte OPQ, "
                             "Grouping(64)+Pruning, nprobe=128, max_codes=100000, k=10, 10k queries/step (BASELINE configs[3] "
                             "scaled)",
+                     "c5s": "SIFT1B ENN variant at 1/50 scale: 20Mx128, 2^15 centroids, 64-byte PQ, IVFADC, nprobe=1, k=1, "
+                            "queries = first 10k base vectors (BASELINE configs[4] scaled)",
                      "tiny": "tiny development workload"}[args.workload]
     config = {"workload": workload_name, "nb": w["nb"], "d": w["d"], "nc": w["nc"], "code_size": w["M"],
               "nsubc": w["nsubc"], "pruning": w["pruning"], "nprobe": nprobe, "max_codes": w["max_codes"], "k": k,

@@ -344,7 +344,7 @@ int ivfb200_coarse_dev(ivfhnsw_b200_t *h, size_t nq, const float *xq, size_t npr
     const int slack = (int)h->coarse_slack;
     int cand_cap = 0;
     const size_t per_q = coarse_work_bytes(1, (int)h->nc, (int)nprobe + slack, &cand_cap);
-    size_t qb = std::min<size_t>(nq, std::max<size_t>(128, ((size_t)3 << 29) / per_q));
+    size_t qb = std::min<size_t>(nq, std::max<size_t>(128, ((size_t)4 << 30) / per_q));
     CU(h->w_coarse.ensure(qb * per_q + 256));
     const int impl = use_tc(h) ? 1 : 0;
     if (impl) CU(h->w_xf16.ensure(qb * ((h->d + 7) / 8 * 8) * 4 + qb * 4 + 256));

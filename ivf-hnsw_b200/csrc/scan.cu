@@ -18,9 +18,11 @@
 //     and the norm lookup (word 32 + l) is conflict free as well.
 //   * a lookup address is built with ONE prmt: byte1 = code byte, byte0 = per-lane word offset.
 //
-// A CTA (8 warps) owns one (query, split); warps pull 128-code pieces of the query's segment
-// list from a shared counter, keep their candidates in a private buffer and merge them into the
-// CTA's top-k under a lock only when the buffer fills (rare once the threshold has dropped).
+// A CTA (8 warps) owns one (query, split); warps pull work items -- (list, part of <= SCAN_SEG positions) --
+// from a shared counter.  An item is processed as 16-wide WINDOWS that may start at any list position (two per
+// warp step, one per half warp; 32-wide for M >= 32): with pruning only the runs of kept sub-groups are tiled.
+// Candidates pass a float prefilter, go to a per-warp buffer and are merged into the warp's register-resident
+// sorted list a batch at a time (k <= 32), inserted one by one (k <= 128) or kept in a locked shared list.
 #include "common.cuh"
 #include "kernels.h"
 #include <type_traits>
@@ -92,14 +94,16 @@ cudaError_t launch_prep_adc(cudaStream_t st, uint64_t *launches, int nq, int npr
 // =============================================================================================
 // Grouping work list (IndexIVF_HNSW_Grouping.cpp:222-262 and :283-353), three kernels:
 //
-//  K-G1  one CTA per query.  Distances from the query to the neighbour centroids n_s of every probed
-//        list (the lazily memoised ivfhnsw::fvec_L2sqr calls of :246-250 and :312-316).  Like the
-//        reference's nc-sized memo (query_centroid_dists, :57) every distinct centroid is evaluated ONCE
-//        per query: the neighbour ids of all probed lists are de-duplicated in a shared-memory hash table
-//        (the 64-NN lists of the probed centroids overlap heavily).  Memo semantics kept: a neighbour that
-//        is itself a probed centroid reuses the coarse distance (:207-220) unless that value is < EPS.
-//        One THREAD per distance, 256-bit row loads, the 8 partial sums of fvec_L2sqr in registers: the
-//        gather is bound by L2 bandwidth, so what matters is the number of sectors in flight.
+//  K-G1  distances from the query to the neighbour centroids n_s of every probed list (the lazily memoised
+//        ivfhnsw::fvec_L2sqr calls of :246-250 and :312-316), three kernels:
+//        K-G1a one CTA per query.  Like the reference's nc-sized memo (query_centroid_dists, :57) every
+//              distinct centroid is evaluated ONCE per query: the neighbour ids of all probed lists are
+//              de-duplicated in a shared-memory hash table (the 64-NN lists of the probed centroids overlap
+//              heavily) into a dense row list.  Memo semantics kept: a neighbour that is itself a probed
+//              centroid reuses the coarse distance (:207-220) unless that value is < EPS.
+//        K-G1b the distances: whole rows fetched with coalesced cp.async into a shared-memory ring, two
+//              lanes per row adding the terms in fvec_L2sqr's order.
+//        K-G1c per (probe, sub-group) pair:
 //        Out: T.qsd[q][i][s]      = the pruning value query_subcentroid_dists (:251-252), NaN where it
 //                                   does not contribute to the threshold
 //             T.sub_base[q][i][s] = term1 + term2 of the sub-group (+inf for empty ones)
@@ -418,14 +422,13 @@ __global__ void __launch_bounds__(256) group_g1b_simple_kernel(int d, const floa
 
 // ---- K-G1c: per sub-group pruning value and base
 __global__ void __launch_bounds__(G1_THREADS) group_g1c_kernel(int nprobe, int nsubc, int sub_shift, uint64_t max_codes,
-                                                               int do_pruning, int dv_in_smem,
+                                                               int do_pruning,
                                                                const float *__restrict__ coarse_d,
                                                                const uint32_t *__restrict__ coarse_i, DeviceLists L,
                                                                SegTables T, G1Work Wk)
 {
     extern __shared__ __align__(16) uint8_t sm[];
-    float2 *s_dv = reinterpret_cast<float2 *>(sm);         // [cap] when dv_in_smem (the pair loop gathers from it)
-    uint32_t *s_c = reinterpret_cast<uint32_t *>(sm + (dv_in_smem ? (size_t)Wk.cap * 8 : 0));      // [nprobe]
+    uint32_t *s_c = reinterpret_cast<uint32_t *>(sm);      // [nprobe]
     uint32_t *s_sz = s_c + nprobe;
     float *s_alpha = reinterpret_cast<float *>(s_sz + nprobe);
     float *s_cd = s_alpha + nprobe;
@@ -447,14 +450,9 @@ __global__ void __launch_bounds__(G1_THREADS) group_g1c_kernel(int nprobe, int n
     __syncthreads();
     const int npairs = nprobe * nsubc;
     const uint16_t *ppos = Wk.ppos + (size_t)q * npairs;
-    const float2 *dv = Wk.dv + (size_t)q * Wk.cap;
-    if (dv_in_smem) {
-        const uint2 cnt = Wk.cnt[q];
-        const int nrows = (int)(cnt.x + cnt.y);
-        for (int i = tid; i < nrows; i += G1_THREADS) s_dv[i] = dv[i];
-        dv = s_dv;
-    }
-    __syncthreads();
+    // (dist, norm) pairs are gathered straight from global memory: staging them in shared memory was measured
+    // slower (occupancy, bank conflicts: C2 0.25 -> 0.39 ms)
+    const float2 *__restrict__ dv = Wk.dv + (size_t)q * Wk.cap;
     uint32_t count = 0;
     for (int e0 = 0; e0 < npairs; e0 += G1_THREADS * 4) {
         uint32_t pos[4];
@@ -714,12 +712,9 @@ cudaError_t launch_prep_grouping(cudaStream_t st, uint64_t *launches, int nq, in
         e = cudaEventRecord(ev_after_g1, st);
         if (e != cudaSuccess) return e;
     }
-    const int dv_in_smem = 0;   // measured: staging (dist, norm) in shared memory costs occupancy and bank conflicts (C2 0.25 -> 0.39 ms)
-    const size_t smc = (size_t)nprobe * 21 + 16 + (dv_in_smem ? (size_t)Wk.cap * 8 : 0);
-    e = cudaFuncSetAttribute(group_g1c_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smc);
-    if (e != cudaSuccess) return e;
-    group_g1c_kernel<<<nq, G1_THREADS, smc, st>>>(nprobe, nsubc, sub_shift, max_codes, do_pruning ? 1 : 0, dv_in_smem,
-                                                 coarse_d, coarse_i, L, T, Wk);
+    const size_t smc = (size_t)nprobe * 21 + 16;
+    group_g1c_kernel<<<nq, G1_THREADS, smc, st>>>(nprobe, nsubc, sub_shift, max_codes, do_pruning ? 1 : 0, coarse_d,
+                                                 coarse_i, L, T, Wk);
     ++*launches;
     e = cudaGetLastError();
     if (e != cudaSuccess) return e;
