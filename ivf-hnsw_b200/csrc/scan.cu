@@ -1301,7 +1301,7 @@ __global__ void __launch_bounds__(SCAN_THREADS) scan_kernel(ScanArgs a)
             if (sb_regs) {
                 sb0 = lane < a.nsubc ? __ldg(sbg + lane) : pinf;
                 sb1 = lane + 32 < a.nsubc ? __ldg(sbg + lane + 32) : pinf;
-                if (W == 16 && a.pruned && hi < (1u << 27)) {
+                if (W == 16 && a.pruned) {
                     // positions of the sub-groups inside the list (lane: sub-groups lane and lane + 32)
                     const uint32_t *szg = a.L.sub_sizes + (size_t)s_cid[seg] * a.nsubc;
                     const uint32_t sz0 = lane < a.nsubc ? __ldg(szg + lane) : 0u;
@@ -1353,11 +1353,11 @@ __global__ void __launch_bounds__(SCAN_THREADS) scan_kernel(ScanArgs a)
                         __syncwarp();
                         for (uint32_t t = 0; t < c0; t++) {
                             const uint32_t p0 = f0 + 16u * t;
-                            wbuf[i0 + t] = p0 | (min(16u, re0 - p0) << 27);
+                            wbuf[i0 + t] = (p0 - lo) | (min(16u, re0 - p0) << 16);
                         }
                         for (uint32_t t = 0; t < c1; t++) {
                             const uint32_t p1 = f1 + 16u * t;
-                            wbuf[i1 + t] = p1 | (min(16u, re1 - p1) << 27);
+                            wbuf[i1 + t] = (p1 - lo) | (min(16u, re1 - p1) << 16);
                         }
                         __syncwarp();
                     }
@@ -1367,6 +1367,14 @@ __global__ void __launch_bounds__(SCAN_THREADS) scan_kernel(ScanArgs a)
                 for (int s = lane; s < a.nsubc; s += 32) wsub[s] = sbg[s];
                 __syncwarp();
             }
+        }
+        if (!runs) {   // plain tiling of the part: same window list format ((start - lo) | len << 16)
+            __syncwarp();
+            for (int wi = lane; wi < nwin; wi += 32) {
+                const uint32_t rel = (uint32_t)wi * W;
+                wbuf[wi] = rel | (min((uint32_t)W, hi - lo - rel) << 16);
+            }
+            __syncwarp();
         }
         if (KPL == 1 || KPL > 0) {
             const uint32_t sh = ctl->thr_key;
@@ -1384,14 +1392,9 @@ __global__ void __launch_bounds__(SCAN_THREADS) scan_kernel(ScanArgs a)
                 const int wi = (j0 + c) * WPS + half;
                 uint32_t start = 0, len = 0;
                 if (c < nlive && wi < nwin) {
-                    if (runs) {
-                        const uint32_t w = wbuf[wi];
-                        start = w & 0x7ffffffu;
-                        len = w >> 27;
-                    } else {
-                        start = lo + (uint32_t)wi * W;
-                        len = min((uint32_t)W, hi - start);
-                    }
+                    const uint32_t w = wbuf[wi];
+                    start = lo + (w & 0xffffu);
+                    len = w >> 16;
                 }
                 const uint32_t rot = ((uint32_t)lane - start) & (W - 1);
                 const bool valid = rot < len;
