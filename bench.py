@@ -563,10 +563,9 @@ def main():
     tf_peak = float(peaks.get("bf16_tflops_sustained", 1400.0))
     peak_src = "MEASURED_PEAKS.json" if peaks else "fallback of B200_PROFILING.md (6650 GB/s, 1400 TFLOP/s)"
     # code_size + 1 bytes per code of the (sub-)lists the reference rule visits; this rank owns
-    # ~1/list_shards of them.  The kernel streams whole lists (pruned sub-groups included): reported as "streamed".
+    # ~1/list_shards of them.  ("walked" = all codes of the active lists: what a scan without run tiling would read.)
     scan_bytes = st2.scanned_codes / 3.0 / world_scan * code_bytes
     scan_gbs = scan_bytes / (scan_kernel_ms * 1e-3) / 1e9 if scan_kernel_ms > 0 else 0.0
-    streamed_gbs = st2.walked_codes / 3.0 / world_scan * code_bytes / (scan_kernel_ms * 1e-3) / 1e9 if scan_kernel_ms > 0 else 0.0
     gemm_flop = 2.0 * w["nc"] * w["d"] * nq_prep
     coarse_tf = gemm_flop / (gemm_ms * 1e-3) / 1e12 if gemm_ms > 0 else 0.0
     # K-G1b: d*4 bytes per DISTINCT neighbour-centroid row gathered
@@ -587,7 +586,6 @@ def main():
         "scan_kernel": {"kernel": "scan_kernel (K-S1/K-S2)", "bound": "hbm", "achieved": scan_gbs, "peak": hbm_peak,
                         "unit": "GB/s", "frac": scan_gbs / hbm_peak, "ms": scan_kernel_ms,
                         "algorithmic": "%d B per code of the sub-lists the reference rule scans" % code_bytes,
-                        "streamed_GBps": streamed_gbs,
                         "traffic": traffic.get("scan_kernel") if world == 1 else None},
         "group_g1b_kernel": {"kernel": "group_g1b_kernel (K-G1b)", "bound": "hbm", "achieved": g1_gbs, "peak": hbm_peak,
                              "unit": "GB/s", "frac": g1_gbs / hbm_peak, "ms": g1_ms,

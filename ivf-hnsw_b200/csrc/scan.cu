@@ -420,7 +420,9 @@ __global__ void __launch_bounds__(256) group_g1b_simple_kernel(int d, const floa
     }
 }
 
-// ---- K-G1c: per sub-group pruning value and base
+// ---- K-G1c: per sub-group pruning value and base (G1C_U pairs per thread in flight: the pair-map load, then the
+// dependent (dist, norm) gather, bound this kernel by latency)
+#define G1C_U 8
 __global__ void __launch_bounds__(G1_THREADS) group_g1c_kernel(int nprobe, int nsubc, int sub_shift, uint64_t max_codes,
                                                                int do_pruning,
                                                                const float *__restrict__ coarse_d,
@@ -454,27 +456,28 @@ __global__ void __launch_bounds__(G1_THREADS) group_g1c_kernel(int nprobe, int n
     // slower (occupancy, bank conflicts: C2 0.25 -> 0.39 ms)
     const float2 *__restrict__ dv = Wk.dv + (size_t)q * Wk.cap;
     uint32_t count = 0;
-    for (int e0 = 0; e0 < npairs; e0 += G1_THREADS * 4) {
-        uint32_t pos[4];
-        float icd[4];
-        float2 v[4];
+    for (int e0 = 0; e0 < npairs; e0 += G1_THREADS * G1C_U) {
+        uint32_t pos[G1C_U];
+        float icd[G1C_U];
+        float2 v[G1C_U];
 #pragma unroll
-        for (int u = 0; u < 4; u++) {
+        for (int u = 0; u < G1C_U; u++) {
             const int e = e0 + u * G1_THREADS + tid;
-            pos[u] = 0xffffu;
+            pos[u] = e < npairs ? ppos[e] : 0xffffu;
+        }
+#pragma unroll
+        for (int u = 0; u < G1C_U; u++) {
+            const int e = e0 + u * G1_THREADS + tid;
             icd[u] = 0.f;
             v[u] = make_float2(0.f, 0.f);
-            if (e < npairs) {
-                pos[u] = ppos[e];
-                if (pos[u] != 0xffffu) {
-                    const int i = pair_probe(e, nsubc, sub_shift), s = e - i * nsubc;
-                    icd[u] = __ldg(L.icd + (size_t)s_c[i] * nsubc + s);
-                    v[u] = dv[pos[u]];
-                }
+            if (pos[u] != 0xffffu) {
+                const int i = pair_probe(e, nsubc, sub_shift), s = e - i * nsubc;
+                icd[u] = __ldg(L.icd + (size_t)s_c[i] * nsubc + s);
+                v[u] = dv[pos[u]];
             }
         }
 #pragma unroll
-        for (int u = 0; u < 4; u++) {
+        for (int u = 0; u < G1C_U; u++) {
             const int e = e0 + u * G1_THREADS + tid;
             if (e >= npairs) continue;
             float r = qnan, sb = __int_as_float(0x7f800000);
