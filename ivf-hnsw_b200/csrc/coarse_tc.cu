@@ -138,6 +138,9 @@ static __device__ __forceinline__ void tma_load_2d(uint32_t dst, const CUtensorM
 static __device__ __forceinline__ void umma_f16(uint32_t d_tmem, uint64_t adesc, uint64_t bdesc, uint32_t idesc,
                                                 uint32_t accumulate)
 {
+#ifdef TC_DIAG_NO_MMA   /* timing experiment only: no tensor-core work, barriers and TMA traffic unchanged */
+    return;
+#endif
     asm volatile(
         "{\n\t.reg .pred p;\n\tsetp.ne.b32 p, %4, 0;\n\t"
         "tcgen05.mma.cta_group::1.kind::f16 [%0], %1, %2, %3, p;\n\t}"
@@ -368,6 +371,9 @@ coarse_tc_kernel(const __grid_constant__ CUtensorMap tm_qhi, const __grid_consta
 #pragma unroll
                         for (int ii = 0; ii < 4; ii++) {
                             const int i = i4 * 4 + ii;
+#ifdef TC_DIAG_NO_EPI   /* timing experiment only: everything but the per-element epilogue work */
+                            if (i) continue;
+#endif
                             const float val = fmaf(__uint_as_float(v[jb & 1][i]), f, cnv[ii]);
                             const float x = __uint_as_float((__float_as_uint(val) & p.keep_mask) | (uint32_t)(jb * 32 + i));
                             const float m0 = fmaxf(a0, x);
