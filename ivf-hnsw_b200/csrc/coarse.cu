@@ -120,8 +120,9 @@ static __device__ __forceinline__ uint32_t fkey(float f)
 }
 
 #define SEL_MAX_FLAGGED 32
-#define SEL_CACHE 8
 
+// SEL_CACHE: keys a thread keeps in registers across the radix passes (rows up to 256 * SEL_CACHE kept values)
+template <int SEL_CACHE>
 __global__ void __launch_bounds__(256) coarse_select_kernel(int nc, int d, int ngroups, int nprobe, int kprime,
                                                             int cand_cap, const float *__restrict__ Q,
                                                             const float *__restrict__ Cn,
@@ -353,10 +354,17 @@ cudaError_t launch_coarse(cudaStream_t st, uint64_t *launches, int impl, int nq,
     if (kprime > ngroups * COARSE_T) kprime = ngroups * COARSE_T;
     if (kprime < 1) kprime = 1;
     const size_t sm2 = (size_t)d * 4 + (size_t)W.cand_cap * 8;
-    e = cudaFuncSetAttribute(coarse_select_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sm2);
-    if (e != cudaSuccess) return e;
-    coarse_select_kernel<<<nq, 256, sm2, st>>>(nc, d, ngroups, nprobe, kprime, W.cand_cap, queries, centroids,
-                                               W.grp_val, W.grp_idx, impl == 1 ? 1 : 0, self_off, W.err, out_d, out_i);
+    if (ngroups * COARSE_T <= 256 * 8) {
+        e = cudaFuncSetAttribute(coarse_select_kernel<8>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sm2);
+        if (e != cudaSuccess) return e;
+        coarse_select_kernel<8><<<nq, 256, sm2, st>>>(nc, d, ngroups, nprobe, kprime, W.cand_cap, queries, centroids,
+                                                      W.grp_val, W.grp_idx, impl == 1 ? 1 : 0, self_off, W.err, out_d, out_i);
+    } else {
+        e = cudaFuncSetAttribute(coarse_select_kernel<16>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sm2);
+        if (e != cudaSuccess) return e;
+        coarse_select_kernel<16><<<nq, 256, sm2, st>>>(nc, d, ngroups, nprobe, kprime, W.cand_cap, queries, centroids,
+                                                       W.grp_val, W.grp_idx, impl == 1 ? 1 : 0, self_off, W.err, out_d, out_i);
+    }
     ++*launches;
     return cudaGetLastError();
 }

@@ -5,26 +5,52 @@
 namespace ivfb200 {
 
 // LinearTransform::apply_noalloc / transform_transpose (faiss/VectorTransform.cpp:106-158) for a
-// d x d matrix without bias.  8 rows per CTA staged in shared memory; thread o owns output column o.
+// d x d matrix without bias.  ROT_ROWS rows per CTA staged in shared memory; thread o owns output column o and
+// adds a_oj * x_j for j = 0, 1, ... in order (one fmaf chain per output, as before).  The matrix goes through
+// shared memory in 128 x 32 tiles loaded along its contiguous dimension: reading A[o][j] straight from global,
+// one row per thread, touched 32 lines per warp load and left the kernel L1-bound (100 us for 10k x 128).
+#define ROT_ROWS 16
+#define ROT_JC 32
 template <bool TRANSPOSE>
 __global__ void __launch_bounds__(128) rotate_kernel(size_t n, int d, const float *__restrict__ A,
                                                      const float *__restrict__ x, float *__restrict__ out)
 {
-    extern __shared__ float sx[];  // [8][d]
-    const size_t row0 = (size_t)blockIdx.x * 8;
-    const int rows = (int)((n - row0) < 8 ? (n - row0) : 8);
-    for (int i = threadIdx.x; i < rows * d; i += blockDim.x) sx[i] = x[row0 * d + i];
-    __syncthreads();
-    for (int o = threadIdx.x; o < d; o += blockDim.x) {
-        float acc[8];
+    extern __shared__ __align__(16) float sx[];  // [ROT_ROWS][d] then the tile [128][ROT_JC + 1]
+    float *sa = sx + (size_t)ROT_ROWS * d;
+    const int tid = threadIdx.x;
+    const size_t row0 = (size_t)blockIdx.x * ROT_ROWS;
+    const int rows = (int)((n - row0) < ROT_ROWS ? (n - row0) : ROT_ROWS);
+    for (int i = tid; i < ROT_ROWS * d; i += 128) sx[i] = i < rows * d ? x[row0 * d + i] : 0.f;
+    for (int ob = 0; ob < d; ob += 128) {
+        const int o = ob + tid;
+        float acc[ROT_ROWS];
 #pragma unroll
-        for (int r = 0; r < 8; r++) acc[r] = 0.f;
-        for (int j = 0; j < d; j++) {
-            const float a = TRANSPOSE ? __ldg(A + (size_t)j * d + o) : __ldg(A + (size_t)o * d + j);
+        for (int r = 0; r < ROT_ROWS; r++) acc[r] = 0.f;
+        for (int j0 = 0; j0 < d; j0 += ROT_JC) {
+            __syncthreads();   // previous tile consumed (and sx written, first time round)
+            if (TRANSPOSE) {
+                // a(o, j) = A[j][o]: contiguous along o
+                for (int it = 0; it < ROT_JC; it++) {
+                    const int j = j0 + it;
+                    sa[tid * (ROT_JC + 1) + it] = (j < d && o < d) ? __ldg(A + (size_t)j * d + o) : 0.f;
+                }
+            } else {
+                // a(o, j) = A[o][j]: contiguous along j
+                for (int it = 0; it < 32; it++) {
+                    const int oo = it * 4 + (tid >> 5), jj = tid & 31;
+                    sa[oo * (ROT_JC + 1) + jj] = (ob + oo < d && j0 + jj < d) ? __ldg(A + (size_t)(ob + oo) * d + j0 + jj) : 0.f;
+                }
+            }
+            __syncthreads();
+            const int jn = min(ROT_JC, d - j0);
+            for (int jj = 0; jj < jn; jj++) {
+                const float a = sa[tid * (ROT_JC + 1) + jj];
 #pragma unroll
-            for (int r = 0; r < 8; r++) acc[r] = fmaf(a, sx[r * d + j], acc[r]);
+                for (int r = 0; r < ROT_ROWS; r++) acc[r] = fmaf(a, sx[r * d + j0 + jj], acc[r]);
+            }
         }
-        for (int r = 0; r < rows; r++) out[(row0 + r) * d + o] = acc[r];
+        if (o < d)
+            for (int r = 0; r < rows; r++) out[(row0 + r) * d + o] = acc[r];
     }
 }
 
@@ -32,10 +58,18 @@ cudaError_t launch_rotate(cudaStream_t st, uint64_t *launches, size_t n, int d, 
                           const float *x, float *out)
 {
     if (n == 0) return cudaSuccess;
-    const unsigned grid = (unsigned)((n + 7) / 8);
-    const size_t sm = (size_t)8 * d * sizeof(float);
-    if (transpose) rotate_kernel<true><<<grid, 128, sm, st>>>(n, d, A, x, out);
-    else rotate_kernel<false><<<grid, 128, sm, st>>>(n, d, A, x, out);
+    const unsigned grid = (unsigned)((n + ROT_ROWS - 1) / ROT_ROWS);
+    const size_t sm = ((size_t)ROT_ROWS * d + 128 * (ROT_JC + 1)) * sizeof(float);
+    cudaError_t e;
+    if (transpose) {
+        e = cudaFuncSetAttribute(rotate_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sm);
+        if (e != cudaSuccess) return e;
+        rotate_kernel<true><<<grid, 128, sm, st>>>(n, d, A, x, out);
+    } else {
+        e = cudaFuncSetAttribute(rotate_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sm);
+        if (e != cudaSuccess) return e;
+        rotate_kernel<false><<<grid, 128, sm, st>>>(n, d, A, x, out);
+    }
     ++*launches;
     return cudaGetLastError();
 }
