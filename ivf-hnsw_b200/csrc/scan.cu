@@ -864,6 +864,7 @@ cudaError_t launch_lut(cudaStream_t st, uint64_t *launches, int M, int nq, int d
 // =============================================================================================
 struct ScanArgs {
     int d, nprobe, nsubc, k, nsplit;
+    int seg;                  // list positions per work item (<= SCAN_SEG)
     int pruned;               // Grouping: sub-groups may be pruned (sub_base = +inf) -> tile kept runs only
     const float *lutc;        // [nq][256][M] compact tables from K-L1
     const float *norm_table;  // [256]
@@ -1174,7 +1175,7 @@ __global__ void __launch_bounds__(SCAN_THREADS) scan_kernel(ScanArgs a)
         uint32_t run = 0;
         for (int b = 0; b < nprobe; b += 32) {
             const int i = b + lane;
-            const uint32_t pieces = i < nprobe ? (s_n[i] + SCAN_SEG - 1) / SCAN_SEG : 0u;
+            const uint32_t pieces = i < nprobe ? (s_n[i] + (uint32_t)a.seg - 1) / (uint32_t)a.seg : 0u;
             uint32_t incl = pieces;
 #pragma unroll
             for (int off = 1; off < 32; off <<= 1) {
@@ -1279,7 +1280,7 @@ __global__ void __launch_bounds__(SCAN_THREADS) scan_kernel(ScanArgs a)
         if (piece < SCAN_ITEMS) {
             const uint32_t it = s_item[piece];
             seg = (int)(it & 0xffffu);
-            lo = (it >> 16) * SCAN_SEG;
+            lo = (it >> 16) * (uint32_t)a.seg;
         } else {
             for (int b = 0; b < nprobe; b += 32) {
                 const int i = b + lane;
@@ -1287,9 +1288,9 @@ __global__ void __launch_bounds__(SCAN_THREADS) scan_kernel(ScanArgs a)
                 seg += __popc(__ballot_sync(IVF_FULL_MASK, le));
             }
             seg -= 1;
-            lo = (uint32_t)(piece - (int)s_poff[seg]) * SCAN_SEG;
+            lo = (uint32_t)(piece - (int)s_poff[seg]) * (uint32_t)a.seg;
         }
-        const uint32_t hi = min(s_n[seg], lo + SCAN_SEG);
+        const uint32_t hi = min(s_n[seg], lo + (uint32_t)a.seg);
         const uint32_t lslot = s_slot[seg], lseq = s_seq[seg];
         const float base = s_base[seg];
         int nwin = (int)((hi - lo + W - 1) / W);
@@ -1638,6 +1639,8 @@ cudaError_t launch_scan(cudaStream_t st, uint64_t *launches, int M, bool groupin
     ScanArgs a;
     a.out_seq = out_seq;
     a.pruned = (grouping && pruned) ? 1 : 0;
+    // few probes: cut the lists finer so that all 8 warps of a query's CTA find work (ENN: ONE list per query)
+    a.seg = nprobe >= 8 ? SCAN_SEG : 128;
     a.d = d; a.nprobe = nprobe; a.nsubc = grouping ? nsubc : 0; a.k = k; a.nsplit = nsplit;
     a.lutc = lutc; a.norm_table = norm_table; a.L = L; a.T = T; a.c_begin = c_begin; a.c_end = c_end;
     a.part_d = part_d; a.part_seq = part_seq; a.part_slot = part_slot; a.out_d = out_d; a.out_labels = out_labels;
