@@ -174,7 +174,7 @@ int ivfhnsw_b200_set_stream(ivfhnsw_b200_t *h, void *stream);
 typedef struct ivfhnsw_b200_stats {
     uint64_t kernel_launches;   /* kernels of this library launched since create/reset          */
     uint64_t scanned_codes;     /* codes whose ADC distance was required by the reference rule  */
-    uint64_t walked_codes;      /* codes actually streamed by the scan kernel (>= scanned)      */
+    uint64_t walked_codes;      /* codes of the active lists, pruned sub-groups included (>= scanned) */
     uint64_t queries;           /* queries searched                                             */
     double scan_ms;             /* CUDA-event time spent in the ADC scan kernel                 */
     double coarse_ms;           /* ... in the coarse GEMM + select kernels                      */

@@ -11,7 +11,6 @@
 // ADC scan geometry
 #define SCAN_THREADS 256
 #define SCAN_WARPS 8
-#define SCAN_CHUNK 32                      // codes per warp step (one per lane)
 #define SCAN_PF 4                          // warp steps (32 codes each) whose loads are in flight together
 #define SCAN_SEG 1024                      // list positions per work item
 #define SCAN_ITEMS 256                     // work items whose (list, part) is tabulated

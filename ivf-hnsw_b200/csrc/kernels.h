@@ -39,7 +39,7 @@ struct SegTables {
     float *qsd;           // [nq][nprobe][nsubc] scratch: pruning values (K-G1 -> K-G2/K-G3), not part of the record
     float *threshold;     // [nq]
     uint32_t *nscanned;   // [nq] codes the reference rule scans (all shards)
-    uint32_t *nwalked;    // [nq] codes the scan kernels stream (all shards)
+    uint32_t *nwalked;    // [nq] codes of the ACTIVE lists (what a scan without kept-run tiling would stream; all shards)
     __host__ __device__ uint32_t *slot(size_t q) const { return rec + q * stride; }                  // first slot of the list
     __host__ __device__ uint32_t *n(size_t q) const { return rec + q * stride + nprobe; }             // codes to walk (0 = skipped)
     __host__ __device__ float *base(size_t q) const { return reinterpret_cast<float *>(rec + q * stride + 2 * nprobe); }   // term1 (IVFADC)
