@@ -129,6 +129,52 @@ static cudaError_t launch_pq_encode_t(cudaStream_t st, size_t n, int M, const fl
     return cudaGetLastError();
 }
 
+// any other sub-vector length: the same summation structure (8-lane blocks, a 4-lane block, a tail of <= 3) with a
+// run-time dsub; slower (no register-resident sub-vector), bit-identical
+static __device__ __forceinline__ float faiss_l2sqr_rt(const float *x, const float *y, int dsub)
+{
+    float l8[8];
+#pragma unroll
+    for (int l = 0; l < 8; l++) l8[l] = 0.f;
+    int i = 0;
+    for (; i + 8 <= dsub; i += 8)
+#pragma unroll
+        for (int l = 0; l < 8; l++) { const float df = x[i + l] - y[i + l]; l8[l] = fmaf(df, df, l8[l]); }
+    float l4[4];
+#pragma unroll
+    for (int l = 0; l < 4; l++) l4[l] = l8[l + 4] + l8[l];
+    if (dsub - i >= 4) {
+#pragma unroll
+        for (int l = 0; l < 4; l++) { const float df = x[i + l] - y[i + l]; l4[l] = fmaf(df, df, l4[l]); }
+        i += 4;
+    }
+#pragma unroll
+    for (int l = 0; l < 3; l++)
+        if (i + l < dsub) { const float df = x[i + l] - y[i + l]; l4[l] = fmaf(df, df, l4[l]); }
+    return (l4[0] + l4[1]) + (l4[2] + l4[3]);
+}
+
+__global__ void __launch_bounds__(256) pq_encode_generic_kernel(size_t n, int M, int dsub, const float *__restrict__ pqc,
+                                                                const float *__restrict__ res,
+                                                                uint8_t *__restrict__ codes)
+{
+    const int d = M * dsub;
+    // one thread per (vector, sub-quantizer)
+    for (size_t e = (size_t)blockIdx.x * blockDim.x + threadIdx.x; e < n * M; e += (size_t)gridDim.x * blockDim.x) {
+        const size_t v = e / M;
+        const int m = (int)(e - v * M);
+        const float *r = res + v * d + (size_t)m * dsub;
+        const float *c = pqc + (size_t)m * 256 * dsub;
+        float best = 1e20f;
+        int bi = -1;
+        for (int j = 0; j < 256; j++) {
+            const float dis = faiss_l2sqr_rt(r, c + (size_t)j * dsub, dsub);
+            if (dis < best) { best = dis; bi = j; }
+        }
+        codes[e] = (uint8_t)bi;
+    }
+}
+
 cudaError_t launch_pq_encode(cudaStream_t st, uint64_t *launches, size_t n, int d, int M, const float *pqc,
                              const float *residuals, uint8_t *codes)
 {
@@ -146,8 +192,12 @@ cudaError_t launch_pq_encode(cudaStream_t st, uint64_t *launches, size_t n, int 
         case 24: return launch_pq_encode_t<24>(st, n, M, pqc, residuals, codes);
         case 32: return launch_pq_encode_t<32>(st, n, M, pqc, residuals, codes);
     }
-    --*launches;
-    return cudaErrorInvalidValue;
+    {
+        size_t blocks = (n * (size_t)M + 255) / 256;
+        if (blocks > 148 * 8) blocks = 148 * 8;
+        pq_encode_generic_kernel<<<(unsigned)blocks, 256, 0, st>>>(n, M, d / M, pqc, residuals, codes);
+    }
+    return cudaGetLastError();
 }
 
 // ProductQuantizer::decode (faiss/ProductQuantizer.cpp:338-360)

@@ -701,7 +701,8 @@ cudaError_t launch_prep_grouping(cudaStream_t st, uint64_t *launches, int nq, in
         if (e != cudaSuccess) return e;
     }
     const int n = (d >> 4) << 4;      // dims fvec_L2sqr uses
-    if ((d & 3) == 0 && n >= 16 && n <= 1024) {
+    // the ring of the transposing kernel must fit shared memory: 4 warps x 2 tiles x 16 rows x (n + 8) floats
+    if ((d & 3) == 0 && n >= 16 && (size_t)G1B_WARPS * 2 * G1B_TILE * (n + 8) * 4 + (size_t)n * 4 <= 200 * 1024) {
         if (n == 128) e = launch_g1b<128>(st, nq, d, n, queries, L, Wk);
         else if (n == 96) e = launch_g1b<96>(st, nq, d, n, queries, L, Wk);
         else e = launch_g1b<0>(st, nq, d, n, queries, L, Wk);

@@ -21,16 +21,25 @@ W_DEEP = dict(kind="deep", nb=2_000_000, d=96, nc=16384, M=16, nsubc=64, pruning
               max_codes=30000, k=10, nq=256, nlearn=400_000, ntrain=30000, lloyd=1, efs=64)
 
 
+# shapes that take the other K-G1b paths: d = 104 uses 96 dims with a 104-float row pitch (fstdistfunc drops the
+# d % 16 tail), d = 512 does not fit the shared-memory ring and falls back to one thread per row
+W_D104 = dict(kind="sift", nb=200_000, d=104, nc=512, M=8, nsubc=32, pruning=True, opq=False, nprobe=16,
+              max_codes=4000, k=10, nq=128, nlearn=60_000, ntrain=20000, lloyd=1, efs=64)
+W_D512 = dict(kind="deep", nb=100_000, d=512, nc=256, M=8, nsubc=16, pruning=True, opq=False, nprobe=8,
+              max_codes=3000, k=10, nq=128, nlearn=40_000, ntrain=20000, lloyd=1, efs=64)
+WORKLOADS = {"long_opq": W_LONG, "deep": W_DEEP, "d104": W_D104, "d512": W_D512}
+
+
 def _bench():
     sys.path.insert(0, ROOT)
     return importlib.import_module("bench")
 
 
-@pytest.fixture(scope="module", params=["long_opq", "deep"])
+@pytest.fixture(scope="module", params=list(WORKLOADS))
 def built(request):
     import torch
     bench = _bench()
-    w = dict(W_LONG if request.param == "long_opq" else W_DEEP)
+    w = dict(WORKLOADS[request.param])
     dev = torch.device("cuda:0")
     idx, queries, gt, cent_h = bench.build_index(w, torch, dev, lambda m: None)
     yield w, idx, queries, gt, cent_h
@@ -57,7 +66,8 @@ def test_cuda_equals_port_on_gpu_built_index(port, built):
     scale = float(ix["centroid_norms"].max())
     assert dist_close(D, Dps, scale)
     assert labels_match_up_to_ties(D, L, Dps, Lps, scale) == 0
-    assert np.mean(L == Lps) >= 0.99
+    # position-wise equality is only expected where distances are distinct (8-byte codes of 512-d vectors collide)
+    assert np.mean(L == Lps) >= (0.99 if w["M"] >= 16 else 0.9)
     assert np.array_equal(scanned.astype(np.int64), np.asarray(pncode).astype(np.int64))
     assert np.allclose(thr, pthr, rtol=1e-5)
 
@@ -89,7 +99,8 @@ def test_search_properties_at_scale(built):
     torch.cuda.synchronize()
     assert torch.equal(D, D100[:, :k]) and torch.equal(L, L100[:, :k])
     # recall of the true nearest neighbour is far above chance
-    assert float((L100 == gt[:nq, None]).any(1).float().mean()) > 0.3
+    if w["M"] >= 16:      # (8-byte codes of 100+-dimensional vectors are too coarse for a meaningful bound)
+        assert float((L100 == gt[:nq, None]).any(1).float().mean()) > 0.3
     # sharded by centroid range (3 shards, query-sliced preparation) == unsharded, bit for bit
     R = 3
     per = (nq + R - 1) // R
