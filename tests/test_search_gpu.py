@@ -208,3 +208,28 @@ def test_sharded_search_equals_single_gpu(name, nshards):
     torch.cuda.synchronize()
     assert torch.equal(L0, L1) and torch.equal(D0, D1)
     idx.close()
+
+
+@pytest.mark.parametrize("name", ["adc_d32", "grp_d32", "grp_sift_m16", "grp_long_m16", "grp_deep_opq"])
+@pytest.mark.parametrize("nprobe,max_codes,k", [(1, 10 ** 9, 1), (3, 1, 5), ("all", 10 ** 9, 10), ("all", 700, 33),
+                                                (7, 50, 129)])
+def test_operating_point_corners(port, name, nprobe, max_codes, k):
+    """Corners of the (nprobe, max_codes, k) space on the GPU's own exact candidate lists: one probe, a max_codes that
+    the first list already exceeds, every list probed, k on both sides of the 32 / 128 result-list switches."""
+    pkg = load_pkg()
+    g, ix, runs = load_golden(name)
+    scale = float(ix["centroid_norms"].max())
+    idx = make_index(pkg, ix)
+    idx.load_index_dict(ix)
+    np_ = ix["nc"] if nprobe == "all" else nprobe
+    idx.nprobe, idx.max_codes = np_, max_codes
+    cd, ci = idx.coarse(g["Q"], np_)
+    for pr in ((False, True) if ix["nsubc"] else (False,)):
+        idx.do_pruning = pr
+        D, L = idx.search2(k, g["Q"], cd, ci)
+        Dp, Lp = port.search(ix, g["Q"], cd, ci, k, np_, max_codes, pr)
+        o = np.argsort(Dp, axis=1, kind="stable")
+        Dps, Lps = np.take_along_axis(Dp, o, 1), np.take_along_axis(Lp, o, 1)
+        assert dist_close(D, Dps, scale), (name, pr)
+        assert labels_match_up_to_ties(D, L, Dps, Lps, scale) == 0, (name, pr)
+    idx.close()
