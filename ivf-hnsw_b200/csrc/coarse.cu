@@ -157,9 +157,22 @@ __global__ void __launch_bounds__(256) coarse_select_kernel(int nc, int d, int n
 
     // ---- radix select: key of the kprime-th smallest kept value.  The keys a thread owns stay in registers
     // across the passes when the row is short enough (nc <= 65536); warp 0 scans the histogram.
-    const bool cached = n <= 256 * SEL_CACHE;
+    // Longer rows (nc > 2^17): the select runs on the 256 per-thread MINIMA instead.  Their kprime-th smallest is
+    // an upper bound of the row's kprime-th smallest (they are 256 distinct entries of the row), and everything
+    // below only needs tau >= the true value: the collect pass takes a few more candidates (expected
+    // n * -ln(1 - kprime/256) / (n/256) instead of kprime), the exact re-rank sorts them out.  Two passes over the
+    // row instead of five.
+    const bool sampled = n > 256 * SEL_CACHE && kprime <= 192;
+    const bool cached = sampled || n <= 256 * SEL_CACHE;
+    const int nsel = sampled ? 256 : n;
     uint32_t kc[SEL_CACHE];
-    if (cached) {
+    if (sampled) {
+        uint32_t mk = 0xffffffffu;
+        for (int i = tid; i < n; i += 256) mk = min(mk, fkey(gv[i]));
+#pragma unroll
+        for (int j = 0; j < SEL_CACHE; j++) kc[j] = 0xffffffffu;
+        kc[0] = mk;
+    } else if (cached) {
 #pragma unroll
         for (int j = 0; j < SEL_CACHE; j++) {
             const int i = tid + 256 * j;
@@ -173,7 +186,7 @@ __global__ void __launch_bounds__(256) coarse_select_kernel(int nc, int d, int n
         if (cached) {
 #pragma unroll
             for (int j = 0; j < SEL_CACHE; j++)
-                if (tid + 256 * j < n) { vor |= kc[j]; vand &= kc[j]; }
+                if (tid + 256 * j < nsel) { vor |= kc[j]; vand &= kc[j]; }
         } else {
             for (int i = tid; i < n; i += 256) { const uint32_t kx = fkey(gv[i]); vor |= kx; vand &= kx; }
         }
@@ -197,7 +210,7 @@ __global__ void __launch_bounds__(256) coarse_select_kernel(int nc, int d, int n
         if (cached) {
 #pragma unroll
             for (int j = 0; j < SEL_CACHE; j++)
-                if ((kc[j] & pmask) == prefix && tid + 256 * j < n) atomicAdd(&hist[(kc[j] >> shift) & dmask], 1u);
+                if ((kc[j] & pmask) == prefix && tid + 256 * j < nsel) atomicAdd(&hist[(kc[j] >> shift) & dmask], 1u);
         } else {
             for (int i = tid; i < n; i += 256) {
                 const uint32_t kx = fkey(gv[i]);

@@ -233,3 +233,23 @@ def test_operating_point_corners(port, name, nprobe, max_codes, k):
         assert dist_close(D, Dps, scale), (name, pr)
         assert labels_match_up_to_ties(D, L, Dps, Lps, scale) == 0, (name, pr)
     idx.close()
+
+
+@pytest.mark.parametrize("nprobe", [1, 40])
+def test_coarse_long_rows_vs_brute_force(nprobe):
+    """nc large enough (> 2^17) for the select kernel's long-row path (threshold from the per-thread minima)."""
+    pkg = load_pkg()
+    d, nc, nq = 32, 150_000, 200
+    rng = np.random.default_rng(5)
+    C = rng.standard_normal((nc, d)).astype(np.float32)
+    Q = (C[rng.integers(0, nc, nq)] + 0.5 * rng.standard_normal((nq, d))).astype(np.float32)
+    idx = pkg.IndexIVF_HNSW(d, nc, 8, 8)
+    idx.build_quantizer(centroids=C)
+    cd, ci = idx.coarse(Q, nprobe)
+    dd = ((Q.astype(np.float64)[:, None, :] - C.astype(np.float64)[None, :, :]) ** 2).sum(-1)
+    want = np.sort(dd, axis=1)[:, :nprobe]
+    assert np.allclose(cd, want, rtol=2e-5, atol=1e-5)
+    got = np.take_along_axis(dd, ci.astype(np.int64), 1)
+    assert np.allclose(got, want, rtol=2e-5, atol=1e-5)
+    assert np.all(np.diff(cd, axis=1) >= 0)
+    idx.close()
