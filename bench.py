@@ -11,6 +11,7 @@ over one batch of NQ synthetic queries.  Workload (config.workload):
       max_codes 30000, k 10, 10k queries   (BASELINE.json configs[1]; default at every N)
   c4s SIFT1B-shape at 1/10 scale with the list length kept: 100M x 128, 2^17 centroids, 16-byte OPQ, Grouping +
       Pruning, nprobe 128, max_codes 100000 (configs[3] scaled: the 1B index build alone is ~17 min of GEMM)
+  c4n the same with the real 2^20 centroids and a tenth of the points (coarse stage and row gather as at 1B)
   c3  assign of 1M x 128 base vectors per step to 2^20 centroids, vectors/s (configs[2])
   c1  SIFT-shape 1M x 128 u8-valued, 2^14 centroids, 8-byte PQ, IVFADC, nprobe 32, k 10 (configs[0])
   tiny  smoke-sized c2 (CPU-side development only)
@@ -44,6 +45,10 @@ WORKLOADS = {
     # same ~760 codes per list / ~12 per sub-group as 1B over 2^20, same nprobe / max_codes operating point
     "c4s": dict(kind="sift", nb=100_000_000, d=128, nc=131072, M=16, nsubc=64, pruning=True, opq=True, nprobe=128,
                 max_codes=100000, k=10, nq=10000, nlearn=4_000_000, ntrain=65536, lloyd=2, efs=210),
+    # configs[3] with its real CENTROID COUNT (2^20) and a tenth of the points: the coarse stage and the neighbour-row
+    # gather (512 MB centroid table: HBM, not L2) as at 1B; the lists are a tenth as long (c4s has the other half)
+    "c4n": dict(kind="sift", nb=100_000_000, d=128, nc=1 << 20, M=16, nsubc=64, pruning=True, opq=True, nprobe=128,
+                max_codes=100000, k=10, nq=10000, nlearn=4_000_000, ntrain=65536, lloyd=1, efs=210),
     # configs[4] (ENN variant, run_sift1b_enn_64bits.sh: 64-BYTE codes, nprobe 1, k 1, queries = base vectors, ground
     # truth = identity, tests/test_ivfhnsw_sift1b_enn.cpp:27-47) at 1/50 scale with the list length kept
     "c5s": dict(kind="sift", enn=True, nb=20_000_000, d=128, nc=32768, M=64, nsubc=0, pruning=False, opq=False, nprobe=1,
@@ -401,6 +406,8 @@ def main():
                      "c4s": "SIFT1B-shape at 1/10 scale, list length kept: 100Mx128, 2^17 centroids, 16-byte OPQ, "
                             "Grouping(64)+Pruning, nprobe=128, max_codes=100000, k=10, 10k queries/step (BASELINE configs[3] "
                             "scaled)",
+                     "c4n": "SIFT1B-shape with the real centroid count: 100Mx128, 2^20 centroids, 16-byte OPQ, Grouping(64)+Pruning, "
+                            "nprobe=128, max_codes=100000, k=10, 10k queries/step (BASELINE configs[3] with a tenth of the points)",
                      "c5s": "SIFT1B ENN variant at 1/50 scale: 20Mx128, 2^15 centroids, 64-byte PQ, IVFADC, nprobe=1, k=1, "
                             "queries = first 10k base vectors (BASELINE configs[4] scaled)",
                      "tiny": "tiny development workload"}[args.workload]

@@ -168,7 +168,13 @@ __global__ void __launch_bounds__(256) coarse_select_kernel(int nc, int d, int n
     uint32_t kc[SEL_CACHE];
     if (sampled) {
         uint32_t mk = 0xffffffffu;
-        for (int i = tid; i < n; i += 256) mk = min(mk, fkey(gv[i]));
+        // entry i = 4 * group + rank-in-group: a thread that strode by 256 would only ever see ONE rank (the threads
+        // with tid % 4 == 3 only 4th-best values) and the minima would say nothing about the row; rotating the
+        // assignment by one entry per pass gives every thread all four ranks (loads stay coalesced)
+        for (int j = 0; j * 256 < n; j++) {
+            const int i = j * 256 + ((tid + j) & 255);
+            if (i < n) mk = min(mk, fkey(gv[i]));
+        }
 #pragma unroll
         for (int j = 0; j < SEL_CACHE; j++) kc[j] = 0xffffffffu;
         kc[0] = mk;
