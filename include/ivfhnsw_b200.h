@@ -194,7 +194,8 @@ int ivfhnsw_b200_reset_stats(ivfhnsw_b200_t *h);
 /* Grouping debug outputs of the last search call's first min(nq, cap) queries: pruning threshold per
  * query (IndexIVF_HNSW_Grouping.cpp:261) and codes scanned per query */
 int ivfhnsw_b200_last_thresholds(ivfhnsw_b200_t *h, size_t cap, float *thresholds, uint32_t *scanned);
-/* tuning knobs: "coarse_slack", "coarse_impl" (0 = SIMT fp32, 1 = tcgen05 bf16), "scan_split" (0 = auto) */
+/* tuning knobs: "coarse_slack", "coarse_impl" (0 = SIMT fp32, 1 = tcgen05 split-fp16 three products, 2 = two products
+ * with a widened select threshold, the default), "scan_split" (0 = auto) */
 int ivfhnsw_b200_set_option(ivfhnsw_b200_t *h, const char *name, long value);
 
 #ifdef __cplusplus

@@ -300,7 +300,7 @@ int ivfhnsw_b200_rotate_quantizer(ivfhnsw_b200_t *h)
 }
 
 // ------------------------------------------------------------------------------------ coarse helpers
-static bool use_tc(const ivfhnsw_b200_t *h) { return h->coarse_impl == 1 && coarse_tc_supported((int)h->d); }
+static bool use_tc(const ivfhnsw_b200_t *h) { return h->coarse_impl >= 1 && coarse_tc_supported((int)h->d); }
 
 // carve the fp16 operand buffers: centroids [hi | lo | max bits], queries [hi | lo | fac]
 static TcSide tc_side(ivfhnsw_b200_t *h, size_t qb)
@@ -329,7 +329,8 @@ static int ensure_gemm_side(ivfhnsw_b200_t *h)
         TcSide S = tc_side(h, 0);
         CU(h->cent_f16.ensure(h->nc * S.dp * 4 + 64));
         S = tc_side(h, 0);
-        CU(launch_tc_prepare_centroids(h->stream, LAUNCHES, h->nc, (int)h->d, h->centroids.as<float>(), S));
+        CU(launch_tc_prepare_centroids(h->stream, LAUNCHES, h->nc, (int)h->d, h->centroids.as<float>(),
+                                       h->cnorm_gemm.as<float>(), S));
         h->f16_valid = true;
     }
     return 0;
@@ -346,7 +347,7 @@ int ivfb200_coarse_dev(ivfhnsw_b200_t *h, size_t nq, const float *xq, size_t npr
     const size_t per_q = coarse_work_bytes(1, (int)h->nc, (int)nprobe + slack, &cand_cap);
     size_t qb = std::min<size_t>(nq, std::max<size_t>(128, ((size_t)4 << 30) / per_q));
     CU(h->w_coarse.ensure(qb * per_q + 256));
-    const int impl = use_tc(h) ? 1 : 0;
+    const int impl = use_tc(h) ? (h->coarse_impl >= 2 ? 2 : 1) : 0;
     if (impl) CU(h->w_xf16.ensure(qb * ((h->d + 7) / 8 * 8) * 4 + qb * 4 + 256));
     const TcSide S = tc_side(h, qb);
     const size_t ngroups = (h->nc + COARSE_GROUP - 1) / COARSE_GROUP;

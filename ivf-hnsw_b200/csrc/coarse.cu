@@ -113,6 +113,10 @@ __global__ void __launch_bounds__(256) coarse_gemm_simt_kernel(int nq, int nc, i
 // ---------------------------------------------------------------------------------------------
 // select + verify + exact re-rank.  One CTA per query.
 // ---------------------------------------------------------------------------------------------
+static __device__ __forceinline__ float key_to_float(uint32_t k)
+{
+    return __uint_as_float((k & 0x80000000u) ? (k ^ 0x80000000u) : ~k);   // inverse of fkey
+}
 static __device__ __forceinline__ uint32_t fkey(float f)
 {
     const uint32_t b = __float_as_uint(f);
@@ -128,7 +132,9 @@ __global__ void __launch_bounds__(256) coarse_select_kernel(int nc, int d, int n
                                                             const float *__restrict__ Cn,
                                                             const float *__restrict__ grp_val,
                                                             const uint32_t *__restrict__ grp_idx,
-                                                            int packed, int self_off, uint32_t *__restrict__ err,
+                                                            int packed, int self_off,
+                                                            const uint32_t *__restrict__ cmax /* two-product GEMM: margin */,
+                                                            uint32_t *__restrict__ err,
                                                             float *__restrict__ out_d, uint32_t *__restrict__ out_i)
 {
     extern __shared__ __align__(16) uint8_t smraw[];
@@ -255,7 +261,19 @@ __global__ void __launch_bounds__(256) coarse_select_kernel(int nc, int d, int n
         __syncthreads();
         remaining_bits = shift;
     }
-    const uint32_t tau = s_prefix;       // key of the kprime-th smallest
+    uint32_t tau = s_prefix;       // key of the kprime-th smallest
+    if (cmax) {
+        // two-product GEMM: every kept value is within eps = 2 * 2^-11 ||q|| ||c|| of its three-product value, so the
+        // true top-kprime all lie below (kprime-th smallest approximate value) + 2 eps; widen the threshold by that
+        // (plus the 2^-16 relative perturbation of the packed column index, with some head room)
+        float qn = 0.f;
+        const int dk = (d >> 4) ? ((d >> 4) << 4) : d;   // coarse_dims(d)
+        for (int i = 0; i < dk; i++) qn = fmaf(sq[i], sq[i], qn);
+        const float tf = key_to_float(tau);
+        const float eps = 9.8e-4f * sqrtf(qn * __uint_as_float(cmax[1]));
+        const float wide = tf + 2.f * 1.02f * eps + fabsf(tf) * 6.2e-5f;
+        if (tf < 1.0e38f) tau = fkey(wide);
+    }
     // ---- verify groups: a group whose COARSE_T-th kept value is <= tau may hide candidates
     for (int g = tid; g < ngroups; g += 256) {
         if (fkey(gv[g * COARSE_T + COARSE_T - 1]) <= tau && (packed ? gv[g * COARSE_T + COARSE_T - 1] < 1.0e38f
@@ -339,7 +357,7 @@ size_t coarse_work_bytes(int nq, int nc, int kprime, int *cand_cap)
 }
 
 cudaError_t launch_coarse_tc(cudaStream_t st, uint64_t *launches, int nq, int nc, int d, const float *queries,
-                             const float *cnorm_gemm, const TcSide &S, float *grp_val);  // coarse_tc.cu
+                             const float *cnorm_gemm, const TcSide &S, float *grp_val, int nterms);  // coarse_tc.cu
 
 cudaError_t launch_coarse(cudaStream_t st, uint64_t *launches, int impl, int nq, int nc, int d, int nprobe,
                           int slack, const float *queries, const float *centroids, const float *cnorm_gemm,
@@ -349,8 +367,8 @@ cudaError_t launch_coarse(cudaStream_t st, uint64_t *launches, int impl, int nq,
     if (nq == 0) return cudaSuccess;
     const int ngroups = (nc + COARSE_GROUP - 1) / COARSE_GROUP;
     cudaError_t e;
-    if (impl == 1) {
-        e = launch_coarse_tc(st, launches, nq, nc, d, queries, cnorm_gemm, S, W.grp_val);
+    if (impl >= 1) {
+        e = launch_coarse_tc(st, launches, nq, nc, d, queries, cnorm_gemm, S, W.grp_val, impl == 2 ? 1 : 2);
         if (e != cudaSuccess) return e;
     } else {
         const size_t sm = (size_t)(CG_BK * CG_BM + CG_BK * CG_BN + CG_BM * (CG_BN + 1)) * sizeof(float);
@@ -368,7 +386,7 @@ cudaError_t launch_coarse(cudaStream_t st, uint64_t *launches, int impl, int nq,
         if (e != cudaSuccess) return e;
     }
     int avail = nc - (self_off >= 0 ? 1 : 0);
-    int kprime = nprobe + slack + ((impl == 1 && self_off >= 0) ? 1 : 0);   // the packed GEMM keeps the self match
+    int kprime = nprobe + slack + ((impl >= 1 && self_off >= 0) ? 1 : 0);   // the packed GEMM keeps the self match
     if (kprime > avail) kprime = avail;
     if (kprime > ngroups * COARSE_T) kprime = ngroups * COARSE_T;
     if (kprime < 1) kprime = 1;
@@ -377,12 +395,12 @@ cudaError_t launch_coarse(cudaStream_t st, uint64_t *launches, int impl, int nq,
         e = cudaFuncSetAttribute(coarse_select_kernel<8>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sm2);
         if (e != cudaSuccess) return e;
         coarse_select_kernel<8><<<nq, 256, sm2, st>>>(nc, d, ngroups, nprobe, kprime, W.cand_cap, queries, centroids,
-                                                      W.grp_val, W.grp_idx, impl == 1 ? 1 : 0, self_off, W.err, out_d, out_i);
+                                                      W.grp_val, W.grp_idx, impl >= 1 ? 1 : 0, self_off, impl == 2 ? S.cmax : nullptr, W.err, out_d, out_i);
     } else {
         e = cudaFuncSetAttribute(coarse_select_kernel<16>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sm2);
         if (e != cudaSuccess) return e;
         coarse_select_kernel<16><<<nq, 256, sm2, st>>>(nc, d, ngroups, nprobe, kprime, W.cand_cap, queries, centroids,
-                                                       W.grp_val, W.grp_idx, impl == 1 ? 1 : 0, self_off, W.err, out_d, out_i);
+                                                       W.grp_val, W.grp_idx, impl >= 1 ? 1 : 0, self_off, impl == 2 ? S.cmax : nullptr, W.err, out_d, out_i);
     }
     ++*launches;
     return cudaGetLastError();

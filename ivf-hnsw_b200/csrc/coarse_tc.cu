@@ -8,7 +8,9 @@
 //     x * s = hi + lo        (s a power of two, |x * s| < 2^14, lo = the fp16-rounded remainder)
 // and the kernel accumulates  hi.hi + lo.hi + hi.lo  in the fp32 TMEM accumulator.  The dropped
 // lo.lo term and the rounding of lo are ~2^-22 relative, i.e. fp32-class accuracy, at three
-// MMAs per (k-step) -- the epilogue, not the MMA, bounds this kernel anyway.
+// MMAs per (k-step).  nterms == 1 (the default, coarse_impl 2) leaves out hi.lo, i.e. q.c_lo: only the centroids'
+// hi blocks are streamed and the select stage widens its threshold by twice the bound 2^-10 ||q|| max||c|| of what
+// that drops (coarse.cu), so the answer is still the exact top-nprobe.
 //
 // CTA = 12 warps, persistent over work units (a tile of 128*MT queries x a range of centroid groups):
 //   warp 0      TMA producer: the query operand (hi and lo, resident per unit) and a ring of
@@ -84,13 +86,16 @@ __global__ void split_rows_kernel(size_t n, int d, int dp, const float *__restri
 }
 
 cudaError_t launch_tc_prepare_centroids(cudaStream_t st, uint64_t *launches, size_t nc, int d, const float *centroids,
-                                        const TcSide &S)
+                                        const float *cnorm_gemm, const TcSide &S)
 {
-    cudaError_t e = cudaMemsetAsync(S.cmax, 0, 4, st);
+    cudaError_t e = cudaMemsetAsync(S.cmax, 0, 8, st);
     if (e != cudaSuccess) return e;
     size_t blocks = (nc * d + 255) / 256;
     if (blocks > 148 * 8) blocks = 148 * 8;
     maxabs_kernel<<<(unsigned)blocks, 256, 0, st>>>(nc * d, centroids, S.cmax);
+    ++*launches;
+    // cmax[1] = bits of max ||c||^2: the select margin of the two-product mode
+    maxabs_kernel<<<(unsigned)((nc + 255) / 256 < 1184 ? (nc + 255) / 256 : 1184), 256, 0, st>>>(nc, cnorm_gemm, S.cmax + 1);
     ++*launches;
     split_rows_kernel<<<(unsigned)((nc + 7) / 8), 256, 0, st>>>(nc, d, S.dp, centroids, S.cmax, nullptr, S.chi, S.clo,
                                                               nullptr);
@@ -182,6 +187,7 @@ static __device__ __forceinline__ uint64_t umma_desc_sw128(uint32_t smem_addr)
 struct TcParams {
     int nq, nc, d, db;                // db = ceil(d / 64) column blocks
     int ntile_c, csplit, tiles_per_unit, nunits, nstages;
+    int nterms;                       // centroid operand terms: 2 = hi and lo (three products), 1 = hi only (two products)
     const float *cnorm;               // [nc] ||c||^2
     const float *qfac;                // [nq] -2 / (s_q * s_c)
     float *grp_val;                   // [nq][ntile_c][COARSE_T] packed (value | column index)
@@ -251,7 +257,7 @@ coarse_tc_kernel(const __grid_constant__ CUtensorMap tm_qhi, const __grid_consta
                 for (int t = t0; t < t1; t++) {
                     for (int j = 0; j < db; j++) {
 #pragma unroll
-                        for (int h = 0; h < 2; h++) {
+                        for (int h = 0; h < p.nterms; h++) {
                             mbar_wait(EMPTY(stage), phase ^ 1);
                             mbar_expect_tx(FULL(stage), TC_BLOCK_BYTES);
                             tma_load_2d(smem_u32(sB + (size_t)stage * TC_BLOCK_BYTES), h ? &tm_clo : &tm_chi, j * 64,
@@ -298,6 +304,7 @@ coarse_tc_kernel(const __grid_constant__ CUtensorMap tm_qhi, const __grid_consta
                         }
                         umma_commit(EMPTY(stage));
                         if (++stage == nst) { stage = 0; phase ^= 1; }
+                        if (p.nterms < 2) continue;   // two-product mode: q.c_lo is covered by the select margin
                         // centroid lo block: q_hi.c_lo
                         mbar_wait(FULL(stage), phase);
                         tc_fence_after();
@@ -438,7 +445,7 @@ static bool make_map(CUtensorMap *m, const void *base, size_t rows, int d, int d
 bool coarse_tc_supported(int d) { return d >= 16 && d <= 256; }
 
 cudaError_t launch_coarse_tc(cudaStream_t st, uint64_t *launches, int nq, int nc, int d, const float *queries,
-                             const float *cnorm_gemm, const TcSide &S, float *grp_val)
+                             const float *cnorm_gemm, const TcSide &S, float *grp_val, int nterms)
 {
     if (!coarse_tc_supported(d)) return cudaErrorNotSupported;
     // split the query rows (per-row power-of-two scale)
@@ -457,6 +464,7 @@ cudaError_t launch_coarse_tc(cudaStream_t st, uint64_t *launches, int nq, int nc
 
     TcParams p;
     p.nq = nq; p.nc = nc; p.d = dk; p.db = (dk + 63) / 64;
+    p.nterms = nterms;
     const int MT = p.db <= 2 ? 2 : 1;
     p.ntile_c = (nc + 127) / 128;
     const int nqt = (nq + 128 * MT - 1) / (128 * MT);

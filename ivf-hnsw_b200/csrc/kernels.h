@@ -117,16 +117,18 @@ size_t coarse_work_bytes(int nq, int nc, int kprime, int *cand_cap);
 // current query batch, row pitch dp halves (a multiple of 8)
 struct TcSide {
     __half *chi, *clo;      // [nc][dp]
-    uint32_t *cmax;         // [1] bits of max |centroid component|
+    uint32_t *cmax;         // [2] bits of max |centroid component|, bits of max ||c||^2
     __half *qhi, *qlo;      // [batch][dp]
     float *qfac;            // [batch] -2 / (query scale * centroid scale)
     int dp;
 };
 bool coarse_tc_supported(int d);
 cudaError_t launch_tc_prepare_centroids(cudaStream_t st, uint64_t *launches, size_t nc, int d, const float *centroids,
-                                        const TcSide &S);
+                                        const float *cnorm_gemm, const TcSide &S);
 // exact top-`nprobe` (ascending (dist, idx), fstdistfunc numerics) of every query among `nc` centroids.
-// impl 0: fp32 SIMT tile GEMM; impl 1: tcgen05 split-fp16 GEMM (needs the TcSide operands).
+// impl 0: fp32 SIMT tile GEMM; impl 1: tcgen05 split-fp16 GEMM, three products (needs the TcSide operands);
+// impl 2: the same with two products (q.c_hi + q_lo.c_hi): the dropped q.c_lo term is bounded by
+// 2^-11 ||q|| ||c|| and the select stage widens its threshold by twice that bound.
 cudaError_t launch_coarse(cudaStream_t st, uint64_t *launches, int impl, int nq, int nc, int d, int nprobe,
                           int slack, const float *queries, const float *centroids, const float *cnorm_gemm,
                           const TcSide &S, const CoarseWork &W, int self_off /* -1 = none */,

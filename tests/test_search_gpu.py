@@ -73,10 +73,11 @@ def test_search_splits_and_port(port, name, split):
 
 
 @pytest.mark.parametrize("name", golden_names())
-@pytest.mark.parametrize("impl", [0, 1])
+@pytest.mark.parametrize("impl", [0, 1, 2])
 def test_coarse_exact_matches_port(port, name, impl):
     """K-A2: exact nprobe nearest centroids, ascending (dist, idx), fstdistfunc numerics; impl 0 is the
-    fp32 SIMT GEMM, impl 1 the tcgen05 split-fp16 GEMM -- both feed the same exact re-rank."""
+    fp32 SIMT GEMM, impl 1 the tcgen05 split-fp16 GEMM with three products, impl 2 the same with two products and
+    a widened select threshold -- all feed the same exact re-rank."""
     pkg = load_pkg()
     g, ix, runs = load_golden(name)
     nprobe = int(g["nprobe"])
@@ -134,17 +135,18 @@ def test_coarse_tensor_core_vs_brute_force(shape, spread):
     idx = pkg.IndexIVF_HNSW(d, nc, 8, 8)
     idx.build_quantizer(centroids=C)
     res = {}
-    for impl in (0, 1):
+    for impl in (0, 1, 2):
         idx.set_option("coarse_impl", impl)
         res[impl] = idx.coarse(Q, nprobe)
     dd = ((Q.astype(np.float64)[:, None, :(d // 16) * 16] - C.astype(np.float64)[None, :, :(d // 16) * 16]) ** 2).sum(-1)
     want = np.sort(dd, axis=1)[:, :nprobe]
-    for impl in (0, 1):
+    for impl in (0, 1, 2):
         cd, ci = res[impl]
         assert np.allclose(cd, want, rtol=2e-5, atol=1e-5 * spread * spread), impl
         got = np.take_along_axis(dd, ci.astype(np.int64), 1)
         assert np.allclose(got, want, rtol=2e-5, atol=1e-5 * spread * spread), impl
     assert np.mean(res[0][1] == res[1][1]) >= 0.999
+    assert np.mean(res[0][1] == res[2][1]) >= 0.999
     idx.close()
 
 
@@ -235,8 +237,9 @@ def test_operating_point_corners(port, name, nprobe, max_codes, k):
     idx.close()
 
 
+@pytest.mark.parametrize("impl", [1, 2])
 @pytest.mark.parametrize("nprobe", [1, 40])
-def test_coarse_long_rows_vs_brute_force(nprobe):
+def test_coarse_long_rows_vs_brute_force(nprobe, impl):
     """nc large enough (> 2^17) for the select kernel's long-row path (threshold from the per-thread minima)."""
     pkg = load_pkg()
     d, nc, nq = 32, 150_000, 200
@@ -245,6 +248,7 @@ def test_coarse_long_rows_vs_brute_force(nprobe):
     Q = (C[rng.integers(0, nc, nq)] + 0.5 * rng.standard_normal((nq, d))).astype(np.float32)
     idx = pkg.IndexIVF_HNSW(d, nc, 8, 8)
     idx.build_quantizer(centroids=C)
+    idx.set_option("coarse_impl", impl)
     cd, ci = idx.coarse(Q, nprobe)
     dd = ((Q.astype(np.float64)[:, None, :] - C.astype(np.float64)[None, :, :]) ** 2).sum(-1)
     want = np.sort(dd, axis=1)[:, :nprobe]
