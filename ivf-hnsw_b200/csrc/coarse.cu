@@ -132,7 +132,7 @@ __global__ void __launch_bounds__(256) coarse_select_kernel(int nc, int d, int n
                                                             const float *__restrict__ Cn,
                                                             const float *__restrict__ grp_val,
                                                             const uint32_t *__restrict__ grp_idx,
-                                                            int packed, int self_off,
+                                                            int packed, int kept, int self_off,
                                                             const uint32_t *__restrict__ cmax /* two-product GEMM: margin */,
                                                             uint32_t *__restrict__ err,
                                                             float *__restrict__ out_d, uint32_t *__restrict__ out_i)
@@ -194,13 +194,16 @@ __global__ void __launch_bounds__(256) coarse_select_kernel(int nc, int d, int n
     // bits every key shares need no pass (and would put all 2048 atomics of a pass on one counter): the keys of
     // one row usually share sign and exponent
     {
+        // empty slots (>= 1e38: masked centroids, the unused 4th slot of the packed GEMM) take no part: they only
+        // matter when kprime exceeds the number of valid entries, and then every valid entry is selected anyway
+        const uint32_t kinv = fkey(1.0e38f);
         uint32_t vor = 0u, vand = 0xffffffffu;
         if (cached) {
 #pragma unroll
             for (int j = 0; j < SEL_CACHE; j++)
-                if (tid + 256 * j < nsel) { vor |= kc[j]; vand &= kc[j]; }
+                if (tid + 256 * j < nsel && kc[j] < kinv) { vor |= kc[j]; vand &= kc[j]; }
         } else {
-            for (int i = tid; i < n; i += 256) { const uint32_t kx = fkey(gv[i]); vor |= kx; vand &= kx; }
+            for (int i = tid; i < n; i += 256) { const uint32_t kx = fkey(gv[i]); if (kx < kinv) { vor |= kx; vand &= kx; } }
         }
         vor = __reduce_or_sync(IVF_FULL_MASK, vor);
         vand = __reduce_and_sync(IVF_FULL_MASK, vand);
@@ -276,8 +279,8 @@ __global__ void __launch_bounds__(256) coarse_select_kernel(int nc, int d, int n
     }
     // ---- verify groups: a group whose COARSE_T-th kept value is <= tau may hide candidates
     for (int g = tid; g < ngroups; g += 256) {
-        if (fkey(gv[g * COARSE_T + COARSE_T - 1]) <= tau && (packed ? gv[g * COARSE_T + COARSE_T - 1] < 1.0e38f
-                                                                     : gi[g * COARSE_T + COARSE_T - 1] != 0xffffffffu)) {
+        const int last = g * COARSE_T + kept - 1;    // the group's last kept value (the GEMM keeps 3 or 4)
+        if (fkey(gv[last]) <= tau && (packed ? gv[last] < 1.0e38f : gi[last] != 0xffffffffu)) {
             const uint32_t f = atomicAdd(&s_nflag, 1u);
             if (f < SEL_MAX_FLAGGED) s_flag[f] = (uint32_t)g;
         }
@@ -357,7 +360,7 @@ size_t coarse_work_bytes(int nq, int nc, int kprime, int *cand_cap)
 }
 
 cudaError_t launch_coarse_tc(cudaStream_t st, uint64_t *launches, int nq, int nc, int d, const float *queries,
-                             const float *cnorm_gemm, const TcSide &S, float *grp_val, int nterms);  // coarse_tc.cu
+                             const float *cnorm_gemm, const TcSide &S, float *grp_val, int nterms, int keep);  // coarse_tc.cu
 
 cudaError_t launch_coarse(cudaStream_t st, uint64_t *launches, int impl, int nq, int nc, int d, int nprobe,
                           int slack, const float *queries, const float *centroids, const float *cnorm_gemm,
@@ -366,9 +369,14 @@ cudaError_t launch_coarse(cudaStream_t st, uint64_t *launches, int impl, int nq,
 {
     if (nq == 0) return cudaSuccess;
     const int ngroups = (nc + COARSE_GROUP - 1) / COARSE_GROUP;
+    // values kept per group: the tensor-core epilogue keeps 3 instead of 4 when the groups are many (two min/max
+    // fewer per accumulator element: -18 % GEMM time at 2^20 centroids); a group whose last kept value passes the
+    // threshold is re-scanned in full by the select stage, which is rare only when the top-k spreads over many
+    // groups (expected C(k,3) / ngroups^2 per query)
+    const int kept = (impl >= 1 && ngroups >= 2048) ? 3 : COARSE_T;
     cudaError_t e;
     if (impl >= 1) {
-        e = launch_coarse_tc(st, launches, nq, nc, d, queries, cnorm_gemm, S, W.grp_val, impl == 2 ? 1 : 2);
+        e = launch_coarse_tc(st, launches, nq, nc, d, queries, cnorm_gemm, S, W.grp_val, impl == 2 ? 1 : 2, kept);
         if (e != cudaSuccess) return e;
     } else {
         const size_t sm = (size_t)(CG_BK * CG_BM + CG_BK * CG_BN + CG_BM * (CG_BN + 1)) * sizeof(float);
@@ -388,19 +396,19 @@ cudaError_t launch_coarse(cudaStream_t st, uint64_t *launches, int impl, int nq,
     int avail = nc - (self_off >= 0 ? 1 : 0);
     int kprime = nprobe + slack + ((impl >= 1 && self_off >= 0) ? 1 : 0);   // the packed GEMM keeps the self match
     if (kprime > avail) kprime = avail;
-    if (kprime > ngroups * COARSE_T) kprime = ngroups * COARSE_T;
+    if (kprime > ngroups * kept) kprime = ngroups * kept;
     if (kprime < 1) kprime = 1;
     const size_t sm2 = (size_t)d * 4 + (size_t)W.cand_cap * 8;
     if (ngroups * COARSE_T <= 256 * 8) {
         e = cudaFuncSetAttribute(coarse_select_kernel<8>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sm2);
         if (e != cudaSuccess) return e;
         coarse_select_kernel<8><<<nq, 256, sm2, st>>>(nc, d, ngroups, nprobe, kprime, W.cand_cap, queries, centroids,
-                                                      W.grp_val, W.grp_idx, impl >= 1 ? 1 : 0, self_off, impl == 2 ? S.cmax : nullptr, W.err, out_d, out_i);
+                                                      W.grp_val, W.grp_idx, impl >= 1 ? 1 : 0, kept, self_off, impl == 2 ? S.cmax : nullptr, W.err, out_d, out_i);
     } else {
         e = cudaFuncSetAttribute(coarse_select_kernel<16>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sm2);
         if (e != cudaSuccess) return e;
         coarse_select_kernel<16><<<nq, 256, sm2, st>>>(nc, d, ngroups, nprobe, kprime, W.cand_cap, queries, centroids,
-                                                       W.grp_val, W.grp_idx, impl >= 1 ? 1 : 0, self_off, impl == 2 ? S.cmax : nullptr, W.err, out_d, out_i);
+                                                       W.grp_val, W.grp_idx, impl >= 1 ? 1 : 0, kept, self_off, impl == 2 ? S.cmax : nullptr, W.err, out_d, out_i);
     }
     ++*launches;
     return cudaGetLastError();

@@ -194,7 +194,8 @@ struct TcParams {
     uint32_t keep_mask;               // ~127, passed at run time so that packing is ONE lop3 (reg & reg | imm)
 };
 
-template <int MT>
+// KEEP: values kept per (query, group of 128 centroids): 4, or 3 when the groups are many (see launch_coarse)
+template <int MT, int KEEP>
 __global__ void __launch_bounds__(TC_THREADS, 1)
 coarse_tc_kernel(const __grid_constant__ CUtensorMap tm_qhi, const __grid_constant__ CUtensorMap tm_qlo,
                  const __grid_constant__ CUtensorMap tm_chi, const __grid_constant__ CUtensorMap tm_clo, TcParams p)
@@ -357,7 +358,7 @@ coarse_tc_kernel(const __grid_constant__ CUtensorMap tm_qhi, const __grid_consta
                 mbar_wait(T_FULL(as), t_phase);
                 tc_fence_after();
                 const uint32_t taddr = tmem_base + ((uint32_t)(quarter * 32) << 16) + (uint32_t)(as * MT * 128 + mt * 128);
-                float a0 = TC_INVALID, a1 = TC_INVALID, a2 = TC_INVALID, a3 = TC_INVALID;
+                float a0 = TC_INVALID, a1 = TC_INVALID, a2 = TC_INVALID, a3 = TC_INVALID;   // KEEP == 3: the 4th slot stays empty
                 uint32_t v[2][32];
                 tmem_ld32(taddr, v[0]);
 #pragma unroll
@@ -383,13 +384,17 @@ coarse_tc_kernel(const __grid_constant__ CUtensorMap tm_qhi, const __grid_consta
 #endif
                             const float val = fmaf(__uint_as_float(v[jb & 1][i]), f, cnv[ii]);
                             const float x = __uint_as_float((__float_as_uint(val) & p.keep_mask) | (uint32_t)(jb * 32 + i));
+                            // sorted insert into the KEEP best of the group: 7 or 5 min/max (with two products per
+                            // k-step the epilogue's ALU pipe, not the MMA side, bounds the kernel)
                             const float m0 = fmaxf(a0, x);
                             a0 = fminf(a0, x);
                             const float m1 = fmaxf(a1, m0);
                             a1 = fminf(a1, m0);
-                            const float m2 = fmaxf(a2, m1);
-                            a2 = fminf(a2, m1);
-                            a3 = fminf(a3, m2);
+                            if (KEEP == 4) {
+                                const float m2 = fmaxf(a2, m1);
+                                a2 = fminf(a2, m1);
+                                a3 = fminf(a3, m2);
+                            } else a2 = fminf(a2, m1);
                         }
                     }
                 }
@@ -445,7 +450,7 @@ static bool make_map(CUtensorMap *m, const void *base, size_t rows, int d, int d
 bool coarse_tc_supported(int d) { return d >= 16 && d <= 256; }
 
 cudaError_t launch_coarse_tc(cudaStream_t st, uint64_t *launches, int nq, int nc, int d, const float *queries,
-                             const float *cnorm_gemm, const TcSide &S, float *grp_val, int nterms)
+                             const float *cnorm_gemm, const TcSide &S, float *grp_val, int nterms, int keep)
 {
     if (!coarse_tc_supported(d)) return cudaErrorNotSupported;
     // split the query rows (per-row power-of-two scale)
@@ -492,15 +497,15 @@ cudaError_t launch_coarse_tc(cudaStream_t st, uint64_t *launches, int nq, int nc
     p.cnorm = cnorm_gemm; p.qfac = S.qfac; p.grp_val = grp_val; p.keep_mask = ~127u;
     const size_t smem = fixed + a_bytes + (size_t)nst * TC_BLOCK_BYTES;
     const int grid = p.nunits < 148 ? p.nunits : 148;
-    if (MT == 2) {
-        e = cudaFuncSetAttribute(coarse_tc_kernel<2>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
-        if (e != cudaSuccess) return e;
-        coarse_tc_kernel<2><<<grid, TC_THREADS, smem, st>>>(m_qhi, m_qlo, m_chi, m_clo, p);
-    } else {
-        e = cudaFuncSetAttribute(coarse_tc_kernel<1>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
-        if (e != cudaSuccess) return e;
-        coarse_tc_kernel<1><<<grid, TC_THREADS, smem, st>>>(m_qhi, m_qlo, m_chi, m_clo, p);
-    }
+#define IVF_TC_LAUNCH(MTV, KV)                                                                                     \
+    do {                                                                                                           \
+        e = cudaFuncSetAttribute(coarse_tc_kernel<MTV, KV>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem); \
+        if (e != cudaSuccess) return e;                                                                            \
+        coarse_tc_kernel<MTV, KV><<<grid, TC_THREADS, smem, st>>>(m_qhi, m_qlo, m_chi, m_clo, p);                  \
+    } while (0)
+    if (MT == 2) { if (keep == 3) IVF_TC_LAUNCH(2, 3); else IVF_TC_LAUNCH(2, 4); }
+    else { if (keep == 3) IVF_TC_LAUNCH(1, 3); else IVF_TC_LAUNCH(1, 4); }
+#undef IVF_TC_LAUNCH
     ++*launches;
     return cudaGetLastError();
 }
