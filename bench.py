@@ -605,7 +605,11 @@ def main():
                              "algorithmic": "2*nc*d FLOP per query (the fp16 hi/lo split issues 3x that)",
                              "traffic": traffic.get("coarse_tc_kernel") if world == 1 else None},
     }
-    dom = max(rl.values(), key=lambda r: r["ms"])
+    # headline roofline: the larger (by live-measured time) of the two kernels whose roof is one of the two bound types
+    # of the contract -- the ADC scan (HBM) and the coarse GEMM (tensor).  K-G1b stays under "others": its rows are L2
+    # hits whenever the centroid table fits L2, so its GB/s is not an HBM fraction (it can exceed the HBM peak).
+    dom = max((rl["scan_kernel"], rl["coarse_tc_kernel"]), key=lambda r: r["ms"])
+    rl["group_g1b_kernel"]["note"] = "rows are L2 hits when the centroid table fits L2: not an HBM fraction"
     roofline = dict(dom)
     roofline["peak_source"] = peak_src
     roofline["others"] = {kk: vv for kk, vv in rl.items() if vv is not dom}
