@@ -103,16 +103,8 @@ def build_index(w, torch, dev, log, dist=None):
     idx = cls(*args, device=dev.index or 0)
     # coarse centroids: Lloyd iterations driven by K-A1 itself (k-means is not on the path; any file works)
     learn = draw(w, torch, dev, means, w["nlearn"], 1234 + 2)
-    cent = learn[torch.randperm(w["nlearn"], device=dev, generator=torch.Generator(device=dev).manual_seed(7))[:w["nc"]]].clone()
-    lab = torch.empty(w["nlearn"], dtype=torch.int32, device=dev)
-    dist_tmp = torch.empty(w["nlearn"], dtype=torch.float32, device=dev)
-    for it in range(w["lloyd"]):
-        idx.build_quantizer(centroids=cent.cpu().numpy())
-        idx.coarse_dev(learn, 1, dist_tmp, lab)
-        idx.sync()
-        sums = torch.zeros_like(cent).index_add_(0, lab.long(), learn)
-        cnt = torch.zeros(w["nc"], device=dev).index_add_(0, lab.long(), torch.ones(w["nlearn"], device=dev))
-        cent = torch.where(cnt[:, None] > 0, sums / cnt.clamp(min=1)[:, None], cent)
+    kmeans = importlib.import_module("ivf-hnsw_b200.kmeans")
+    cent = kmeans.lloyd_centroids(idx, learn, w["nc"], iters=w["lloyd"], seed=7)
     if dist is not None:
         # every rank must hold the SAME index (in production they load one file): the Lloyd sums use float
         # atomics, so take rank 0's centroids
@@ -135,7 +127,7 @@ def build_index(w, torch, dev, log, dist=None):
             opq = opq.cpu().numpy()
         idx.set_pq(pqc.cpu().numpy(), nrm.cpu().numpy(), opq)
     log("train_pq %.1fs" % (time.time() - t0))
-    del learn, lab, dist_tmp
+    del learn
     # base vectors: generated, assigned (K-A1) and added in 1M batches (tests/...:102,142-153)
     bs = 1_000_000
     queries = draw(w, torch, dev, means, w["nq"], 1234 + 1)
