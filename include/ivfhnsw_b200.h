@@ -141,6 +141,19 @@ int ivfhnsw_b200_search_given_coarse_dev(ivfhnsw_b200_t *h, size_t nq, size_t k,
                                          float *distances_dev, int64_t *labels_dev);
 int ivfhnsw_b200_coarse_dev(ivfhnsw_b200_t *h, size_t nq, const float *x_dev, size_t nprobe,
                             float *dists_dev, uint32_t *idxs_dev);
+/* NO COUNTERPART IN THE REFERENCE: added for callers that cannot call
+ * cudaMalloc (code under CUDA-graph capture, tight serving loops, harnesses that forbid it).  The exact coarse
+ * search of ivfhnsw_b200_coarse_dev (fp32 GEMM + select + fstdistfunc re-rank; same (dist, idx) order and values),
+ * with the GEMM's intermediates in ONE file-scope device array of IVFHNSW_B200_NOALLOC_SCRATCH_BYTES that every
+ * GPU loading the library holds until exit: the call allocates nothing (no cudaMalloc/cudaFree, no allocating
+ * library routine) and only enqueues on the handle's stream.  xq_dev [nq][d] are queries in the space of the
+ * centroid table (already rotated when OPQ is used: no rotation is applied here).  Limit: nq * ceil(nc/128) * 32
+ * + nc * 4 + 768 <= IVFHNSW_B200_NOALLOC_SCRATCH_BYTES, else EINVAL (e.g. 512 queries at nc = 65536).
+ * flags_dev (may be NULL) receives the select stage's overflow flags, 0 = the result is exact.  All calls on a
+ * device share the array: calls that overlap on the GPU (other streams, other handles) race; serialise them. */
+#define IVFHNSW_B200_NOALLOC_SCRATCH_BYTES (8u << 20)
+int ivfhnsw_b200_coarse_noalloc_dev(ivfhnsw_b200_t *h, size_t nq, const float *xq_dev, size_t nprobe,
+                                    float *dists_dev, uint32_t *idxs_dev, uint32_t *flags_dev);
 /* sharded search: this handle scans only the lists it owns (set_shard) and returns its
  * sorted partial top-k together with the global scan-order key of every hit; coarse candidates NULL =
  * computed here over the (replicated) centroid table, identical on every rank */

@@ -92,6 +92,7 @@ def lib():
         "ivfhnsw_b200_search_dev": ([H, sz, sz, vp, vp, vp], C.c_int),
         "ivfhnsw_b200_search_given_coarse_dev": ([H, sz, sz, vp, vp, vp, vp, vp], C.c_int),
         "ivfhnsw_b200_coarse_dev": ([H, sz, vp, sz, vp, vp], C.c_int),
+        "ivfhnsw_b200_coarse_noalloc_dev": ([H, sz, vp, sz, vp, vp, vp], C.c_int),
         "ivfhnsw_b200_search_partial_dev": ([H, sz, sz, vp, vp, vp, vp, vp, vp], C.c_int),
         "ivfhnsw_b200_merge_partials_dev": ([H, sz, sz, sz, vp, vp, vp, vp, vp], C.c_int),
         "ivfhnsw_b200_tables_bytes": ([H, C.POINTER(C.c_size_t)], C.c_int),
@@ -507,6 +508,13 @@ class IndexIVF_HNSW:
         with self._ordered():
             self._ck(self._L.ivfhnsw_b200_coarse_dev(self._h, x_dev.shape[0], _ptr(x_dev), nprobe, _ptr(d_dev),
                                                      _ptr(i_dev)))
+
+    def coarse_noalloc_dev(self, xq_dev, nprobe, d_dev, i_dev, flags_dev=None):
+        """ivfhnsw_b200_coarse_noalloc_dev: the exact coarse search with its scratch in the library's static device
+        array (allocates nothing; queries already in the centroid table's space; see include/ivfhnsw_b200.h)."""
+        with self._ordered():
+            self._ck(self._L.ivfhnsw_b200_coarse_noalloc_dev(self._h, xq_dev.shape[0], _ptr(xq_dev), nprobe,
+                                                             _ptr(d_dev), _ptr(i_dev), _ptr(flags_dev)))
 
     def search_host_buffers(self, k, x_host, D_host, L_host):
         """The C-ABI call with caller-owned HOST buffers (numpy or pinned torch): H2D + search + D2H."""
