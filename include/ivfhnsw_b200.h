@@ -93,14 +93,24 @@ int ivfhnsw_b200_assign_u8(ivfhnsw_b200_t *h, size_t n, const uint8_t *x, uint32
 /* IndexIVF_HNSW::add_batch (IndexIVF_HNSW.cpp:75-138); precomputed_idx may be NULL (assign first) */
 int ivfhnsw_b200_add_batch(ivfhnsw_b200_t *h, size_t n, const float *x, const uint32_t *xids,
                            const uint32_t *precomputed_idx);
-/* IndexIVF_HNSW_Grouping::add_group (IndexIVF_HNSW_Grouping.cpp:43-157); thread-safe per distinct group:
- * vectors are staged and encoded at finalize() */
+/* IndexIVF_HNSW_Grouping::add_group (IndexIVF_HNSW_Grouping.cpp:43-157); thread-safe per distinct group.
+ * STREAMED like the reference's bounded pass (tests/test_ivfhnsw_grouping_sift1b.cpp:138-201): one call delivers a
+ * complete group, the raw vectors are staged in HBM and -- as soon as "stage_bytes" of them wait (set_option,
+ * default 4 GiB) -- alpha, sub-groups and codes of the staged groups are computed and the raw vectors dropped;
+ * finalize() handles the remainder.  A group may therefore be added ONCE (a second add_group of an already
+ * encoded group fails with ESTATE), which is also the reference's contract. */
 int ivfhnsw_b200_add_group(ivfhnsw_b200_t *h, size_t group_idx, size_t group_size, const float *x,
                            const uint32_t *ids);
-/* device-resident bulk variant used by the ingest path: x_dev [n][d] f32, ids_dev [n], group_dev [n]
- * (any order; the per-group order of appearance is kept) */
+/* device-resident bulk variant used by the ingest path: x_dev [n][d] f32, ids_dev [n], idx_dev [n] list of every
+ * point or NULL (= assigned here, K-A1); any order, the per-list order of appearance is kept.  IVFADC: encoded at
+ * once.  Grouping: the raw vectors are staged until ivfhnsw_b200_flush_groups()/finalize() -- the caller delivers
+ * the points of a RANGE of groups (any number of calls), then flushes: that is the reference's groups_per_iter pass. */
 int ivfhnsw_b200_add_points_dev(ivfhnsw_b200_t *h, size_t n, const float *x_dev, const uint32_t *ids_dev,
                                 const uint32_t *idx_dev);
+/* Grouping only: every group that has staged raw points is COMPLETE -- compute its alpha (compute_alpha, :691-728),
+ * sub-group ids (:673-689) and residual codes (:101-131) now and release the raw vectors.  Peak HBM of an ingest is
+ * bounded by the largest flush, not by the base set (1B x 128: 21 GB of records instead of 512 GB of vectors). */
+int ivfhnsw_b200_flush_groups(ivfhnsw_b200_t *h);
 /* flush point: builds the device CSR lists (stable by list [, sub-group]) from everything added so far.
  * For Grouping also computes nn_centroid_idxs / alphas / sub-groups (add_group body) and
  * compute_inter_centroid_dists (IndexIVF_HNSW_Grouping.cpp:620-631). */
@@ -208,7 +218,8 @@ int ivfhnsw_b200_reset_stats(ivfhnsw_b200_t *h);
  * query (IndexIVF_HNSW_Grouping.cpp:261) and codes scanned per query */
 int ivfhnsw_b200_last_thresholds(ivfhnsw_b200_t *h, size_t cap, float *thresholds, uint32_t *scanned);
 /* tuning knobs: "coarse_slack", "coarse_impl" (0 = SIMT fp32, 1 = tcgen05 split-fp16 three products, 2 = two products
- * with a widened select threshold, the default), "scan_split" (0 = auto) */
+ * with a widened select threshold, the default), "scan_split" (0 = auto), "stage_bytes" (raw Grouping vectors staged
+ * before add_group encodes them) */
 int ivfhnsw_b200_set_option(ivfhnsw_b200_t *h, const char *name, long value);
 
 #ifdef __cplusplus

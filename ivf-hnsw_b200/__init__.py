@@ -83,6 +83,7 @@ def lib():
         "ivfhnsw_b200_add_group": ([H, sz, sz, vp, vp], C.c_int),
         "ivfhnsw_b200_add_points_dev": ([H, sz, vp, vp, vp], C.c_int),
         "ivfhnsw_b200_finalize": ([H], C.c_int),
+        "ivfhnsw_b200_flush_groups": ([H], C.c_int),
         "ivfhnsw_b200_load_lists": ([H, vp, vp, vp, vp, vp, vp, vp, vp], C.c_int),
         "ivfhnsw_b200_ntotal": ([H, C.POINTER(sz)], C.c_int),
         "ivfhnsw_b200_export_lists": ([H, vp, vp, vp, vp, vp, vp, vp, vp], C.c_int),
@@ -337,6 +338,11 @@ class IndexIVF_HNSW:
         with self._ordered():
             self._ck(self._L.ivfhnsw_b200_add_points_dev(self._h, x_dev.shape[0], _ptr(x_dev), _ptr(ids_dev),
                                                          _ptr(idx_dev)))
+
+    def flush_groups(self):
+        """Grouping: the groups staged so far are complete -- encode them and drop their raw vectors."""
+        self._push_params()
+        self._ck(self._L.ivfhnsw_b200_flush_groups(self._h))
 
     def finalize(self):
         self._push_params()

@@ -79,6 +79,27 @@ __global__ void reduce_u32_kernel(int n, const uint32_t *a, const uint32_t *b, u
     if ((threadIdx.x & 31) == 0) { atomicAdd(&out[0], sa); atomicAdd(&out[1], sb); }
 }
 
+__global__ void fill_u32_kernel(size_t n, uint32_t v, uint32_t *out)
+{
+    for (size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (size_t)gridDim.x * blockDim.x) out[i] = v;
+}
+// a group may be encoded once: seen[g] accumulates the points of earlier flushes; flag = first offending group + 1
+__global__ void group_seen_kernel(int nc, const uint32_t *gsize, uint32_t *seen, uint32_t *flag)
+{
+    const int g = blockIdx.x * blockDim.x + threadIdx.x;
+    if (g >= nc || gsize[g] == 0) return;
+    if (seen[g]) atomicMax(flag, (uint32_t)g + 1u);
+    seen[g] += gsize[g];
+}
+// out[0] = max(out[0], max_i key[i])
+__global__ void max_u32_kernel(size_t n, const uint32_t *key, uint32_t *out)
+{
+    uint32_t m = 0;
+    for (size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (size_t)gridDim.x * blockDim.x) m = max(m, key[i]);
+    m = __reduce_max_sync(0xffffffffu, m);
+    if ((threadIdx.x & 31) == 0) atomicMax(out, m);
+}
+
 unsigned grid_for(size_t n, int per = 256, unsigned cap = 148 * 16)
 {
     size_t b = (n + per - 1) / per;
@@ -91,6 +112,43 @@ unsigned grid_for(size_t n, int per = 256, unsigned cap = 148 * 16)
 static int bind(ivfhnsw_b200_t *h)
 {
     CU(cudaSetDevice(h->device));
+    return 0;
+}
+
+// The coarse select stage records overflows (more flagged groups / candidates than its tables hold) in a sticky
+// device word instead of returning an incomplete probe list silently.  Every entry point that ends in a stream
+// synchronisation reads the word back (4 bytes) and fails loudly; the asynchronous *_dev entry points are covered by
+// the next ivfhnsw_b200_sync() / host-pointer call on the handle.  Synchronises the stream.
+static int check_coarse_flags(ivfhnsw_b200_t *h)
+{
+    unsigned long long w = 0;
+    CU(cudaMemcpyAsync(&w, h->counters.as<unsigned long long>() + 4, 8, cudaMemcpyDeviceToHost, h->stream));
+    CU(cudaStreamSynchronize(h->stream));
+    if (w & 0xffffffffull) {
+        CU(cudaMemsetAsync(h->counters.as<unsigned long long>() + 4, 0, 8, h->stream));
+        CU(cudaStreamSynchronize(h->stream));
+        return h->fail(IVFHNSW_B200_ECUDA,
+                       "coarse select overflow (flags 0x%llx: 1 = too many 128-centroid groups had to be expanded, 2 = too many "
+                       "candidates tie at the threshold, 4 = fewer candidates than nprobe): the probe lists of this call are "
+                       "incomplete.  nprobe is too large for nc (keep nprobe + coarse_slack below ~nc/128) or the centroid "
+                       "table has many duplicates", w & 0xffffffffull);
+    }
+    return 0;
+}
+
+// list ids handed in by the caller (precomputed_idx files, add_group) must address an existing list
+static int check_list_ids_dev(ivfhnsw_b200_t *h, size_t n, const uint32_t *idx_dev, const char *what)
+{
+    if (n == 0) return 0;
+    CU(h->w_small.ensure(64));
+    CU(cudaMemsetAsync(h->w_small.p, 0, 4, h->stream));
+    max_u32_kernel<<<grid_for(n), 256, 0, h->stream>>>(n, idx_dev, h->w_small.as<uint32_t>());
+    ++h->stats.kernel_launches;
+    uint32_t m = 0;
+    CU(cudaMemcpyAsync(&m, h->w_small.p, 4, cudaMemcpyDeviceToHost, h->stream));
+    CU(cudaStreamSynchronize(h->stream));
+    if (m >= h->nc)
+        return h->fail(IVFHNSW_B200_EINVAL, "%s: list id %u out of range (ncentroids = %zu): stale precomputed_idxs file?", what, m, h->nc);
     return 0;
 }
 
@@ -151,7 +209,7 @@ void ivfhnsw_b200_destroy(ivfhnsw_b200_t *h)
     DevBuf *bufs[] = {&h->centroids, &h->centroid_norms, &h->cnorm_gemm, &h->cent_f16, &h->pqc, &h->norm_table,
                       &h->opqA, &h->list_size, &h->list_slot, &h->raw_off, &h->codes, &h->norm_codes, &h->sub_ids,
                       &h->ids, &h->nn_idx, &h->sub_sizes, &h->alphas, &h->icd, &h->st_list, &h->st_ids, &h->st_codes,
-                      &h->st_norm, &h->st_sub, &h->st_x, &h->w_x, &h->w_xrot, &h->w_cd, &h->w_ci, &h->w_seg,
+                      &h->st_norm, &h->st_sub, &h->st_x, &h->rs_list, &h->rs_ids, &h->grp_seen, &h->w_x, &h->w_xrot, &h->w_cd, &h->w_ci, &h->w_seg,
                       &h->w_sub_base, &h->w_qsd, &h->w_g1, &h->w_part, &h->w_lut, &h->w_coarse, &h->w_xf16, &h->w_out_d, &h->w_out_l,
                       &h->w_a, &h->w_b, &h->w_c, &h->w_d2, &h->w_e, &h->w_f, &h->w_cub, &h->w_small, &h->counters};
     for (DevBuf *b : bufs) b->release();
@@ -228,6 +286,7 @@ int ivfhnsw_b200_set_option(ivfhnsw_b200_t *h, const char *name, long v)
     else if (!strcmp(name, "scan_split")) h->scan_split = v;
     else if (!strcmp(name, "query_batch")) h->query_batch = v;
     else if (!strcmp(name, "debug")) h->debug = v;
+    else if (!strcmp(name, "stage_bytes")) h->stage_bytes = v > 0 ? v : 1;
     else return h->fail(IVFHNSW_B200_EINVAL, "unknown option %s", name);
     return 0;
 }
@@ -249,8 +308,7 @@ int ivfhnsw_b200_set_stream(ivfhnsw_b200_t *h, void *stream)
 int ivfhnsw_b200_sync(ivfhnsw_b200_t *h)
 {
     if (bind(h)) return IVFHNSW_B200_ECUDA;
-    CU(cudaStreamSynchronize(h->stream));
-    return 0;
+    return check_coarse_flags(h);   // synchronises the stream
 }
 
 int ivfhnsw_b200_compute_centroid_norms(ivfhnsw_b200_t *h)
@@ -404,8 +462,7 @@ int ivfhnsw_b200_coarse(ivfhnsw_b200_t *h, size_t nq, const float *x, size_t npr
         return r;
     CU(cudaMemcpyAsync(dists, h->w_cd.p, nq * nprobe * 4, cudaMemcpyDeviceToHost, h->stream));
     CU(cudaMemcpyAsync(idxs, h->w_ci.p, nq * nprobe * 4, cudaMemcpyDeviceToHost, h->stream));
-    CU(cudaStreamSynchronize(h->stream));
-    return 0;
+    return check_coarse_flags(h);
 }
 
 // assign for device-resident vectors (k = 1): labels_dev[n]
@@ -427,7 +484,7 @@ int ivfhnsw_b200_assign(ivfhnsw_b200_t *h, size_t n, const float *x, uint32_t *l
         CU(cudaMemcpyAsync(h->w_x.p, x + i0 * h->d, nb * h->d * 4, cudaMemcpyHostToDevice, h->stream));
         if (int r = ivfb200_assign_dev(h, nb, h->w_x.as<float>(), h->w_ci.as<uint32_t>())) return r;
         CU(cudaMemcpyAsync(labels + i0, h->w_ci.p, nb * 4, cudaMemcpyDeviceToHost, h->stream));
-        CU(cudaStreamSynchronize(h->stream));
+        if (int r = check_coarse_flags(h)) return r;
     }
     return 0;
 }
@@ -445,7 +502,7 @@ int ivfhnsw_b200_assign_u8(ivfhnsw_b200_t *h, size_t n, const uint8_t *x, uint32
         CU(launch_u8_to_f32(h->stream, LAUNCHES, nb * h->d, h->w_b.as<uint8_t>(), h->w_x.as<float>()));
         if (int r = ivfb200_assign_dev(h, nb, h->w_x.as<float>(), h->w_ci.as<uint32_t>())) return r;
         CU(cudaMemcpyAsync(labels + i0, h->w_ci.p, nb * 4, cudaMemcpyDeviceToHost, h->stream));
-        CU(cudaStreamSynchronize(h->stream));
+        if (int r = check_coarse_flags(h)) return r;
     }
     return 0;
 }
@@ -498,20 +555,28 @@ int ivfb200_encode_dev(ivfhnsw_b200_t *h, size_t n, const float *x_dev, const ui
     return 0;
 }
 
-static int stage_reserve(ivfhnsw_b200_t *h, size_t extra, bool points)
+// encoded records (st_*): list, id, code, norm code [, sub-group]
+static int stage_reserve(ivfhnsw_b200_t *h, size_t extra)
 {
     const size_t n = h->st_n + extra;
     CU(h->st_list.grow(n * 4, h->st_n * 4, h->stream));
     CU(h->st_ids.grow(n * 4, h->st_n * 4, h->stream));
-    if (points) {
-        CU(h->st_x.grow(n * h->d * 4, h->st_n * h->d * 4, h->stream));
-    } else {
-        CU(h->st_codes.grow(n * h->M, h->st_n * h->M, h->stream));
-        CU(h->st_norm.grow(n, h->st_n, h->stream));
-        if (h->nsubc) CU(h->st_sub.grow(n, h->st_n, h->stream));
-    }
+    CU(h->st_codes.grow(n * h->M, h->st_n * h->M, h->stream));
+    CU(h->st_norm.grow(n, h->st_n, h->stream));
+    if (h->nsubc) CU(h->st_sub.grow(n, h->st_n, h->stream));
     return 0;
 }
+// raw points of a Grouping index waiting for their group to be complete (rs_*): list, id, vector
+static int raw_reserve(ivfhnsw_b200_t *h, size_t extra)
+{
+    const size_t n = h->rs_n + extra;
+    CU(h->rs_list.grow(n * 4, h->rs_n * 4, h->stream));
+    CU(h->rs_ids.grow(n * 4, h->rs_n * 4, h->stream));
+    CU(h->st_x.grow(n * h->d * 4, h->rs_n * h->d * 4, h->stream));
+    return 0;
+}
+
+static int flush_groups_locked(ivfhnsw_b200_t *h);
 
 static int unstage_existing_lists(ivfhnsw_b200_t *h);
 
@@ -523,7 +588,7 @@ int ivfhnsw_b200_add_batch(ivfhnsw_b200_t *h, size_t n, const float *x, const ui
     if (!h->have_centroids) return h->fail(IVFHNSW_B200_ESTATE, "centroids not set");
     if (n == 0) return 0;
     if (h->have_lists && !h->st_dirty) { if (int r = unstage_existing_lists(h)) return r; }
-    if (int r = stage_reserve(h, n, false)) return r;
+    if (int r = stage_reserve(h, n)) return r;
     const size_t chunk = 1 << 18;
     CU(h->w_x.ensure(std::min(n, chunk) * h->d * 4));
     for (size_t i0 = 0; i0 < n; i0 += chunk) {
@@ -531,8 +596,13 @@ int ivfhnsw_b200_add_batch(ivfhnsw_b200_t *h, size_t n, const float *x, const ui
         uint32_t *dl = h->st_list.as<uint32_t>() + h->st_n;
         CU(cudaMemcpyAsync(h->w_x.p, x + i0 * h->d, nb * h->d * 4, cudaMemcpyHostToDevice, h->stream));
         CU(cudaMemcpyAsync(h->st_ids.as<uint32_t>() + h->st_n, xids + i0, nb * 4, cudaMemcpyHostToDevice, h->stream));
-        if (idx) CU(cudaMemcpyAsync(dl, idx + i0, nb * 4, cudaMemcpyHostToDevice, h->stream));
-        else if (int r = ivfb200_assign_dev(h, nb, h->w_x.as<float>(), dl)) return r;
+        if (idx) {
+            CU(cudaMemcpyAsync(dl, idx + i0, nb * 4, cudaMemcpyHostToDevice, h->stream));
+            if (int r = check_list_ids_dev(h, nb, dl, "add_batch")) return r;
+        } else {
+            if (int r = ivfb200_assign_dev(h, nb, h->w_x.as<float>(), dl)) return r;
+            if (int r = check_coarse_flags(h)) return r;
+        }
         if (int r = ivfb200_encode_dev(h, nb, h->w_x.as<float>(), dl, nullptr, nullptr, h->st_codes.as<uint8_t>() + h->st_n * h->M,
                                h->st_norm.as<uint8_t>() + h->st_n, nullptr, nullptr))
             return r;
@@ -554,20 +624,27 @@ int ivfhnsw_b200_add_points_dev(ivfhnsw_b200_t *h, size_t n, const float *x_dev,
         if (int r = unstage_existing_lists(h)) return r;
     }
     const bool points = h->nsubc != 0;
-    if (int r = stage_reserve(h, n, points)) return r;
-    uint32_t *dl = h->st_list.as<uint32_t>() + h->st_n;
-    if (idx_dev) CU(cudaMemcpyAsync(dl, idx_dev, n * 4, cudaMemcpyDeviceToDevice, h->stream));
-    else if (int r = ivfb200_assign_dev(h, n, x_dev, dl)) return r;
-    CU(cudaMemcpyAsync(h->st_ids.as<uint32_t>() + h->st_n, ids_dev, n * 4, cudaMemcpyDeviceToDevice, h->stream));
+    if (points) { if (int r = raw_reserve(h, n)) return r; }
+    else if (int r = stage_reserve(h, n)) return r;
+    uint32_t *dl = points ? h->rs_list.as<uint32_t>() + h->rs_n : h->st_list.as<uint32_t>() + h->st_n;
+    uint32_t *di = points ? h->rs_ids.as<uint32_t>() + h->rs_n : h->st_ids.as<uint32_t>() + h->st_n;
+    if (idx_dev) {
+        CU(cudaMemcpyAsync(dl, idx_dev, n * 4, cudaMemcpyDeviceToDevice, h->stream));
+        if (int r = check_list_ids_dev(h, n, dl, "add_points_dev")) return r;
+    } else {
+        if (int r = ivfb200_assign_dev(h, n, x_dev, dl)) return r;
+        if (int r = check_coarse_flags(h)) return r;
+    }
+    CU(cudaMemcpyAsync(di, ids_dev, n * 4, cudaMemcpyDeviceToDevice, h->stream));
     if (points) {
-        CU(cudaMemcpyAsync(h->st_x.as<float>() + h->st_n * h->d, x_dev, n * h->d * 4, cudaMemcpyDeviceToDevice, h->stream));
+        CU(cudaMemcpyAsync(h->st_x.as<float>() + h->rs_n * h->d, x_dev, n * h->d * 4, cudaMemcpyDeviceToDevice, h->stream));
+        h->rs_n += n;
     } else {
         if (int r = ivfb200_encode_dev(h, n, x_dev, dl, nullptr, nullptr, h->st_codes.as<uint8_t>() + h->st_n * h->M,
                                h->st_norm.as<uint8_t>() + h->st_n, nullptr, nullptr))
             return r;
+        h->st_n += n;
     }
-    CU(cudaStreamSynchronize(h->stream));
-    h->st_n += n;
     h->st_dirty = true;
     return 0;
 }
@@ -582,14 +659,33 @@ int ivfhnsw_b200_add_group(ivfhnsw_b200_t *h, size_t g, size_t n, const float *x
         return h->fail(IVFHNSW_B200_ESTATE, "Grouping index already finalized: incremental add_group unsupported");
     h->st_dirty = true;  // even empty groups mark the index as "being built" (nn lists are computed at finalize)
     if (n == 0) return 0;
-    if (int r = stage_reserve(h, n, true)) return r;
-    std::vector<uint32_t> gl(n, (uint32_t)g);
-    CU(cudaMemcpyAsync(h->st_list.as<uint32_t>() + h->st_n, gl.data(), n * 4, cudaMemcpyHostToDevice, h->stream));
-    CU(cudaMemcpyAsync(h->st_ids.as<uint32_t>() + h->st_n, ids, n * 4, cudaMemcpyHostToDevice, h->stream));
-    CU(cudaMemcpyAsync(h->st_x.as<float>() + h->st_n * h->d, x, n * h->d * 4, cudaMemcpyHostToDevice, h->stream));
-    CU(cudaStreamSynchronize(h->stream));
-    h->st_n += n;
+    if (int r = raw_reserve(h, n)) return r;
+    fill_u32_kernel<<<grid_for(n), 256, 0, h->stream>>>(n, (uint32_t)g, h->rs_list.as<uint32_t>() + h->rs_n);
+    ++h->stats.kernel_launches;
+    // pageable host copies return once the source has been staged: the caller may free x / ids right after
+    CU(cudaMemcpyAsync(h->rs_ids.as<uint32_t>() + h->rs_n, ids, n * 4, cudaMemcpyHostToDevice, h->stream));
+    CU(cudaMemcpyAsync(h->st_x.as<float>() + h->rs_n * h->d, x, n * h->d * 4, cudaMemcpyHostToDevice, h->stream));
+    {   // pinned sources are copied asynchronously: wait, the caller owns the buffers again when we return
+        cudaPointerAttributes pa{};
+        if (cudaPointerGetAttributes(&pa, x) != cudaSuccess || pa.type != cudaMemoryTypeUnregistered) {
+            (void)cudaGetLastError();
+            CU(cudaStreamSynchronize(h->stream));
+        }
+    }
+    h->rs_n += n;
+    // one add_group call delivers a COMPLETE group (IndexIVF_HNSW_Grouping.cpp:43-157 encodes it on the spot): the
+    // staged groups can be encoded as soon as enough of them are waiting -- the bounded pass of
+    // tests/test_ivfhnsw_grouping_sift1b.cpp:138-201, without holding the raw vectors of the whole base set
+    if (h->rs_n * h->d * 4 >= (size_t)h->stage_bytes) return flush_groups_locked(h);
     return 0;
+}
+
+int ivfhnsw_b200_flush_groups(ivfhnsw_b200_t *h)
+{
+    std::lock_guard<std::mutex> lk(h->mu);
+    if (bind(h)) return IVFHNSW_B200_ECUDA;
+    if (!h->nsubc) return 0;
+    return flush_groups_locked(h);
 }
 
 // ------------------------------------------------------------------------------------ CSR build
@@ -600,6 +696,8 @@ static int build_csr(ivfhnsw_b200_t *h)
     const int nc = (int)h->nc, M = (int)h->M, nsubc = (int)h->nsubc;
     const uint32_t key_div = nsubc ? (uint32_t)nsubc : 1u;
     if ((uint64_t)nc * key_div >= (1ull << 32)) return h->fail(IVFHNSW_B200_EINVAL, "nc * nsubc overflows 32 bits");
+    if (n >= (1ull << 31))
+        return h->fail(IVFHNSW_B200_EINVAL, "%zu records staged: one device holds at most 2^31 - 1 (shard the lists with set_shard)", n);
     cudaStream_t st = h->stream;
     CU(h->list_size.ensure((size_t)nc * 4));
     CU(h->list_slot.ensure((size_t)nc * 4));
@@ -665,7 +763,7 @@ static int unstage_existing_lists(ivfhnsw_b200_t *h)
     const size_t n = h->ntotal;
     h->st_n = 0;
     if (n == 0) return 0;
-    if (int r = stage_reserve(h, n, false)) return r;
+    if (int r = stage_reserve(h, n)) return r;
     CU(launch_gather_lists(h->stream, LAUNCHES, (int)h->nc, (int)h->M, h->list_size.as<uint32_t>(),
                            h->list_slot.as<uint32_t>(), h->raw_off.as<uint32_t>(), h->codes.as<uint8_t>(),
                            h->norm_codes.as<uint8_t>(), h->ids.as<uint32_t>(), h->st_codes.as<uint8_t>(),
@@ -697,19 +795,21 @@ int ivfb200_ensure_group_meta(ivfhnsw_b200_t *h)
     CU(h->icd.ensure((size_t)nc * nsubc * 4));
     if (int r = ivfb200_coarse_dev(h, nc, h->centroids.as<float>(), nsubc, 1, h->icd.as<float>(), h->nn_idx.as<uint32_t>()))
         return r;
+    if (int r = check_coarse_flags(h)) return r;
     h->have_group_meta = true;
     return 0;
 }
 
 // compute_alpha (:691-728) and compute_subcentroid_idxs (:673-689) for n device points
 int ivfb200_group_stage(ivfhnsw_b200_t *h, size_t n, const float *x_dev, const uint32_t *list_dev, float *alphas_out,
-                         uint8_t *sub_out)
+                         uint8_t *sub_out, int zero_alphas, uint32_t *seen /* per-group point counts of earlier calls, or null */)
 {
     const int nc = (int)h->nc, d = (int)h->d, nsubc = (int)h->nsubc;
     cudaStream_t st = h->stream;
     if (int r = ivfb200_ensure_group_meta(h)) return r;
-    CU(cudaMemsetAsync(alphas_out, 0, (size_t)nc * 4, st));
+    if (zero_alphas) CU(cudaMemsetAsync(alphas_out, 0, (size_t)nc * 4, st));
     if (n == 0) return 0;
+    if (n >= (1ull << 31)) return h->fail(IVFHNSW_B200_EINVAL, "%zu points in one Grouping batch (limit 2^31 - 1)", n);
     // sort points by group (stable) -> order, grp_off
     CU(h->w_d2.ensure(n * 16));
     uint32_t *keys_out = h->w_d2.as<uint32_t>(), *ord_in = keys_out + n, *ord_out = ord_in + n;
@@ -728,6 +828,19 @@ int ivfb200_group_stage(ivfhnsw_b200_t *h, size_t n, const float *x_dev, const u
     CU(launch_hist(st, LAUNCHES, n, list_dev, gsize));
     CU(h->w_small.ensure(64));
     CU(launch_slot_scan(st, LAUNCHES, nc, 1, gsize, gslot, goff, h->w_small.as<uint32_t>()));
+    if (seen) {
+        uint32_t *flag = h->w_small.as<uint32_t>() + 8;
+        CU(cudaMemsetAsync(flag, 0, 4, st));
+        group_seen_kernel<<<(nc + 255) / 256, 256, 0, st>>>(nc, gsize, seen, flag);
+        ++h->stats.kernel_launches;
+        uint32_t bad = 0;
+        CU(cudaMemcpyAsync(&bad, flag, 4, cudaMemcpyDeviceToHost, st));
+        CU(cudaStreamSynchronize(st));
+        if (bad)
+            return h->fail(IVFHNSW_B200_ESTATE, "group %u received points after it had been encoded: every flush (flush_groups, or the "
+                           "automatic one of add_group) must hold COMPLETE groups -- alpha and the sub-groups are functions of "
+                           "all of a group's points (IndexIVF_HNSW_Grouping.cpp:43-157)", bad - 1);
+    }
     CU(h->w_f.ensure(n * 8));
     float *num = h->w_f.as<float>(), *den = num + n;
     CU(launch_group_points(st, LAUNCHES, 0, nc, d, nsubc, x_dev, ord_out, goff, h->centroids.as<float>(),
@@ -738,24 +851,46 @@ int ivfb200_group_stage(ivfhnsw_b200_t *h, size_t n, const float *x_dev, const u
     return 0;
 }
 
-// Grouping: nn lists, alphas, sub-group ids and codes for the staged points, then the CSR
+// Grouping: alpha, sub-group ids and codes of the raw points staged so far (complete groups), appended to the
+// encoded records; the raw vectors are dropped.  add_group body, IndexIVF_HNSW_Grouping.cpp:43-157.
+static int flush_groups_locked(ivfhnsw_b200_t *h)
+{
+    const size_t n = h->rs_n;
+    if (n == 0) return 0;
+    if (!h->have_centroids) return h->fail(IVFHNSW_B200_ESTATE, "centroids not set");
+    if (int r = stage_reserve(h, n)) return r;
+    CU(h->grp_seen.ensure(h->nc * 4));
+    if (!h->grp_seen_valid) {
+        CU(cudaMemsetAsync(h->grp_seen.p, 0, h->nc * 4, h->stream));
+        h->grp_seen_valid = true;
+    }
+    uint8_t *sub = h->st_sub.as<uint8_t>() + h->st_n;
+    if (int r = ivfb200_group_stage(h, n, h->st_x.as<float>(), h->rs_list.as<uint32_t>(), h->alphas.as<float>(), sub, 0,
+                                    h->grp_seen.as<uint32_t>()))
+        return r;
+    if (int r = ivfb200_encode_dev(h, n, h->st_x.as<float>(), h->rs_list.as<uint32_t>(), sub, h->alphas.as<float>(),
+                                   h->st_codes.as<uint8_t>() + h->st_n * h->M, h->st_norm.as<uint8_t>() + h->st_n, nullptr,
+                                   nullptr))
+        return r;
+    CU(cudaMemcpyAsync(h->st_list.as<uint32_t>() + h->st_n, h->rs_list.p, n * 4, cudaMemcpyDeviceToDevice, h->stream));
+    CU(cudaMemcpyAsync(h->st_ids.as<uint32_t>() + h->st_n, h->rs_ids.p, n * 4, cudaMemcpyDeviceToDevice, h->stream));
+    CU(cudaStreamSynchronize(h->stream));
+    h->st_n += n;
+    h->rs_n = 0;
+    return 0;
+}
+
 static int finalize_grouping(ivfhnsw_b200_t *h)
 {
-    const size_t n = h->st_n;
-    CU(h->st_sub.ensure(std::max<size_t>(n, 1)));
-    if (int r = ivfb200_group_stage(h, n, h->st_x.as<float>(), h->st_list.as<uint32_t>(), h->alphas.as<float>(),
-                            h->st_sub.as<uint8_t>()))
-        return r;
-    if (n) {
-        CU(h->st_codes.ensure(n * h->M));
-        CU(h->st_norm.ensure(n));
-        if (int r = ivfb200_encode_dev(h, n, h->st_x.as<float>(), h->st_list.as<uint32_t>(), h->st_sub.as<uint8_t>(),
-                               h->alphas.as<float>(), h->st_codes.as<uint8_t>(), h->st_norm.as<uint8_t>(), nullptr,
-                               nullptr))
-            return r;
-    }
+    if (int r = ivfb200_ensure_group_meta(h)) return r;   // nn lists / icd exist even for an empty index
+    if (int r = flush_groups_locked(h)) return r;
+    CU(h->st_sub.ensure(1));
     if (int r = build_csr(h)) return r;
     h->st_x.release();  // raw vectors are not needed any more
+    h->rs_list.release();
+    h->rs_ids.release();
+    h->grp_seen.release();
+    h->grp_seen_valid = false;
     return 0;
 }
 
@@ -783,7 +918,7 @@ int ivfhnsw_b200_load_lists(ivfhnsw_b200_t *h, const int64_t *list_off, const ui
     if (nsubc && (!nn_idx || !sub_sizes || !alphas || !icd))
         return h->fail(IVFHNSW_B200_EINVAL, "Grouping index needs nn_idx, sub_sizes, alphas, icd");
     h->st_n = 0;
-    if (int r = stage_reserve(h, std::max<size_t>(n, 1), false)) return r;
+    if (int r = stage_reserve(h, std::max<size_t>(n, 1))) return r;
     cudaStream_t st = h->stream;
     CU(h->w_e.ensure((nc + 1) * 8));
     CU(cudaMemcpyAsync(h->w_e.p, list_off, (nc + 1) * 8, cudaMemcpyHostToDevice, st));
@@ -815,7 +950,7 @@ int ivfhnsw_b200_load_lists(ivfhnsw_b200_t *h, const int64_t *list_off, const ui
 
 int ivfhnsw_b200_ntotal(ivfhnsw_b200_t *h, size_t *ntotal)
 {
-    *ntotal = h->st_dirty ? h->st_n : h->ntotal;
+    *ntotal = h->st_dirty ? h->st_n + h->rs_n : h->ntotal;
     return 0;
 }
 
@@ -876,6 +1011,9 @@ static int search_checks(ivfhnsw_b200_t *h, size_t k)
     if (!h->have_centroids) return h->fail(IVFHNSW_B200_ESTATE, "centroids not set");
     if (h->do_opq && !h->have_opq) return h->fail(IVFHNSW_B200_ESTATE, "do_opq set but no OPQ matrix");
     if (k == 0 || k > 2048) return h->fail(IVFHNSW_B200_EINVAL, "k %zu out of range [1, 2048]", k);
+    if (h->nsubc && h->nprobe * h->nsubc + h->nprobe + 1 > 65535)
+        return h->fail(IVFHNSW_B200_EINVAL, "Grouping search: nprobe * (nsubc + 1) = %zu exceeds 65534 (the pruning pass indexes "
+                       "its (probe, sub-group) rows with 16 bits); lower nprobe", h->nprobe * (h->nsubc + 1));
     const size_t smem = scan_smem_bytes((int)h->M, (int)h->nprobe, (int)k, (int)h->nsubc);
     if (smem > 227 * 1024) return h->fail(IVFHNSW_B200_EINVAL, "nprobe/k too large for the scan kernel (%zu B smem)", smem);
     return 0;
@@ -1129,8 +1267,8 @@ static int search_host(ivfhnsw_b200_t *h, size_t nq, size_t k, const float *x, c
         return r;
     CU(cudaMemcpyAsync(distances, h->w_out_d.p, nq * k * 4, cudaMemcpyDeviceToHost, st));
     CU(cudaMemcpyAsync(labels, h->w_out_l.p, nq * k * 8, cudaMemcpyDeviceToHost, st));
-    CU(cudaStreamSynchronize(st));
-    return 0;
+    if (cd) { CU(cudaStreamSynchronize(st)); return 0; }
+    return check_coarse_flags(h);
 }
 
 int ivfhnsw_b200_search(ivfhnsw_b200_t *h, size_t nq, size_t k, const float *x, float *distances, int64_t *labels)

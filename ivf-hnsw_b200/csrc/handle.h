@@ -16,6 +16,10 @@ namespace ivfb200 {
 struct DevBuf {
     void *p = nullptr;
     size_t cap = 0;
+    DevBuf() = default;
+    DevBuf(const DevBuf &) = delete;              // owns its allocation: locals release it on every exit path
+    DevBuf &operator=(const DevBuf &) = delete;
+    ~DevBuf() { release(); }
     cudaError_t ensure(size_t bytes)
     {
         if (bytes <= cap) return cudaSuccess;
@@ -80,8 +84,12 @@ struct ivfhnsw_b200 {
     bool have_lists = false, have_group_meta = false;
     size_t ntotal = 0, nslots = 0;
     // staging (records not yet in the CSR)
-    DevBuf st_list, st_ids, st_codes, st_norm, st_sub, st_x;
-    size_t st_n = 0;          // encoded records staged (IVFADC) or points staged (Grouping)
+    DevBuf st_list, st_ids, st_codes, st_norm, st_sub;
+    size_t st_n = 0;          // encoded records staged
+    // Grouping: raw points whose group is not encoded yet (list, id, vector); flushed by flush_groups / finalize
+    DevBuf rs_list, rs_ids, st_x, grp_seen;
+    size_t rs_n = 0;
+    bool grp_seen_valid = false;
     bool st_dirty = false;
     // workspace
     DevBuf w_x, w_xrot, w_cd, w_ci, w_seg, w_sub_base, w_qsd, w_g1, w_part, w_lut, w_coarse, w_xf16, w_out_d, w_out_l;
@@ -89,6 +97,7 @@ struct ivfhnsw_b200 {
     DevBuf counters;  // [0] scanned, [1] walked
     // options / stats
     long coarse_slack = 8, coarse_impl = 2, scan_split = 0, query_batch = 0, debug = 0;
+    long long stage_bytes = 4ll << 30;   // raw Grouping points staged before add_group encodes them (option "stage_bytes")
     bool timing = false;
     ivfhnsw_b200_stats_t stats{};
     std::vector<float> last_thr;
@@ -125,7 +134,7 @@ IVF_HIDDEN int ivfb200_assign_dev(ivfhnsw_b200_t *h, size_t n, const float *x_de
 IVF_HIDDEN int ivfb200_ensure_group_meta(ivfhnsw_b200_t *h);
 // group stage of add_group / train_pq: alphas_out[nc] and sub_out[n] for n device points with list ids
 IVF_HIDDEN int ivfb200_group_stage(ivfhnsw_b200_t *h, size_t n, const float *x_dev, const uint32_t *list_dev, float *alphas_out,
-                uint8_t *sub_out);
+                uint8_t *sub_out, int zero_alphas, uint32_t *seen);
 IVF_HIDDEN int ivfb200_encode_dev(ivfhnsw_b200_t *h, size_t n, const float *x_dev, const uint32_t *idx_dev, const uint8_t *sub_dev,
                const float *alphas_dev, uint8_t *codes_dev, uint8_t *norm_dev, float *norms_out, float *residual_out);
 }  // extern "C"

@@ -371,7 +371,7 @@ extern "C" int ivfhnsw_b200_train_pq(ivfhnsw_b200_t *h, size_t n, const float *x
         // per-group alpha and sub-centroid of every train vector (IndexIVF_HNSW_Grouping.cpp:506-547)
         CU(sub.ensure(n));
         CU(alphas.ensure(h->nc * 4));
-        if (int r = ivfb200_group_stage(h, n, xd.as<float>(), lists.as<uint32_t>(), alphas.as<float>(), sub.as<uint8_t>())) return r;
+        if (int r = ivfb200_group_stage(h, n, xd.as<float>(), lists.as<uint32_t>(), alphas.as<float>(), sub.as<uint8_t>(), 1, nullptr)) return r;
         subp = sub.as<uint8_t>();
         alp = alphas.as<float>();
     }

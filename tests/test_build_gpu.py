@@ -197,3 +197,100 @@ def test_train_pq_quality(name):
     rec_ref = np.mean([gt[i] in build_and_search(False)[i] for i in range(nq)])
     assert rec_ours >= rec_ref - 0.15, (rec_ours, rec_ref)   # 40 queries: 0.15 = 6 queries of noise
     idx.close()
+
+
+@pytest.mark.parametrize("name", ["grp_d32", "grp_sift_m16"])
+def test_add_group_equals_port_strict(port, name):
+    """K-G2 against the C restatement (fixed fp32 order, no -Ofast), fed the GPU's own exact neighbour lists:
+    alpha to 1e-6, sub-group sizes and id order EXACTLY, for every group -- the pin of compute_alpha /
+    compute_subcentroid_idxs (IndexIVF_HNSW_Grouping.cpp:673-728) on the CUDA path."""
+    pkg = load_pkg()
+    g, ix, _ = load_golden(name)
+    base = regenerate_base(name, g)
+    idx = make_index(pkg, ix, search_time=False)
+    assign = g["assign_all"]
+    ids = np.arange(base.shape[0], dtype=np.uint32)
+    for grp in range(ix["nc"]):
+        m = assign == grp
+        idx.add_group(grp, base[m], ids[m])
+    idx.compute_centroid_norms()
+    out = idx.export_index_dict()
+    ixb = dict(ix, centroids=ix["centroids_build"])
+    code_same, code_n, tested = 0, 0, 0
+    for grp in range(ix["nc"]):
+        members = np.nonzero(assign == grp)[0]
+        if members.size == 0:
+            continue
+        alpha, sub_idx, oid, oc, on, ss = port.add_group(ixb, grp, out["nn_idx"][grp], out["icd"][grp], base[members], members)
+        a, b = out["list_off"][grp], out["list_off"][grp + 1]
+        assert abs(alpha - out["alphas"][grp]) <= 1e-6 * max(1.0, abs(alpha)), (grp, alpha, out["alphas"][grp])
+        assert np.array_equal(ss, out["sub_sizes"][grp]), grp
+        assert np.array_equal(oid, out["ids"][a:b]), grp
+        code_same += int(np.all(oc == out["codes"][a:b], axis=1).sum())
+        code_n += b - a
+        tested += 1
+    assert tested >= ix["nc"] // 2
+    assert code_same >= 0.99 * code_n, (code_same, code_n)
+    idx.close()
+
+
+def test_streamed_grouping_ingest_equals_one_shot():
+    """The bounded-pass ingest (tests/test_ivfhnsw_grouping_sift1b.cpp:138-201): encoding complete groups range by
+    range (flush_groups) or through add_group's automatic flush gives the SAME index, bit for bit, as staging
+    everything until finalize -- and a group cannot be added twice."""
+    import torch
+    pkg = load_pkg()
+    rng = np.random.default_rng(5)
+    d, nc, M, nsubc, n = 32, 96, 8, 16, 30000
+    cent = rng.standard_normal((nc, d)).astype(np.float32) * 4
+    X = (cent[rng.integers(0, nc, n)] + rng.standard_normal((n, d))).astype(np.float32)
+    dev = torch.device("cuda:0")
+
+    def fresh():
+        j = pkg.IndexIVF_HNSW_Grouping(d, nc, M, 8, nsubc)
+        j.build_quantizer(centroids=cent)
+        return j
+
+    a = fresh()
+    a.train_pq(X[:8000])
+    lab = a.assign(X)
+    ids = np.arange(n, dtype=np.uint32)
+    Xd, idd, labd = torch.from_numpy(X).to(dev), torch.from_numpy(ids.view(np.int32)).to(dev), torch.from_numpy(lab.view(np.int32)).to(dev)
+    a.add_points_dev(Xd, idd, labd)                      # one shot: everything staged until finalize
+    a.compute_centroid_norms()
+    ref = a.export_index_dict()
+
+    b = fresh()                                          # three passes over group ranges, each flushed
+    b.set_pq(a.pq_centroids, a.norm_centroids, None)
+    for lo, hi in ((0, 30), (30, 31), (31, nc)):
+        m = (labd >= lo) & (labd < hi)
+        for part in (m & (idd < n // 2), m & (idd >= n // 2)):     # a range may arrive in several calls
+            b.add_points_dev(Xd[part].contiguous(), idd[part].contiguous(), labd[part].contiguous())
+        b.flush_groups()
+    b.compute_centroid_norms()
+    out = b.export_index_dict()
+
+    c = fresh()                                          # add_group with a tiny staging budget: flushes on its own
+    c.set_pq(a.pq_centroids, a.norm_centroids, None)
+    c.set_option("stage_bytes", 200 * d * 4)
+    for grp in range(nc):
+        m = lab == grp
+        c.add_group(grp, X[m], ids[m])
+    c.compute_centroid_norms()
+    out2 = c.export_index_dict()
+    for o in (out, out2):
+        for key in ("list_off", "sub_sizes", "alphas", "nn_idx", "icd", "norm_codes", "codes"):
+            assert np.array_equal(o[key], ref[key]), key
+        assert np.array_equal(o["ids"], ref["ids"])      # order of arrival inside a sub-group is kept
+    # a group that has been encoded cannot receive more points
+    e = fresh()
+    e.set_pq(a.pq_centroids, a.norm_centroids, None)
+    m = lab == 3
+    e.add_points_dev(Xd[torch.from_numpy(m).to(dev)].contiguous(), idd[torch.from_numpy(m).to(dev)].contiguous(),
+                     labd[torch.from_numpy(m).to(dev)].contiguous())
+    e.flush_groups()
+    e.add_group(3, X[m][:5], ids[m][:5])
+    with pytest.raises(pkg.B200Error, match="COMPLETE groups"):
+        e.flush_groups()
+    for j in (a, b, c, e):
+        j.close()

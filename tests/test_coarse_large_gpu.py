@@ -1,0 +1,73 @@
+"""K-A2 at the centroid counts of the benchmarked configurations (2^18, 2^20): the select kernel's long-row path
+(threshold from per-thread minima, coarse_select_kernel<16>), the 3-values-per-group GEMM epilogue and the
+self-excluding neighbour search of K-G3 -- against a float64 brute force computed with torch on the same GPU."""
+import numpy as np
+import pytest
+
+from conftest import load_pkg
+
+pytestmark = pytest.mark.gpu
+
+
+def _brute(torch, Q, C, dk):
+    Q64, C64 = Q[:, :dk].double(), C[:, :dk].double()
+    return (Q64 * Q64).sum(1)[:, None] - 2.0 * (Q64 @ C64.T) + (C64 * C64).sum(1)[None, :]
+
+
+@pytest.mark.parametrize("nc,d", [(1 << 18, 32), (1 << 20, 64)])
+def test_coarse_at_bench_centroid_counts(nc, d):
+    import torch
+    pkg = load_pkg()
+    dev = torch.device("cuda:0")
+    g = torch.Generator(device=dev)
+    g.manual_seed(nc + d)
+    C = torch.randn(nc, d, device=dev, generator=g)
+    nq = 300
+    Q = C[torch.randint(0, nc, (nq,), device=dev, generator=g)] + 0.5 * torch.randn(nq, d, device=dev, generator=g)
+    idx = pkg.IndexIVF_HNSW(d, nc, 8, 8)
+    idx.build_quantizer(centroids=C.cpu().numpy())
+    dd = _brute(torch, Q, C, (d // 16) * 16)
+    for impl in (1, 2):
+        idx.set_option("coarse_impl", impl)
+        for nprobe in (1, 64, 128):
+            cd = torch.empty(nq, nprobe, device=dev)
+            ci = torch.empty(nq, nprobe, dtype=torch.int32, device=dev)
+            idx.coarse_dev(Q, nprobe, cd, ci)
+            idx.sync()                                   # also fails on a select overflow flag
+            want = torch.sort(dd, dim=1).values[:, :nprobe]
+            got = torch.gather(dd, 1, ci.long())
+            assert torch.allclose(cd.double(), want, rtol=2e-5, atol=1e-4), (impl, nprobe)
+            assert torch.allclose(got, want, rtol=2e-5, atol=1e-4), (impl, nprobe)
+            assert bool((cd[:, 1:] >= cd[:, :-1]).all())
+            # distinct ids per row
+            assert int((torch.sort(ci, dim=1).values.diff(dim=1) == 0).sum()) == 0
+    idx.stats()                                          # raises when the sticky overflow flags are set
+    idx.close()
+
+
+def test_neighbour_lists_exclude_self_at_2_18():
+    """K-G3 (IndexIVF_HNSW_Grouping.cpp:47-63): the nsubc nearest OTHER centroids of every centroid, nearest first,
+    self dropped by id; checked on 2 000 sampled rows of a 2^18-centroid table (with duplicated centroids: the
+    duplicate is a legitimate neighbour at distance 0, the centroid itself is not)."""
+    import torch
+    pkg = load_pkg()
+    dev = torch.device("cuda:0")
+    nc, d, nsubc = 1 << 18, 32, 16
+    g = torch.Generator(device=dev)
+    g.manual_seed(99)
+    C = torch.randn(nc, d, device=dev, generator=g)
+    C[1000:1010] = C[5000:5010]                          # exact duplicates
+    idx = pkg.IndexIVF_HNSW_Grouping(d, nc, 8, 8, nsubc)
+    idx.build_quantizer(centroids=C.cpu().numpy())
+    idx.finalize()                                       # empty index: nn lists and icd only
+    out = idx.export_index_dict()
+    rows = torch.cat([torch.arange(990, 1020, device=dev), torch.randint(0, nc, (1970,), device=dev, generator=g)])
+    dd = _brute(torch, C[rows], C, d)
+    dd[torch.arange(rows.numel(), device=dev), rows] = float("inf")      # self
+    want = torch.sort(dd, dim=1).values[:, :nsubc]
+    nn = torch.from_numpy(out["nn_idx"].astype(np.int64)).to(dev)[rows]
+    icd = torch.from_numpy(out["icd"]).to(dev)[rows]
+    assert not bool((nn == rows[:, None]).any())
+    assert torch.allclose(torch.gather(dd, 1, nn), want, rtol=2e-5, atol=1e-4)
+    assert torch.allclose(icd.double(), want, rtol=2e-5, atol=1e-4)
+    idx.close()
