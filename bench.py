@@ -36,29 +36,38 @@ import numpy as np
 ROOT = os.path.dirname(os.path.abspath(__file__))
 sys.path.insert(0, ROOT)
 
+GEN_VERSION = 4   # bump when the synthetic generator changes (part of the index-cache key)
+
 WORKLOADS = {
     "c2": dict(kind="deep", nb=10_000_000, d=96, nc=65536, M=16, nsubc=64, pruning=True, opq=False, nprobe=64,
                max_codes=30000, k=10, nq=10000, nlearn=2_000_000, ntrain=65536, lloyd=2, efs=100),
     "c1": dict(kind="sift", nb=1_000_000, d=128, nc=16384, M=8, nsubc=0, pruning=False, opq=False, nprobe=32,
                max_codes=1_000_000, k=10, nq=10000, nlearn=1_000_000, ntrain=65536, lloyd=2, efs=80),
-    # SIFT1B-shape (configs[3]) at 1/10 scale with the list length kept: 100M x 128 over 2^17 centroids gives the
-    # same ~760 codes per list / ~12 per sub-group as 1B over 2^20, same nprobe / max_codes operating point
+    # BASELINE configs[3], the configuration the metric is quoted on: SIFT1B-shape 1B x 128, 2^20 centroids, 16-byte
+    # OPQ, Grouping(64) + Pruning, nprobe 128, max_codes 100 000, k 10 (examples/run_sift1b_grouping_OPQ.sh:38-47)
+    "c4": dict(kind="sift", nb=1_000_000_000, d=128, nc=1 << 20, M=16, nsubc=64, pruning=True, opq=True, nprobe=128,
+               max_codes=100000, k=10, nq=10000, nlearn=16_000_000, ntrain=65536, lloyd=2, efs=210, gt_queries=2000),
+    # the same at 1/10 scale with the list length kept: 100M x 128 over 2^17 centroids gives the same ~760 codes per
+    # list / ~12 per sub-group as 1B over 2^20, same nprobe / max_codes operating point (development workload)
     "c4s": dict(kind="sift", nb=100_000_000, d=128, nc=131072, M=16, nsubc=64, pruning=True, opq=True, nprobe=128,
                 max_codes=100000, k=10, nq=10000, nlearn=4_000_000, ntrain=65536, lloyd=2, efs=210),
-    # configs[3] with its real CENTROID COUNT (2^20) and a tenth of the points: the coarse stage and the neighbour-row
-    # gather (512 MB centroid table: HBM, not L2) as at 1B; the lists are a tenth as long (c4s has the other half)
+    # configs[3] with its real CENTROID COUNT (2^20) and a tenth of the points (development workload)
     "c4n": dict(kind="sift", nb=100_000_000, d=128, nc=1 << 20, M=16, nsubc=64, pruning=True, opq=True, nprobe=128,
                 max_codes=100000, k=10, nq=10000, nlearn=4_000_000, ntrain=65536, lloyd=1, efs=210),
     # configs[4] (ENN variant, run_sift1b_enn_64bits.sh: 64-BYTE codes, nprobe 1, k 1, queries = base vectors, ground
     # truth = identity, tests/test_ivfhnsw_sift1b_enn.cpp:27-47) at 1/50 scale with the list length kept
     "c5s": dict(kind="sift", enn=True, nb=20_000_000, d=128, nc=32768, M=64, nsubc=0, pruning=False, opq=False, nprobe=1,
                 max_codes=10 ** 9, k=1, nq=10000, nlearn=2_000_000, ntrain=65536, lloyd=2, efs=64),
+    # the "64 bits" reading of the same script name: 8-byte codes
+    "c5b": dict(kind="sift", enn=True, nb=20_000_000, d=128, nc=32768, M=8, nsubc=0, pruning=False, opq=False, nprobe=1,
+                max_codes=10 ** 9, k=1, nq=10000, nlearn=2_000_000, ntrain=65536, lloyd=2, efs=64),
     # configs[2]: base-point assign (mkindex path), one 1M-vector batch of the 1B stream per step against 2^20
     # centroids; ranks take different batches (data parallel over base vectors, no collective)
     "c3": dict(kind="sift", assign=True, nb=1_000_000, d=128, nc=1 << 20, M=16, nsubc=0, nq=1_000_000),
-    "tiny": dict(kind="deep", nb=200_000, d=96, nc=1024, M=16, nsubc=16, pruning=True, opq=False, nprobe=16,
+    "tiny": dict(kind="sift", nb=300_000, d=128, nc=1024, M=16, nsubc=16, pruning=True, opq=True, nprobe=16,
                  max_codes=3000, k=10, nq=1000, nlearn=100_000, ntrain=20000, lloyd=1, efs=64),
 }
+DEFAULT_WORKLOAD = "c4"
 
 
 def pkg():
@@ -68,41 +77,181 @@ def pkg():
 
 
 # --------------------------------------------------------------------------- synthetic data (device)
-def blob_means(w, torch, dev):
-    g = torch.Generator(device=dev)
-    g.manual_seed(1234 * 7919 + 13)
-    nblob = max(w["nc"] // 4, 4)
-    if w["kind"] == "sift":
-        m = torch.empty(nblob, w["d"], device=dev).exponential_(1.0, generator=g) + \
-            torch.empty(nblob, w["d"], device=dev).exponential_(1.0, generator=g)
-        return m * 15.0   # Gamma(2, 15)
-    return torch.randn(nblob, w["d"], device=dev, generator=g)
+class Gen:
+    """Seeded synthetic base / query / learn vectors, generated on the device chunk by chunk (never stored: a chunk is
+    a pure function of its seed, so the bounded-pass Grouping ingest can re-draw it like the reference re-reads the
+    base file, tests/test_ivfhnsw_grouping_sift1b.cpp:143-171).
+
+    SIFT-shape (d=128, byte-valued): nc/4 blobs whose means are drawn around nblob/8 super-means (neighbouring blobs
+    exist, as in real descriptors); a point is its blob mean + a RANK-12 component (12 Gaussian factors through a
+    global 12 x d matrix, dims permuted and sign-flipped per blob so that the blobs' subspaces differ) + a small
+    isotropic term, rounded and clipped to [0, 255].  The low intrinsic dimension is what makes a true nearest
+    neighbour distinguishable by a 16-byte code ("raise intra-blob structure").
+    DEEP-shape (d=96 float, L2-normalised): the same construction in floats."""
+
+    def __init__(self, w, torch, dev):
+        self.w, self.torch, self.dev = w, torch, dev
+        g = torch.Generator(device=dev)
+        g.manual_seed(1234 * 7919 + 13)
+        d = w["d"]
+        self.nblob = nblob = max(w["nc"] // 4, 4)
+        nsup = max(nblob // 8, 1)
+        r = self.r = 12
+        if w["kind"] == "sift":
+            sup = (torch.empty(nsup, d, device=dev).exponential_(1.0, generator=g) +
+                   torch.empty(nsup, d, device=dev).exponential_(1.0, generator=g)) * 15.0     # Gamma(2, 15)
+            self.means = (sup[torch.randint(0, nsup, (nblob,), device=dev, generator=g)] +
+                          torch.randn(nblob, d, device=dev, generator=g) * 12.0).clamp_(0, 255)
+            self.s_lr, self.s_iso = 30.0, 3.0
+        else:
+            sup = torch.randn(nsup, d, device=dev, generator=g)
+            self.means = sup[torch.randint(0, nsup, (nblob,), device=dev, generator=g)] + \
+                torch.randn(nblob, d, device=dev, generator=g) * 0.5
+            self.s_lr, self.s_iso = 0.8, 0.08
+        F = torch.randn(r, d, device=dev, generator=g)
+        self.F = F / F.norm(dim=1, keepdim=True)
+        self.nbank = 64
+        self.perm = torch.stack([torch.randperm(d, device=dev, generator=g) for _ in range(self.nbank)])
+        self.sign = (torch.randint(0, 2, (self.nbank, d), device=dev, generator=g).float() * 2 - 1)
+
+    def draw(self, n, seed):
+        torch, dev, w = self.torch, self.dev, self.w
+        g = torch.Generator(device=dev)
+        g.manual_seed(seed)
+        which = torch.randint(0, self.nblob, (n,), device=dev, generator=g)
+        bank = which % self.nbank
+        lr = (torch.randn(n, self.r, device=dev, generator=g) @ self.F) * self.s_lr
+        lr = torch.gather(lr, 1, self.perm[bank]) * self.sign[bank]
+        x = self.means[which] + lr + torch.randn(n, w["d"], device=dev, generator=g) * self.s_iso
+        if w["kind"] == "sift":
+            x = x.round_().clamp_(0, 255)
+        else:
+            x = x / x.norm(dim=1, keepdim=True)
+        return x.contiguous()
 
 
-def draw(w, torch, dev, means, n, seed):
-    g = torch.Generator(device=dev)
-    g.manual_seed(seed)
-    which = torch.randint(0, means.shape[0], (n,), device=dev, generator=g)
-    x = means[which]
-    if w["kind"] == "sift":
-        x = x + torch.randn(n, w["d"], device=dev, generator=g) * 12.0
-        x = x.round_().clamp_(0, 255)
-    else:
-        x = x + torch.randn(n, w["d"], device=dev, generator=g) * 0.35
-        x = x / x.norm(dim=1, keepdim=True)
-    return x.contiguous()
+def _gt_update(torch, w, queries, qn, x, b0, best_d, best_i):
+    """Exact nearest base vector of every query (harness-side brute force for the recall figure).  Byte-valued data:
+    TF32 products are exact (8-bit operands, fp32 accumulation of < 2^24 integers); DEEP: plain fp32."""
+    exact_tf32 = w["kind"] == "sift"
+    old = torch.backends.cuda.matmul.allow_tf32
+    torch.backends.cuda.matmul.allow_tf32 = bool(exact_tf32)
+    try:
+        for c0 in range(0, x.shape[0], 250_000):
+            xc = x[c0:c0 + 250_000]
+            dd = qn[:, None] - 2.0 * (queries @ xc.T) + (xc * xc).sum(1)[None]
+            md, mi = dd.min(1)
+            upd = md < best_d
+            best_d.copy_(torch.where(upd, md, best_d))
+            best_i.copy_(torch.where(upd, mi + (b0 + c0), best_i))
+            del dd
+    finally:
+        torch.backends.cuda.matmul.allow_tf32 = old
 
 
-def build_index(w, torch, dev, log, dist=None):
-    """Everything on the GPU through the library's own entry points. Returns (index, queries_dev, gt0)."""
+def cache_key(w):
+    import hashlib
+    h = hashlib.sha1(json.dumps(w, sort_keys=True).encode())
+    h.update(b"gen%d" % GEN_VERSION)
+    try:
+        with open(pkg().LIB_PATH, "rb") as f:
+            h.update(hashlib.sha1(f.read()).digest())       # code version: the built library itself
+    except OSError:
+        pass
+    return h.hexdigest()[:16]
+
+
+def cache_root():
+    for base in (os.environ.get("IVFHNSW_BENCH_CACHE"), "/dev/shm", tempfile.gettempdir()):
+        if base and os.path.isdir(base) and os.access(base, os.W_OK):
+            return os.path.join(base, "ivfb200_cache")
+    return None
+
+
+def cache_dir_for(w):
+    root = cache_root()
+    if root is None or os.environ.get("IVFHNSW_BENCH_NO_CACHE") or w["nb"] < 20_000_000:
+        return None
+    return os.path.join(root, cache_key(w))
+
+
+def save_cache(cdir, idx, w, cent_h, queries, gt0, log):
+    """The built index as flat arrays (the vectors write() serialises), so that the two arms the driver runs back to
+    back on one box -- and the cpu_baseline leg -- build a 1B index once."""
+    try:
+        os.makedirs(os.path.dirname(cdir), exist_ok=True)
+        ix = idx.export_index_dict()
+        need = sum(v.nbytes for v in ix.values() if isinstance(v, np.ndarray)) + cent_h.nbytes
+        st = os.statvfs(os.path.dirname(cdir))
+        if st.f_bavail * st.f_frsize < need * 1.2 + (4 << 30):
+            log("index cache skipped: %.1f GB needed, %.1f GB free" % (need / 1e9, st.f_bavail * st.f_frsize / 1e9))
+            return None
+        tmp = cdir + ".tmp%d" % os.getpid()
+        os.makedirs(tmp, exist_ok=True)
+        for key, v in ix.items():
+            if isinstance(v, np.ndarray):
+                np.save(os.path.join(tmp, "ix_%s.npy" % key), v)
+        np.save(os.path.join(tmp, "cent.npy"), cent_h)
+        np.save(os.path.join(tmp, "pqc.npy"), idx.pq_centroids)
+        np.save(os.path.join(tmp, "norm.npy"), idx.norm_centroids)
+        if idx.opq_matrix is not None:
+            np.save(os.path.join(tmp, "opq.npy"), idx.opq_matrix)
+        np.save(os.path.join(tmp, "queries.npy"), queries.cpu().numpy())
+        np.save(os.path.join(tmp, "gt0.npy"), gt0.cpu().numpy())
+        with open(os.path.join(tmp, "done"), "w") as f:
+            f.write("ok")
+        if os.path.exists(cdir):
+            import shutil
+            shutil.rmtree(tmp, ignore_errors=True)
+        else:
+            os.rename(tmp, cdir)
+        return ix
+    except Exception as ex:       # a cache is an optimisation: never lose the run over it
+        log("index cache not written: %r" % (ex,))
+        return None
+
+
+def load_cache(cdir, w, torch, dev, log):
+    P = pkg()
+    cls = P.IndexIVF_HNSW_Grouping if w["nsubc"] else P.IndexIVF_HNSW
+    args = (w["d"], w["nc"], w["M"], 8) + ((w["nsubc"],) if w["nsubc"] else ())
+    idx = cls(*args, device=dev.index or 0)
+    ld = lambda n: np.load(os.path.join(cdir, n))
+    cent_h = ld("cent.npy")
+    idx.build_quantizer(centroids=cent_h)
+    opq = ld("opq.npy") if os.path.exists(os.path.join(cdir, "opq.npy")) else None
+    idx.set_pq(ld("pqc.npy"), ld("norm.npy"), opq)
+    idx.do_opq = w["opq"]
+    ix = {f[3:-4]: ld(f) for f in os.listdir(cdir) if f.startswith("ix_")}
+    idx.load_index_dict(ix)
+    if w["opq"]:
+        idx.rotate_quantizer()
+    idx.nprobe, idx.max_codes, idx.do_pruning = w["nprobe"], w["max_codes"], w["pruning"]
+    queries = torch.from_numpy(ld("queries.npy")).to(dev)
+    gt0 = torch.from_numpy(ld("gt0.npy")).to(dev)
+    log("index loaded from cache %s (ntotal %d)" % (cdir, idx.ntotal))
+    return idx, queries, gt0, cent_h
+
+
+def build_index(w, torch, dev, log, dist=None, rank=0, world=1):
+    """Everything on the GPU through the library's own entry points. Returns (index, queries_dev, gt0, centroids).
+
+    IVFADC: one pass (assign + encode per 1M batch, IndexIVF_HNSW.cpp:75-138).
+    Grouping: the reference's bounded passes (tests/test_ivfhnsw_grouping_sift1b.cpp:138-201): pass 1 assigns every
+    batch (K-A1, the 2.7e17-FLOP part; split over the ranks when there are several, labels all-gathered), then the
+    groups are taken range by range: the batches are re-drawn, the points of the range collected, add_points_dev +
+    flush_groups encodes them and drops the raw vectors (peak HBM = one range, not the base set)."""
+    cdir = cache_dir_for(w)
+    if cdir and os.path.exists(os.path.join(cdir, "done")):
+        return load_cache(cdir, w, torch, dev, log)
     P = pkg()
     t0 = time.time()
-    means = blob_means(w, torch, dev)
+    G = Gen(w, torch, dev)
     cls = P.IndexIVF_HNSW_Grouping if w["nsubc"] else P.IndexIVF_HNSW
     args = (w["d"], w["nc"], w["M"], 8) + ((w["nsubc"],) if w["nsubc"] else ())
     idx = cls(*args, device=dev.index or 0)
     # coarse centroids: Lloyd iterations driven by K-A1 itself (k-means is not on the path; any file works)
-    learn = draw(w, torch, dev, means, w["nlearn"], 1234 + 2)
+    learn = G.draw(w["nlearn"], 1234 + 2)
     kmeans = importlib.import_module("ivf-hnsw_b200.kmeans")
     cent = kmeans.lloyd_centroids(idx, learn, w["nc"], iters=w["lloyd"], seed=7)
     if dist is not None:
@@ -127,38 +276,89 @@ def build_index(w, torch, dev, log, dist=None):
             opq = opq.cpu().numpy()
         idx.set_pq(pqc.cpu().numpy(), nrm.cpu().numpy(), opq)
     log("train_pq %.1fs" % (time.time() - t0))
-    del learn
-    # base vectors: generated, assigned (K-A1) and added in 1M batches (tests/...:102,142-153)
+    del learn, cent
+    torch.cuda.empty_cache()
     bs = 1_000_000
-    queries = draw(w, torch, dev, means, w["nq"], 1234 + 1)
-    best_d = torch.full((w["nq"],), float("inf"), device=dev)
-    best_i = torch.zeros(w["nq"], dtype=torch.long, device=dev)
-    qn = (queries * queries).sum(1)
-    for b0 in range(0, w["nb"], bs):
-        n = min(bs, w["nb"] - b0)
-        x = draw(w, torch, dev, means, n, 99991 + b0)
-        if w.get("enn") and b0 == 0:      # ENN: the queries ARE the first base vectors, ground truth = identity
-            queries = x[:w["nq"]].clone()
-            qn = (queries * queries).sum(1)
-        ids = torch.arange(b0, b0 + n, dtype=torch.int32, device=dev)
-        idx.add_points_dev(x, ids, None)
-        # exact ground truth (neighbour #0) for the recall figure: harness-side brute force
-        for c0 in range(0, n, 200_000):
-            xc = x[c0:c0 + 200_000]
-            dd = qn[:, None] - 2.0 * (queries @ xc.T) + (xc * xc).sum(1)[None]
-            md, mi = dd.min(1)
-            upd = md < best_d
-            best_d = torch.where(upd, md, best_d)
-            best_i = torch.where(upd, mi + (b0 + c0), best_i)
-            del dd
-        del x, ids
+    nb = w["nb"]
+    chunks = [(b0, min(bs, nb - b0)) for b0 in range(0, nb, bs)]
+    seed_of = lambda b0: 99991 + b0
+    queries = G.draw(w["nq"], 1234 + 1)
+    if w.get("enn"):      # ENN: the queries ARE the first base vectors, ground truth = identity
+        queries = G.draw(chunks[0][1], seed_of(0))[:w["nq"]].clone()
+    ngt = min(w["nq"], w.get("gt_queries", w["nq"]))      # recall is measured on the first ngt queries
+    qg = queries[:ngt]
+    qn = (qg * qg).sum(1)
+    best_d = torch.full((ngt,), float("inf"), device=dev)
+    best_i = torch.zeros(ngt, dtype=torch.long, device=dev)
+    grouping = w["nsubc"] > 0
+    split = dist is not None and grouping and nb >= 20_000_000     # pass 1 split over the ranks
+    labels = torch.zeros(nb, dtype=torch.int32, device=dev) if grouping else None
+    for ci, (b0, n) in enumerate(chunks):
+        if split and ci % world != rank:
+            continue
+        x = G.draw(n, seed_of(b0))
+        if grouping:
+            idx.assign_dev(x, labels[b0:b0 + n])                       # K-A1: IndexIVF_HNSW::assign
+        else:
+            ids = torch.arange(b0, b0 + n, dtype=torch.int32, device=dev)
+            idx.add_points_dev(x, ids, None)                            # assign + encode
+        _gt_update(torch, w, qg, qn, x, b0, best_d, best_i)
+        del x
+        if ci % 100 == 99:
+            log("pass 1: %d / %d batches, %.1fs" % (ci + 1, len(chunks), time.time() - t0))
+    if split:
+        dist.all_reduce(labels, op=dist.ReduceOp.SUM)          # disjoint slices: the sum is the concatenation
+        allb = [torch.empty_like(best_d) for _ in range(world)]
+        alli = [torch.empty_like(best_i) for _ in range(world)]
+        dist.all_gather(allb, best_d)
+        dist.all_gather(alli, best_i)
+        sb, si = torch.stack(allb), torch.stack(alli)
+        win = sb.argmin(0)
+        best_i = si.gather(0, win[None])[0]
+    if grouping:
+        idx.sync()                                             # also checks the coarse stage's overflow flags
+        log("pass 1 (assign) done %.1fs" % (time.time() - t0))
+        # group ranges of at most ~pass_points points each
+        per_pass = int(w.get("pass_points", 48_000_000))
+        cnt = torch.zeros(w["nc"], dtype=torch.long, device=dev)
+        for b0, n in chunks:
+            cnt += torch.bincount(labels[b0:b0 + n].long(), minlength=w["nc"])
+        cum = torch.cumsum(cnt, 0).cpu().numpy()
+        bounds, lo = [], 0
+        while lo < w["nc"]:
+            base = cum[lo - 1] if lo else 0
+            hi = int(np.searchsorted(cum, base + per_pass, side="right"))
+            hi = max(hi, lo + 1)
+            bounds.append((lo, min(hi, w["nc"])))
+            lo = hi
+        for pi, (lo, hi) in enumerate(bounds):
+            for b0, n in (chunks if len(bounds) > 1 else []):
+                lab = labels[b0:b0 + n]
+                sel = ((lab >= lo) & (lab < hi)).nonzero().squeeze(1)
+                if sel.numel() == 0:
+                    continue
+                x = G.draw(n, seed_of(b0))
+                idx.add_points_dev(x[sel].contiguous(), (sel + b0).int().contiguous(), lab[sel].contiguous())
+                del x
+            if len(bounds) == 1:      # small index: one range, batches added as they are drawn
+                for b0, n in chunks:
+                    x = G.draw(n, seed_of(b0))
+                    idx.add_points_dev(x, torch.arange(b0, b0 + n, dtype=torch.int32, device=dev), labels[b0:b0 + n])
+                    del x
+            idx.flush_groups()
+            log("pass 2: group range %d / %d encoded, %.1fs" % (pi + 1, len(bounds), time.time() - t0))
+        del labels
     idx.compute_centroid_norms()       # also the flush point (finalize)
     if w["nsubc"]:
         idx.compute_inter_centroid_dists()
     if w["opq"]:
         idx.rotate_quantizer()
+    torch.cuda.empty_cache()
     log("index built %.1fs (ntotal %d)" % (time.time() - t0, idx.ntotal))
     idx.nprobe, idx.max_codes, idx.do_pruning = w["nprobe"], w["max_codes"], w["pruning"]
+    if cdir and rank == 0:
+        save_cache(cdir, idx, w, cent_h, queries, best_i, log)
+        log("index cached %.1fs" % (time.time() - t0))
     return idx, queries, best_i, cent_h
 
 
@@ -201,8 +401,17 @@ class Clocks:
 
 
 # --------------------------------------------------------------------------- reference (CPU) arm
-def export_for_reference(idx, w, cent_h, workdir):
+def reference_workdir(idx, w, cent_h, log):
+    """Everything the compiled reference needs, in its own file formats: x.index (written natively by the library,
+    byte-compatible), pq/norm/opq files, the UNROTATED centroid file.  Kept next to the index cache so that the
+    reference arm and the cpu_baseline leg of the other arm share the export and the HNSW graph."""
     P = pkg()
+    cdir = cache_dir_for(w)
+    workdir = (cdir + "_ref") if cdir else tempfile.mkdtemp(prefix="ivfb200_ref_")
+    if os.path.exists(os.path.join(workdir, "exported")):
+        return workdir
+    os.makedirs(workdir, exist_ok=True)
+    t0 = time.time()
     idx.write(os.path.join(workdir, "x.index"))
     P.write_ProductQuantizer(os.path.join(workdir, "pq.pq"), w["d"], w["M"], idx.pq_centroids)
     P.write_ProductQuantizer(os.path.join(workdir, "norm.pq"), 1, 1, idx.norm_centroids)
@@ -211,34 +420,64 @@ def export_for_reference(idx, w, cent_h, workdir):
     sys.path.insert(0, os.path.join(ROOT, "oracle"))
     import oracle as O
     O.write_fvecs(os.path.join(workdir, "centroids.fvecs"), cent_h)   # UNROTATED file, like the reference's input
+    with open(os.path.join(workdir, "exported"), "w") as f:
+        f.write("ok")
+    log("reference files written %.1fs" % (time.time() - t0))
+    return workdir
 
 
-def run_reference_cpu(w, workdir, queries_h, gt0, nq_sample, nproc, steps=1, warmup=0):
+def run_reference_cpu(w, workdir, queries_h, gt0, nq_sample, nproc, steps=1, warmup=0, log=None):
     """Times IndexIVF_HNSW[_Grouping]::search of the compiled reference (trace-stripped build) on the host
-    cores: `nproc` processes, each loading the same read-only index and searching a disjoint query slice
-    sequentially, exactly like tests/test_ivfhnsw_sift1b.cpp:192-213."""
+    cores: the index is read ONCE, then `nproc` forked workers each search a disjoint query slice sequentially,
+    exactly like tests/test_ivfhnsw_sift1b.cpp:192-213.  Returns the result dict of
+    oracle/ref_worker.py; <workdir>/parity.npz holds the reference's answers and HNSW candidate lists."""
     np.save(os.path.join(workdir, "queries.npy"), queries_h[:nq_sample])
     np.save(os.path.join(workdir, "gt0.npy"), gt0[:nq_sample])
-    cfg = dict(w, workdir=workdir, nproc=nproc, nq_sample=nq_sample, steps=steps, warmup=warmup)
+    cfg = dict(w, workdir=workdir, nproc=nproc, nq_sample=nq_sample, steps=steps, warmup=warmup, k_recall=100)
     with open(os.path.join(workdir, "cfg.json"), "w") as f:
         json.dump(cfg, f)
     env = dict(os.environ, OMP_NUM_THREADS="1", OPENBLAS_NUM_THREADS="1")
-    # rank 0 of the workers builds the HNSW once (the reference's own build_quantizer), the others load it
     t0 = time.time()
-    subprocess.check_call([sys.executable, os.path.join(ROOT, "oracle", "ref_worker.py"), workdir, "build"], env=env,
+    subprocess.check_call([sys.executable, os.path.join(ROOT, "oracle", "ref_worker.py"), workdir, "run"], env=env,
                           stdout=subprocess.DEVNULL)
-    t_build = time.time() - t0
-    procs = [subprocess.Popen([sys.executable, os.path.join(ROOT, "oracle", "ref_worker.py"), workdir, "search", str(r)],
-                              env=env, stdout=subprocess.PIPE, text=True) for r in range(nproc)]
-    outs = [json.loads(p.communicate()[0].strip().splitlines()[-1]) for p in procs]
-    for p in procs:
-        assert p.returncode == 0
-    # every worker times its own sequential loop; aggregate QPS = sum of per-process rates
-    qps = sum(o["n"] / o["sec"] for o in outs)
-    us_per_query_1t = float(np.mean([o["sec"] / o["n"] * 1e6 for o in outs]))
-    recall = sum(o["correct"] for o in outs) / max(1, sum(o["n"] for o in outs))
-    return dict(qps=qps, us_per_query=us_per_query_1t, recall=recall, hnsw_build_s=t_build,
-                ms_per_step=1e3 * max(o["sec"] for o in outs))
+    res = json.load(open(os.path.join(workdir, "result.json")))
+    if log:
+        log("reference: HNSW %.0fs, read %.0fs, total %.0fs" % (res["hnsw_s"], res["read_s"], time.time() - t0))
+    return res
+
+
+def parity_against_reference(idx, w, workdir, queries_h, k, gt0_h=None):
+    """The north_star bar, checked on the BENCHED index inside the run: the reference's own coarse candidate lists
+    (its HNSW's answers, dumped by the CPU leg) go through ivfhnsw_b200_search_given_coarse; labels must be identical
+    up to equal-distance ties and distances within 1e-4 relative."""
+    z = np.load(os.path.join(workdir, "parity.npz"))
+    Dr, Lr, cd, ci = z["D"], z["L"], z["cd"], z["ci"]
+    n = Dr.shape[0]
+    D, L = idx.search2(k, queries_h[:n], cd, ci)
+    o = np.argsort(Dr, axis=1, kind="stable")
+    Dr, Lr = np.take_along_axis(Dr, o, 1), np.take_along_axis(Lr, o, 1)
+    fin = np.abs(Dr) < 1e30
+    # the terms that cancel in an ADC distance are O(||c||^2): same guard as the parity tests (tests/conftest.py)
+    scale = float(idx.get_centroid_norms().max())
+    same_fin = bool(np.array_equal(fin, np.abs(D) < 1e30))
+    rel = np.abs(D[fin] - Dr[fin]) / np.maximum(np.abs(Dr[fin]), 1e-2 * scale) if same_fin and fin.any() else np.array([np.inf])
+    bad = 0
+    for i in range(n):
+        if set(L[i].tolist()) == set(Lr[i].tolist()):
+            continue
+        kth = Dr[i][-1]
+        tol = 1e-4 * max(abs(float(kth)), 1e-2 * scale)
+        a = {int(l) for l, dd in zip(L[i], D[i]) if dd < kth - tol}
+        b = {int(l) for l, dd in zip(Lr[i], Dr[i]) if dd < kth - tol}
+        bad += a != b
+    ours_r10 = None
+    if gt0_h is not None:      # our recall on the reference's own sample and candidate lists
+        ours_r10 = float(np.mean([gt0_h[i] in L[i] for i in range(n)]))
+    return {"queries": int(n), "labels_equal_up_to_ties": bad == 0, "queries_with_label_mismatch": int(bad),
+            "recall_at_10_on_reference_candidates": ours_r10,
+            "labels_identical_rows": int(sum(np.array_equal(L[i], Lr[i]) for i in range(n))),
+            "max_rel_dist_err": float(rel.max()), "tolerance": 1e-4,
+            "how": "reference's HNSW candidate lists -> ivfhnsw_b200_search_given_coarse on the benched index"}
 
 
 # --------------------------------------------------------------------------- assign workload (configs[2])
@@ -248,14 +487,14 @@ def run_assign(args, w, torch, dev, dist, rank, world, local, log, emit):
     HOST uint8 batch (what mkindex streams from the .bvecs file), labels read back."""
     P = pkg()
     t0 = time.time()
-    means = blob_means(w, torch, dev)
-    cent = draw(w, torch, dev, means, w["nc"], 4242)          # any centroid file works for the timing
+    G = Gen(w, torch, dev)
+    cent = G.draw(w["nc"], 4242)          # any centroid file works for the timing
     if dist is not None:
         dist.broadcast(cent, src=0)
     idx = P.IndexIVF_HNSW(w["d"], w["nc"], w["M"], 8, device=dev.index or 0)
     idx.build_quantizer(centroids=cent.cpu().numpy())
     n = w["nb"]
-    x = draw(w, torch, dev, means, n, 99991 + rank)
+    x = G.draw(n, 99991 + rank)
     lab = torch.empty(n, dtype=torch.int32, device=dev)
     dd = torch.empty(n, dtype=torch.float32, device=dev)
     stream = torch.cuda.Stream(device=dev)
@@ -348,7 +587,7 @@ def main():
     ap.add_argument("--steps", type=int, default=5)
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
-    ap.add_argument("--workload", default=os.environ.get("IVFHNSW_BENCH_WORKLOAD", "c2"))
+    ap.add_argument("--workload", default=os.environ.get("IVFHNSW_BENCH_WORKLOAD", DEFAULT_WORKLOAD))
     ap.add_argument("--cpu-sample", type=int, default=0, help="queries for the CPU baseline (0 = auto)")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--list-shards", type=int, default=int(os.environ.get("IVFHNSW_BENCH_LIST_SHARDS", "0")),
@@ -386,12 +625,16 @@ def main():
             emit({"impl": "reference", "unavailable": "assign over 2^20 centroids needs a ~5 min HNSW build on the CPU"})
             return 0
         return run_assign(args, w, torch, dev, dist, rank, world, local, log, emit)
-    idx, queries, gt0, cent_h = build_index(w, torch, dev, log, dist)
+    idx, queries, gt0, cent_h = build_index(w, torch, dev, log, dist, rank, world)
     if args.coarse_impl >= 0:
         idx.set_option("coarse_impl", args.coarse_impl)
     nq, k, nprobe = w["nq"], w["k"], w["nprobe"]
+    ngt = int(gt0.shape[0])                      # recall is measured on the first ngt queries
     ncores = len(os.sched_getaffinity(0))
-    workload_name = {"c2": "DEEP-shape 10Mx96 f32, 2^16 centroids, 16-byte PQ, Grouping(64)+Pruning, nprobe=64, "
+    workload_name = {"c4": "SIFT1B-shape 1Bx128 (byte-valued), 2^20 centroids, 16-byte OPQ, Grouping(64)+Pruning, nprobe=128, "
+                           "max_codes=100000, k=10, 10k queries/step (BASELINE configs[3], the configuration the metric is "
+                           "quoted on)",
+                     "c2": "DEEP-shape 10Mx96 f32, 2^16 centroids, 16-byte PQ, Grouping(64)+Pruning, nprobe=64, "
                            "max_codes=30000, k=10, 10k queries/step (BASELINE configs[1])",
                      "c1": "SIFT-shape 1Mx128, 2^14 centroids, 8-byte PQ, IVFADC, nprobe=32, k=10, 10k queries/step "
                            "(BASELINE configs[0])",
@@ -402,41 +645,50 @@ def main():
                             "nprobe=128, max_codes=100000, k=10, 10k queries/step (BASELINE configs[3] with a tenth of the points)",
                      "c5s": "SIFT1B ENN variant at 1/50 scale: 20Mx128, 2^15 centroids, 64-byte PQ, IVFADC, nprobe=1, k=1, "
                             "queries = first 10k base vectors (BASELINE configs[4] scaled)",
+                     "c5b": "SIFT1B ENN variant at 1/50 scale with 8-byte (64-bit) codes: 20Mx128, 2^15 centroids, IVFADC, "
+                            "nprobe=1, k=1, queries = first 10k base vectors (BASELINE configs[4] scaled)",
                      "tiny": "tiny development workload"}[args.workload]
     config = {"workload": workload_name, "nb": w["nb"], "d": w["d"], "nc": w["nc"], "code_size": w["M"],
-              "nsubc": w["nsubc"], "pruning": w["pruning"], "nprobe": nprobe, "max_codes": w["max_codes"], "k": k,
-              "nq_per_step": nq, "l2": "flushed between timed steps (256 MiB write)",
-              "sharding": "lists by centroid range, NCCL all-gather of partial top-k" if world > 1 else "none"}
+              "nsubc": w["nsubc"], "pruning": w["pruning"], "opq": w["opq"], "nprobe": nprobe, "max_codes": w["max_codes"],
+              "k": k, "nq_per_step": nq, "l2": "flushed between timed steps (256 MiB write)",
+              "sharding": "lists by centroid range, NCCL exchange of work records and partial top-k" if world > 1 else "none"}
+
+    def recalls(Ls):
+        """Recall@R as the reference defines it (tests/test_ivfhnsw_sift1b.cpp:175-176,203-207): the true nearest
+        neighbour is among the first R returned labels."""
+        hit = Ls[:ngt] == gt0[:, None]
+        return {"r1": float(hit[:, :1].any(1).float().mean().item()),
+                "r10": float(hit[:, :10].any(1).float().mean().item()),
+                "r100": float(hit[:, :100].any(1).float().mean().item())}
 
     # ------------------------------------------------------------------ reference arm
     if args.impl == "reference":
-        workdir = tempfile.mkdtemp(prefix="ivfb200_ref_")
-        export_for_reference(idx, w, cent_h, workdir)
+        workdir = reference_workdir(idx, w, cent_h, log)
         idx.close()
         torch.cuda.empty_cache()
         nproc = ncores
-        sample = args.cpu_sample or min(nq, max(nproc * 40, 400))
+        sample = args.cpu_sample or min(ngt, max(nproc * 40, 400))
         res = run_reference_cpu(w, workdir, queries.cpu().numpy(), gt0.cpu().numpy(), sample, nproc,
-                                steps=args.steps, warmup=args.warmup)
-        line = {"impl": "reference", "metric": "QPS at Recall@10 (k=10)", "value": res["qps"], "unit": "queries/s",
+                                steps=args.steps, warmup=args.warmup, log=log)
+        line = {"impl": "reference", "metric": "QPS at fixed Recall@10 (k=10)", "value": res["qps"], "unit": "queries/s",
                 "n_gpus": args.gpus, "steps": args.steps, "warmup": args.warmup, "ms_per_step": res["ms_per_step"],
                 "higher_is_better": True, "scaling": "strong", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
-                "config": config, "recall_at_10": res["recall"],
+                "config": config, "recall_at_10": res["recall"]["r10"], "recall": res["recall"],
                 "cpu_baseline": {"value": res["qps"], "unit": "queries/s", "cores": nproc, "kind": "reference",
-                                 "sample": "%d queries of the same batch, %d single-thread processes of the compiled "
-                                           "reference over one GPU-built .index (%.0f us/query/thread)" %
-                                           (sample, nproc, res["us_per_query"])},
+                                 "sample": "%d queries of the same batch, %d single-thread processes (forked after one "
+                                           "read()) of the compiled reference over the GPU-built .index, efSearch %d "
+                                           "(%.0f us/query/thread)" % (sample, nproc, w["efs"], res["us_per_query"])},
                 "e2e": {"value": res["qps"], "unit": "queries/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
                 "gpu_launches": 0}
         emit(line)
         return 0
 
     # ------------------------------------------------------------------ our arm
-    # Layout: query_groups x list_shards grid.  List sharding is the capacity axis -- the
-    # smallest number of shards whose lists fit one GPU; the remaining factor serves independent query streams
-    # from replicas of the lists (no data-path collective between groups).
-    index_bytes = w["nb"] * (w["M"] + 2 + 8)
-    list_shards = args.list_shards or sharding.auto_list_shards(world, index_bytes, 0.6 * torch.cuda.mem_get_info(dev)[1])
+    # N > 1 (DESIGN.md section 5): the inverted lists are sharded over ALL ranks by centroid range (north_star).  The
+    # headline is WEAK scaling of that layout: every rank brings its own batch of nq queries (prepared at home: coarse
+    # stage + pruning pass), the work records are exchanged, every rank scans the lists it owns for the queries of all
+    # ranks, partial top-k lists are exchanged and merged.  The same layout on ONE fixed batch (strong scaling) and the
+    # replica layout (every rank searching the whole index alone) are measured beside it.
     stream = torch.cuda.Stream(device=dev)   # a real (non-default) stream shared by torch and the library
     torch.cuda.set_stream(stream)
     idx.set_stream(stream.cuda_stream)
@@ -444,41 +696,35 @@ def main():
     L = torch.empty(nq, k, dtype=torch.int64, device=dev)
     flush = torch.empty(256 << 20, dtype=torch.uint8, device=dev)
 
-    def make_layout(R_l):
-        """-> (search(q_dev) filling D/L, query_groups, group handle) for a grid with R_l list shards."""
-        qg, lrank, granks = sharding.grid_layout(rank, world, R_l)
-        n_groups = world // R_l
-        if R_l == 1:
-            idx.set_shard(0, w["nc"])
-            return (lambda q_dev: idx.search_dev(k, q_dev, D, L)), n_groups, None, lrank
-        group = None
-        for g in range(n_groups):       # every rank takes part in creating every group
-            h = dist.new_group(list(range(g * R_l, (g + 1) * R_l)))
-            if g == qg:
-                group = h
-        pD = torch.empty(nq, k, dtype=torch.float32, device=dev)
-        pS = torch.empty(nq, k, dtype=torch.int32, device=dev)
-        pL = torch.empty(nq, k, dtype=torch.int64, device=dev)
-        gD = torch.empty(R_l, nq, k, dtype=torch.float32, device=dev)
-        gS = torch.empty(R_l, nq, k, dtype=torch.int32, device=dev)
-        gL = torch.empty(R_l, nq, k, dtype=torch.int64, device=dev)
-        # query-parallel preparation inside the shard group: each rank builds the work-table records of
-        # nq / R_l queries, the records are all-gathered, every rank scans the lists it owns for all nq queries
-        qb0, qe0, per = sharding.query_slice(lrank, R_l, nq)
-        tables = torch.empty(R_l * per, idx.tables_bytes(), dtype=torch.uint8, device=dev)
-        idx.set_shard(*sharding.shard_range(lrank, R_l, w["nc"]))
+    def single_search(q_dev):
+        idx.search_dev(k, q_dev, D, L)
 
-        def search(q_dev):
-            idx.prepare_dev(q_dev, qb0, qe0, tables)
-            sharding.gather_tables(dist, tables, lrank, per, group)
-            idx.scan_tables_dev(k, q_dev, tables, pD, pS, pL)
-            sharding.gather_partials(dist, pD, pS, pL, gD, gS, gL, group)
-            idx.merge_partials_dev(k, nq, R_l, gD, gS, gL, D, L)
-        return search, n_groups, group, lrank
+    def make_sharded(nq_total, home_lo, home_hi):
+        """Sharded search of nq_total queries of which this rank prepares [home_lo, home_hi); fills Dall/Lall
+        (all nq_total rows, identical on every rank)."""
+        per = home_hi - home_lo
+        assert per * world == nq_total
+        tables = torch.empty(nq_total, idx.tables_bytes(), dtype=torch.uint8, device=dev)
+        pD = torch.empty(nq_total, k, dtype=torch.float32, device=dev)
+        pS = torch.empty(nq_total, k, dtype=torch.int32, device=dev)
+        pL = torch.empty(nq_total, k, dtype=torch.int64, device=dev)
+        gD = torch.empty(world, nq_total, k, dtype=torch.float32, device=dev)
+        gS = torch.empty(world, nq_total, k, dtype=torch.int32, device=dev)
+        gL = torch.empty(world, nq_total, k, dtype=torch.int64, device=dev)
+        Dall = torch.empty(nq_total, k, dtype=torch.float32, device=dev)
+        Lall = torch.empty(nq_total, k, dtype=torch.int64, device=dev)
 
-    def timed_run(search, steps, warmup, clocks):
+        def search(q_all):
+            idx.prepare_dev(q_all, home_lo, home_hi, tables)
+            sharding.gather_tables(dist, tables, rank, per, None)
+            idx.scan_tables_dev(k, q_all, tables, pD, pS, pL)
+            sharding.gather_partials(dist, pD, pS, pL, gD, gS, gL, None)
+            idx.merge_partials_dev(k, nq_total, world, gD, gS, gL, Dall, Lall)
+        return search, Dall, Lall
+
+    def timed_run(search, q_dev, steps, warmup, clocks):
         for _ in range(max(warmup, 3)):
-            search(queries)
+            search(q_dev)
         torch.cuda.synchronize()
         idx.reset_stats()
         evs = [(torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)) for _ in range(steps)]
@@ -487,16 +733,16 @@ def main():
         torch.cuda.synchronize()
         torch.cuda.nvtx.range_push("timed")     # ncu --nvtx --nvtx-include "timed/" profiles exactly this region
         with clocks:
-            for s, e in evs:
+            for s_, e_ in evs:
                 flush.zero_()
-                s.record()
-                search(queries)
-                e.record()
+                s_.record()
+                search(q_dev)
+                e_.record()
             torch.cuda.synchronize()
         torch.cuda.nvtx.range_pop()
         if dist is not None:
             dist.barrier()
-        ms = sum(s.elapsed_time(e) for s, e in evs)
+        ms = sum(s_.elapsed_time(e_) for s_, e_ in evs)
         st = idx.stats()
         if dist is not None:
             t = torch.tensor([ms], device=dev)
@@ -504,44 +750,71 @@ def main():
             ms = float(t.item())
         return ms, st
 
-    search, n_groups, group, lrank = make_layout(list_shards)
-    config["sharding"] = ("none" if world == 1 else
-                          "%d query group(s) x %d list shard(s): lists by centroid range inside a group (NCCL all-gather "
-                          "of work-table records and partial top-k), replicas across groups" % (n_groups, list_shards))
-    config["list_shards"], config["query_groups"] = list_shards, n_groups
-    config["nq_per_step"] = nq * n_groups
     clk = Clocks(local)
-    ms, st = timed_run(search, args.steps, args.warmup, clk)
-    recall = float((L == gt0[:, None]).any(1).float().mean().item())
+    sharded_ok, layouts = None, None
+    if world == 1:
+        idx.set_shard(0, w["nc"])
+        ms, st = timed_run(single_search, queries, args.steps, args.warmup, clk)
+        value = nq * args.steps / (ms / 1e3)
+        scaling = "weak"
+        search = single_search
+        q_timed = queries
+    else:
+        # replicas first (also gives the unsharded answer for the equality check)
+        idx.set_shard(0, w["nc"])
+        ms_rep, _ = timed_run(single_search, queries, args.steps, args.warmup, contextlib.nullcontext())
+        D_ref, L_ref = D.clone(), L.clone()
+        idx.set_shard(*sharding.shard_range(rank, world, w["nc"]))
+        # strong: ONE batch of nq queries over all ranks
+        per = (nq + world - 1) // world
+        nq_s = per * world
+        q_strong = torch.cat([queries, queries[:nq_s - nq]]) if nq_s > nq else queries
+        s_search, s_D, s_L = make_sharded(nq_s, rank * per, (rank + 1) * per)
+        ms_str, _ = timed_run(s_search, q_strong, args.steps, args.warmup, contextlib.nullcontext())
+        sharded_ok = bool(torch.equal(s_L[:nq], L_ref) and torch.equal(s_D[:nq], D_ref))
+        # weak (headline): every rank brings its own nq queries (rank r's batch = the same seeded batch rotated by
+        # r * 997 rows, so that all ranks hold the full tensor without a broadcast in the timed region)
+        q_weak = torch.cat([torch.roll(queries, shifts=-997 * r, dims=0) for r in range(world)])
+        w_search, w_D, w_L = make_sharded(nq * world, rank * nq, (rank + 1) * nq)
+        ms, st = timed_run(w_search, q_weak, args.steps, args.warmup, clk)
+        value = nq * world * args.steps / (ms / 1e3)
+        scaling = "weak"
+        search, q_timed = w_search, q_weak
+        # rank 0's home batch is the un-rotated one: its rows must equal the single-GPU answer too
+        sharded_ok = sharded_ok and bool(torch.equal(w_L[:nq], L_ref) and torch.equal(w_D[:nq], D_ref))
+        D.copy_(w_D[:nq]); L.copy_(w_L[:nq])
+        layouts = {"list_sharded_weak": {"value": value, "ms_per_step": ms / args.steps, "nq_per_step": nq * world},
+                   "list_sharded_strong": {"value": nq * args.steps / (ms_str / 1e3), "ms_per_step": ms_str / args.steps,
+                                           "nq_per_step": nq},
+                   "replicas": {"value": nq * world * args.steps / (ms_rep / 1e3), "ms_per_step": ms_rep / args.steps,
+                                "nq_per_step": nq * world, "note": "every rank searches the whole index alone, no collective"}}
+        config["nq_per_step"] = nq * world
+        config["sharding"] = ("lists sharded over all %d ranks by centroid range; per step every rank prepares its own %d "
+                              "queries, work records and partial top-k are exchanged over NCCL, every rank scans its lists "
+                              "for all %d queries" % (world, nq, nq * world))
+        config["layouts"] = layouts
+        config["sharded_equals_single_gpu"] = sharded_ok
     launches = int(st.kernel_launches)
     scanned = int(st.scanned_codes)
     ms_per_step = ms / args.steps
-    value = nq * n_groups * args.steps / (ms / 1e3)     # every query group serves its own batch of nq queries
 
-    # the list-sharded layout over ALL ranks (north_star's sharding), measured beside the chosen one, and its
-    # answer checked against the unsharded search: same keys (distance, scan order) => bit-identical
-    sharded_ok, list_sharded = None, None
+    # recall@1/10/100 of the benched index (one untimed k=100 search of the first ngt queries)
+    kr = 100
+    Dr = torch.empty(ngt, kr, dtype=torch.float32, device=dev)
+    Lr = torch.empty(ngt, kr, dtype=torch.int64, device=dev)
+    idx.set_shard(0, w["nc"])
+    idx.search_dev(kr, queries[:ngt].contiguous(), Dr, Lr)
+    torch.cuda.synchronize()
+    recall = recalls(Lr)
     if world > 1:
-        search_ls, group_ls = search, group
-        if list_shards != world:
-            search_ls, _, group_ls, _ = make_layout(world)
-        ms_ls, _ = timed_run(search_ls, args.steps, args.warmup, contextlib.nullcontext())
-        Ds, Ls = D.clone(), L.clone()
-        idx.set_shard(0, w["nc"])
-        idx.search_dev(k, queries, D, L)
-        torch.cuda.synchronize()
-        sharded_ok = bool(torch.equal(Ls, L) and torch.equal(Ds, D))
-        list_sharded = {"list_shards": world, "query_groups": 1, "value": nq * args.steps / (ms_ls / 1e3),
-                        "unit": "queries/s", "ms_per_step": ms_ls / args.steps, "nq_per_step": nq, "scaling": "strong"}
-        idx.set_shard(*sharding.shard_range(lrank, list_shards, w["nc"]))
-    world_scan = list_shards            # ranks sharing one query's lists
+        idx.set_shard(*sharding.shard_range(rank, world, w["nc"]))
 
     # per-stage device times (separate pass: the timing mode adds one sync per stage)
     idx.reset_stats()
     idx.set_timing(True)
     for _ in range(3):
         flush.zero_()
-        search(queries)
+        search(q_timed)
     torch.cuda.synchronize()
     st2 = idx.stats()
     idx.set_timing(False)
@@ -550,8 +823,6 @@ def main():
     scan_ms, coarse_ms, prep_ms = st2.scan_ms / n_t, st2.coarse_ms / n_p, st2.prep_ms / n_p
     gemm_ms, g1_ms, lut_ms = st2.gemm_ms / n_p, st2.g1_ms / n_p, st2.lut_ms / n_t
     scan_kernel_ms = scan_ms - lut_ms
-    qb0, qe0, _ = sharding.query_slice(lrank, list_shards, nq)
-    nq_prep = qe0 - qb0                             # queries this rank prepares per step
     code_bytes = w["M"] + 1
     peaks = {}
     try:
@@ -562,29 +833,41 @@ def main():
     tf_peak = float(peaks.get("bf16_tflops_sustained", 1400.0))
     peak_src = "MEASURED_PEAKS.json" if peaks else "fallback of B200_PROFILING.md (6650 GB/s, 1400 TFLOP/s)"
     # code_size + 1 bytes per code of the (sub-)lists the reference rule visits; this rank owns
-    # ~1/list_shards of them.  ("walked" = all codes of the active lists: what a scan without run tiling would read.)
-    scan_bytes = st2.scanned_codes / 3.0 / world_scan * code_bytes
+    # ~1/world of them.  Per LAUNCH: the timing pass ran 3 steps of n_t / 3 scan launches each.
+    # (N > 1: the counter holds the codes of the queries this rank PREPARED, over all shards; by symmetry that is the
+    # number of codes this rank scans for the queries of all ranks)
+    scan_bytes = st2.scanned_codes / float(n_t) * code_bytes
     scan_gbs = scan_bytes / (scan_kernel_ms * 1e-3) / 1e9 if scan_kernel_ms > 0 else 0.0
-    gemm_flop = 2.0 * w["nc"] * w["d"] * nq_prep
+    nq_prep = nq                                   # queries this rank prepares per step
+    gemm_flop = 2.0 * w["nc"] * w["d"] * nq_prep * 3 / n_p
     coarse_tf = gemm_flop / (gemm_ms * 1e-3) / 1e12 if gemm_ms > 0 else 0.0
     # K-G1b: d*4 bytes per DISTINCT neighbour-centroid row gathered
-    g1_bytes = (st2.g1_rows / 3.0) * w["d"] * 4
+    g1_bytes = (st2.g1_rows / float(n_p)) * w["d"] * 4
     g1_gbs = g1_bytes / (g1_ms * 1e-3) / 1e9 if g1_ms > 0 else 0.0
-    stages = {"coarse_ms": coarse_ms, "prep_ms": prep_ms, "scan_ms": scan_ms, "gemm_kernel_ms": gemm_ms,
-              "g1b_kernel_ms": g1_ms, "lut_kernel_ms": lut_ms, "scan_kernel_ms": scan_kernel_ms,
+    nq_step = nq * world if world > 1 else nq
+    stages = {"coarse_ms": coarse_ms * n_p / 3, "prep_ms": prep_ms * n_p / 3, "scan_ms": scan_ms * n_t / 3,
+              "gemm_kernel_ms": gemm_ms * n_p / 3, "g1b_kernel_ms": g1_ms * n_p / 3, "lut_kernel_ms": lut_ms * n_t / 3,
+              "scan_kernel_ms": scan_kernel_ms * n_t / 3, "launches_per_step": {"prep": n_p / 3, "scan": n_t / 3},
               "scan_GBps_algorithmic": scan_gbs, "coarse_TFLOPs_algorithmic": coarse_tf,
               "g1_distinct_rows_per_query": st2.g1_rows / 3.0 / max(1, nq_prep),
-              "scanned_codes_per_query": st2.scanned_codes / 3.0 / nq, "walked_codes_per_query": st2.walked_codes / 3.0 / nq}
-    # per-launch DRAM traffic of each kernel from the committed `ncu --set full` capture (C2, one GPU)
-    traffic = {}
+              "scanned_codes_per_query": st2.scanned_codes / 3.0 / nq_step,
+              "walked_codes_per_query": st2.walked_codes / 3.0 / nq_step}
+    # per-launch DRAM traffic of each kernel: measured by `ncu --set full` on THIS code (profiles/ncu_traffic.py writes
+    # the file with a hash of csrc/); a file captured from other kernel sources is refused
+    traffic, traffic_note = {}, "no capture for this workload"
     try:
-        traffic = json.load(open(os.path.join(ROOT, "profiles", "r01_ncu_traffic.json"))).get(args.workload, {})
+        tj = json.load(open(os.path.join(ROOT, "profiles", "r02_ncu_traffic.json")))
+        if tj.get("csrc_sha1") == csrc_hash():
+            traffic = tj.get(args.workload, {})
+            traffic_note = "ncu --set full capture of these kernel sources (csrc sha1 %s)" % tj.get("csrc_sha1", "")[:12]
+        else:
+            traffic_note = "stale capture refused (taken from other kernel sources)"
     except Exception:
         pass
     rl = {
         "scan_kernel": {"kernel": "scan_kernel (K-S1/K-S2)", "bound": "hbm", "achieved": scan_gbs, "peak": hbm_peak,
                         "unit": "GB/s", "frac": scan_gbs / hbm_peak, "ms": scan_kernel_ms,
-                        "algorithmic": "%d B per code of the sub-lists the reference rule scans" % code_bytes,
+                        "algorithmic": "%d B per code of the sub-lists the reference rule scans, per launch" % code_bytes,
                         "traffic": traffic.get("scan_kernel") if world == 1 else None},
         "group_g1b_kernel": {"kernel": "group_g1b_kernel (K-G1b)", "bound": "hbm", "achieved": g1_gbs, "peak": hbm_peak,
                              "unit": "GB/s", "frac": g1_gbs / hbm_peak, "ms": g1_ms,
@@ -594,16 +877,18 @@ def main():
                              "traffic": traffic.get("group_g1b_kernel") if world == 1 else None},
         "coarse_tc_kernel": {"kernel": "coarse_tc_kernel (K-A2 GEMM)", "bound": "tensor", "achieved": coarse_tf,
                              "peak": tf_peak, "unit": "TFLOP/s", "frac": coarse_tf / tf_peak, "ms": gemm_ms,
-                             "algorithmic": "2*nc*d FLOP per query (the fp16 hi/lo split issues 3x that)",
+                             "algorithmic": "2*nc*d FLOP per query (one nominal pass; the fp16 hi/lo split issues 2x that)",
                              "traffic": traffic.get("coarse_tc_kernel") if world == 1 else None},
     }
-    # headline roofline: the larger (by live-measured time) of the two kernels whose roof is one of the two bound types
-    # of the contract -- the ADC scan (HBM) and the coarse GEMM (tensor).  K-G1b stays under "others": its rows are L2
-    # hits whenever the centroid table fits L2, so its GB/s is not an HBM fraction (it can exceed the HBM peak).
-    dom = max((rl["scan_kernel"], rl["coarse_tc_kernel"]), key=lambda r: r["ms"])
+    # headline roofline: the larger (by live-measured time per step) of the two kernels whose roof is one of the two bound
+    # types of the contract -- the ADC scan (HBM) and the coarse GEMM (tensor).  K-G1b stays under "others": its rows are
+    # L2 hits whenever the centroid table fits L2, so its GB/s is not an HBM fraction (it can exceed the HBM peak).
+    dom = max((rl["scan_kernel"], rl["coarse_tc_kernel"]),
+              key=lambda r_: r_["ms"] * (n_t if r_ is rl["scan_kernel"] else n_p))
     rl["group_g1b_kernel"]["note"] = "rows are L2 hits when the centroid table fits L2: not an HBM fraction"
     roofline = dict(dom)
     roofline["peak_source"] = peak_src
+    roofline["traffic_source"] = traffic_note
     roofline["others"] = {kk: vv for kk, vv in rl.items() if vv is not dom}
 
     # e2e: the C-ABI call with HOST buffers (H2D of the queries + D2H of distances and labels inside)
@@ -621,20 +906,25 @@ def main():
         t1 = time.perf_counter()
         e2e = {"value": nq * args.steps / (t1 - t0), "unit": "queries/s",
                "h2d_bytes_per_step": int(qh.numel() * 4), "d2h_bytes_per_step": int(Dh.numel() * 4 + Lh.numel() * 8)}
-        assert torch.equal(Lh.to(dev), L) or True
+        # the host-buffer path must return exactly what the device-resident path returned
+        e2e["equals_device_path"] = bool(torch.equal(Lh.to(dev), L) and torch.equal(Dh.to(dev), D))
+        if not e2e["equals_device_path"]:
+            log("ERROR: ivfhnsw_b200_search (host buffers) and search_dev disagree")
     else:
-        # multi-GPU e2e: every rank copies its group's queries in, searches (collectives inside a shard group), and
-        # reads the group's answer back
-        qh = queries.cpu().pin_memory()
+        # multi-GPU e2e: every rank copies ITS batch in from pinned host memory, the batches are all-gathered, the
+        # sharded search runs, the rank reads its own rows of the answer back
+        nqt = q_timed.shape[0]
+        qh = q_timed[rank * nq:(rank + 1) * nq].cpu().pin_memory()
         Dh = torch.empty(nq, k, dtype=torch.float32).pin_memory()
         Lh = torch.empty(nq, k, dtype=torch.int64).pin_memory()
-        qd = torch.empty_like(queries)
+        qd = torch.empty_like(q_timed)
 
         def e2e_step():
-            qd.copy_(qh, non_blocking=True)
+            qd[rank * nq:(rank + 1) * nq].copy_(qh, non_blocking=True)
+            dist.all_gather_into_tensor(qd, qd[rank * nq:(rank + 1) * nq])
             search(qd)
-            Dh.copy_(D, non_blocking=True)
-            Lh.copy_(L, non_blocking=True)
+            Dh.copy_(w_D[rank * nq:(rank + 1) * nq], non_blocking=True)
+            Lh.copy_(w_L[rank * nq:(rank + 1) * nq], non_blocking=True)
             torch.cuda.synchronize()
         e2e_step()
         dist.barrier()
@@ -645,37 +935,58 @@ def main():
         t1 = time.perf_counter()
         t = torch.tensor([t1 - t0], device=dev)
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
-        e2e = {"value": nq * n_groups * args.steps / float(t.item()), "unit": "queries/s",
+        e2e = {"value": nqt * args.steps / float(t.item()), "unit": "queries/s",
                "h2d_bytes_per_step": int(qh.numel() * 4) * world,
                "d2h_bytes_per_step": int(Dh.numel() * 4 + Lh.numel() * 8) * world}
 
-    cpu_baseline = None
+    cpu_baseline, parity, ref_recall = None, None, None
     if rank == 0 and world == 1 and not args.no_cpu_baseline:
         try:
-            workdir = tempfile.mkdtemp(prefix="ivfb200_ref_")
-            export_for_reference(idx, w, cent_h, workdir)
-            sample = args.cpu_sample or min(nq, max(ncores * 40, 400))
-            res = run_reference_cpu(w, workdir, queries.cpu().numpy(), gt0.cpu().numpy(), sample, ncores)
+            workdir = reference_workdir(idx, w, cent_h, log)
+            sample = args.cpu_sample or min(ngt, max(ncores * 40, 400))
+            qh_np = queries.cpu().numpy()
+            res = run_reference_cpu(w, workdir, qh_np, gt0.cpu().numpy(), sample, ncores, log=log)
+            ref_recall = res["recall"]
             cpu_baseline = {"value": res["qps"], "unit": "queries/s", "cores": ncores, "kind": "reference",
-                            "sample": "%d queries of the same batch; %d single-thread processes of the compiled reference "
-                                      "(trace-stripped Grouping) over the GPU-built .index; %.0f us/query/thread; "
-                                      "reference recall@10 %.3f" % (sample, ncores, res["us_per_query"], res["recall"])}
+                            "sample": "%d queries of the same batch; %d single-thread processes (forked after one read()) "
+                                      "of the compiled reference (trace-stripped Grouping) over the GPU-built .index, "
+                                      "efSearch %d; %.0f us/query/thread; reference recall@10 %.3f" %
+                                      (sample, ncores, w["efs"], res["us_per_query"], res["recall"]["r10"])}
+            parity = parity_against_reference(idx, w, workdir, qh_np, k, gt0.cpu().numpy())
+            Ls = L[:res["nq"]]          # full GPU path (exact coarse stage) on the reference's sample
+            parity["recall_at_10_same_queries"] = {"ours": float((Ls == gt0[:res["nq"], None]).any(1).float().mean().item()),
+                                                   "reference": res["recall"]["r10"]}
         except Exception as ex:   # the baseline is a reported extra; never lose the GPU line over it
             cpu_baseline = {"value": None, "unit": "queries/s", "cores": ncores, "kind": "reference",
                             "sample": "failed: %r" % (ex,)}
+        if parity is not None and not parity["labels_equal_up_to_ties"]:
+            log("PARITY FAILURE against the reference: %r" % (parity,))
 
     if rank == 0:
-        line = {"metric": "QPS at Recall@10 (k=10)", "value": value, "unit": "queries/s", "n_gpus": world,
+        line = {"metric": "QPS at fixed Recall@10 (k=10)", "value": value, "unit": "queries/s", "n_gpus": world,
                 "steps": args.steps, "warmup": max(args.warmup, 3), "ms_per_step": ms_per_step, "higher_is_better": True,
-                "scaling": "strong" if (world > 1 and n_groups == 1) else "weak", "vs_baseline": None, "dtype": "f32",
-                "data": "synthetic", "config": config, "recall_at_10": recall,
-                "sharded_equals_single_gpu": sharded_ok, "list_sharded": list_sharded, "clocks": clk.summary(), "e2e": e2e, "gpu_launches": launches,
+                "scaling": scaling, "vs_baseline": None, "dtype": "f32",
+                "data": "synthetic", "config": config, "recall_at_10": recall["r10"], "recall": recall,
+                "reference_recall": ref_recall, "recall_queries": ngt, "parity": parity,
+                "clocks": clk.summary(), "e2e": e2e, "gpu_launches": launches,
                 "roofline": roofline, "stages": stages, "cpu_baseline": cpu_baseline,
                 "scanned_codes_per_step": scanned // max(1, args.steps)}
         emit(line)
     if dist is not None:
         dist.destroy_process_group()
     return 0
+
+
+def csrc_hash():
+    """sha1 over the kernel sources: ties profiles/r02_ncu_traffic.json to the code it was captured from."""
+    import hashlib
+    h = hashlib.sha1()
+    cs = os.path.join(ROOT, "ivf-hnsw_b200", "csrc")
+    for f in sorted(os.listdir(cs)):
+        if f.endswith((".cu", ".cuh", ".h", ".cpp")):
+            with open(os.path.join(cs, f), "rb") as fh:
+                h.update(f.encode() + b"\0" + fh.read())
+    return h.hexdigest()
 
 
 if __name__ == "__main__":

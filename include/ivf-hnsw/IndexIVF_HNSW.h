@@ -101,8 +101,6 @@ protected:
     void sync_quantizers();            // re-upload pq / norm_pq / opq_matrix / parameters if they changed
     void pull_quantizers();            // after train_pq: device -> pq / norm_pq / opq_matrix
     void ck(int rc, const char *what) const;   // C-ABI error -> message + exit(1)
-    void write_common(std::ofstream &out, bool grouping);
-    void read_common(std::ifstream &in, bool grouping);
 };
 
 }  // namespace ivfhnsw

@@ -88,6 +88,9 @@ int ivfhnsw_b200_get_pq(ivfhnsw_b200_t *h, float *pq_centroids, float *norm_cent
 /* -- indexing ---------------------------------------------------------------*/
 /* IndexIVF_HNSW::assign (IndexIVF_HNSW.cpp:68-72): exact nearest centroid (k must be 1) */
 int ivfhnsw_b200_assign(ivfhnsw_b200_t *h, size_t n, const float *x, uint32_t *labels, size_t k);
+/* same for device-resident vectors (asynchronous on the handle's stream; base vectors are NOT rotated: the OPQ
+ * rotation applies to residuals, IndexIVF_HNSW.cpp:85-103) */
+int ivfhnsw_b200_assign_dev(ivfhnsw_b200_t *h, size_t n, const float *x_dev, uint32_t *labels_dev);
 /* same, base vectors given as bytes (what readXvecFvec<uint8_t> expands, utils.h:112-127) */
 int ivfhnsw_b200_assign_u8(ivfhnsw_b200_t *h, size_t n, const uint8_t *x, uint32_t *labels);
 /* IndexIVF_HNSW::add_batch (IndexIVF_HNSW.cpp:75-138); precomputed_idx may be NULL (assign first) */
@@ -127,6 +130,12 @@ int ivfhnsw_b200_ntotal(ivfhnsw_b200_t *h, size_t *ntotal);
 int ivfhnsw_b200_export_lists(ivfhnsw_b200_t *h, int64_t *list_off, uint32_t *ids, uint8_t *codes,
                               uint8_t *norm_codes, uint32_t *nn_idx, uint32_t *sub_sizes, float *alphas,
                               float *icd);
+
+/* IndexIVF_HNSW::write / read and IndexIVF_HNSW_Grouping::write / read (IndexIVF_HNSW.cpp:637-663,758-779;
+ * IndexIVF_HNSW_Grouping.cpp:397-483): the reference's own .index file, byte for byte -- the reference reads what
+ * this writes and vice versa.  write finalizes first; read needs a handle created with the file's (d, nc, nsubc). */
+int ivfhnsw_b200_write_index(ivfhnsw_b200_t *h, const char *path);
+int ivfhnsw_b200_read_index(ivfhnsw_b200_t *h, const char *path);
 
 /* -- search -----------------------------------------------------------------*/
 /* coarse stage alone = quantizer->searchKnn(query, nprobe) unloaded nearest-first

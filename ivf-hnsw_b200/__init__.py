@@ -79,6 +79,7 @@ def lib():
         "ivfhnsw_b200_get_pq": ([H, vp, vp, vp], C.c_int),
         "ivfhnsw_b200_assign": ([H, sz, vp, vp, sz], C.c_int),
         "ivfhnsw_b200_assign_u8": ([H, sz, vp, vp], C.c_int),
+        "ivfhnsw_b200_assign_dev": ([H, sz, vp, vp], C.c_int),
         "ivfhnsw_b200_add_batch": ([H, sz, vp, vp, vp], C.c_int),
         "ivfhnsw_b200_add_group": ([H, sz, sz, vp, vp], C.c_int),
         "ivfhnsw_b200_add_points_dev": ([H, sz, vp, vp, vp], C.c_int),
@@ -87,6 +88,8 @@ def lib():
         "ivfhnsw_b200_load_lists": ([H, vp, vp, vp, vp, vp, vp, vp, vp], C.c_int),
         "ivfhnsw_b200_ntotal": ([H, C.POINTER(sz)], C.c_int),
         "ivfhnsw_b200_export_lists": ([H, vp, vp, vp, vp, vp, vp, vp, vp], C.c_int),
+        "ivfhnsw_b200_write_index": ([H, C.c_char_p], C.c_int),
+        "ivfhnsw_b200_read_index": ([H, C.c_char_p], C.c_int),
         "ivfhnsw_b200_coarse": ([H, sz, vp, sz, vp, vp], C.c_int),
         "ivfhnsw_b200_search": ([H, sz, sz, vp, vp, vp], C.c_int),
         "ivfhnsw_b200_search_given_coarse": ([H, sz, sz, vp, vp, vp, vp, vp], C.c_int),
@@ -299,6 +302,11 @@ class IndexIVF_HNSW:
         self._ck(self._L.ivfhnsw_b200_assign(self._h, x.shape[0], x.ctypes.data, labels.ctypes.data, k))
         return labels
 
+    def assign_dev(self, x_dev, labels_dev):
+        """IndexIVF_HNSW::assign for device-resident vectors (torch tensors): labels_dev int32 [n]."""
+        with self._ordered():
+            self._ck(self._L.ivfhnsw_b200_assign_dev(self._h, x_dev.shape[0], _ptr(x_dev), _ptr(labels_dev)))
+
     def add_batch(self, x, xids, precomputed_idx=None):
         self._push_params()
         x = _np(x, np.float32).reshape(-1, self.d)
@@ -395,75 +403,14 @@ class IndexIVF_HNSW:
 
     def write(self, path):
         """Byte-compatible with IndexIVF_HNSW::write / IndexIVF_HNSW_Grouping::write
-        (IndexIVF_HNSW.cpp:637-663, IndexIVF_HNSW_Grouping.cpp:397-438)."""
-        ix = self.export_index_dict()
-        off = ix["list_off"]
-
-        def wv(f, a):
-            f.write(struct.pack("<I", a.size)); f.write(a.tobytes())
-
-        with open(path, "wb") as f:
-            f.write(struct.pack("<QQ", self.d, self.nc))
-            if self.nsubc:
-                f.write(struct.pack("<Q", self.nsubc))
-            for c in range(self.nc):
-                wv(f, ix["ids"][off[c]:off[c + 1]])
-            for c in range(self.nc):
-                wv(f, ix["codes"][off[c]:off[c + 1]].ravel())
-            for c in range(self.nc):
-                wv(f, ix["norm_codes"][off[c]:off[c + 1]])
-            if self.nsubc:
-                for c in range(self.nc):
-                    wv(f, ix["nn_idx"][c])
-                for c in range(self.nc):
-                    # the reference leaves subgroup_sizes empty for groups that never received points
-                    wv(f, ix["sub_sizes"][c] if off[c + 1] > off[c] else np.zeros(0, np.uint32))
-                wv(f, ix["alphas"])
-            wv(f, ix["centroid_norms"])
-            if self.nsubc:
-                for c in range(self.nc):
-                    wv(f, ix["icd"][c])
+        (IndexIVF_HNSW.cpp:637-663, IndexIVF_HNSW_Grouping.cpp:397-438); native (ivfhnsw_b200_write_index)."""
+        self._push_params()
+        self._ck(self._L.ivfhnsw_b200_write_index(self._h, os.fsencode(path)))
 
     def read(self, path):
         """IndexIVF_HNSW::read / IndexIVF_HNSW_Grouping::read (IndexIVF_HNSW.cpp:758-779, ...Grouping.cpp:445-483)."""
-        with open(path, "rb") as f:
-            buf = f.read()
-        pos = [0]
-
-        def rd(fmt):
-            v = struct.unpack_from(fmt, buf, pos[0]); pos[0] += struct.calcsize(fmt); return v
-
-        def rv(dt):
-            (n,) = rd("<I")
-            a = np.frombuffer(buf, dtype=dt, count=n, offset=pos[0]); pos[0] += n * np.dtype(dt).itemsize
-            return a
-
-        d, nc = rd("<QQ")
-        if (d, nc) != (self.d, self.nc):
-            raise B200Error("index file is for d=%d nc=%d" % (d, nc))
-        if self.nsubc:
-            (ns,) = rd("<Q")
-            if ns != self.nsubc:
-                raise B200Error("index file has nsubc=%d" % ns)
-        ids = [rv(np.uint32) for _ in range(nc)]
-        codes = [rv(np.uint8) for _ in range(nc)]
-        ncodes = [rv(np.uint8) for _ in range(nc)]
-        sizes = np.array([a.size for a in ids], np.int64)
-        off = np.zeros(nc + 1, np.int64); np.cumsum(sizes, out=off[1:])
-        ix = dict(list_off=off, ids=np.concatenate(ids) if nc else ids, codes=np.concatenate(codes).reshape(-1, self.code_size),
-                  norm_codes=np.concatenate(ncodes))
-        if self.nsubc:
-            nn = np.stack([rv(np.uint32) for _ in range(nc)])
-            ss = np.zeros((nc, self.nsubc), np.uint32)
-            for c in range(nc):
-                a = rv(np.uint32)
-                if a.size:
-                    ss[c] = a
-            ix.update(nn_idx=nn, sub_sizes=ss, alphas=rv(np.float32))
-        ix["centroid_norms"] = rv(np.float32)
-        if self.nsubc:
-            ix["icd"] = np.stack([rv(np.float32) for _ in range(nc)])
-        self.load_index_dict(ix)
+        self._push_params()
+        self._ck(self._L.ivfhnsw_b200_read_index(self._h, os.fsencode(path)))
 
     # -- search
     def coarse(self, x, nprobe=None):

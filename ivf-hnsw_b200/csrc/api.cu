@@ -472,6 +472,13 @@ int ivfb200_assign_dev(ivfhnsw_b200_t *h, size_t n, const float *x_dev, uint32_t
     return ivfb200_coarse_dev(h, n, x_dev, 1, 0, h->w_cd.as<float>(), labels_dev);
 }
 
+int ivfhnsw_b200_assign_dev(ivfhnsw_b200_t *h, size_t n, const float *x_dev, uint32_t *labels_dev)
+{
+    if (bind(h)) return IVFHNSW_B200_ECUDA;
+    if (n == 0) return 0;
+    return ivfb200_assign_dev(h, n, x_dev, labels_dev);
+}
+
 int ivfhnsw_b200_assign(ivfhnsw_b200_t *h, size_t n, const float *x, uint32_t *labels, size_t k)
 {
     if (bind(h)) return IVFHNSW_B200_ECUDA;
@@ -884,14 +891,14 @@ static int finalize_grouping(ivfhnsw_b200_t *h)
 {
     if (int r = ivfb200_ensure_group_meta(h)) return r;   // nn lists / icd exist even for an empty index
     if (int r = flush_groups_locked(h)) return r;
-    CU(h->st_sub.ensure(1));
-    if (int r = build_csr(h)) return r;
-    h->st_x.release();  // raw vectors are not needed any more
+    h->st_x.release();  // raw vectors are not needed any more (and the CSR build wants the memory)
     h->rs_list.release();
     h->rs_ids.release();
     h->grp_seen.release();
     h->grp_seen_valid = false;
-    return 0;
+    h->w_f.release();
+    CU(h->st_sub.ensure(1));
+    return build_csr(h);
 }
 
 int ivfhnsw_b200_finalize(ivfhnsw_b200_t *h)
@@ -903,6 +910,11 @@ int ivfhnsw_b200_finalize(ivfhnsw_b200_t *h)
     int r = h->nsubc ? finalize_grouping(h) : build_csr(h);
     if (r) return r;
     h->st_dirty = false;
+    // the staged records now live in the CSR: give the staging and sort buffers back (26 + 16 GB at 1B vectors);
+    // a later add_batch re-stages from the lists (unstage_existing_lists)
+    DevBuf *tmp[] = {&h->st_list, &h->st_ids, &h->st_codes, &h->st_norm, &h->st_sub, &h->w_d2, &h->w_cub};
+    for (DevBuf *b : tmp) b->release();
+    h->st_n = 0;
     return 0;
 }
 
@@ -945,6 +957,9 @@ int ivfhnsw_b200_load_lists(ivfhnsw_b200_t *h, const int64_t *list_off, const ui
     h->st_n = n;
     if (int r = build_csr(h)) return r;
     h->st_dirty = false;
+    DevBuf *tmp[] = {&h->st_list, &h->st_ids, &h->st_codes, &h->st_norm, &h->st_sub, &h->w_d2, &h->w_cub};
+    for (DevBuf *b : tmp) b->release();
+    h->st_n = 0;
     return 0;
 }
 

@@ -417,122 +417,18 @@ void IndexIVF_HNSW::sync_host_lists()
     }
 }
 
-// File layout (reference IndexIVF_HNSW.cpp:637-663,758-779; Grouping.cpp:397-483), all vectors as
-// [uint32 count][elements]:  size_t d, nc, (nsubc); ids[nc]; codes[nc]; norm_codes[nc];
-// (nn_centroid_idxs[nc]; subgroup_sizes[nc]; alphas); centroid_norms; (inter_centroid_dists[nc])
-void IndexIVF_HNSW::write_common(std::ofstream &out, bool grouping)
-{
-    ck(ivfhnsw_b200_finalize(h_), "finalize");
-    size_t n = 0;
-    ck(ivfhnsw_b200_ntotal(h_, &n), "ntotal");
-    HostLists L;
-    L.off.resize(nc + 1);
-    L.ids.resize(std::max<size_t>(n, 1));
-    L.codes.resize(std::max<size_t>(n, 1) * code_size);
-    L.ncodes.resize(std::max<size_t>(n, 1));
-    if (grouping) { L.nn.resize(nc * nsubc_); L.ss.resize(nc * nsubc_); L.alphas.resize(nc); L.icd.resize(nc * nsubc_); }
-    ck(ivfhnsw_b200_export_lists(h_, L.off.data(), L.ids.data(), L.codes.data(), L.ncodes.data(),
-                                 grouping ? L.nn.data() : nullptr, grouping ? L.ss.data() : nullptr,
-                                 grouping ? L.alphas.data() : nullptr, grouping ? L.icd.data() : nullptr),
-       "export_lists");
-    auto put_vec = [&](const void *p, size_t count, size_t elem) {
-        const uint32_t c32 = (uint32_t)count;
-        out.write(reinterpret_cast<const char *>(&c32), 4);
-        if (count) out.write(reinterpret_cast<const char *>(p), (std::streamsize)(count * elem));
-    };
-    write_variable(out, d);
-    write_variable(out, nc);
-    if (grouping) write_variable(out, nsubc_);
-    for (size_t c = 0; c < nc; c++) put_vec(L.ids.data() + L.off[c], (size_t)(L.off[c + 1] - L.off[c]), 4);
-    for (size_t c = 0; c < nc; c++)
-        put_vec(L.codes.data() + (size_t)L.off[c] * code_size, (size_t)(L.off[c + 1] - L.off[c]) * code_size, 1);
-    for (size_t c = 0; c < nc; c++) put_vec(L.ncodes.data() + L.off[c], (size_t)(L.off[c + 1] - L.off[c]), 1);
-    if (grouping) {
-        for (size_t c = 0; c < nc; c++) put_vec(L.nn.data() + c * nsubc_, nsubc_, 4);
-        // the reference leaves subgroup_sizes empty for groups that never received points
-        for (size_t c = 0; c < nc; c++) put_vec(L.ss.data() + c * nsubc_, L.off[c + 1] > L.off[c] ? nsubc_ : 0, 4);
-        put_vec(L.alphas.data(), nc, 4);
-    }
-    std::vector<float> &cn = get_centroid_norms();
-    put_vec(cn.data(), nc, 4);
-    if (grouping)
-        for (size_t c = 0; c < nc; c++) put_vec(L.icd.data() + c * nsubc_, nsubc_, 4);
-}
-
-void IndexIVF_HNSW::read_common(std::ifstream &in, bool grouping)
-{
-    size_t fd = 0, fnc = 0, fns = 0;
-    read_variable(in, fd);
-    read_variable(in, fnc);
-    if (grouping) read_variable(in, fns);
-    if (fd != d || fnc != nc || (grouping && fns != nsubc_)) {
-        fprintf(stderr, "ivfhnsw_b200: index file is for d=%zu nc=%zu nsubc=%zu\n", fd, fnc, fns);
-        exit(1);
-    }
-    HostLists L;
-    L.off.assign(nc + 1, 0);
-    std::vector<uint32_t> v32;
-    std::vector<uint8_t> v8;
-    std::vector<float> vf;
-    for (size_t c = 0; c < nc; c++) {
-        read_vector(in, v32);
-        L.off[c + 1] = L.off[c] + (int64_t)v32.size();
-        L.ids.insert(L.ids.end(), v32.begin(), v32.end());
-    }
-    for (size_t c = 0; c < nc; c++) {
-        read_vector(in, v8);
-        L.codes.insert(L.codes.end(), v8.begin(), v8.end());
-    }
-    for (size_t c = 0; c < nc; c++) {
-        read_vector(in, v8);
-        L.ncodes.insert(L.ncodes.end(), v8.begin(), v8.end());
-    }
-    if (grouping) {
-        L.nn.assign(nc * nsubc_, 0);
-        L.ss.assign(nc * nsubc_, 0);
-        for (size_t c = 0; c < nc; c++) {
-            read_vector(in, v32);
-            std::copy(v32.begin(), v32.begin() + std::min(v32.size(), nsubc_), L.nn.begin() + c * nsubc_);
-        }
-        for (size_t c = 0; c < nc; c++) {
-            read_vector(in, v32);
-            std::copy(v32.begin(), v32.begin() + std::min(v32.size(), nsubc_), L.ss.begin() + c * nsubc_);
-        }
-        read_vector(in, L.alphas);
-    }
-    read_vector(in, vf);   // centroid norms
-    if (grouping) {
-        L.icd.assign(nc * nsubc_, 0.f);
-        std::vector<float> row;
-        for (size_t c = 0; c < nc; c++) {
-            read_vector(in, row);
-            std::copy(row.begin(), row.begin() + std::min(row.size(), nsubc_), L.icd.begin() + c * nsubc_);
-        }
-    }
-    if (L.ids.empty()) { L.ids.resize(1); L.codes.resize(code_size); L.ncodes.resize(1); }
-    sync_quantizers();
-    ck(ivfhnsw_b200_load_lists(h_, L.off.data(), L.ids.data(), L.codes.data(), L.ncodes.data(),
-                               grouping ? L.nn.data() : nullptr, grouping ? L.ss.data() : nullptr,
-                               grouping ? L.alphas.data() : nullptr, grouping ? L.icd.data() : nullptr),
-       "load_lists");
-    if (vf.size() == nc) ck(ivfhnsw_b200_set_centroid_norms(h_, vf.data()), "set_centroid_norms");
-}
-
+// File layout (reference IndexIVF_HNSW.cpp:637-663,758-779; Grouping.cpp:397-483): written / read natively by the
+// C ABI (ivfhnsw_b200_write_index / ivfhnsw_b200_read_index, csrc/io.cu) straight from / into the device lists.
 void IndexIVF_HNSW::write(const char *path_index)
 {
-    std::ofstream out(path_index, std::ios::binary);
-    write_common(out, false);
+    ck(ivfhnsw_b200_write_index(h_, path_index), "write");
 }
 void IndexIVF_HNSW::write(const char *path_index, bool) { write(path_index); }
 
 void IndexIVF_HNSW::read(const char *path)
 {
-    std::ifstream in(path, std::ios::binary);
-    if (!in) {
-        fprintf(stderr, "ivfhnsw_b200: cannot open index file %s\n", path);
-        exit(1);
-    }
-    read_common(in, false);
+    sync_quantizers();
+    ck(ivfhnsw_b200_read_index(h_, path), "read");
 }
 
 // ------------------------------------------------------------------------------------------ Grouping
@@ -574,20 +470,15 @@ void IndexIVF_HNSW_Grouping::compute_inter_centroid_dists()
 
 void IndexIVF_HNSW_Grouping::write(const char *path_index)
 {
-    std::ofstream out(path_index, std::ios::binary);
-    write_common(out, true);
+    ck(ivfhnsw_b200_write_index(h_, path_index), "write");
 }
 void IndexIVF_HNSW_Grouping::write(const char *path_index, bool) { write(path_index); }
 
 void IndexIVF_HNSW_Grouping::read(const char *path_index)
 {
-    std::ifstream in(path_index, std::ios::binary);
-    if (!in) {
-        fprintf(stderr, "ivfhnsw_b200: cannot open index file %s\n", path_index);
-        exit(1);
-    }
     pruning_flag_ = do_pruning;
-    read_common(in, true);
+    sync_quantizers();
+    ck(ivfhnsw_b200_read_index(h_, path_index), "read");
 }
 
 void IndexIVF_HNSW_Grouping::sync_host_lists()

@@ -23,7 +23,10 @@ def test_workloads_are_well_formed():
         assert w["nprobe"] * max(w["nsubc"], 1) + w["nprobe"] < 65536, name      # uint16 row indices of K-G1
         assert w["nlearn"] >= w["nc"] and w["ntrain"] <= w["nlearn"], name
         assert w["nq"] <= w["nb"], name
-    # the default is configs[1]; the SIFT1B-shape configuration is covered from both sides
+    # the default is the configuration the metric is quoted on (configs[3], SIFT1B-shape, 1B x 128, 2^20 centroids)
+    c4 = bench.WORKLOADS[bench.DEFAULT_WORKLOAD]
+    assert (c4["nb"], c4["nc"], c4["M"], c4["nsubc"], c4["nprobe"], c4["max_codes"], c4["k"]) == \
+        (10 ** 9, 1 << 20, 16, 64, 128, 100000, 10) and c4["opq"] and c4["pruning"]
     assert bench.WORKLOADS["c2"]["nc"] == 65536 and bench.WORKLOADS["c2"]["nsubc"] == 64
     assert bench.WORKLOADS["c4s"]["nprobe"] == bench.WORKLOADS["c4n"]["nprobe"] == 128
     assert bench.WORKLOADS["c4n"]["nc"] == 1 << 20 and bench.WORKLOADS["c3"]["nc"] == 1 << 20
@@ -32,3 +35,11 @@ def test_workloads_are_well_formed():
 def test_kmeans_helper_imports_without_a_gpu():
     kmeans = importlib.import_module("ivf-hnsw_b200.kmeans")
     assert callable(kmeans.lloyd_centroids)
+
+
+def test_cache_key_depends_on_workload_and_is_stable():
+    sys.path.insert(0, ROOT)
+    bench = importlib.import_module("bench")
+    a = bench.cache_key(bench.WORKLOADS["c4"])
+    assert a == bench.cache_key(dict(bench.WORKLOADS["c4"])) and a != bench.cache_key(bench.WORKLOADS["c4s"])
+    assert len(bench.csrc_hash()) == 40
