@@ -27,6 +27,7 @@
 #include <faiss/utils.h>
 #include <hnswlib/hnswalg.h>
 
+#include "orcv.h"
 #include "utils.h"
 
 struct ivfhnsw_b200;   // opaque C-ABI handle (include/ivfhnsw_b200.h)
@@ -53,7 +54,16 @@ struct IndexIVF_HNSW {
     std::vector<std::vector<uint8_t> > codes;
     std::vector<std::vector<uint8_t> > norm_codes;
 
+    // information associated with the hdr.vec file of write2 (reference IndexIVF_HNSW.h:68-69)
+    orcvhdr_t hdr_idx;
+
     std::vector<float> &get_centroid_norms();
+
+    // probes of the last search() call, FARTHEST first like the reference's TRACE_CENTROIDS vectors
+    // (IndexIVF_HNSW.h:73-77, IndexIVF_HNSW.cpp:249-256); filled on demand by trace_centroids()
+    std::vector<float> trace_query_centroid_dists;
+    std::vector<idx_t> trace_centroid_idxs;
+    void trace_centroids(size_t idx_q, bool missed);
 
 public:
     explicit IndexIVF_HNSW(size_t dim, size_t ncentroids, size_t bytes_per_code, size_t nbits_per_idx,
@@ -74,7 +84,12 @@ public:
     void search2(size_t k, const float *x, float *distances, long *labels, float *query_centroid_dists,
                  idx_t *centroid_idxs);
 
-    // ---- fork extras kept so that the orca / enn mains link (thin wrappers, not accelerated paths)
+    // ---- fork extras so that the orca / disk / vector_add / mkindex mains compile and link (thin host wrappers over the
+    // same C ABI; reference IndexIVF_HNSW.h:151,167)
+    // add_batch + the batch's records [uint64 eid][code_size bytes][norm code] packed into obuf (IndexIVF_HNSW.cpp:140-204)
+    virtual void add_batch2(size_t n, const float *x, const idx_t *xids, const idx_t *idx, uint64_t *eids, char *obuf);
+    // ORCV directory: hdr.vec, cnorms.vec, pq.vec, normpq.vec, (opq.vec), edge.vec (IndexIVF_HNSW.cpp:672-755)
+    virtual void write2(const char *home_dir, size_t n_vecs, bool do_opq, const char *path_edge);
     virtual void search_debug(size_t k, const float *x, float *distances, long *labels) { search(k, x, distances, labels); }
     virtual idx_t search_enn(const float *x, float *distances, long *labels);
 
@@ -87,6 +102,11 @@ public:
     ivfhnsw_b200 *handle() { return h_; }
 
 protected:
+    int copy_file(const char *file_src, const char *file_dst);
+    size_t M;                 // HNSW edges per point as passed to build_quantizer
+    float dmatch = 4444.0;    // reference IndexIVF_HNSW.h:90-91
+    float dnear = 8888.0;
+    std::vector<float> last_query_;   // copy of the last search() query (for trace_centroids)
     std::vector<float> centroid_norms;
     ivfhnsw_b200 *h_;
     size_t nsubc_;

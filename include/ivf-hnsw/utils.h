@@ -5,6 +5,7 @@
 #pragma once
 #include <sys/stat.h>
 
+#include <cassert>
 #include <chrono>
 #include <cstdint>
 #include <cstdio>
@@ -94,11 +95,22 @@ inline bool exists(const char *path)
     return path && stat(path, &st) == 0;
 }
 
+enum vec_t { base_vec = 0, centroid_vec = 1 };   // which file getL2Distance reads (reference utils.h:134-137)
+
 typedef struct SearchInfo {
-    long label;
     float distance;
+    long label;
 } SearchInfo_t;
-inline bool cmp(SearchInfo_t a, SearchInfo_t b) { return a.distance < b.distance; }
+// ascending distance; distances within 0.001 of each other are ordered by label (reference utils.cpp:192-202)
+bool cmp(SearchInfo_t a, SearchInfo_t b);
+// distance between the query and record vec_id of a .bvecs base file / .fvecs centroid file (utils.cpp:98-137)
+float getL2Distance(const float *query, const char *path_vec, const size_t dim, const long vec_id, vec_t type_v);
+// records of a .bvecs file of dimension vec_dim (0 when it does not exist; utils.cpp:204-219)
+size_t base_vec_num(const char *path_base, size_t vec_dim);
+// sorted names of the files of path_dir that end in file_ext; every name must start with file_prefix (utils.cpp:221-272)
+void get_files(const char *path_dir, const char *file_ext, std::vector<std::string> &file_list);
+void check_files(const char *file_prefix, std::vector<std::string> &file_list);
+void get_index_name(const char *path_idx, size_t idx, char *idx_name);   // "<path>_%02lu.index"
 
 // first sub_nx rows of a seed-1234 faiss::rand_perm of the nx input rows (reference utils.cpp:12-19)
 void random_subset(const float *x, float *x_out, size_t d, size_t nx, size_t sub_nx);

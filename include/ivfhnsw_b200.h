@@ -96,6 +96,10 @@ int ivfhnsw_b200_assign_u8(ivfhnsw_b200_t *h, size_t n, const uint8_t *x, uint32
 /* IndexIVF_HNSW::add_batch (IndexIVF_HNSW.cpp:75-138); precomputed_idx may be NULL (assign first) */
 int ivfhnsw_b200_add_batch(ivfhnsw_b200_t *h, size_t n, const float *x, const uint32_t *xids,
                            const uint32_t *precomputed_idx);
+/* IndexIVF_HNSW::add_batch2 (IndexIVF_HNSW.cpp:140-204): add_batch that also hands the residual codes and norm codes
+ * of the batch back (the caller packs them into its ORCV output buffer); codes_out [n][code_size], norm_codes_out [n] */
+int ivfhnsw_b200_add_batch_codes(ivfhnsw_b200_t *h, size_t n, const float *x, const uint32_t *xids,
+                                 const uint32_t *idx, uint8_t *codes_out, uint8_t *norm_codes_out);
 /* IndexIVF_HNSW_Grouping::add_group (IndexIVF_HNSW_Grouping.cpp:43-157); thread-safe per distinct group.
  * STREAMED like the reference's bounded pass (tests/test_ivfhnsw_grouping_sift1b.cpp:138-201): one call delivers a
  * complete group, the raw vectors are staged in HBM and -- as soon as "stage_bytes" of them wait (set_option,
@@ -127,6 +131,8 @@ int ivfhnsw_b200_load_lists(ivfhnsw_b200_t *h, const int64_t *list_off, const ui
                             const uint8_t *codes, const uint8_t *norm_codes, const uint32_t *nn_idx,
                             const uint32_t *sub_sizes, const float *alphas, const float *icd);
 int ivfhnsw_b200_ntotal(ivfhnsw_b200_t *h, size_t *ntotal);
+/* ids[c].size() of every list (what the reference's tracing prints, IndexIVF_HNSW.cpp:298-326); sizes [nc] */
+int ivfhnsw_b200_list_sizes(ivfhnsw_b200_t *h, uint32_t *sizes);
 int ivfhnsw_b200_export_lists(ivfhnsw_b200_t *h, int64_t *list_off, uint32_t *ids, uint8_t *codes,
                               uint8_t *norm_codes, uint32_t *nn_idx, uint32_t *sub_sizes, float *alphas,
                               float *icd);
@@ -194,6 +200,12 @@ int ivfhnsw_b200_prepare_dev(ivfhnsw_b200_t *h, size_t nq, const float *x_dev, s
                              void *tables_dev);
 int ivfhnsw_b200_scan_tables_dev(ivfhnsw_b200_t *h, size_t nq, size_t k, const float *x_dev, const void *tables_dev,
                                  float *part_d_dev, uint32_t *part_seq_dev, int64_t *part_labels_dev);
+/* The re-rank half of IndexIVF_HNSW_Grouping::searchDisk (IndexIVF_HNSW_Grouping.cpp:365-395; getL2Distance +
+ * fvec_L2sqr, utils.cpp:22-51,98-137): exact distances of ncand candidate RAW vectors per query (cand [nq][ncand][d]
+ * floats as readXvecFvec<uint8_t> delivers them, cand_labels [nq][ncand], < 0 = padding), the k best per query
+ * ascending by (distance, label).  Host pointers. */
+int ivfhnsw_b200_rerank(ivfhnsw_b200_t *h, size_t nq, size_t ncand, size_t k, const float *queries, const float *cand,
+                        const int64_t *cand_labels, float *distances, int64_t *labels);
 int ivfhnsw_b200_sync(ivfhnsw_b200_t *h);
 /* run on a caller-owned CUDA stream (cudaStream_t, e.g. torch's current stream); NULL = back to a private one.
  * STREAM ORDERING: every *_dev entry point only ENQUEUES work on the handle's stream.  Device buffers

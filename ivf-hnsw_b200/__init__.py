@@ -81,12 +81,15 @@ def lib():
         "ivfhnsw_b200_assign_u8": ([H, sz, vp, vp], C.c_int),
         "ivfhnsw_b200_assign_dev": ([H, sz, vp, vp], C.c_int),
         "ivfhnsw_b200_add_batch": ([H, sz, vp, vp, vp], C.c_int),
+        "ivfhnsw_b200_add_batch_codes": ([H, sz, vp, vp, vp, vp, vp], C.c_int),
+        "ivfhnsw_b200_rerank": ([H, sz, sz, sz, vp, vp, vp, vp, vp], C.c_int),
         "ivfhnsw_b200_add_group": ([H, sz, sz, vp, vp], C.c_int),
         "ivfhnsw_b200_add_points_dev": ([H, sz, vp, vp, vp], C.c_int),
         "ivfhnsw_b200_finalize": ([H], C.c_int),
         "ivfhnsw_b200_flush_groups": ([H], C.c_int),
         "ivfhnsw_b200_load_lists": ([H, vp, vp, vp, vp, vp, vp, vp, vp], C.c_int),
         "ivfhnsw_b200_ntotal": ([H, C.POINTER(sz)], C.c_int),
+        "ivfhnsw_b200_list_sizes": ([H, vp], C.c_int),
         "ivfhnsw_b200_export_lists": ([H, vp, vp, vp, vp, vp, vp, vp, vp], C.c_int),
         "ivfhnsw_b200_write_index": ([H, C.c_char_p], C.c_int),
         "ivfhnsw_b200_read_index": ([H, C.c_char_p], C.c_int),
@@ -468,6 +471,30 @@ class IndexIVF_HNSW:
         with self._ordered():
             self._ck(self._L.ivfhnsw_b200_coarse_noalloc_dev(self._h, xq_dev.shape[0], _ptr(xq_dev), nprobe,
                                                              _ptr(d_dev), _ptr(i_dev), _ptr(flags_dev)))
+
+    def rerank(self, k, x, cand, cand_labels):
+        """The re-rank half of searchDisk (IndexIVF_HNSW_Grouping.cpp:365-395): exact fvec_L2sqr distances of the
+        candidates' raw vectors cand [nq][ncand][d], k best per query ascending by (distance, label)."""
+        x = _np(x, np.float32).reshape(-1, self.d)
+        cand = _np(cand, np.float32)
+        lab = _np(cand_labels, np.int64)
+        nq, ncand = lab.shape
+        D = np.zeros((nq, k), np.float32)
+        L = np.zeros((nq, k), np.int64)
+        self._ck(self._L.ivfhnsw_b200_rerank(self._h, nq, ncand, k, x.ctypes.data, cand.ctypes.data, lab.ctypes.data,
+                                             D.ctypes.data, L.ctypes.data))
+        return D, L
+
+    def add_batch2(self, x, xids, precomputed_idx):
+        """add_batch that also returns (codes, norm_codes) of the batch, what IndexIVF_HNSW::add_batch2 packs into obuf."""
+        self._push_params()
+        x = _np(x, np.float32).reshape(-1, self.d)
+        xids, idx = _np(xids, np.uint32), _np(precomputed_idx, np.uint32)
+        codes = np.zeros((x.shape[0], self.code_size), np.uint8)
+        ncodes = np.zeros(x.shape[0], np.uint8)
+        self._ck(self._L.ivfhnsw_b200_add_batch_codes(self._h, x.shape[0], x.ctypes.data, xids.ctypes.data, idx.ctypes.data,
+                                                      codes.ctypes.data, ncodes.ctypes.data))
+        return codes, ncodes
 
     def search_host_buffers(self, k, x_host, D_host, L_host):
         """The C-ABI call with caller-owned HOST buffers (numpy or pinned torch): H2D + search + D2H."""

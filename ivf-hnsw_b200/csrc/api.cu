@@ -587,7 +587,21 @@ static int flush_groups_locked(ivfhnsw_b200_t *h);
 
 static int unstage_existing_lists(ivfhnsw_b200_t *h);
 
+static int add_batch_impl(ivfhnsw_b200_t *h, size_t n, const float *x, const uint32_t *xids, const uint32_t *idx,
+                          uint8_t *codes_out, uint8_t *norm_out);
+
 int ivfhnsw_b200_add_batch(ivfhnsw_b200_t *h, size_t n, const float *x, const uint32_t *xids, const uint32_t *idx)
+{
+    return add_batch_impl(h, n, x, xids, idx, nullptr, nullptr);
+}
+int ivfhnsw_b200_add_batch_codes(ivfhnsw_b200_t *h, size_t n, const float *x, const uint32_t *xids, const uint32_t *idx,
+                                 uint8_t *codes_out, uint8_t *norm_codes_out)
+{
+    return add_batch_impl(h, n, x, xids, idx, codes_out, norm_codes_out);
+}
+
+static int add_batch_impl(ivfhnsw_b200_t *h, size_t n, const float *x, const uint32_t *xids, const uint32_t *idx,
+                          uint8_t *codes_out, uint8_t *norm_out)
 {
     std::lock_guard<std::mutex> lk(h->mu);
     if (bind(h)) return IVFHNSW_B200_ECUDA;
@@ -613,6 +627,11 @@ int ivfhnsw_b200_add_batch(ivfhnsw_b200_t *h, size_t n, const float *x, const ui
         if (int r = ivfb200_encode_dev(h, nb, h->w_x.as<float>(), dl, nullptr, nullptr, h->st_codes.as<uint8_t>() + h->st_n * h->M,
                                h->st_norm.as<uint8_t>() + h->st_n, nullptr, nullptr))
             return r;
+        if (codes_out)
+            CU(cudaMemcpyAsync(codes_out + i0 * h->M, h->st_codes.as<uint8_t>() + h->st_n * h->M, nb * h->M,
+                               cudaMemcpyDeviceToHost, h->stream));
+        if (norm_out)
+            CU(cudaMemcpyAsync(norm_out + i0, h->st_norm.as<uint8_t>() + h->st_n, nb, cudaMemcpyDeviceToHost, h->stream));
         CU(cudaStreamSynchronize(h->stream));
         h->st_n += nb;
     }
@@ -963,6 +982,16 @@ int ivfhnsw_b200_load_lists(ivfhnsw_b200_t *h, const int64_t *list_off, const ui
     return 0;
 }
 
+int ivfhnsw_b200_list_sizes(ivfhnsw_b200_t *h, uint32_t *sizes)
+{
+    if (int r = ivfhnsw_b200_finalize(h)) return r;
+    if (bind(h)) return IVFHNSW_B200_ECUDA;
+    if (!h->have_lists) return h->fail(IVFHNSW_B200_ESTATE, "no lists");
+    CU(cudaMemcpyAsync(sizes, h->list_size.p, h->nc * 4, cudaMemcpyDeviceToHost, h->stream));
+    CU(cudaStreamSynchronize(h->stream));
+    return 0;
+}
+
 int ivfhnsw_b200_ntotal(ivfhnsw_b200_t *h, size_t *ntotal)
 {
     *ntotal = h->st_dirty ? h->st_n + h->rs_n : h->ntotal;
@@ -1295,6 +1324,30 @@ int ivfhnsw_b200_search_given_coarse(ivfhnsw_b200_t *h, size_t nq, size_t k, con
 {
     if (!cd || !ci) return h->fail(IVFHNSW_B200_EINVAL, "coarse candidates missing");
     return search_host(h, nq, k, x, cd, ci, distances, labels);
+}
+
+int ivfhnsw_b200_rerank(ivfhnsw_b200_t *h, size_t nq, size_t ncand, size_t k, const float *queries, const float *cand,
+                        const int64_t *cand_labels, float *distances, int64_t *labels)
+{
+    if (bind(h)) return IVFHNSW_B200_ECUDA;
+    if (nq == 0) return 0;
+    if (k == 0 || k > ncand || ncand > 8192) return h->fail(IVFHNSW_B200_EINVAL, "rerank: need 1 <= k <= ncand <= 8192");
+    cudaStream_t st = h->stream;
+    const size_t d = h->d;
+    CU(h->w_x.ensure(nq * d * 4));
+    CU(h->w_a.ensure(nq * ncand * d * 4));
+    CU(h->w_e.ensure(nq * ncand * 8));
+    CU(h->w_out_d.ensure(nq * k * 4));
+    CU(h->w_out_l.ensure(nq * k * 8));
+    CU(cudaMemcpyAsync(h->w_x.p, queries, nq * d * 4, cudaMemcpyHostToDevice, st));
+    CU(cudaMemcpyAsync(h->w_a.p, cand, nq * ncand * d * 4, cudaMemcpyHostToDevice, st));
+    CU(cudaMemcpyAsync(h->w_e.p, cand_labels, nq * ncand * 8, cudaMemcpyHostToDevice, st));
+    CU(launch_rerank(st, LAUNCHES, (int)nq, (int)ncand, (int)k, (int)d, h->w_x.as<float>(), h->w_a.as<float>(),
+                     h->w_e.as<int64_t>(), h->w_out_d.as<float>(), h->w_out_l.as<int64_t>()));
+    CU(cudaMemcpyAsync(distances, h->w_out_d.p, nq * k * 4, cudaMemcpyDeviceToHost, st));
+    CU(cudaMemcpyAsync(labels, h->w_out_l.p, nq * k * 8, cudaMemcpyDeviceToHost, st));
+    CU(cudaStreamSynchronize(st));
+    return 0;
 }
 
 int ivfhnsw_b200_get_stats(ivfhnsw_b200_t *h, ivfhnsw_b200_stats_t *out)

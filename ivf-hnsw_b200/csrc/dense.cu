@@ -121,4 +121,58 @@ cudaError_t launch_u8_to_f32(cudaStream_t st, uint64_t *launches, size_t n, cons
     return cudaGetLastError();
 }
 
+// ---------------------------------------------------------------------------------------------
+// K-RR: exact re-rank of a query's candidates against their RAW vectors -- the second half of
+// IndexIVF_HNSW_Grouping::searchDisk (IndexIVF_HNSW_Grouping.cpp:365-395): d(q, x) with
+// ivfhnsw::fvec_L2sqr numerics (utils.cpp:22-51: floor(d/16)*16 dims, 8 partial sums), then ascending
+// (distance, label).  One CTA per query, 8 lanes per candidate; candidates with label < 0 (padding of a
+// short result list) sort last.
+// ---------------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(256) rerank_kernel(int ncand, int k, int d, const float *__restrict__ Q,
+                                                     const float *__restrict__ cand,
+                                                     const int64_t *__restrict__ cand_labels,
+                                                     float *__restrict__ out_d, int64_t *__restrict__ out_l)
+{
+    extern __shared__ __align__(16) float rr_sm[];
+    float *sq = rr_sm;           // [d]
+    float *sd = rr_sm + d;       // [ncand]
+    const int q = blockIdx.x, tid = threadIdx.x, lane = tid & 31, sub = lane & 7;
+    for (int i = tid; i < d; i += 256) sq[i] = Q[(size_t)q * d + i];
+    __syncthreads();
+    const int oct = tid >> 3;    // 32 octets per CTA
+    for (int c0 = 0; c0 < ncand; c0 += 32) {
+        const int c = c0 + oct;
+        const int cc = c < ncand ? c : ncand - 1;
+        const float dist = l2sqr16_octet(sq, cand + ((size_t)q * ncand + cc) * d, d, sub);
+        if (c < ncand && sub == 0) sd[c] = cand_labels[(size_t)q * ncand + c] < 0 ? FLT_MAX : dist;
+    }
+    __syncthreads();
+    for (int e = tid; e < ncand; e += 256) {
+        const float ed = sd[e];
+        const int64_t el = cand_labels[(size_t)q * ncand + e];
+        int rank = 0;
+        for (int o = 0; o < ncand; o++) {
+            const float od = sd[o];
+            const int64_t ol = cand_labels[(size_t)q * ncand + o];
+            rank += (od < ed || (od == ed && (ol < el || (ol == el && o < e)))) ? 1 : 0;
+        }
+        if (rank < k) {
+            out_d[(size_t)q * k + rank] = ed;
+            out_l[(size_t)q * k + rank] = el < 0 ? -1 : el;
+        }
+    }
+}
+
+cudaError_t launch_rerank(cudaStream_t st, uint64_t *launches, int nq, int ncand, int k, int d, const float *queries,
+                          const float *cand, const int64_t *cand_labels, float *out_d, int64_t *out_l)
+{
+    if (nq == 0) return cudaSuccess;
+    const size_t sm = (size_t)(d + ncand) * sizeof(float);
+    cudaError_t e = cudaFuncSetAttribute(rerank_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sm);
+    if (e != cudaSuccess) return e;
+    rerank_kernel<<<nq, 256, sm, st>>>(ncand, k, d, queries, cand, cand_labels, out_d, out_l);
+    ++*launches;
+    return cudaGetLastError();
+}
+
 }  // namespace ivfb200

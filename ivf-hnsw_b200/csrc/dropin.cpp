@@ -1,6 +1,8 @@
 // Host side of the drop-in: ivfhnsw::IndexIVF_HNSW / IndexIVF_HNSW_Grouping (include/ivf-hnsw/*.h) and the
 // faiss file helpers (include/faiss/index_io.h), all forwarding to the C ABI of libivfhnsw_b200.so.
 // Compiled into libivfhnsw_dropin.so.  No arithmetic of the search / indexing path happens here.
+#include <dirent.h>
+
 #include <algorithm>
 #include <cstdarg>
 #include <cstdlib>
@@ -167,6 +169,71 @@ void random_subset(const float *x, float *x_out, size_t d, size_t nx, size_t sub
     for (size_t i = 0; i < sub_nx; i++) memcpy(x_out + i * d, x + (size_t)perm[i] * d, sizeof(float) * d);
 }
 
+bool cmp(SearchInfo_t a, SearchInfo_t b)
+{
+    if (a.distance > b.distance) return false;
+    if (std::abs(b.distance - a.distance) <= 0.001f) return a.label < b.label;   // "equal" distances: by label
+    return true;
+}
+
+float getL2Distance(const float *query, const char *path_vec, const size_t dim, const long vec_id, vec_t type_v)
+{
+    std::vector<float> v(dim);
+    std::ifstream in(path_vec, std::ios::binary);
+    if (type_v == base_vec) {          // .bvecs record: [uint32 dim][dim x uint8]
+        in.seekg((std::streamoff)vec_id * (std::streamoff)(sizeof(uint32_t) + dim), in.beg);
+        readXvecFvec<uint8_t>(in, v.data(), dim, 1);
+    } else if (type_v == centroid_vec) {   // .fvecs record: [uint32 dim][dim x float]
+        in.seekg((std::streamoff)vec_id * (std::streamoff)(sizeof(uint32_t) + dim * sizeof(float)), in.beg);
+        readXvec<float>(in, v.data(), dim, 1);
+    } else {
+        std::cout << "Invalid vector type: " << type_v << std::endl;
+        assert(0);
+    }
+    return fvec_L2sqr(query, v.data(), dim);
+}
+
+size_t base_vec_num(const char *path_base, size_t vec_dim)
+{
+    struct stat st;
+    if (stat(path_base, &st)) return 0;
+    const size_t rec = sizeof(uint32_t) + vec_dim * sizeof(uint8_t);
+    const size_t n = (size_t)st.st_size / rec;
+    if ((size_t)st.st_size != rec * n) {
+        std::cout << "Invalid size of file: " << path_base << std::endl;
+        assert(0);
+    }
+    return n;
+}
+
+void get_files(const char *path_dir, const char *file_ext, std::vector<std::string> &file_list)
+{
+    DIR *dir = opendir(path_dir);
+    if (!dir) {
+        std::cout << "Failed to open dir: " << path_dir << std::endl;
+        return;
+    }
+    const size_t le = strlen(file_ext);
+    while (struct dirent *e = readdir(dir)) {
+        const size_t ln = strlen(e->d_name);
+        // a name that ends in the extension and is longer than it
+        if (ln > le && !strcmp(e->d_name + ln - le, file_ext)) file_list.push_back(e->d_name);
+    }
+    closedir(dir);
+    std::sort(file_list.begin(), file_list.end());
+}
+
+void check_files(const char *file_prefix, std::vector<std::string> &file_list)
+{
+    for (const std::string &f : file_list)
+        if (f.compare(0, strlen(file_prefix), file_prefix) != 0) assert(0);
+}
+
+void get_index_name(const char *path_idx, size_t idx, char *idx_name)
+{
+    sprintf(idx_name, "%s_%02lu%s", path_idx, (unsigned long)idx, ".index");
+}
+
 float fvec_L2sqr(const float *x, const float *y, size_t d)
 {
     float lane[8] = {0, 0, 0, 0, 0, 0, 0, 0};
@@ -203,6 +270,8 @@ void IndexIVF_HNSW::init(size_t dim, size_t ncentroids, size_t bytes_per_code, s
     nprobe = 16;
     max_codes = 10000;
     pruning_flag_ = false;
+    M = 16;
+    memset(&hdr_idx, 0, sizeof hdr_idx);
     fp_pq_ = fp_norm_ = fp_opq_ = 0;
     sent_nprobe_ = sent_max_codes_ = (size_t)-1;
     sent_flags_ = -1;
@@ -244,6 +313,8 @@ std::vector<float> &IndexIVF_HNSW::get_centroid_norms()
 
 void IndexIVF_HNSW::build_quantizer(const char *path_data, const char *, const char *, size_t M, size_t efConstruction)
 {
+    this->M = M;
+    hdr_idx.efConstruction = (uint32_t)efConstruction;   // reference IndexIVF_HNSW.cpp:43
     // only the centroid table is needed: the coarse quantizer is the exact GEMM over it, no graph files
     std::vector<float> cent(nc * d);
     {
@@ -313,7 +384,8 @@ void IndexIVF_HNSW::pull_quantizers()
 
 void IndexIVF_HNSW::assign(size_t n, const float *x, idx_t *labels, size_t k)
 {
-    // k > 1 returns the k-th nearest like the reference (top of a k-element max-heap, IndexIVF_HNSW.cpp:71)
+    // the reference returns the k-th nearest for k > 1 (top of a k-element max-heap, IndexIVF_HNSW.cpp:71); every
+    // caller passes k = 1 and so does the C ABI, which rejects anything else with EINVAL
     ck(ivfhnsw_b200_assign(h_, n, x, labels, k), "assign");
 }
 
@@ -333,7 +405,113 @@ void IndexIVF_HNSW::search_batch(size_t nq, size_t k, const float *x, float *dis
 
 void IndexIVF_HNSW::search(size_t k, const float *x, float *distances, long *labels)
 {
+    last_query_.assign(x, x + d);
     search_batch(1, k, x, distances, labels, false);
+}
+
+// Tracing of the probed centroids (reference IndexIVF_HNSW.cpp:298-326).  The reference records them inside every
+// search(); here they are recomputed on demand for the last query (one coarse call) so that the hot path stays clean.
+void IndexIVF_HNSW::trace_centroids(size_t idx_q, bool missed)
+{
+    trace_query_centroid_dists.clear();
+    trace_centroid_idxs.clear();
+    if (last_query_.size() == d) {
+        std::vector<float> cd(nprobe);
+        std::vector<idx_t> ci(nprobe);
+        sync_quantizers();
+        ck(ivfhnsw_b200_coarse(h_, 1, last_query_.data(), nprobe, cd.data(), ci.data()), "coarse");
+        for (size_t j = nprobe; j-- > 0;) {     // farthest first, like the unload loop of IndexIVF_HNSW.cpp:249-256
+            trace_query_centroid_dists.push_back(cd[j]);
+            trace_centroid_idxs.push_back(ci[j]);
+        }
+    }
+    std::ofstream log_trace(missed ? "centroids_miss.log" : "centroids_hit.log", std::ofstream::out | std::ofstream::app);
+    if (!log_trace.is_open()) {
+        std::cout << "Failed to open log file for centroids traceing" << std::endl;
+        return;
+    }
+    std::vector<uint32_t> sizes(nc);
+    ck(ivfhnsw_b200_list_sizes(h_, sizes.data()), "list_sizes");
+    const size_t sz = trace_centroid_idxs.size();
+    std::cout << "centroids number " << sz << std::endl;
+    if (sz > 0) log_trace << "query " << idx_q << " centroids info\n";
+    for (size_t i = 0; i < sz; i++)
+        log_trace << "centroid " << trace_centroid_idxs[i] << " with distance " << trace_query_centroid_dists[i]
+                  << " with group size " << sizes[trace_centroid_idxs[i]] << "\n";
+}
+
+void IndexIVF_HNSW::add_batch2(size_t n, const float *x, const idx_t *xids, const idx_t *idx, uint64_t *eids, char *obuf)
+{
+    sync_quantizers();
+    std::vector<uint8_t> xcodes(n * code_size), xnorm(n);
+    ck(ivfhnsw_b200_add_batch_codes(h_, n, x, xids, idx, xcodes.data(), xnorm.data()), "add_batch2");
+    char *p = obuf;     // record = [uint64 external id][code_size code bytes][norm code], IndexIVF_HNSW.cpp:181-203
+    for (size_t i = 0; i < n; i++) {
+        memcpy(p, eids + i, sizeof(uint64_t));
+        p += sizeof(uint64_t);
+        memcpy(p, xcodes.data() + i * code_size, code_size);
+        p += code_size;
+        *p++ = (char)xnorm[i];
+    }
+}
+
+int IndexIVF_HNSW::copy_file(const char *file_src, const char *file_dst)
+{
+    std::ifstream in(file_src, std::ios::binary);
+    if (!in) return -1;
+    std::ofstream out(file_dst, std::ios::binary);
+    out << in.rdbuf();
+    return out.good() ? 0 : -1;
+}
+
+// ORCV directory (reference IndexIVF_HNSW.cpp:672-755).  Not reproduced: the reference's write2 also rotates the
+// quantizer's centroids IN PLACE while producing opq.vec ("TODO: confirm it" there); the file holds what it holds in
+// the reference -- one d-vector, the last centroid -- and the centroid table is left alone.
+void IndexIVF_HNSW::write2(const char *home_dir, size_t n_vecs, bool do_opq_flag, const char *path_edge)
+{
+    sync_host_lists();
+    char path_f[512];
+    {
+        snprintf(path_f, sizeof path_f, "%s/hdr.vec", home_dir);
+        std::cout << "write file: " << path_f << std::endl;
+        std::ofstream output(path_f, std::ios::binary);
+        hdr_idx.n = (uint32_t)n_vecs;
+        hdr_idx.nc = (uint32_t)nc;
+        hdr_idx.code_size = (uint32_t)code_size;
+        hdr_idx.code_bytes = (uint32_t)(code_size / 8);
+        hdr_idx.d = (uint32_t)d;
+        hdr_idx.do_opq = do_opq_flag ? 1 : 0;
+        hdr_idx.M = (uint32_t)M;
+        hdr_idx.dmatch = dmatch;
+        hdr_idx.dnear = dnear;
+        write_variable(output, hdr_idx);
+    }
+    {
+        snprintf(path_f, sizeof path_f, "%s/cnorms.vec", home_dir);
+        std::cout << "write file: " << path_f << std::endl;
+        std::ofstream output(path_f, std::ios::binary);
+        write_vector(output, get_centroid_norms());
+    }
+    {
+        snprintf(path_f, sizeof path_f, "%s/pq.vec", home_dir);
+        std::ofstream output(path_f, std::ios::binary);
+        for (size_t i = 0; i < nc; i++) write_vector(output, codes[i]);
+    }
+    if (do_opq_flag) {
+        std::vector<float> cent(nc * d), last(d);
+        ck(ivfhnsw_b200_get_centroids(h_, cent.data()), "get_centroids");
+        memcpy(last.data(), cent.data() + (nc - 1) * d, d * sizeof(float));
+        snprintf(path_f, sizeof path_f, "%s/opq.vec", home_dir);
+        std::ofstream output(path_f, std::ios::binary);
+        write_vector(output, last);
+    }
+    {
+        snprintf(path_f, sizeof path_f, "%s/normpq.vec", home_dir);
+        std::ofstream output(path_f, std::ios::binary);
+        for (size_t i = 0; i < nc; i++) write_vector(output, norm_codes[i]);
+    }
+    snprintf(path_f, sizeof path_f, "%s/edge.vec", home_dir);
+    copy_file(path_edge, path_f);
 }
 
 IndexIVF_HNSW::idx_t IndexIVF_HNSW::search_enn(const float *x, float *distances, long *labels)
@@ -455,6 +633,62 @@ void IndexIVF_HNSW_Grouping::search(size_t k, const float *x, float *distances, 
 {
     pruning_flag_ = do_pruning;
     IndexIVF_HNSW::search(k, x, distances, labels);
+}
+
+void IndexIVF_HNSW_Grouping::searchDisk_batch(size_t nq, size_t k, const float *queries, float *distances, long *labels,
+                                              const char *path_base)
+{
+    // 2k candidates from the index (the reference's intent, IndexIVF_HNSW_Grouping.cpp:373-374), ascending
+    const size_t k2 = 2 * k;
+    std::vector<float> d2(nq * k2);
+    std::vector<long> l2(nq * k2);
+    pruning_flag_ = do_pruning;
+    search_batch(nq, k2, queries, d2.data(), l2.data(), true);
+    // their raw vectors from the .bvecs file (getL2Distance -> readBaseVec, utils.cpp:98-107), expanded to float
+    std::vector<float> cand(nq * k2 * d, 0.f);
+    std::ifstream in(path_base, std::ios::binary);
+    if (!in) {
+        fprintf(stderr, "ivfhnsw_b200: cannot open base file %s\n", path_base);
+        exit(1);
+    }
+    for (size_t i = 0; i < nq * k2; i++) {
+        if (l2[i] < 0) continue;
+        in.seekg((std::streamoff)l2[i] * (std::streamoff)(sizeof(uint32_t) + d), in.beg);
+        readXvecFvec<uint8_t>(in, cand.data() + i * d, d, 1);
+    }
+    static_assert(sizeof(long) == sizeof(int64_t), "labels are 64-bit");
+    ck(ivfhnsw_b200_rerank(h_, nq, k2, k, queries, cand.data(), reinterpret_cast<const int64_t *>(l2.data()), distances,
+                           reinterpret_cast<int64_t *>(labels)),
+       "rerank");
+}
+
+void IndexIVF_HNSW_Grouping::searchDisk(size_t k, const float *query, float *distances, long *labels, const char *path_base)
+{
+    searchDisk_batch(1, k, query, distances, labels, path_base);
+}
+
+void IndexIVF_HNSW_Grouping::dump_inter_centroid_dists(char *path)
+{
+    FILE *fp = fopen(path, "w");
+    if (!fp) {
+        std::cout << "Failed to open file: " << path << std::endl;
+        return;
+    }
+    ck(ivfhnsw_b200_finalize(h_), "finalize");
+    size_t n = 0;
+    ck(ivfhnsw_b200_ntotal(h_, &n), "ntotal");
+    std::vector<int64_t> off(nc + 1);
+    std::vector<uint32_t> ids_(std::max<size_t>(n, 1)), nn(nc * nsubc), ss(nc * nsubc);
+    std::vector<uint8_t> cd(std::max<size_t>(n, 1) * code_size), ncd(std::max<size_t>(n, 1));
+    std::vector<float> icd(nc * nsubc), al(nc);
+    ck(ivfhnsw_b200_export_lists(h_, off.data(), ids_.data(), cd.data(), ncd.data(), nn.data(), ss.data(), al.data(),
+                                 icd.data()),
+       "export_lists");
+    for (size_t i = 0; i < nc; i++)
+        for (size_t subc = 0; subc < nsubc; subc++)
+            fprintf(fp, "distance of centriod %lu to centriod %lu is %f\n", (unsigned long)i, (unsigned long)subc,
+                    icd[i * nsubc + subc]);
+    fclose(fp);
 }
 
 void IndexIVF_HNSW_Grouping::train_pq(size_t n, const float *x)

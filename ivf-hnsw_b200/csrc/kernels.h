@@ -101,6 +101,9 @@ cudaError_t launch_row_norms(cudaStream_t st, uint64_t *launches, size_t n, int 
                              int dk = -1);
 // dims the coarse distance really uses: hnswlib's fstdistfunc drops the d % 16 tail (hnswalg.cpp:326-356)
 static inline int coarse_dims(int d) { return (d >> 4) ? ((d >> 4) << 4) : d; }
+// exact re-rank of ncand candidates per query against their raw vectors (searchDisk), ascending (distance, label)
+cudaError_t launch_rerank(cudaStream_t st, uint64_t *launches, int nq, int ncand, int k, int d, const float *queries,
+                          const float *cand, const int64_t *cand_labels, float *out_d, int64_t *out_l);
 cudaError_t launch_u8_to_f32(cudaStream_t st, uint64_t *launches, size_t n, const uint8_t *x, float *out);
 
 // ----------------------------------------------------------------------------- coarse stage
