@@ -699,28 +699,11 @@ def main():
     def single_search(q_dev):
         idx.search_dev(k, q_dev, D, L)
 
-    def make_sharded(nq_total, home_lo, home_hi):
-        """Sharded search of nq_total queries of which this rank prepares [home_lo, home_hi); fills Dall/Lall
-        (all nq_total rows, identical on every rank)."""
-        per = home_hi - home_lo
-        assert per * world == nq_total
-        tables = torch.empty(nq_total, idx.tables_bytes(), dtype=torch.uint8, device=dev)
-        pD = torch.empty(nq_total, k, dtype=torch.float32, device=dev)
-        pS = torch.empty(nq_total, k, dtype=torch.int32, device=dev)
-        pL = torch.empty(nq_total, k, dtype=torch.int64, device=dev)
-        gD = torch.empty(world, nq_total, k, dtype=torch.float32, device=dev)
-        gS = torch.empty(world, nq_total, k, dtype=torch.int32, device=dev)
-        gL = torch.empty(world, nq_total, k, dtype=torch.int64, device=dev)
-        Dall = torch.empty(nq_total, k, dtype=torch.float32, device=dev)
-        Lall = torch.empty(nq_total, k, dtype=torch.int64, device=dev)
-
-        def search(q_all):
-            idx.prepare_dev(q_all, home_lo, home_hi, tables)
-            sharding.gather_tables(dist, tables, rank, per, None)
-            idx.scan_tables_dev(k, q_all, tables, pD, pS, pL)
-            sharding.gather_partials(dist, pD, pS, pL, gD, gS, gL, None)
-            idx.merge_partials_dev(k, nq_total, world, gD, gS, gL, Dall, Lall)
-        return search, Dall, Lall
+    def make_sharded(nq_home):
+        """Sharded search of world * nq_home queries per step of which this rank is the home of rows [rank * nq_home,
+        (rank + 1) * nq_home): sharding.PackedShardedSearch (all-to-all-v of packed per-owner records)."""
+        ps = sharding.PackedShardedSearch(torch, dist, idx, rank, world, nq_home, k, dev)
+        return ps.search, ps
 
     def timed_run(search, q_dev, steps, warmup, clocks):
         for _ in range(max(warmup, 3)):
@@ -769,29 +752,39 @@ def main():
         per = (nq + world - 1) // world
         nq_s = per * world
         q_strong = torch.cat([queries, queries[:nq_s - nq]]) if nq_s > nq else queries
-        s_search, s_D, s_L = make_sharded(nq_s, rank * per, (rank + 1) * per)
+        s_search, s_ps = make_sharded(per)
         ms_str, _ = timed_run(s_search, q_strong, args.steps, args.warmup, contextlib.nullcontext())
-        sharded_ok = bool(torch.equal(s_L[:nq], L_ref) and torch.equal(s_D[:nq], D_ref))
+        lo_s, hi_s = rank * per, min((rank + 1) * per, nq)
+        ok_here = bool(torch.equal(s_ps.L[:hi_s - lo_s], L_ref[lo_s:hi_s]) and torch.equal(s_ps.D[:hi_s - lo_s], D_ref[lo_s:hi_s]))
         # weak (headline): every rank brings its own nq queries (rank r's batch = the same seeded batch rotated by
         # r * 997 rows, so that all ranks hold the full tensor without a broadcast in the timed region)
         q_weak = torch.cat([torch.roll(queries, shifts=-997 * r, dims=0) for r in range(world)])
-        w_search, w_D, w_L = make_sharded(nq * world, rank * nq, (rank + 1) * nq)
+        w_search, w_ps = make_sharded(nq)
         ms, st = timed_run(w_search, q_weak, args.steps, args.warmup, clk)
         value = nq * world * args.steps / (ms / 1e3)
         scaling = "weak"
         search, q_timed = w_search, q_weak
-        # rank 0's home batch is the un-rotated one: its rows must equal the single-GPU answer too
-        sharded_ok = sharded_ok and bool(torch.equal(w_L[:nq], L_ref) and torch.equal(w_D[:nq], D_ref))
-        D.copy_(w_D[:nq]); L.copy_(w_L[:nq])
+        # a rank's home batch is the seeded batch rotated by 997 * rank rows: its answer must be the single-GPU answer
+        # rotated the same way, bit for bit
+        ok_here = ok_here and bool(torch.equal(w_ps.L, torch.roll(L_ref, shifts=-997 * rank, dims=0)) and
+                                   torch.equal(w_ps.D, torch.roll(D_ref, shifts=-997 * rank, dims=0)))
+        okt = torch.tensor([1 if ok_here else 0], device=dev)
+        dist.all_reduce(okt, op=dist.ReduceOp.MIN)
+        sharded_ok = bool(okt.item())
+        if rank == 0:
+            D.copy_(w_ps.D); L.copy_(w_ps.L)
+        exchange_mb = w_ps.last_recv_words * 4 / 1e6
         layouts = {"list_sharded_weak": {"value": value, "ms_per_step": ms / args.steps, "nq_per_step": nq * world},
                    "list_sharded_strong": {"value": nq * args.steps / (ms_str / 1e3), "ms_per_step": ms_str / args.steps,
                                            "nq_per_step": nq},
                    "replicas": {"value": nq * world * args.steps / (ms_rep / 1e3), "ms_per_step": ms_rep / args.steps,
-                                "nq_per_step": nq * world, "note": "every rank searches the whole index alone, no collective"}}
+                                "nq_per_step": nq * world, "note": "every rank searches the whole index alone, no collective"},
+                   "record_exchange_MB_received_per_rank_per_step": exchange_mb}
         config["nq_per_step"] = nq * world
         config["sharding"] = ("lists sharded over all %d ranks by centroid range; per step every rank prepares its own %d "
-                              "queries, work records and partial top-k are exchanged over NCCL, every rank scans its lists "
-                              "for all %d queries" % (world, nq, nq * world))
+                              "queries, packs their work records per owning rank, ONE NCCL all-to-all-v moves them, every "
+                              "rank scans its lists for all %d queries, partial top-k go home by all-to-all and are merged"
+                              % (world, nq, nq * world))
         config["layouts"] = layouts
         config["sharded_equals_single_gpu"] = sharded_ok
     launches = int(st.kernel_launches)
@@ -923,8 +916,8 @@ def main():
             qd[rank * nq:(rank + 1) * nq].copy_(qh, non_blocking=True)
             dist.all_gather_into_tensor(qd, qd[rank * nq:(rank + 1) * nq])
             search(qd)
-            Dh.copy_(w_D[rank * nq:(rank + 1) * nq], non_blocking=True)
-            Lh.copy_(w_L[rank * nq:(rank + 1) * nq], non_blocking=True)
+            Dh.copy_(w_ps.D, non_blocking=True)
+            Lh.copy_(w_ps.L, non_blocking=True)
             torch.cuda.synchronize()
         e2e_step()
         dist.barrier()

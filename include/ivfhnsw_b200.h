@@ -206,6 +206,20 @@ int ivfhnsw_b200_scan_tables_dev(ivfhnsw_b200_t *h, size_t nq, size_t k, const f
  * ascending by (distance, label).  Host pointers. */
 int ivfhnsw_b200_rerank(ivfhnsw_b200_t *h, size_t nq, size_t ncand, size_t k, const float *queries, const float *cand,
                         const int64_t *cand_labels, float *distances, int64_t *labels);
+/* Sharded search without the all-gather of whole records: the HOME rank of a query (the one that prepared it) splits
+ * its records into one PACKED stream per owning rank -- per query a mini record of only the probes that rank owns and
+ * the max_codes rule scans -- which the ranks exchange with ONE all-to-all-v (~(5 + nsubc) words per probe instead of
+ * the whole 35 KB record to everybody).  tables_dev: nq records as written by prepare_dev.  Outputs: packed_dev (capacity
+ * nq * tables_bytes) = the nparts streams back to back, cnt_dev / off_dev [nparts][nq] = probes and 32-bit-word offset
+ * (inside its stream) of every (part, query), part_words_dev [nparts] = length of every stream in 32-bit words.
+ * Ownership = equal centroid ranges of ceil(nc / nparts), the same split as set_shard in an nparts-rank deployment. */
+int ivfhnsw_b200_pack_records_dev(ivfhnsw_b200_t *h, size_t nq, const void *tables_dev, size_t nparts, void *packed_dev,
+                                  uint32_t *cnt_dev, uint32_t *off_dev, uint64_t *part_words_dev);
+/* scan_tables_dev over packed records: query q's record starts at 32-bit word qoff_dev[q] of packed_dev and holds
+ * qnp_dev[q] probes (0 = nothing of this query lives here: an empty partial result is written) */
+int ivfhnsw_b200_scan_packed_dev(ivfhnsw_b200_t *h, size_t nq, size_t k, const float *x_dev, const void *packed_dev,
+                                 const uint32_t *qoff_dev, const uint32_t *qnp_dev, float *part_d_dev,
+                                 uint32_t *part_seq_dev, int64_t *part_labels_dev);
 int ivfhnsw_b200_sync(ivfhnsw_b200_t *h);
 /* run on a caller-owned CUDA stream (cudaStream_t, e.g. torch's current stream); NULL = back to a private one.
  * STREAM ORDERING: every *_dev entry point only ENQUEUES work on the handle's stream.  Device buffers
@@ -239,7 +253,7 @@ int ivfhnsw_b200_reset_stats(ivfhnsw_b200_t *h);
  * query (IndexIVF_HNSW_Grouping.cpp:261) and codes scanned per query */
 int ivfhnsw_b200_last_thresholds(ivfhnsw_b200_t *h, size_t cap, float *thresholds, uint32_t *scanned);
 /* tuning knobs: "coarse_slack", "coarse_impl" (0 = SIMT fp32, 1 = tcgen05 split-fp16 three products, 2 = two products
- * with a widened select threshold, the default), "scan_split" (0 = auto), "stage_bytes" (raw Grouping vectors staged
+ * with a widened select threshold, 3 = one product + integer keys, the default), "scan_split" (0 = auto), "stage_bytes" (raw Grouping vectors staged
  * before add_group encodes them) */
 int ivfhnsw_b200_set_option(ivfhnsw_b200_t *h, const char *name, long value);
 

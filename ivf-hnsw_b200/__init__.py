@@ -105,6 +105,8 @@ def lib():
         "ivfhnsw_b200_tables_bytes": ([H, C.POINTER(C.c_size_t)], C.c_int),
         "ivfhnsw_b200_prepare_dev": ([H, sz, vp, sz, sz, vp], C.c_int),
         "ivfhnsw_b200_scan_tables_dev": ([H, sz, sz, vp, vp, vp, vp, vp], C.c_int),
+        "ivfhnsw_b200_pack_records_dev": ([H, sz, vp, sz, vp, vp, vp, vp], C.c_int),
+        "ivfhnsw_b200_scan_packed_dev": ([H, sz, sz, vp, vp, vp, vp, vp, vp, vp], C.c_int),
         "ivfhnsw_b200_sync": ([H], C.c_int),
         "ivfhnsw_b200_set_stream": ([H, vp], C.c_int),
         "ivfhnsw_b200_set_timing": ([H, C.c_int], C.c_int),
@@ -530,6 +532,21 @@ class IndexIVF_HNSW:
         with self._ordered():
             self._ck(self._L.ivfhnsw_b200_scan_tables_dev(self._h, x_dev.shape[0], k, _ptr(x_dev), _ptr(tables_dev),
                                                           _ptr(part_d), _ptr(part_seq), _ptr(part_labels)))
+
+    def pack_records_dev(self, nq, tables_dev, nparts, packed_dev, cnt_dev, off_dev, part_words_dev):
+        """Records of nq home queries -> one packed stream per owning rank (ivfhnsw_b200_pack_records_dev)."""
+        self._push_params()
+        with self._ordered():
+            self._ck(self._L.ivfhnsw_b200_pack_records_dev(self._h, nq, _ptr(tables_dev), nparts, _ptr(packed_dev),
+                                                           _ptr(cnt_dev), _ptr(off_dev), _ptr(part_words_dev)))
+
+    def scan_packed_dev(self, k, x_dev, packed_dev, qoff_dev, qnp_dev, part_d, part_seq, part_labels):
+        """Scan of this shard's lists driven by packed records (ivfhnsw_b200_scan_packed_dev)."""
+        self._push_params()
+        with self._ordered():
+            self._ck(self._L.ivfhnsw_b200_scan_packed_dev(self._h, x_dev.shape[0], k, _ptr(x_dev), _ptr(packed_dev),
+                                                          _ptr(qoff_dev), _ptr(qnp_dev), _ptr(part_d), _ptr(part_seq),
+                                                          _ptr(part_labels)))
 
     def merge_partials_dev(self, k, nq, nparts, part_d, part_seq, part_labels, D_dev, L_dev):
         with self._ordered():

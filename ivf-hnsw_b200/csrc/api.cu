@@ -371,6 +371,7 @@ static TcSide tc_side(ivfhnsw_b200_t *h, size_t qb)
     S.qhi = h->w_xf16.as<__half>();
     S.qlo = S.qhi ? S.qhi + qb * S.dp : nullptr;
     S.qfac = S.qhi ? reinterpret_cast<float *>(S.qlo + qb * S.dp) : nullptr;
+    S.qstat = S.qhi ? reinterpret_cast<uint32_t *>(S.qfac + ((qb + 3) & ~(size_t)3)) : nullptr;
     return S;
 }
 
@@ -405,8 +406,8 @@ int ivfb200_coarse_dev(ivfhnsw_b200_t *h, size_t nq, const float *xq, size_t npr
     const size_t per_q = coarse_work_bytes(1, (int)h->nc, (int)nprobe + slack, &cand_cap);
     size_t qb = std::min<size_t>(nq, std::max<size_t>(128, ((size_t)4 << 30) / per_q));
     CU(h->w_coarse.ensure(qb * per_q + 256));
-    const int impl = use_tc(h) ? (h->coarse_impl >= 2 ? 2 : 1) : 0;
-    if (impl) CU(h->w_xf16.ensure(qb * ((h->d + 7) / 8 * 8) * 4 + qb * 4 + 256));
+    const int impl = use_tc(h) ? (int)std::min<long>(h->coarse_impl, 3) : 0;
+    if (impl) CU(h->w_xf16.ensure(qb * ((h->d + 7) / 8 * 8) * 4 + qb * 4 + 512));
     const TcSide S = tc_side(h, qb);
     const size_t ngroups = (h->nc + COARSE_GROUP - 1) / COARSE_GROUP;
     for (size_t q0 = 0; q0 < nq; q0 += qb) {
@@ -1152,7 +1153,8 @@ static int prepare_core(ivfhnsw_b200_t *h, size_t q_begin, size_t q_end, const f
 
 // Stage 2: lookup tables + ADC scan of THIS GPU's lists for all nq queries, driven by the records.
 static int scan_core(ivfhnsw_b200_t *h, size_t nq, size_t k, const float *x_dev, const uint32_t *tables, float *out_d,
-                     int64_t *out_l, uint32_t *out_seq, bool xrot_ready = false)
+                     int64_t *out_l, uint32_t *out_seq, bool xrot_ready = false, const uint32_t *qoff = nullptr,
+                     const uint32_t *qnp = nullptr)
 {
     if (nq == 0) return 0;
     const int d = (int)h->d, M = (int)h->M, nprobe = (int)h->nprobe, nsubc = (int)h->nsubc;
@@ -1173,9 +1175,11 @@ static int scan_core(ivfhnsw_b200_t *h, size_t nq, size_t k, const float *x_dev,
     for (size_t q0 = 0; q0 < nq; q0 += qb) {
         const int nb = (int)std::min(qb, nq - q0);
         SegTables T;
-        T.rec = const_cast<uint32_t *>(tables) + q0 * stride;
+        T.rec = const_cast<uint32_t *>(tables) + (qoff ? 0 : q0 * stride);
         T.stride = stride; T.nprobe = nprobe; T.nsubc = nsubc;
         T.qsd = nullptr; T.threshold = nullptr; T.nscanned = nullptr; T.nwalked = nullptr;
+        T.qoff = qoff ? qoff + q0 : nullptr;
+        T.qnp = qnp ? qnp + q0 : nullptr;
         const float *xq = x_dev + q0 * d;
         if (h->timing) CU(cudaEventRecord(h->ev[2], st));
         if (h->do_opq) {
@@ -1274,6 +1278,29 @@ int ivfhnsw_b200_scan_tables_dev(ivfhnsw_b200_t *h, size_t nq, size_t k, const f
     if (bind(h)) return IVFHNSW_B200_ECUDA;
     if (int r = search_checks(h, k)) return r;
     return scan_core(h, nq, k, x_dev, reinterpret_cast<const uint32_t *>(tables_dev), part_d, part_labels, part_seq);
+}
+int ivfhnsw_b200_pack_records_dev(ivfhnsw_b200_t *h, size_t nq, const void *tables_dev, size_t nparts, void *packed_dev,
+                                  uint32_t *cnt_dev, uint32_t *off_dev, uint64_t *part_words_dev)
+{
+    if (bind(h)) return IVFHNSW_B200_ECUDA;
+    if (nparts == 0 || nparts > 64) return h->fail(IVFHNSW_B200_EINVAL, "nparts out of range [1, 64]");
+    const size_t stride = seg_record_words((int)h->nprobe, (int)h->nsubc);
+    if (nq * stride >= (1ull << 32)) return h->fail(IVFHNSW_B200_EINVAL, "pack_records: batch too large (32-bit word offsets)");
+    static_assert(sizeof(unsigned long long) == sizeof(uint64_t), "64-bit counters");
+    CU(launch_pack_records(h->stream, LAUNCHES, (int)nq, (int)h->nprobe, (int)h->nsubc, (int)h->nc, (int)nparts,
+                           reinterpret_cast<const uint32_t *>(tables_dev), stride, reinterpret_cast<uint32_t *>(packed_dev),
+                           cnt_dev, off_dev, reinterpret_cast<unsigned long long *>(part_words_dev)));
+    return 0;
+}
+int ivfhnsw_b200_scan_packed_dev(ivfhnsw_b200_t *h, size_t nq, size_t k, const float *x_dev, const void *packed_dev,
+                                 const uint32_t *qoff_dev, const uint32_t *qnp_dev, float *part_d, uint32_t *part_seq,
+                                 int64_t *part_labels)
+{
+    if (bind(h)) return IVFHNSW_B200_ECUDA;
+    if (int r = search_checks(h, k)) return r;
+    if (!qoff_dev || !qnp_dev) return h->fail(IVFHNSW_B200_EINVAL, "scan_packed: per-query offsets / probe counts missing");
+    return scan_core(h, nq, k, x_dev, reinterpret_cast<const uint32_t *>(packed_dev), part_d, part_labels, part_seq, false,
+                     qoff_dev, qnp_dev);
 }
 int ivfhnsw_b200_merge_partials_dev(ivfhnsw_b200_t *h, size_t nq, size_t k, size_t nparts, const float *part_d,
                                     const uint32_t *part_seq, const int64_t *part_labels, float *out_d,

@@ -134,6 +134,7 @@ __global__ void __launch_bounds__(256) coarse_select_kernel(int nc, int d, int n
                                                             const uint32_t *__restrict__ grp_idx,
                                                             int packed, int kept, int self_off,
                                                             const uint32_t *__restrict__ cmax /* two-product GEMM: margin */,
+                                                            const uint32_t *__restrict__ qstat /* packed == 2 */,
                                                             uint32_t *__restrict__ err,
                                                             float *__restrict__ out_d, uint32_t *__restrict__ out_i)
 {
@@ -149,12 +150,24 @@ __global__ void __launch_bounds__(256) coarse_select_kernel(int nc, int d, int n
     const float *gv = grp_val + (size_t)q * n;
     // packed (tensor-core GEMM): the centroid is group * COARSE_GROUP + low 7 bits of the value and
     // masked entries are >= 1e38; otherwise ids come from grp_idx and masked entries have id ~0
+    // packed == 2 (impl 3): the entries are order-preserving integer keys (common.cuh), column in the low 7 bits,
+    // padding columns / unused slots >= COARSE_KEY_INVALID_MIN
     const uint32_t *gi = packed ? nullptr : grp_idx + (size_t)q * n;
+    const uint32_t *gk = reinterpret_cast<const uint32_t *>(gv);
+    const uint32_t kinv = packed == 2 ? COARSE_KEY_INVALID_MIN : fkey(1.0e38f);
+    auto entry_key = [&](int i) -> uint32_t { return packed == 2 ? gk[i] : fkey(gv[i]); };
     auto entry_id = [&](int i) -> uint32_t {
         if (!packed) return gi[i];
-        const float v = gv[i];
-        if (!(v < 1.0e38f)) return 0xffffffffu;
-        const uint32_t id = (uint32_t)(i / COARSE_T) * COARSE_GROUP + (__float_as_uint(v) & 127u);
+        uint32_t col;
+        if (packed == 2) {
+            if (gk[i] >= COARSE_KEY_INVALID_MIN) return 0xffffffffu;
+            col = gk[i] & 127u;
+        } else {
+            const float v = gv[i];
+            if (!(v < 1.0e38f)) return 0xffffffffu;
+            col = __float_as_uint(v) & 127u;
+        }
+        const uint32_t id = (uint32_t)(i / COARSE_T) * COARSE_GROUP + col;
         return (self_off >= 0 && id == (uint32_t)(q + self_off)) ? 0xffffffffu : id;
     };
     for (int i = tid; i < d; i += 256) sq[i] = Q[(size_t)q * d + i];
@@ -179,7 +192,7 @@ __global__ void __launch_bounds__(256) coarse_select_kernel(int nc, int d, int n
         // assignment by one entry per pass gives every thread all four ranks (loads stay coalesced)
         for (int j = 0; j * 256 < n; j++) {
             const int i = j * 256 + ((tid + j) & 255);
-            if (i < n) mk = min(mk, fkey(gv[i]));
+            if (i < n) mk = min(mk, entry_key(i));
         }
 #pragma unroll
         for (int j = 0; j < SEL_CACHE; j++) kc[j] = 0xffffffffu;
@@ -188,7 +201,7 @@ __global__ void __launch_bounds__(256) coarse_select_kernel(int nc, int d, int n
 #pragma unroll
         for (int j = 0; j < SEL_CACHE; j++) {
             const int i = tid + 256 * j;
-            kc[j] = i < n ? fkey(gv[i]) : 0xffffffffu;
+            kc[j] = i < n ? entry_key(i) : 0xffffffffu;
         }
     }
     // bits every key shares need no pass (and would put all 2048 atomics of a pass on one counter): the keys of
@@ -196,14 +209,13 @@ __global__ void __launch_bounds__(256) coarse_select_kernel(int nc, int d, int n
     {
         // empty slots (>= 1e38: masked centroids, the unused 4th slot of the packed GEMM) take no part: they only
         // matter when kprime exceeds the number of valid entries, and then every valid entry is selected anyway
-        const uint32_t kinv = fkey(1.0e38f);
         uint32_t vor = 0u, vand = 0xffffffffu;
         if (cached) {
 #pragma unroll
             for (int j = 0; j < SEL_CACHE; j++)
                 if (tid + 256 * j < nsel && kc[j] < kinv) { vor |= kc[j]; vand &= kc[j]; }
         } else {
-            for (int i = tid; i < n; i += 256) { const uint32_t kx = fkey(gv[i]); if (kx < kinv) { vor |= kx; vand &= kx; } }
+            for (int i = tid; i < n; i += 256) { const uint32_t kx = entry_key(i); if (kx < kinv) { vor |= kx; vand &= kx; } }
         }
         vor = __reduce_or_sync(IVF_FULL_MASK, vor);
         vand = __reduce_and_sync(IVF_FULL_MASK, vand);
@@ -228,7 +240,7 @@ __global__ void __launch_bounds__(256) coarse_select_kernel(int nc, int d, int n
                 if ((kc[j] & pmask) == prefix && tid + 256 * j < nsel) atomicAdd(&hist[(kc[j] >> shift) & dmask], 1u);
         } else {
             for (int i = tid; i < n; i += 256) {
-                const uint32_t kx = fkey(gv[i]);
+                const uint32_t kx = entry_key(i);
                 if ((kx & pmask) == prefix) atomicAdd(&hist[(kx >> shift) & dmask], 1u);
             }
         }
@@ -265,7 +277,24 @@ __global__ void __launch_bounds__(256) coarse_select_kernel(int nc, int d, int n
         remaining_bits = shift;
     }
     uint32_t tau = s_prefix;       // key of the kprime-th smallest
-    if (cmax) {
+    if (packed == 2) {
+        // one-product GEMM: each dropped cross term (q.c_lo always, q_lo.c when some query of the batch has a lo
+        // part) moves a value by at most 2 * 2^-11 ||q|| ||c||; the true top-kprime all lie below the kprime-th
+        // smallest approximate value + twice the total bound.  In key units (value * S) plus the quantisation of the
+        // keys: one quantum of 128 for the rounding, one for the column bits.
+        float qn = 0.f;
+        const int dk = (d >> 4) ? ((d >> 4) << 4) : d;   // coarse_dims(d)
+        for (int i = 0; i < dk; i++) qn = fmaf(sq[i], sq[i], qn);
+        const float cmax2 = __uint_as_float(cmax[1]);
+        const float S = coarse_key_scale(__uint_as_float(qstat[0]), cmax2);
+        const float terms = qstat[1] ? 2.f : 1.f;
+        const float eps = terms * 9.8e-4f * sqrtf(qn * cmax2);
+        const float wide = 2.f * 1.02f * eps * S + 3.f * 128.f;
+        if (tau < COARSE_KEY_INVALID_MIN) {
+            const float room = (float)(COARSE_KEY_INVALID_MIN - 1u - tau);
+            tau += (uint32_t)fminf(wide, room);
+        }
+    } else if (cmax) {
         // two-product GEMM: every kept value is within eps = 2 * 2^-11 ||q|| ||c|| of its three-product value, so the
         // true top-kprime all lie below (kprime-th smallest approximate value) + 2 eps; widen the threshold by that
         // (plus the 2^-16 relative perturbation of the packed column index, with some head room)
@@ -280,7 +309,8 @@ __global__ void __launch_bounds__(256) coarse_select_kernel(int nc, int d, int n
     // ---- verify groups: a group whose COARSE_T-th kept value is <= tau may hide candidates
     for (int g = tid; g < ngroups; g += 256) {
         const int last = g * COARSE_T + kept - 1;    // the group's last kept value (the GEMM keeps 3 or 4)
-        if (fkey(gv[last]) <= tau && (packed ? gv[last] < 1.0e38f : gi[last] != 0xffffffffu)) {
+        if (entry_key(last) <= tau && (packed == 2 ? gk[last] < COARSE_KEY_INVALID_MIN
+                                                   : (packed ? gv[last] < 1.0e38f : gi[last] != 0xffffffffu))) {
             const uint32_t f = atomicAdd(&s_nflag, 1u);
             if (f < SEL_MAX_FLAGGED) s_flag[f] = (uint32_t)g;
         }
@@ -293,7 +323,7 @@ __global__ void __launch_bounds__(256) coarse_select_kernel(int nc, int d, int n
     }
     // ---- collect: kept entries with key <= tau outside flagged groups, then flagged groups in full
     for (int i = tid; i < n; i += 256) {
-        const uint32_t kx = fkey(gv[i]);
+        const uint32_t kx = entry_key(i);
         if (kx > tau) continue;
         const uint32_t id = entry_id(i);
         if (id != 0xffffffffu) {
@@ -360,7 +390,7 @@ size_t coarse_work_bytes(int nq, int nc, int kprime, int *cand_cap)
 }
 
 cudaError_t launch_coarse_tc(cudaStream_t st, uint64_t *launches, int nq, int nc, int d, const float *queries,
-                             const float *cnorm_gemm, const TcSide &S, float *grp_val, int nterms, int keep);  // coarse_tc.cu
+                             const float *cnorm_gemm, const TcSide &S, float *grp_val, int nterms, int keep, int ikey);  // coarse_tc.cu
 
 cudaError_t launch_coarse(cudaStream_t st, uint64_t *launches, int impl, int nq, int nc, int d, int nprobe,
                           int slack, const float *queries, const float *centroids, const float *cnorm_gemm,
@@ -373,10 +403,12 @@ cudaError_t launch_coarse(cudaStream_t st, uint64_t *launches, int impl, int nq,
     // fewer per accumulator element: -18 % GEMM time at 2^20 centroids); a group whose last kept value passes the
     // threshold is re-scanned in full by the select stage, which is rare only when the top-k spreads over many
     // groups (expected C(k,3) / ngroups^2 per query)
-    const int kept = (impl >= 1 && ngroups >= 2048) ? 3 : COARSE_T;
+    // impl 3 keeps 2 when they are very many (nc >= 2^19): expected C(k', 2) / ngroups expanded groups per query
+    const int kept = (impl >= 3 && ngroups >= 4096) ? 2 : ((impl >= 1 && ngroups >= 2048) ? 3 : COARSE_T);
     cudaError_t e;
     if (impl >= 1) {
-        e = launch_coarse_tc(st, launches, nq, nc, d, queries, cnorm_gemm, S, W.grp_val, impl == 2 ? 1 : 2, kept);
+        e = launch_coarse_tc(st, launches, nq, nc, d, queries, cnorm_gemm, S, W.grp_val, impl >= 2 ? 1 : 2, kept,
+                             impl >= 3 ? 1 : 0);
         if (e != cudaSuccess) return e;
     } else {
         const size_t sm = (size_t)(CG_BK * CG_BM + CG_BK * CG_BN + CG_BM * (CG_BN + 1)) * sizeof(float);
@@ -403,12 +435,12 @@ cudaError_t launch_coarse(cudaStream_t st, uint64_t *launches, int impl, int nq,
         e = cudaFuncSetAttribute(coarse_select_kernel<8>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sm2);
         if (e != cudaSuccess) return e;
         coarse_select_kernel<8><<<nq, 256, sm2, st>>>(nc, d, ngroups, nprobe, kprime, W.cand_cap, queries, centroids,
-                                                      W.grp_val, W.grp_idx, impl >= 1 ? 1 : 0, kept, self_off, impl == 2 ? S.cmax : nullptr, W.err, out_d, out_i);
+                                                      W.grp_val, W.grp_idx, impl >= 3 ? 2 : (impl >= 1 ? 1 : 0), kept, self_off, impl >= 2 ? S.cmax : nullptr, S.qstat, W.err, out_d, out_i);
     } else {
         e = cudaFuncSetAttribute(coarse_select_kernel<16>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sm2);
         if (e != cudaSuccess) return e;
         coarse_select_kernel<16><<<nq, 256, sm2, st>>>(nc, d, ngroups, nprobe, kprime, W.cand_cap, queries, centroids,
-                                                       W.grp_val, W.grp_idx, impl >= 1 ? 1 : 0, kept, self_off, impl == 2 ? S.cmax : nullptr, W.err, out_d, out_i);
+                                                       W.grp_val, W.grp_idx, impl >= 3 ? 2 : (impl >= 1 ? 1 : 0), kept, self_off, impl >= 2 ? S.cmax : nullptr, S.qstat, W.err, out_d, out_i);
     }
     ++*launches;
     return cudaGetLastError();

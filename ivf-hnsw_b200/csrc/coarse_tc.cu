@@ -54,7 +54,9 @@ static __device__ __forceinline__ float pow2_scale_for(float maxabs)
 // otherwise each row has its own scale and fac[row] = -2 / (s_row * s_other) is written.
 __global__ void split_rows_kernel(size_t n, int d, int dp, const float *__restrict__ x,
                                   const uint32_t *__restrict__ shared_max, const uint32_t *__restrict__ other_max,
-                                  __half *__restrict__ hi, __half *__restrict__ lo, float *__restrict__ fac)
+                                  __half *__restrict__ hi, __half *__restrict__ lo, float *__restrict__ fac,
+                                  uint32_t *__restrict__ stat /* [2]: max ||row||^2 bits, any non-zero lo; may be null */,
+                                  int dk /* dims the GEMM uses */)
 {
     const int lane = threadIdx.x & 31;
     const size_t row = (size_t)blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
@@ -72,12 +74,27 @@ __global__ void split_rows_kernel(size_t n, int d, int dp, const float *__restri
         for (int off = 16; off > 0; off >>= 1) m = fmaxf(m, __shfl_xor_sync(IVF_FULL_MASK, m, off));
         s = pow2_scale_for(m);
     }
+    float n2 = 0.f;
+    bool any_lo = false;
     for (int i = lane; i < dp; i += 32) {
         float v = i < d ? xr[i] * s : 0.f;
         const __half h = __float2half_rn(v);
         const __half l = __float2half_rn(v - __half2float(h));
         hi[row * dp + i] = h;
         lo[row * dp + i] = l;
+        if (i < dk) {
+            n2 = fmaf(xr[i], xr[i], n2);
+            any_lo |= (v - __half2float(h)) != 0.f;
+        }
+    }
+    if (stat) {
+#pragma unroll
+        for (int off = 16; off > 0; off >>= 1) n2 += __shfl_xor_sync(IVF_FULL_MASK, n2, off);
+        const bool any = __any_sync(IVF_FULL_MASK, any_lo);
+        if (lane == 0) {
+            if (n2 < 1.0e30f) atomicMax(stat, __float_as_uint(n2 * 1.0001f));   // sums differ by rounding: head room
+            if (any) atomicOr(stat + 1, 1u);
+        }
     }
     if (fac && lane == 0) {
         const float so = pow2_scale_for(__uint_as_float(*other_max));
@@ -98,7 +115,7 @@ cudaError_t launch_tc_prepare_centroids(cudaStream_t st, uint64_t *launches, siz
     maxabs_kernel<<<(unsigned)((nc + 255) / 256 < 1184 ? (nc + 255) / 256 : 1184), 256, 0, st>>>(nc, cnorm_gemm, S.cmax + 1);
     ++*launches;
     split_rows_kernel<<<(unsigned)((nc + 7) / 8), 256, 0, st>>>(nc, d, S.dp, centroids, S.cmax, nullptr, S.chi, S.clo,
-                                                              nullptr);
+                                                              nullptr, nullptr, 0);
     ++*launches;
     return cudaGetLastError();
 }
@@ -188,14 +205,21 @@ struct TcParams {
     int nq, nc, d, db;                // db = ceil(d / 64) column blocks
     int ntile_c, csplit, tiles_per_unit, nunits, nstages;
     int nterms;                       // centroid operand terms: 2 = hi and lo (three products), 1 = hi only (two products)
+    int qterms;                       // query operand terms: 2 = hi and lo, 1 = hi only (impl 3)
+    const uint32_t *cmax;             // [2] bits of max |c component|, max ||c||^2   (integer keys: scale)
+    const uint32_t *qstat;            // [2] bits of max ||q||^2 of the batch, any-lo flag
     const float *cnorm;               // [nc] ||c||^2
     const float *qfac;                // [nq] -2 / (s_q * s_c)
     float *grp_val;                   // [nq][ntile_c][COARSE_T] packed (value | column index)
     uint32_t keep_mask;               // ~127, passed at run time so that packing is ONE lop3 (reg & reg | imm)
+    uint32_t key_mul;                 // 128, passed at run time so that the key is built by ONE IMAD (FMA pipe): a
+                                      // literal power of two becomes a LEA on the ALU pipe, which is the busy one
 };
 
-// KEEP: values kept per (query, group of 128 centroids): 4, or 3 when the groups are many (see launch_coarse)
-template <int MT, int KEEP>
+// KEEP: values kept per (query, group of 128 centroids): 4, or 3 / 2 when the groups are many (see launch_coarse)
+// IKEY: integer keys (impl 3, common.cuh): one FFMA + one IMAD on the FMA pipe build the key, KEEP * 2 - 1 integer
+// min/max insert it -- the ALU pipe (half rate for min/max and logic ops) is what bounds this kernel
+template <int MT, int KEEP, bool IKEY>
 __global__ void __launch_bounds__(TC_THREADS, 1)
 coarse_tc_kernel(const __grid_constant__ CUtensorMap tm_qhi, const __grid_constant__ CUtensorMap tm_qlo,
                  const __grid_constant__ CUtensorMap tm_chi, const __grid_constant__ CUtensorMap tm_clo, TcParams p)
@@ -247,12 +271,12 @@ coarse_tc_kernel(const __grid_constant__ CUtensorMap tm_qhi, const __grid_consta
                 const int t1 = min(t0 + p.tiles_per_unit, p.ntile_c);
                 const int q0 = qt * 128 * MT;
                 mbar_wait(A_EMPTY, a_phase ^ 1);
-                mbar_expect_tx(A_FULL, (uint32_t)(MT * db * 2 * TC_BLOCK_BYTES));
+                mbar_expect_tx(A_FULL, (uint32_t)(MT * db * p.qterms * TC_BLOCK_BYTES));
                 for (int mt = 0; mt < MT; mt++)
                     for (int j = 0; j < db; j++) {
                         const uint32_t dst = smem_u32(sA + (size_t)((mt * db + j) * 2) * TC_BLOCK_BYTES);
                         tma_load_2d(dst, &tm_qhi, j * 64, q0 + mt * 128, A_FULL);
-                        tma_load_2d(dst + TC_BLOCK_BYTES, &tm_qlo, j * 64, q0 + mt * 128, A_FULL);
+                        if (p.qterms == 2) tma_load_2d(dst + TC_BLOCK_BYTES, &tm_qlo, j * 64, q0 + mt * 128, A_FULL);
                     }
                 a_phase ^= 1;
                 for (int t = t0; t < t1; t++) {
@@ -298,8 +322,9 @@ coarse_tc_kernel(const __grid_constant__ CUtensorMap tm_qhi, const __grid_consta
                                 for (int k = 0; k < ks; k++) {
                                     umma_f16(dcol, umma_desc_sw128(a + k * 32), umma_desc_sw128(b + k * 32), idesc,
                                              (j | k) ? 1u : 0u);
-                                    umma_f16(dcol, umma_desc_sw128(a + TC_BLOCK_BYTES + k * 32),
-                                             umma_desc_sw128(b + k * 32), idesc, 1u);
+                                    if (p.qterms == 2)
+                                        umma_f16(dcol, umma_desc_sw128(a + TC_BLOCK_BYTES + k * 32),
+                                                 umma_desc_sw128(b + k * 32), idesc, 1u);
                                 }
                             }
                         }
@@ -341,24 +366,35 @@ coarse_tc_kernel(const __grid_constant__ CUtensorMap tm_qhi, const __grid_consta
             const int t0 = cs * p.tiles_per_unit;
             const int t1 = min(t0 + p.tiles_per_unit, p.ntile_c);
             const int q = qt * 128 * MT + mt * 128 + row;
-            const float f = q < p.nq ? p.qfac[q] : 0.f;
+            float f = q < p.nq ? p.qfac[q] : 0.f;
+            // integer keys: everything is scaled by S (one scale per batch) and biased by the magic constant, so that
+            // ONE fmaf per element yields a float whose bit pattern counts quanta of 128 / S
+            float S = 1.f;
+            if (IKEY) {
+                S = coarse_key_scale(__uint_as_float(p.qstat[0]), __uint_as_float(p.cmax[1]));
+                f *= S;
+            }
+            const float pad_cn = IKEY ? (COARSE_KEY_BIAS - 128.f + COARSE_KEY_MAGIC) : TC_INVALID;
+            const uint32_t key_mul = p.key_mul;
+            auto stage_cn = [&](int c) -> float {
+                if (c >= p.nc) return pad_cn;
+                const float cn = p.cnorm[c];
+                return IKEY ? fmaf(cn, S, COARSE_KEY_MAGIC) : cn;
+            };
             // stage ||c||^2 of the first tile
             {
-                const int c = t0 * 128 + gt;
-                cn_buf[gt] = c < p.nc ? p.cnorm[c] : TC_INVALID;
+                cn_buf[gt] = stage_cn(t0 * 128 + gt);
                 asm volatile("bar.sync %0, 128;" ::"r"(bar_id) : "memory");
             }
             for (int t = t0; t < t1; t++) {
                 const int b = (t - t0) & 1;
-                float cn_next = TC_INVALID;
-                if (t + 1 < t1) {
-                    const int c = (t + 1) * 128 + gt;
-                    if (c < p.nc) cn_next = p.cnorm[c];
-                }
+                float cn_next = pad_cn;
+                if (t + 1 < t1) cn_next = stage_cn((t + 1) * 128 + gt);
                 mbar_wait(T_FULL(as), t_phase);
                 tc_fence_after();
                 const uint32_t taddr = tmem_base + ((uint32_t)(quarter * 32) << 16) + (uint32_t)(as * MT * 128 + mt * 128);
                 float a0 = TC_INVALID, a1 = TC_INVALID, a2 = TC_INVALID, a3 = TC_INVALID;   // KEEP == 3: the 4th slot stays empty
+                uint32_t k0 = 0xffffffffu, k1 = 0xffffffffu, k2 = 0xffffffffu, k3 = 0xffffffffu;
                 uint32_t v[2][32];
                 tmem_ld32(taddr, v[0]);
 #pragma unroll
@@ -383,24 +419,49 @@ coarse_tc_kernel(const __grid_constant__ CUtensorMap tm_qhi, const __grid_consta
                             if (i) continue;
 #endif
                             const float val = fmaf(__uint_as_float(v[jb & 1][i]), f, cnv[ii]);
-                            const float x = __uint_as_float((__float_as_uint(val) & p.keep_mask) | (uint32_t)(jb * 32 + i));
-                            // sorted insert into the KEEP best of the group: 7 or 5 min/max (with two products per
-                            // k-step the epilogue's ALU pipe, not the MMA side, bounds the kernel)
-                            const float m0 = fmaxf(a0, x);
-                            a0 = fminf(a0, x);
-                            const float m1 = fmaxf(a1, m0);
-                            a1 = fminf(a1, m0);
-                            if (KEEP == 4) {
-                                const float m2 = fmaxf(a2, m1);
-                                a2 = fminf(a2, m1);
-                                a3 = fminf(a3, m2);
-                            } else a2 = fminf(a2, m1);
+                            if (IKEY) {
+                                // val in [2^30, 2^31): its bits count quanta.  (bits - bits(2^30)) * 128 + column in one
+                                // multiply-add that wraps mod 2^32 (the FMA pipe; the ALU pipe keeps the min/max)
+                                uint32_t key;
+                                const uint32_t cst = (uint32_t)(jb * 32 + i) - (0x4e800000u << 7);
+                                asm("mad.lo.u32 %0, %1, %2, %3;" : "=r"(key) : "r"(__float_as_uint(val)), "r"(key_mul), "r"(cst));
+                                const uint32_t m0 = max(k0, key);
+                                k0 = min(k0, key);
+                                if (KEEP == 2) k1 = min(k1, m0);
+                                else {
+                                    const uint32_t m1 = max(k1, m0);
+                                    k1 = min(k1, m0);
+                                    if (KEEP == 4) {
+                                        const uint32_t m2 = max(k2, m1);
+                                        k2 = min(k2, m1);
+                                        k3 = min(k3, m2);
+                                    } else k2 = min(k2, m1);
+                                }
+                            } else {
+                                const float x = __uint_as_float((__float_as_uint(val) & p.keep_mask) | (uint32_t)(jb * 32 + i));
+                                // sorted insert into the KEEP best of the group: 7 or 5 min/max (with two products per
+                                // k-step the epilogue's ALU pipe, not the MMA side, bounds the kernel)
+                                const float m0 = fmaxf(a0, x);
+                                a0 = fminf(a0, x);
+                                const float m1 = fmaxf(a1, m0);
+                                a1 = fminf(a1, m0);
+                                if (KEEP == 4) {
+                                    const float m2 = fmaxf(a2, m1);
+                                    a2 = fminf(a2, m1);
+                                    a3 = fminf(a3, m2);
+                                } else a2 = fminf(a2, m1);
+                            }
                         }
                     }
                 }
-                if (q < p.nq)
-                    *reinterpret_cast<float4 *>(p.grp_val + ((size_t)q * p.ntile_c + t) * COARSE_T) =
-                        make_float4(a0, a1, a2, a3);
+                if (q < p.nq) {
+                    if (IKEY)
+                        *reinterpret_cast<uint4 *>(p.grp_val + ((size_t)q * p.ntile_c + t) * COARSE_T) =
+                            make_uint4(k0, k1, k2, k3);
+                    else
+                        *reinterpret_cast<float4 *>(p.grp_val + ((size_t)q * p.ntile_c + t) * COARSE_T) =
+                            make_float4(a0, a1, a2, a3);
+                }
                 cn_buf[(b ^ 1) * 128 + gt] = cn_next;
                 asm volatile("bar.sync %0, 128;" ::"r"(bar_id) : "memory");
                 if (++as == 2) { as = 0; t_phase ^= 1; }
@@ -450,14 +511,16 @@ static bool make_map(CUtensorMap *m, const void *base, size_t rows, int d, int d
 bool coarse_tc_supported(int d) { return d >= 16 && d <= 256; }
 
 cudaError_t launch_coarse_tc(cudaStream_t st, uint64_t *launches, int nq, int nc, int d, const float *queries,
-                             const float *cnorm_gemm, const TcSide &S, float *grp_val, int nterms, int keep)
+                             const float *cnorm_gemm, const TcSide &S, float *grp_val, int nterms, int keep, int ikey)
 {
     if (!coarse_tc_supported(d)) return cudaErrorNotSupported;
-    // split the query rows (per-row power-of-two scale)
+    // split the query rows (per-row power-of-two scale); batch statistics for the integer-key scale / select margin
+    cudaError_t e = cudaMemsetAsync(S.qstat, 0, 8, st);
+    if (e != cudaSuccess) return e;
     split_rows_kernel<<<(unsigned)((nq + 7) / 8), 256, 0, st>>>((size_t)nq, d, S.dp, queries, nullptr, S.cmax, S.qhi,
-                                                               S.qlo, S.qfac);
+                                                               S.qlo, S.qfac, S.qstat, coarse_dims(d));
     ++*launches;
-    cudaError_t e = cudaGetLastError();
+    e = cudaGetLastError();
     if (e != cudaSuccess) return e;
 
     // only the dims fstdistfunc uses take part; the tensor maps zero-fill beyond them
@@ -470,6 +533,8 @@ cudaError_t launch_coarse_tc(cudaStream_t st, uint64_t *launches, int nq, int nc
     TcParams p;
     p.nq = nq; p.nc = nc; p.d = dk; p.db = (dk + 63) / 64;
     p.nterms = nterms;
+    p.qterms = ikey ? 1 : 2;
+    p.cmax = S.cmax; p.qstat = S.qstat;
     const int MT = p.db <= 2 ? 2 : 1;
     p.ntile_c = (nc + 127) / 128;
     const int nqt = (nq + 128 * MT - 1) / (128 * MT);
@@ -494,17 +559,22 @@ cudaError_t launch_coarse_tc(cudaStream_t st, uint64_t *launches, int nq, int nc
     if (nst > 8) nst = 8;
     if (nst < 2) return cudaErrorNotSupported;
     p.nstages = nst;
-    p.cnorm = cnorm_gemm; p.qfac = S.qfac; p.grp_val = grp_val; p.keep_mask = ~127u;
+    p.cnorm = cnorm_gemm; p.qfac = S.qfac; p.grp_val = grp_val; p.keep_mask = ~127u; p.key_mul = 128u;
     const size_t smem = fixed + a_bytes + (size_t)nst * TC_BLOCK_BYTES;
     const int grid = p.nunits < 148 ? p.nunits : 148;
-#define IVF_TC_LAUNCH(MTV, KV)                                                                                     \
-    do {                                                                                                           \
-        e = cudaFuncSetAttribute(coarse_tc_kernel<MTV, KV>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem); \
-        if (e != cudaSuccess) return e;                                                                            \
-        coarse_tc_kernel<MTV, KV><<<grid, TC_THREADS, smem, st>>>(m_qhi, m_qlo, m_chi, m_clo, p);                  \
+#define IVF_TC_LAUNCH(MTV, KV, IK)                                                                                     \
+    do {                                                                                                               \
+        e = cudaFuncSetAttribute(coarse_tc_kernel<MTV, KV, IK>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem); \
+        if (e != cudaSuccess) return e;                                                                                \
+        coarse_tc_kernel<MTV, KV, IK><<<grid, TC_THREADS, smem, st>>>(m_qhi, m_qlo, m_chi, m_clo, p);                  \
     } while (0)
-    if (MT == 2) { if (keep == 3) IVF_TC_LAUNCH(2, 3); else IVF_TC_LAUNCH(2, 4); }
-    else { if (keep == 3) IVF_TC_LAUNCH(1, 3); else IVF_TC_LAUNCH(1, 4); }
+    if (ikey) {
+        if (MT == 2) { if (keep == 2) IVF_TC_LAUNCH(2, 2, true); else if (keep == 3) IVF_TC_LAUNCH(2, 3, true); else IVF_TC_LAUNCH(2, 4, true); }
+        else { if (keep == 2) IVF_TC_LAUNCH(1, 2, true); else if (keep == 3) IVF_TC_LAUNCH(1, 3, true); else IVF_TC_LAUNCH(1, 4, true); }
+    } else {
+        if (MT == 2) { if (keep == 3) IVF_TC_LAUNCH(2, 3, false); else IVF_TC_LAUNCH(2, 4, false); }
+        else { if (keep == 3) IVF_TC_LAUNCH(1, 3, false); else IVF_TC_LAUNCH(1, 4, false); }
+    }
 #undef IVF_TC_LAUNCH
     ++*launches;
     return cudaGetLastError();

@@ -22,6 +22,23 @@
 #define COARSE_GROUP 128
 #define COARSE_T 4
 
+// impl 3 of the coarse stage keeps order-preserving integer keys instead of floats:
+//   t   = v * S + 1.5 * 2^30      (S = power of two with |v| * S < 2^22 for every (query, centroid) of the batch)
+//   key = ((bits(t) - bits(2^30)) << 7) + column          t in [2^30, 2^31) has ulp 128: bits(t) counts quanta
+// i.e. key = round(v * S / 128) * 128 + 2^29 + column, < 2^30.  Padding columns get the largest quantum.
+#define COARSE_KEY_MAGIC 1610612736.0f             /* 1.5 * 2^30 */
+#define COARSE_KEY_BIAS 536870912.0f               /* 2^29: key ~ v * S + 2^29 */
+#define COARSE_KEY_INVALID_MIN 0x3fffff80u         /* quantum 2^23 - 1: reserved for padding columns */
+static __host__ __device__ __forceinline__ float coarse_key_scale(float qmax2, float cmax2)
+{
+    // bound of |v| = | ||c||^2 - 2<q,c> | over the batch, then the largest power of two S with bound * S <= 2^22
+    const float bound = cmax2 + 2.f * sqrtf(qmax2 * cmax2);
+    if (!(bound > 0.f) || !(bound < 1.0e30f)) return 1.f;
+    int ex;
+    frexpf(bound, &ex);                 // bound = m * 2^ex, m in [0.5, 1)
+    return ldexpf(1.f, 22 - ex);
+}
+
 static __device__ __forceinline__ uint32_t lane_id() { return threadIdx.x & 31; }
 
 static __device__ __forceinline__ uint32_t prmt(uint32_t a, uint32_t b, uint32_t sel)

@@ -96,7 +96,7 @@ struct ivfhnsw_b200 {
     DevBuf w_a, w_b, w_c, w_d2, w_e, w_f, w_cub, w_small;
     DevBuf counters;  // [0] scanned, [1] walked
     // options / stats
-    long coarse_slack = 8, coarse_impl = 2, scan_split = 0, query_batch = 0, debug = 0;
+    long coarse_slack = 8, coarse_impl = 3, scan_split = 0, query_batch = 0, debug = 0;
     long long stage_bytes = 4ll << 30;   // raw Grouping points staged before add_group encodes them (option "stage_bytes")
     bool timing = false;
     ivfhnsw_b200_stats_t stats{};

@@ -40,6 +40,10 @@ struct SegTables {
     float *threshold;     // [nq]
     uint32_t *nscanned;   // [nq] codes the reference rule scans (all shards)
     uint32_t *nwalked;    // [nq] codes of the ACTIVE lists (what a scan without kept-run tiling would stream; all shards)
+    // PACKED records (sharded search, see launch_pack_records): query q's record starts at rec + qoff[q] and holds
+    // only qnp[q] probes -- the ones the receiving rank owns -- in the same field order; null = the fixed layout
+    const uint32_t *qoff = nullptr;
+    const uint32_t *qnp = nullptr;
     __host__ __device__ uint32_t *slot(size_t q) const { return rec + q * stride; }                  // first slot of the list
     __host__ __device__ uint32_t *n(size_t q) const { return rec + q * stride + nprobe; }             // codes to walk (0 = skipped)
     __host__ __device__ float *base(size_t q) const { return reinterpret_cast<float *>(rec + q * stride + 2 * nprobe); }   // term1 (IVFADC)
@@ -52,6 +56,13 @@ static inline size_t seg_record_words(int nprobe, int nsubc)
     return ((size_t)5 * nprobe + (size_t)nprobe * nsubc + 3) & ~(size_t)3;
 }
 
+// Sharded search: split the fixed-stride records of nq queries into `nparts` packed streams, one per owning rank
+// (equal centroid ranges of ceil(nc / nparts)): part r receives, per query, a mini record [slot][n][base][seq][cid]
+// [sub_base] of the probes whose centroid rank r owns and that the max_codes rule scans, in probe order.
+//   out[pbase[r] + off[r][q] ...], cnt[r][q] probes, pwords[r] 32-bit words in part r (pbase = their exclusive scan)
+cudaError_t launch_pack_records(cudaStream_t st, uint64_t *launches, int nq, int nprobe, int nsubc, int nc, int nparts,
+                                const uint32_t *rec, size_t stride, uint32_t *out, uint32_t *cnt, uint32_t *off,
+                                unsigned long long *pwords);
 cudaError_t launch_prep_adc(cudaStream_t st, uint64_t *launches, int nq, int nprobe, uint64_t max_codes,
                             const float *coarse_d, const uint32_t *coarse_i, const DeviceLists &L, const SegTables &T);
 
@@ -123,6 +134,7 @@ struct TcSide {
     uint32_t *cmax;         // [2] bits of max |centroid component|, bits of max ||c||^2
     __half *qhi, *qlo;      // [batch][dp]
     float *qfac;            // [batch] -2 / (query scale * centroid scale)
+    uint32_t *qstat;        // [2] impl 3: bits of max ||q||^2 over the batch, 1 if any query has a non-zero lo part
     int dp;
 };
 bool coarse_tc_supported(int d);
@@ -132,6 +144,9 @@ cudaError_t launch_tc_prepare_centroids(cudaStream_t st, uint64_t *launches, siz
 // impl 0: fp32 SIMT tile GEMM; impl 1: tcgen05 split-fp16 GEMM, three products (needs the TcSide operands);
 // impl 2: the same with two products (q.c_hi + q_lo.c_hi): the dropped q.c_lo term is bounded by
 // 2^-11 ||q|| ||c|| and the select stage widens its threshold by twice that bound.
+// impl 3: ONE product (q_hi.c_hi), both cross terms covered by the select margin (q_lo == 0 exactly for byte-valued
+// vectors: then only the centroid term counts), values kept as order-preserving INTEGER keys (quantised value * 128 +
+// column, built on the FMA pipe) and 2 kept per group when the groups are many.
 cudaError_t launch_coarse(cudaStream_t st, uint64_t *launches, int impl, int nq, int nc, int d, int nprobe,
                           int slack, const float *queries, const float *centroids, const float *cnorm_gemm,
                           const TcSide &S, const CoarseWork &W, int self_off /* -1 = none */,

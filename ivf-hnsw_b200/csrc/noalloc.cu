@@ -89,7 +89,7 @@ extern "C" int ivfhnsw_b200_coarse_noalloc_dev(ivfhnsw_b200_t *h, size_t nq, con
     W.cand_d = nullptr;
     W.err = flags;
     W.cand_cap = cand_cap;
-    TcSide S{};   // the tensor-core operands are not used by impl 0
+    TcSide S{};   // the tensor-core operands are not used by impl 0 (all pointers null)
     CU(launch_coarse(st, LAUNCHES, /*impl=*/0, (int)nq, (int)h->nc, (int)h->d, (int)nprobe, slack, xq_dev,
                      h->centroids.as<float>(), cnorm, S, W, -1, dists_dev, idxs_dev, nullptr));
     if (flags_dev) CU(cudaMemcpyAsync(flags_dev, flags, 4, cudaMemcpyDeviceToDevice, st));

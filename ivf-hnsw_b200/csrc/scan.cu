@@ -1140,12 +1140,16 @@ __global__ void __launch_bounds__(SCAN_THREADS) scan_kernel(ScanArgs a)
 
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     const int q = blockIdx.x / a.nsplit, split = blockIdx.x - q * a.nsplit;
-    const int nprobe = a.nprobe, k = a.k;
+    const int k = a.k;
+    // fixed-stride record of a.nprobe probes, or a packed one holding only the probes this rank owns
+    const int nprobe = a.T.qnp ? (int)a.T.qnp[q] : a.nprobe;
+    const uint32_t *rec = a.T.qoff ? a.T.rec + a.T.qoff[q] : a.T.rec + (size_t)q * a.T.stride;
+    const float *rec_sub_base = reinterpret_cast<const float *>(rec + 5 * (size_t)nprobe);
 
     // ---- stage the query's segment tables (keeping only the lists this GPU owns) and initialise the top-k
     {
-        const uint32_t *r_slot = a.T.slot(q), *r_n = a.T.n(q), *r_seq = a.T.seq(q), *r_cid = a.T.cid(q);
-        const float *r_base = a.T.base(q);
+        const uint32_t *r_slot = rec, *r_n = rec + nprobe, *r_seq = rec + 3 * (size_t)nprobe, *r_cid = rec + 4 * (size_t)nprobe;
+        const float *r_base = reinterpret_cast<const float *>(rec + 2 * (size_t)nprobe);
         for (int i = tid; i < nprobe; i += SCAN_THREADS) {
             const uint32_t c = r_cid[i];
             s_slot[i] = r_slot[i];
@@ -1302,7 +1306,7 @@ __global__ void __launch_bounds__(SCAN_THREADS) scan_kernel(ScanArgs a)
         const bool sb_regs = a.nsubc <= 64;
         if (GROUPING) {
             const float pinf = __int_as_float(0x7f800000);
-            const float *sbg = a.T.sub_base(q) + (size_t)seg * a.nsubc;
+            const float *sbg = rec_sub_base + (size_t)seg * a.nsubc;
             if (sb_regs) {
                 sb0 = lane < a.nsubc ? __ldg(sbg + lane) : pinf;
                 sb1 = lane + 32 < a.nsubc ? __ldg(sbg + lane + 32) : pinf;
@@ -1657,6 +1661,125 @@ cudaError_t launch_scan(cudaStream_t st, uint64_t *launches, int M, bool groupin
 #undef IVF_SCAN_CASE
     --*launches;
     return cudaErrorInvalidValue;
+}
+
+// =============================================================================================
+// Sharded search: records -> one packed stream per owning rank (kernels.h launch_pack_records).
+// The preparation (coarse stage, pruning pass, max_codes cut) runs on the query's HOME rank; a scanning rank needs,
+// per query, only the probes it owns.  Shipping exactly those (an all-to-all-v of ~(5 + nsubc) words per owned probe)
+// instead of all-gathering every 35 KB record is what lets the list-sharded layout scale.
+// =============================================================================================
+#define PACK_MAX_PARTS 64
+__global__ void __launch_bounds__(128) pack_count_kernel(int nprobe, int nc_per, int nparts, const uint32_t *__restrict__ rec,
+                                                         size_t stride, int nq, uint32_t *__restrict__ cnt)
+{
+    __shared__ uint32_t s_cnt[PACK_MAX_PARTS];
+    const int q = blockIdx.x;
+    for (int r = threadIdx.x; r < nparts; r += 128) s_cnt[r] = 0;
+    __syncthreads();
+    const uint32_t *rn = rec + (size_t)q * stride + nprobe, *rc = rec + (size_t)q * stride + 4 * (size_t)nprobe;
+    for (int i = threadIdx.x; i < nprobe; i += 128)
+        if (rn[i]) atomicAdd(&s_cnt[min((int)(rc[i] / (uint32_t)nc_per), nparts - 1)], 1u);
+    __syncthreads();
+    for (int r = threadIdx.x; r < nparts; r += 128) cnt[(size_t)r * nq + q] = s_cnt[r];
+}
+
+// one CTA per part: off[r][q] = exclusive scan over q of cnt[r][q] * W; pwords[r] = total
+__global__ void __launch_bounds__(1024) pack_scan_kernel(int nq, int W, const uint32_t *__restrict__ cnt,
+                                                         uint32_t *__restrict__ off, unsigned long long *__restrict__ pwords)
+{
+    __shared__ unsigned long long s_v[1024];
+    __shared__ unsigned long long carry;
+    const int r = blockIdx.x;
+    if (threadIdx.x == 0) carry = 0;
+    __syncthreads();
+    for (int base = 0; base < nq; base += 1024) {
+        const int q = base + threadIdx.x;
+        const unsigned long long w = q < nq ? (unsigned long long)cnt[(size_t)r * nq + q] * W : 0ull;
+        s_v[threadIdx.x] = w;
+        __syncthreads();
+        for (int o = 1; o < 1024; o <<= 1) {
+            const unsigned long long t = (int)threadIdx.x >= o ? s_v[threadIdx.x - o] : 0ull;
+            __syncthreads();
+            s_v[threadIdx.x] += t;
+            __syncthreads();
+        }
+        if (q < nq) off[(size_t)r * nq + q] = (uint32_t)(carry + s_v[threadIdx.x] - w);
+        __syncthreads();
+        if (threadIdx.x == 1023) carry += s_v[1023];
+        __syncthreads();
+    }
+    if (threadIdx.x == 0) pwords[r] = carry;
+}
+
+__global__ void __launch_bounds__(128) pack_fill_kernel(int nprobe, int nsubc, int nc_per, int nparts,
+                                                        const uint32_t *__restrict__ rec, size_t stride, int nq,
+                                                        const uint32_t *__restrict__ cnt, const uint32_t *__restrict__ off,
+                                                        const unsigned long long *__restrict__ pwords,
+                                                        uint32_t *__restrict__ out)
+{
+    extern __shared__ uint32_t pk_sm[];
+    uint32_t *s_dst = pk_sm;                 // [nprobe] word offset of the probe's mini record start in `out`, ~0 = dropped
+    uint32_t *s_pos = s_dst + nprobe;        // [nprobe] position inside its (query, part)
+    uint32_t *s_np = s_pos + nprobe;         // [nprobe] probes of its (query, part)
+    __shared__ unsigned long long s_pbase[PACK_MAX_PARTS];
+    const int q = blockIdx.x, tid = threadIdx.x, lane = tid & 31;
+    const uint32_t *r0 = rec + (size_t)q * stride;
+    if (tid == 0) {
+        unsigned long long run = 0;
+        for (int r = 0; r < nparts; r++) { s_pbase[r] = run; run += pwords[r]; }
+    }
+    __syncthreads();
+    if (tid < 32) {
+        // order-preserving position of every kept probe among the probes of its part: ballots per part
+        uint32_t run[1];
+        for (int r = 0; r < nparts; r++) {
+            run[0] = 0;
+            const uint32_t np = cnt[(size_t)r * nq + q];
+            const unsigned long long start = s_pbase[r] + off[(size_t)r * nq + q];
+            for (int b = 0; b < nprobe; b += 32) {
+                const int i = b + lane;
+                const bool mine = i < nprobe && r0[nprobe + i] != 0u &&
+                                  min((int)(r0[4 * (size_t)nprobe + i] / (uint32_t)nc_per), nparts - 1) == r;
+                const uint32_t bal = __ballot_sync(IVF_FULL_MASK, mine);
+                if (mine) {
+                    s_pos[i] = run[0] + __popc(bal & ((1u << lane) - 1u));
+                    s_np[i] = np;
+                    s_dst[i] = (uint32_t)start;     // part streams are < 2^32 words (checked on the host)
+                }
+                run[0] += __popc(bal);
+            }
+        }
+        for (int i = lane; i < nprobe; i += 32)
+            if (r0[nprobe + i] == 0u) s_dst[i] = 0xffffffffu;
+    }
+    __syncthreads();
+    // the five scalar fields
+    for (int e = tid; e < 5 * nprobe; e += 128) {
+        const int f = e / nprobe, i = e - f * nprobe;
+        if (s_dst[i] != 0xffffffffu) out[(size_t)s_dst[i] + (size_t)f * s_np[i] + s_pos[i]] = r0[(size_t)f * nprobe + i];
+    }
+    // sub-group bases: coalesced rows of nsubc words
+    for (int e = tid; e < nprobe * nsubc; e += 128) {
+        const int i = e / nsubc, sg = e - i * nsubc;
+        if (s_dst[i] != 0xffffffffu)
+            out[(size_t)s_dst[i] + 5 * (size_t)s_np[i] + (size_t)s_pos[i] * nsubc + sg] = r0[5 * (size_t)nprobe + e];
+    }
+}
+
+cudaError_t launch_pack_records(cudaStream_t st, uint64_t *launches, int nq, int nprobe, int nsubc, int nc, int nparts,
+                                const uint32_t *rec, size_t stride, uint32_t *out, uint32_t *cnt, uint32_t *off,
+                                unsigned long long *pwords)
+{
+    if (nq == 0) return cudaSuccess;
+    if (nparts < 1 || nparts > PACK_MAX_PARTS) return cudaErrorInvalidValue;
+    const int nc_per = (nc + nparts - 1) / nparts;
+    pack_count_kernel<<<nq, 128, 0, st>>>(nprobe, nc_per, nparts, rec, stride, nq, cnt);
+    pack_scan_kernel<<<nparts, 1024, 0, st>>>(nq, 5 + nsubc, cnt, off, pwords);
+    pack_fill_kernel<<<nq, 128, (size_t)nprobe * 12, st>>>(nprobe, nsubc, nc_per, nparts, rec, stride, nq, cnt, off, pwords,
+                                                          out);
+    *launches += 3;
+    return cudaGetLastError();
 }
 
 // =============================================================================================

@@ -52,3 +52,69 @@ def gather_tables(dist, tables, rank, per, group=None):
     rank r has filled rows [r * per, (r + 1) * per) (ivfhnsw_b200_prepare_dev); afterwards every rank of the shard
     group holds all records."""
     dist.all_gather_into_tensor(tables, tables[rank * per:(rank + 1) * per], group=group)
+
+
+class PackedShardedSearch:
+    """The list-sharded search of SURVEY.md 8(e) without an all-gather of whole records.
+
+    Every rank is the HOME of `nq_home` queries per step (rows [rank * nq_home, (rank + 1) * nq_home) of the batch
+    `q_all`, which every rank holds).  Per step:
+      1. home: coarse stage + pruning pass + max_codes cut of the home queries      (ivfhnsw_b200_prepare_dev)
+      2. home: records -> one packed stream per owning rank                          (ivfhnsw_b200_pack_records_dev)
+      3. the stream lengths are all-gathered (world x world numbers; the ONE host read of the step), then ONE
+         all-to-all-v moves the streams and one fixed all-to-all the per-query (count, offset) tables
+      4. every rank scans the lists it owns for the queries of all ranks            (ivfhnsw_b200_scan_packed_dev)
+      5. the partial top-k lists go back to the queries' homes (fixed all-to-all) and are merged there by
+         (distance, global scan order): bit-identical to a single-GPU search        (ivfhnsw_b200_merge_partials_dev)
+    Backend agnostic (`nccl` on the GPUs, `gloo` in the CPU tests of the exchange arithmetic)."""
+
+    def __init__(self, torch, dist, index, rank, world, nq_home, k, device, group=None):
+        self.torch, self.dist, self.idx, self.rank, self.world = torch, dist, index, rank, world
+        self.nq_home, self.k, self.group = nq_home, k, group
+        nqt = nq_home * world
+        i32, f32, i64 = torch.int32, torch.float32, torch.int64
+        rec_words = index.tables_bytes() // 4
+        self.tables = torch.empty(nq_home, rec_words, dtype=i32, device=device)
+        self.packed = torch.empty(nq_home * rec_words, dtype=i32, device=device)
+        self.cnt = torch.empty(world, nq_home, dtype=i32, device=device)            # [part][query] probes
+        self.off = torch.empty(world, nq_home, dtype=i32, device=device)            # [part][query] word offset in its stream
+        self.meta_in = torch.empty(world, 2, nq_home, dtype=i32, device=device)     # [source][cnt | off][query]
+        self.pwords = torch.empty(world, dtype=i64, device=device)
+        self.pw_all = torch.empty(world, world, dtype=i64, device=device)
+        self.pD = torch.empty(nqt, k, dtype=f32, device=device)
+        self.pS = torch.empty(nqt, k, dtype=i32, device=device)
+        self.pL = torch.empty(nqt, k, dtype=i64, device=device)
+        self.gD = torch.empty(world, nq_home, k, dtype=f32, device=device)
+        self.gS = torch.empty(world, nq_home, k, dtype=i32, device=device)
+        self.gL = torch.empty(world, nq_home, k, dtype=i64, device=device)
+        self.D = torch.empty(nq_home, k, dtype=f32, device=device)
+        self.L = torch.empty(nq_home, k, dtype=i64, device=device)
+        self.last_recv_words = 0
+
+    @staticmethod
+    def recv_layout(torch, meta_in, recv_words):
+        """(qoff, qnp) of all queries from the received (count, offset) tables: source s's stream starts where the
+        streams of the sources before it end."""
+        base = torch.cumsum(recv_words, 0) - recv_words                     # exclusive scan, int64
+        qoff = (meta_in[:, 1, :].to(torch.int64) + base[:, None]).to(torch.int32)
+        return qoff.reshape(-1).contiguous(), meta_in[:, 0, :].reshape(-1).contiguous()
+
+    def search(self, q_all):
+        torch, dist, idx, r, W, nh = self.torch, self.dist, self.idx, self.rank, self.world, self.nq_home
+        q_home = q_all[r * nh:(r + 1) * nh]
+        idx.prepare_dev(q_home, 0, nh, self.tables)
+        idx.pack_records_dev(nh, self.tables, W, self.packed, self.cnt, self.off, self.pwords)
+        dist.all_gather_into_tensor(self.pw_all.view(-1), self.pwords, group=self.group)
+        pw = self.pw_all.cpu()                                              # the step's one host read
+        send = [int(v) for v in pw[r]]
+        recv = [int(v) for v in pw[:, r]]
+        self.last_recv_words = sum(recv)
+        blob = torch.empty(max(1, sum(recv)), dtype=torch.int32, device=q_all.device)
+        dist.all_to_all_single(blob[:sum(recv)], self.packed[:sum(send)], recv, send, group=self.group)
+        dist.all_to_all_single(self.meta_in, torch.stack((self.cnt, self.off), 1), group=self.group)
+        qoff, qnp = self.recv_layout(torch, self.meta_in, self.pw_all[:, r])
+        idx.scan_packed_dev(self.k, q_all, blob, qoff, qnp, self.pD, self.pS, self.pL)
+        for out, part in ((self.gD, self.pD), (self.gS, self.pS), (self.gL, self.pL)):
+            dist.all_to_all_single(out.view(-1, self.k), part, group=self.group)
+        idx.merge_partials_dev(self.k, nh, W, self.gD, self.gS, self.gL, self.D, self.L)
+        return self.D, self.L

@@ -24,10 +24,12 @@ def test_coarse_at_bench_centroid_counts(nc, d):
     C = torch.randn(nc, d, device=dev, generator=g)
     nq = 300
     Q = C[torch.randint(0, nc, (nq,), device=dev, generator=g)] + 0.5 * torch.randn(nq, d, device=dev, generator=g)
+    Q[1] = 0                                              # a zero query next to full-norm ones (one key scale per batch)
+    Q[2] = Q[2].round()                                   # exactly representable in fp16: no lo part
     idx = pkg.IndexIVF_HNSW(d, nc, 8, 8)
     idx.build_quantizer(centroids=C.cpu().numpy())
     dd = _brute(torch, Q, C, (d // 16) * 16)
-    for impl in (1, 2):
+    for impl in (1, 2, 3):
         idx.set_option("coarse_impl", impl)
         for nprobe in (1, 64, 128):
             cd = torch.empty(nq, nprobe, device=dev)

@@ -1,5 +1,7 @@
 """GPU parity tests: the CUDA path (through the C ABI) against the golden fixtures of the compiled
 reference and against the plain-C port, on the reference's own candidate lists (search2 seam)."""
+import importlib
+
 import numpy as np
 import pytest
 
@@ -73,11 +75,11 @@ def test_search_splits_and_port(port, name, split):
 
 
 @pytest.mark.parametrize("name", golden_names())
-@pytest.mark.parametrize("impl", [0, 1, 2])
+@pytest.mark.parametrize("impl", [0, 1, 2, 3])
 def test_coarse_exact_matches_port(port, name, impl):
     """K-A2: exact nprobe nearest centroids, ascending (dist, idx), fstdistfunc numerics; impl 0 is the
     fp32 SIMT GEMM, impl 1 the tcgen05 split-fp16 GEMM with three products, impl 2 the same with two products and
-    a widened select threshold -- all feed the same exact re-rank."""
+    a widened select threshold, impl 3 (default) ONE product with integer keys -- all feed the same exact re-rank."""
     pkg = load_pkg()
     g, ix, runs = load_golden(name)
     nprobe = int(g["nprobe"])
@@ -135,18 +137,19 @@ def test_coarse_tensor_core_vs_brute_force(shape, spread):
     idx = pkg.IndexIVF_HNSW(d, nc, 8, 8)
     idx.build_quantizer(centroids=C)
     res = {}
-    for impl in (0, 1, 2):
+    for impl in (0, 1, 2, 3):
         idx.set_option("coarse_impl", impl)
         res[impl] = idx.coarse(Q, nprobe)
     dd = ((Q.astype(np.float64)[:, None, :(d // 16) * 16] - C.astype(np.float64)[None, :, :(d // 16) * 16]) ** 2).sum(-1)
     want = np.sort(dd, axis=1)[:, :nprobe]
-    for impl in (0, 1, 2):
+    for impl in (0, 1, 2, 3):
         cd, ci = res[impl]
         assert np.allclose(cd, want, rtol=2e-5, atol=1e-5 * spread * spread), impl
         got = np.take_along_axis(dd, ci.astype(np.int64), 1)
         assert np.allclose(got, want, rtol=2e-5, atol=1e-5 * spread * spread), impl
     assert np.mean(res[0][1] == res[1][1]) >= 0.999
     assert np.mean(res[0][1] == res[2][1]) >= 0.999
+    assert np.mean(res[0][1] == res[3][1]) >= 0.999
     idx.close()
 
 
@@ -237,7 +240,7 @@ def test_operating_point_corners(port, name, nprobe, max_codes, k):
     idx.close()
 
 
-@pytest.mark.parametrize("impl", [1, 2])
+@pytest.mark.parametrize("impl", [1, 2, 3])
 @pytest.mark.parametrize("nprobe", [1, 40])
 def test_coarse_long_rows_vs_brute_force(nprobe, impl):
     """nc large enough (>= 2^18) for the select kernel's long-row path (threshold from the per-thread minima) and for
@@ -258,4 +261,55 @@ def test_coarse_long_rows_vs_brute_force(nprobe, impl):
     got = np.take_along_axis(dd, ci.astype(np.int64), 1)
     assert np.allclose(got, want, rtol=2e-5, atol=1e-4)
     assert np.all(np.diff(cd, axis=1) >= 0)
+    idx.close()
+
+
+@pytest.mark.parametrize("name", ["grp_sift_m16", "adc_sift_m16", "grp_long_m16"])
+def test_packed_records_sharded_search_equals_single_gpu(name):
+    """The all-to-all form of the sharded search on ONE GPU: records -> one packed stream per owning rank
+    (pack_records_dev, checked word for word against the numpy statement tests/pack_ref.py), every 'rank' scans its
+    lists from its stream (scan_packed_dev), the merged answer equals the unsharded search bit for bit."""
+    import torch
+    import pack_ref
+    pkg = load_pkg()
+    sharding = importlib.import_module("ivf-hnsw_b200.sharding")
+    g, ix, runs = load_golden(name)
+    k, nprobe = int(g["k"]), int(g["nprobe"])
+    idx = make_index(pkg, ix)
+    idx.load_index_dict(ix)
+    idx.nprobe = nprobe
+    tag, mc, pr = runs[-1]
+    idx.max_codes, idx.do_pruning = mc, pr
+    dev = torch.device("cuda:0")
+    Q = torch.from_numpy(np.ascontiguousarray(g["Q"])).to(dev)
+    nq, W = Q.shape[0], 3
+    D0 = torch.empty(nq, k, device=dev); L0 = torch.empty(nq, k, dtype=torch.int64, device=dev)
+    idx.search_dev(k, Q, D0, L0)
+    words = idx.tables_bytes() // 4
+    assert words == pack_ref.record_words(nprobe, ix["nsubc"])
+    tables = torch.zeros(nq, words, dtype=torch.int32, device=dev)
+    idx.prepare_dev(Q, 0, nq, tables)
+    packed = torch.full((nq * words,), -1, dtype=torch.int32, device=dev)
+    cnt = torch.zeros(W, nq, dtype=torch.int32, device=dev)
+    off = torch.zeros(W, nq, dtype=torch.int32, device=dev)
+    pw = torch.zeros(W, dtype=torch.int64, device=dev)
+    idx.pack_records_dev(nq, tables, W, packed, cnt, off, pw)
+    torch.cuda.synchronize()
+    streams, rcnt, roff, rpw = pack_ref.pack_records(tables.cpu().numpy().view(np.uint32), nprobe, ix["nsubc"], ix["nc"], W)
+    assert np.array_equal(cnt.cpu().numpy().view(np.uint32), rcnt)
+    assert np.array_equal(off.cpu().numpy().view(np.uint32), roff)
+    assert np.array_equal(pw.cpu().numpy().astype(np.uint64), rpw)
+    assert np.array_equal(packed.cpu().numpy().view(np.uint32)[:int(rpw.sum())], np.concatenate(streams))
+    # every 'rank' scans from its own stream; here all queries have one home, so the stream IS the receive buffer
+    gD = torch.empty(W, nq, k, device=dev); gS = torch.empty(W, nq, k, dtype=torch.int32, device=dev)
+    gL = torch.empty(W, nq, k, dtype=torch.int64, device=dev)
+    base = np.concatenate([[0], np.cumsum(rpw)[:-1]]).astype(np.int64)
+    for r in range(W):
+        idx.set_shard(*sharding.shard_range(r, W, ix["nc"]))
+        stream = packed[int(base[r]):int(base[r] + rpw[r])].contiguous() if rpw[r] else torch.zeros(1, dtype=torch.int32, device=dev)
+        idx.scan_packed_dev(k, Q, stream, off[r].contiguous(), cnt[r].contiguous(), gD[r], gS[r], gL[r])
+    D1 = torch.empty_like(D0); L1 = torch.empty_like(L0)
+    idx.merge_partials_dev(k, nq, W, gD, gS, gL, D1, L1)
+    torch.cuda.synchronize()
+    assert torch.equal(L0, L1) and torch.equal(D0, D1)
     idx.close()

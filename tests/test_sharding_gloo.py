@@ -120,3 +120,101 @@ def test_grid_layout_and_capacity_rule():
             b, e = sharding.shard_range(r, R, 1000)
             cover[b:e] += 1
         assert (cover == 1).all()
+
+
+# ------------------------------------------------------------------ PackedShardedSearch (all-to-all-v protocol) on gloo
+class _FakeIndex:
+    """Stands in for the CUDA library in the world-2 CPU test of sharding.PackedShardedSearch: records are synthetic
+    (IVFADC layout, no sub-groups), the pack step is the numpy statement of ivfhnsw_b200_pack_records_dev
+    (tests/pack_ref.py), a 'scan' turns every received probe into one candidate."""
+    NPROBE, NC = 6, 40
+
+    def __init__(self, rank, world):
+        self.rank, self.world = rank, world
+
+    def tables_bytes(self):
+        import pack_ref
+        return pack_ref.record_words(self.NPROBE, 0) * 4
+
+    @classmethod
+    def records_of(cls, q_home):
+        import pack_ref
+        P = cls.NPROBE
+        rec = np.zeros((q_home.shape[0], pack_ref.record_words(P, 0)), np.uint32)
+        for i, q in enumerate(q_home[:, 0].numpy().astype(np.int64)):
+            rng = np.random.default_rng(int(q))
+            cid = rng.permutation(cls.NC)[:P].astype(np.uint32)
+            n = rng.integers(0, 3, P).astype(np.uint32)              # 0 = skipped by the max_codes rule
+            rec[i, 0:P] = cid * 10                                    # slot
+            rec[i, P:2 * P] = n
+            rec[i, 2 * P:3 * P] = (np.float32(q) + cid.astype(np.float32)).view(np.uint32)   # base = the candidate's distance
+            rec[i, 3 * P:4 * P] = np.arange(P, dtype=np.uint32) * 100   # seq
+            rec[i, 4 * P:5 * P] = cid
+        return rec
+
+    def prepare_dev(self, q_home, lo, hi, tables):
+        tables.copy_(torch.from_numpy(self.records_of(q_home).view(np.int32)))
+
+    def pack_records_dev(self, nq, tables, nparts, packed, cnt, off, pwords):
+        import pack_ref
+        streams, c, o, pw = pack_ref.pack_records(tables.numpy().view(np.uint32), self.NPROBE, 0, self.NC, nparts)
+        flat = np.concatenate(streams)
+        packed[:flat.size] = torch.from_numpy(flat.view(np.int32))
+        cnt.copy_(torch.from_numpy(c.view(np.int32))); off.copy_(torch.from_numpy(o.view(np.int32)))
+        pwords.copy_(torch.from_numpy(pw.astype(np.int64)))
+
+    def scan_packed_dev(self, k, q_all, blob, qoff, qnp, pD, pS, pL):
+        sharding = importlib.import_module("ivf-hnsw_b200.sharding")
+        b, e = sharding.shard_range(self.rank, self.world, self.NC)
+        pD.fill_(np.finfo(np.float32).max); pL.fill_(-1)
+        pS.copy_(torch.arange(k, dtype=torch.int32).flip(0).expand_as(pS) * -1 + np.iinfo(np.int32).max)
+        blob_np = blob.numpy().view(np.uint32)
+        for q in range(q_all.shape[0]):
+            npq, o = int(qnp[q]), int(qoff[q])
+            r = blob_np[o:o + 5 * npq]
+            cid = r[4 * npq:5 * npq]
+            assert np.all((cid >= b) & (cid < e))                     # only probes this rank owns arrive here
+            cand = sorted(zip(r[2 * npq:3 * npq].view(np.float32).tolist(), r[3 * npq:4 * npq].tolist(), cid.tolist()))[:k]
+            for j, (dd, ss, cc) in enumerate(cand):
+                pD[q, j], pS[q, j], pL[q, j] = dd, ss, cc
+
+    def merge_partials_dev(self, k, nq, nparts, gD, gS, gL, D, L):
+        d, l = merge_host(gD.numpy(), gS.numpy(), gL.numpy(), k)
+        D.copy_(torch.from_numpy(d)); L.copy_(torch.from_numpy(l))
+
+
+def _packed_worker(rank, world, port_no, out):
+    os.environ.update(MASTER_ADDR="127.0.0.1", MASTER_PORT=str(port_no))
+    dist.init_process_group("gloo", rank=rank, world_size=world)
+    sys.path.insert(0, os.path.dirname(os.path.abspath(__file__)))
+    sharding = importlib.import_module("ivf-hnsw_b200.sharding")
+    nq_home, k = 7, 4
+    q_all = torch.arange(1, world * nq_home + 1, dtype=torch.float32)[:, None].repeat(1, 3) * 1000.0
+    fake = _FakeIndex(rank, world)
+    ps = sharding.PackedShardedSearch(torch, dist, fake, rank, world, nq_home, k, torch.device("cpu"))
+    D, L = ps.search(q_all)
+    # expected: all scanned probes of the home queries, k best by (distance, seq)
+    rec = _FakeIndex.records_of(q_all[rank * nq_home:(rank + 1) * nq_home])
+    P = _FakeIndex.NPROBE
+    ok = True
+    for i in range(nq_home):
+        keep = rec[i, P:2 * P] != 0
+        cand = sorted(zip(rec[i, 2 * P:3 * P].view(np.float32)[keep].tolist(), rec[i, 3 * P:4 * P][keep].tolist(),
+                          rec[i, 4 * P:5 * P][keep].tolist()))[:k]
+        want_l = [c for _, _, c in cand] + [-1] * (k - len(cand))
+        ok = ok and L[i].tolist() == want_l and np.allclose(D[i].numpy()[:len(cand)], [c[0] for c in cand])
+    out[rank] = bool(ok)
+    dist.destroy_process_group()
+
+
+def test_packed_sharded_search_protocol_on_gloo():
+    """World size 2: every rank prepares its own queries, the packed per-owner streams travel by all-to-all-v, every
+    rank 'scans' only what it owns, the partial lists return home and merge to the answer over ALL probes."""
+    with socket.socket() as s:
+        s.bind(("127.0.0.1", 0))
+        port_no = s.getsockname()[1]
+    world = 2
+    with mp.Manager() as m:
+        out = m.dict()
+        mp.spawn(_packed_worker, args=(world, port_no, out), nprocs=world, join=True)
+        assert all(out.get(r) for r in range(world)), dict(out)
