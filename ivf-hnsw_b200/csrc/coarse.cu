@@ -14,6 +14,8 @@
 // did NOT keep is >= that group's COARSE_T-th kept value; so if that value is > tau the group hides
 // nothing that could be among the K' best.  Groups that fail the test are expanded in full.
 // The K' (+ expansions) candidates are then re-ranked with exact fp32 distances.
+#include <cstdlib>
+
 #include "common.cuh"
 #include "kernels.h"
 
@@ -403,8 +405,16 @@ cudaError_t launch_coarse(cudaStream_t st, uint64_t *launches, int impl, int nq,
     // fewer per accumulator element: -18 % GEMM time at 2^20 centroids); a group whose last kept value passes the
     // threshold is re-scanned in full by the select stage, which is rare only when the top-k spreads over many
     // groups (expected C(k,3) / ngroups^2 per query)
-    // impl 3 keeps 2 when they are very many (nc >= 2^19): expected C(k', 2) / ngroups expanded groups per query
-    const int kept = (impl >= 3 && ngroups >= 4096) ? 2 : ((impl >= 1 && ngroups >= 2048) ? 3 : COARSE_T);
+    // impl 3 keeps 2 when the groups are very many AND few neighbours are wanted (assign: nprobe 1): a group is expanded
+    // by the select stage when its LAST kept value passes the threshold, expected C(k', kept) / ngroups^(kept-1) groups
+    // per query -- at nprobe 128 / 2^20 centroids keeping 2 costs the select stage more than the GEMM gains (measured)
+    const int kp = nprobe + slack;
+    int kept = (impl >= 3 && ngroups >= 4096 && kp * kp < ngroups / 8) ? 2
+                                                                        : ((impl >= 1 && ngroups >= 2048) ? 3 : COARSE_T);
+    if (const char *e = getenv("IVFHNSW_B200_COARSE_KEEP")) {      // profiling switch
+        const int kv = atoi(e);
+        if (impl >= 1 && kv >= (impl >= 3 ? 2 : 3) && kv <= 4) kept = kv;
+    }
     cudaError_t e;
     if (impl >= 1) {
         e = launch_coarse_tc(st, launches, nq, nc, d, queries, cnorm_gemm, S, W.grp_val, impl >= 2 ? 1 : 2, kept,

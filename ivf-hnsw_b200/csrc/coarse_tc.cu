@@ -24,6 +24,8 @@
 #include <cuda.h>
 #include <cuda_fp16.h>
 
+#include <cstdlib>
+
 #include "common.cuh"
 #include "kernels.h"
 
@@ -150,6 +152,13 @@ static __device__ __forceinline__ void mbar_wait(uint32_t bar, uint32_t parity)
         if (spins > (1u << 22)) __trap();
     }
 }
+// one lane of a converged warp (the others get false)
+static __device__ __forceinline__ bool elect_one_sync()
+{
+    uint32_t pred;
+    asm volatile("{\n\t.reg .pred p;\n\telect.sync _|p, 0xffffffff;\n\tselp.u32 %0, 1, 0, p;\n\t}" : "=r"(pred));
+    return pred != 0;
+}
 static __device__ __forceinline__ void tma_load_2d(uint32_t dst, const CUtensorMap *map, int x, int y, uint32_t bar)
 {
     asm volatile(
@@ -160,9 +169,6 @@ static __device__ __forceinline__ void tma_load_2d(uint32_t dst, const CUtensorM
 static __device__ __forceinline__ void umma_f16(uint32_t d_tmem, uint64_t adesc, uint64_t bdesc, uint32_t idesc,
                                                 uint32_t accumulate)
 {
-#ifdef TC_DIAG_NO_MMA   /* timing experiment only: no tensor-core work, barriers and TMA traffic unchanged */
-    return;
-#endif
     asm volatile(
         "{\n\t.reg .pred p;\n\tsetp.ne.b32 p, %4, 0;\n\t"
         "tcgen05.mma.cta_group::1.kind::f16 [%0], %1, %2, %3, p;\n\t}"
@@ -219,7 +225,7 @@ struct TcParams {
 // KEEP: values kept per (query, group of 128 centroids): 4, or 3 / 2 when the groups are many (see launch_coarse)
 // IKEY: integer keys (impl 3, common.cuh): one FFMA + one IMAD on the FMA pipe build the key, KEEP * 2 - 1 integer
 // min/max insert it -- the ALU pipe (half rate for min/max and logic ops) is what bounds this kernel
-template <int MT, int KEEP, bool IKEY>
+template <int MT, int KEEP, bool IKEY, int DIAG = 0>
 __global__ void __launch_bounds__(TC_THREADS, 1)
 coarse_tc_kernel(const __grid_constant__ CUtensorMap tm_qhi, const __grid_constant__ CUtensorMap tm_qlo,
                  const __grid_constant__ CUtensorMap tm_chi, const __grid_constant__ CUtensorMap tm_clo, TcParams p)
@@ -262,6 +268,8 @@ coarse_tc_kernel(const __grid_constant__ CUtensorMap tm_qhi, const __grid_consta
     const int d = p.d;
     if (warp == 0) {
         // ================================================================ TMA producer
+        // (one lane runs the whole loop: two loads per tile, nowhere near the issue limit -- the converged-warp form
+        // of the MMA issuer below was measured slower here: 32 polling lanes take issue slots from the epilogue)
         if (lane == 0) {
             int stage = 0;
             uint32_t phase = 0, a_phase = 0;
@@ -295,62 +303,77 @@ coarse_tc_kernel(const __grid_constant__ CUtensorMap tm_qhi, const __grid_consta
         }
     } else if (warp == 1) {
         // ================================================================ MMA issuer
-        if (lane == 0) {
-            // kind::f16: D fp32, A/B fp16 K-major, M = 128, N = 128
-            const uint32_t idesc = (1u << 4) | ((128u >> 3) << 17) | ((128u >> 4) << 24);
-            int stage = 0, as = 0;
-            uint32_t phase = 0, a_phase = 0, t_phase = 0;
-            for (int u = blockIdx.x; u < p.nunits; u += gridDim.x) {
-                const int cs = u % p.csplit;
-                const int t0 = cs * p.tiles_per_unit;
-                const int t1 = min(t0 + p.tiles_per_unit, p.ntile_c);
-                mbar_wait(A_FULL, a_phase);
-                a_phase ^= 1;
-                for (int t = t0; t < t1; t++) {
-                    mbar_wait(T_EMPTY(as), t_phase ^ 1);
+        // The WHOLE warp runs the control flow (barrier waits, loop counters) and one elected lane issues the
+        // tcgen05.mma instructions.  With the loop inside an `if (lane == 0)` the compiler wraps every tcgen05.mma in
+        // an election loop and rebuilds both 64-bit descriptors from scratch: ~45 dependent instructions = ~200 clocks
+        // per 64-clock MMA, which made the ISSUE rate, not the tensor pipe, the ceiling of this kernel (measured:
+        // 369 ms per 1M x 2^20 batch with the epilogue's arithmetic removed, 3x the tensor pipe's time).
+        // kind::f16: D fp32, A/B fp16 K-major, M = 128, N = 128
+        const uint32_t idesc = (1u << 4) | ((128u >> 3) << 17) | ((128u >> 4) << 24);
+        const bool leader = elect_one_sync();
+        // descriptors of the resident query operand: one per (M tile, column block, hi/lo); a k-step of 16 fp16 = 32 B
+        // advances the 16-byte-granular start address field by 2
+        const uint64_t adesc0 = umma_desc_sw128(smem_u32(sA));
+        const uint64_t bdesc0 = umma_desc_sw128(smem_u32(sB));
+        constexpr uint64_t BLK = TC_BLOCK_BYTES >> 4;      // one 16 KB block in descriptor address units
+        int stage = 0, as = 0;
+        uint32_t phase = 0, a_phase = 0, t_phase = 0;
+        for (int u = blockIdx.x; u < p.nunits; u += gridDim.x) {
+            const int cs = u % p.csplit;
+            const int t0 = cs * p.tiles_per_unit;
+            const int t1 = min(t0 + p.tiles_per_unit, p.ntile_c);
+            mbar_wait(A_FULL, a_phase);
+            a_phase ^= 1;
+            for (int t = t0; t < t1; t++) {
+                mbar_wait(T_EMPTY(as), t_phase ^ 1);
+                tc_fence_after();
+                for (int j = 0; j < db; j++) {
+                    const int ks = min(4, (d - j * 64 + 15) >> 4);
+                    // centroid hi block: q_hi.c_hi (and q_lo.c_hi)
+                    mbar_wait(FULL(stage), phase);
                     tc_fence_after();
-                    for (int j = 0; j < db; j++) {
-                        const int ks = min(4, (d - j * 64 + 15) >> 4);
-                        // centroid hi block: q_hi.c_hi and q_lo.c_hi
-                        mbar_wait(FULL(stage), phase);
-                        tc_fence_after();
-                        {
-                            const uint32_t b = smem_u32(sB + (size_t)stage * TC_BLOCK_BYTES);
-                            for (int mt = 0; mt < MT; mt++) {
-                                const uint32_t a = smem_u32(sA + (size_t)((mt * db + j) * 2) * TC_BLOCK_BYTES);
-                                const uint32_t dcol = tmem_base + (uint32_t)(as * MT * 128 + mt * 128);
-                                for (int k = 0; k < ks; k++) {
-                                    umma_f16(dcol, umma_desc_sw128(a + k * 32), umma_desc_sw128(b + k * 32), idesc,
-                                             (j | k) ? 1u : 0u);
-                                    if (p.qterms == 2)
-                                        umma_f16(dcol, umma_desc_sw128(a + TC_BLOCK_BYTES + k * 32),
-                                                 umma_desc_sw128(b + k * 32), idesc, 1u);
-                                }
+                    if (leader) {
+                        const uint64_t bd = bdesc0 + (uint64_t)stage * BLK;
+#pragma unroll
+                        for (int mt = 0; mt < MT; mt++) {
+                            const uint64_t ad = adesc0 + (uint64_t)((mt * db + j) * 2) * BLK;
+                            const uint32_t dcol = tmem_base + (uint32_t)(as * MT * 128 + mt * 128);
+#pragma unroll
+                            for (int k = 0; k < 4; k++) {
+                                if ((DIAG & 1) || k >= ks) continue;      // DIAG: timing experiment, no tensor-core work
+                                umma_f16(dcol, ad + 2u * k, bd + 2u * k, idesc, (j | k) ? 1u : 0u);
+                                if (p.qterms == 2) umma_f16(dcol, ad + BLK + 2u * k, bd + 2u * k, idesc, 1u);
                             }
                         }
                         umma_commit(EMPTY(stage));
-                        if (++stage == nst) { stage = 0; phase ^= 1; }
-                        if (p.nterms < 2) continue;   // two-product mode: q.c_lo is covered by the select margin
-                        // centroid lo block: q_hi.c_lo
-                        mbar_wait(FULL(stage), phase);
-                        tc_fence_after();
-                        {
-                            const uint32_t b = smem_u32(sB + (size_t)stage * TC_BLOCK_BYTES);
-                            for (int mt = 0; mt < MT; mt++) {
-                                const uint32_t a = smem_u32(sA + (size_t)((mt * db + j) * 2) * TC_BLOCK_BYTES);
-                                const uint32_t dcol = tmem_base + (uint32_t)(as * MT * 128 + mt * 128);
-                                for (int k = 0; k < ks; k++)
-                                    umma_f16(dcol, umma_desc_sw128(a + k * 32), umma_desc_sw128(b + k * 32), idesc, 1u);
-                            }
-                        }
-                        umma_commit(EMPTY(stage));
-                        if (++stage == nst) { stage = 0; phase ^= 1; }
                     }
-                    umma_commit(T_FULL(as));
-                    if (++as == 2) { as = 0; t_phase ^= 1; }
+                    __syncwarp();
+                    if (++stage == nst) { stage = 0; phase ^= 1; }
+                    if (p.nterms < 2) continue;   // the q.c_lo product is covered by the select margin
+                    // centroid lo block: q_hi.c_lo
+                    mbar_wait(FULL(stage), phase);
+                    tc_fence_after();
+                    if (leader) {
+                        const uint64_t bd = bdesc0 + (uint64_t)stage * BLK;
+#pragma unroll
+                        for (int mt = 0; mt < MT; mt++) {
+                            const uint64_t ad = adesc0 + (uint64_t)((mt * db + j) * 2) * BLK;
+                            const uint32_t dcol = tmem_base + (uint32_t)(as * MT * 128 + mt * 128);
+#pragma unroll
+                            for (int k = 0; k < 4; k++)
+                                if (k < ks) umma_f16(dcol, ad + 2u * k, bd + 2u * k, idesc, 1u);
+                        }
+                        umma_commit(EMPTY(stage));
+                    }
+                    __syncwarp();
+                    if (++stage == nst) { stage = 0; phase ^= 1; }
                 }
-                umma_commit(A_EMPTY);   // every MMA that reads this unit's query operand has retired
+                if (leader) umma_commit(T_FULL(as));
+                __syncwarp();
+                if (++as == 2) { as = 0; t_phase ^= 1; }
             }
+            if (leader) umma_commit(A_EMPTY);   // every MMA that reads this unit's query operand has retired
+            __syncwarp();
         }
     } else if (warp >= 4 && warp < 4 + EPI_WARPS) {
         // ================================================================ epilogue
@@ -376,37 +399,66 @@ coarse_tc_kernel(const __grid_constant__ CUtensorMap tm_qhi, const __grid_consta
             }
             const float pad_cn = IKEY ? (COARSE_KEY_BIAS - 128.f + COARSE_KEY_MAGIC) : TC_INVALID;
             const uint32_t key_mul = p.key_mul;
-            auto stage_cn = [&](int c) -> float {
-                if (c >= p.nc) return pad_cn;
-                const float cn = p.cnorm[c];
-                return IKEY ? fmaf(cn, S, COARSE_KEY_MAGIC) : cn;
+            // ||c||^2 of a tile's column as staged in shared memory (integer keys: scaled and biased).  The global load
+            // and the transform are kept apart: the load is issued a whole tile before its value is needed.
+            auto load_cn = [&](int c) -> float { return c < p.nc ? p.cnorm[c] : TC_INVALID; };
+            auto xform_cn = [&](float cn) -> float {
+                if (!IKEY) return cn;
+                return cn < 1.0e38f ? fmaf(cn, S, COARSE_KEY_MAGIC) : pad_cn;
             };
             // stage ||c||^2 of the first tile
             {
-                cn_buf[gt] = stage_cn(t0 * 128 + gt);
+                cn_buf[gt] = xform_cn(load_cn(t0 * 128 + gt));
                 asm volatile("bar.sync %0, 128;" ::"r"(bar_id) : "memory");
+            }
+            // TMEM -> register pipeline: ONE tcgen05.ld is always in flight.  Chunk jb of a tile lives in v[jb & 1];
+            // while it is processed the next chunk -- or chunk 0 of the NEXT tile, whose accumulator the MMA warp
+            // finished long ago -- is on its way.  (Left to itself ptxas sinks each load below the arithmetic of the
+            // previous chunk -- it reuses the destination registers as temporaries -- and every chunk then pays the
+            // full TMEM latency: 4 exposed round trips per tile were ~70 % of this kernel's time.  pin_regs() makes
+            // the chunk's registers "written" after the next load has been issued, which fixes the order.)
+            uint32_t v[2][32];
+            auto pin_regs = [&](uint32_t (&r)[32]) {
+                asm volatile("" : "+r"(r[0]), "+r"(r[1]), "+r"(r[2]), "+r"(r[3]), "+r"(r[4]), "+r"(r[5]), "+r"(r[6]), "+r"(r[7]),
+                                  "+r"(r[8]), "+r"(r[9]), "+r"(r[10]), "+r"(r[11]), "+r"(r[12]), "+r"(r[13]), "+r"(r[14]),
+                                  "+r"(r[15]), "+r"(r[16]), "+r"(r[17]), "+r"(r[18]), "+r"(r[19]), "+r"(r[20]), "+r"(r[21]),
+                                  "+r"(r[22]), "+r"(r[23]), "+r"(r[24]), "+r"(r[25]), "+r"(r[26]), "+r"(r[27]), "+r"(r[28]),
+                                  "+r"(r[29]), "+r"(r[30]), "+r"(r[31]) :: "memory");
+            };
+            auto tmem_addr = [&](int stage) -> uint32_t {
+                return tmem_base + ((uint32_t)(quarter * 32) << 16) + (uint32_t)(stage * MT * 128 + mt * 128);
+            };
+            if (t0 < t1) {
+                mbar_wait(T_FULL(as), t_phase);
+                tc_fence_after();
+                tmem_ld32(tmem_addr(as), v[0]);
             }
             for (int t = t0; t < t1; t++) {
                 const int b = (t - t0) & 1;
-                float cn_next = pad_cn;
-                if (t + 1 < t1) cn_next = stage_cn((t + 1) * 128 + gt);
-                mbar_wait(T_FULL(as), t_phase);
-                tc_fence_after();
-                const uint32_t taddr = tmem_base + ((uint32_t)(quarter * 32) << 16) + (uint32_t)(as * MT * 128 + mt * 128);
+                const float cn_next = (t + 1 < t1) ? load_cn((t + 1) * 128 + gt) : TC_INVALID;
+                const uint32_t taddr = tmem_addr(as);
                 float a0 = TC_INVALID, a1 = TC_INVALID, a2 = TC_INVALID, a3 = TC_INVALID;   // KEEP == 3: the 4th slot stays empty
                 uint32_t k0 = 0xffffffffu, k1 = 0xffffffffu, k2 = 0xffffffffu, k3 = 0xffffffffu;
-                uint32_t v[2][32];
-                tmem_ld32(taddr, v[0]);
 #pragma unroll
                 for (int jb = 0; jb < 4; jb++) {
                     tmem_ld_wait();
                     if (jb < 3) tmem_ld32(taddr + (jb + 1) * 32, v[(jb + 1) & 1]);
                     else {
-                        // all TMEM reads of this accumulator stage are done: hand it back to the MMA warp
+                        // all TMEM reads of this accumulator stage are done: hand it back to the MMA warp ...
                         tc_fence_before();
                         __syncwarp();
                         if (lane == 0) mbar_arrive(T_EMPTY(as));
+                        // ... and start on the next tile's accumulator (the other stage)
+                        if (t + 1 < t1) {
+                            const int as2 = as ^ 1;
+                            const uint32_t ph2 = as == 1 ? (t_phase ^ 1) : t_phase;
+                            mbar_wait(T_FULL(as2), ph2);
+                            tc_fence_after();
+                            tmem_ld32(tmem_addr(as2), v[0]);
+                        }
                     }
+                    pin_regs(v[jb & 1]);
+                    __syncwarp();     // a real instruction between the load and the arithmetic: ptxas sinks neither across it
                     const float4 *cn4 = reinterpret_cast<const float4 *>(cn_buf + b * 128 + jb * 32);
 #pragma unroll
                     for (int i4 = 0; i4 < 8; i4++) {
@@ -415,9 +467,7 @@ coarse_tc_kernel(const __grid_constant__ CUtensorMap tm_qhi, const __grid_consta
 #pragma unroll
                         for (int ii = 0; ii < 4; ii++) {
                             const int i = i4 * 4 + ii;
-#ifdef TC_DIAG_NO_EPI   /* timing experiment only: everything but the per-element epilogue work */
-                            if (i) continue;
-#endif
+                            if ((DIAG & 2) && i) continue;   // timing experiment: everything but the per-element work
                             const float val = fmaf(__uint_as_float(v[jb & 1][i]), f, cnv[ii]);
                             if (IKEY) {
                                 // val in [2^30, 2^31): its bits count quanta.  (bits - bits(2^30)) * 128 + column in one
@@ -439,8 +489,7 @@ coarse_tc_kernel(const __grid_constant__ CUtensorMap tm_qhi, const __grid_consta
                                 }
                             } else {
                                 const float x = __uint_as_float((__float_as_uint(val) & p.keep_mask) | (uint32_t)(jb * 32 + i));
-                                // sorted insert into the KEEP best of the group: 7 or 5 min/max (with two products per
-                                // k-step the epilogue's ALU pipe, not the MMA side, bounds the kernel)
+                                // sorted insert into the KEEP best of the group: 7 or 5 min/max
                                 const float m0 = fmaxf(a0, x);
                                 a0 = fminf(a0, x);
                                 const float m1 = fmaxf(a1, m0);
@@ -462,7 +511,7 @@ coarse_tc_kernel(const __grid_constant__ CUtensorMap tm_qhi, const __grid_consta
                         *reinterpret_cast<float4 *>(p.grp_val + ((size_t)q * p.ntile_c + t) * COARSE_T) =
                             make_float4(a0, a1, a2, a3);
                 }
-                cn_buf[(b ^ 1) * 128 + gt] = cn_next;
+                cn_buf[(b ^ 1) * 128 + gt] = xform_cn(cn_next);
                 asm volatile("bar.sync %0, 128;" ::"r"(bar_id) : "memory");
                 if (++as == 2) { as = 0; t_phase ^= 1; }
             }
@@ -562,13 +611,24 @@ cudaError_t launch_coarse_tc(cudaStream_t st, uint64_t *launches, int nq, int nc
     p.cnorm = cnorm_gemm; p.qfac = S.qfac; p.grp_val = grp_val; p.keep_mask = ~127u; p.key_mul = 128u;
     const size_t smem = fixed + a_bytes + (size_t)nst * TC_BLOCK_BYTES;
     const int grid = p.nunits < 148 ? p.nunits : 148;
+#define IVF_TC_LAUNCH4(MTV, KV, IK, DG)                                                                                \
+    do {                                                                                                               \
+        e = cudaFuncSetAttribute(coarse_tc_kernel<MTV, KV, IK, DG>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem); \
+        if (e != cudaSuccess) return e;                                                                                \
+        coarse_tc_kernel<MTV, KV, IK, DG><<<grid, TC_THREADS, smem, st>>>(m_qhi, m_qlo, m_chi, m_clo, p);              \
+    } while (0)
 #define IVF_TC_LAUNCH(MTV, KV, IK)                                                                                     \
     do {                                                                                                               \
         e = cudaFuncSetAttribute(coarse_tc_kernel<MTV, KV, IK>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem); \
         if (e != cudaSuccess) return e;                                                                                \
         coarse_tc_kernel<MTV, KV, IK><<<grid, TC_THREADS, smem, st>>>(m_qhi, m_qlo, m_chi, m_clo, p);                  \
     } while (0)
-    if (ikey) {
+    static const int diag = getenv("IVFHNSW_B200_TC_DIAG") ? atoi(getenv("IVFHNSW_B200_TC_DIAG")) : 0;   // timing experiments
+    if (diag && ikey && MT == 2 && keep == 2) {
+        if (diag == 1) IVF_TC_LAUNCH4(2, 2, true, 1);
+        else if (diag == 2) IVF_TC_LAUNCH4(2, 2, true, 2);
+        else IVF_TC_LAUNCH4(2, 2, true, 3);
+    } else if (ikey) {
         if (MT == 2) { if (keep == 2) IVF_TC_LAUNCH(2, 2, true); else if (keep == 3) IVF_TC_LAUNCH(2, 3, true); else IVF_TC_LAUNCH(2, 4, true); }
         else { if (keep == 2) IVF_TC_LAUNCH(1, 2, true); else if (keep == 3) IVF_TC_LAUNCH(1, 3, true); else IVF_TC_LAUNCH(1, 4, true); }
     } else {
@@ -576,6 +636,7 @@ cudaError_t launch_coarse_tc(cudaStream_t st, uint64_t *launches, int nq, int nc
         else { if (keep == 3) IVF_TC_LAUNCH(1, 3, false); else IVF_TC_LAUNCH(1, 4, false); }
     }
 #undef IVF_TC_LAUNCH
+#undef IVF_TC_LAUNCH4
     ++*launches;
     return cudaGetLastError();
 }
