@@ -137,6 +137,7 @@ __global__ void __launch_bounds__(256) coarse_select_kernel(int nc, int d, int n
                                                             int packed, int kept, int self_off,
                                                             const uint32_t *__restrict__ cmax /* two-product GEMM: margin */,
                                                             const uint32_t *__restrict__ qstat /* packed == 2 */,
+                                                            int gshift /* packed == 2: log2(tiles per record) */,
                                                             uint32_t *__restrict__ err,
                                                             float *__restrict__ out_d, uint32_t *__restrict__ out_i)
 {
@@ -156,6 +157,8 @@ __global__ void __launch_bounds__(256) coarse_select_kernel(int nc, int d, int n
     // padding columns / unused slots >= COARSE_KEY_INVALID_MIN
     const uint32_t *gi = packed ? nullptr : grp_idx + (size_t)q * n;
     const uint32_t *gk = reinterpret_cast<const uint32_t *>(gv);
+    const uint32_t gsize = (uint32_t)COARSE_GROUP << gshift;          // centroids per record
+    const uint32_t max_flag = SEL_MAX_FLAGGED >> gshift;              // expanded records (cand_cap holds 32 * 128 rows)
     const uint32_t kinv = packed == 2 ? COARSE_KEY_INVALID_MIN : fkey(1.0e38f);
     auto entry_key = [&](int i) -> uint32_t { return packed == 2 ? gk[i] : fkey(gv[i]); };
     auto entry_id = [&](int i) -> uint32_t {
@@ -163,13 +166,13 @@ __global__ void __launch_bounds__(256) coarse_select_kernel(int nc, int d, int n
         uint32_t col;
         if (packed == 2) {
             if (gk[i] >= COARSE_KEY_INVALID_MIN) return 0xffffffffu;
-            col = gk[i] & 127u;
+            col = gk[i] & (gsize - 1u);      // super-groups: sub-tile in bits 7-8 = the column inside 512
         } else {
             const float v = gv[i];
             if (!(v < 1.0e38f)) return 0xffffffffu;
             col = __float_as_uint(v) & 127u;
         }
-        const uint32_t id = (uint32_t)(i / COARSE_T) * COARSE_GROUP + col;
+        const uint32_t id = (uint32_t)(i / COARSE_T) * gsize + col;
         return (self_off >= 0 && id == (uint32_t)(q + self_off)) ? 0xffffffffu : id;
     };
     for (int i = tid; i < d; i += 256) sq[i] = Q[(size_t)q * d + i];
@@ -291,7 +294,7 @@ __global__ void __launch_bounds__(256) coarse_select_kernel(int nc, int d, int n
         const float S = coarse_key_scale(__uint_as_float(qstat[0]), cmax2);
         const float terms = qstat[1] ? 2.f : 1.f;
         const float eps = terms * 9.8e-4f * sqrtf(qn * cmax2);
-        const float wide = 2.f * 1.02f * eps * S + 3.f * 128.f;
+        const float wide = 2.f * 1.02f * eps * S + 3.f * (float)gsize;
         if (tau < COARSE_KEY_INVALID_MIN) {
             const float room = (float)(COARSE_KEY_INVALID_MIN - 1u - tau);
             tau += (uint32_t)fminf(wide, room);
@@ -310,18 +313,35 @@ __global__ void __launch_bounds__(256) coarse_select_kernel(int nc, int d, int n
     }
     // ---- verify groups: a group whose COARSE_T-th kept value is <= tau may hide candidates
     for (int g = tid; g < ngroups; g += 256) {
-        const int last = g * COARSE_T + kept - 1;    // the group's last kept value (the GEMM keeps 3 or 4)
-        if (entry_key(last) <= tau && (packed == 2 ? gk[last] < COARSE_KEY_INVALID_MIN
-                                                   : (packed ? gv[last] < 1.0e38f : gi[last] != 0xffffffffu))) {
+        bool hide;
+        if (packed == 2 && gshift) {
+            // super-group record = the 4 smallest of what its tiles kept (3 each).  A tile may hide a value <= tau only if
+            // all 3 of its kept values are <= tau: then either those 3 are in the record (same sub-tile bits) or the
+            // record's 4th value is <= tau too.
+            const uint32_t e0 = gk[g * COARSE_T], e1 = gk[g * COARSE_T + 1], e2 = gk[g * COARSE_T + 2], e3 = gk[g * COARSE_T + 3];
+            hide = e3 <= tau && e3 < COARSE_KEY_INVALID_MIN;
+            if (!hide && e2 <= tau && e2 < COARSE_KEY_INVALID_MIN) {
+                const uint32_t s0 = (e0 >> 7) & 3u, s1 = (e1 >> 7) & 3u, s2 = (e2 >> 7) & 3u;
+                hide = (kept <= 3) && s0 == s1 && s1 == s2;
+                if (kept <= 2) hide = hide || s0 == s1 || s0 == s2 || s1 == s2;
+            } else if (!hide && kept <= 2 && e1 <= tau && e1 < COARSE_KEY_INVALID_MIN) {
+                hide = ((e0 >> 7) & 3u) == ((e1 >> 7) & 3u);
+            }
+        } else {
+            const int last = g * COARSE_T + kept - 1;    // the group's last kept value (the GEMM keeps 2, 3 or 4)
+            hide = entry_key(last) <= tau && (packed == 2 ? gk[last] < COARSE_KEY_INVALID_MIN
+                                                         : (packed ? gv[last] < 1.0e38f : gi[last] != 0xffffffffu));
+        }
+        if (hide) {
             const uint32_t f = atomicAdd(&s_nflag, 1u);
-            if (f < SEL_MAX_FLAGGED) s_flag[f] = (uint32_t)g;
+            if (f < max_flag) s_flag[f] = (uint32_t)g;
         }
     }
     __syncthreads();
     uint32_t nflag = s_nflag;
-    if (nflag > SEL_MAX_FLAGGED) {
+    if (nflag > max_flag) {
         if (tid == 0) atomicOr(err, 1u);
-        nflag = SEL_MAX_FLAGGED;
+        nflag = max_flag;
     }
     // ---- collect: kept entries with key <= tau outside flagged groups, then flagged groups in full
     for (int i = tid; i < n; i += 256) {
@@ -341,8 +361,8 @@ __global__ void __launch_bounds__(256) coarse_select_kernel(int nc, int d, int n
     __syncthreads();
     for (uint32_t f = 0; f < nflag; f++) {
         const uint32_t g = s_flag[f];
-        for (int j = tid; j < COARSE_GROUP; j += 256) {
-            const uint32_t id = g * COARSE_GROUP + j;
+        for (uint32_t j = tid; j < gsize; j += 256) {
+            const uint32_t id = g * gsize + j;
             if (id < (uint32_t)nc && !(self_off >= 0 && id == (uint32_t)(q + self_off))) {
                 const uint32_t p = atomicAdd(&s_ncand, 1u);
                 if (p < (uint32_t)cand_cap) cand[p] = id;
@@ -392,7 +412,8 @@ size_t coarse_work_bytes(int nq, int nc, int kprime, int *cand_cap)
 }
 
 cudaError_t launch_coarse_tc(cudaStream_t st, uint64_t *launches, int nq, int nc, int d, const float *queries,
-                             const float *cnorm_gemm, const TcSide &S, float *grp_val, int nterms, int keep, int ikey);  // coarse_tc.cu
+                             const float *cnorm_gemm, const TcSide &S, float *grp_val, int nterms, int keep, int ikey,
+                             int gshift);  // coarse_tc.cu
 
 cudaError_t launch_coarse(cudaStream_t st, uint64_t *launches, int impl, int nq, int nc, int d, int nprobe,
                           int slack, const float *queries, const float *centroids, const float *cnorm_gemm,
@@ -415,10 +436,15 @@ cudaError_t launch_coarse(cudaStream_t st, uint64_t *launches, int impl, int nq,
         const int kv = atoi(e);
         if (impl >= 1 && kv >= (impl >= 3 ? 2 : 3) && kv <= 4) kept = kv;
     }
+    // impl 3 with many groups: the kept keys of 4 consecutive tiles leave the GEMM as ONE record of 4 (a 512-centroid
+    // super-group): the select stage is bound by reading these records (three passes over 128 KB per query at 2^20
+    // centroids); 3 kept per tile are needed for the hide test of the merged record
+    int gshift = (impl >= 3 && ngroups >= 2048) ? 2 : 0;
+    if (const char *e2 = getenv("IVFHNSW_B200_COARSE_GSHIFT")) gshift = (impl >= 3 && atoi(e2) == 2) ? 2 : 0;   // profiling switch
     cudaError_t e;
     if (impl >= 1) {
         e = launch_coarse_tc(st, launches, nq, nc, d, queries, cnorm_gemm, S, W.grp_val, impl >= 2 ? 1 : 2, kept,
-                             impl >= 3 ? 1 : 0);
+                             impl >= 3 ? 1 : 0, gshift);
         if (e != cudaSuccess) return e;
     } else {
         const size_t sm = (size_t)(CG_BK * CG_BM + CG_BK * CG_BN + CG_BM * (CG_BN + 1)) * sizeof(float);
@@ -435,22 +461,23 @@ cudaError_t launch_coarse(cudaStream_t st, uint64_t *launches, int impl, int nq,
         e = cudaEventRecord(ev_after_gemm, st);
         if (e != cudaSuccess) return e;
     }
+    const int nrec = gshift ? (ngroups + 3) >> 2 : ngroups;      // records per query the select stage reads
     int avail = nc - (self_off >= 0 ? 1 : 0);
     int kprime = nprobe + slack + ((impl >= 1 && self_off >= 0) ? 1 : 0);   // the packed GEMM keeps the self match
     if (kprime > avail) kprime = avail;
-    if (kprime > ngroups * kept) kprime = ngroups * kept;
+    if (kprime > nrec * (gshift ? COARSE_T : kept)) kprime = nrec * (gshift ? COARSE_T : kept);
     if (kprime < 1) kprime = 1;
     const size_t sm2 = (size_t)d * 4 + (size_t)W.cand_cap * 8;
-    if (ngroups * COARSE_T <= 256 * 8) {
+    if (nrec * COARSE_T <= 256 * 8) {
         e = cudaFuncSetAttribute(coarse_select_kernel<8>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sm2);
         if (e != cudaSuccess) return e;
-        coarse_select_kernel<8><<<nq, 256, sm2, st>>>(nc, d, ngroups, nprobe, kprime, W.cand_cap, queries, centroids,
-                                                      W.grp_val, W.grp_idx, impl >= 3 ? 2 : (impl >= 1 ? 1 : 0), kept, self_off, impl >= 2 ? S.cmax : nullptr, S.qstat, W.err, out_d, out_i);
+        coarse_select_kernel<8><<<nq, 256, sm2, st>>>(nc, d, nrec, nprobe, kprime, W.cand_cap, queries, centroids,
+                                                      W.grp_val, W.grp_idx, impl >= 3 ? 2 : (impl >= 1 ? 1 : 0), kept, self_off, impl >= 2 ? S.cmax : nullptr, S.qstat, gshift, W.err, out_d, out_i);
     } else {
         e = cudaFuncSetAttribute(coarse_select_kernel<16>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sm2);
         if (e != cudaSuccess) return e;
-        coarse_select_kernel<16><<<nq, 256, sm2, st>>>(nc, d, ngroups, nprobe, kprime, W.cand_cap, queries, centroids,
-                                                       W.grp_val, W.grp_idx, impl >= 3 ? 2 : (impl >= 1 ? 1 : 0), kept, self_off, impl >= 2 ? S.cmax : nullptr, S.qstat, W.err, out_d, out_i);
+        coarse_select_kernel<16><<<nq, 256, sm2, st>>>(nc, d, nrec, nprobe, kprime, W.cand_cap, queries, centroids,
+                                                       W.grp_val, W.grp_idx, impl >= 3 ? 2 : (impl >= 1 ? 1 : 0), kept, self_off, impl >= 2 ? S.cmax : nullptr, S.qstat, gshift, W.err, out_d, out_i);
     }
     ++*launches;
     return cudaGetLastError();

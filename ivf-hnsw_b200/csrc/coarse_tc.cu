@@ -214,6 +214,8 @@ struct TcParams {
     int qterms;                       // query operand terms: 2 = hi and lo, 1 = hi only (impl 3)
     const uint32_t *cmax;             // [2] bits of max |c component|, max ||c||^2   (integer keys: scale)
     const uint32_t *qstat;            // [2] bits of max ||q||^2 of the batch, any-lo flag
+    int gshift;                       // integer keys: 2 = the kept keys of 4 consecutive tiles are merged into ONE record of
+                                      // 4 (a 512-centroid super-group): a quarter of the output volume for the select stage
     const float *cnorm;               // [nc] ||c||^2
     const float *qfac;                // [nq] -2 / (s_q * s_c)
     float *grp_val;                   // [nq][ntile_c][COARSE_T] packed (value | column index)
@@ -433,6 +435,15 @@ coarse_tc_kernel(const __grid_constant__ CUtensorMap tm_qhi, const __grid_consta
                 tc_fence_after();
                 tmem_ld32(tmem_addr(as), v[0]);
             }
+            // super-group record (gshift): the 4 smallest keys of up to 4 tiles, sub-tile in bits 7-8, value quantum 512
+            uint32_t G0 = 0xffffffffu, G1 = 0xffffffffu, G2 = 0xffffffffu, G3 = 0xffffffffu;
+            auto sg_insert = [&](uint32_t k, uint32_t sub) {
+                uint32_t x = k >= COARSE_KEY_INVALID_MIN ? 0xffffffffu : (((k >> 9) << 9) | (sub << 7) | (k & 127u));
+                const uint32_t m0 = max(G0, x); G0 = min(G0, x);
+                const uint32_t m1 = max(G1, m0); G1 = min(G1, m0);
+                const uint32_t m2 = max(G2, m1); G2 = min(G2, m1);
+                G3 = min(G3, m2);
+            };
             for (int t = t0; t < t1; t++) {
                 const int b = (t - t0) & 1;
                 const float cn_next = (t + 1 < t1) ? load_cn((t + 1) * 128 + gt) : TC_INVALID;
@@ -503,7 +514,19 @@ coarse_tc_kernel(const __grid_constant__ CUtensorMap tm_qhi, const __grid_consta
                         }
                     }
                 }
-                if (q < p.nq) {
+                if (IKEY && p.gshift) {
+                    const uint32_t sub = (uint32_t)t & 3u;
+                    sg_insert(k0, sub);
+                    sg_insert(k1, sub);
+                    if (KEEP >= 3) sg_insert(k2, sub);
+                    if (KEEP >= 4) sg_insert(k3, sub);
+                    if (sub == 3u || t == t1 - 1) {
+                        if (q < p.nq)
+                            *reinterpret_cast<uint4 *>(p.grp_val + ((size_t)q * ((p.ntile_c + 3) >> 2) + (t >> 2)) * COARSE_T) =
+                                make_uint4(G0, G1, G2, G3);
+                        G0 = G1 = G2 = G3 = 0xffffffffu;
+                    }
+                } else if (q < p.nq) {
                     if (IKEY)
                         *reinterpret_cast<uint4 *>(p.grp_val + ((size_t)q * p.ntile_c + t) * COARSE_T) =
                             make_uint4(k0, k1, k2, k3);
@@ -560,9 +583,11 @@ static bool make_map(CUtensorMap *m, const void *base, size_t rows, int d, int d
 bool coarse_tc_supported(int d) { return d >= 16 && d <= 256; }
 
 cudaError_t launch_coarse_tc(cudaStream_t st, uint64_t *launches, int nq, int nc, int d, const float *queries,
-                             const float *cnorm_gemm, const TcSide &S, float *grp_val, int nterms, int keep, int ikey)
+                             const float *cnorm_gemm, const TcSide &S, float *grp_val, int nterms, int keep, int ikey,
+                             int gshift)
 {
     if (!coarse_tc_supported(d)) return cudaErrorNotSupported;
+    if (gshift && (!ikey || gshift != 2)) return cudaErrorInvalidValue;
     // split the query rows (per-row power-of-two scale); batch statistics for the integer-key scale / select margin
     cudaError_t e = cudaMemsetAsync(S.qstat, 0, 8, st);
     if (e != cudaSuccess) return e;
@@ -600,6 +625,8 @@ cudaError_t launch_coarse_tc(cudaStream_t st, uint64_t *launches, int nq, int nc
         if (cost < best - 1e-9) { best = cost; best_cs = ncs; }
     }
     p.tiles_per_unit = (p.ntile_c + best_cs - 1) / best_cs;
+    if (gshift) p.tiles_per_unit = (p.tiles_per_unit + 3) & ~3;     // a super-group never straddles two units
+    p.gshift = gshift;
     p.csplit = (p.ntile_c + p.tiles_per_unit - 1) / p.tiles_per_unit;
     p.nunits = nqt * p.csplit;
     const size_t a_bytes = (size_t)MT * p.db * 2 * TC_BLOCK_BYTES;
