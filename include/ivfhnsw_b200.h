@@ -85,6 +85,15 @@ int ivfhnsw_b200_train_pq(ivfhnsw_b200_t *h, size_t n, const float *x);
 /* host copies of the model for index->pq->centroids / norm_pq->centroids / opq_matrix->A (any may be NULL) */
 int ivfhnsw_b200_get_pq(ivfhnsw_b200_t *h, float *pq_centroids, float *norm_centroids, float *opq_A);
 
+/* Coarse k-means for the centroid file.  The reference does not train its centroids ("centroids file
+ * create by k-means tool, not here", IndexIVF_HNSW.cpp:703); this is faiss::Clustering::train (faiss/Clustering.cpp:
+ * 67-230) with K-A1 as the assignment step and km_update_centroids (faiss/utils.cpp:1401-1484, void clusters re-seeded
+ * with faiss' random stream) as the update.  x_dev [n][d] float32 DEVICE vectors, n >= nc; the result becomes the
+ * handle's centroid table (read it back with get_centroids).  objective_out = sum of squared distances of the last
+ * assignment, nsplit_out = void clusters re-seeded over all iterations (either may be NULL). */
+int ivfhnsw_b200_train_centroids(ivfhnsw_b200_t *h, size_t n, const float *x_dev, int niter, long seed,
+                                 double *objective_out, size_t *nsplit_out);
+
 /* -- indexing ---------------------------------------------------------------*/
 /* IndexIVF_HNSW::assign (IndexIVF_HNSW.cpp:68-72): exact nearest centroid (k must be 1) */
 int ivfhnsw_b200_assign(ivfhnsw_b200_t *h, size_t n, const float *x, uint32_t *labels, size_t k);

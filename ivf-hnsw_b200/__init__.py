@@ -77,6 +77,7 @@ def lib():
         "ivfhnsw_b200_get_centroids": ([H, vp], C.c_int),
         "ivfhnsw_b200_train_pq": ([H, sz, vp], C.c_int),
         "ivfhnsw_b200_get_pq": ([H, vp, vp, vp], C.c_int),
+        "ivfhnsw_b200_train_centroids": ([H, sz, vp, C.c_int, C.c_long, C.POINTER(C.c_double), C.POINTER(sz)], C.c_int),
         "ivfhnsw_b200_assign": ([H, sz, vp, vp, sz], C.c_int),
         "ivfhnsw_b200_assign_u8": ([H, sz, vp, vp], C.c_int),
         "ivfhnsw_b200_assign_dev": ([H, sz, vp, vp], C.c_int),
@@ -272,6 +273,16 @@ class IndexIVF_HNSW:
         self._ck(self._L.ivfhnsw_b200_get_pq(self._h, self.pq_centroids.ctypes.data, self.norm_centroids.ctypes.data,
                                              None if A is None else A.ctypes.data))
         self.opq_matrix = A
+
+    def train_centroids(self, x_dev, niter=10, seed=1234):
+        """Coarse k-means for the centroid file on the GPU (faiss::Clustering::train with K-A1 as the assignment
+        step, void clusters re-seeded like km_update_centroids).  x_dev: float32 CUDA tensor [n][d].  The result
+        becomes the index' centroid table; returns (objective, void clusters re-seeded)."""
+        obj, ns = C.c_double(), C.c_size_t()
+        with self._ordered():
+            self._ck(self._L.ivfhnsw_b200_train_centroids(self._h, x_dev.shape[0], _ptr(x_dev), niter, seed,
+                                                          C.byref(obj), C.byref(ns)))
+        return obj.value, ns.value
 
     def compute_centroid_norms(self):
         self._ck(self._L.ivfhnsw_b200_finalize(self._h))  # flush point, SURVEY.md 8(b)

@@ -84,6 +84,49 @@ __global__ void kmeans_accum_kernel(size_t n, int d, int M, const float *__restr
     }
 }
 
+// coarse k-means: sums[label][j] += x[v][j] (double), counts[label] += 1, obj += d(x, centroid)
+__global__ void coarse_accum_kernel(size_t n, int d, const float *__restrict__ x, const uint32_t *__restrict__ lab,
+                                    const float *__restrict__ dist, double *__restrict__ sums,
+                                    unsigned int *__restrict__ counts, double *__restrict__ obj)
+{
+    const size_t total = n * (size_t)d;
+    double o = 0;
+    for (size_t e = (size_t)blockIdx.x * blockDim.x + threadIdx.x; e < total; e += (size_t)gridDim.x * blockDim.x) {
+        const size_t v = e / d;
+        const int j = (int)(e - v * d);
+        const uint32_t c = lab[v];
+        atomicAdd(&sums[(size_t)c * d + j], (double)x[e]);
+        if (j == 0) { atomicAdd(&counts[c], 1u); o += (double)dist[v]; }
+    }
+    for (int off = 16; off > 0; off >>= 1) o += __shfl_xor_sync(0xffffffffu, o, off);
+    if ((threadIdx.x & 31) == 0 && o != 0) atomicAdd(obj, o);
+}
+// centroid <- sum / count where the cluster is not void (void ones are re-seeded by the split list)
+__global__ void coarse_mean_kernel(size_t k, int d, const double *__restrict__ sums, const unsigned int *__restrict__ counts,
+                                   float *__restrict__ cent)
+{
+    const size_t total = k * (size_t)d;
+    for (size_t e = (size_t)blockIdx.x * blockDim.x + threadIdx.x; e < total; e += (size_t)gridDim.x * blockDim.x) {
+        const unsigned int n = counts[e / d];
+        cent[e] = n ? (float)(sums[e] / (double)n) : 0.f;
+    }
+}
+// km_update_centroids' void-cluster loop (faiss/utils.cpp:1450-1478) applied IN ORDER: pair p copies centroid cj over
+// ci and perturbs both symmetrically; a cluster may be split more than once, hence one CTA walking the list
+__global__ void coarse_split_kernel(int npairs, int d, const uint32_t *__restrict__ pairs, float *__restrict__ cent)
+{
+    const float eps = 1 / 1024.f;
+    for (int p = 0; p < npairs; p++) {
+        const size_t ci = pairs[2 * p], cj = pairs[2 * p + 1];
+        for (int j = threadIdx.x; j < d; j += blockDim.x) {
+            const float v = cent[cj * d + j];
+            cent[ci * d + j] = v * ((j % 2 == 0) ? 1 + eps : 1 - eps);
+            cent[cj * d + j] = v * ((j % 2 == 0) ? 1 - eps : 1 + eps);
+        }
+        __syncthreads();
+    }
+}
+
 __global__ void center_kernel(size_t n, int d, const double *__restrict__ colsum, float *__restrict__ x)
 {
     const size_t total = n * (size_t)d;
@@ -431,5 +474,102 @@ extern "C" int ivfhnsw_b200_get_pq(ivfhnsw_b200_t *h, float *pq_centroids, float
         CU(cudaMemcpyAsync(opq_A, h->opqA.p, h->d * h->d * 4, cudaMemcpyDeviceToHost, st));
     }
     CU(cudaStreamSynchronize(st));
+    return 0;
+}
+
+// ------------------------------------------------------------------------------------ coarse k-means
+// faiss::Clustering::train (faiss/Clustering.cpp:67-230) for the CENTROID FILE of the index -- the reference leaves it
+// to an offline tool ("centroids file create by k-means tool, not here", IndexIVF_HNSW.cpp:703): k = nc clusters of
+// the n device vectors x_dev, initial centroids x[perm[i]] (rand_perm with seed + 1, :158-162), niter Lloyd
+// iterations whose assignment step is K-A1 itself (the tensor-core GEMM of this library instead of IndexFlatL2) and
+// whose update is km_update_centroids (faiss/utils.cpp:1401-1484) including the re-seeding of void clusters with
+// faiss' own random stream.  The result becomes the handle's centroid table.
+extern "C" int ivfhnsw_b200_train_centroids(ivfhnsw_b200_t *h, size_t n, const float *x_dev, int niter, long seed,
+                                            double *objective_out, size_t *nsplit_out)
+{
+    CU(cudaSetDevice(h->device));
+    const size_t k = h->nc;
+    const int d = (int)h->d;
+    cudaStream_t st = h->stream;
+    if (n < k) return h->fail(IVFHNSW_B200_EINVAL, "Number of training points (%zu) should be at least as large as number of clusters (%zu)", n, k);
+    if (n >= (1ull << 31)) return h->fail(IVFHNSW_B200_EINVAL, "too many training points");
+    if (niter < 0) return h->fail(IVFHNSW_B200_EINVAL, "niter < 0");
+    CU(h->centroids.ensure(k * d * 4));
+    {   // initial centroids
+        std::vector<int> perm;
+        faiss_rand_perm(perm, n, seed + 1);
+        DevBuf ridx;
+        CU(ridx.ensure(k * 4));
+        CU(cudaMemcpyAsync(ridx.p, perm.data(), k * 4, cudaMemcpyHostToDevice, st));
+        gather_rows_kernel<<<grid_for(k * d), 256, 0, st>>>(k, d, x_dev, ridx.as<int>(), h->centroids.as<float>());
+        ++*LAUNCHES;
+        CU(cudaStreamSynchronize(st));
+    }
+    auto centroids_changed = [&]() {
+        h->have_centroids = true;
+        h->gemm_norms_valid = false;
+        h->f16_valid = false;
+        if (!h->have_lists) h->have_group_meta = false;
+    };
+    centroids_changed();
+    if (n == k || niter == 0) {
+        if (objective_out) *objective_out = 0;
+        if (nsplit_out) *nsplit_out = 0;
+        return 0;
+    }
+    DevBuf lab, dist, sums, counts, objb, pairs;
+    CU(lab.ensure(n * 4));
+    CU(dist.ensure(n * 4));
+    CU(sums.ensure(k * d * 8));
+    CU(counts.ensure(k * 4));
+    CU(objb.ensure(8));
+    std::vector<unsigned> hc(k);
+    std::vector<uint32_t> hp;
+    double obj = 0;
+    size_t nsplit_total = 0;
+    for (int it = 0; it < niter; it++) {
+        // assignment = IndexIVF_HNSW::assign: exact nearest centroid + its distance
+        if (int r = ivfb200_coarse_dev(h, n, x_dev, 1, 0, dist.as<float>(), lab.as<uint32_t>())) return r;
+        CU(cudaMemsetAsync(sums.p, 0, k * d * 8, st));
+        CU(cudaMemsetAsync(counts.p, 0, k * 4, st));
+        CU(cudaMemsetAsync(objb.p, 0, 8, st));
+        coarse_accum_kernel<<<grid_for(n * d), 256, 0, st>>>(n, d, x_dev, lab.as<uint32_t>(), dist.as<float>(),
+                                                           sums.as<double>(), counts.as<unsigned>(), objb.as<double>());
+        coarse_mean_kernel<<<grid_for(k * d), 256, 0, st>>>(k, d, sums.as<double>(), counts.as<unsigned>(),
+                                                          h->centroids.as<float>());
+        *LAUNCHES += 2;
+        CU(cudaMemcpyAsync(hc.data(), counts.p, k * 4, cudaMemcpyDeviceToHost, st));
+        CU(cudaMemcpyAsync(&obj, objb.p, 8, cudaMemcpyDeviceToHost, st));
+        CU(cudaStreamSynchronize(st));
+        // void clusters: the reference's loop, on the counts (faiss/utils.cpp:1450-1478)
+        hp.clear();
+        {
+            std::vector<size_t> hassign(hc.begin(), hc.end());
+            FaissRng rng(1234);
+            for (size_t ci = 0; ci < k; ci++) {
+                if (hassign[ci] != 0) continue;
+                size_t cj;
+                for (cj = 0; true; cj = (cj + 1) % k) {
+                    const float pr = (hassign[cj] - 1.0f) / (float)(n - k);
+                    if (rng.rand_float() < pr) break;
+                }
+                hp.push_back((uint32_t)ci);
+                hp.push_back((uint32_t)cj);
+                hassign[ci] = hassign[cj] / 2;
+                hassign[cj] -= hassign[ci];
+            }
+        }
+        if (!hp.empty()) {
+            CU(pairs.ensure(hp.size() * 4));
+            CU(cudaMemcpyAsync(pairs.p, hp.data(), hp.size() * 4, cudaMemcpyHostToDevice, st));
+            coarse_split_kernel<<<1, 128, 0, st>>>((int)(hp.size() / 2), d, pairs.as<uint32_t>(), h->centroids.as<float>());
+            ++*LAUNCHES;
+            CU(cudaStreamSynchronize(st));
+            nsplit_total += hp.size() / 2;
+        }
+        centroids_changed();
+    }
+    if (objective_out) *objective_out = obj;   // sum of squared distances of the LAST assignment (Clustering.cpp:201-206)
+    if (nsplit_out) *nsplit_out = nsplit_total;
     return 0;
 }

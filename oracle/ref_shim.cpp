@@ -18,6 +18,8 @@
 
 #include <ivf-hnsw/IndexIVF_HNSW.h>
 #include <ivf-hnsw/IndexIVF_HNSW_Grouping.h>
+#include <faiss/Clustering.h>
+#include <faiss/IndexFlat.h>
 
 using namespace ivfhnsw;
 typedef IndexIVF_HNSW::idx_t idx_t;
@@ -258,3 +260,18 @@ int ref_get_group_meta(void *hv, size_t c, uint32_t *nn_idxs, uint32_t *sub_size
 float ref_fvec_L2sqr(const float *x, const float *y, size_t d) { return ivfhnsw::fvec_L2sqr(x, y, d); }
 
 }  // extern "C"
+
+// faiss::Clustering::train over an IndexFlatL2 (faiss/Clustering.cpp:67-230): the k-means the reference's tooling
+// would use for the centroid file; returns the last iteration's objective.
+extern "C" double ref_kmeans(size_t d, size_t n, size_t k, const float *x, int niter, int seed, float *centroids_out)
+{
+    faiss::Clustering clus((int)d, (int)k);
+    clus.niter = niter;
+    clus.seed = seed;
+    clus.verbose = false;
+    clus.max_points_per_centroid = 1 << 30;     // no sub-sampling: same training set on both sides
+    faiss::IndexFlatL2 index(d);
+    clus.train(n, x, index);
+    memcpy(centroids_out, clus.centroids.data(), sizeof(float) * d * k);
+    return clus.obj.empty() ? 0.0 : (double)clus.obj.back();
+}
