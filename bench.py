@@ -233,7 +233,7 @@ def load_cache(cdir, w, torch, dev, log):
     return idx, queries, gt0, cent_h
 
 
-def build_index(w, torch, dev, log, dist=None, rank=0, world=1):
+def build_index(w, torch, dev, log, dist=None, rank=0, world=1, sharded=False):
     """Everything on the GPU through the library's own entry points. Returns (index, queries_dev, gt0, centroids).
 
     IVFADC: one pass (assign + encode per 1M batch, IndexIVF_HNSW.cpp:75-138).
@@ -241,7 +241,8 @@ def build_index(w, torch, dev, log, dist=None, rank=0, world=1):
     batch (K-A1, the 2.7e17-FLOP part; split over the ranks when there are several, labels all-gathered), then the
     groups are taken range by range: the batches are re-drawn, the points of the range collected, add_points_dev +
     flush_groups encodes them and drops the raw vectors (peak HBM = one range, not the base set)."""
-    cdir = cache_dir_for(w)
+    sharded = bool(sharded and dist is not None and w["nsubc"] > 0)
+    cdir = None if sharded else cache_dir_for(w)
     if cdir and os.path.exists(os.path.join(cdir, "done")):
         return load_cache(cdir, w, torch, dev, log)
     P = pkg()
@@ -291,7 +292,7 @@ def build_index(w, torch, dev, log, dist=None, rank=0, world=1):
     best_d = torch.full((ngt,), float("inf"), device=dev)
     best_i = torch.zeros(ngt, dtype=torch.long, device=dev)
     grouping = w["nsubc"] > 0
-    split = dist is not None and grouping and nb >= 20_000_000     # pass 1 split over the ranks
+    split = dist is not None and grouping and (nb >= 20_000_000 or sharded)     # pass 1 split over the ranks
     labels = torch.zeros(nb, dtype=torch.int32, device=dev) if grouping else None
     for ci, (b0, n) in enumerate(chunks):
         if split and ci % world != rank:
@@ -324,15 +325,22 @@ def build_index(w, torch, dev, log, dist=None, rank=0, world=1):
         for b0, n in chunks:
             cnt += torch.bincount(labels[b0:b0 + n].long(), minlength=w["nc"])
         cum = torch.cumsum(cnt, 0).cpu().numpy()
-        bounds, lo = [], 0
-        while lo < w["nc"]:
+        own_lo, own_hi = 0, w["nc"]
+        if sharded:
+            # SHARDED CONSTRUCTION: this rank keeps and encodes only the groups it owns (1/world of the points, of the
+            # encode work and of the HBM); the per-list tables are summed over the ranks at the end
+            sharding = importlib.import_module("ivf-hnsw_b200.sharding")
+            own_lo, own_hi = sharding.shard_range(rank, world, w["nc"])
+            idx.set_shard(own_lo, own_hi)
+        bounds, lo = [], own_lo
+        while lo < own_hi:
             base = cum[lo - 1] if lo else 0
             hi = int(np.searchsorted(cum, base + per_pass, side="right"))
             hi = max(hi, lo + 1)
-            bounds.append((lo, min(hi, w["nc"])))
+            bounds.append((lo, min(hi, own_hi)))
             lo = hi
         for pi, (lo, hi) in enumerate(bounds):
-            for b0, n in (chunks if len(bounds) > 1 else []):
+            for b0, n in (chunks if (len(bounds) > 1 or sharded) else []):
                 lab = labels[b0:b0 + n]
                 sel = ((lab >= lo) & (lab < hi)).nonzero().squeeze(1)
                 if sel.numel() == 0:
@@ -340,7 +348,7 @@ def build_index(w, torch, dev, log, dist=None, rank=0, world=1):
                 x = G.draw(n, seed_of(b0))
                 idx.add_points_dev(x[sel].contiguous(), (sel + b0).int().contiguous(), lab[sel].contiguous())
                 del x
-            if len(bounds) == 1:      # small index: one range, batches added as they are drawn
+            if len(bounds) == 1 and not sharded:      # small index: one range, batches added as they are drawn
                 for b0, n in chunks:
                     x = G.draw(n, seed_of(b0))
                     idx.add_points_dev(x, torch.arange(b0, b0 + n, dtype=torch.int32, device=dev), labels[b0:b0 + n])
@@ -353,6 +361,8 @@ def build_index(w, torch, dev, log, dist=None, rank=0, world=1):
         idx.compute_inter_centroid_dists()
     if w["opq"]:
         idx.rotate_quantizer()
+    if sharded:
+        sharding.exchange_list_meta(torch, dist, idx, dev)
     torch.cuda.empty_cache()
     log("index built %.1fs (ntotal %d)" % (time.time() - t0, idx.ntotal))
     idx.nprobe, idx.max_codes, idx.do_pruning = w["nprobe"], w["max_codes"], w["pruning"]
@@ -593,6 +603,10 @@ def main():
     ap.add_argument("--list-shards", type=int, default=int(os.environ.get("IVFHNSW_BENCH_LIST_SHARDS", "0")),
                     help="list shards per query group (0 = the smallest count whose lists fit one GPU)")
     ap.add_argument("--coarse-impl", type=int, default=int(os.environ.get("IVFHNSW_COARSE_IMPL", "-1")))
+    ap.add_argument("--sharded-build", action="store_true",
+                    help="N > 1, Grouping workloads: every rank ingests and keeps only the lists it owns "
+                         "(ivfhnsw_b200_set_shard before the build + exchange of the per-list tables); measures the "
+                         "list-sharded layout alone")
     args = ap.parse_args()
     # stdout carries the ONE JSON line and nothing else: libraries that print there (NCCL's version banner) are
     # pointed at stderr for the life of the process
@@ -625,7 +639,10 @@ def main():
             emit({"impl": "reference", "unavailable": "assign over 2^20 centroids needs a ~5 min HNSW build on the CPU"})
             return 0
         return run_assign(args, w, torch, dev, dist, rank, world, local, log, emit)
-    idx, queries, gt0, cent_h = build_index(w, torch, dev, log, dist, rank, world)
+    t_build = time.time()
+    sharded_build = bool(args.sharded_build and world > 1 and w["nsubc"] > 0 and args.impl == "ours")
+    idx, queries, gt0, cent_h = build_index(w, torch, dev, log, dist, rank, world, sharded=sharded_build)
+    t_build = time.time() - t_build
     if args.coarse_impl >= 0:
         idx.set_option("coarse_impl", args.coarse_impl)
     nq, k, nprobe = w["nq"], w["k"], w["nprobe"]
@@ -735,6 +752,34 @@ def main():
 
     clk = Clocks(local)
     sharded_ok, layouts = None, None
+    if sharded_build:
+        # no rank holds the whole index: only the list-sharded layout exists.  Its answers are checked through recall
+        # (the index is bit-identical to the one a single GPU builds, tests/test_build_gpu.py::
+        # test_sharded_construction_equals_one_index, so recall must equal the N=1 line's)
+        free_b, total_b = torch.cuda.mem_get_info()
+        q_weak = torch.cat([torch.roll(queries, shifts=-997 * r, dims=0) for r in range(world)])
+        w_search, w_ps = make_sharded(nq)
+        ms, st = timed_run(w_search, q_weak, args.steps, args.warmup, clk)
+        Lh = w_ps.L.clone()
+        hit = Lh[:ngt] == gt0[:, None]
+        line = {"metric": "QPS at fixed Recall@10 (k=10)", "mode": "sharded_build",
+                "value": nq * world * args.steps / (ms / 1e3), "unit": "queries/s", "n_gpus": world, "steps": args.steps,
+                "warmup": max(args.warmup, 3), "ms_per_step": ms / args.steps, "higher_is_better": True, "scaling": "weak",
+                "vs_baseline": None, "dtype": "u8 codes, f32 accumulate", "data": "synthetic",
+                "config": dict(config, nq_per_step=nq * world,
+                               sharding="lists sharded over %d ranks at CONSTRUCTION: every rank assigned 1/%d of the base "
+                                        "vectors (labels all-reduced), then ingested, encoded and keeps only the groups of "
+                                        "its centroid range; per-list tables summed by all-reduce" % (world, world)),
+                "build_seconds": t_build, "hbm_used_bytes_after_build_rank0": int(total_b - free_b),
+                "recall_rank0": {"r1": float(hit[:, :1].any(1).float().mean().item()),
+                                 "r10": float(hit[:, :10].any(1).float().mean().item())},
+                "record_exchange_MB_received_per_rank_per_step": w_ps.last_recv_words * 4 / 1e6,
+                "clocks": clk.summary(), "gpu_launches": int(st.kernel_launches)}
+        if rank == 0:
+            emit(line)
+        idx.close()
+        dist.destroy_process_group()
+        return 0
     if world == 1:
         idx.set_shard(0, w["nc"])
         ms, st = timed_run(single_search, queries, args.steps, args.warmup, clk)

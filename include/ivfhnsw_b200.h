@@ -52,8 +52,23 @@ const char *ivfhnsw_b200_last_error(const ivfhnsw_b200_t *h);
 /* -- sharding: this handle owns the inverted lists of
  * centroids [c_begin, c_end) only; all metadata stays replicated.  Lists
  * outside the range still count for the max_codes rule but are not scanned.
- * Default is [0, nc).  Must be called before lists are loaded/added. */
+ * Default is [0, nc).
+ * Called BEFORE the lists are built (finalize / load_lists / read_index), the
+ * build keeps only the owned lists' codes and ids in HBM (1/N of the index per
+ * rank); records of other lists are counted in the size tables and dropped.
+ * Called afterwards it only narrows what is scanned and must stay inside the
+ * resident range (ESTATE otherwise).  A handle whose resident range is not
+ * [0, nc) cannot export_lists / write_index / take further add_batch calls. */
 int ivfhnsw_b200_set_shard(ivfhnsw_b200_t *h, size_t c_begin, size_t c_end);
+/* Sharded CONSTRUCTION: each rank set_shard()s, ingests only the points of its own lists (add_batch with given
+ * assignments, add_group for its groups), finalizes, then the ranks SUM these per-list tables (their supports are
+ * disjoint: an all-reduce) and install the sums, after which every rank prunes / applies max_codes exactly like a
+ * rank holding the whole index.  Device pointers: list_size [nc], sub_sizes [nc*nsubc], alphas [nc] (the last two
+ * NULL / ignored without Grouping).  set checks that the resident lists keep their sizes.  No counterpart in the
+ * reference (single-process). */
+int ivfhnsw_b200_get_list_meta_dev(ivfhnsw_b200_t *h, uint32_t *list_size_dev, uint32_t *sub_sizes_dev, float *alphas_dev);
+int ivfhnsw_b200_set_list_meta_dev(ivfhnsw_b200_t *h, const uint32_t *list_size_dev, const uint32_t *sub_sizes_dev,
+                                   const float *alphas_dev);
 
 /* -- model state ------------------------------------------------------------*/
 /* centroid table = hnswlib::HierarchicalNSW::getDataByInternalId (hnswlib/hnswalg.h:76-78),

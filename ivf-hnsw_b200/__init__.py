@@ -91,6 +91,8 @@ def lib():
         "ivfhnsw_b200_load_lists": ([H, vp, vp, vp, vp, vp, vp, vp, vp], C.c_int),
         "ivfhnsw_b200_ntotal": ([H, C.POINTER(sz)], C.c_int),
         "ivfhnsw_b200_list_sizes": ([H, vp], C.c_int),
+        "ivfhnsw_b200_get_list_meta_dev": ([H, vp, vp, vp], C.c_int),
+        "ivfhnsw_b200_set_list_meta_dev": ([H, vp, vp, vp], C.c_int),
         "ivfhnsw_b200_export_lists": ([H, vp, vp, vp, vp, vp, vp, vp, vp], C.c_int),
         "ivfhnsw_b200_write_index": ([H, C.c_char_p], C.c_int),
         "ivfhnsw_b200_read_index": ([H, C.c_char_p], C.c_int),
@@ -558,6 +560,17 @@ class IndexIVF_HNSW:
             self._ck(self._L.ivfhnsw_b200_scan_packed_dev(self._h, x_dev.shape[0], k, _ptr(x_dev), _ptr(packed_dev),
                                                           _ptr(qoff_dev), _ptr(qnp_dev), _ptr(part_d), _ptr(part_seq),
                                                           _ptr(part_labels)))
+
+    def get_list_meta_dev(self, list_size_dev, sub_sizes_dev=None, alphas_dev=None):
+        """This handle's per-list tables (sharded construction, ivfhnsw_b200_get_list_meta_dev)."""
+        with self._ordered():
+            self._ck(self._L.ivfhnsw_b200_get_list_meta_dev(self._h, _ptr(list_size_dev), _ptr(sub_sizes_dev),
+                                                            _ptr(alphas_dev)))
+
+    def set_list_meta_dev(self, list_size_dev, sub_sizes_dev=None, alphas_dev=None):
+        with self._ordered():
+            self._ck(self._L.ivfhnsw_b200_set_list_meta_dev(self._h, _ptr(list_size_dev), _ptr(sub_sizes_dev),
+                                                            _ptr(alphas_dev)))
 
     def merge_partials_dev(self, k, nq, nparts, part_d, part_seq, part_labels, D_dev, L_dev):
         with self._ordered():

@@ -22,12 +22,12 @@ cudaError_t launch_group_points(cudaStream_t st, uint64_t *launches, int mode, i
                                 const float *centroids, const uint32_t *nn_idx, const float *icd,
                                 const float *alphas, float *num, float *den, uint8_t *sub);
 cudaError_t launch_slot_scan(cudaStream_t st, uint64_t *launches, int nc, uint32_t align, const uint32_t *size,
-                             uint32_t *slot, uint32_t *raw_off, uint32_t *total_slots);
+                             uint32_t *slot, uint32_t *raw_off, uint32_t *total_slots, int keep_b, int keep_e);
 cudaError_t launch_scatter_lists2(cudaStream_t st, uint64_t *launches, size_t n, int M, int key_div,
                                   const uint32_t *order, const uint32_t *sorted_key, const uint32_t *raw_off,
                                   const uint32_t *list_slot, const uint32_t *ids, const uint8_t *codes,
                                   const uint8_t *norm_codes, uint8_t *out_codes, uint8_t *out_norm, uint8_t *out_sub,
-                                  uint32_t *out_ids);
+                                  uint32_t *out_ids, uint32_t keep_b, uint32_t keep_e);
 cudaError_t launch_gather_lists(cudaStream_t st, uint64_t *launches, int nc, int M, const uint32_t *list_size,
                                 const uint32_t *list_slot, const uint32_t *raw_off, const uint8_t *codes,
                                 const uint8_t *norm_codes, const uint32_t *ids, uint8_t *out_codes, uint8_t *out_norm,
@@ -224,6 +224,9 @@ const char *ivfhnsw_b200_last_error(const ivfhnsw_b200_t *h) { return h ? h->err
 int ivfhnsw_b200_set_shard(ivfhnsw_b200_t *h, size_t c_begin, size_t c_end)
 {
     if (c_begin > c_end || c_end > h->nc) return h->fail(IVFHNSW_B200_EINVAL, "bad shard range");
+    if (h->have_lists && !h->st_dirty && (c_begin < h->res_begin || c_end > h->res_end))
+        return h->fail(IVFHNSW_B200_ESTATE, "shard [%zu, %zu) is not resident: the lists were built for [%u, %u)", c_begin,
+                       c_end, h->res_begin, h->res_end);
     h->c_begin = (uint32_t)c_begin;
     h->c_end = (uint32_t)c_end;
     return 0;
@@ -755,7 +758,7 @@ static int build_csr(ivfhnsw_b200_t *h)
     const uint32_t align = M <= 16 ? 16u : 32u;
     CU(h->w_small.ensure(64));
     CU(launch_slot_scan(st, LAUNCHES, nc, align, h->list_size.as<uint32_t>(), h->list_slot.as<uint32_t>(),
-                        h->raw_off.as<uint32_t>(), h->w_small.as<uint32_t>()));
+                        h->raw_off.as<uint32_t>(), h->w_small.as<uint32_t>(), (int)h->c_begin, (int)h->c_end));
     uint32_t tot[2] = {0, 0};
     CU(cudaMemcpyAsync(tot, h->w_small.p, 8, cudaMemcpyDeviceToHost, st));
     CU(cudaStreamSynchronize(st));
@@ -776,11 +779,13 @@ static int build_csr(ivfhnsw_b200_t *h)
         CU(launch_scatter_lists2(st, LAUNCHES, n, M, (int)key_div, ord_out, keys_out, h->raw_off.as<uint32_t>(),
                                  h->list_slot.as<uint32_t>(), h->st_ids.as<uint32_t>(), h->st_codes.as<uint8_t>(),
                                  h->st_norm.as<uint8_t>(), h->codes.as<uint8_t>(), h->norm_codes.as<uint8_t>(),
-                                 nsubc ? h->sub_ids.as<uint8_t>() : nullptr, h->ids.as<uint32_t>()));
+                                 nsubc ? h->sub_ids.as<uint8_t>() : nullptr, h->ids.as<uint32_t>(), h->c_begin, h->c_end));
     CU(cudaStreamSynchronize(st));
     h->nslots = nslots;
     h->ntotal = n;
     h->have_lists = true;
+    h->res_begin = h->c_begin;   // only these lists are resident from here on
+    h->res_end = h->c_end;
     return 0;
 }
 
@@ -790,6 +795,8 @@ static int unstage_existing_lists(ivfhnsw_b200_t *h)
     const size_t n = h->ntotal;
     h->st_n = 0;
     if (n == 0) return 0;
+    if (h->res_begin != 0 || h->res_end != h->nc)
+        return h->fail(IVFHNSW_B200_ESTATE, "cannot append to lists built for the shard [%u, %u) only", h->res_begin, h->res_end);
     if (int r = stage_reserve(h, n)) return r;
     CU(launch_gather_lists(h->stream, LAUNCHES, (int)h->nc, (int)h->M, h->list_size.as<uint32_t>(),
                            h->list_slot.as<uint32_t>(), h->raw_off.as<uint32_t>(), h->codes.as<uint8_t>(),
@@ -854,7 +861,7 @@ int ivfb200_group_stage(ivfhnsw_b200_t *h, size_t n, const float *x_dev, const u
     CU(cudaMemsetAsync(gsize, 0, (size_t)nc * 4, st));
     CU(launch_hist(st, LAUNCHES, n, list_dev, gsize));
     CU(h->w_small.ensure(64));
-    CU(launch_slot_scan(st, LAUNCHES, nc, 1, gsize, gslot, goff, h->w_small.as<uint32_t>()));
+    CU(launch_slot_scan(st, LAUNCHES, nc, 1, gsize, gslot, goff, h->w_small.as<uint32_t>(), 0, nc));
     if (seen) {
         uint32_t *flag = h->w_small.as<uint32_t>() + 8;
         CU(cudaMemsetAsync(flag, 0, 4, st));
@@ -993,6 +1000,55 @@ int ivfhnsw_b200_list_sizes(ivfhnsw_b200_t *h, uint32_t *sizes)
     return 0;
 }
 
+// Sharded construction: every rank ingests only the points of the lists it owns, so its per-list metadata is
+// zero elsewhere; the ranks sum the arrays (NCCL all-reduce over disjoint supports) and install the result.
+int ivfhnsw_b200_get_list_meta_dev(ivfhnsw_b200_t *h, uint32_t *list_size_dev, uint32_t *sub_sizes_dev, float *alphas_dev)
+{
+    if (int r = ivfhnsw_b200_finalize(h)) return r;
+    std::lock_guard<std::mutex> lk(h->mu);
+    if (bind(h)) return IVFHNSW_B200_ECUDA;
+    if (!h->have_lists) return h->fail(IVFHNSW_B200_ESTATE, "no lists");
+    cudaStream_t st = h->stream;
+    const size_t nc = h->nc, nsubc = h->nsubc;
+    if (list_size_dev) CU(cudaMemcpyAsync(list_size_dev, h->list_size.p, nc * 4, cudaMemcpyDeviceToDevice, st));
+    if (nsubc && sub_sizes_dev) CU(cudaMemcpyAsync(sub_sizes_dev, h->sub_sizes.p, nc * nsubc * 4, cudaMemcpyDeviceToDevice, st));
+    if (nsubc && alphas_dev) CU(cudaMemcpyAsync(alphas_dev, h->alphas.p, nc * 4, cudaMemcpyDeviceToDevice, st));
+    return 0;
+}
+
+int ivfhnsw_b200_set_list_meta_dev(ivfhnsw_b200_t *h, const uint32_t *list_size_dev, const uint32_t *sub_sizes_dev,
+                                   const float *alphas_dev)
+{
+    if (int r = ivfhnsw_b200_finalize(h)) return r;
+    std::lock_guard<std::mutex> lk(h->mu);
+    if (bind(h)) return IVFHNSW_B200_ECUDA;
+    if (!h->have_lists) return h->fail(IVFHNSW_B200_ESTATE, "no lists");
+    if (!list_size_dev || (h->nsubc && (!sub_sizes_dev || !alphas_dev)))
+        return h->fail(IVFHNSW_B200_EINVAL, "set_list_meta: null array");
+    cudaStream_t st = h->stream;
+    const size_t nc = h->nc, nsubc = h->nsubc;
+    // the resident lists must keep their sizes: their slots were laid out from them
+    std::vector<uint32_t> mine(nc), all(nc);
+    CU(cudaMemcpyAsync(mine.data(), h->list_size.p, nc * 4, cudaMemcpyDeviceToHost, st));
+    CU(cudaMemcpyAsync(all.data(), list_size_dev, nc * 4, cudaMemcpyDeviceToHost, st));
+    CU(cudaStreamSynchronize(st));
+    uint64_t total = 0;
+    for (size_t c = 0; c < nc; c++) {
+        total += all[c];
+        if (c >= h->res_begin && c < h->res_end && all[c] != mine[c])
+            return h->fail(IVFHNSW_B200_EINVAL, "set_list_meta: resident list %zu has %u records here, %u in the new table", c,
+                           mine[c], all[c]);
+    }
+    CU(cudaMemcpyAsync(h->list_size.p, list_size_dev, nc * 4, cudaMemcpyDeviceToDevice, st));
+    if (nsubc) {
+        CU(cudaMemcpyAsync(h->sub_sizes.p, sub_sizes_dev, nc * nsubc * 4, cudaMemcpyDeviceToDevice, st));
+        CU(cudaMemcpyAsync(h->alphas.p, alphas_dev, nc * 4, cudaMemcpyDeviceToDevice, st));
+    }
+    CU(cudaStreamSynchronize(st));
+    h->ntotal = (size_t)total;
+    return 0;
+}
+
 int ivfhnsw_b200_ntotal(ivfhnsw_b200_t *h, size_t *ntotal)
 {
     *ntotal = h->st_dirty ? h->st_n + h->rs_n : h->ntotal;
@@ -1006,6 +1062,9 @@ int ivfhnsw_b200_export_lists(ivfhnsw_b200_t *h, int64_t *list_off, uint32_t *id
     std::lock_guard<std::mutex> lk(h->mu);
     if (bind(h)) return IVFHNSW_B200_ECUDA;
     if (!h->have_lists) return h->fail(IVFHNSW_B200_ESTATE, "no lists");
+    if (h->res_begin != 0 || h->res_end != h->nc)
+        return h->fail(IVFHNSW_B200_ESTATE, "cannot export: only the lists [%u, %u) are resident on this handle", h->res_begin,
+                       h->res_end);
     const size_t nc = h->nc, n = h->ntotal, M = h->M, nsubc = h->nsubc;
     cudaStream_t st = h->stream;
     std::vector<uint32_t> ro(nc + 1);

@@ -517,9 +517,11 @@ cudaError_t launch_hist(cudaStream_t st, uint64_t *launches, size_t n, const uin
 }
 
 // list_slot[c] = aligned exclusive prefix of list sizes; single CTA (nc <= a few million is fine)
+// lists outside [keep_b, keep_e) get no slots (a sharded handle stores only the lists it owns); raw_off always counts
+// every record, it is the position in the sorted staging order
 __global__ void __launch_bounds__(1024) slot_scan_kernel(int nc, uint32_t align, const uint32_t *__restrict__ size,
                                                          uint32_t *__restrict__ slot, uint32_t *__restrict__ raw_off,
-                                                         uint32_t *__restrict__ total_slots)
+                                                         uint32_t *__restrict__ total_slots, int keep_b, int keep_e)
 {
     __shared__ uint64_t s_a[1024], s_r[1024];
     __shared__ uint64_t carry_a, carry_r;
@@ -528,7 +530,7 @@ __global__ void __launch_bounds__(1024) slot_scan_kernel(int nc, uint32_t align,
     for (int base = 0; base < nc; base += 1024) {
         const int i = base + threadIdx.x;
         const uint32_t sz = i < nc ? size[i] : 0u;
-        const uint64_t al = ((uint64_t)sz + align - 1) / align * align;
+        const uint64_t al = (i >= keep_b && i < keep_e) ? ((uint64_t)sz + align - 1) / align * align : 0;
         s_a[threadIdx.x] = al;
         s_r[threadIdx.x] = sz;
         __syncthreads();
@@ -556,9 +558,9 @@ __global__ void __launch_bounds__(1024) slot_scan_kernel(int nc, uint32_t align,
 }
 
 cudaError_t launch_slot_scan(cudaStream_t st, uint64_t *launches, int nc, uint32_t align, const uint32_t *size,
-                             uint32_t *slot, uint32_t *raw_off, uint32_t *total_slots)
+                             uint32_t *slot, uint32_t *raw_off, uint32_t *total_slots, int keep_b, int keep_e)
 {
-    slot_scan_kernel<<<1, 1024, 0, st>>>(nc, align, size, slot, raw_off, total_slots);
+    slot_scan_kernel<<<1, 1024, 0, st>>>(nc, align, size, slot, raw_off, total_slots, keep_b, keep_e);
     ++*launches;
     return cudaGetLastError();
 }
@@ -569,11 +571,13 @@ __global__ void scatter_lists_kernel(size_t n, int M, int ml_mask, int key_div, 
                                      const uint32_t *__restrict__ list_slot, const uint32_t *__restrict__ ids,
                                      const uint8_t *__restrict__ codes, const uint8_t *__restrict__ norm_codes,
                                      uint8_t *__restrict__ out_codes, uint8_t *__restrict__ out_norm,
-                                     uint8_t *__restrict__ out_sub, uint32_t *__restrict__ out_ids)
+                                     uint8_t *__restrict__ out_sub, uint32_t *__restrict__ out_ids, uint32_t keep_b,
+                                     uint32_t keep_e)
 {
     for (size_t r = (size_t)blockIdx.x * blockDim.x + threadIdx.x; r < n; r += (size_t)gridDim.x * blockDim.x) {
         const uint32_t key = sorted_key[r];
         const uint32_t list = key / key_div, sub = key - list * key_div;
+        if (list < keep_b || list >= keep_e) continue;   // not resident on this shard
         const size_t src = order ? order[r] : r;
         const uint32_t slot = list_slot[list] + (uint32_t)(r - raw_off[list]);
         const uint32_t x = slot & ml_mask;
@@ -588,14 +592,15 @@ cudaError_t launch_scatter_lists2(cudaStream_t st, uint64_t *launches, size_t n,
                                   const uint32_t *order, const uint32_t *sorted_key, const uint32_t *raw_off,
                                   const uint32_t *list_slot, const uint32_t *ids, const uint8_t *codes,
                                   const uint8_t *norm_codes, uint8_t *out_codes, uint8_t *out_norm, uint8_t *out_sub,
-                                  uint32_t *out_ids)
+                                  uint32_t *out_ids, uint32_t keep_b, uint32_t keep_e)
 {
     if (n == 0) return cudaSuccess;
     const int ml = M < 32 ? M : 32;
     size_t blocks = (n + 255) / 256;
     if (blocks > 148 * 16) blocks = 148 * 16;
     scatter_lists_kernel<<<(unsigned)blocks, 256, 0, st>>>(n, M, ml - 1, key_div, order, sorted_key, raw_off, list_slot,
-                                                        ids, codes, norm_codes, out_codes, out_norm, out_sub, out_ids);
+                                                        ids, codes, norm_codes, out_codes, out_norm, out_sub, out_ids,
+                                                        keep_b, keep_e);
     ++*launches;
     return cudaGetLastError();
 }

@@ -67,7 +67,8 @@ struct ivfhnsw_b200 {
     size_t d = 0, nc = 0, M = 0, nsubc = 0;
     size_t nprobe = 1, max_codes = 1000000000;
     bool do_opq = false, do_pruning = false;
-    uint32_t c_begin = 0, c_end = 0;
+    uint32_t c_begin = 0, c_end = 0;       // lists this handle scans
+    uint32_t res_begin = 0, res_end = 0;   // lists whose codes are resident (the shard at CSR-build time)
     cudaStream_t stream = nullptr;
     bool own_stream = true;
     cudaEvent_t ev[10] = {nullptr, nullptr, nullptr, nullptr, nullptr, nullptr, nullptr, nullptr, nullptr, nullptr};

@@ -1148,12 +1148,15 @@ __global__ void __launch_bounds__(SCAN_THREADS) scan_kernel(ScanArgs a)
 
     // ---- stage the query's segment tables (keeping only the lists this GPU owns) and initialise the top-k
     {
-        const uint32_t *r_slot = rec, *r_n = rec + nprobe, *r_seq = rec + 3 * (size_t)nprobe, *r_cid = rec + 4 * (size_t)nprobe;
+        const uint32_t *r_n = rec + nprobe, *r_seq = rec + 3 * (size_t)nprobe, *r_cid = rec + 4 * (size_t)nprobe;
         const float *r_base = reinterpret_cast<const float *>(rec + 2 * (size_t)nprobe);
         for (int i = tid; i < nprobe; i += SCAN_THREADS) {
             const uint32_t c = r_cid[i];
-            s_slot[i] = r_slot[i];
-            s_n[i] = (c >= a.c_begin && c < a.c_end) ? r_n[i] : 0u;
+            const bool own = c >= a.c_begin && c < a.c_end;
+            // the slot comes from THIS rank's layout, not from the record: the record may have been written by another
+            // rank, and ranks built with set_shard lay out only their own lists (slot spaces differ)
+            s_slot[i] = own ? a.L.list_slot[c] : 0u;
+            s_n[i] = own ? r_n[i] : 0u;
             s_base[i] = r_base[i];
             s_seq[i] = r_seq[i];
             s_cid[i] = c;

@@ -54,6 +54,25 @@ def gather_tables(dist, tables, rank, per, group=None):
     dist.all_gather_into_tensor(tables, tables[rank * per:(rank + 1) * per], group=group)
 
 
+def exchange_list_meta(torch, dist, index, device, group=None):
+    """Last step of a SHARDED index construction (ivfhnsw_b200_set_list_meta_dev): every rank has set_shard() its
+    range, ingested only the points of its own lists and finalized; the per-list tables (sizes, sub-group sizes,
+    alphas) are zero outside a rank's range, so one SUM all-reduce of each gives the whole tables, which every rank
+    installs.  Afterwards pruning and the max_codes rule behave as on a rank that holds the complete index."""
+    nc, nsubc = index.nc, getattr(index, "nsubc", 0)
+    ls = torch.zeros(nc, dtype=torch.int32, device=device)
+    ss = torch.zeros(max(nc * nsubc, 1), dtype=torch.int32, device=device)
+    al = torch.zeros(nc, dtype=torch.float32, device=device)
+    index.get_list_meta_dev(ls, ss if nsubc else None, al if nsubc else None)
+    index.sync()
+    dist.all_reduce(ls, group=group)
+    if nsubc:
+        dist.all_reduce(ss, group=group)
+        dist.all_reduce(al, group=group)
+    index.set_list_meta_dev(ls, ss if nsubc else None, al if nsubc else None)
+    return int(ls.sum().item())
+
+
 class PackedShardedSearch:
     """The list-sharded search of SURVEY.md 8(e) without an all-gather of whole records.
 

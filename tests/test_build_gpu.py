@@ -294,3 +294,134 @@ def test_streamed_grouping_ingest_equals_one_shot():
         e.flush_groups()
     for j in (a, b, c, e):
         j.close()
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("grouping", [True, False])
+def test_sharded_construction_equals_one_index(grouping):
+    """SURVEY.md 8(e), construction side: W 'ranks' (W handles on one GPU here) each set_shard() their range,
+    ingest ONLY the points of their own lists, finalize, sum the per-list tables (the all-reduce of
+    sharding.exchange_list_meta) and install them; the packed sharded search over those W partial indexes is
+    bit-identical to the search of one index that ingested everything.  Also: a complete lists file loaded into a
+    sharded handle keeps the owned lists only and answers the same."""
+    import torch
+    pkg = load_pkg()
+    from conftest import ROOT  # noqa: F401
+    import importlib
+    sharding = importlib.import_module("ivf-hnsw_b200.sharding")
+    rng = np.random.default_rng(11)
+    d, nc, M, nsubc, n, W, k, nprobe = 32, 120, 8, 8, 40000, 3, 10, 16
+    cent = rng.standard_normal((nc, d)).astype(np.float32) * 4
+    X = (cent[rng.integers(0, nc, n)] + rng.standard_normal((n, d))).astype(np.float32)
+    Q = (cent[rng.integers(0, nc, 300)] + rng.standard_normal((300, d))).astype(np.float32)
+    dev = torch.device("cuda:0")
+
+    def fresh():
+        j = pkg.IndexIVF_HNSW_Grouping(d, nc, M, 8, nsubc) if grouping else pkg.IndexIVF_HNSW(d, nc, M, 8)
+        j.build_quantizer(centroids=cent)
+        return j
+
+    full = fresh()
+    full.train_pq(X[:8000])
+    lab = full.assign(X)
+    ids = np.arange(n, dtype=np.uint32)
+    Xd = torch.from_numpy(X).to(dev)
+    idd = torch.from_numpy(ids.view(np.int32)).to(dev)
+    labd = torch.from_numpy(lab.view(np.int32)).to(dev)
+
+    def ingest(j, mask=None):
+        if grouping:
+            if mask is None:
+                j.add_points_dev(Xd, idd, labd)
+            else:
+                j.add_points_dev(Xd[mask].contiguous(), idd[mask].contiguous(), labd[mask].contiguous())
+        else:
+            m = np.ones(n, bool) if mask is None else mask.cpu().numpy()
+            j.add_batch(X[m], ids[m], lab[m])
+        j.compute_centroid_norms()
+
+    ingest(full)
+    for j in (full,):
+        j.nprobe, j.max_codes = nprobe, 3000
+        if grouping:
+            j.do_pruning = True
+    Qd = torch.from_numpy(Q).to(dev)
+    nq = Q.shape[0]
+    D0 = torch.empty(nq, k, device=dev); L0 = torch.empty(nq, k, dtype=torch.int64, device=dev)
+    full.search_dev(k, Qd, D0, L0)
+    torch.cuda.synchronize()
+    ref = full.export_index_dict()
+
+    def packed_search(ranks):
+        words = ranks[0].tables_bytes() // 4
+        tables = torch.zeros(nq, words, dtype=torch.int32, device=dev)
+        ranks[0].prepare_dev(Qd, 0, nq, tables)          # any rank can be the home: the metadata is replicated
+        packed = torch.zeros(nq * words, dtype=torch.int32, device=dev)
+        cnt = torch.zeros(W, nq, dtype=torch.int32, device=dev)
+        off = torch.zeros(W, nq, dtype=torch.int32, device=dev)
+        pw = torch.zeros(W, dtype=torch.int64, device=dev)
+        ranks[0].pack_records_dev(nq, tables, W, packed, cnt, off, pw)
+        torch.cuda.synchronize()
+        base = np.concatenate([[0], np.cumsum(pw.cpu().numpy())[:-1]]).astype(np.int64)
+        gD = torch.empty(W, nq, k, device=dev); gS = torch.empty(W, nq, k, dtype=torch.int32, device=dev)
+        gL = torch.empty(W, nq, k, dtype=torch.int64, device=dev)
+        for r, j in enumerate(ranks):
+            nw = int(pw[r])
+            stream = packed[int(base[r]):int(base[r]) + nw].contiguous() if nw else torch.zeros(1, dtype=torch.int32, device=dev)
+            j.scan_packed_dev(k, Qd, stream, off[r].contiguous(), cnt[r].contiguous(), gD[r], gS[r], gL[r])
+            j.sync()
+        D1 = torch.empty_like(D0); L1 = torch.empty_like(L0)
+        ranks[0].merge_partials_dev(k, nq, W, gD, gS, gL, D1, L1)
+        torch.cuda.synchronize()
+        return D1, L1
+
+    # (1) sharded ingest + metadata exchange
+    ranks = []
+    for r in range(W):
+        j = fresh()
+        j.set_pq(full.pq_centroids, full.norm_centroids, None)
+        lo, hi = sharding.shard_range(r, W, nc)
+        j.set_shard(lo, hi)
+        ingest(j, (labd >= lo) & (labd < hi))
+        j.nprobe, j.max_codes = nprobe, 3000
+        if grouping:
+            j.do_pruning = True
+        ranks.append(j)
+    ls = [torch.zeros(nc, dtype=torch.int32, device=dev) for _ in range(W)]
+    ss = [torch.zeros(max(nc * nsubc, 1), dtype=torch.int32, device=dev) for _ in range(W)]
+    al = [torch.zeros(nc, dtype=torch.float32, device=dev) for _ in range(W)]
+    for r, j in enumerate(ranks):
+        j.get_list_meta_dev(ls[r], ss[r] if grouping else None, al[r] if grouping else None)
+        j.sync()
+    LS, SS, AL = sum(ls), sum(ss), sum(al)               # what the all-reduce leaves on every rank
+    assert np.array_equal(LS.cpu().numpy(), np.diff(ref["list_off"]).astype(np.int32))
+    for j in ranks:
+        j.set_list_meta_dev(LS, SS if grouping else None, AL if grouping else None)
+        assert j.ntotal == n
+    D1, L1 = packed_search(ranks)
+    assert torch.equal(L0, L1) and torch.equal(D0, D1)
+    # a sharded handle holds its own lists only: no export, no widening of the shard
+    with pytest.raises(pkg.B200Error, match="resident"):
+        ranks[1].export_index_dict()
+    with pytest.raises(pkg.B200Error, match="resident"):
+        ranks[1].set_shard(0, nc)
+    bad = LS.clone(); lo, hi = sharding.shard_range(1, W, nc); bad[lo] += 1
+    with pytest.raises(pkg.B200Error, match="resident list"):
+        ranks[1].set_list_meta_dev(bad, SS if grouping else None, AL if grouping else None)
+    # (2) a complete index loaded into sharded handles: every rank keeps 1/W of the codes
+    loaded = []
+    for r in range(W):
+        j = fresh()
+        j.set_pq(full.pq_centroids, full.norm_centroids, None)
+        j.set_shard(*sharding.shard_range(r, W, nc))
+        j.load_index_dict(ref)
+        j.compute_centroid_norms()
+        j.nprobe, j.max_codes = nprobe, 3000
+        if grouping:
+            j.do_pruning = True
+        assert j.ntotal == n
+        loaded.append(j)
+    D2, L2 = packed_search(loaded)
+    assert torch.equal(L0, L2) and torch.equal(D0, D2)
+    for j in [full] + ranks + loaded:
+        j.close()

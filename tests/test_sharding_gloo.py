@@ -218,3 +218,57 @@ def test_packed_sharded_search_protocol_on_gloo():
         out = m.dict()
         mp.spawn(_packed_worker, args=(world, port_no, out), nprocs=world, join=True)
         assert all(out.get(r) for r in range(world)), dict(out)
+
+
+class _FakeShardIndex:
+    """Per-list tables of a rank that ingested only the lists it owns (zero elsewhere), for the world-2 CPU test of
+    sharding.exchange_list_meta."""
+    nc, nsubc = 10, 4
+
+    def __init__(self, rank, world):
+        sharding = importlib.import_module("ivf-hnsw_b200.sharding")
+        self.lo, self.hi = sharding.shard_range(rank, world, self.nc)
+        self.installed = None
+
+    @classmethod
+    def whole(cls):
+        sub = (np.arange(cls.nc * cls.nsubc, dtype=np.int32).reshape(cls.nc, cls.nsubc) * 7) % 5
+        return sub.sum(1).astype(np.int32), sub.reshape(-1), (np.arange(cls.nc, dtype=np.float32) + 1) / 16
+
+    def get_list_meta_dev(self, ls, ss, al):
+        wl, ws, wa = self.whole()
+        own = np.zeros(self.nc, bool); own[self.lo:self.hi] = True
+        ls.copy_(torch.from_numpy(np.where(own, wl, 0).astype(np.int32)))
+        ss.copy_(torch.from_numpy(np.where(np.repeat(own, self.nsubc), ws, 0).astype(np.int32)))
+        al.copy_(torch.from_numpy(np.where(own, wa, 0).astype(np.float32)))
+
+    def set_list_meta_dev(self, ls, ss, al):
+        self.installed = (ls.numpy().copy(), ss.numpy().copy(), al.numpy().copy())
+
+    def sync(self):
+        pass
+
+
+def _meta_worker(rank, world, port_no, out):
+    os.environ.update(MASTER_ADDR="127.0.0.1", MASTER_PORT=str(port_no))
+    dist.init_process_group("gloo", rank=rank, world_size=world)
+    sharding = importlib.import_module("ivf-hnsw_b200.sharding")
+    fake = _FakeShardIndex(rank, world)
+    total = sharding.exchange_list_meta(torch, dist, fake, torch.device("cpu"))
+    wl, ws, wa = _FakeShardIndex.whole()
+    out[rank] = bool(total == int(wl.sum()) and np.array_equal(fake.installed[0], wl) and
+                     np.array_equal(fake.installed[1], ws) and np.array_equal(fake.installed[2], wa))
+    dist.destroy_process_group()
+
+
+def test_sharded_construction_metadata_exchange_on_gloo():
+    """World size 2: the per-list tables of ranks that ingested disjoint list ranges sum to the whole tables, and
+    every rank installs the same whole tables (the last step of a sharded index construction)."""
+    with socket.socket() as s:
+        s.bind(("127.0.0.1", 0))
+        port_no = s.getsockname()[1]
+    world = 2
+    with mp.Manager() as m:
+        out = m.dict()
+        mp.spawn(_meta_worker, args=(world, port_no, out), nprocs=world, join=True)
+        assert all(out.get(r) for r in range(world)), dict(out)
