@@ -138,6 +138,8 @@ __global__ void __launch_bounds__(256) coarse_select_kernel(int nc, int d, int n
                                                             const uint32_t *__restrict__ cmax /* two-product GEMM: margin */,
                                                             const uint32_t *__restrict__ qstat /* packed == 2 */,
                                                             int gshift /* packed == 2: log2(tiles per record) */,
+                                                            int pre /* packed == 2: 2 = a key stands for a column pair */,
+                                                            int pcap /* pre == 2: capacity of the partner list */,
                                                             uint32_t *__restrict__ err,
                                                             float *__restrict__ out_d, uint32_t *__restrict__ out_i)
 {
@@ -145,8 +147,9 @@ __global__ void __launch_bounds__(256) coarse_select_kernel(int nc, int d, int n
     float *sq = reinterpret_cast<float *>(smraw);                 // [d]
     uint32_t *cand = reinterpret_cast<uint32_t *>(sq + d);        // [cand_cap]
     float *cand_d = reinterpret_cast<float *>(cand + cand_cap);   // [cand_cap]
+    uint32_t *pcand = reinterpret_cast<uint32_t *>(cand_d + cand_cap);   // [pcap] pre == 2: the other column of each pair
     __shared__ uint32_t hist[256];
-    __shared__ uint32_t s_prefix, s_remaining, s_ncand, s_nflag, s_less, s_or, s_and;
+    __shared__ uint32_t s_prefix, s_remaining, s_ncand, s_nflag, s_less, s_or, s_and, s_npc;
     __shared__ uint32_t s_flag[SEL_MAX_FLAGGED];
     const int q = blockIdx.x, tid = threadIdx.x;
     const int n = ngroups * COARSE_T;
@@ -161,7 +164,8 @@ __global__ void __launch_bounds__(256) coarse_select_kernel(int nc, int d, int n
     const uint32_t max_flag = SEL_MAX_FLAGGED >> gshift;              // expanded records (cand_cap holds 32 * 128 rows)
     const uint32_t kinv = packed == 2 ? COARSE_KEY_INVALID_MIN : fkey(1.0e38f);
     auto entry_key = [&](int i) -> uint32_t { return packed == 2 ? gk[i] : fkey(gv[i]); };
-    auto entry_id = [&](int i) -> uint32_t {
+    auto is_self = [&](uint32_t id) -> bool { return self_off >= 0 && id == (uint32_t)(q + self_off); };
+    auto entry_id = [&](int i) -> uint32_t {     // NOT filtered for the self match when packed (see the collect pass)
         if (!packed) return gi[i];
         uint32_t col;
         if (packed == 2) {
@@ -172,11 +176,10 @@ __global__ void __launch_bounds__(256) coarse_select_kernel(int nc, int d, int n
             if (!(v < 1.0e38f)) return 0xffffffffu;
             col = __float_as_uint(v) & 127u;
         }
-        const uint32_t id = (uint32_t)(i / COARSE_T) * gsize + col;
-        return (self_off >= 0 && id == (uint32_t)(q + self_off)) ? 0xffffffffu : id;
+        return (uint32_t)(i / COARSE_T) * gsize + col;
     };
     for (int i = tid; i < d; i += 256) sq[i] = Q[(size_t)q * d + i];
-    if (tid == 0) { s_prefix = 0; s_remaining = (uint32_t)kprime; s_ncand = 0; s_nflag = 0; s_less = 0; s_or = 0u; s_and = 0xffffffffu; }
+    if (tid == 0) { s_prefix = 0; s_remaining = (uint32_t)kprime; s_ncand = 0; s_nflag = 0; s_less = 0; s_or = 0u; s_and = 0xffffffffu; s_npc = 0; }
     __syncthreads();
 
     // ---- radix select: key of the kprime-th smallest kept value.  The keys a thread owns stay in registers
@@ -188,20 +191,27 @@ __global__ void __launch_bounds__(256) coarse_select_kernel(int nc, int d, int n
     // row instead of five.
     const bool sampled = n > 256 * SEL_CACHE && kprime <= 192;
     const bool cached = sampled || n <= 256 * SEL_CACHE;
-    const int nsel = sampled ? 256 : n;
+    const int nsel = sampled ? 512 : n;
     uint32_t kc[SEL_CACHE];
     if (sampled) {
-        uint32_t mk = 0xffffffffu;
+        // the TWO smallest entries of every thread's share (512 distinct entries of the row): with kprime = 160 about
+        // 169 row entries lie below their kprime-th smallest, against 251 with one minimum per thread
+        uint32_t mk = 0xffffffffu, mk2 = 0xffffffffu;
         // entry i = 4 * group + rank-in-group: a thread that strode by 256 would only ever see ONE rank (the threads
         // with tid % 4 == 3 only 4th-best values) and the minima would say nothing about the row; rotating the
         // assignment by one entry per pass gives every thread all four ranks (loads stay coalesced)
         for (int j = 0; j * 256 < n; j++) {
             const int i = j * 256 + ((tid + j) & 255);
-            if (i < n) mk = min(mk, entry_key(i));
+            if (i < n) {
+                const uint32_t kx = entry_key(i);
+                mk2 = min(mk2, max(mk, kx));
+                mk = min(mk, kx);
+            }
         }
 #pragma unroll
         for (int j = 0; j < SEL_CACHE; j++) kc[j] = 0xffffffffu;
         kc[0] = mk;
+        kc[1] = mk2;
     } else if (cached) {
 #pragma unroll
         for (int j = 0; j < SEL_CACHE; j++) {
@@ -282,6 +292,7 @@ __global__ void __launch_bounds__(256) coarse_select_kernel(int nc, int d, int n
         remaining_bits = shift;
     }
     uint32_t tau = s_prefix;       // key of the kprime-th smallest
+    float pair_dmax = FLT_MAX;     // pre == 2: a partner column farther than this cannot be among the nprobe nearest
     if (packed == 2) {
         // one-product GEMM: each dropped cross term (q.c_lo always, q_lo.c when some query of the batch has a lo
         // part) moves a value by at most 2 * 2^-11 ||q|| ||c||; the true top-kprime all lie below the kprime-th
@@ -299,6 +310,15 @@ __global__ void __launch_bounds__(256) coarse_select_kernel(int nc, int d, int n
             const float room = (float)(COARSE_KEY_INVALID_MIN - 1u - tau);
             tau += (uint32_t)fminf(wide, room);
         }
+        // pre == 2: the widened threshold as an exact distance.  key >> 7 counts quanta of 128 of t = v * S + 1.5 * 2^30
+        // above 2^30 (v = ||c||^2 - 2 q.c, the distance without ||q||^2); every centroid of the true top-nprobe has
+        // an approximate v <= v(tau) - eps, hence an exact distance <= v(tau) + ||q||^2.  Generous rounding head room:
+        // a looser bound only lets a few more partner columns into the ranking.
+        {
+            const float tq = (float)(tau >> 7) * 128.f - COARSE_KEY_BIAS + 1024.f;
+            const float vt = tq / S + qn;
+            pair_dmax = vt + eps + fabsf(vt) * 1.0e-5f + fabsf(qn) * 1.0e-5f;
+        }
     } else if (cmax) {
         // two-product GEMM: every kept value is within eps = 2 * 2^-11 ||q|| ||c|| of its three-product value, so the
         // true top-kprime all lie below (kprime-th smallest approximate value) + 2 eps; widen the threshold by that
@@ -311,27 +331,59 @@ __global__ void __launch_bounds__(256) coarse_select_kernel(int nc, int d, int n
         const float wide = tf + 2.f * 1.02f * eps + fabsf(tf) * 6.2e-5f;
         if (tf < 1.0e38f) tau = fkey(wide);
     }
-    // ---- verify groups: a group whose COARSE_T-th kept value is <= tau may hide candidates
-    for (int g = tid; g < ngroups; g += 256) {
-        bool hide;
-        if (packed == 2 && gshift) {
-            // super-group record = the 4 smallest of what its tiles kept (3 each).  A tile may hide a value <= tau only if
-            // all 3 of its kept values are <= tau: then either those 3 are in the record (same sub-tile bits) or the
-            // record's 4th value is <= tau too.
-            const uint32_t e0 = gk[g * COARSE_T], e1 = gk[g * COARSE_T + 1], e2 = gk[g * COARSE_T + 2], e3 = gk[g * COARSE_T + 3];
-            hide = e3 <= tau && e3 < COARSE_KEY_INVALID_MIN;
-            if (!hide && e2 <= tau && e2 < COARSE_KEY_INVALID_MIN) {
-                const uint32_t s0 = (e0 >> 7) & 3u, s1 = (e1 >> 7) & 3u, s2 = (e2 >> 7) & 3u;
-                hide = (kept <= 3) && s0 == s1 && s1 == s2;
-                if (kept <= 2) hide = hide || s0 == s1 || s0 == s2 || s1 == s2;
-            } else if (!hide && kept <= 2 && e1 <= tau && e1 < COARSE_KEY_INVALID_MIN) {
-                hide = ((e0 >> 7) & 3u) == ((e1 >> 7) & 3u);
-            }
-        } else {
-            const int last = g * COARSE_T + kept - 1;    // the group's last kept value (the GEMM keeps 2, 3 or 4)
-            hide = entry_key(last) <= tau && (packed == 2 ? gk[last] < COARSE_KEY_INVALID_MIN
-                                                         : (packed ? gv[last] < 1.0e38f : gi[last] != 0xffffffffu));
+    auto push_entry = [&](uint32_t id) {
+        if (!is_self(id)) {
+            const uint32_t p = atomicAdd(&s_ncand, 1u);
+            if (p < (uint32_t)cand_cap) cand[p] = id;
         }
+        if (pre == 2) {      // the kept key is the smaller of columns (id, id ^ 1): the other one may pass too
+            const uint32_t pid = id ^ 1u;
+            if (pid < (uint32_t)nc && !is_self(pid)) {
+                const uint32_t p = atomicAdd(&s_npc, 1u);
+                if (p < (uint32_t)pcap) pcand[p] = pid;
+            }
+        }
+    };
+    const uint32_t tau_all = tau;
+    if (packed == 2) {
+        // ---- integer keys: ONE pass over the records (16 bytes each, keys ascending).  A record that may hide candidates
+        // is flagged and expanded in full below; of the others every key <= tau is a candidate.
+        const uint32_t tau = min(tau_all, COARSE_KEY_INVALID_MIN - 1u);     // an empty slot never passes
+        for (int g = tid; g < ngroups; g += 256) {
+            const uint4 r4 = reinterpret_cast<const uint4 *>(gk)[g];
+            const uint32_t ev[4] = {r4.x, r4.y, r4.z, r4.w};
+            if (ev[0] > tau) continue;
+            bool hide;
+            if (gshift) {
+                // super-group record = the 4 smallest of what its tiles kept (3 each).  A tile may hide a value <= tau only
+                // if all 3 of its kept values are <= tau: then either those 3 are in the record (same sub-tile bits) or
+                // the record's 4th value is <= tau too.
+                hide = ev[3] <= tau;
+                if (!hide && ev[2] <= tau) {
+                    const uint32_t s0 = (ev[0] >> 7) & 3u, s1 = (ev[1] >> 7) & 3u, s2 = (ev[2] >> 7) & 3u;
+                    hide = (kept <= 3) && s0 == s1 && s1 == s2;
+                    if (kept <= 2) hide = hide || s0 == s1 || s0 == s2 || s1 == s2;
+                } else if (!hide && kept <= 2 && ev[1] <= tau) {
+                    hide = ((ev[0] >> 7) & 3u) == ((ev[1] >> 7) & 3u);
+                }
+            } else {
+                hide = (kept <= 2 ? ev[1] : (kept == 3 ? ev[2] : ev[3])) <= tau;
+            }
+            if (hide) {
+                const uint32_t f = atomicAdd(&s_nflag, 1u);
+                if (f < max_flag) s_flag[f] = (uint32_t)g;
+                continue;
+            }
+#pragma unroll
+            for (int j = 0; j < 4; j++)
+                if (ev[j] <= tau) push_entry((uint32_t)g * gsize + (ev[j] & (gsize - 1u)));
+        }
+        __syncthreads();
+    }
+    // ---- verify groups: a group whose COARSE_T-th kept value is <= tau may hide candidates
+    for (int g = tid; packed != 2 && g < ngroups; g += 256) {
+        const int last = g * COARSE_T + kept - 1;    // the group's last kept value (the GEMM keeps 3 or 4)
+        const bool hide = entry_key(last) <= tau && (packed ? gv[last] < 1.0e38f : gi[last] != 0xffffffffu);
         if (hide) {
             const uint32_t f = atomicAdd(&s_nflag, 1u);
             if (f < max_flag) s_flag[f] = (uint32_t)g;
@@ -344,7 +396,7 @@ __global__ void __launch_bounds__(256) coarse_select_kernel(int nc, int d, int n
         nflag = max_flag;
     }
     // ---- collect: kept entries with key <= tau outside flagged groups, then flagged groups in full
-    for (int i = tid; i < n; i += 256) {
+    for (int i = tid; packed != 2 && i < n; i += 256) {
         const uint32_t kx = entry_key(i);
         if (kx > tau) continue;
         const uint32_t id = entry_id(i);
@@ -352,10 +404,7 @@ __global__ void __launch_bounds__(256) coarse_select_kernel(int nc, int d, int n
             const uint32_t g = (uint32_t)(i / COARSE_T);
             bool flagged = false;
             for (uint32_t f = 0; f < nflag; f++) flagged |= (s_flag[f] == g);
-            if (!flagged) {
-                const uint32_t p = atomicAdd(&s_ncand, 1u);
-                if (p < (uint32_t)cand_cap) cand[p] = id;
-            }
+            if (!flagged) push_entry(id);
         }
     }
     __syncthreads();
@@ -363,7 +412,7 @@ __global__ void __launch_bounds__(256) coarse_select_kernel(int nc, int d, int n
         const uint32_t g = s_flag[f];
         for (uint32_t j = tid; j < gsize; j += 256) {
             const uint32_t id = g * gsize + j;
-            if (id < (uint32_t)nc && !(self_off >= 0 && id == (uint32_t)(q + self_off))) {
+            if (id < (uint32_t)nc && !is_self(id)) {
                 const uint32_t p = atomicAdd(&s_ncand, 1u);
                 if (p < (uint32_t)cand_cap) cand[p] = id;
             }
@@ -382,6 +431,29 @@ __global__ void __launch_bounds__(256) coarse_select_kernel(int nc, int d, int n
         const uint32_t id = e < ncand ? cand[e] : 0u;
         const float dist = l2sqr16_octet(sq, Cn + (size_t)id * d, d, sub);
         if (e < ncand && sub == 0) cand_d[e] = dist;
+    }
+    if (pre == 2) {
+        // partner columns: exact distance, appended behind the candidates only when it can matter
+        uint32_t npc = s_npc;
+        if (npc > (uint32_t)pcap) {
+            if (tid == 0) atomicOr(err, 2u);
+            npc = pcap;
+        }
+        for (uint32_t e0 = warp * 4; e0 < npc; e0 += 32) {
+            const uint32_t e = e0 + oct;
+            const uint32_t id = e < npc ? pcand[e] : 0u;
+            const float dist = l2sqr16_octet(sq, Cn + (size_t)id * d, d, sub);
+            if (e < npc && sub == 0 && dist <= pair_dmax) {
+                const uint32_t p = atomicAdd(&s_ncand, 1u);
+                if (p < (uint32_t)cand_cap) { cand[p] = id; cand_d[p] = dist; }
+            }
+        }
+        __syncthreads();
+        ncand = s_ncand;
+        if (ncand > (uint32_t)cand_cap) {
+            if (tid == 0) atomicOr(err, 2u);
+            ncand = cand_cap;
+        }
     }
     __syncthreads();
     // ---- rank by (dist, idx) ascending == unload order of priority_queue<pair<float, idx_t>>
@@ -413,7 +485,7 @@ size_t coarse_work_bytes(int nq, int nc, int kprime, int *cand_cap)
 
 cudaError_t launch_coarse_tc(cudaStream_t st, uint64_t *launches, int nq, int nc, int d, const float *queries,
                              const float *cnorm_gemm, const TcSide &S, float *grp_val, int nterms, int keep, int ikey,
-                             int gshift);  // coarse_tc.cu
+                             int gshift, int pre);  // coarse_tc.cu
 
 cudaError_t launch_coarse(cudaStream_t st, uint64_t *launches, int impl, int nq, int nc, int d, int nprobe,
                           int slack, const float *queries, const float *centroids, const float *cnorm_gemm,
@@ -441,10 +513,15 @@ cudaError_t launch_coarse(cudaStream_t st, uint64_t *launches, int impl, int nq,
     // centroids); 3 kept per tile are needed for the hide test of the merged record
     int gshift = (impl >= 3 && ngroups >= 2048) ? 2 : 0;
     if (const char *e2 = getenv("IVFHNSW_B200_COARSE_GSHIFT")) gshift = (impl >= 3 && atoi(e2) == 2) ? 2 : 0;   // profiling switch
+    // impl 3 with many groups: the epilogue reduces every column pair to its smaller key before the sorted insert (the
+    // ALU pipe bounds that kernel); the select stage scores the other column of each surviving pair exactly
+    int pre = (impl >= 3 && ngroups >= 2048 && kept <= 3) ? 2 : 1;
+    if (const char *e3 = getenv("IVFHNSW_B200_COARSE_PRE")) pre = (impl >= 3 && kept <= 3 && atoi(e3) == 2) ? 2 : 1;   // profiling switch
+    const int pcap = pre == 2 ? 1024 : 0;
     cudaError_t e;
     if (impl >= 1) {
         e = launch_coarse_tc(st, launches, nq, nc, d, queries, cnorm_gemm, S, W.grp_val, impl >= 2 ? 1 : 2, kept,
-                             impl >= 3 ? 1 : 0, gshift);
+                             impl >= 3 ? 1 : 0, gshift, pre);
         if (e != cudaSuccess) return e;
     } else {
         const size_t sm = (size_t)(CG_BK * CG_BM + CG_BK * CG_BN + CG_BM * (CG_BN + 1)) * sizeof(float);
@@ -467,17 +544,17 @@ cudaError_t launch_coarse(cudaStream_t st, uint64_t *launches, int impl, int nq,
     if (kprime > avail) kprime = avail;
     if (kprime > nrec * (gshift ? COARSE_T : kept)) kprime = nrec * (gshift ? COARSE_T : kept);
     if (kprime < 1) kprime = 1;
-    const size_t sm2 = (size_t)d * 4 + (size_t)W.cand_cap * 8;
+    const size_t sm2 = (size_t)d * 4 + (size_t)W.cand_cap * 8 + (size_t)pcap * 4;
     if (nrec * COARSE_T <= 256 * 8) {
         e = cudaFuncSetAttribute(coarse_select_kernel<8>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sm2);
         if (e != cudaSuccess) return e;
         coarse_select_kernel<8><<<nq, 256, sm2, st>>>(nc, d, nrec, nprobe, kprime, W.cand_cap, queries, centroids,
-                                                      W.grp_val, W.grp_idx, impl >= 3 ? 2 : (impl >= 1 ? 1 : 0), kept, self_off, impl >= 2 ? S.cmax : nullptr, S.qstat, gshift, W.err, out_d, out_i);
+                                                      W.grp_val, W.grp_idx, impl >= 3 ? 2 : (impl >= 1 ? 1 : 0), kept, self_off, impl >= 2 ? S.cmax : nullptr, S.qstat, gshift, pre, pcap, W.err, out_d, out_i);
     } else {
         e = cudaFuncSetAttribute(coarse_select_kernel<16>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sm2);
         if (e != cudaSuccess) return e;
         coarse_select_kernel<16><<<nq, 256, sm2, st>>>(nc, d, nrec, nprobe, kprime, W.cand_cap, queries, centroids,
-                                                       W.grp_val, W.grp_idx, impl >= 3 ? 2 : (impl >= 1 ? 1 : 0), kept, self_off, impl >= 2 ? S.cmax : nullptr, S.qstat, gshift, W.err, out_d, out_i);
+                                                       W.grp_val, W.grp_idx, impl >= 3 ? 2 : (impl >= 1 ? 1 : 0), kept, self_off, impl >= 2 ? S.cmax : nullptr, S.qstat, gshift, pre, pcap, W.err, out_d, out_i);
     }
     ++*launches;
     return cudaGetLastError();

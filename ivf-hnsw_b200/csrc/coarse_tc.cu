@@ -227,7 +227,10 @@ struct TcParams {
 // KEEP: values kept per (query, group of 128 centroids): 4, or 3 / 2 when the groups are many (see launch_coarse)
 // IKEY: integer keys (impl 3, common.cuh): one FFMA + one IMAD on the FMA pipe build the key, KEEP * 2 - 1 integer
 // min/max insert it -- the ALU pipe (half rate for min/max and logic ops) is what bounds this kernel
-template <int MT, int KEEP, bool IKEY, int DIAG = 0>
+// PRE (IKEY only): 2 = the keys of columns (2j, 2j+1) are reduced to their minimum BEFORE the sorted insert (1 + (2 KEEP
+// - 1) min/max per two elements instead of 2 (2 KEEP - 1)); a kept key then stands for its column PAIR and the select
+// stage scores the other column of every surviving pair exactly
+template <int MT, int KEEP, bool IKEY, int DIAG = 0, int PRE = 1>
 __global__ void __launch_bounds__(TC_THREADS, 1)
 coarse_tc_kernel(const __grid_constant__ CUtensorMap tm_qhi, const __grid_constant__ CUtensorMap tm_qlo,
                  const __grid_constant__ CUtensorMap tm_chi, const __grid_constant__ CUtensorMap tm_clo, TcParams p)
@@ -475,6 +478,7 @@ coarse_tc_kernel(const __grid_constant__ CUtensorMap tm_qhi, const __grid_consta
                     for (int i4 = 0; i4 < 8; i4++) {
                         const float4 cn = cn4[i4];
                         const float cnv[4] = {cn.x, cn.y, cn.z, cn.w};
+                        uint32_t kprev = 0xffffffffu;
 #pragma unroll
                         for (int ii = 0; ii < 4; ii++) {
                             const int i = i4 * 4 + ii;
@@ -486,6 +490,10 @@ coarse_tc_kernel(const __grid_constant__ CUtensorMap tm_qhi, const __grid_consta
                                 uint32_t key;
                                 const uint32_t cst = (uint32_t)(jb * 32 + i) - (0x4e800000u << 7);
                                 asm("mad.lo.u32 %0, %1, %2, %3;" : "=r"(key) : "r"(__float_as_uint(val)), "r"(key_mul), "r"(cst));
+                                if (PRE == 2) {
+                                    if (!(ii & 1)) { kprev = key; continue; }
+                                    key = min(key, kprev);
+                                }
                                 const uint32_t m0 = max(k0, key);
                                 k0 = min(k0, key);
                                 if (KEEP == 2) k1 = min(k1, m0);
@@ -584,10 +592,11 @@ bool coarse_tc_supported(int d) { return d >= 16 && d <= 256; }
 
 cudaError_t launch_coarse_tc(cudaStream_t st, uint64_t *launches, int nq, int nc, int d, const float *queries,
                              const float *cnorm_gemm, const TcSide &S, float *grp_val, int nterms, int keep, int ikey,
-                             int gshift)
+                             int gshift, int pre)
 {
     if (!coarse_tc_supported(d)) return cudaErrorNotSupported;
     if (gshift && (!ikey || gshift != 2)) return cudaErrorInvalidValue;
+    if (pre != 1 && (pre != 2 || !ikey || keep > 3)) return cudaErrorInvalidValue;
     // split the query rows (per-row power-of-two scale); batch statistics for the integer-key scale / select margin
     cudaError_t e = cudaMemsetAsync(S.qstat, 0, 8, st);
     if (e != cudaSuccess) return e;
@@ -644,6 +653,12 @@ cudaError_t launch_coarse_tc(cudaStream_t st, uint64_t *launches, int nq, int nc
         if (e != cudaSuccess) return e;                                                                                \
         coarse_tc_kernel<MTV, KV, IK, DG><<<grid, TC_THREADS, smem, st>>>(m_qhi, m_qlo, m_chi, m_clo, p);              \
     } while (0)
+#define IVF_TC_LAUNCH5(MTV, KV, IK, DG, PR)                                                                            \
+    do {                                                                                                               \
+        e = cudaFuncSetAttribute(coarse_tc_kernel<MTV, KV, IK, DG, PR>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem); \
+        if (e != cudaSuccess) return e;                                                                                \
+        coarse_tc_kernel<MTV, KV, IK, DG, PR><<<grid, TC_THREADS, smem, st>>>(m_qhi, m_qlo, m_chi, m_clo, p);          \
+    } while (0)
 #define IVF_TC_LAUNCH(MTV, KV, IK)                                                                                     \
     do {                                                                                                               \
         e = cudaFuncSetAttribute(coarse_tc_kernel<MTV, KV, IK>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem); \
@@ -651,10 +666,13 @@ cudaError_t launch_coarse_tc(cudaStream_t st, uint64_t *launches, int nq, int nc
         coarse_tc_kernel<MTV, KV, IK><<<grid, TC_THREADS, smem, st>>>(m_qhi, m_qlo, m_chi, m_clo, p);                  \
     } while (0)
     static const int diag = getenv("IVFHNSW_B200_TC_DIAG") ? atoi(getenv("IVFHNSW_B200_TC_DIAG")) : 0;   // timing experiments
-    if (diag && ikey && MT == 2 && keep == 2) {
+    if (diag && ikey && MT == 2 && keep == 2 && pre == 1) {
         if (diag == 1) IVF_TC_LAUNCH4(2, 2, true, 1);
         else if (diag == 2) IVF_TC_LAUNCH4(2, 2, true, 2);
         else IVF_TC_LAUNCH4(2, 2, true, 3);
+    } else if (ikey && pre == 2) {
+        if (MT == 2) { if (keep == 2) IVF_TC_LAUNCH5(2, 2, true, 0, 2); else IVF_TC_LAUNCH5(2, 3, true, 0, 2); }
+        else { if (keep == 2) IVF_TC_LAUNCH5(1, 2, true, 0, 2); else IVF_TC_LAUNCH5(1, 3, true, 0, 2); }
     } else if (ikey) {
         if (MT == 2) { if (keep == 2) IVF_TC_LAUNCH(2, 2, true); else if (keep == 3) IVF_TC_LAUNCH(2, 3, true); else IVF_TC_LAUNCH(2, 4, true); }
         else { if (keep == 2) IVF_TC_LAUNCH(1, 2, true); else if (keep == 3) IVF_TC_LAUNCH(1, 3, true); else IVF_TC_LAUNCH(1, 4, true); }
@@ -664,6 +682,7 @@ cudaError_t launch_coarse_tc(cudaStream_t st, uint64_t *launches, int nq, int nc
     }
 #undef IVF_TC_LAUNCH
 #undef IVF_TC_LAUNCH4
+#undef IVF_TC_LAUNCH5
     ++*launches;
     return cudaGetLastError();
 }

@@ -73,3 +73,52 @@ def test_neighbour_lists_exclude_self_at_2_18():
     assert torch.allclose(torch.gather(dd, 1, nn), want, rtol=2e-5, atol=1e-4)
     assert torch.allclose(icd.double(), want, rtol=2e-5, atol=1e-4)
     idx.close()
+
+
+@pytest.mark.parametrize("exclude_self", [False, True])
+def test_adjacent_columns_both_among_the_nearest(exclude_self):
+    """impl 3 at >= 2048 groups reduces every column pair (2j, 2j+1) to its smaller key in the GEMM epilogue; the select
+    stage must bring the other column back.  Worst case on purpose: centroid 2j+1 is a slightly perturbed copy of
+    centroid 2j, so BOTH columns of a pair are among the nearest of every query -- including the pair that holds the
+    query's own centroid in the self-excluding search of K-G3."""
+    import torch
+    pkg = load_pkg()
+    dev = torch.device("cuda:0")
+    nc, d = 1 << 18, 32
+    g = torch.Generator(device=dev)
+    g.manual_seed(4242)
+    C = torch.randn(nc, d, device=dev, generator=g)
+    C[1::2] = C[0::2] + 1e-3 * torch.randn(nc // 2, d, device=dev, generator=g)
+    if exclude_self:
+        nsubc = 16
+        idx = pkg.IndexIVF_HNSW_Grouping(d, nc, 8, 8, nsubc)
+        idx.build_quantizer(centroids=C.cpu().numpy())
+        idx.finalize()
+        out = idx.export_index_dict()
+        rows = torch.randint(0, nc, (2000,), device=dev, generator=g)
+        dd = _brute(torch, C[rows], C, d)
+        dd[torch.arange(rows.numel(), device=dev), rows] = float("inf")
+        want = torch.sort(dd, dim=1).values[:, :nsubc]
+        nn = torch.from_numpy(out["nn_idx"].astype(np.int64)).to(dev)[rows]
+        assert not bool((nn == rows[:, None]).any())
+        assert bool((nn[:, 0] == (rows ^ 1)).all())      # the perturbed copy is the nearest OTHER centroid
+        assert torch.allclose(torch.gather(dd, 1, nn), want, rtol=2e-5, atol=1e-4)
+    else:
+        idx = pkg.IndexIVF_HNSW(d, nc, 8, 8)
+        idx.build_quantizer(centroids=C.cpu().numpy())
+        nq = 400
+        Q = C[torch.randint(0, nc, (nq,), device=dev, generator=g)] + 0.3 * torch.randn(nq, d, device=dev, generator=g)
+        dd = _brute(torch, Q, C, d)
+        for nprobe in (1, 2, 32, 128):
+            cd = torch.empty(nq, nprobe, device=dev)
+            ci = torch.empty(nq, nprobe, dtype=torch.int32, device=dev)
+            idx.coarse_dev(Q, nprobe, cd, ci)
+            idx.sync()
+            want = torch.sort(dd, dim=1).values[:, :nprobe]
+            assert torch.allclose(torch.gather(dd, 1, ci.long()), want, rtol=2e-5, atol=1e-4), nprobe
+            assert torch.allclose(cd.double(), want, rtol=2e-5, atol=1e-4), nprobe
+            assert int((torch.sort(ci, dim=1).values.diff(dim=1) == 0).sum()) == 0
+            if nprobe >= 2:   # both columns of the nearest pair are returned
+                assert float(((ci[:, 0] ^ 1) == ci[:, 1]).float().mean()) > 0.9
+    idx.stats()
+    idx.close()
