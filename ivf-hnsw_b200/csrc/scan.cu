@@ -124,16 +124,32 @@ struct ProbeMeta {
 };
 
 // pass-1 horizon (:229-259): list i is visited iff non-empty and the sizes before it sum to < 2*max_codes.
-// Executed by warp 0; results in shared memory.
-static __device__ __forceinline__ void probe_meta_warp0(int nprobe, uint64_t max_codes, const uint32_t *coarse_i_q,
-                                                        const DeviceLists &L, uint32_t *s_c, uint32_t *s_sz,
-                                                        uint8_t *s_inh, int lane)
+// Whole CTA: every probe's (centroid id, list size) is fetched by its own thread -- ONE round of dependent global loads
+// for all probes -- then warp 0 runs the prefix over shared memory.  (One warp doing both, 32 probes per trip, left
+// the other 15 warps of the three preparation kernels at the barrier for 4 serial round trips: 25-35 % of K-G1c/K-G3.)
+// Contains a __syncthreads(); the caller syncs again before reading the results.
+struct ProbeNoExtra {
+    __device__ __forceinline__ void operator()(int, uint32_t) const {}
+};
+template <class Extra = ProbeNoExtra>   // extra(i, c): further per-probe loads that ride the same round trip
+static __device__ __forceinline__ void probe_meta_cta(int nprobe, uint64_t max_codes, const uint32_t *coarse_i_q,
+                                                      const DeviceLists &L, uint32_t *s_c, uint32_t *s_sz,
+                                                      uint8_t *s_inh, int tid, int nthreads, Extra extra = Extra())
 {
+    for (int i = tid; i < nprobe; i += nthreads) {
+        const uint32_t c = coarse_i_q[i];
+        const uint32_t sz = L.list_size[c];
+        extra(i, c);
+        s_c[i] = c;
+        s_sz[i] = sz;
+    }
+    __syncthreads();
+    if (tid >= 32) return;
+    const int lane = tid;
     uint64_t run = 0;
     for (int base = 0; base < nprobe; base += 32) {
         const int i = base + lane;
-        uint32_t c = 0, sz = 0;
-        if (i < nprobe) { c = coarse_i_q[i]; sz = L.list_size[c]; }
+        const uint32_t sz = i < nprobe ? s_sz[i] : 0u;
         uint64_t incl = sz;
 #pragma unroll
         for (int off = 1; off < 32; off <<= 1) {
@@ -141,11 +157,7 @@ static __device__ __forceinline__ void probe_meta_warp0(int nprobe, uint64_t max
             if (lane >= off) incl += t;
         }
         const uint64_t excl = run + incl - sz;
-        if (i < nprobe) {
-            s_c[i] = c;
-            s_sz[i] = sz;
-            s_inh[i] = (sz > 0 && excl < 2 * max_codes) ? 1 : 0;
-        }
+        if (i < nprobe) s_inh[i] = (sz > 0 && excl < 2 * max_codes) ? 1 : 0;
         run += __shfl_sync(IVF_FULL_MASK, incl, 31);
     }
 }
@@ -221,7 +233,7 @@ __global__ void __launch_bounds__(G1_THREADS) group_g1a_kernel(int nprobe, int n
     float2 *dv = Wk.dv + (size_t)q * Wk.cap;
     for (int i = tid; i < ht_size; i += G1_THREADS) hk[i] = 0xffffffffu;
     if (tid == 0) { s_nwork = 0; s_nmemo = 0; }
-    if (warp == 0) probe_meta_warp0(nprobe, max_codes, coarse_i + qo, L, s_c, s_sz, s_inh, lane);
+    probe_meta_cta(nprobe, max_codes, coarse_i + qo, L, s_c, s_sz, s_inh, tid, G1_THREADS);
     __syncthreads();
     // ---- the coarse stage already knows d(q, c) of the probed centroids: they enter the table as done (the
     // reference's query_centroid_dists memo), unless the value is < EPS, which the reference treats as "not
@@ -441,14 +453,12 @@ __global__ void __launch_bounds__(G1_THREADS) group_g1c_kernel(int nprobe, int n
     const size_t qo = (size_t)q * nprobe;
     const float qnan = __int_as_float(0x7fc00000);
     if (tid == 0) s_count = 0;
-    if (warp == 0) probe_meta_warp0(nprobe, max_codes, coarse_i + qo, L, s_c, s_sz, s_inh, lane);
-    __syncthreads();
-    for (int i = tid; i < nprobe; i += G1_THREADS) {
-        const uint32_t c = s_c[i];
-        s_alpha[i] = L.alphas[c];
-        s_cd[i] = coarse_d[qo + i];
-        s_cn[i] = L.centroid_norms[c];
-    }
+    probe_meta_cta(nprobe, max_codes, coarse_i + qo, L, s_c, s_sz, s_inh, tid, G1_THREADS, [&](int i, uint32_t c) {
+        const float al = L.alphas[c], cd = coarse_d[qo + i], cn = L.centroid_norms[c];
+        s_alpha[i] = al;
+        s_cd[i] = cd;
+        s_cn[i] = cn;
+    });
     __syncthreads();
     const int npairs = nprobe * nsubc;
     const uint16_t *ppos = Wk.ppos + (size_t)q * npairs;
@@ -566,7 +576,7 @@ __global__ void __launch_bounds__(G1_THREADS) group_g3_kernel(int nprobe, int ns
     const int q = blockIdx.x, tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     const size_t qo = (size_t)q * nprobe;
     const int npairs = nprobe * nsubc;
-    if (warp == 0) probe_meta_warp0(nprobe, max_codes, coarse_i + qo, L, s_c, s_sz, s_inh, lane);
+    probe_meta_cta(nprobe, max_codes, coarse_i + qo, L, s_c, s_sz, s_inh, tid, G1_THREADS);
     for (int i = tid; i < nprobe; i += G1_THREADS) s_kept[i] = 0;
     __syncthreads();
     const float threshold = do_pruning ? T.threshold[q] : 0.f;
