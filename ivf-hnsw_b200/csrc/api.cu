@@ -371,6 +371,8 @@ static TcSide tc_side(ivfhnsw_b200_t *h, size_t qb)
     S.chi = h->cent_f16.as<__half>();
     S.clo = S.chi ? S.chi + h->nc * S.dp : nullptr;
     S.cmax = S.chi ? reinterpret_cast<uint32_t *>(S.clo + h->nc * S.dp) : nullptr;
+    S.cnp = S.chi ? reinterpret_cast<float *>(S.cmax + 16) : nullptr;
+    S.idmul = coarse_col_multiplier(h->nc);
     S.qhi = h->w_xf16.as<__half>();
     S.qlo = S.qhi ? S.qhi + qb * S.dp : nullptr;
     S.qfac = S.qhi ? reinterpret_cast<float *>(S.qlo + qb * S.dp) : nullptr;
@@ -389,7 +391,7 @@ static int ensure_gemm_side(ivfhnsw_b200_t *h)
     }
     if (use_tc(h) && !h->f16_valid) {
         TcSide S = tc_side(h, 0);
-        CU(h->cent_f16.ensure(h->nc * S.dp * 4 + 64));
+        CU(h->cent_f16.ensure(h->nc * S.dp * 4 + 64 + h->nc * 4));
         S = tc_side(h, 0);
         CU(launch_tc_prepare_centroids(h->stream, LAUNCHES, h->nc, (int)h->d, h->centroids.as<float>(),
                                        h->cnorm_gemm.as<float>(), S));
@@ -1254,7 +1256,7 @@ static int scan_core(ivfhnsw_b200_t *h, size_t nq, size_t k, const float *x_dev,
             ps = reinterpret_cast<uint32_t *>(pd + (size_t)qb * nsplit * k);
             pl = ps + (size_t)qb * nsplit * k;
         }
-        CU(launch_lut(st, LAUNCHES, M, nb, d, xq, h->pqc.as<float>(), h->w_lut.as<float>()));
+        CU(launch_lut(st, LAUNCHES, M, nb, d, xq, h->pqc.as<float>(), h->w_lut.as<float>(), T.qnp));
         if (h->debug >= 2) CU(cudaStreamSynchronize(st));   // localise asynchronous kernel faults
         if (h->timing) CU(cudaEventRecord(h->ev[5], st));
         CU(launch_scan(st, LAUNCHES, M, grouping, nb, d, nprobe, nsubc, h->do_pruning, (int)k, nsplit, h->w_lut.as<float>(),

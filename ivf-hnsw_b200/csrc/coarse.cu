@@ -140,6 +140,7 @@ __global__ void __launch_bounds__(256) coarse_select_kernel(int nc, int d, int n
                                                             int gshift /* packed == 2: log2(tiles per record) */,
                                                             int pre /* packed == 2: 2 = a key stands for a column pair */,
                                                             int pcap /* pre == 2: capacity of the partner list */,
+                                                            uint32_t idmul /* packed: column -> id multiplier, 0 = identity */,
                                                             uint32_t *__restrict__ err,
                                                             float *__restrict__ out_d, uint32_t *__restrict__ out_i)
 {
@@ -165,6 +166,8 @@ __global__ void __launch_bounds__(256) coarse_select_kernel(int nc, int d, int n
     const uint32_t kinv = packed == 2 ? COARSE_KEY_INVALID_MIN : fkey(1.0e38f);
     auto entry_key = [&](int i) -> uint32_t { return packed == 2 ? gk[i] : fkey(gv[i]); };
     auto is_self = [&](uint32_t id) -> bool { return self_off >= 0 && id == (uint32_t)(q + self_off); };
+    // tensor-core GEMM: column -> centroid id (TcSide::idmul)
+    auto col_id = [&](uint32_t col) -> uint32_t { return idmul ? (uint32_t)(((uint64_t)col * idmul) % (uint32_t)nc) : col; };
     auto entry_id = [&](int i) -> uint32_t {     // NOT filtered for the self match when packed (see the collect pass)
         if (!packed) return gi[i];
         uint32_t col;
@@ -176,7 +179,7 @@ __global__ void __launch_bounds__(256) coarse_select_kernel(int nc, int d, int n
             if (!(v < 1.0e38f)) return 0xffffffffu;
             col = __float_as_uint(v) & 127u;
         }
-        return (uint32_t)(i / COARSE_T) * gsize + col;
+        return col_id((uint32_t)(i / COARSE_T) * gsize + col);
     };
     for (int i = tid; i < d; i += 256) sq[i] = Q[(size_t)q * d + i];
     if (tid == 0) { s_prefix = 0; s_remaining = (uint32_t)kprime; s_ncand = 0; s_nflag = 0; s_less = 0; s_or = 0u; s_and = 0xffffffffu; s_npc = 0; }
@@ -331,16 +334,22 @@ __global__ void __launch_bounds__(256) coarse_select_kernel(int nc, int d, int n
         const float wide = tf + 2.f * 1.02f * eps + fabsf(tf) * 6.2e-5f;
         if (tf < 1.0e38f) tau = fkey(wide);
     }
-    auto push_entry = [&](uint32_t id) {
+    auto push_id = [&](uint32_t id) {
         if (!is_self(id)) {
             const uint32_t p = atomicAdd(&s_ncand, 1u);
             if (p < (uint32_t)cand_cap) cand[p] = id;
         }
-        if (pre == 2) {      // the kept key is the smaller of columns (id, id ^ 1): the other one may pass too
-            const uint32_t pid = id ^ 1u;
-            if (pid < (uint32_t)nc && !is_self(pid)) {
-                const uint32_t p = atomicAdd(&s_npc, 1u);
-                if (p < (uint32_t)pcap) pcand[p] = pid;
+    };
+    auto push_col = [&](uint32_t col) {      // integer keys: a GEMM column
+        push_id(col_id(col));
+        if (pre == 2) {      // the kept key is the smaller of columns (col, col ^ 1): the other one may pass too
+            const uint32_t pc = col ^ 1u;
+            if (pc < (uint32_t)nc) {
+                const uint32_t pid = col_id(pc);
+                if (!is_self(pid)) {
+                    const uint32_t p = atomicAdd(&s_npc, 1u);
+                    if (p < (uint32_t)pcap) pcand[p] = pid;
+                }
             }
         }
     };
@@ -376,7 +385,7 @@ __global__ void __launch_bounds__(256) coarse_select_kernel(int nc, int d, int n
             }
 #pragma unroll
             for (int j = 0; j < 4; j++)
-                if (ev[j] <= tau) push_entry((uint32_t)g * gsize + (ev[j] & (gsize - 1u)));
+                if (ev[j] <= tau) push_col((uint32_t)g * gsize + (ev[j] & (gsize - 1u)));
         }
         __syncthreads();
     }
@@ -404,15 +413,16 @@ __global__ void __launch_bounds__(256) coarse_select_kernel(int nc, int d, int n
             const uint32_t g = (uint32_t)(i / COARSE_T);
             bool flagged = false;
             for (uint32_t f = 0; f < nflag; f++) flagged |= (s_flag[f] == g);
-            if (!flagged) push_entry(id);
+            if (!flagged) push_id(id);
         }
     }
     __syncthreads();
     for (uint32_t f = 0; f < nflag; f++) {
         const uint32_t g = s_flag[f];
         for (uint32_t j = tid; j < gsize; j += 256) {
-            const uint32_t id = g * gsize + j;
-            if (id < (uint32_t)nc && !is_self(id)) {
+            const uint32_t col = g * gsize + j;
+            const uint32_t id = (packed && col < (uint32_t)nc) ? col_id(col) : col;
+            if (col < (uint32_t)nc && !is_self(id)) {
                 const uint32_t p = atomicAdd(&s_ncand, 1u);
                 if (p < (uint32_t)cand_cap) cand[p] = id;
             }
@@ -520,7 +530,7 @@ cudaError_t launch_coarse(cudaStream_t st, uint64_t *launches, int impl, int nq,
     const int pcap = pre == 2 ? 1024 : 0;
     cudaError_t e;
     if (impl >= 1) {
-        e = launch_coarse_tc(st, launches, nq, nc, d, queries, cnorm_gemm, S, W.grp_val, impl >= 2 ? 1 : 2, kept,
+        e = launch_coarse_tc(st, launches, nq, nc, d, queries, S.cnp, S, W.grp_val, impl >= 2 ? 1 : 2, kept,
                              impl >= 3 ? 1 : 0, gshift, pre);
         if (e != cudaSuccess) return e;
     } else {
@@ -549,12 +559,12 @@ cudaError_t launch_coarse(cudaStream_t st, uint64_t *launches, int impl, int nq,
         e = cudaFuncSetAttribute(coarse_select_kernel<8>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sm2);
         if (e != cudaSuccess) return e;
         coarse_select_kernel<8><<<nq, 256, sm2, st>>>(nc, d, nrec, nprobe, kprime, W.cand_cap, queries, centroids,
-                                                      W.grp_val, W.grp_idx, impl >= 3 ? 2 : (impl >= 1 ? 1 : 0), kept, self_off, impl >= 2 ? S.cmax : nullptr, S.qstat, gshift, pre, pcap, W.err, out_d, out_i);
+                                                      W.grp_val, W.grp_idx, impl >= 3 ? 2 : (impl >= 1 ? 1 : 0), kept, self_off, impl >= 2 ? S.cmax : nullptr, S.qstat, gshift, pre, pcap, impl >= 1 ? S.idmul : 0u, W.err, out_d, out_i);
     } else {
         e = cudaFuncSetAttribute(coarse_select_kernel<16>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sm2);
         if (e != cudaSuccess) return e;
         coarse_select_kernel<16><<<nq, 256, sm2, st>>>(nc, d, nrec, nprobe, kprime, W.cand_cap, queries, centroids,
-                                                       W.grp_val, W.grp_idx, impl >= 3 ? 2 : (impl >= 1 ? 1 : 0), kept, self_off, impl >= 2 ? S.cmax : nullptr, S.qstat, gshift, pre, pcap, W.err, out_d, out_i);
+                                                       W.grp_val, W.grp_idx, impl >= 3 ? 2 : (impl >= 1 ? 1 : 0), kept, self_off, impl >= 2 ? S.cmax : nullptr, S.qstat, gshift, pre, pcap, impl >= 1 ? S.idmul : 0u, W.err, out_d, out_i);
     }
     ++*launches;
     return cudaGetLastError();

@@ -58,12 +58,12 @@ __global__ void split_rows_kernel(size_t n, int d, int dp, const float *__restri
                                   const uint32_t *__restrict__ shared_max, const uint32_t *__restrict__ other_max,
                                   __half *__restrict__ hi, __half *__restrict__ lo, float *__restrict__ fac,
                                   uint32_t *__restrict__ stat /* [2]: max ||row||^2 bits, any non-zero lo; may be null */,
-                                  int dk /* dims the GEMM uses */)
+                                  int dk /* dims the GEMM uses */, uint32_t idmul = 0 /* output row j = input row j*idmul mod n */)
 {
     const int lane = threadIdx.x & 31;
     const size_t row = (size_t)blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
     if (row >= n) return;
-    const float *xr = x + row * d;
+    const float *xr = x + (idmul ? (size_t)(((uint64_t)row * idmul) % n) : row) * d;
     float s;
     if (shared_max) s = pow2_scale_for(__uint_as_float(*shared_max));
     else {
@@ -104,6 +104,33 @@ __global__ void split_rows_kernel(size_t n, int d, int dp, const float *__restri
     }
 }
 
+__global__ void permute_norms_kernel(size_t n, uint32_t idmul, const float *__restrict__ in, float *__restrict__ out)
+{
+    const size_t j = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (j < n) out[j] = in[idmul ? (size_t)(((uint64_t)j * idmul) % n) : j];
+}
+
+// id(col) = col * A mod nc with A the inverse of G ~ nc / golden ratio: consecutive ids sit G columns apart (mod nc), the
+// most evenly spread arrangement there is (three-distance theorem), so a run of neighbouring ids never piles up in one
+// group of 128 columns
+uint32_t coarse_col_multiplier(size_t nc)
+{
+    if (nc < 4) return 0;
+    auto gcd = [](uint64_t a, uint64_t b) { while (b) { const uint64_t t = a % b; a = b; b = t; } return a; };
+    uint64_t G = (uint64_t)((double)nc * 0.6180339887498949);
+    if (G < 1) G = 1;
+    while (gcd(G, nc) != 1) G++;
+    // modular inverse of G (extended Euclid)
+    int64_t t0 = 0, t1 = 1, r0 = (int64_t)nc, r1 = (int64_t)(G % nc);
+    while (r1) {
+        const int64_t qv = r0 / r1;
+        const int64_t t2 = t0 - qv * t1; t0 = t1; t1 = t2;
+        const int64_t r2 = r0 - qv * r1; r0 = r1; r1 = r2;
+    }
+    if (t0 < 0) t0 += (int64_t)nc;
+    return (uint32_t)t0;
+}
+
 cudaError_t launch_tc_prepare_centroids(cudaStream_t st, uint64_t *launches, size_t nc, int d, const float *centroids,
                                         const float *cnorm_gemm, const TcSide &S)
 {
@@ -117,7 +144,9 @@ cudaError_t launch_tc_prepare_centroids(cudaStream_t st, uint64_t *launches, siz
     maxabs_kernel<<<(unsigned)((nc + 255) / 256 < 1184 ? (nc + 255) / 256 : 1184), 256, 0, st>>>(nc, cnorm_gemm, S.cmax + 1);
     ++*launches;
     split_rows_kernel<<<(unsigned)((nc + 7) / 8), 256, 0, st>>>(nc, d, S.dp, centroids, S.cmax, nullptr, S.chi, S.clo,
-                                                              nullptr, nullptr, 0);
+                                                              nullptr, nullptr, 0, S.idmul);
+    ++*launches;
+    permute_norms_kernel<<<(unsigned)((nc + 255) / 256), 256, 0, st>>>(nc, S.idmul, cnorm_gemm, S.cnp);
     ++*launches;
     return cudaGetLastError();
 }

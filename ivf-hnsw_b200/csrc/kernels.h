@@ -89,7 +89,7 @@ size_t scan_smem_bytes(int M, int nprobe, int k, int nsubc);
 // partial outputs [nq][nsplit][k]; when nsplit == 1 the kernel writes the final (distances, labels) directly
 // compact per-query tables lutc[q][j][m] = -2 <q_m, c_{m,j}> consumed by launch_scan
 cudaError_t launch_lut(cudaStream_t st, uint64_t *launches, int M, int nq, int d, const float *queries,
-                       const float *pqc, float *lutc);
+                       const float *pqc, float *lutc, const uint32_t *qnp = nullptr);
 cudaError_t launch_scan(cudaStream_t st, uint64_t *launches, int M, bool grouping, int nq, int d, int nprobe,
                         int nsubc, bool pruned, int k, int nsplit, const float *lutc, const float *norm_table,
                         const DeviceLists &L, const SegTables &T, uint32_t c_begin, uint32_t c_end, float *part_d,
@@ -136,7 +136,14 @@ struct TcSide {
     float *qfac;            // [batch] -2 / (query scale * centroid scale)
     uint32_t *qstat;        // [2] impl 3: bits of max ||q||^2 over the batch, 1 if any query has a non-zero lo part
     int dp;
+    // GEMM column j holds centroid id (j * idmul) mod nc: a fixed low-discrepancy permutation, so that centroids with
+    // NEIGHBOURING ids (locality-ordered tables, see coarse_col_multiplier) never share a group of 128 columns -- the
+    // epilogue keeps a few values per group and the select stage re-scans a group that may hide more
+    float *cnp;             // [nc] ||c||^2 in column order
+    uint32_t idmul;         // 0 = identity
 };
+// multiplier of the column -> centroid id map for a table of nc centroids (host)
+uint32_t coarse_col_multiplier(size_t nc);
 bool coarse_tc_supported(int d);
 cudaError_t launch_tc_prepare_centroids(cudaStream_t st, uint64_t *launches, size_t nc, int d, const float *centroids,
                                         const float *cnorm_gemm, const TcSide &S);

@@ -755,7 +755,8 @@ cudaError_t launch_prep_grouping(cudaStream_t st, uint64_t *launches, int nq, in
 #define LUT_QPB 8
 template <int M>
 __global__ void __launch_bounds__(256) lut_kernel(int nq, int d, const float *__restrict__ queries,
-                                                  const float *__restrict__ pqc, float *__restrict__ lutc)
+                                                  const float *__restrict__ pqc, float *__restrict__ lutc,
+                                                  const uint32_t *__restrict__ qnp /* may be null: 0 = skip the query */)
 {
     extern __shared__ __align__(16) float sq[];   // [LUT_QPB][d]
     const int q0 = blockIdx.x * LUT_QPB, j = threadIdx.x;
@@ -764,6 +765,7 @@ __global__ void __launch_bounds__(256) lut_kernel(int nq, int d, const float *__
     __syncthreads();
     const int dsub = d / M;
     for (int qq = 0; qq < nqb; qq++) {
+        if (qnp && qnp[q0 + qq] == 0) continue;     // sharded scan: nothing of this query lives on this rank
         float v[M];
 #pragma unroll
         for (int m = 0; m < M; m++) {
@@ -801,7 +803,8 @@ __global__ void __launch_bounds__(256) lut_kernel(int nq, int d, const float *__
 #define LUT_REG_QPB 32
 template <int M, int DSUB>
 __global__ void __launch_bounds__(256) lut_reg_kernel(int nq, const float *__restrict__ queries,
-                                                      const float *__restrict__ pqc, float *__restrict__ lutc)
+                                                      const float *__restrict__ pqc, float *__restrict__ lutc,
+                                                      const uint32_t *__restrict__ qnp /* may be null: 0 = skip */)
 {
     constexpr int D = M * DSUB;
     __shared__ __align__(16) float sq[LUT_REG_QPB * D];
@@ -815,6 +818,7 @@ __global__ void __launch_bounds__(256) lut_reg_kernel(int nq, const float *__res
         for (int t = 0; t < DSUB; t++) c[m * DSUB + t] = __ldg(pqc + ((size_t)m * 256 + j) * DSUB + t);
     __syncthreads();
     for (int qq = 0; qq < nqb; qq++) {
+        if (qnp && qnp[q0 + qq] == 0) continue;     // sharded scan: nothing of this query lives on this rank
         float qv[D];
 #pragma unroll
         for (int i = 0; i < D / 4; i++) {
@@ -839,20 +843,21 @@ __global__ void __launch_bounds__(256) lut_reg_kernel(int nq, const float *__res
 }
 
 template <int M, int DSUB>
-static cudaError_t launch_lut_reg(cudaStream_t st, int nq, const float *queries, const float *pqc, float *lutc)
+static cudaError_t launch_lut_reg(cudaStream_t st, int nq, const float *queries, const float *pqc, float *lutc,
+                                  const uint32_t *qnp)
 {
-    lut_reg_kernel<M, DSUB><<<(unsigned)((nq + LUT_REG_QPB - 1) / LUT_REG_QPB), 256, 0, st>>>(nq, queries, pqc, lutc);
+    lut_reg_kernel<M, DSUB><<<(unsigned)((nq + LUT_REG_QPB - 1) / LUT_REG_QPB), 256, 0, st>>>(nq, queries, pqc, lutc, qnp);
     return cudaGetLastError();
 }
 
 cudaError_t launch_lut(cudaStream_t st, uint64_t *launches, int M, int nq, int d, const float *queries,
-                       const float *pqc, float *lutc)
+                       const float *pqc, float *lutc, const uint32_t *qnp)
 {
     if (nq == 0) return cudaSuccess;
     ++*launches;
     const int dsub = d / M;
     // register-resident codebook for the usual shapes (d <= 128, d % 4 == 0)
-#define IVF_LUT_CASE(MM, DS) if (M == MM && dsub == DS) return launch_lut_reg<MM, DS>(st, nq, queries, pqc, lutc);
+#define IVF_LUT_CASE(MM, DS) if (M == MM && dsub == DS) return launch_lut_reg<MM, DS>(st, nq, queries, pqc, lutc, qnp);
     IVF_LUT_CASE(8, 4) IVF_LUT_CASE(8, 12) IVF_LUT_CASE(8, 16)
     IVF_LUT_CASE(16, 2) IVF_LUT_CASE(16, 6) IVF_LUT_CASE(16, 8)
     IVF_LUT_CASE(32, 3) IVF_LUT_CASE(32, 4)
@@ -861,10 +866,10 @@ cudaError_t launch_lut(cudaStream_t st, uint64_t *launches, int M, int nq, int d
     const unsigned grid = (unsigned)((nq + LUT_QPB - 1) / LUT_QPB);
     const size_t sm = (size_t)LUT_QPB * d * 4;
     switch (M) {
-    case 8: lut_kernel<8><<<grid, 256, sm, st>>>(nq, d, queries, pqc, lutc); break;
-    case 16: lut_kernel<16><<<grid, 256, sm, st>>>(nq, d, queries, pqc, lutc); break;
-    case 32: lut_kernel<32><<<grid, 256, sm, st>>>(nq, d, queries, pqc, lutc); break;
-    case 64: lut_kernel<64><<<grid, 256, sm, st>>>(nq, d, queries, pqc, lutc); break;
+    case 8: lut_kernel<8><<<grid, 256, sm, st>>>(nq, d, queries, pqc, lutc, qnp); break;
+    case 16: lut_kernel<16><<<grid, 256, sm, st>>>(nq, d, queries, pqc, lutc, qnp); break;
+    case 32: lut_kernel<32><<<grid, 256, sm, st>>>(nq, d, queries, pqc, lutc, qnp); break;
+    case 64: lut_kernel<64><<<grid, 256, sm, st>>>(nq, d, queries, pqc, lutc, qnp); break;
     default: --*launches; return cudaErrorInvalidValue;
     }
     return cudaGetLastError();
@@ -875,7 +880,9 @@ cudaError_t launch_lut(cudaStream_t st, uint64_t *launches, int M, int nq, int d
 // =============================================================================================
 struct ScanArgs {
     int d, nprobe, nsubc, k, nsplit;
-    int seg;                  // list positions per work item (<= SCAN_SEG)
+    int seg;                  // most list positions per work item (<= SCAN_SEG)
+    int seg_min;              // fewest; a query's item length is the power of two in between that gives ~items_target items
+    int items_target;
     int pruned;               // Grouping: sub-groups may be pruned (sub_base = +inf) -> tile kept runs only
     const float *lutc;        // [nq][256][M] compact tables from K-L1
     const float *norm_table;  // [256]
@@ -932,7 +939,8 @@ struct ScanCtl {
     uint32_t worst_seq;
     float worst_d;      // == the insertion threshold (lock path)
     uint32_t thr_key;   // min over the warps of fkey(k-th best): a bound on the CTA's final k-th best
-    int pad[2];
+    int seg_len;        // list positions per work item of THIS query (power of two, <= SCAN_SEG)
+    int pad[1];
 };
 
 static __device__ __forceinline__ uint32_t fkey_u32(float f)
@@ -1155,6 +1163,24 @@ __global__ void __launch_bounds__(SCAN_THREADS) scan_kernel(ScanArgs a)
     const int nprobe = a.T.qnp ? (int)a.T.qnp[q] : a.nprobe;
     const uint32_t *rec = a.T.qoff ? a.T.rec + a.T.qoff[q] : a.T.rec + (size_t)q * a.T.stride;
     const float *rec_sub_base = reinterpret_cast<const float *>(rec + 5 * (size_t)nprobe);
+    if (a.T.qnp && nprobe == 0) {
+        // packed records, nothing of this query lives on this rank: the empty result (the order the general path gives
+        // k empty entries), before any table is built
+        for (int r = tid; r < k; r += SCAN_THREADS) {
+            const uint32_t es = 0xffffffffu - (uint32_t)(k - 1 - r);
+            if (a.nsplit == 1) {
+                a.out_d[(size_t)q * k + r] = FLT_MAX;
+                a.out_labels[(size_t)q * k + r] = -1;
+                if (a.out_seq) a.out_seq[(size_t)q * k + r] = es;
+            } else {
+                const size_t o = ((size_t)q * a.nsplit + split) * k + r;
+                a.part_d[o] = FLT_MAX;
+                a.part_seq[o] = es;
+                a.part_slot[o] = IVF_INVALID_SLOT;
+            }
+        }
+        return;
+    }
 
     // ---- stage the query's segment tables (keeping only the lists this GPU owns) and initialise the top-k
     {
@@ -1190,10 +1216,20 @@ __global__ void __launch_bounds__(SCAN_THREADS) scan_kernel(ScanArgs a)
     __syncthreads();
     // exclusive prefix of the work items (ceil(n / SCAN_SEG) parts) of the kept lists
     if (warp == 0) {
+        // work items of this query: the lists are cut so that the CTA has ~4 items per warp -- a query with little to scan
+        // (few probes, a 1/N shard of its lists) would otherwise leave most warps at the final barrier while one
+        // walks a whole list (43 % of the warp samples of a 1/8-shard scan were barrier waits)
+        uint32_t total = 0;
+        for (int b = 0; b < nprobe; b += 32) total += (b + lane < nprobe) ? s_n[b + lane] : 0u;
+#pragma unroll
+        for (int off = 16; off > 0; off >>= 1) total += __shfl_xor_sync(IVF_FULL_MASK, total, off);
+        uint32_t sl = (uint32_t)a.seg_min;
+        while (sl < (uint32_t)a.seg && sl * (uint32_t)a.items_target < total) sl <<= 1;
+        if (lane == 0) ctl->seg_len = (int)sl;
         uint32_t run = 0;
         for (int b = 0; b < nprobe; b += 32) {
             const int i = b + lane;
-            const uint32_t pieces = i < nprobe ? (s_n[i] + (uint32_t)a.seg - 1) / (uint32_t)a.seg : 0u;
+            const uint32_t pieces = i < nprobe ? (s_n[i] + sl - 1) / sl : 0u;
             uint32_t incl = pieces;
 #pragma unroll
             for (int off = 1; off < 32; off <<= 1) {
@@ -1213,6 +1249,7 @@ __global__ void __launch_bounds__(SCAN_THREADS) scan_kernel(ScanArgs a)
     }
     __syncthreads();
     const int npieces = (int)s_poff[nprobe];
+    const uint32_t seg_len = (uint32_t)ctl->seg_len;
     const bool has_work = split < npieces;   // CTA-uniform
 
     // ---- expand the compact table of K-L1 into the bank-conflict-free layout
@@ -1298,7 +1335,7 @@ __global__ void __launch_bounds__(SCAN_THREADS) scan_kernel(ScanArgs a)
         if (piece < SCAN_ITEMS) {
             const uint32_t it = s_item[piece];
             seg = (int)(it & 0xffffu);
-            lo = (it >> 16) * (uint32_t)a.seg;
+            lo = (it >> 16) * seg_len;
         } else {
             for (int b = 0; b < nprobe; b += 32) {
                 const int i = b + lane;
@@ -1306,9 +1343,9 @@ __global__ void __launch_bounds__(SCAN_THREADS) scan_kernel(ScanArgs a)
                 seg += __popc(__ballot_sync(IVF_FULL_MASK, le));
             }
             seg -= 1;
-            lo = (uint32_t)(piece - (int)s_poff[seg]) * (uint32_t)a.seg;
+            lo = (uint32_t)(piece - (int)s_poff[seg]) * seg_len;
         }
-        const uint32_t hi = min(s_n[seg], lo + (uint32_t)a.seg);
+        const uint32_t hi = min(s_n[seg], lo + seg_len);
         const uint32_t lslot = s_slot[seg], lseq = s_seq[seg];
         const float base = s_base[seg];
         int nwin = (int)((hi - lo + W - 1) / W);
@@ -1659,6 +1696,9 @@ cudaError_t launch_scan(cudaStream_t st, uint64_t *launches, int M, bool groupin
     a.pruned = (grouping && pruned) ? 1 : 0;
     // few probes: cut the lists finer so that all 8 warps of a query's CTA find work (ENN: ONE list per query)
     a.seg = nprobe >= 8 ? SCAN_SEG : 128;
+    a.seg_min = 128;
+    static const int items_env = getenv("IVFHNSW_B200_SCAN_ITEMS") ? atoi(getenv("IVFHNSW_B200_SCAN_ITEMS")) : 0;   // profiling switch
+    a.items_target = items_env > 0 ? items_env : 32;
     a.d = d; a.nprobe = nprobe; a.nsubc = grouping ? nsubc : 0; a.k = k; a.nsplit = nsplit;
     a.lutc = lutc; a.norm_table = norm_table; a.L = L; a.T = T; a.c_begin = c_begin; a.c_end = c_end;
     a.part_d = part_d; a.part_seq = part_seq; a.part_slot = part_slot; a.out_d = out_d; a.out_labels = out_labels;

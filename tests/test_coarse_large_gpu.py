@@ -122,3 +122,42 @@ def test_adjacent_columns_both_among_the_nearest(exclude_self):
                 assert float(((ci[:, 0] ^ 1) == ci[:, 1]).float().mean()) > 0.9
     idx.stats()
     idx.close()
+
+
+def test_locality_ordered_centroid_table():
+    """A centroid file whose ids follow the geometry (hierarchical k-means output, a space-filling order): the nprobe
+    nearest centroids of a query are then ~nprobe CONSECUTIVE ids.  The tensor-core GEMM keeps a few values per group
+    of 128 columns, so its columns are a fixed low-discrepancy permutation of the ids (TcSide::idmul): neighbouring ids
+    never share a group and nothing overflows.  Worst case here: the centroids are a random WALK in id order."""
+    import torch
+    pkg = load_pkg()
+    dev = torch.device("cuda:0")
+    nc, d, nq = 1 << 18, 32, 300
+    g = torch.Generator(device=dev)
+    g.manual_seed(77)
+    # AR(1) walk in id order: centroid i+k is at squared distance ~2 (1 - rho^k) ||c||^2 from centroid i, so the 128
+    # nearest of a query sitting on centroid i are ids i-64 .. i+64, two fp16 margins apart from each other
+    from scipy.signal import lfilter
+    rho = 0.999
+    rng = np.random.default_rng(77)
+    walk = lfilter([np.sqrt(1 - rho * rho)], [1.0, -rho], rng.standard_normal((nc + 4096, d)), axis=0)[4096:]
+    C = torch.from_numpy(np.ascontiguousarray(walk, dtype=np.float32)).to(dev)
+    Q = C[torch.randint(0, nc, (nq,), device=dev, generator=g)] + 0.001 * torch.randn(nq, d, device=dev, generator=g)
+    dd = _brute(torch, Q, C, d)
+    for cls, nc_use in ((pkg.IndexIVF_HNSW, nc), (pkg.IndexIVF_HNSW, 100_000)):     # 100 000: not a power of two
+        Cu = C[:nc_use].contiguous()
+        idx = cls(d, nc_use, 8, 8)
+        idx.build_quantizer(centroids=Cu.cpu().numpy())
+        ddu = dd[:, :nc_use]
+        for impl in (2, 3):
+            idx.set_option("coarse_impl", impl)
+            for nprobe in (1, 128):
+                cd = torch.empty(nq, nprobe, device=dev)
+                ci = torch.empty(nq, nprobe, dtype=torch.int32, device=dev)
+                idx.coarse_dev(Q, nprobe, cd, ci)
+                idx.sync()                                   # raises on a select overflow flag
+                want = torch.sort(ddu, dim=1).values[:, :nprobe]
+                assert torch.allclose(torch.gather(ddu, 1, ci.long()), want, rtol=2e-5, atol=1e-4), (nc_use, impl, nprobe)
+                assert int((torch.sort(ci, dim=1).values.diff(dim=1) == 0).sum()) == 0
+        idx.stats()
+        idx.close()

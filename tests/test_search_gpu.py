@@ -264,11 +264,13 @@ def test_coarse_long_rows_vs_brute_force(nprobe, impl):
     idx.close()
 
 
+@pytest.mark.parametrize("W", [3, 24])
 @pytest.mark.parametrize("name", ["grp_sift_m16", "adc_sift_m16", "grp_long_m16"])
-def test_packed_records_sharded_search_equals_single_gpu(name):
+def test_packed_records_sharded_search_equals_single_gpu(name, W):
     """The all-to-all form of the sharded search on ONE GPU: records -> one packed stream per owning rank
     (pack_records_dev, checked word for word against the numpy statement tests/pack_ref.py), every 'rank' scans its
-    lists from its stream (scan_packed_dev), the merged answer equals the unsharded search bit for bit."""
+    lists from its stream (scan_packed_dev), the merged answer equals the unsharded search bit for bit.  With 24
+    'ranks' most (query, rank) pairs hold no probe at all: the scan's early exit for such queries."""
     import torch
     import pack_ref
     pkg = load_pkg()
@@ -282,7 +284,7 @@ def test_packed_records_sharded_search_equals_single_gpu(name):
     idx.max_codes, idx.do_pruning = mc, pr
     dev = torch.device("cuda:0")
     Q = torch.from_numpy(np.ascontiguousarray(g["Q"])).to(dev)
-    nq, W = Q.shape[0], 3
+    nq = Q.shape[0]
     D0 = torch.empty(nq, k, device=dev); L0 = torch.empty(nq, k, dtype=torch.int64, device=dev)
     idx.search_dev(k, Q, D0, L0)
     words = idx.tables_bytes() // 4
