@@ -502,6 +502,8 @@ def run_assign(args, w, torch, dev, dist, rank, world, local, log, emit):
     if dist is not None:
         dist.broadcast(cent, src=0)
     idx = P.IndexIVF_HNSW(w["d"], w["nc"], w["M"], 8, device=dev.index or 0)
+    if args.coarse_impl >= 0:
+        idx.set_option("coarse_impl", args.coarse_impl)
     idx.build_quantizer(centroids=cent.cpu().numpy())
     n = w["nb"]
     x = G.draw(n, 99991 + rank)
@@ -580,7 +582,7 @@ def run_assign(args, w, torch, dev, dist, rank, world, local, log, emit):
               "gpu_launches": launches,
               "roofline": {"kernel": "coarse_tc_kernel (K-A1 GEMM)", "bound": "tensor", "achieved": tf, "peak": tf_peak,
                            "unit": "TFLOP/s", "frac": tf / tf_peak, "ms": gemm_ms,
-                           "algorithmic": "2*nc*d FLOP per vector (the fp16 hi/lo split issues 3x that)", "traffic": None,
+                           "algorithmic": "2*nc*d FLOP per vector (coarse_impl 3 issues exactly that: ONE fp16 product, the dropped cross terms are covered by the select margin + exact fp32 re-rank)", "traffic": None,
                            "peak_source": "MEASURED_PEAKS.json" if peaks else "fallback"},
               "cpu_baseline": {"value": None, "unit": "vectors/s", "cores": len(os.sched_getaffinity(0)), "kind": "reference",
                                "sample": "not run: the reference's assign is an HNSW search whose graph over 2^20 centroids "
@@ -915,7 +917,7 @@ def main():
                              "traffic": traffic.get("group_g1b_kernel") if world == 1 else None},
         "coarse_tc_kernel": {"kernel": "coarse_tc_kernel (K-A2 GEMM)", "bound": "tensor", "achieved": coarse_tf,
                              "peak": tf_peak, "unit": "TFLOP/s", "frac": coarse_tf / tf_peak, "ms": gemm_ms,
-                             "algorithmic": "2*nc*d FLOP per query (one nominal pass; the fp16 hi/lo split issues 2x that)",
+                             "algorithmic": "2*nc*d FLOP per query (coarse_impl 3 issues exactly that: ONE fp16 product, the dropped cross terms are covered by the select margin + exact fp32 re-rank)",
                              "traffic": traffic.get("coarse_tc_kernel") if world == 1 else None},
     }
     # headline roofline: the larger (by live-measured time per step) of the two kernels whose roof is one of the two bound
