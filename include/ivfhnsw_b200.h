@@ -110,7 +110,8 @@ int ivfhnsw_b200_train_centroids(ivfhnsw_b200_t *h, size_t n, const float *x_dev
                                  double *objective_out, size_t *nsplit_out);
 
 /* -- indexing ---------------------------------------------------------------*/
-/* IndexIVF_HNSW::assign (IndexIVF_HNSW.cpp:68-72): exact nearest centroid (k must be 1) */
+/* IndexIVF_HNSW::assign (IndexIVF_HNSW.cpp:68-72): labels[i] = searchKnn(x_i, k).top() = the k-th nearest centroid,
+ * exact (k = 1 in every caller of the reference: the nearest; 1 <= k <= min(nc, 2048)) */
 int ivfhnsw_b200_assign(ivfhnsw_b200_t *h, size_t n, const float *x, uint32_t *labels, size_t k);
 /* same for device-resident vectors (asynchronous on the handle's stream; base vectors are NOT rotated: the OPQ
  * rotation applies to residuals, IndexIVF_HNSW.cpp:85-103) */

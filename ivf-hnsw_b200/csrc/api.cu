@@ -488,7 +488,26 @@ int ivfhnsw_b200_assign_dev(ivfhnsw_b200_t *h, size_t n, const float *x_dev, uin
 int ivfhnsw_b200_assign(ivfhnsw_b200_t *h, size_t n, const float *x, uint32_t *labels, size_t k)
 {
     if (bind(h)) return IVFHNSW_B200_ECUDA;
-    if (k != 1) return h->fail(IVFHNSW_B200_EINVAL, "assign: only k = 1 is supported (every caller of the reference uses 1)");
+    if (k == 0 || k > h->nc || k > 2048) return h->fail(IVFHNSW_B200_EINVAL, "assign: k = %zu out of range", k);
+    if (k > 1) {
+        // IndexIVF_HNSW.cpp:68-72 takes searchKnn(x, k).top(): the k-th nearest centroid.  Exact coarse search with
+        // nprobe = k, column k - 1 (every caller of the reference passes 1; kept for the interface)
+        const size_t chunk = 1 << 16;
+        const size_t cb = std::min(n, chunk);
+        CU(h->w_x.ensure(cb * h->d * 4));
+        CU(h->w_cd.ensure(cb * k * 4));
+        CU(h->w_ci.ensure(std::max<size_t>(cb * k * 4, h->w_ci.cap)));
+        for (size_t i0 = 0; i0 < n; i0 += chunk) {
+            const size_t nb = std::min(chunk, n - i0);
+            CU(cudaMemcpyAsync(h->w_x.p, x + i0 * h->d, nb * h->d * 4, cudaMemcpyHostToDevice, h->stream));
+            if (int r = ivfb200_coarse_dev(h, nb, h->w_x.as<float>(), k, 0, h->w_cd.as<float>(), h->w_ci.as<uint32_t>()))
+                return r;
+            CU(cudaMemcpy2DAsync(labels + i0, 4, h->w_ci.as<uint32_t>() + (k - 1), k * 4, 4, nb, cudaMemcpyDeviceToHost,
+                                 h->stream));
+            if (int r = check_coarse_flags(h)) return r;
+        }
+        return 0;
+    }
     const size_t chunk = 1 << 18;
     CU(h->w_x.ensure(std::min(n, chunk) * h->d * 4));
     CU(h->w_ci.ensure(std::max<size_t>(std::min(n, chunk) * 4, h->w_ci.cap)));

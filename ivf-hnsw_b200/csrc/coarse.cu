@@ -203,12 +203,24 @@ __global__ void __launch_bounds__(256) coarse_select_kernel(int nc, int d, int n
         // entry i = 4 * group + rank-in-group: a thread that strode by 256 would only ever see ONE rank (the threads
         // with tid % 4 == 3 only 4th-best values) and the minima would say nothing about the row; rotating the
         // assignment by one entry per pass gives every thread all four ranks (loads stay coalesced)
-        for (int j = 0; j * 256 < n; j++) {
-            const int i = j * 256 + ((tid + j) & 255);
-            if (i < n) {
-                const uint32_t kx = entry_key(i);
-                mk2 = min(mk2, max(mk, kx));
-                mk = min(mk, kx);
+        if (packed == 2) {
+            // integer-key records are 16 bytes with ascending keys: a thread's two smallest entries are among the first
+            // two keys of its records -- one 128-bit load and three min/max per record
+            const uint4 *rec4 = reinterpret_cast<const uint4 *>(gk);
+#pragma unroll 4
+            for (int g = tid; g < ngroups; g += 256) {
+                const uint4 r4 = rec4[g];
+                mk2 = min(mk2, min(max(mk, r4.x), r4.y));
+                mk = min(mk, r4.x);
+            }
+        } else {
+            for (int j = 0; j * 256 < n; j++) {
+                const int i = j * 256 + ((tid + j) & 255);
+                if (i < n) {
+                    const uint32_t kx = entry_key(i);
+                    mk2 = min(mk2, max(mk, kx));
+                    mk = min(mk, kx);
+                }
             }
         }
 #pragma unroll

@@ -384,8 +384,8 @@ void IndexIVF_HNSW::pull_quantizers()
 
 void IndexIVF_HNSW::assign(size_t n, const float *x, idx_t *labels, size_t k)
 {
-    // the reference returns the k-th nearest for k > 1 (top of a k-element max-heap, IndexIVF_HNSW.cpp:71); every
-    // caller passes k = 1 and so does the C ABI, which rejects anything else with EINVAL
+    // the reference returns the k-th nearest for k > 1 (top of a k-element max-heap, IndexIVF_HNSW.cpp:71) and so does
+    // the C ABI; every caller passes k = 1
     ck(ivfhnsw_b200_assign(h_, n, x, labels, k), "assign");
 }
 

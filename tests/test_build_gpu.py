@@ -38,6 +38,12 @@ def test_assign_exact(port, name):
     if name.startswith("adc_sift"):   # byte input path
         lab8 = idx.assign(X.astype(np.uint8))
         assert np.array_equal(lab8, lab)
+    # k > 1: the k-th nearest (IndexIVF_HNSW.cpp:71 takes the top of a k-element max-heap)
+    lab3 = idx.assign(X[:500], k=3)
+    dd = l2(X[:500].astype(np.float64)[:, None, :], C[None, :, :]) if C.shape[0] <= 4096 else None
+    if dd is not None:
+        third = np.sort(dd, axis=1)[:, 2]
+        assert np.allclose(l2(X[:500].astype(np.float64), C[lab3]), third, rtol=1e-6, atol=1e-6)
     idx.close()
 
 
