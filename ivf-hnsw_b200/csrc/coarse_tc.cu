@@ -178,11 +178,7 @@ static __device__ __forceinline__ void mbar_wait(uint32_t bar, uint32_t parity)
             : "r"(bar), "r"(parity), "r"(20000u)
             : "memory");
         if (done) break;
-        if (spins > (1u << 22)) {
-            printf("ivfhnsw_b200 coarse_tc_kernel: mbarrier 0x%x (parity %u) never completed in block %d thread %d -- "
-                   "pipeline protocol error, aborting the launch\n", bar, parity, (int)blockIdx.x, (int)threadIdx.x);
-            __trap();
-        }
+        if (spins > (1u << 22)) __trap();
     }
 }
 // one lane of a converged warp (the others get false)

@@ -83,9 +83,19 @@ static __device__ __forceinline__ float l2sqr16_octet(const float *__restrict__ 
 {
     const int n = (d >> 4) << 4;
     float acc = 0.f;
-    for (int i = sub; i < n; i += 8) {
-        const float df = x[i] - y[i];
-        acc = __fadd_rn(acc, __fmul_rn(df, df));   // unfused, like the pinned C restatement
+    // 16 loads of the (random, usually HBM-resident) row are issued before the first use: the row gather of the
+    // coarse re-rank is bound by latency, not by arithmetic (56 % of coarse_select_kernel's stall samples at 2^20 centroids)
+    for (int i0 = sub; i0 < n; i0 += 128) {
+        float yv[16];
+#pragma unroll
+        for (int u = 0; u < 16; u++) yv[u] = (i0 + 8 * u < n) ? __ldg(y + i0 + 8 * u) : 0.f;
+#pragma unroll
+        for (int u = 0; u < 16; u++) {
+            if (i0 + 8 * u < n) {
+                const float df = x[i0 + 8 * u] - yv[u];
+                acc = __fadd_rn(acc, __fmul_rn(df, df));   // unfused, like the pinned C restatement
+            }
+        }
     }
     const uint32_t lane = lane_id();
     const int base = lane & ~7;
