@@ -985,7 +985,8 @@ def main():
             workdir = reference_workdir(idx, w, cent_h, log)
             sample = args.cpu_sample or min(ngt, max(ncores * 40, 400))
             qh_np = queries.cpu().numpy()
-            res = run_reference_cpu(w, workdir, qh_np, gt0.cpu().numpy(), sample, ncores, log=log)
+            # one untimed pass first: the forked workers touch the index pages (25 GB at C4) for the first time in it
+            res = run_reference_cpu(w, workdir, qh_np, gt0.cpu().numpy(), sample, ncores, steps=3, warmup=1, log=log)
             ref_recall = res["recall"]
             cpu_baseline = {"value": res["qps"], "unit": "queries/s", "cores": ncores, "kind": "reference",
                             "sample": "%d queries of the same batch; %d single-thread processes (forked after one read()) "

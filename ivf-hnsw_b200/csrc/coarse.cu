@@ -539,7 +539,6 @@ cudaError_t launch_coarse(cudaStream_t st, uint64_t *launches, int impl, int nq,
     // ALU pipe bounds that kernel); the select stage scores the other column of each surviving pair exactly
     int pre = (impl >= 3 && ngroups >= 2048 && kept <= 3) ? 2 : 1;
     if (const char *e3 = getenv("IVFHNSW_B200_COARSE_PRE")) pre = (impl >= 3 && kept <= 3 && atoi(e3) == 2) ? 2 : 1;   // profiling switch
-    const int pcap = pre == 2 ? 1024 : 0;
     cudaError_t e;
     if (impl >= 1) {
         e = launch_coarse_tc(st, launches, nq, nc, d, queries, S.cnp, S, W.grp_val, impl >= 2 ? 1 : 2, kept,
@@ -566,6 +565,9 @@ cudaError_t launch_coarse(cudaStream_t st, uint64_t *launches, int impl, int nq,
     if (kprime > avail) kprime = avail;
     if (kprime > nrec * (gshift ? COARSE_T : kept)) kprime = nrec * (gshift ? COARSE_T : kept);
     if (kprime < 1) kprime = 1;
+    // partner columns of the pair prefilter: one per candidate outside the expanded groups (candidates: kprime, plus the
+    // overshoot of the sampled threshold and the margin band)
+    const int pcap = pre == 2 ? kprime + 64 + 512 : 0;
     const size_t sm2 = (size_t)d * 4 + (size_t)W.cand_cap * 8 + (size_t)pcap * 4;
     if (nrec * COARSE_T <= 256 * 8) {
         e = cudaFuncSetAttribute(coarse_select_kernel<8>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sm2);
