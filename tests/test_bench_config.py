@@ -43,3 +43,36 @@ def test_cache_key_depends_on_workload_and_is_stable():
     a = bench.cache_key(bench.WORKLOADS["c4"])
     assert a == bench.cache_key(dict(bench.WORKLOADS["c4"])) and a != bench.cache_key(bench.WORKLOADS["c4s"])
     assert len(bench.csrc_hash()) == 40
+
+
+def test_generator_is_deterministic_and_ground_truth_is_exact():
+    """The synthetic base set is re-drawn batch by batch from seeds (pass 1 / pass 2 of the build, every rank of a
+    multi-GPU run): the same (n, seed) must give the same batch; SIFT-shape data is byte-valued, which is what makes
+    the harness's TF32/fp32 brute force for the recall figure exact; the streaming ground-truth update equals a float64
+    brute force."""
+    import numpy as np
+    import torch
+    sys.path.insert(0, ROOT)
+    bench = importlib.import_module("bench")
+    w = dict(bench.WORKLOADS["c4s"])
+    dev = torch.device("cpu")
+    G = bench.Gen(w, torch, dev)
+    a, b = G.draw(3000, 99991), G.draw(3000, 99991)
+    assert torch.equal(a, b) and not torch.equal(a, G.draw(3000, 99992))
+    assert a.dtype == torch.float32 and a.shape == (3000, w["d"])
+    assert float(a.min()) >= 0 and float(a.max()) <= 255 and torch.equal(a, a.round())       # byte-valued
+    G2 = bench.Gen(w, torch, dev)                      # another process / rank
+    assert torch.equal(a, G2.draw(3000, 99991))
+    q = G.draw(40, 1235)
+    qn = (q * q).sum(1)
+    best_d = torch.full((40,), float("inf"))
+    best_i = torch.zeros(40, dtype=torch.long)
+    chunks = [(0, 3000, 99991), (3000, 2500, 99992 + 3000)]
+    allx = []
+    for b0, n, seed in chunks:
+        x = G.draw(n, seed)
+        allx.append(x)
+        bench._gt_update(torch, w, q, qn, x, b0, best_d, best_i)
+    X = torch.cat(allx).double()
+    dd = ((q.double()[:, None, :] - X[None, :, :]) ** 2).sum(-1)
+    assert np.array_equal(best_i.numpy(), dd.argmin(1).numpy())
