@@ -216,7 +216,9 @@ def load_cache(cdir, w, torch, dev, log):
     cls = P.IndexIVF_HNSW_Grouping if w["nsubc"] else P.IndexIVF_HNSW
     args = (w["d"], w["nc"], w["M"], 8) + ((w["nsubc"],) if w["nsubc"] else ())
     idx = cls(*args, device=dev.index or 0)
-    ld = lambda n: np.load(os.path.join(cdir, n))
+    # memory-mapped: the cache lives in tmpfs, so the arrays are used in place -- N ranks loading a 25 GB index must not
+    # each copy it into their own address space (8 x 21 GB + the tmpfs itself would not fit the host)
+    ld = lambda n: np.load(os.path.join(cdir, n), mmap_mode="r")
     cent_h = ld("cent.npy")
     idx.build_quantizer(centroids=cent_h)
     opq = ld("opq.npy") if os.path.exists(os.path.join(cdir, "opq.npy")) else None
@@ -227,8 +229,8 @@ def load_cache(cdir, w, torch, dev, log):
     if w["opq"]:
         idx.rotate_quantizer()
     idx.nprobe, idx.max_codes, idx.do_pruning = w["nprobe"], w["max_codes"], w["pruning"]
-    queries = torch.from_numpy(ld("queries.npy")).to(dev)
-    gt0 = torch.from_numpy(ld("gt0.npy")).to(dev)
+    queries = torch.from_numpy(np.array(ld("queries.npy"))).to(dev)
+    gt0 = torch.from_numpy(np.array(ld("gt0.npy"))).to(dev)
     log("index loaded from cache %s (ntotal %d)" % (cdir, idx.ntotal))
     return idx, queries, gt0, cent_h
 

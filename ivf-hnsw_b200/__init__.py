@@ -395,6 +395,7 @@ class IndexIVF_HNSW:
         self._keep = (off, ids, codes, ncodes, nn, ss, al, icd)
         self._ck(self._L.ivfhnsw_b200_load_lists(self._h, off.ctypes.data, ids.ctypes.data, codes.ctypes.data,
                                                  ncodes.ctypes.data, _ptr(nn), _ptr(ss), _ptr(al), _ptr(icd)))
+        self._keep = None       # load_lists returns after its copies have completed: the host arrays are free again
         if "centroid_norms" in ix:
             cn = _np(ix["centroid_norms"], np.float32)
             self._ck(self._L.ivfhnsw_b200_set_centroid_norms(self._h, cn.ctypes.data))
