@@ -34,58 +34,64 @@ public:
     void reset() { start_ = std::chrono::steady_clock::now(); }
 };
 
-template <typename T> void read_variable(std::istream &in, T &pod) { in.read(reinterpret_cast<char *>(&pod), sizeof(T)); }
-template <typename T> void write_variable(std::ostream &out, const T &pod) { out.write(reinterpret_cast<const char *>(&pod), sizeof(T)); }
-
-// uint32 element count followed by the elements (reference utils.h:45-62)
-template <typename T> void read_vector(std::istream &in, std::vector<T> &vec)
+namespace detail {
+// raw byte transfers of the xvecs / index streams
+inline void get_bytes(std::istream &s, void *dst, size_t nbytes) { s.read(static_cast<char *>(dst), (std::streamsize)nbytes); }
+inline void put_bytes(std::ostream &s, const void *src, size_t nbytes) { s.write(static_cast<const char *>(src), (std::streamsize)nbytes); }
+// the uint32 dimension word in front of every xvecs record; a mismatch ends the program like the reference does
+inline void expect_dim(std::istream &s, size_t want)
 {
-    uint32_t size = 0;
-    in.read(reinterpret_cast<char *>(&size), sizeof(uint32_t));
-    vec.resize(size);
-    if (size) in.read(reinterpret_cast<char *>(vec.data()), (std::streamsize)size * sizeof(T));
-}
-template <typename T> void write_vector(std::ostream &out, std::vector<T> &vec)
-{
-    const uint32_t size = (uint32_t)vec.size();
-    out.write(reinterpret_cast<const char *>(&size), sizeof(uint32_t));
-    if (size) out.write(reinterpret_cast<const char *>(vec.data()), (std::streamsize)size * sizeof(T));
-}
-
-// n records of [uint32 dim][dim x T]; a record whose dim differs from d aborts (reference utils.h:64-75,91-94)
-template <typename T> void readXvec(std::ifstream &in, T *data, const size_t d, const size_t n = 1)
-{
-    for (size_t i = 0; i < n; i++) {
-        uint32_t dim = 0;
-        in.read(reinterpret_cast<char *>(&dim), sizeof(uint32_t));
-        if (dim != d) {
-            std::cout << "file error\n";
-            exit(1);
-        }
-        in.read(reinterpret_cast<char *>(data + i * d), (std::streamsize)(d * sizeof(T)));
+    uint32_t got = 0;
+    get_bytes(s, &got, sizeof got);
+    if (got != want) {
+        std::cout << "file error\n";
+        exit(1);
     }
 }
-template <typename T> void writeXvec(std::ofstream &out, T *data, const size_t d, const size_t n = 1)
+}  // namespace detail
+
+template <class P> void read_variable(std::istream &s, P &value) { detail::get_bytes(s, &value, sizeof(P)); }
+template <class P> void write_variable(std::ostream &s, const P &value) { detail::put_bytes(s, &value, sizeof(P)); }
+
+// uint32 element count followed by the elements (reference utils.h:45-62)
+template <class E> void read_vector(std::istream &s, std::vector<E> &v)
 {
-    const uint32_t dim = (uint32_t)d;
-    for (size_t i = 0; i < n; i++) {
-        out.write(reinterpret_cast<const char *>(&dim), sizeof(uint32_t));
-        out.write(reinterpret_cast<const char *>(data + i * d), (std::streamsize)(d * sizeof(T)));
+    uint32_t count = 0;
+    detail::get_bytes(s, &count, sizeof count);
+    v.resize(count);
+    if (count) detail::get_bytes(s, v.data(), (size_t)count * sizeof(E));
+}
+template <class E> void write_vector(std::ostream &s, std::vector<E> &v)
+{
+    const uint32_t count = (uint32_t)v.size();
+    detail::put_bytes(s, &count, sizeof count);
+    if (count) detail::put_bytes(s, v.data(), (size_t)count * sizeof(E));
+}
+
+// nrec records of [uint32 dim][dim x E]; a record whose dim differs from dim aborts (reference utils.h:64-75,91-94)
+template <class E> void readXvec(std::ifstream &s, E *rows, const size_t dim, const size_t nrec = 1)
+{
+    for (size_t r = 0; r < nrec; r++) {
+        detail::expect_dim(s, dim);
+        detail::get_bytes(s, rows + r * dim, dim * sizeof(E));
+    }
+}
+template <class E> void writeXvec(std::ofstream &s, E *rows, const size_t dim, const size_t nrec = 1)
+{
+    const uint32_t word = (uint32_t)dim;
+    for (size_t r = 0; r < nrec; r++) {
+        detail::put_bytes(s, &word, sizeof word);
+        detail::put_bytes(s, rows + r * dim, dim * sizeof(E));
     }
 }
 // like readXvec but widens every component to float (reference utils.h:86-100)
-template <typename T> void readXvecFvec(std::ifstream &in, float *data, const size_t d, const size_t n = 1)
+template <class E> void readXvecFvec(std::ifstream &s, float *rows, const size_t dim, const size_t nrec = 1)
 {
-    std::vector<T> row(d);
-    for (size_t i = 0; i < n; i++) {
-        uint32_t dim = 0;
-        in.read(reinterpret_cast<char *>(&dim), sizeof(uint32_t));
-        if (dim != d) {
-            std::cout << "file error\n";
-            exit(1);
-        }
-        in.read(reinterpret_cast<char *>(row.data()), (std::streamsize)(d * sizeof(T)));
-        for (size_t j = 0; j < d; j++) data[i * d + j] = (float)row[j];
+    std::vector<E> one(dim);
+    for (size_t r = 0; r < nrec; r++) {
+        detail::expect_dim(s, dim);
+        detail::get_bytes(s, one.data(), dim * sizeof(E));
+        for (size_t c = 0; c < dim; c++) rows[r * dim + c] = (float)one[c];
     }
 }
 
